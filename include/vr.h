@@ -1,0 +1,237 @@
+/*
+ * vr.h -- C ABI of the B200-native ray-march backend (libvr_b200.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of TomBeacock/volumetric-renderer:
+ * the offscreen ray-march pass.  The reference has no FFI layer; the seam is the public
+ * C++ surface of Vol::Rendering::OffscreenPass (src/rendering/offscreen_pass.h:39-54)
+ * plus the camera it pulls through the application singleton
+ * (src/rendering/offscreen_pass.cpp:1152-1171).  Every entry point below names the
+ * reference member it replaces.  Paths are relative to the reference checkout.
+ *
+ * Conventions
+ *   - plain C types only; no C++/torch/CUDA types in any signature (a CUDA stream is
+ *     passed as void*, NULL = the context's own stream);
+ *   - every function returns a vr_status (0 = ok); no exception crosses the ABI.  The
+ *     reference throws std::runtime_error on any failure (e.g. offscreen_pass.cpp:309-313);
+ *     here the message is kept per context and read with vr_last_error();
+ *   - a context is bound to one CUDA device and is not thread-safe (the reference is
+ *     single-threaded, src/application.cpp:59-95);
+ *   - matrices are column-major float[16] in glm's memory layout;
+ *   - there is NO CPU fallback: creating a context without a usable CUDA device fails.
+ */
+#ifndef VR_H
+#define VR_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VR_ABI_VERSION 1
+
+typedef enum vr_status {
+    VR_OK = 0,
+    VR_ERR_INVALID = 1,  /* bad argument */
+    VR_ERR_CUDA = 2,     /* a CUDA runtime call failed (message in vr_last_error) */
+    VR_ERR_IO = 3,       /* file could not be read */
+    VR_ERR_FORMAT = 4,   /* file parsed but is not a supported 3-D scalar NRRD */
+    VR_ERR_NOMEM = 5,
+    VR_ERR_STATE = 6     /* call not valid in the current state */
+} vr_status;
+
+/* Device storage type of the volume.  The reference widens every NRRD type to float on
+ * the host (src/data/nrrd_file_parser.cpp:49-77) and uploads VK_FORMAT_R32_SFLOAT
+ * (offscreen_pass.cpp:943,:968); this backend keeps u8/u16 native and converts on fetch
+ * (the values seen by the march are the same floats). */
+typedef enum vr_dtype { VR_U8 = 0, VR_U16 = 1, VR_F32 = 2 } vr_dtype;
+
+/* How the density is fetched (res/shaders/volume.frag:41 `texture(u_volume, ray_pos)`). */
+typedef enum vr_sampler {
+    VR_SAMPLER_HW = 0,    /* one hardware-filtered trilinear fetch (9-bit fixed-point weights,
+                             as a GPU running the reference shader would do) -- default */
+    VR_SAMPLER_EXACT = 1  /* eight point fetches + fp32 lerp, one rounding per operation:
+                             bit-exact with the CPU oracle; the verification mode */
+} vr_sampler;
+
+typedef struct vr_ctx vr_ctx;
+
+typedef struct vr_options {
+    int sampler;          /* vr_sampler */
+    int empty_skip;       /* 1: skip samples in cells whose transfer-function alpha is exactly 0 (result-identical) */
+    int early_term;       /* 1: stop a ray once its transmittance < early_term_eps */
+    float early_term_eps; /* default 1/1024: bounds the error of every channel by eps */
+    int collect_stats;    /* 1: count samples per frame (vr_get_stats) */
+    int write_raw;        /* 1: also keep the shader's float4 output (vr_get_raw) */
+} vr_options;
+
+typedef struct vr_stats {
+    uint64_t covered_pixels; /* pixels that received a fragment */
+    uint64_t n_ref;          /* loop iterations passing the bounds test of volume.frag:34-37 that this
+                                frame accounts for (exact only when early_term = 0) */
+    uint64_t n_inslice;      /* iterations that passed the slice test (volume.frag:39-40) and were visited */
+    uint64_t n_fetch;        /* volume fetches actually executed (after empty-space skipping) */
+} vr_stats;
+
+/* ---- lifetime ---------------------------------------------------------------------- */
+
+/* OffscreenPass::OffscreenPass(context, width, height) (offscreen_pass.cpp:112-134).
+ * Starts, like the reference, with a 1x1x1 zero volume (:118,:130) and a one-texel
+ * 0xFFFFFFFF transfer function (:119,:131), default camera, slices [0,1]^3. */
+int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **out);
+/* OffscreenPass::~OffscreenPass (offscreen_pass.cpp:136-161). */
+int vr_destroy(vr_ctx *ctx);
+/* Message of the last failed call on this context ("" if none).  ctx may be NULL for
+ * the message of a failed vr_create. */
+const char *vr_last_error(const vr_ctx *ctx);
+int vr_abi_version(void);
+
+/* ---- per-frame ----------------------------------------------------------------------- */
+
+/* OffscreenPass::record(command_buffer, frame_index) (offscreen_pass.cpp:163-230):
+ * clear to (0.11,0.11,0.11,1), draw the cube's front faces with volume.frag, blend,
+ * store RGBA8.  Asynchronous on `cuda_stream` like command recording; results are
+ * complete after the stream is synchronised (vr_sync / vr_download do that). */
+int vr_render(vr_ctx *ctx, void *cuda_stream);
+int vr_sync(vr_ctx *ctx);
+
+/* The uniform block the reference fills by pulling the camera inside record()
+ * (OffscreenPass::update_uniform_buffer, offscreen_pass.cpp:1152-1171): pull -> push. */
+int vr_set_camera(vr_ctx *ctx, const float view[16], const float proj[16], const float camera_position[3]);
+
+/* ---- mutators ------------------------------------------------------------------------ */
+
+/* OffscreenPass::framebuffer_size_changed(width, height) (offscreen_pass.cpp:232-255):
+ * a zero size is ignored (:237-239); otherwise synchronous re-creation of the target.
+ * The projection is NOT touched: the caller pushes a new one, as record() would. */
+int vr_resize(vr_ctx *ctx, uint32_t width, uint32_t height);
+
+/* OffscreenPass::volume_dataset_changed(dataset) (offscreen_pass.cpp:257-269).
+ * data: host pointer, x fastest, tightly packed (nrrd_file_parser.cpp:33); copied.
+ * min/max: the Dataset's min/max (offscreen_pass.cpp:265-266); pass NULL to have them
+ * computed on the device (replaces nrrd_file_parser.cpp:39-40).  Synchronous. */
+int vr_set_volume(vr_ctx *ctx, const void *data, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
+                  const float *min_density, const float *max_density);
+/* Same, `data` is a device pointer on the context's device (x fastest, tightly packed). */
+int vr_set_volume_device(vr_ctx *ctx, const void *dev_data, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
+                         const float *min_density, const float *max_density);
+/* Importer::import -> NrrdFileParser::parse -> volume_dataset_changed
+ * (src/data/importer.cpp:36-46, src/data/nrrd_file_parser.cpp:21-47) in one call with a
+ * native reader: 3-D scalar NRRD/NHDR, raw/ascii/hex encoding, any of the ten scalar
+ * types (u8/u16 stay native on the device, the rest are widened to float like :49-77). */
+int vr_load_nrrd(vr_ctx *ctx, const char *path);
+int vr_get_volume_info(const vr_ctx *ctx, int *dtype, uint32_t dims[3], float *min_density, float *max_density);
+/* Overwrite ubo.min_density / max_density (offscreen_pass.cpp:265-266), e.g. with the global
+ * range after each sort-last rank measured its own sub-volume. */
+int vr_set_density_range(vr_ctx *ctx, float min_density, float max_density);
+
+/* OffscreenPass::slicing_changed(min, max) (offscreen_pass.cpp:271-277). */
+int vr_set_slicing(vr_ctx *ctx, const float min_slice[3], const float max_slice[3]);
+
+/* OffscreenPass::transfer_function_changed(data) (offscreen_pass.cpp:279-288): n >= 1
+ * texels packed R | G<<8 | B<<16 | A<<24, interpreted as VK_FORMAT_R8G8B8A8_SRGB (:1076). */
+int vr_set_transfer_function(vr_ctx *ctx, const uint32_t *rgba8_srgb, uint32_t n);
+
+/* The two shader literals ray_dist = 1.8, step_size = 0.005 (res/shaders/volume.frag:29-30)
+ * as parameters; steps = int(ray_dist / step_size) in fp32 (:31). */
+int vr_set_march(vr_ctx *ctx, float ray_dist, float step_size);
+
+int vr_get_options(const vr_ctx *ctx, vr_options *out);
+int vr_set_options(vr_ctx *ctx, const vr_options *opt);
+
+/* ---- outputs ------------------------------------------------------------------------- */
+
+/* OffscreenPass::get_image_view() / get_sampler() (offscreen_pass.h:53-54): the colour
+ * attachment, here a headless device buffer of height rows of width RGBA8 pixels, row 0
+ * at the top (Vulkan framebuffer orientation).  Re-created by vr_resize. */
+int vr_get_image(vr_ctx *ctx, void **dev_rgba8, size_t *pitch_bytes);
+/* Synchronise and copy the image to host memory (width*height*4 bytes). */
+int vr_download(vr_ctx *ctx, void *host_rgba8);
+/* Asynchronous copy on the stream used by the last vr_render (host should be pinned). */
+int vr_download_async(vr_ctx *ctx, void *host_rgba8, void *cuda_stream);
+/* The fragment shader's own output before the blend: float4 per pixel, premultiplied rgb
+ * and alpha = 1 - transmittance, (0,0,0,0) where no fragment.  Needs options.write_raw. */
+int vr_get_raw(vr_ctx *ctx, void **dev_rgba_f32);
+int vr_download_raw(vr_ctx *ctx, float *host_rgba_f32);
+int vr_get_stats(vr_ctx *ctx, vr_stats *out);
+int vr_get_size(const vr_ctx *ctx, uint32_t *width, uint32_t *height);
+/* Empty-space-skipping grid: cells per axis, voxels per cell edge, cells whose samples are all
+ * skipped under the current transfer function. */
+int vr_get_occupancy_info(vr_ctx *ctx, uint32_t cells[3], uint32_t *cell_voxels, uint64_t *empty_cells);
+
+/* ---- input surfaces kept from the app (host-side, no GPU needed) ---------------------- */
+
+/* Vol::Scene::Camera (src/scene/camera.h:9-23, camera.cpp:7-48). */
+typedef struct vr_camera vr_camera;
+vr_camera *vr_camera_new(void);
+void vr_camera_free(vr_camera *cam);
+void vr_camera_rotate(vr_camera *cam, float dx, float dy); /* Camera::rotate(vec2) */
+void vr_camera_zoom(vr_camera *cam, float delta);          /* Camera::zoom(float) */
+void vr_camera_get_position(const vr_camera *cam, float out[3]);
+void vr_camera_get_view(const vr_camera *cam, float out[16]);
+/* proj of update_uniform_buffer (offscreen_pass.cpp:1154-1168). */
+void vr_projection(uint32_t width, uint32_t height, float out[16]);
+/* update_uniform_buffer in one call: view/proj/position from `cam` at the context's size. */
+int vr_set_camera_orbit(vr_ctx *ctx, const vr_camera *cam);
+
+/* Gradient::discretize (src/ui/components/gradient.cpp:90-108,:471-485).
+ * color_markers: nc x {location, r, g, b}; alpha_markers: na x {location, a}; sorted. */
+int vr_gradient_discretize(const float *color_markers, uint32_t nc, const float *alpha_markers, uint32_t na,
+                           uint32_t count, uint32_t *out);
+
+/* ---- synthetic volumes (BASELINE.json configs), generated on the device ---------------- */
+
+typedef enum vr_synth_kind { VR_SYNTH_MARSCHNER_LOBB = 0, VR_SYNTH_FBM = 1, VR_SYNTH_BLOBS = 2 } vr_synth_kind;
+/* Generate the volume on the device and make it the context's volume (min/max computed on
+ * the device). */
+int vr_synth_volume(vr_ctx *ctx, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz);
+/* Copy the current volume back to the host (tests feed it to the CPU oracle). */
+int vr_download_volume(vr_ctx *ctx, void *host_out);
+
+/* ---- multi-GPU partitioning (new; the reference is single-GPU) -------------------------- */
+
+/* Sort-first: this context renders only the screen tiles t with t % nranks == rank
+ * (tiles of tile_px x tile_px in row-major order); other pixels are left untouched.
+ * nranks = 1 restores the whole frame. */
+int vr_set_partition_sort_first(vr_ctx *ctx, uint32_t rank, uint32_t nranks, uint32_t tile_px);
+
+/* Sort-last: this context holds voxels [org, org+n) (+ ghost layers) of a
+ * global grid `full` and accumulates only samples whose position lies in its half-open
+ * sub-box.  The volume passed to vr_set_volume* / vr_synth_volume afterwards is the
+ * sub-volume INCLUDING ghosts. */
+int vr_set_partition_sort_last(vr_ctx *ctx, const uint32_t full_dims[3], const uint32_t own_org[3],
+                               const uint32_t own_dims[3]);
+/* Generate this rank's sub-volume (+ ghosts) of the full synthetic grid on the device.  The
+ * density range is the LOCAL one: reduce it across ranks and call vr_set_density_range. */
+int vr_synth_subvolume(vr_ctx *ctx, int kind, uint32_t seed, int dtype);
+int vr_clear_partition(vr_ctx *ctx);
+
+/* K2: ordered `over` of nparts partial images (float4: premultiplied rgb, alpha = 1 - T)
+ * for pixels [pixel_begin, pixel_end) of the frame, front to back in the order given,
+ * fused with the display blend + RGBA8 store into this context's image.  parts[i] are
+ * device pointers readable from this context's device (local or NVLink peer memory),
+ * each pointing at that partial's pixel 0. */
+int vr_composite(vr_ctx *ctx, const void *const *parts, uint32_t nparts, uint64_t pixel_begin, uint64_t pixel_end,
+                 void *cuda_stream);
+/* Regular split of a grid into grid[0]*grid[1]*grid[2] sub-boxes: box `index` (x fastest)
+ * owns voxels [org, org+dims) with faces at floor(k * full / grid). */
+int vr_partition_box(const uint32_t grid[3], const uint32_t full_dims[3], uint32_t index, uint32_t org[3],
+                     uint32_t dims[3]);
+/* Front-to-back visiting order of those sub-boxes for a camera position (model space), valid
+ * for every pixel of the frame: out[k] = box index visited k-th. */
+int vr_partition_order(const uint32_t grid[3], const uint32_t full_dims[3], const float camera_position[3],
+                       uint32_t *out);
+
+/* ---- measurement ----------------------------------------------------------------------- */
+
+/* Texture-fetch roofline micro-benchmark: trilinear tex3D fetches of an L1-resident
+ * volume of `dtype` from all SMs; returns fetches per second (device-timed). */
+int vr_bench_tex_peak(int device, int dtype, int hw_filter, double *fetches_per_s);
+/* Test hook: the 16 floats (4 columns) of inverse(proj * view) the kernel uses. */
+int vr_debug_ray_context(const vr_ctx *ctx, float out[16]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VR_H */

@@ -1,0 +1,790 @@
+/*
+ * api.cu -- the C ABI of include/vr.h: the render context that stands where
+ * Vol::Rendering::OffscreenPass stands in the reference (src/rendering/offscreen_pass.{h,cpp}).
+ *
+ * The reference's pass owns Vulkan objects (colour/depth attachments, pipeline, descriptor
+ * sets, a 3-D image + sampler, a 1-D sRGB image + sampler, two uniform buffers); this context
+ * owns their CUDA equivalents: an RGBA8 device buffer, a 3-D CUDA array with two texture
+ * objects, the decoded LUT, the occupancy grid, and one stream.  Every mutator keeps the
+ * reference's semantics (synchronous, copy-in), every failure becomes a status + message.
+ */
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <new>
+#include <vector>
+
+#include "nrrd.h"
+#include "vr_ctx.h"
+
+namespace
+{
+thread_local std::string g_create_error;
+
+int fail(vr_ctx *c, int status, const std::string &msg)
+{
+    if (c) c->err = msg;
+    else g_create_error = msg;
+    return status;
+}
+
+int cuda_fail(vr_ctx *c, cudaError_t e, const char *what)
+{
+    return fail(c, VR_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+#define VR_CUDA(c, call)                                     \
+    do {                                                     \
+        cudaError_t e__ = (call);                            \
+        if (e__ != cudaSuccess) return cuda_fail(c, e__, #call); \
+    } while (0)
+
+size_t dtype_size(int dtype) { return dtype == VR_U8 ? 1 : (dtype == VR_U16 ? 2 : 4); }
+
+/* ---- S2 host part: inverse(proj * view) in double, rounded to fp32 -------------------- */
+
+void mat4_mul_d(const double *a, const double *b, double *out)
+{
+    for (int c = 0; c < 4; c++)
+        for (int r = 0; r < 4; r++) {
+            double s = 0.0;
+            for (int k = 0; k < 4; k++) s += a[k * 4 + r] * b[c * 4 + k];
+            out[c * 4 + r] = s;
+        }
+}
+
+/* 4x4 inverse through 2x2 sub-determinants (Laplace expansion by complementary minors) */
+bool mat4_inverse_d(const double *m, double *inv)
+{
+    const double a00 = m[0], a01 = m[1], a02 = m[2], a03 = m[3], a10 = m[4], a11 = m[5], a12 = m[6], a13 = m[7],
+                 a20 = m[8], a21 = m[9], a22 = m[10], a23 = m[11], a30 = m[12], a31 = m[13], a32 = m[14], a33 = m[15];
+    const double b00 = a00 * a11 - a01 * a10, b01 = a00 * a12 - a02 * a10, b02 = a00 * a13 - a03 * a10,
+                 b03 = a01 * a12 - a02 * a11, b04 = a01 * a13 - a03 * a11, b05 = a02 * a13 - a03 * a12,
+                 b06 = a20 * a31 - a21 * a30, b07 = a20 * a32 - a22 * a30, b08 = a20 * a33 - a23 * a30,
+                 b09 = a21 * a32 - a22 * a31, b10 = a21 * a33 - a23 * a31, b11 = a22 * a33 - a23 * a32;
+    const double det = b00 * b11 - b01 * b10 + b02 * b09 + b03 * b08 - b04 * b07 + b05 * b06;
+    if (det == 0.0 || !(det == det)) return false;
+    const double r = 1.0 / det;
+    inv[0] = (a11 * b11 - a12 * b10 + a13 * b09) * r;
+    inv[1] = (a02 * b10 - a01 * b11 - a03 * b09) * r;
+    inv[2] = (a31 * b05 - a32 * b04 + a33 * b03) * r;
+    inv[3] = (a22 * b04 - a21 * b05 - a23 * b03) * r;
+    inv[4] = (a12 * b08 - a10 * b11 - a13 * b07) * r;
+    inv[5] = (a00 * b11 - a02 * b08 + a03 * b07) * r;
+    inv[6] = (a32 * b02 - a30 * b05 - a33 * b01) * r;
+    inv[7] = (a20 * b05 - a22 * b02 + a23 * b01) * r;
+    inv[8] = (a10 * b10 - a11 * b08 + a13 * b06) * r;
+    inv[9] = (a01 * b08 - a00 * b10 - a03 * b06) * r;
+    inv[10] = (a30 * b04 - a31 * b02 + a33 * b00) * r;
+    inv[11] = (a21 * b02 - a20 * b04 - a23 * b00) * r;
+    inv[12] = (a11 * b07 - a10 * b09 - a12 * b06) * r;
+    inv[13] = (a00 * b09 - a01 * b07 + a02 * b06) * r;
+    inv[14] = (a31 * b01 - a30 * b03 - a32 * b00) * r;
+    inv[15] = (a20 * b03 - a21 * b01 + a22 * b00) * r;
+    return true;
+}
+
+bool update_ray_context(vr_ctx *c)
+{
+    double v[16], p[16], pv[16], inv[16];
+    for (int i = 0; i < 16; i++) v[i] = (double)c->view[i], p[i] = (double)c->proj[i];
+    mat4_mul_d(p, v, pv); /* gl_Position = proj * view * vec4(pos, 1): volume.vert:23 */
+    c->ray_valid = mat4_inverse_d(pv, inv);
+    if (!c->ray_valid) return false;
+    for (int col = 0; col < 4; col++)
+        for (int r = 0; r < 4; r++) c->rc[col][r] = (float)inv[col * 4 + r];
+    return true;
+}
+
+/* ---- S6 host part: VK_FORMAT_R8G8B8A8_SRGB decode, edge padding ------------------------ */
+
+float srgb8_to_linear(unsigned c8)
+{
+    const double c = (double)c8 / 255.0;
+    return (float)(c <= 0.04045 ? c / 12.92 : std::pow((c + 0.055) / 1.055, 2.4));
+}
+
+int upload_lut(vr_ctx *c)
+{
+    const uint32_t n = c->nlut;
+    std::vector<float4> L(n), P(n + 3), D(n + 2);
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t p = c->h_lut[i];
+        L[i] = make_float4(srgb8_to_linear(p & 0xff), srgb8_to_linear((p >> 8) & 0xff), srgb8_to_linear((p >> 16) & 0xff),
+                           (float)((p >> 24) & 0xff) / 255.0f);
+    }
+    for (uint32_t k = 0; k < n + 3; k++) {
+        long j = (long)k - 1;
+        j = j < 0 ? 0 : (j > (long)n - 1 ? (long)n - 1 : j);
+        P[k] = L[j];
+    }
+    for (uint32_t k = 0; k < n + 2; k++)
+        D[k] = make_float4(P[k + 1].x - P[k].x, P[k + 1].y - P[k].y, P[k + 1].z - P[k].z, P[k + 1].w - P[k].w);
+    if (c->d_lut_pad) cudaFree(c->d_lut_pad), c->d_lut_pad = nullptr;
+    if (c->d_lut_dif) cudaFree(c->d_lut_dif), c->d_lut_dif = nullptr;
+    VR_CUDA(c, cudaMalloc(&c->d_lut_pad, sizeof(float4) * (n + 3)));
+    VR_CUDA(c, cudaMalloc(&c->d_lut_dif, sizeof(float4) * (n + 2)));
+    VR_CUDA(c, cudaMemcpy(c->d_lut_pad, P.data(), sizeof(float4) * (n + 3), cudaMemcpyHostToDevice));
+    VR_CUDA(c, cudaMemcpy(c->d_lut_dif, D.data(), sizeof(float4) * (n + 2), cudaMemcpyHostToDevice));
+    c->occ_dirty = true;
+    return VR_OK;
+}
+
+void release_volume(vr_ctx *c)
+{
+    if (c->tex_lin) cudaDestroyTextureObject(c->tex_lin), c->tex_lin = 0;
+    if (c->tex_pt) cudaDestroyTextureObject(c->tex_pt), c->tex_pt = 0;
+    if (c->array) cudaFreeArray(c->array), c->array = nullptr;
+    if (c->d_cell_range) cudaFree(c->d_cell_range), c->d_cell_range = nullptr;
+    if (c->d_occ) cudaFree(c->d_occ), c->d_occ = nullptr;
+}
+
+int alloc_target(vr_ctx *c, uint32_t w, uint32_t h)
+{
+    if (c->d_image) cudaFree(c->d_image), c->d_image = nullptr;
+    if (c->d_raw) cudaFree(c->d_raw), c->d_raw = nullptr;
+    c->W = w, c->H = h;
+    VR_CUDA(c, cudaMalloc(&c->d_image, (size_t)w * h * sizeof(uchar4)));
+    VR_CUDA(c, cudaMemset(c->d_image, 0, (size_t)w * h * sizeof(uchar4)));
+    if (c->opt.write_raw) {
+        VR_CUDA(c, cudaMalloc(&c->d_raw, (size_t)w * h * sizeof(float4)));
+        VR_CUDA(c, cudaMemset(c->d_raw, 0, (size_t)w * h * sizeof(float4)));
+    }
+    return VR_OK;
+}
+
+/* Make `dev` (linear, x fastest, local extent) the context's volume. */
+int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, const float *mn,
+                   const float *mx)
+{
+    release_volume(c);
+    c->dtype = dtype, c->nx = nx, c->ny = ny, c->nz = nz;
+    cudaChannelFormatDesc cd = dtype == VR_U8    ? cudaCreateChannelDesc<unsigned char>()
+                               : dtype == VR_U16 ? cudaCreateChannelDesc<unsigned short>()
+                                                 : cudaCreateChannelDesc<float>();
+    VR_CUDA(c, cudaMalloc3DArray(&c->array, &cd, make_cudaExtent(nx, ny, nz)));
+    cudaMemcpy3DParms cp = {};
+    cp.srcPtr = make_cudaPitchedPtr(const_cast<void *>(dev), (size_t)nx * dtype_size(dtype), nx, ny);
+    cp.dstArray = c->array;
+    cp.extent = make_cudaExtent(nx, ny, nz);
+    cp.kind = cudaMemcpyDeviceToDevice;
+    VR_CUDA(c, cudaMemcpy3DAsync(&cp, c->stream));
+
+    cudaResourceDesc rd = {};
+    rd.resType = cudaResourceTypeArray;
+    rd.res.array.array = c->array;
+    /* offscreen_pass.cpp:1016-1032: LINEAR, CLAMP_TO_BORDER, FLOAT_TRANSPARENT_BLACK, normalised */
+    cudaTextureDesc td = {};
+    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeBorder;
+    td.filterMode = cudaFilterModeLinear;
+    td.readMode = dtype == VR_F32 ? cudaReadModeElementType : cudaReadModeNormalizedFloat;
+    td.normalizedCoords = 1;
+    VR_CUDA(c, cudaCreateTextureObject(&c->tex_lin, &rd, &td, nullptr));
+    cudaTextureDesc tp = {};
+    tp.addressMode[0] = tp.addressMode[1] = tp.addressMode[2] = cudaAddressModeBorder;
+    tp.filterMode = cudaFilterModePoint;
+    tp.readMode = cudaReadModeElementType;
+    tp.normalizedCoords = 0;
+    VR_CUDA(c, cudaCreateTextureObject(&c->tex_pt, &rd, &tp, nullptr));
+
+    /* ubo.min_density / max_density = dataset.min / max (offscreen_pass.cpp:265-266) */
+    if (mn && mx) {
+        c->min_density = *mn, c->max_density = *mx;
+    } else {
+        float a = 0.f, b = 0.f;
+        VR_CUDA(c, vr_k0_global_minmax(dev, dtype, (size_t)nx * ny * nz, &a, &b, c->stream));
+        c->min_density = mn ? *mn : a;
+        c->max_density = mx ? *mx : b;
+    }
+
+    /* occupancy grid: power-of-two cells, at most 64 per axis */
+    uint32_t maxdim = nx > ny ? nx : ny;
+    maxdim = maxdim > nz ? maxdim : nz;
+    int cell = 4;
+    while ((maxdim + cell - 1) / cell > VR_OCC_MAX_AXIS) cell *= 2;
+    c->occ_cell = cell;
+    c->occ_n[0] = (int)((nx + cell - 1) / cell), c->occ_n[1] = (int)((ny + cell - 1) / cell),
+    c->occ_n[2] = (int)((nz + cell - 1) / cell);
+    const int ncells = c->occ_n[0] * c->occ_n[1] * c->occ_n[2];
+    c->occ_words = (ncells + 31) / 32;
+    VR_CUDA(c, cudaMalloc(&c->d_cell_range, sizeof(float2) * ncells));
+    VR_CUDA(c, cudaMalloc(&c->d_occ, sizeof(uint32_t) * c->occ_words));
+    VR_CUDA(c, vr_k0_cell_ranges(dev, dtype, nx, ny, nz, cell, c->occ_n, c->d_cell_range, c->stream));
+    c->occ_dirty = true;
+    VR_CUDA(c, cudaStreamSynchronize(c->stream)); /* the reference's upload is synchronous too */
+    return VR_OK;
+}
+
+int default_state(vr_ctx *c)
+{
+    /* offscreen_pass.cpp:118-119,:130-131: 1x1x1 zero volume, one white opaque LUT texel */
+    float *d0 = nullptr;
+    VR_CUDA(c, cudaMalloc(&d0, sizeof(float)));
+    VR_CUDA(c, cudaMemset(d0, 0, sizeof(float)));
+    const float zero = 0.0f;
+    int rc = install_volume(c, d0, VR_F32, 1, 1, 1, &zero, &zero);
+    cudaFree(d0);
+    if (rc != VR_OK) return rc;
+    c->nlut = 1;
+    c->h_lut = (uint32_t *)std::malloc(sizeof(uint32_t));
+    if (!c->h_lut) return fail(c, VR_ERR_NOMEM, "out of host memory");
+    c->h_lut[0] = 0xFFFFFFFFu;
+    rc = upload_lut(c);
+    if (rc != VR_OK) return rc;
+    vr_camera *cam = vr_camera_new();
+    if (!cam) return fail(c, VR_ERR_NOMEM, "out of host memory");
+    vr_camera_get_view(cam, c->view);
+    vr_camera_get_position(cam, c->cam_pos);
+    vr_camera_free(cam);
+    vr_projection(c->W, c->H, c->proj);
+    update_ray_context(c);
+    return VR_OK;
+}
+}  // namespace
+
+/* =============================================================== lifetime == */
+
+extern "C" int vr_abi_version(void) { return VR_ABI_VERSION; }
+
+extern "C" const char *vr_last_error(const vr_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **out)
+{
+    if (!out || width == 0 || height == 0) return fail(nullptr, VR_ERR_INVALID, "vr_create: bad arguments");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, VR_ERR_CUDA,
+                    std::string("vr_create: no CUDA device (this backend has no CPU fallback): ") +
+                        (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+    if (device < 0 || device >= ndev) return fail(nullptr, VR_ERR_INVALID, "vr_create: device index out of range");
+    vr_ctx *c = new (std::nothrow) vr_ctx;
+    if (!c) return fail(nullptr, VR_ERR_NOMEM, "out of host memory");
+    c->device = device;
+    c->opt.sampler = VR_SAMPLER_HW;
+    c->opt.empty_skip = 1;
+    c->opt.early_term = 0;
+    c->opt.early_term_eps = 1.0f / 1024.0f;
+    c->opt.collect_stats = 0;
+    c->opt.write_raw = 0;
+    int rc = VR_OK;
+    do {
+        if ((e = cudaSetDevice(device)) != cudaSuccess) { rc = cuda_fail(c, e, "cudaSetDevice"); break; }
+        if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(c, e, "cudaStreamCreate"); break; }
+        if ((e = cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(c, e, "cudaMalloc"); break; }
+        if ((e = cudaMallocHost(&c->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(c, e, "cudaMallocHost"); break; }
+        std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
+        if ((rc = alloc_target(c, width, height)) != VR_OK) break;
+        if ((rc = default_state(c)) != VR_OK) break;
+    } while (0);
+    if (rc != VR_OK) {
+        g_create_error = c->err;
+        vr_destroy(c);
+        return rc;
+    }
+    c->last_stream = c->stream;
+    *out = c;
+    return VR_OK;
+}
+
+extern "C" int vr_destroy(vr_ctx *c)
+{
+    if (!c) return VR_OK;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream); /* vkDeviceWaitIdle, offscreen_pass.cpp:138 */
+    release_volume(c);
+    if (c->d_lut_pad) cudaFree(c->d_lut_pad);
+    if (c->d_lut_dif) cudaFree(c->d_lut_dif);
+    if (c->d_image) cudaFree(c->d_image);
+    if (c->d_raw) cudaFree(c->d_raw);
+    if (c->d_counters) cudaFree(c->d_counters);
+    if (c->h_counters) cudaFreeHost(c->h_counters);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    std::free(c->h_lut);
+    delete c;
+    return VR_OK;
+}
+
+/* =============================================================== mutators == */
+
+extern "C" int vr_set_camera(vr_ctx *c, const float view[16], const float proj[16], const float camera_position[3])
+{
+    if (!c || !view || !proj || !camera_position) return fail(c, VR_ERR_INVALID, "vr_set_camera: null argument");
+    std::memcpy(c->view, view, sizeof(c->view));
+    std::memcpy(c->proj, proj, sizeof(c->proj));
+    std::memcpy(c->cam_pos, camera_position, sizeof(c->cam_pos));
+    if (!update_ray_context(c)) return fail(c, VR_ERR_INVALID, "vr_set_camera: proj * view is singular");
+    return VR_OK;
+}
+
+extern "C" int vr_set_camera_orbit(vr_ctx *c, const vr_camera *cam)
+{
+    if (!c || !cam) return fail(c, VR_ERR_INVALID, "vr_set_camera_orbit: null argument");
+    float view[16], proj[16], pos[3];
+    vr_camera_get_view(cam, view);
+    vr_projection(c->W, c->H, proj);
+    vr_camera_get_position(cam, pos);
+    return vr_set_camera(c, view, proj, pos);
+}
+
+extern "C" int vr_resize(vr_ctx *c, uint32_t width, uint32_t height)
+{
+    if (!c) return VR_ERR_INVALID;
+    if (width == 0 || height == 0) return VR_OK; /* offscreen_pass.cpp:237-239 */
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream)); /* vkDeviceWaitIdle, :241 */
+    return alloc_target(c, width, height);
+}
+
+extern "C" int vr_set_volume_device(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
+                                    const float *mn, const float *mx)
+{
+    if (!c || !dev || dtype < VR_U8 || dtype > VR_F32 || nx == 0 || ny == 0 || nz == 0)
+        return fail(c, VR_ERR_INVALID, "vr_set_volume: bad arguments");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    return install_volume(c, dev, dtype, nx, ny, nz, mn, mx);
+}
+
+extern "C" int vr_set_volume(vr_ctx *c, const void *data, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
+                             const float *mn, const float *mx)
+{
+    if (!c || !data || dtype < VR_U8 || dtype > VR_F32 || nx == 0 || ny == 0 || nz == 0)
+        return fail(c, VR_ERR_INVALID, "vr_set_volume: bad arguments");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    const size_t bytes = (size_t)nx * ny * nz * dtype_size(dtype);
+    void *stage = nullptr;
+    VR_CUDA(c, cudaMalloc(&stage, bytes));
+    cudaError_t e = cudaMemcpy(stage, data, bytes, cudaMemcpyHostToDevice); /* staging copy, offscreen_pass.cpp:955-959 */
+    if (e != cudaSuccess) {
+        cudaFree(stage);
+        return cuda_fail(c, e, "cudaMemcpy(volume)");
+    }
+    const int rc = install_volume(c, stage, dtype, nx, ny, nz, mn, mx);
+    cudaFree(stage);
+    return rc;
+}
+
+extern "C" int vr_load_nrrd(vr_ctx *c, const char *path)
+{
+    if (!c || !path) return fail(c, VR_ERR_INVALID, "vr_load_nrrd: null argument");
+    VrNrrd n;
+    std::string err;
+    const int rc = vr_nrrd_read(path, n, err);
+    if (rc != VR_OK) return fail(c, rc, err);
+    return vr_set_volume(c, n.bytes.data(), n.dtype, n.dims[0], n.dims[1], n.dims[2], nullptr, nullptr);
+}
+
+extern "C" int vr_get_volume_info(const vr_ctx *c, int *dtype, uint32_t dims[3], float *mn, float *mx)
+{
+    if (!c) return VR_ERR_INVALID;
+    if (dtype) *dtype = c->dtype;
+    if (dims) dims[0] = c->nx, dims[1] = c->ny, dims[2] = c->nz;
+    if (mn) *mn = c->min_density;
+    if (mx) *mx = c->max_density;
+    return VR_OK;
+}
+
+extern "C" int vr_set_density_range(vr_ctx *c, float mn, float mx)
+{
+    if (!c) return VR_ERR_INVALID;
+    c->min_density = mn, c->max_density = mx;
+    c->occ_dirty = true;
+    return VR_OK;
+}
+
+extern "C" int vr_set_slicing(vr_ctx *c, const float mn[3], const float mx[3])
+{
+    if (!c || !mn || !mx) return fail(c, VR_ERR_INVALID, "vr_set_slicing: null argument");
+    std::memcpy(c->min_slice, mn, sizeof(c->min_slice)); /* offscreen_pass.cpp:271-277 */
+    std::memcpy(c->max_slice, mx, sizeof(c->max_slice));
+    return VR_OK;
+}
+
+extern "C" int vr_set_transfer_function(vr_ctx *c, const uint32_t *rgba8, uint32_t n)
+{
+    if (!c || !rgba8 || n == 0) return fail(c, VR_ERR_INVALID, "vr_set_transfer_function: need n >= 1 texels");
+    if (n > 4096) return fail(c, VR_ERR_INVALID, "vr_set_transfer_function: at most 4096 texels (shared-memory staged)");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream)); /* wait_till_idle, offscreen_pass.cpp:282 */
+    uint32_t *copy = (uint32_t *)std::malloc(sizeof(uint32_t) * n);
+    if (!copy) return fail(c, VR_ERR_NOMEM, "out of host memory");
+    std::memcpy(copy, rgba8, sizeof(uint32_t) * n);
+    std::free(c->h_lut);
+    c->h_lut = copy, c->nlut = n;
+    return upload_lut(c);
+}
+
+extern "C" int vr_set_march(vr_ctx *c, float ray_dist, float step_size)
+{
+    if (!c || !(step_size > 0.0f) || !(ray_dist >= 0.0f)) return fail(c, VR_ERR_INVALID, "vr_set_march: bad arguments");
+    c->ray_dist = ray_dist, c->step_size = step_size;
+    return VR_OK;
+}
+
+extern "C" int vr_get_options(const vr_ctx *c, vr_options *out)
+{
+    if (!c || !out) return VR_ERR_INVALID;
+    *out = c->opt;
+    return VR_OK;
+}
+
+extern "C" int vr_set_options(vr_ctx *c, const vr_options *o)
+{
+    if (!c || !o || (o->sampler != VR_SAMPLER_HW && o->sampler != VR_SAMPLER_EXACT) || !(o->early_term_eps >= 0.0f))
+        return fail(c, VR_ERR_INVALID, "vr_set_options: bad arguments");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    const bool need_raw = o->write_raw && !c->d_raw;
+    c->opt = *o;
+    if (need_raw) {
+        VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+        VR_CUDA(c, cudaMalloc(&c->d_raw, (size_t)c->W * c->H * sizeof(float4)));
+        VR_CUDA(c, cudaMemset(c->d_raw, 0, (size_t)c->W * c->H * sizeof(float4)));
+    }
+    return VR_OK;
+}
+
+/* ================================================================ render == */
+
+namespace
+{
+int prepare_occupancy(vr_ctx *c, cudaStream_t s)
+{
+    if (!c->occ_dirty) return VR_OK;
+    VR_CUDA(c, vr_k0_classify(c->d_cell_range, c->occ_n, c->d_lut_pad, c->nlut, c->min_density, c->max_density, c->d_occ,
+                              c->occ_words, c->d_counters + 4, s));
+    VR_CUDA(c, cudaMemcpyAsync(&c->h_counters[4], c->d_counters + 4, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    VR_CUDA(c, cudaStreamSynchronize(s));
+    c->occ_empty_cells = c->h_counters[4];
+    c->occ_dirty = false;
+    return VR_OK;
+}
+
+void fill_params(const vr_ctx *c, MarchParams &p)
+{
+    std::memset(&p, 0, sizeof(p));
+    for (int r = 0; r < 4; r++) p.c0[r] = c->rc[0][r], p.c1[r] = c->rc[1][r], p.c2[r] = c->rc[2][r], p.c3[r] = c->rc[3][r];
+    p.sx = 2.0f / (float)c->W, p.sy = 2.0f / (float)c->H;
+    for (int i = 0; i < 3; i++) p.cam[i] = c->cam_pos[i], p.min_slice[i] = c->min_slice[i], p.max_slice[i] = c->max_slice[i];
+    p.W = c->W, p.H = c->H;
+    p.min_density = c->min_density, p.max_density = c->max_density;
+    p.range = c->max_density - c->min_density;
+    p.steps = (int)(c->ray_dist / c->step_size); /* volume.frag:31, fp32 divide */
+    p.step_size = c->step_size;
+    p.tex_lin = c->tex_lin, p.tex_pt = c->tex_pt;
+    const uint32_t ldims[3] = {c->nx, c->ny, c->nz};
+    const float inf = std::numeric_limits<float>::infinity();
+    for (int i = 0; i < 3; i++) {
+        const uint32_t full = c->sort_last ? c->full[i] : ldims[i];
+        p.dims[i] = (float)full;
+        p.org[i] = c->sort_last ? c->tex_org[i] : 0;
+        p.forg[i] = (float)p.org[i];
+        p.inv_ldims[i] = 1.0f / (float)ldims[i];
+        p.own_lo[i] = -inf, p.own_hi[i] = inf;
+        if (c->sort_last) {
+            /* both neighbours evaluate the shared face with the same integers -> same float */
+            if (c->own_org[i] > 0) p.own_lo[i] = (float)c->own_org[i] / (float)full;
+            if (c->own_org[i] + c->own_dims[i] < full) p.own_hi[i] = (float)(c->own_org[i] + c->own_dims[i]) / (float)full;
+        }
+        p.occ_n[i] = c->occ_n[i];
+        p.occ_scale[i] = (float)full / (float)c->occ_cell;
+        p.occ_off[i] = (float)p.org[i] / (float)c->occ_cell;
+    }
+    p.dtype = c->dtype;
+    p.dscale = c->dtype == VR_U8 ? 255.0f : (c->dtype == VR_U16 ? 65535.0f : 1.0f);
+    p.lut_pad = c->d_lut_pad, p.lut_dif = c->d_lut_dif, p.nlut = c->nlut;
+    const double range = (double)p.range, n = (double)c->nlut;
+    p.lutA = (float)((double)p.dscale * n / range);
+    p.lutB = (float)(0.5 - (double)c->min_density * n / range);
+    p.occ = c->d_occ, p.occ_words = c->occ_words;
+    p.out = c->d_image;
+    p.raw = c->opt.write_raw ? c->d_raw : nullptr;
+    p.counters = c->d_counters;
+    p.ert_eps = c->opt.early_term ? c->opt.early_term_eps : -1.0f;
+    p.pt_px = c->pt_px, p.pt_rank = c->pt_rank, p.pt_nranks = c->pt_nranks;
+    p.pt_nx = (c->W + c->pt_px - 1) / c->pt_px, p.pt_ny = (c->H + c->pt_px - 1) / c->pt_px;
+    p.pt_sub = c->pt_px / VR_TILE;
+}
+}  // namespace
+
+extern "C" int vr_render(vr_ctx *c, void *cuda_stream)
+{
+    if (!c) return VR_ERR_INVALID;
+    if (!c->ray_valid) return fail(c, VR_ERR_STATE, "vr_render: no valid camera");
+    if (!c->array) return fail(c, VR_ERR_STATE, "vr_render: no volume");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+    c->last_stream = s;
+    const float range = c->max_density - c->min_density;
+    const bool nondegenerate = range > 0.0f;
+    /* max_density == min_density divides by zero in volume.frag:42; only the exact path
+     * reproduces the oracle's definition of that case */
+    const bool exact = c->opt.sampler == VR_SAMPLER_EXACT || !nondegenerate;
+    const bool ess = c->opt.empty_skip && nondegenerate;
+    if (ess) {
+        const int rc = prepare_occupancy(c, s);
+        if (rc != VR_OK) return rc;
+    }
+    MarchParams p;
+    fill_params(c, p);
+    if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
+    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, s));
+    if (c->opt.collect_stats)
+        VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    return VR_OK;
+}
+
+extern "C" int vr_sync(vr_ctx *c)
+{
+    if (!c) return VR_ERR_INVALID;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    return VR_OK;
+}
+
+/* =============================================================== outputs == */
+
+extern "C" int vr_get_size(const vr_ctx *c, uint32_t *w, uint32_t *h)
+{
+    if (!c) return VR_ERR_INVALID;
+    if (w) *w = c->W;
+    if (h) *h = c->H;
+    return VR_OK;
+}
+
+extern "C" int vr_get_image(vr_ctx *c, void **dev, size_t *pitch)
+{
+    if (!c || !dev) return VR_ERR_INVALID;
+    *dev = c->d_image;
+    if (pitch) *pitch = (size_t)c->W * sizeof(uchar4);
+    return VR_OK;
+}
+
+extern "C" int vr_download_async(vr_ctx *c, void *host, void *cuda_stream)
+{
+    if (!c || !host) return fail(c, VR_ERR_INVALID, "vr_download: null argument");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->last_stream;
+    VR_CUDA(c, cudaMemcpyAsync(host, c->d_image, (size_t)c->W * c->H * sizeof(uchar4), cudaMemcpyDeviceToHost, s));
+    return VR_OK;
+}
+
+extern "C" int vr_download(vr_ctx *c, void *host)
+{
+    const int rc = vr_download_async(c, host, nullptr);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    return VR_OK;
+}
+
+extern "C" int vr_get_raw(vr_ctx *c, void **dev)
+{
+    if (!c || !dev) return VR_ERR_INVALID;
+    if (!c->d_raw) return fail(c, VR_ERR_STATE, "vr_get_raw: options.write_raw is off");
+    *dev = c->d_raw;
+    return VR_OK;
+}
+
+extern "C" int vr_download_raw(vr_ctx *c, float *host)
+{
+    if (!c || !host) return VR_ERR_INVALID;
+    if (!c->d_raw) return fail(c, VR_ERR_STATE, "vr_download_raw: options.write_raw is off");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaMemcpyAsync(host, c->d_raw, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->last_stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    return VR_OK;
+}
+
+extern "C" int vr_get_stats(vr_ctx *c, vr_stats *out)
+{
+    if (!c || !out) return VR_ERR_INVALID;
+    if (!c->opt.collect_stats) return fail(c, VR_ERR_STATE, "vr_get_stats: options.collect_stats is off");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    out->covered_pixels = c->h_counters[0], out->n_ref = c->h_counters[1];
+    out->n_inslice = c->h_counters[2], out->n_fetch = c->h_counters[3];
+    return VR_OK;
+}
+
+extern "C" int vr_get_occupancy_info(vr_ctx *c, uint32_t cells[3], uint32_t *cell_voxels, uint64_t *empty_cells)
+{
+    if (!c) return VR_ERR_INVALID;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    if (c->max_density - c->min_density > 0.0f) {
+        const int rc = prepare_occupancy(c, c->last_stream);
+        if (rc != VR_OK) return rc;
+    }
+    if (cells) cells[0] = c->occ_n[0], cells[1] = c->occ_n[1], cells[2] = c->occ_n[2];
+    if (cell_voxels) *cell_voxels = (uint32_t)c->occ_cell;
+    if (empty_cells) *empty_cells = c->occ_dirty ? 0 : c->occ_empty_cells;
+    return VR_OK;
+}
+
+extern "C" int vr_download_volume(vr_ctx *c, void *host)
+{
+    if (!c || !host) return VR_ERR_INVALID;
+    if (!c->array) return fail(c, VR_ERR_STATE, "no volume");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaMemcpy3DParms cp = {};
+    cp.srcArray = c->array;
+    cp.dstPtr = make_cudaPitchedPtr(host, (size_t)c->nx * dtype_size(c->dtype), c->nx, c->ny);
+    cp.extent = make_cudaExtent(c->nx, c->ny, c->nz);
+    cp.kind = cudaMemcpyDeviceToHost;
+    VR_CUDA(c, cudaMemcpy3D(&cp));
+    return VR_OK;
+}
+
+/* ============================================================ synthetic == */
+
+extern "C" int vr_synth_volume(vr_ctx *c, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz)
+{
+    if (!c || kind < 0 || kind > 2 || dtype < VR_U8 || dtype > VR_F32 || nx == 0 || ny == 0 || nz == 0)
+        return fail(c, VR_ERR_INVALID, "vr_synth_volume: bad arguments");
+    if (c->sort_last) return fail(c, VR_ERR_STATE, "vr_synth_volume: context is sort-last partitioned (use vr_synth_subvolume)");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    void *lin = nullptr;
+    VR_CUDA(c, cudaMalloc(&lin, (size_t)nx * ny * nz * dtype_size(dtype)));
+    const int org[3] = {0, 0, 0};
+    const uint32_t full[3] = {nx, ny, nz};
+    cudaError_t e = vr_k0_synth(lin, kind, seed, dtype, nx, ny, nz, org, full, c->stream);
+    if (e != cudaSuccess) {
+        cudaFree(lin);
+        return cuda_fail(c, e, "k_synth");
+    }
+    const int rc = install_volume(c, lin, dtype, nx, ny, nz, nullptr, nullptr);
+    cudaFree(lin);
+    return rc;
+}
+
+extern "C" int vr_synth_subvolume(vr_ctx *c, int kind, uint32_t seed, int dtype)
+{
+    if (!c || kind < 0 || kind > 2 || dtype < VR_U8 || dtype > VR_F32) return fail(c, VR_ERR_INVALID, "vr_synth_subvolume: bad arguments");
+    if (!c->sort_last) return fail(c, VR_ERR_STATE, "vr_synth_subvolume: call vr_set_partition_sort_last first");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    uint32_t l[3];
+    for (int i = 0; i < 3; i++) {
+        const uint32_t end = c->own_org[i] + c->own_dims[i];
+        l[i] = c->own_dims[i] + (c->own_org[i] > 0 ? 1 : 0) + (end < c->full[i] ? 1 : 0);
+    }
+    void *lin = nullptr;
+    VR_CUDA(c, cudaMalloc(&lin, (size_t)l[0] * l[1] * l[2] * dtype_size(dtype)));
+    cudaError_t e = vr_k0_synth(lin, kind, seed, dtype, l[0], l[1], l[2], c->tex_org, c->full, c->stream);
+    if (e != cudaSuccess) {
+        cudaFree(lin);
+        return cuda_fail(c, e, "k_synth");
+    }
+    const int rc = install_volume(c, lin, dtype, l[0], l[1], l[2], nullptr, nullptr);
+    cudaFree(lin);
+    return rc;
+}
+
+/* =========================================================== partitioning == */
+
+extern "C" int vr_set_partition_sort_first(vr_ctx *c, uint32_t rank, uint32_t nranks, uint32_t tile_px)
+{
+    if (!c || nranks == 0 || rank >= nranks || tile_px == 0 || tile_px % VR_TILE != 0)
+        return fail(c, VR_ERR_INVALID, "vr_set_partition_sort_first: need rank < nranks and tile_px a multiple of 16");
+    c->pt_rank = rank, c->pt_nranks = nranks, c->pt_px = tile_px;
+    return VR_OK;
+}
+
+extern "C" int vr_set_partition_sort_last(vr_ctx *c, const uint32_t full_dims[3], const uint32_t own_org[3],
+                                          const uint32_t own_dims[3])
+{
+    if (!c || !full_dims || !own_org || !own_dims) return fail(c, VR_ERR_INVALID, "vr_set_partition_sort_last: null argument");
+    for (int i = 0; i < 3; i++)
+        if (own_dims[i] == 0 || own_org[i] + own_dims[i] > full_dims[i])
+            return fail(c, VR_ERR_INVALID, "vr_set_partition_sort_last: sub-box outside the grid");
+    c->sort_last = true;
+    for (int i = 0; i < 3; i++) {
+        c->full[i] = full_dims[i], c->own_org[i] = own_org[i], c->own_dims[i] = own_dims[i];
+        c->tex_org[i] = (int)own_org[i] - (own_org[i] > 0 ? 1 : 0); /* one ghost voxel towards each neighbour */
+    }
+    return VR_OK;
+}
+
+extern "C" int vr_clear_partition(vr_ctx *c)
+{
+    if (!c) return VR_ERR_INVALID;
+    c->sort_last = false;
+    c->pt_rank = 0, c->pt_nranks = 1, c->pt_px = 64;
+    for (int i = 0; i < 3; i++) c->tex_org[i] = 0;
+    return VR_OK;
+}
+
+extern "C" int vr_partition_box(const uint32_t grid[3], const uint32_t full_dims[3], uint32_t index, uint32_t org[3],
+                                uint32_t dims[3])
+{
+    if (!grid || !full_dims || !org || !dims) return VR_ERR_INVALID;
+    const uint32_t total = grid[0] * grid[1] * grid[2];
+    if (total == 0 || index >= total) return VR_ERR_INVALID;
+    const uint32_t b[3] = {index % grid[0], (index / grid[0]) % grid[1], index / (grid[0] * grid[1])};
+    for (int i = 0; i < 3; i++) {
+        if (grid[i] > full_dims[i]) return VR_ERR_INVALID;
+        const uint64_t lo = (uint64_t)b[i] * full_dims[i] / grid[i], hi = (uint64_t)(b[i] + 1) * full_dims[i] / grid[i];
+        org[i] = (uint32_t)lo, dims[i] = (uint32_t)(hi - lo);
+    }
+    return VR_OK;
+}
+
+extern "C" int vr_partition_order(const uint32_t grid[3], const uint32_t full_dims[3], const float camera_position[3],
+                                  uint32_t *out)
+{
+    if (!grid || !full_dims || !camera_position || !out) return VR_ERR_INVALID;
+    const uint32_t total = grid[0] * grid[1] * grid[2];
+    if (total == 0) return VR_ERR_INVALID;
+    /* per axis: index of the slab holding the camera (-1 / grid when outside the cube).  A ray
+     * leaving the camera moves monotonically away from it on every axis, so |slab - camera slab|
+     * never decreases along a ray: sorting by the sum of the three distances is a valid
+     * front-to-back order for every pixel of the frame. */
+    int cs[3];
+    for (int a = 0; a < 3; a++) {
+        const double t = (double)camera_position[a] + 0.5; /* model -> texture space */
+        int s = -1;
+        for (uint32_t k = 0; k < grid[a]; k++) {
+            const double lo = (double)((uint64_t)k * full_dims[a] / grid[a]) / (double)full_dims[a];
+            if (t >= lo) s = (int)k;
+        }
+        if (t >= 1.0) s = (int)grid[a];
+        cs[a] = s;
+    }
+    std::vector<std::pair<int, uint32_t>> keyed(total);
+    for (uint32_t i = 0; i < total; i++) {
+        const int b[3] = {(int)(i % grid[0]), (int)((i / grid[0]) % grid[1]), (int)(i / (grid[0] * grid[1]))};
+        int key = 0;
+        for (int a = 0; a < 3; a++) key += std::abs(b[a] - cs[a]);
+        keyed[i] = {key, i};
+    }
+    std::stable_sort(keyed.begin(), keyed.end(), [](const auto &x, const auto &y) { return x.first < y.first; });
+    for (uint32_t i = 0; i < total; i++) out[i] = keyed[i].second;
+    return VR_OK;
+}
+
+extern "C" int vr_composite(vr_ctx *c, const void *const *parts, uint32_t nparts, uint64_t pixel_begin, uint64_t pixel_end,
+                            void *cuda_stream)
+{
+    if (!c || !parts || nparts == 0) return fail(c, VR_ERR_INVALID, "vr_composite: bad arguments");
+    if (pixel_end > (uint64_t)c->W * c->H || pixel_begin > pixel_end) return fail(c, VR_ERR_INVALID, "vr_composite: pixel range outside the frame");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+    c->last_stream = s;
+    VR_CUDA(c, vr_launch_composite(reinterpret_cast<const float4 *const *>(parts), nparts, pixel_begin, pixel_end, c->d_image,
+                                   nullptr, s));
+    return VR_OK;
+}
+
+/* test hook: the fp32 columns of inverse(proj*view) the kernel will use */
+extern "C" int vr_debug_ray_context(const vr_ctx *c, float out[16])
+{
+    if (!c || !out || !c->ray_valid) return VR_ERR_INVALID;
+    std::memcpy(out, c->rc, sizeof(float) * 16);
+    return VR_OK;
+}

@@ -1,0 +1,90 @@
+/*
+ * composite.cu -- K2: view-ordered `over` of partial images (sort-last), fused with the
+ * display blend and RGBA8 store (src/rendering/offscreen_pass.cpp:715-725,:170-173,:293).
+ *
+ * Not in the reference (it is single-GPU).  A partial is what res/shaders/volume.frag:44-50
+ * leaves in out_color for the samples one rank owns: premultiplied rgb and alpha = 1 - T.
+ * Front-to-back accumulation is associative, so merging partials in visiting order
+ *     C += T * C_k ;  T *= (1 - A_k)
+ * equals the single-GPU loop up to fp32 re-association.
+ *
+ * The partials are read through plain global loads, 16 bytes per pixel per part; the pointers
+ * may be local HBM or peer memory mapped over NVLink (cudaIpcOpenMemHandle /
+ * cudaDeviceEnablePeerAccess), in which case the exchange and the merge are this one kernel:
+ * no staging copy, the NVLink transfer overlaps the arithmetic of the other pixels.
+ */
+#include <cuda_runtime.h>
+
+#include "vr_ctx.h"
+
+#define VR_MAX_PARTS 64
+
+namespace
+{
+struct PartTable {
+    const float4 *p[VR_MAX_PARTS];
+};
+
+__device__ __forceinline__ float4 ld_stream(const float4 *ptr)
+{
+    /* read-once data: do not allocate in L1 */
+    float4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(ptr));
+    return v;
+}
+
+__global__ void __launch_bounds__(256) k_composite(const __grid_constant__ PartTable tab, uint32_t nparts,
+                                                   uint64_t begin, uint64_t end, uchar4 *out, float4 *raw_out)
+{
+    for (uint64_t i = begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < end;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        float cr = 0.f, cg = 0.f, cb = 0.f, T = 1.f;
+        /* issue up to 8 loads before the dependent chain */
+        for (uint32_t k0 = 0; k0 < nparts; k0 += 8) {
+            float4 v[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                if (k0 + k < nparts) v[k] = ld_stream(tab.p[k0 + k] + i);
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                if (k0 + k < nparts) {
+                    cr = fmaf(T, v[k].x, cr);
+                    cg = fmaf(T, v[k].y, cg);
+                    cb = fmaf(T, v[k].z, cb);
+                    T *= (1.0f - v[k].w);
+                }
+        }
+        const float A = 1.0f - T, iA = 1.0f - A;
+        if (raw_out) raw_out[i] = make_float4(cr, cg, cb, A);
+        const float ov[4] = {cr * A + VR_CLEAR_RGB * iA, cg * A + VR_CLEAR_RGB * iA, cb * A + VR_CLEAR_RGB * iA,
+                             A * A + 1.0f * iA};
+        unsigned char q[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            float x = ov[c];
+            x = x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x);
+            if (!(x == x)) x = 0.0f;
+            q[c] = (unsigned char)(x * 255.0f + 0.5f);
+        }
+        out[i] = make_uchar4(q[0], q[1], q[2], q[3]);
+    }
+}
+}  // namespace
+
+cudaError_t vr_launch_composite(const float4 *const *parts, uint32_t nparts, uint64_t begin, uint64_t end, uchar4 *out,
+                                float4 *raw_out, cudaStream_t s)
+{
+    if (nparts == 0 || nparts > VR_MAX_PARTS) return cudaErrorInvalidValue;
+    if (end <= begin) return cudaSuccess;
+    PartTable tab;
+    for (uint32_t k = 0; k < VR_MAX_PARTS; k++) tab.p[k] = k < nparts ? parts[k] : nullptr;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    uint64_t blocks = (end - begin + 255) / 256;
+    if (blocks > (uint64_t)sms * 8) blocks = (uint64_t)sms * 8;
+    k_composite<<<(unsigned)blocks, 256, 0, s>>>(tab, nparts, begin, end, out, raw_out);
+    return cudaGetLastError();
+}

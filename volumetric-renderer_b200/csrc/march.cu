@@ -1,0 +1,361 @@
+/*
+ * march.cu -- K1, the ray-march kernel (sm_100a).
+ *
+ * One launch does what one draw of the reference's offscreen pass does
+ * (src/rendering/offscreen_pass.cpp:163-230): per pixel, the coverage decision and ray
+ * entry of the rasterised front faces of the unit cube (res/shaders/volume.vert:19-24,
+ * offscreen_pass.cpp:55-90,:661-712), the fragment-shader loop (res/shaders/volume.frag:21-52),
+ * and the fixed-function blend over the clear colour into RGBA8 (offscreen_pass.cpp:170-173,
+ * :715-725,:293).
+ *
+ * Mapping: a CTA of 256 threads owns a 16x16 pixel tile; each warp an 8x4 block of it, so the
+ * 32 rays of a warp stay within a few voxels of one another at every step and share texture
+ * cache lines.  The transfer function (decoded sRGB -> linear fp32, edge-padded so the two
+ * taps need no clamp) and the occupancy bit grid are staged in shared memory.  The volume is
+ * a 3-D CUDA array (hardware block-linear = bricked layout) read through texture objects.
+ *
+ * This file is compiled with -fmad=false: every fp32 operation rounds once, in the order
+ * written, so ray entry and the sample positions (volume.frag:47 accumulates them) are
+ * bit-identical to the CPU oracle.  Fused multiply-adds are written explicitly (fmaf) where
+ * the hardware-sampler path is allowed to differ in rounding.
+ */
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "vr_ctx.h"
+
+namespace
+{
+
+struct Entry {
+    float frag[3];
+    float tex[3];
+};
+
+/* S2: does pixel (px,py) get a fragment, and where does its ray enter the cube?
+ * Pixel centre -> NDC -> line through the near/far plane points (inverse(proj*view)),
+ * slab test against [-0.5,0.5]^3, front face inside the clip volume 0 <= z_ndc <= 1. */
+__device__ __forceinline__ bool pixel_entry(const MarchParams &p, uint32_t px, uint32_t py, Entry &e)
+{
+    const float xn = ((float)px + 0.5f) * p.sx - 1.0f;
+    const float yn = ((float)py + 0.5f) * p.sy - 1.0f;
+    float nh[4], fh[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        nh[i] = (xn * p.c0[i] + yn * p.c1[i]) + p.c3[i];
+        fh[i] = nh[i] + p.c2[i];
+    }
+    float pn[3], d[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        pn[i] = nh[i] / nh[3];
+        d[i] = fh[i] / fh[3] - pn[i];
+    }
+    float tnear = -CUDART_INF_F, tfar = CUDART_INF_F;
+    int axis = 0;
+    bool miss = false;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        float lo, hi;
+        if (d[i] != 0.0f) {
+            const float inv = 1.0f / d[i];
+            const float ta = (-0.5f - pn[i]) * inv;
+            const float tb = (0.5f - pn[i]) * inv;
+            lo = fminf(ta, tb);
+            hi = fmaxf(ta, tb);
+        } else {
+            if (pn[i] < -0.5f || pn[i] > 0.5f) miss = true;
+            lo = -CUDART_INF_F;
+            hi = CUDART_INF_F;
+        }
+        if (lo > tnear) {
+            tnear = lo;
+            axis = i;
+        }
+        if (hi < tfar) tfar = hi;
+    }
+    if (miss || !(tnear < tfar) || !(tnear >= 0.0f) || !(tnear <= 1.0f)) return false;
+#pragma unroll
+    for (int i = 0; i < 3; i++) e.frag[i] = pn[i] + tnear * d[i];
+    /* the entry coordinate is the face itself (vertex table: tex = pos + 0.5) */
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+        if (i == axis) e.frag[i] = d[i] > 0.0f ? -0.5f : 0.5f;
+#pragma unroll
+    for (int i = 0; i < 3; i++) e.tex[i] = e.frag[i] + 0.5f;
+    return true;
+}
+
+__device__ __forceinline__ float lerp1(float a, float b, float w) { return a + w * (b - a); }
+
+/* S4, verification sampler: VK_FILTER_LINEAR with CLAMP_TO_BORDER(0) restated as eight point
+ * fetches (border mode returns 0 outside) and fp32 lerps in x, y, z order. */
+__device__ __forceinline__ float sample_exact(const MarchParams &p, float s, float t, float r)
+{
+    const float u = s * p.dims[0] - 0.5f, v = t * p.dims[1] - 0.5f, w = r * p.dims[2] - 0.5f;
+    const float fu = floorf(u), fv = floorf(v), fw = floorf(w);
+    const float a = u - fu, b = v - fv, c = w - fw;
+    const float x0 = (float)((int)fu - p.org[0]) + 0.5f, y0 = (float)((int)fv - p.org[1]) + 0.5f,
+                z0 = (float)((int)fw - p.org[2]) + 0.5f;
+    const float x1 = x0 + 1.0f, y1 = y0 + 1.0f, z1 = z0 + 1.0f;
+    float v000, v100, v010, v110, v001, v101, v011, v111;
+#define VR_FETCH8(T)                                                                                      \
+    v000 = (float)tex3D<T>(p.tex_pt, x0, y0, z0), v100 = (float)tex3D<T>(p.tex_pt, x1, y0, z0),           \
+    v010 = (float)tex3D<T>(p.tex_pt, x0, y1, z0), v110 = (float)tex3D<T>(p.tex_pt, x1, y1, z0),           \
+    v001 = (float)tex3D<T>(p.tex_pt, x0, y0, z1), v101 = (float)tex3D<T>(p.tex_pt, x1, y0, z1),           \
+    v011 = (float)tex3D<T>(p.tex_pt, x0, y1, z1), v111 = (float)tex3D<T>(p.tex_pt, x1, y1, z1)
+    switch (p.dtype) {
+        case VR_U8: VR_FETCH8(unsigned char); break;
+        case VR_U16: VR_FETCH8(unsigned short); break;
+        default: VR_FETCH8(float); break;
+    }
+#undef VR_FETCH8
+    const float x00 = lerp1(v000, v100, a), x10 = lerp1(v010, v110, a);
+    const float x01 = lerp1(v001, v101, a), x11 = lerp1(v011, v111, a);
+    return lerp1(lerp1(x00, x10, b), lerp1(x01, x11, b), c);
+}
+
+/* Is the occupancy bit of the cell holding this position set? */
+template <bool PART>
+__device__ __forceinline__ bool cell_occupied(const MarchParams &p, const uint32_t *sOcc, float x, float y, float z)
+{
+    /* a one-ulp slip across a cell face is harmless: every cell's range includes a 1-voxel apron */
+    int cx = PART ? (int)(x * p.occ_scale[0] - p.occ_off[0]) : (int)(x * p.occ_scale[0]);
+    int cy = PART ? (int)(y * p.occ_scale[1] - p.occ_off[1]) : (int)(y * p.occ_scale[1]);
+    int cz = PART ? (int)(z * p.occ_scale[2] - p.occ_off[2]) : (int)(z * p.occ_scale[2]);
+    cx = min(max(cx, 0), p.occ_n[0] - 1);
+    cy = min(max(cy, 0), p.occ_n[1] - 1);
+    cz = min(max(cz, 0), p.occ_n[2] - 1);
+    const int bit = (cz * p.occ_n[1] + cy) * p.occ_n[0] + cx;
+    return (sOcc[bit >> 5] >> (bit & 31)) & 1u;
+}
+
+template <bool EXACT, bool ESS, bool STATS, bool PART>
+__global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant__ MarchParams p)
+{
+    extern __shared__ float4 smem[];
+    float4 *sP = smem;                 /* nlut + 3 */
+    float4 *sD = sP + (p.nlut + 3);    /* nlut + 2 */
+    uint32_t *sOcc = reinterpret_cast<uint32_t *>(sD + (p.nlut + 2));
+
+    /* which tile: partition tiles dealt round-robin to ranks, 16x16 sub-tiles inside */
+    const uint32_t sub2 = p.pt_sub * p.pt_sub;
+    const uint32_t own_tile = blockIdx.x / sub2, r = blockIdx.x - own_tile * sub2;
+    const uint32_t t = p.pt_rank + own_tile * p.pt_nranks;
+    const uint32_t pty = t / p.pt_nx, ptx = t - pty * p.pt_nx;
+    const uint32_t sy_ = r / p.pt_sub, sx_ = r - sy_ * p.pt_sub;
+    const uint32_t x0 = ptx * p.pt_px + sx_ * VR_TILE, y0 = pty * p.pt_px + sy_ * VR_TILE;
+    if (x0 >= p.W || y0 >= p.H) return; /* uniform per CTA */
+
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t px = x0 + (warp & 1) * 8 + (lane & 7);
+    const uint32_t py = y0 + (warp >> 1) * 4 + (lane >> 3);
+    const bool valid = px < p.W && py < p.H;
+
+    Entry e;
+    const bool covered = valid && pixel_entry(p, px, py, e);
+    const size_t pix = (size_t)py * p.W + px;
+
+    if (!__syncthreads_or(covered)) {
+        /* nothing to march in this tile: clear colour only (offscreen_pass.cpp:170-173) */
+        if (valid) {
+            const unsigned char c = (unsigned char)(VR_CLEAR_RGB * 255.0f + 0.5f);
+            p.out[pix] = make_uchar4(c, c, c, 255);
+            if (p.raw) p.raw[pix] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        return;
+    }
+
+    for (uint32_t i = threadIdx.x; i < p.nlut + 3; i += VR_CTA_THREADS) sP[i] = p.lut_pad[i];
+    if (!EXACT)
+        for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += VR_CTA_THREADS) sD[i] = p.lut_dif[i];
+    if (ESS)
+        for (int i = threadIdx.x; i < p.occ_words; i += VR_CTA_THREADS) sOcc[i] = p.occ[i];
+    __syncthreads();
+
+    /* volume.frag:22-24 */
+    float cr = 0.0f, cg = 0.0f, cb = 0.0f, T = 1.0f;
+    float posx = 0.f, posy = 0.f, posz = 0.f, dx = 0.f, dy = 0.f, dz = 0.f;
+    if (covered) {
+        const float vx = e.frag[0] - p.cam[0], vy = e.frag[1] - p.cam[1], vz = e.frag[2] - p.cam[2];
+        const float d2 = (vx * vx + vy * vy) + vz * vz;
+        const float inv = 1.0f / sqrtf(d2); /* glm::normalize = v * inversesqrt(dot(v,v)) */
+        dx = (vx * inv) * p.step_size;
+        dy = (vy * inv) * p.step_size;
+        dz = (vz * inv) * p.step_size;
+        posx = e.tex[0], posy = e.tex[1], posz = e.tex[2];
+    }
+
+    constexpr int U = EXACT ? 1 : VR_BATCH;
+    const float lut_hi = (float)p.nlut;
+    uint32_t nb = 0, ns = 0, nf = 0;
+    bool done = !covered;
+    int i = 0;
+
+    while (!done) {
+        float qx[U], qy[U], qz[U], val[U];
+        bool ok[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            /* volume.frag:33-37: loop bound and the strict bounds test */
+            const bool inb = !done && i < p.steps &&
+                             !(posx > 1.0f || posy > 1.0f || posz > 1.0f || posx < 0.0f || posy < 0.0f || posz < 0.0f);
+            if (!inb) done = true;
+            /* volume.frag:39-40: strict on both sides */
+            bool s = inb && posx < p.max_slice[0] && posy < p.max_slice[1] && posz < p.max_slice[2] &&
+                     posx > p.min_slice[0] && posy > p.min_slice[1] && posz > p.min_slice[2];
+            if (PART)
+                s = s && posx >= p.own_lo[0] && posy >= p.own_lo[1] && posz >= p.own_lo[2] && posx < p.own_hi[0] &&
+                    posy < p.own_hi[1] && posz < p.own_hi[2];
+            if (STATS) {
+                nb += inb;
+                ns += s;
+            }
+            if (ESS) s = s && cell_occupied<PART>(p, sOcc, posx, posy, posz);
+            ok[u] = s;
+            qx[u] = posx, qy[u] = posy, qz[u] = posz;
+            /* volume.frag:47 */
+            posx += dx, posy += dy, posz += dz;
+            i++;
+        }
+        /* volume.frag:41: all fetches of the batch are issued before any is consumed */
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            val[u] = 0.0f;
+            if (ok[u]) {
+                if (EXACT) {
+                    val[u] = sample_exact(p, qx[u], qy[u], qz[u]);
+                } else if (PART) {
+                    val[u] = tex3D<float>(p.tex_lin, (qx[u] * p.dims[0] - p.forg[0]) * p.inv_ldims[0],
+                                          (qy[u] * p.dims[1] - p.forg[1]) * p.inv_ldims[1],
+                                          (qz[u] * p.dims[2] - p.forg[2]) * p.inv_ldims[2]);
+                } else {
+                    val[u] = tex3D<float>(p.tex_lin, qx[u], qy[u], qz[u]);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (ok[u]) {
+                if (STATS) nf++;
+                float sr, sg, sb, sa;
+                if (EXACT) {
+                    /* volume.frag:42-43 and the LINEAR / CLAMP_TO_EDGE 1-D sampler */
+                    const float tt = (val[u] - p.min_density) / p.range;
+                    float uu = tt * lut_hi - 0.5f;
+                    uu = (uu > -1.0f) ? uu : -1.0f; /* NaN -> texel 0 */
+                    uu = (uu < lut_hi) ? uu : lut_hi;
+                    const float fu = floorf(uu);
+                    const int k = (int)fu + 1;
+                    const float w = uu - fu;
+                    const float4 a = sP[k], b = sP[k + 1];
+                    sr = lerp1(a.x, b.x, w), sg = lerp1(a.y, b.y, w), sb = lerp1(a.z, b.z, w), sa = lerp1(a.w, b.w, w);
+                    /* volume.frag:44-45 */
+                    cr += T * (sa * sr);
+                    cg += T * (sa * sg);
+                    cb += T * (sa * sb);
+                    T *= (1.0f - sa);
+                } else {
+                    float uu = fmaf(val[u], p.lutA, p.lutB); /* padded LUT coordinate, u + 1 */
+                    uu = fminf(fmaxf(uu, 0.0f), lut_hi + 1.0f);
+                    const int k = (int)uu;
+                    const float w = uu - (float)k;
+                    const float4 a = sP[k], d = sD[k];
+                    sr = fmaf(w, d.x, a.x), sg = fmaf(w, d.y, a.y), sb = fmaf(w, d.z, a.z), sa = fmaf(w, d.w, a.w);
+                    const float ta = T * sa;
+                    cr = fmaf(ta, sr, cr);
+                    cg = fmaf(ta, sg, cg);
+                    cb = fmaf(ta, sb, cb);
+                    T = fmaf(-T, sa, T);
+                }
+                if (T < p.ert_eps) {
+                    /* early ray termination: what is left contributes < eps per channel */
+                    done = true;
+#pragma unroll
+                    for (int v = u + 1; v < U; v++) ok[v] = false;
+                }
+            }
+        }
+    }
+
+    if (valid) {
+        uchar4 o;
+        float4 rawv;
+        if (covered) {
+            /* volume.frag:50 then the blend: src*srcA + dst*(1-srcA) for colour and alpha */
+            const float A = 1.0f - T, iA = 1.0f - A;
+            rawv = make_float4(cr, cg, cb, A);
+            float o0 = cr * A + VR_CLEAR_RGB * iA, o1 = cg * A + VR_CLEAR_RGB * iA, o2 = cb * A + VR_CLEAR_RGB * iA,
+                  o3 = A * A + 1.0f * iA;
+            float ov[4] = {o0, o1, o2, o3};
+            unsigned char q[4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                float x = ov[c];
+                x = x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x);
+                if (!(x == x)) x = 0.0f;
+                q[c] = (unsigned char)(x * 255.0f + 0.5f);
+            }
+            o = make_uchar4(q[0], q[1], q[2], q[3]);
+        } else {
+            const unsigned char c = (unsigned char)(VR_CLEAR_RGB * 255.0f + 0.5f);
+            o = make_uchar4(c, c, c, 255);
+            rawv = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        p.out[pix] = o;
+        if (p.raw) p.raw[pix] = rawv;
+    }
+
+    if (STATS) {
+        const uint32_t ncov = __reduce_add_sync(0xffffffffu, covered ? 1u : 0u);
+        nb = __reduce_add_sync(0xffffffffu, nb);
+        ns = __reduce_add_sync(0xffffffffu, ns);
+        nf = __reduce_add_sync(0xffffffffu, nf);
+        if (lane == 0 && ncov) {
+            atomicAdd(&p.counters[0], (unsigned long long)ncov);
+            atomicAdd(&p.counters[1], (unsigned long long)nb);
+            atomicAdd(&p.counters[2], (unsigned long long)ns);
+            atomicAdd(&p.counters[3], (unsigned long long)nf);
+        }
+    }
+}
+
+template <bool EXACT, bool ESS, bool STATS, bool PART>
+cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, cudaStream_t s)
+{
+    auto kern = k_march<EXACT, ESS, STATS, PART>;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    kern<<<grid, VR_CTA_THREADS, smem, s>>>(p);
+    return cudaGetLastError();
+}
+
+template <bool EXACT, bool ESS>
+cudaError_t launch2(const MarchParams &p, bool stats, bool part, size_t smem, dim3 grid, cudaStream_t s)
+{
+    if (stats) return part ? launch<EXACT, ESS, true, true>(p, smem, grid, s) : launch<EXACT, ESS, true, false>(p, smem, grid, s);
+    return part ? launch<EXACT, ESS, false, true>(p, smem, grid, s) : launch<EXACT, ESS, false, false>(p, smem, grid, s);
+}
+
+}  // namespace
+
+size_t vr_march_smem_bytes(const MarchParams &p, bool ess)
+{
+    return sizeof(float4) * (size_t)(2 * p.nlut + 5) + (ess ? sizeof(uint32_t) * (size_t)p.occ_words : 0);
+}
+
+cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, cudaStream_t s)
+{
+    const uint64_t ntiles = (uint64_t)p.pt_nx * p.pt_ny;
+    if (p.pt_rank >= ntiles) return cudaSuccess; /* more ranks than tiles */
+    const uint64_t own = (ntiles - p.pt_rank + p.pt_nranks - 1) / p.pt_nranks;
+    const uint64_t ctas = own * p.pt_sub * p.pt_sub;
+    if (ctas == 0) return cudaSuccess;
+    if (ctas > 0x7fffffffull) return cudaErrorInvalidConfiguration;
+    const size_t smem = vr_march_smem_bytes(p, ess);
+    const dim3 grid((unsigned)ctas);
+    if (exact) return ess ? launch2<true, true>(p, stats, part, smem, grid, s) : launch2<true, false>(p, stats, part, smem, grid, s);
+    return ess ? launch2<false, true>(p, stats, part, smem, grid, s) : launch2<false, false>(p, stats, part, smem, grid, s);
+}

@@ -1,0 +1,109 @@
+/*
+ * texbench.cu -- the texture-fetch roofline denominator.
+ *
+ * MEASURED_PEAKS.json has no texture-fetch figure, so the build measures it: a 32^3 volume
+ * of the requested texel type (L1-resident after the first touches) is fetched with tex3D
+ * from every SM, addresses laid out like the march's (a warp = 8x4 neighbouring rays
+ * advancing along z), 8 independent fetches in flight per thread and no other work.
+ * The result (fetches/s) is what K1's executed fetch rate is divided by.
+ */
+#include <cuda_runtime.h>
+
+#include <vector>
+
+#include "vr_ctx.h"
+
+namespace
+{
+__global__ void __launch_bounds__(256) k_texbench(cudaTextureObject_t tex, int iters, float step, float *sink)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    /* 8x4 rays one texel apart, each warp at its own offset */
+    const float inv = 1.0f / 32.0f;
+    float x = ((lane & 7) + 0.37f + (warp & 3) * 6.0f) * inv;
+    float y = ((lane >> 3) + 0.61f + (warp >> 2) * 9.0f + (blockIdx.x & 7)) * inv;
+    float z = 0.013f * (blockIdx.x & 15);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            acc[k] += tex3D<float>(tex, x, y, z);
+            z += step;
+            if (z > 1.0f) z -= 1.0f;
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += acc[k];
+    if (s == -12345.678f) sink[0] = s; /* never true: keeps the fetches alive */
+}
+}  // namespace
+
+extern "C" int vr_bench_tex_peak(int device, int dtype, int hw_filter, double *fetches_per_s)
+{
+    if (!fetches_per_s || dtype < VR_U8 || dtype > VR_F32) return VR_ERR_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return VR_ERR_CUDA;
+    const int N = 32;
+    const size_t esz = dtype == VR_U8 ? 1 : (dtype == VR_U16 ? 2 : 4);
+    std::vector<unsigned char> host((size_t)N * N * N * esz);
+    uint32_t h = 0x1234567u;
+    for (size_t i = 0; i < (size_t)N * N * N; i++) {
+        h = h * 1664525u + 1013904223u;
+        if (dtype == VR_U8) host[i] = (unsigned char)(h >> 24);
+        else if (dtype == VR_U16) reinterpret_cast<unsigned short *>(host.data())[i] = (unsigned short)(h >> 16);
+        else reinterpret_cast<float *>(host.data())[i] = (float)(h >> 8) * (1.0f / 16777216.0f);
+    }
+    cudaChannelFormatDesc cd = dtype == VR_U8    ? cudaCreateChannelDesc<unsigned char>()
+                               : dtype == VR_U16 ? cudaCreateChannelDesc<unsigned short>()
+                                                 : cudaCreateChannelDesc<float>();
+    cudaArray_t arr = nullptr;
+    cudaTextureObject_t tex = 0;
+    float *sink = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    int rc = VR_ERR_CUDA;
+    do {
+        if (cudaMalloc3DArray(&arr, &cd, make_cudaExtent(N, N, N)) != cudaSuccess) break;
+        cudaMemcpy3DParms cp = {};
+        cp.srcPtr = make_cudaPitchedPtr(host.data(), N * esz, N, N);
+        cp.dstArray = arr;
+        cp.extent = make_cudaExtent(N, N, N);
+        cp.kind = cudaMemcpyHostToDevice;
+        if (cudaMemcpy3D(&cp) != cudaSuccess) break;
+        cudaResourceDesc rd = {};
+        rd.resType = cudaResourceTypeArray;
+        rd.res.array.array = arr;
+        cudaTextureDesc td = {};
+        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeBorder;
+        td.filterMode = hw_filter ? cudaFilterModeLinear : cudaFilterModePoint;
+        td.readMode = dtype == VR_F32 ? cudaReadModeElementType : cudaReadModeNormalizedFloat;
+        td.normalizedCoords = 1;
+        if (cudaCreateTextureObject(&tex, &rd, &td, nullptr) != cudaSuccess) break;
+        if (cudaMalloc(&sink, sizeof(float)) != cudaSuccess) break;
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        const int blocks = sms * 8, iters = 2048;
+        const float step = 2.56f / 32.0f * 0.125f;
+        cudaEventCreate(&e0), cudaEventCreate(&e1);
+        k_texbench<<<blocks, 256>>>(tex, 64, step, sink); /* warm-up */
+        double best = 0.0;
+        for (int rep = 0; rep < 5; rep++) {
+            cudaEventRecord(e0);
+            k_texbench<<<blocks, 256>>>(tex, iters, step, sink);
+            cudaEventRecord(e1);
+            if (cudaEventSynchronize(e1) != cudaSuccess) break;
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            const double rate = (double)blocks * 256.0 * iters * 8.0 / (ms * 1e-3);
+            if (rate > best) best = rate;
+        }
+        if (cudaGetLastError() != cudaSuccess || best == 0.0) break;
+        *fetches_per_s = best;
+        rc = VR_OK;
+    } while (0);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (sink) cudaFree(sink);
+    if (tex) cudaDestroyTextureObject(tex);
+    if (arr) cudaFreeArray(arr);
+    return rc;
+}

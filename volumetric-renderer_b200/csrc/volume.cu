@@ -1,0 +1,364 @@
+/*
+ * volume.cu -- K0: what happens to a volume between the loader and the march.
+ *
+ * Replaces, on the device and in the dataset's native type:
+ *   - the two O(N) host passes std::min_element / std::max_element of
+ *     NrrdFileParser::parse (src/data/nrrd_file_parser.cpp:39-40)        -> k_global_minmax
+ *   - (new) per-cell value ranges for empty-space skipping                -> k_cell_ranges
+ *   - (new) cell classification against the transfer function            -> k_classify
+ *   - (new) the synthetic volumes BASELINE.json names, generated in HBM  -> k_synth
+ * The copy into the bricked (block-linear) 3-D CUDA array that replaces
+ * vkCmdCopyBufferToImage (src/rendering/offscreen_pass.cpp:1379-1406) is a cudaMemcpy3D
+ * issued from api.cu.
+ *
+ * Compiled with -fmad=false (see march.cu): k_classify evaluates the transfer-function
+ * coordinate with the same single-rounding operations as the march, and the fBm generator is
+ * bit-identical to the CPU generator the tests use.
+ */
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include <vector>
+
+#include "vr_ctx.h"
+
+namespace
+{
+
+template <typename T>
+__device__ __forceinline__ float ldval(const void *base, size_t i)
+{
+    return (float)__ldg(reinterpret_cast<const T *>(base) + i);
+}
+
+__device__ __forceinline__ float ld_any(const void *base, int dtype, size_t i)
+{
+    switch (dtype) {
+        case VR_U8: return ldval<unsigned char>(base, i);
+        case VR_U16: return ldval<unsigned short>(base, i);
+        default: return ldval<float>(base, i);
+    }
+}
+
+__device__ __forceinline__ void block_minmax(float &mn, float &mx, float2 *out)
+{
+    __shared__ float smn[32], smx[32];
+    for (int o = 16; o; o >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    if ((threadIdx.x & 31) == 0) smn[w] = mn, smx[w] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < nw; i++) mn = fminf(mn, smn[i]), mx = fmaxf(mx, smx[i]);
+        *out = make_float2(mn, mx);
+    }
+}
+
+/* grid-stride min/max over the whole volume, 16 bytes per load; one partial per block */
+template <typename T>
+__global__ void __launch_bounds__(256) k_global_minmax(const T *__restrict__ v, size_t n, float2 *partial)
+{
+    constexpr int PER = 16 / sizeof(T);
+    float mn = CUDART_INF_F, mx = -CUDART_INF_F;
+    const size_t nvec = n / PER;
+    const uint4 *v4 = reinterpret_cast<const uint4 *>(v);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 q = __ldg(v4 + i);
+        const T *e = reinterpret_cast<const T *>(&q);
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            const float f = (float)e[k];
+            mn = fminf(mn, f), mx = fmaxf(mx, f);
+        }
+    }
+    if (blockIdx.x == 0)
+        for (size_t i = nvec * PER + threadIdx.x; i < n; i += blockDim.x) {
+            const float f = (float)v[i];
+            mn = fminf(mn, f), mx = fmaxf(mx, f);
+        }
+    block_minmax(mn, mx, partial + blockIdx.x);
+}
+
+/* One block per occupancy cell: (min,max) over the voxels any sample positioned in the cell can
+ * touch = the cell's own `cell`^3 voxels plus a one-voxel apron; voxels outside the local
+ * texture read 0, which is what the border sampler returns (offscreen_pass.cpp:1020-1026). */
+__global__ void __launch_bounds__(64) k_cell_ranges(const void *__restrict__ v, int dtype, int nx, int ny, int nz,
+                                                    int cell, int cnx, int cny, float2 *ranges)
+{
+    const int c = blockIdx.x;
+    const int cx = c % cnx, cy = (c / cnx) % cny, cz = c / (cnx * cny);
+    const int x0 = cx * cell - 1, y0 = cy * cell - 1, z0 = cz * cell - 1;
+    const int w = cell + 2;
+    float mn = CUDART_INF_F, mx = -CUDART_INF_F;
+    for (int row = threadIdx.x; row < w * w; row += blockDim.x) {
+        const int y = y0 + row % w, z = z0 + row / w;
+        if (y < 0 || y >= ny || z < 0 || z >= nz) {
+            mn = fminf(mn, 0.0f), mx = fmaxf(mx, 0.0f);
+            continue;
+        }
+        const size_t base = ((size_t)z * ny + y) * nx;
+        for (int k = 0; k < w; k++) {
+            const int x = x0 + k;
+            const float f = (x < 0 || x >= nx) ? 0.0f : ld_any(v, dtype, base + x);
+            mn = fminf(mn, f), mx = fmaxf(mx, f);
+        }
+    }
+    block_minmax(mn, mx, ranges + c);
+}
+
+/* padded-LUT tap index of a raw density, computed exactly as the EXACT march path does */
+__device__ __forceinline__ int lut_tap(float v, float min_density, float range, float n)
+{
+    const float tt = (v - min_density) / range;
+    float uu = tt * n - 0.5f;
+    uu = (uu > -1.0f) ? uu : -1.0f;
+    uu = (uu < n) ? uu : n;
+    return (int)floorf(uu) + 1;
+}
+
+/* bit = 1: some sample in the cell may have alpha != 0 and must be fetched.
+ * bit = 0: every density in the cell's range maps between LUT texels whose alpha is exactly 0,
+ * so volume.frag:44-45 leaves colour and transmittance unchanged -- skipping is exact.
+ * The tap range is widened by one texel each side for the HW path's fused coordinate. */
+__global__ void __launch_bounds__(256) k_classify(const float2 *__restrict__ ranges, int ncells,
+                                                  const float4 *__restrict__ lut_pad, int nlut, float min_density,
+                                                  float max_density, uint32_t *occ, unsigned long long *empty_count)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    bool occupied = false;
+    if (c < ncells) {
+        const float range = max_density - min_density;
+        const float2 r = ranges[c];
+        occupied = true;
+        if (range > 0.0f && r.x == r.x && r.y == r.y) {
+            int k0 = lut_tap(r.x, min_density, range, (float)nlut) - 1;
+            int k1 = lut_tap(r.y, min_density, range, (float)nlut) + 2;
+            k0 = max(k0, 0), k1 = min(k1, nlut + 2);
+            occupied = false;
+            for (int k = k0; k <= k1; k++)
+                if (lut_pad[k].w != 0.0f) {
+                    occupied = true;
+                    break;
+                }
+        }
+    }
+    const uint32_t word = __ballot_sync(0xffffffffu, occupied);
+    if ((threadIdx.x & 31) == 0) {
+        occ[c >> 5] = word;
+        const int live = min(32, ncells - c);
+        if (live > 0) {
+            const uint32_t mask = live == 32 ? 0xffffffffu : ((1u << live) - 1u);
+            atomicAdd(empty_count, (unsigned long long)__popc(~word & mask));
+        }
+    }
+}
+
+/* ------------------------------------------------------------------ synth -- */
+
+__device__ __forceinline__ uint32_t hash_u32(uint32_t h)
+{
+    h ^= h >> 16;
+    h *= 0x7feb352du;
+    h ^= h >> 15;
+    h *= 0x846ca68bu;
+    h ^= h >> 16;
+    return h;
+}
+
+__device__ __forceinline__ float lattice(uint32_t seed, int ix, int iy, int iz, int oct)
+{
+    const uint32_t h = seed ^ ((uint32_t)ix * 0x8da6b343u) ^ ((uint32_t)iy * 0xd8163841u) ^
+                       ((uint32_t)iz * 0xcb1ab31fu) ^ ((uint32_t)oct * 0x9e3779b9u);
+    return (float)(hash_u32(h) >> 8) * (1.0f / 16777216.0f);
+}
+
+__device__ __forceinline__ float fade(float t) { return t * t * (3.0f - 2.0f * t); }
+__device__ __forceinline__ float mixf(float a, float b, float t) { return a + t * (b - a); }
+
+__device__ float value_noise(uint32_t seed, float x, float y, float z, int oct)
+{
+    const float fx = floorf(x), fy = floorf(y), fz = floorf(z);
+    const int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    const float tx = fade(x - fx), ty = fade(y - fy), tz = fade(z - fz);
+    const float c000 = lattice(seed, ix, iy, iz, oct), c100 = lattice(seed, ix + 1, iy, iz, oct);
+    const float c010 = lattice(seed, ix, iy + 1, iz, oct), c110 = lattice(seed, ix + 1, iy + 1, iz, oct);
+    const float c001 = lattice(seed, ix, iy, iz + 1, oct), c101 = lattice(seed, ix + 1, iy, iz + 1, oct);
+    const float c011 = lattice(seed, ix, iy + 1, iz + 1, oct), c111 = lattice(seed, ix + 1, iy + 1, iz + 1, oct);
+    return mixf(mixf(mixf(c000, c100, tx), mixf(c010, c110, tx), ty), mixf(mixf(c001, c101, tx), mixf(c011, c111, tx), ty),
+                tz);
+}
+
+/* 5-octave value-noise fBm, lacunarity 2, gain 0.5, contrast-stretched about 0.5 */
+__device__ float fbm(uint32_t seed, float vx, float vy, float vz, float inv_period)
+{
+    float sum = 0.0f, amp = 1.0f, norm = 0.0f, f = inv_period;
+    for (int o = 0; o < 5; o++) {
+        sum += amp * value_noise(seed, vx * f, vy * f, vz * f, o);
+        norm += amp;
+        amp *= 0.5f;
+        f *= 2.0f;
+    }
+    const float v = 0.5f + (sum / norm - 0.5f) * 2.2f;
+    return v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+}
+
+/* Marschner-Lobb test signal, f_M = 6, alpha = 0.25 */
+__device__ float marschner_lobb(float x, float y, float z)
+{
+    const float PI = 3.14159265358979323846f, fM = 6.0f, al = 0.25f;
+    const float r = sqrtf(x * x + y * y);
+    const float pr = cosf(2.0f * PI * fM * cosf(PI * r / 2.0f));
+    return (1.0f - sinf(PI * z / 2.0f) + al * (1.0f + pr)) / (2.0f * (1.0f + al));
+}
+
+#define VR_NBLOBS 64
+struct Blobs {
+    float cx[VR_NBLOBS], cy[VR_NBLOBS], cz[VR_NBLOBS], sigma[VR_NBLOBS], amp[VR_NBLOBS];
+};
+
+/* sum of truncated Gaussians on an exactly-zero background */
+__device__ float blobs_at(const Blobs &b, float x, float y, float z)
+{
+    const float cut = 2.5f, floor_v = 0.0439369336f; /* exp(-cut^2/2) */
+    float sum = 0.0f;
+    for (int i = 0; i < VR_NBLOBS; i++) {
+        const float dx = x - b.cx[i], dy = y - b.cy[i], dz = z - b.cz[i];
+        const float d2 = dx * dx + dy * dy + dz * dz;
+        const float s2 = b.sigma[i] * b.sigma[i];
+        if (d2 < cut * cut * s2) sum += b.amp[i] * (expf(-0.5f * d2 / s2) - floor_v) / (1.0f - floor_v);
+    }
+    return sum > 1.0f ? 1.0f : sum;
+}
+
+struct SynthParams {
+    void *out;
+    int kind, dtype;
+    uint32_t seed;
+    uint32_t nx, ny, nz;    /* local extent written */
+    int ox, oy, oz;         /* global index of local voxel 0 */
+    uint32_t fx, fy, fz;    /* full grid */
+    float inv_period;
+};
+
+__global__ void __launch_bounds__(256) k_synth(const __grid_constant__ SynthParams s, const __grid_constant__ Blobs blobs)
+{
+    const size_t total = (size_t)s.nx * s.ny * s.nz;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t li = (uint32_t)(idx % s.nx), lj = (uint32_t)((idx / s.nx) % s.ny), lk = (uint32_t)(idx / ((size_t)s.nx * s.ny));
+        const int i = (int)li + s.ox, j = (int)lj + s.oy, k = (int)lk + s.oz;
+        float v = 0.0f;
+        const bool inside = i >= 0 && j >= 0 && k >= 0 && (uint32_t)i < s.fx && (uint32_t)j < s.fy && (uint32_t)k < s.fz;
+        if (inside) {
+            if (s.kind == VR_SYNTH_MARSCHNER_LOBB) {
+                const float x = -1.0f + 2.0f * ((float)i + 0.5f) / (float)s.fx;
+                const float y = -1.0f + 2.0f * ((float)j + 0.5f) / (float)s.fy;
+                const float z = -1.0f + 2.0f * ((float)k + 0.5f) / (float)s.fz;
+                v = marschner_lobb(x, y, z);
+            } else if (s.kind == VR_SYNTH_FBM) {
+                v = fbm(s.seed, (float)i + 0.5f, (float)j + 0.5f, (float)k + 0.5f, s.inv_period);
+            } else {
+                v = blobs_at(blobs, (float)i + 0.5f, (float)j + 0.5f, (float)k + 0.5f);
+            }
+        }
+        switch (s.dtype) {
+            case VR_U8: reinterpret_cast<unsigned char *>(s.out)[idx] = (unsigned char)(v * 255.0f + 0.5f); break;
+            case VR_U16: reinterpret_cast<unsigned short *>(s.out)[idx] = (unsigned short)(v * 65535.0f + 0.5f); break;
+            default: reinterpret_cast<float *>(s.out)[idx] = v; break;
+        }
+    }
+}
+
+inline uint64_t splitmix64(uint64_t *s)
+{
+    uint64_t z = (*s += 0x9e3779b97f4a7c15ull);
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+inline float rnd01(uint64_t *s) { return (float)(splitmix64(s) >> 40) * (1.0f / 16777216.0f); }
+
+}  // namespace
+
+cudaError_t vr_k0_global_minmax(const void *dev, int dtype, size_t n, float *h_min, float *h_max, cudaStream_t s)
+{
+    int dev_id = 0, sms = 148;
+    cudaGetDevice(&dev_id);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev_id);
+    const int blocks = sms * 8;
+    float2 *d_partial = nullptr;
+    cudaError_t e = cudaMalloc(&d_partial, sizeof(float2) * blocks);
+    if (e != cudaSuccess) return e;
+    switch (dtype) {
+        case VR_U8: k_global_minmax<unsigned char><<<blocks, 256, 0, s>>>((const unsigned char *)dev, n, d_partial); break;
+        case VR_U16: k_global_minmax<unsigned short><<<blocks, 256, 0, s>>>((const unsigned short *)dev, n, d_partial); break;
+        default: k_global_minmax<float><<<blocks, 256, 0, s>>>((const float *)dev, n, d_partial); break;
+    }
+    e = cudaGetLastError();
+    std::vector<float2> h(blocks);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h.data(), d_partial, sizeof(float2) * blocks, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d_partial);
+    if (e != cudaSuccess) return e;
+    float mn = h[0].x, mx = h[0].y;
+    for (int i = 1; i < blocks; i++) mn = fminf(mn, h[i].x), mx = fmaxf(mx, h[i].y);
+    *h_min = mn, *h_max = mx;
+    return cudaSuccess;
+}
+
+cudaError_t vr_k0_cell_ranges(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int cell,
+                              const int occ_n[3], float2 *d_ranges, cudaStream_t s)
+{
+    const int ncells = occ_n[0] * occ_n[1] * occ_n[2];
+    k_cell_ranges<<<ncells, 64, 0, s>>>(dev, dtype, (int)nx, (int)ny, (int)nz, cell, occ_n[0], occ_n[1], d_ranges);
+    return cudaGetLastError();
+}
+
+cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const float4 *d_lut_pad, uint32_t nlut,
+                           float min_density, float max_density, uint32_t *d_occ, int occ_words,
+                           unsigned long long *d_empty_count, cudaStream_t s)
+{
+    const int ncells = occ_n[0] * occ_n[1] * occ_n[2];
+    cudaError_t e = cudaMemsetAsync(d_empty_count, 0, sizeof(unsigned long long), s);
+    if (e != cudaSuccess) return e;
+    const int threads = occ_words * 32;
+    k_classify<<<(threads + 255) / 256, 256, 0, s>>>(d_ranges, ncells, d_lut_pad, (int)nlut, min_density, max_density,
+                                                     d_occ, d_empty_count);
+    return cudaGetLastError();
+}
+
+cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
+                        const int org[3], const uint32_t full[3], cudaStream_t s)
+{
+    SynthParams sp;
+    sp.out = dev, sp.kind = kind, sp.dtype = dtype, sp.seed = seed;
+    sp.nx = nx, sp.ny = ny, sp.nz = nz;
+    sp.ox = org[0], sp.oy = org[1], sp.oz = org[2];
+    sp.fx = full[0], sp.fy = full[1], sp.fz = full[2];
+    float period = (float)full[0] / 8.0f;
+    if (period < 2.0f) period = 2.0f;
+    sp.inv_period = 1.0f / period;
+    Blobs b;
+    {
+        /* blob table: centres, sigmas (8..40 voxels at 1024^3, scaled with the grid), amplitudes */
+        uint64_t st = (uint64_t)seed * 0x100000001b3ull + 0x5eedull;
+        const float n = (float)full[0], scale = n / 1024.0f;
+        for (int i = 0; i < VR_NBLOBS; i++) {
+            b.cx[i] = (0.12f + 0.76f * rnd01(&st)) * n;
+            b.cy[i] = (0.12f + 0.76f * rnd01(&st)) * n;
+            b.cz[i] = (0.12f + 0.76f * rnd01(&st)) * n;
+            b.sigma[i] = (8.0f + 32.0f * rnd01(&st)) * scale;
+            b.amp[i] = 0.35f + 0.65f * rnd01(&st);
+        }
+    }
+    int dev_id = 0, sms = 148;
+    cudaGetDevice(&dev_id);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev_id);
+    const size_t total = (size_t)nx * ny * nz;
+    size_t blocks = (total + 255) / 256;
+    if (blocks > (size_t)sms * 32) blocks = (size_t)sms * 32;
+    if (blocks == 0) blocks = 1;
+    k_synth<<<(unsigned)blocks, 256, 0, s>>>(sp, b);
+    return cudaGetLastError();
+}

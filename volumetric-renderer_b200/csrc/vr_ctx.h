@@ -1,0 +1,132 @@
+/*
+ * vr_ctx.h -- internal state of a render context and the kernel parameter blocks.
+ * Not part of the ABI (include/vr.h is).
+ */
+#ifndef VR_CTX_H
+#define VR_CTX_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/vr.h"
+
+#define VR_TILE 16        /* a CTA marches a 16x16 pixel tile: 8 warps of 8x4 pixels */
+#define VR_CTA_THREADS 256
+#define VR_BATCH 4        /* steps whose fetches are issued back to back before compositing */
+#define VR_OCC_MAX_AXIS 64 /* occupancy grid is at most 64^3 cells = 32 KiB of bits in shared memory */
+#define VR_CLEAR_RGB 0.11f /* offscreen_pass.cpp:171 */
+
+/* Everything K1 needs, passed by value as a __grid_constant__ kernel parameter. */
+struct MarchParams {
+    /* S2: columns of inverse(proj*view) (fp32), pixel->NDC scale, camera */
+    float c0[4], c1[4], c2[4], c3[4];
+    float sx, sy;
+    float cam[3];
+    uint32_t W, H;
+    /* S3/S5 uniforms */
+    float min_density, max_density, range;
+    float min_slice[3], max_slice[3];
+    int steps;
+    float step_size;
+    /* S4: volume */
+    cudaTextureObject_t tex_lin; /* normalised coords, linear, border 0, normalised-float read for u8/u16 */
+    cudaTextureObject_t tex_pt;  /* texel coords, point, border 0, element read */
+    float dims[3];      /* GLOBAL grid size as float */
+    int org[3];         /* global voxel index of local texel 0 (0 unless sort-last) */
+    float forg[3];      /* same as float */
+    float inv_ldims[3]; /* 1 / local texture size */
+    float dscale;       /* normalised-float texel -> raw value: 255, 65535 or 1 */
+    int dtype;          /* vr_dtype of the texels (point fetches read the element type) */
+    /* sort-last ownership, texture space, half-open [lo, hi) */
+    float own_lo[3], own_hi[3];
+    /* S6: LUT, decoded to linear fp32, padded: P[k] = L[clamp(k-1, 0, n-1)], k = 0..n+2 (n+3 entries) */
+    const float4 *lut_pad;
+    const float4 *lut_dif; /* D[k] = P[k+1] - P[k], k = 0..n+1 (n+2 entries) */
+    uint32_t nlut;
+    float lutA, lutB; /* HW sampler: padded LUT coordinate = texel * lutA + lutB */
+    /* empty-space skipping: bit per cell, x fastest */
+    const uint32_t *occ;
+    int occ_n[3];
+    int occ_words;
+    float occ_scale[3], occ_off[3]; /* cell = int(pos * occ_scale - occ_off) */
+    /* outputs */
+    uchar4 *out;
+    float4 *raw;
+    unsigned long long *counters; /* [4]: covered, n_ref, n_inslice, n_fetch */
+    float ert_eps;
+    /* screen partition (sort-first): partition tiles of pt_px pixels, round-robin */
+    uint32_t pt_px, pt_nx, pt_ny, pt_rank, pt_nranks, pt_sub; /* pt_sub = pt_px / VR_TILE */
+};
+
+struct vr_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    uint32_t W = 0, H = 0;
+    uchar4 *d_image = nullptr;
+    float4 *d_raw = nullptr;
+    unsigned long long *d_counters = nullptr;
+    unsigned long long *h_counters = nullptr; /* pinned */
+
+    /* camera / uniforms (host copy of the UBO, offscreen_pass.h:29-37) */
+    float view[16], proj[16], cam_pos[3];
+    float min_density = 0.f, max_density = 0.f;
+    float min_slice[3] = {0.f, 0.f, 0.f}, max_slice[3] = {1.f, 1.f, 1.f};
+    float ray_dist = 1.8f, step_size = 0.005f;
+    bool ray_valid = false; /* inverse(proj*view) exists */
+    float rc[4][4];         /* columns of the inverse */
+
+    /* volume */
+    int dtype = VR_F32;
+    uint32_t nx = 0, ny = 0, nz = 0; /* local texture size */
+    cudaArray_t array = nullptr;
+    cudaTextureObject_t tex_lin = 0, tex_pt = 0;
+
+    /* sort-last */
+    bool sort_last = false;
+    uint32_t full[3] = {0, 0, 0}, own_org[3] = {0, 0, 0}, own_dims[3] = {0, 0, 0};
+    int tex_org[3] = {0, 0, 0}; /* global voxel index of local texel 0 */
+
+    /* LUT */
+    uint32_t nlut = 0;
+    uint32_t *h_lut = nullptr; /* packed, as set */
+    float4 *d_lut_pad = nullptr, *d_lut_dif = nullptr;
+
+    /* occupancy */
+    int occ_n[3] = {0, 0, 0};
+    int occ_cell = 0; /* voxels per cell edge (power of two) */
+    float2 *d_cell_range = nullptr; /* per cell (min,max) incl. 1-voxel apron and border zeros */
+    uint32_t *d_occ = nullptr;
+    int occ_words = 0;
+    bool occ_dirty = true;
+    uint64_t occ_empty_cells = 0;
+
+    vr_options opt;
+    uint32_t pt_px = 64, pt_rank = 0, pt_nranks = 1;
+    cudaStream_t last_stream = nullptr;
+};
+
+/* ---- kernels / device-side stages (each .cu implements its own) ---- */
+
+/* K1 (march.cu) */
+cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, cudaStream_t s);
+size_t vr_march_smem_bytes(const MarchParams &p, bool ess);
+
+/* K0 (volume.cu) */
+cudaError_t vr_k0_global_minmax(const void *dev, int dtype, size_t n, float *h_min, float *h_max, cudaStream_t s);
+cudaError_t vr_k0_cell_ranges(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int cell,
+                              const int occ_n[3], float2 *d_ranges, cudaStream_t s);
+cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const float4 *d_lut_pad, uint32_t nlut,
+                           float min_density, float max_density, uint32_t *d_occ, int occ_words,
+                           unsigned long long *d_empty_count, cudaStream_t s);
+cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
+                        const int org[3], const uint32_t full[3], cudaStream_t s);
+
+/* K2 (composite.cu) */
+cudaError_t vr_launch_composite(const float4 *const *d_parts_table, uint32_t nparts, uint64_t begin, uint64_t end,
+                                uchar4 *out, float4 *raw_out, cudaStream_t s);
+
+#endif
