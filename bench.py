@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric on BASELINE.json's config.
+
+Metric: reference-equivalent ray samples/s (= iterations of res/shaders/volume.frag:33-48 that pass
+the bounds test, what the reference shader would execute for the same frames) on config C2:
+512^3 uint16 fractal-noise volume, 1920x1080, 360-frame orbit (frame k = default camera after k x
+Camera::rotate({4,0})), transfer function TF-B.
+
+A step = one frame = one launch of K1 (march).  N GPUs: the orbit's frames are independent units;
+rank r renders frames r, r+N, ... (K frames per rank, weak scaling, no data-path collective).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            this backend
+  python bench.py --impl reference [...]                         the reference's own CPU code
+                                                                 (oracle/_ref: its shader compiled as C++)
+Other workloads (not the driver's line): --workload c1|c3|c4|c5, see DESIGN.md.
+"""
+import argparse
+import json
+import math
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (synth kind, dtype name, n, W, H, TF, description)
+    "c1": (0, "u8", 256, 512, 512, "A", "256^3 u8 Marschner-Lobb, 512x512, TF-A (reference default gradient)"),
+    "c2": (1, "u16", 512, 1920, 1080, "B", "512^3 u16 fBm, 1920x1080, 360-frame orbit, TF-B"),
+    "c3": (2, "u16", 1024, 3840, 2160, "C", "1024^3 u16 sparse blobs, 3840x2160, 360-frame orbit, TF-C"),
+}
+ORBIT_FRAMES = 360
+
+
+# transfer functions of SURVEY.md section 8(d): (colour markers (loc, r, g, b), alpha markers (loc, a))
+TF_MARKERS = {
+    "A": ([(0.0, 0, 0, 0), (1.0, 1, 1, 1)], [(0.0, 1.0), (1.0, 1.0)]),  # gradient.cpp:64-70 default
+    "B": ([(0.0, 0, 0, 0.5), (0.5, 1, 0.5, 0), (1.0, 1, 1, 1)], [(0.0, 0.0), (0.3, 0.0), (1.0, 0.08)]),
+    "C": ([(0.0, 0, 0, 0.5), (0.5, 1, 0.5, 0), (1.0, 1, 1, 1)], [(0.0, 0.0), (0.05, 0.0), (1.0, 0.6)]),
+}
+
+
+def tf_markers(name):
+    return TF_MARKERS[name]
+
+
+def product_lut(vr, name):
+    cm, am = tf_markers(name)
+    return vr.Gradient([(m[0], tuple(m[1:])) for m in cm], [tuple(m) for m in am]).discretize(256)
+
+
+def orbit_uniforms(vr, w, h, frames):
+    """(view, proj, camera_position) of orbit frame k, k = 0..frames-1."""
+    cam, proj, out = vr.Camera(), vr.projection(w, h), []
+    for _ in range(frames):
+        out.append((cam.get_view(), proj, cam.get_position()))
+        cam.rotate((4.0, 0.0))
+    return out
+
+
+class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons of one GPU, sampled with NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz, self.ok = index, [], set(), False, None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def sample(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for name, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("hw_thermal_slowdown", 0x40),
+                              ("sw_thermal_slowdown", 0x20), ("hw_power_brake_slowdown", 0x80)):
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def run(self):
+        while not self.stop_flag:
+            self.sample()
+            time.sleep(0.002)
+
+    def result(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def physical_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import volumetric_renderer_b200 as vr  # raises if libvr_b200.so is missing: no fallback
+
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this backend has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    kind, dname, n, W, H, tfn, desc = WORKLOADS[args.workload]
+    dtype = {"u8": vr.U8, "u16": vr.U16, "f32": vr.F32}[dname]
+    esz = {"u8": 1, "u16": 2, "f32": 4}[dname]
+    K, Wu = args.steps, args.warmup
+
+    op = vr.OffscreenPass(W, H, device=local)
+    op.synth_volume(kind, {"c1": 0x5EED0001, "c2": 0x5EED0002, "c3": 0x5EED0003}[args.workload], dtype, n)
+    lut = product_lut(vr, tfn)
+    op.transfer_function_changed(lut)
+    prod = dict(sampler=vr.SAMPLER_EXACT if args.exact else vr.SAMPLER_HW, empty_skip=int(not args.no_ess),
+                early_term=int(not args.no_ert), early_term_eps=1.0 / 1024.0)
+    uniforms = orbit_uniforms(vr, W, H, ORBIT_FRAMES)
+    my_frames = [(rank + j * world) % ORBIT_FRAMES for j in range(K)]
+    warm_frames = [(rank + j * world) % ORBIT_FRAMES for j in range(Wu)]
+    stream = torch.cuda.Stream()
+    sp = stream.cuda_stream
+
+    # ---- untimed: work per frame (reference-equivalent samples, executed fetches) ----------------
+    n_ref, n_exec = {}, {}
+    for k in sorted(set(my_frames)):
+        op.set_uniforms(*uniforms[k])
+        op.set_options(collect_stats=1, write_raw=0, sampler=prod["sampler"], empty_skip=0, early_term=0,
+                       early_term_eps=prod["early_term_eps"])
+        op.record(sp)
+        n_ref[k] = op.stats().n_ref
+        op.set_options(collect_stats=1, **prod)
+        op.record(sp)
+        n_exec[k] = op.stats().n_fetch
+    op.set_options(collect_stats=0, **prod)
+    cells, cell_vox, empty = op.occupancy_info()
+    total_ref = sum(n_ref[k] for k in my_frames)
+    total_exec = sum(n_exec[k] for k in my_frames)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-timed: inputs resident, K launches of K1 --------------------------------------------
+    for k in warm_frames:
+        op.set_uniforms(*uniforms[k])
+        op.record(sp)
+    clocks = ClockSampler(physical_gpu_index(local))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    clocks.start()
+    ev0.record(stream)
+    for k in my_frames:
+        op.set_uniforms(*uniforms[k])
+        op.record(sp)
+    ev1.record(stream)
+    clocks.sample()  # at least one sample while the queue is still draining
+    barrier()
+    clocks.stop_flag = True
+    dev_ms = ev0.elapsed_time(ev1)
+
+    # ---- end to end through the public API: host uniforms in, RGBA8 frame out to pinned host memory ---
+    host = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True)
+    for k in warm_frames[:3]:
+        op.set_uniforms(*uniforms[k])
+        op.record(sp)
+        op.download_async(host.data_ptr(), sp)
+        stream.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for k in my_frames:
+        op.set_uniforms(*uniforms[k])      # 192-byte uniform block: the step's input, goes down with the launch
+        op.record(sp)
+        op.download_async(host.data_ptr(), sp)
+        stream.synchronize()               # the frame is in host memory before the next step starts
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    checksum = int(host.view(torch.int32).sum().item())
+
+    t = torch.tensor([dev_ms, e2e_ms, float(total_ref), float(total_exec)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = t.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = t.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        dev_ms, e2e_ms = mx[0].item(), mx[1].item()
+        all_ref, all_exec = sm[2].item(), sm[3].item()
+    else:
+        all_ref, all_exec = float(total_ref), float(total_exec)
+
+    line = None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        ncell = cells[0] * cells[1] * cells[2]
+        occ_frac = (ncell - empty) / ncell if prod["empty_skip"] else 1.0
+        alg_bytes = n ** 3 * esz * occ_frac + W * H * 4 + 1024   # touched bricks once + RGBA8 out + LUT
+        step_s = dev_ms * 1e-3 / K                                # one launch per step
+        tex_peak = vr.bench_tex_peak(local, dtype, True)
+        exec_rate = (total_exec / K) / step_s
+        line = {
+            "metric": "ray samples/s @1920x1080, 512^3 u16" if args.workload == "c2" else f"ray samples/s ({args.workload})",
+            "value": all_ref / (dev_ms * 1e-3), "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wu,
+            "ms_per_step": dev_ms / K, "fps": world * K / (dev_ms * 1e-3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {desc}", "volume_dtype": dname,
+                       "sampler": "exact(8 point fetches + fp32 lerp)" if args.exact else "hw trilinear",
+                       "empty_space_skipping": bool(prod["empty_skip"]), "early_ray_termination_eps": prod["early_term_eps"] if prod["early_term"] else 0,
+                       "l2": f"inputs larger than L2 ({n ** 3 * esz / 2 ** 20:.0f} MiB volume, no flush)",
+                       "parallelism": f"frames of the orbit dealt round-robin to {world} GPU(s), no collective"},
+            "executed_samples_per_s": all_exec / (dev_ms * 1e-3),
+            "roofline": {"bound": "hbm", "achieved": alg_bytes / step_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": alg_bytes / step_s / 1e9 / hbm_peak, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback",
+                         "algorithmic_bytes_per_launch": alg_bytes},
+            "roofline_tex": {"bound": "tex", "achieved": exec_rate / 1e9, "peak": tex_peak / 1e9, "unit": "Gfetch/s",
+                             "frac": exec_rate / tex_peak,
+                             "peak_source": "vr_bench_tex_peak: L1-resident 3-D trilinear fetches, measured in this run"},
+            "e2e": {"value": all_ref / (e2e_ms * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": 192,
+                    "d2h_bytes_per_step": W * H * 4, "ms_per_step": e2e_ms / K, "fps": world * K / (e2e_ms * 1e-3),
+                    "frame_checksum": checksum},
+            "gpu_launches": K,
+            "clocks": clocks.result(),
+            "occupancy": {"cells": list(cells), "cell_voxels": cell_vox, "empty_cells": int(empty)},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(op, vr, uniforms, lut, W, H, my_frames[0], sp)
+    op.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line:
+        print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs.  The ONLY places bench.py touches oracle/: the reported cpu_baseline and --impl reference.
+# ------------------------------------------------------------------------------------------------
+
+def load_cpu_oracle():
+    """oracle/_ref (the reference's shader, camera and gradient compiled as CPU code) when it is
+    there, else the plain-C port."""
+    from oracle import pyoracle
+    try:
+        return pyoracle.Oracle("reference"), "reference"
+    except Exception:
+        return pyoracle.Oracle("port"), "port"
+
+
+def oracle_orbit_camera(o, k):
+    cam = o.camera()
+    for _ in range(k):
+        cam.rotate(4.0, 0.0)
+    return cam
+
+
+def timed_rows(o, frame, vol, lut, stride, start=0):
+    t0 = time.perf_counter()
+    r = o.render(frame, vol, lut, row_start=start, row_stride=stride)
+    return time.perf_counter() - t0, r
+
+
+def cpu_baseline(op, vr, uniforms, lut, W, H, k, sp, budget_s=15.0):
+    """The same frame on the host cores: a bounded sample (every s-th row) sized for ~budget_s."""
+    import numpy as np
+    o, kind = load_cpu_oracle()
+    vol = op.download_volume()
+    _, _, mn, mx = op.volume_info()
+    frame = o.frame(W, H, oracle_orbit_camera(o, k), mn, mx)
+    t_probe, _ = timed_rows(o, frame, vol, lut, 64)
+    stride = max(1, int(math.ceil(t_probe * 64 / budget_s)))
+    t, r = timed_rows(o, frame, vol, lut, stride)
+    # parity of the very frame the GPU renders, on the sampled rows (tolerance: tests/common.py)
+    op.set_uniforms(*uniforms[k])
+    op.record(sp)
+    img = op.download()
+    a, b = img[0::stride].astype(np.int16), r["rgba8"][0::stride].astype(np.int16)
+    d = np.abs(a - b).max(axis=-1).ravel()
+    mse = float(np.mean((a - b).astype(np.float64) ** 2))
+    return {"value": r["stats"].n_ref / t, "unit": "samples/s", "cores": os.cpu_count(), "kind": kind,
+            "sample": f"orbit frame {k}, every {stride}-th row of {W}x{H} ({r['stats'].n_ref} samples, {t:.2f} s, OpenMP all cores)",
+            "parity_vs_gpu_frame": {"p99.9_abs_diff_of_255": float(np.percentile(d, 99.9)),
+                                    "psnr_db": None if mse == 0 else 10.0 * math.log10(255.0 ** 2 / mse)}}
+
+
+def run_reference(args):
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    if rank != 0:
+        return
+    import numpy as np
+    from oracle import pyoracle
+    o, kind_name = load_cpu_oracle()
+    port = pyoracle.Oracle("port")  # synthetic input generator (data only)
+    kind, dname, n, W, H, tfn, desc = WORKLOADS[args.workload]
+    np_dt = {"u8": np.uint8, "u16": np.uint16, "f32": np.float32}[dname]
+    vol = port.synth(kind, {"c1": 0x5EED0001, "c2": 0x5EED0002, "c3": 0x5EED0003}[args.workload], np_dt, n)
+    mn, mx = float(vol.min()), float(vol.max())
+    lut = o.discretize(*tf_markers(tfn))
+    K, Wu = args.steps, args.warmup
+    cams = {}
+
+    def frame_of(k):
+        if k not in cams:
+            cams[k] = o.frame(W, H, oracle_orbit_camera(o, k), mn, mx)
+        return cams[k]
+
+    t_probe, _ = timed_rows(o, frame_of(0), vol, lut, 32)
+    budget = 150.0
+    stride = max(1, int(math.ceil(t_probe * 32 * (K + Wu) / budget)))
+    for j in range(Wu):
+        timed_rows(o, frame_of((j * world) % ORBIT_FRAMES), vol, lut, stride, start=j % stride)
+    total, t0 = 0, time.perf_counter()
+    for j in range(K):
+        _, r = timed_rows(o, frame_of((j * world) % ORBIT_FRAMES), vol, lut, stride, start=j % stride)
+        total += r["stats"].n_ref
+    dt = time.perf_counter() - t0
+    v = total / dt
+    sample = f"each step = every {stride}-th row of one {W}x{H} orbit frame ({total // K} samples/step), OpenMP on all cores"
+    print(json.dumps({
+        "impl": "reference", "metric": "ray samples/s @1920x1080, 512^3 u16" if args.workload == "c2" else f"ray samples/s ({args.workload})",
+        "value": v, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wu, "ms_per_step": dt * 1e3 / K,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {desc}", "volume_dtype": dname,
+                   "what": "reference shader body (res/shaders/volume.frag) compiled as C++ with its camera and gradient; "
+                           "no graphics stack on this box, so this CPU build is the reference arm" if kind_name == "reference"
+                           else "plain-C port of the reference shader (oracle/_ref missing)"},
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": os.cpu_count(), "kind": kind_name, "sample": sample},
+        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=ORBIT_FRAMES)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
+    ap.add_argument("--exact", action="store_true", help="verification sampler instead of hardware trilinear")
+    ap.add_argument("--no-ess", action="store_true")
+    ap.add_argument("--no-ert", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

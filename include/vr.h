@@ -121,6 +121,10 @@ int vr_set_volume_device(vr_ctx *ctx, const void *dev_data, int dtype, uint32_t 
  * native reader: 3-D scalar NRRD/NHDR, raw/ascii/hex encoding, any of the ten scalar
  * types (u8/u16 stay native on the device, the rest are widened to float like :49-77). */
 int vr_load_nrrd(vr_ctx *ctx, const char *path);
+/* The reader alone, no context and no GPU: dtype/dims/data as vr_load_nrrd would upload them.
+ * *data is malloc'd (release with vr_free_host); errbuf receives the message on failure. */
+int vr_nrrd_read_host(const char *path, int *dtype, uint32_t dims[3], void **data, char *errbuf, size_t errbuf_len);
+void vr_free_host(void *p);
 int vr_get_volume_info(const vr_ctx *ctx, int *dtype, uint32_t dims[3], float *min_density, float *max_density);
 /* Overwrite ubo.min_density / max_density (offscreen_pass.cpp:265-266), e.g. with the global
  * range after each sort-last rank measured its own sub-volume. */

@@ -72,6 +72,8 @@ class Oracle:
         lib.vro_render.restype = C.c_int
         lib.vro_render.argtypes = [C.POINTER(Frame), C.POINTER(Volume), C.c_void_p, C.c_uint32,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(Stats), C.c_int]
+        lib.vro_render_rows.restype = C.c_int
+        lib.vro_render_rows.argtypes = lib.vro_render.argtypes + [C.c_uint32, C.c_uint32]
         lib.vro_camera_new.restype = C.c_void_p
         lib.vro_camera_free.argtypes = [C.c_void_p]
         lib.vro_camera_rotate.argtypes = [C.c_void_p, C.c_float, C.c_float]
@@ -120,20 +122,21 @@ class Oracle:
 
     # -- render ----------------------------------------------------------------
     def render(self, frame: Frame, volume: np.ndarray, lut: np.ndarray, want_raw=False, want_iters=False,
-               nthreads=0):
+               nthreads=0, row_start=0, row_stride=1):
         """volume: ndarray [nz, ny, nx] (x fastest) of uint8/uint16/float32.
         Returns dict(rgba8=[H,W,4] u8, raw=[H,W,4] f32 | None, iters=[H,W] u16 | None, stats=Stats)"""
         assert volume.ndim == 3 and volume.flags.c_contiguous
         vol = Volume(volume.ctypes.data, _DTYPE_OF[volume.dtype], volume.shape[2], volume.shape[1], volume.shape[0])
         lut = np.ascontiguousarray(lut, np.uint32)
         H, W = frame.height, frame.width
-        rgba8 = np.empty((H, W, 4), np.uint8)
-        raw = np.empty((H, W, 4), np.float32) if want_raw else None
-        iters = np.empty((H, W), np.uint16) if want_iters else None
+        rgba8 = np.zeros((H, W, 4), np.uint8)
+        raw = np.zeros((H, W, 4), np.float32) if want_raw else None
+        iters = np.zeros((H, W), np.uint16) if want_iters else None
         st = Stats()
-        rc = self.lib.vro_render(C.byref(frame), C.byref(vol), lut.ctypes.data, len(lut), rgba8.ctypes.data,
-                                 raw.ctypes.data if want_raw else None, iters.ctypes.data if want_iters else None,
-                                 C.byref(st), nthreads)
+        rc = self.lib.vro_render_rows(C.byref(frame), C.byref(vol), lut.ctypes.data, len(lut), rgba8.ctypes.data,
+                                      raw.ctypes.data if want_raw else None,
+                                      iters.ctypes.data if want_iters else None, C.byref(st), nthreads,
+                                      row_start, row_stride)
         if rc != 0:
             raise RuntimeError(f"vro_render failed: {rc}")
         return dict(rgba8=rgba8, raw=raw, iters=iters, stats=st)

@@ -59,7 +59,14 @@ static uint32_t count_bounds_iterations(const glm::vec3 &frag, const glm::vec3 &
 extern "C" int vro_render(const vro_frame *f, const vro_volume *vol, const uint32_t *lut, uint32_t nlut,
                           uint8_t *rgba8, float *raw, uint16_t *iters, vro_stats *stats, int nthreads)
 {
-    if (!f || !vol || !lut || nlut == 0 || !rgba8 || f->width == 0 || f->height == 0) return -1;
+    return vro_render_rows(f, vol, lut, nlut, rgba8, raw, iters, stats, nthreads, 0, 1);
+}
+
+extern "C" int vro_render_rows(const vro_frame *f, const vro_volume *vol, const uint32_t *lut, uint32_t nlut,
+                               uint8_t *rgba8, float *raw, uint16_t *iters, vro_stats *stats, int nthreads,
+                               uint32_t row_start, uint32_t row_stride)
+{
+    if (!f || !vol || !lut || nlut == 0 || !rgba8 || f->width == 0 || f->height == 0 || row_stride == 0) return -1;
     /* the shader's march constants are literals (volume.frag:29-30) */
     if (f->ray_dist != 1.8f || f->step_size != 0.005f) return -4;
     vro_rayctx rc;
@@ -76,8 +83,10 @@ extern "C" int vro_render(const vro_frame *f, const vro_volume *vol, const uint3
     nthreads = 1;
 #endif
     const long W = f->width, H = f->height;
+    const long nrows = ((long)H - (long)row_start + (long)row_stride - 1) / (long)row_stride;
 #pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads) reduction(+ : covered, n_ref, n_in)
-    for (long py = 0; py < H; py++) {
+    for (long row = 0; row < nrows; row++) {
+        const long py = (long)row_start + row * (long)row_stride;
         for (long px = 0; px < W; px++) {
             size_t p = (size_t)py * W + px;
             float frag[3], tex[3];

@@ -66,6 +66,13 @@ const char *vro_kind(void);
 int vro_render(const vro_frame *frame, const vro_volume *vol, const uint32_t *lut, uint32_t nlut,
                uint8_t *rgba8, float *raw, uint16_t *iters, vro_stats *stats, int nthreads);
 
+/* Same, but only rows row_start, row_start + row_stride, ... are rendered (other rows of the
+ * outputs are left untouched; stats count the rendered rows only).  A bounded sample of a frame
+ * for the timed CPU baseline of bench.py. */
+int vro_render_rows(const vro_frame *frame, const vro_volume *vol, const uint32_t *lut, uint32_t nlut,
+                    uint8_t *rgba8, float *raw, uint16_t *iters, vro_stats *stats, int nthreads,
+                    uint32_t row_start, uint32_t row_stride);
+
 /* Orbit camera (src/scene/camera.cpp:7-48). */
 typedef struct vro_camera vro_camera;
 vro_camera *vro_camera_new(void);

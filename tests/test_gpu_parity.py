@@ -1,0 +1,188 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle.
+
+Bars (BASELINE.json north_star):
+  * VR_SAMPLER_EXACT: the shader's float4 output is BIT-IDENTICAL to the oracle, and so are
+    the RGBA8 image and the sample counts;
+  * VR_SAMPLER_HW (hardware trilinear, 9-bit weights): <= 2/255 per channel at the
+    99.9th-percentile pixel and >= 45 dB PSNR (tests/common.py).
+Empty-space skipping must not change a single bit; early ray termination at eps changes a
+channel by less than eps.
+"""
+import numpy as np
+import pytest
+
+from common import assert_within_tolerance, bits, oracle_frame, p999, psnr, tf, twin_cameras
+
+pytestmark = pytest.mark.gpu
+
+W, H = 160, 120
+
+
+def small_volume(port, kind, dtype, n):
+    return port.synth(kind, 0x5EED0000 + kind, dtype, n)
+
+
+def render_both(vr, port, vol, lut, moves=(), zoom=0.0, w=W, h=H, min_slice=(0, 0, 0), max_slice=(1, 1, 1),
+                minmax=None, **opts):
+    cam, ocam = twin_cameras(vr, port, moves, zoom)
+    mn, mx = minmax if minmax is not None else (float(vol.min()), float(vol.max()))
+    op = vr.OffscreenPass(w, h)
+    try:
+        op.set_options(write_raw=1, collect_stats=1, **opts)
+        op.volume_dataset_changed(vr.Dataset(vol, mn, mx))
+        op.transfer_function_changed(lut)
+        op.slicing_changed(min_slice, max_slice)
+        op.set_camera(cam)
+        op.record()
+        img, raw, st = op.download(), op.download_raw(), op.stats()
+    finally:
+        op.close()
+    o = port.render(oracle_frame(port, ocam, w, h, mn, mx, min_slice, max_slice), vol, lut, want_raw=True)
+    return img, raw, st, o
+
+
+CASES = [
+    # (volume kind, dtype, size, TF, camera moves, zoom, slices)
+    (0, np.uint8, 32, "A", [(-120, 80)], 0.0, None),
+    (0, np.uint8, 32, "B", [], 0.0, None),
+    (0, np.uint8, 32, "0", [(37, -21)], 0.0, None),
+    (1, np.uint16, 48, "B", [(-120, 80)], 0.0, None),
+    (1, np.uint16, 48, "B", [(200, 10)], 1.2, ((0.2, 0.1, 0.3), (0.9, 0.8, 0.7))),
+    (2, np.uint16, 40, "C", [(45, 30)], 0.0, None),
+    (1, np.float32, (33, 20, 7), "B", [(10, 55)], 0.5, None),
+    (0, np.uint8, 32, "A", [(15, 15)], 2.6, None),    # radius 0.4: camera inside the cube -> nothing drawn
+    (0, np.uint8, 32, "B", [(15, 15)], 2.05, None),   # radius 0.95: near plane clips part of the front face
+    (1, np.uint16, 48, "B", [(0, 0)], 0.0, ((0.0, 0.0, 0.0), (1.5, 1.5, 1.5))),  # max_slice > 1: pos == 1 samples
+]
+
+
+@pytest.mark.parametrize("case", range(len(CASES)))
+@pytest.mark.parametrize("ess", [0, 1])
+def test_exact_sampler_is_bit_identical(vr, port, case, ess):
+    kind, dtype, n, tfn, moves, zoom, slices = CASES[case]
+    vol = small_volume(port, kind, dtype, n)
+    lut = tf(port, tfn)
+    kw = dict(min_slice=slices[0], max_slice=slices[1]) if slices else {}
+    img, raw, st, o = render_both(vr, port, vol, lut, moves, zoom, sampler=vr.SAMPLER_EXACT, empty_skip=ess, **kw)
+    assert st.covered_pixels == o["stats"].covered_pixels
+    assert st.n_ref == o["stats"].n_ref
+    assert st.n_inslice == o["stats"].n_inslice
+    assert st.n_fetch <= st.n_inslice
+    if not ess:
+        assert st.n_fetch == st.n_inslice
+    assert np.array_equal(bits(raw), bits(o["raw"])), "shader output differs from the oracle"
+    assert np.array_equal(img, o["rgba8"])
+
+
+@pytest.mark.parametrize("case", range(len(CASES)))
+def test_hw_sampler_within_tolerance(vr, port, case):
+    kind, dtype, n, tfn, moves, zoom, slices = CASES[case]
+    vol = small_volume(port, kind, dtype, n)
+    lut = tf(port, tfn)
+    kw = dict(min_slice=slices[0], max_slice=slices[1]) if slices else {}
+    img, raw, st, o = render_both(vr, port, vol, lut, moves, zoom, sampler=vr.SAMPLER_HW, empty_skip=1, **kw)
+    assert st.covered_pixels == o["stats"].covered_pixels
+    assert st.n_ref == o["stats"].n_ref  # positions are bit-exact in both modes
+    assert_within_tolerance(img, o["rgba8"], f"case {case}")
+
+
+def test_empty_space_skipping_skips_and_changes_nothing(vr, port):
+    vol = small_volume(port, 2, np.uint16, 64)
+    lut = tf(port, "C")
+    a = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=0)
+    b = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=1)
+    assert np.array_equal(bits(a[1]), bits(b[1]))
+    assert np.array_equal(a[0], b[0])
+    assert b[2].n_fetch < a[2].n_fetch * 0.7, (a[2].n_fetch, b[2].n_fetch)
+
+
+def test_early_termination_error_is_bounded(vr, port):
+    vol = small_volume(port, 2, np.uint16, 64)
+    lut = tf(port, "C")
+    eps = 1.0 / 1024.0
+    a = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_EXACT, empty_skip=0)
+    b = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_EXACT, empty_skip=0, early_term=1, early_term_eps=eps)
+    assert np.abs(a[1] - b[1]).max() < eps
+    assert np.abs(a[0].astype(int) - b[0].astype(int)).max() <= 1
+    assert b[2].n_fetch < a[2].n_fetch
+
+
+def test_startup_state_matches_reference_defaults(vr, port):
+    """1x1x1 zero volume + one white opaque texel (offscreen_pass.cpp:118-119): every covered pixel
+    is white; min == max divides by zero in volume.frag:42 (NaN -> texel 0 by the oracle's definition)."""
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_options(write_raw=1)
+        op.record()
+        img = op.download()
+    finally:
+        op.close()
+    cam = port.camera()
+    o = port.render(oracle_frame(port, cam, W, H, 0.0, 0.0), np.zeros((1, 1, 1), np.float32), tf(port, "0"), want_raw=True)
+    assert np.array_equal(img, o["rgba8"])
+    covered = o["raw"][..., 3] > 0
+    assert covered.any() and (img[covered] == 255).all() and (img[~covered] == (28, 28, 28, 255)).all()
+
+
+def test_resize_and_errors(vr, port):
+    op = vr.OffscreenPass(64, 48)
+    try:
+        op.framebuffer_size_changed(0, 10)  # ignored like offscreen_pass.cpp:237-239
+        assert op.size == (64, 48)
+        op.framebuffer_size_changed(96, 80)
+        assert op.size == (96, 80)
+        op.set_camera(vr.Camera())
+        op.record()
+        assert op.download().shape == (80, 96, 4)
+        with pytest.raises(vr.VrError):
+            op.transfer_function_changed(np.zeros(0, np.uint32))
+        with pytest.raises(vr.VrError):
+            op.set_march(1.8, 0.0)
+        with pytest.raises(vr.VrError):
+            op.set_uniforms(np.zeros(16), np.zeros(16), np.zeros(3))  # singular proj*view
+        with pytest.raises(vr.VrError):
+            op.import_nrrd("/nonexistent/file.nrrd")
+        with pytest.raises(vr.VrError):
+            op.download_raw()  # write_raw is off
+    finally:
+        op.close()
+
+
+def test_step_size_parameter(vr, port):
+    vol = small_volume(port, 1, np.uint16, 48)
+    lut = tf(port, "B")
+    cam, ocam = twin_cameras(vr, port, [(30, 20)])
+    mn, mx = float(vol.min()), float(vol.max())
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_options(write_raw=1, sampler=vr.SAMPLER_EXACT)
+        op.volume_dataset_changed(vr.Dataset(vol, mn, mx))
+        op.transfer_function_changed(lut)
+        op.set_march(1.0, 0.0125)
+        op.set_camera(cam)
+        op.record()
+        raw = op.download_raw()
+    finally:
+        op.close()
+    f = oracle_frame(port, ocam, W, H, mn, mx)
+    f.ray_dist, f.step_size = 1.0, 0.0125
+    o = port.render(f, vol, lut, want_raw=True)
+    assert np.array_equal(bits(raw), bits(o["raw"]))
+
+
+def test_device_minmax_and_synth_match_cpu(vr, port):
+    op = vr.OffscreenPass(32, 32)
+    try:
+        for kind, dt, code in [(1, np.uint16, vr.U16), (0, np.uint8, vr.U8), (1, np.float32, vr.F32)]:
+            op.synth_volume(kind, 0x5EED0000 + kind, code, 48)
+            g = op.download_volume()
+            c = port.synth(kind, 0x5EED0000 + kind, dt, 48)
+            _, dims, mn, mx = op.volume_info()
+            assert dims == (48, 48, 48)
+            assert mn == float(g.min()) and mx == float(g.max())
+            if kind == 1:
+                assert np.array_equal(g, c), "fBm generator is pure fp32 arithmetic: must be bit-identical"
+            else:
+                assert np.abs(g.astype(np.int64) - c.astype(np.int64)).max() <= 1  # libm vs device sin/cos
+    finally:
+        op.close()

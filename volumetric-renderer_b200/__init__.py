@@ -1,0 +1,317 @@
+"""volumetric-renderer_b200 -- B200-native ray-march backend, host-side mirror of the
+reference's interface for this path.
+
+The compute lives in libvr_b200.so (CUDA kernels for sm_100a behind the C ABI of
+include/vr.h).  This module mirrors the reference's public surface with the same names and
+argument meaning so parity tests read like the reference's call sites:
+
+    Vol::Rendering::OffscreenPass   src/rendering/offscreen_pass.h:27-148   -> OffscreenPass
+    Vol::Scene::Camera              src/scene/camera.h:9-23                 -> Camera
+    Vol::Data::Dataset              src/data/dataset.h:9-13                 -> Dataset
+    Vol::Data::NrrdFileParser       src/data/nrrd_file_parser.cpp:21-47     -> OffscreenPass.import_nrrd
+    Vol::UI::Components::Gradient   src/ui/components/gradient.h:11-36      -> Gradient
+
+Nothing here computes pixels: every method is a thin call into the C ABI.  Import as
+`volumetric_renderer_b200` (shim at the repo root; the directory name has a hyphen).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _lib
+from ._lib import (F32, U8, U16, SAMPLER_EXACT, SAMPLER_HW, SYNTH_BLOBS, SYNTH_FBM, SYNTH_MARSCHNER_LOBB,
+                   Options, Stats)
+
+lib = _lib.load()
+
+_NP = {U8: np.uint8, U16: np.uint16, F32: np.float32}
+_CODE = {np.dtype(np.uint8): U8, np.dtype(np.uint16): U16, np.dtype(np.float32): F32}
+
+
+class VrError(RuntimeError):
+    """The reference throws std::runtime_error on failure; this is its counterpart."""
+
+    def __init__(self, status: int, message: str):
+        super().__init__(f"[vr status {status}] {message}")
+        self.status = status
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Camera:
+    """Vol::Scene::Camera (src/scene/camera.cpp:7-48)."""
+
+    def __init__(self):
+        self._h = lib.vr_camera_new()
+        if not self._h:
+            raise MemoryError("vr_camera_new")
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib.vr_camera_free(h)
+
+    def rotate(self, delta) -> "Camera":
+        lib.vr_camera_rotate(self._h, float(delta[0]), float(delta[1]))
+        return self
+
+    def zoom(self, delta: float) -> "Camera":
+        lib.vr_camera_zoom(self._h, float(delta))
+        return self
+
+    def get_position(self) -> np.ndarray:
+        out = np.zeros(3, np.float32)
+        lib.vr_camera_get_position(self._h, _ptr(out))
+        return out
+
+    def get_view(self) -> np.ndarray:
+        out = np.zeros(16, np.float32)
+        lib.vr_camera_get_view(self._h, _ptr(out))
+        return out
+
+
+def projection(width: int, height: int) -> np.ndarray:
+    """proj of OffscreenPass::update_uniform_buffer (offscreen_pass.cpp:1154-1168)."""
+    out = np.zeros(16, np.float32)
+    lib.vr_projection(width, height, _ptr(out))
+    return out
+
+
+@dataclass
+class Gradient:
+    """Vol::UI::Components::Gradient (gradient.h:11-36); default = gradient.cpp:64-70."""
+    color_markers: list = field(default_factory=lambda: [(0.0, (0.0, 0.0, 0.0)), (1.0, (1.0, 1.0, 1.0))])
+    alpha_markers: list = field(default_factory=lambda: [(0.0, 1.0), (1.0, 1.0)])
+
+    def discretize(self, count: int = 256) -> np.ndarray:
+        cm = np.ascontiguousarray([[loc, *rgb] for loc, rgb in self.color_markers], np.float32)
+        am = np.ascontiguousarray([[loc, a] for loc, a in self.alpha_markers], np.float32)
+        out = np.zeros(count, np.uint32)
+        rc = lib.vr_gradient_discretize(_ptr(cm), len(cm), _ptr(am), len(am), count, _ptr(out))
+        if rc != _lib.VR_OK:
+            raise VrError(rc, "vr_gradient_discretize: bad markers")
+        return out
+
+
+@dataclass
+class Dataset:
+    """Vol::Data::Dataset (src/data/dataset.h:9-13); `data` is [nz, ny, nx], x fastest.
+    uint8 / uint16 / float32 arrays go to the device as they are."""
+    data: np.ndarray
+    min: float | None = None
+    max: float | None = None
+
+    @property
+    def dimensions(self):
+        return (self.data.shape[2], self.data.shape[1], self.data.shape[0])
+
+
+class OffscreenPass:
+    """Vol::Rendering::OffscreenPass with the Vulkan objects replaced by a CUDA context."""
+
+    def __init__(self, width: int, height: int, device: int = 0):
+        h = C.c_void_p()
+        rc = lib.vr_create(device, width, height, C.byref(h))
+        if rc != _lib.VR_OK:
+            raise VrError(rc, lib.vr_last_error(None).decode())
+        self._h = h
+
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib.vr_destroy(h)
+
+    __del__ = close
+
+    def _check(self, rc: int):
+        if rc != _lib.VR_OK:
+            raise VrError(rc, lib.vr_last_error(self._h).decode())
+
+    # ---- the reference's members ------------------------------------------------------
+    def record(self, stream: int | None = None):
+        """record(command_buffer, frame_index), offscreen_pass.cpp:163-230 (asynchronous)."""
+        self._check(lib.vr_render(self._h, stream))
+
+    def framebuffer_size_changed(self, width: int, height: int):
+        self._check(lib.vr_resize(self._h, width, height))
+
+    def volume_dataset_changed(self, dataset: Dataset):
+        a = dataset.data
+        if a.dtype not in _CODE:
+            a = a.astype(np.float32)  # nrrd_file_parser.cpp:67-77 widens everything else
+        a = np.ascontiguousarray(a)
+        mn = C.c_float(dataset.min) if dataset.min is not None else None
+        mx = C.c_float(dataset.max) if dataset.max is not None else None
+        nz, ny, nx = a.shape
+        self._check(lib.vr_set_volume(self._h, _ptr(a), _CODE[a.dtype], nx, ny, nz,
+                                      C.byref(mn) if mn is not None else None,
+                                      C.byref(mx) if mx is not None else None))
+
+    def slicing_changed(self, min_slice, max_slice):
+        lo, hi = np.asarray(min_slice, np.float32), np.asarray(max_slice, np.float32)
+        self._check(lib.vr_set_slicing(self._h, _ptr(lo), _ptr(hi)))
+
+    def transfer_function_changed(self, data):
+        d = np.ascontiguousarray(data, np.uint32)
+        self._check(lib.vr_set_transfer_function(self._h, _ptr(d), len(d)))
+
+    # ---- the implicit camera pull of update_uniform_buffer, made a push ------------------
+    def set_camera(self, camera: Camera):
+        self._check(lib.vr_set_camera_orbit(self._h, camera._h))
+
+    def set_uniforms(self, view, proj, camera_position):
+        v, p, c = (np.ascontiguousarray(x, np.float32) for x in (view, proj, camera_position))
+        self._check(lib.vr_set_camera(self._h, _ptr(v), _ptr(p), _ptr(c)))
+
+    # ---- loader fast path, knobs ---------------------------------------------------------
+    def import_nrrd(self, path: str):
+        """Importer::import(Nrrd) -> parse -> volume_dataset_changed (importer.cpp:36-46)."""
+        self._check(lib.vr_load_nrrd(self._h, str(path).encode()))
+
+    def synth_volume(self, kind: int, seed: int, dtype: int, n):
+        nx, ny, nz = (n, n, n) if isinstance(n, int) else n
+        self._check(lib.vr_synth_volume(self._h, kind, seed & 0xFFFFFFFF, dtype, nx, ny, nz))
+
+    def set_march(self, ray_dist: float, step_size: float):
+        self._check(lib.vr_set_march(self._h, ray_dist, step_size))
+
+    def set_density_range(self, mn: float, mx: float):
+        self._check(lib.vr_set_density_range(self._h, mn, mx))
+
+    @property
+    def options(self) -> Options:
+        o = Options()
+        self._check(lib.vr_get_options(self._h, C.byref(o)))
+        return o
+
+    def set_options(self, **kw):
+        o = self.options
+        for k, v in kw.items():
+            if not hasattr(o, k):
+                raise AttributeError(k)
+            setattr(o, k, v)
+        self._check(lib.vr_set_options(self._h, C.byref(o)))
+
+    # ---- outputs -------------------------------------------------------------------------
+    @property
+    def size(self):
+        w, h = C.c_uint32(), C.c_uint32()
+        lib.vr_get_size(self._h, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def sync(self):
+        self._check(lib.vr_sync(self._h))
+
+    def get_image(self):
+        """get_image_view(): (device pointer, pitch in bytes) of the RGBA8 target."""
+        p, pitch = C.c_void_p(), C.c_size_t()
+        self._check(lib.vr_get_image(self._h, C.byref(p), C.byref(pitch)))
+        return p.value, pitch.value
+
+    def get_raw(self) -> int:
+        p = C.c_void_p()
+        self._check(lib.vr_get_raw(self._h, C.byref(p)))
+        return p.value
+
+    def download(self, out: np.ndarray | None = None) -> np.ndarray:
+        w, h = self.size
+        if out is None:
+            out = np.empty((h, w, 4), np.uint8)
+        self._check(lib.vr_download(self._h, _ptr(out)))
+        return out
+
+    def download_async(self, host_ptr: int, stream: int | None = None):
+        self._check(lib.vr_download_async(self._h, host_ptr, stream))
+
+    def download_raw(self) -> np.ndarray:
+        w, h = self.size
+        out = np.empty((h, w, 4), np.float32)
+        self._check(lib.vr_download_raw(self._h, _ptr(out)))
+        return out
+
+    def download_volume(self) -> np.ndarray:
+        dt, dims, mn, mx = self.volume_info()
+        out = np.empty((dims[2], dims[1], dims[0]), _NP[dt])
+        self._check(lib.vr_download_volume(self._h, _ptr(out)))
+        return out
+
+    def volume_info(self):
+        dt, dims, mn, mx = C.c_int(), (C.c_uint32 * 3)(), C.c_float(), C.c_float()
+        self._check(lib.vr_get_volume_info(self._h, C.byref(dt), dims, C.byref(mn), C.byref(mx)))
+        return dt.value, tuple(dims), mn.value, mx.value
+
+    def stats(self) -> Stats:
+        s = Stats()
+        self._check(lib.vr_get_stats(self._h, C.byref(s)))
+        return s
+
+    def occupancy_info(self):
+        cells, cv, empty = (C.c_uint32 * 3)(), C.c_uint32(), C.c_uint64()
+        self._check(lib.vr_get_occupancy_info(self._h, cells, C.byref(cv), C.byref(empty)))
+        return tuple(cells), cv.value, empty.value
+
+    # ---- multi-GPU partitioning ------------------------------------------------------------
+    def set_partition_sort_first(self, rank: int, nranks: int, tile_px: int = 64):
+        self._check(lib.vr_set_partition_sort_first(self._h, rank, nranks, tile_px))
+
+    def set_partition_sort_last(self, full_dims, own_org, own_dims):
+        f, o, d = (np.asarray(x, np.uint32) for x in (full_dims, own_org, own_dims))
+        self._check(lib.vr_set_partition_sort_last(self._h, _ptr(f), _ptr(o), _ptr(d)))
+
+    def synth_subvolume(self, kind: int, seed: int, dtype: int):
+        self._check(lib.vr_synth_subvolume(self._h, kind, seed & 0xFFFFFFFF, dtype))
+
+    def clear_partition(self):
+        self._check(lib.vr_clear_partition(self._h))
+
+    def composite(self, part_ptrs, pixel_begin: int, pixel_end: int, stream: int | None = None):
+        arr = (C.c_void_p * len(part_ptrs))(*part_ptrs)
+        self._check(lib.vr_composite(self._h, arr, len(part_ptrs), pixel_begin, pixel_end, stream))
+
+
+def read_nrrd(path: str) -> np.ndarray:
+    """The native NRRD reader alone (host only): array [nz, ny, nx] as it would be uploaded."""
+    dt, dims, data = C.c_int(), (C.c_uint32 * 3)(), C.c_void_p()
+    err = C.create_string_buffer(512)
+    rc = lib.vr_nrrd_read_host(str(path).encode(), C.byref(dt), dims, C.byref(data), err, len(err))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, err.value.decode())
+    try:
+        n = dims[0] * dims[1] * dims[2]
+        np_dt = np.dtype(_NP[dt.value])
+        buf = (C.c_char * (n * np_dt.itemsize)).from_address(data.value)
+        return np.frombuffer(buf, np_dt).reshape(dims[2], dims[1], dims[0]).copy()
+    finally:
+        lib.vr_free_host(data)
+
+
+def partition_box(grid, full_dims, index: int):
+    g, f = np.asarray(grid, np.uint32), np.asarray(full_dims, np.uint32)
+    org, dims = np.zeros(3, np.uint32), np.zeros(3, np.uint32)
+    rc = lib.vr_partition_box(_ptr(g), _ptr(f), index, _ptr(org), _ptr(dims))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, "vr_partition_box: bad arguments")
+    return tuple(int(x) for x in org), tuple(int(x) for x in dims)
+
+
+def partition_order(grid, full_dims, camera_position) -> np.ndarray:
+    g, f = np.asarray(grid, np.uint32), np.asarray(full_dims, np.uint32)
+    c = np.asarray(camera_position, np.float32)
+    out = np.zeros(int(g[0]) * int(g[1]) * int(g[2]), np.uint32)
+    rc = lib.vr_partition_order(_ptr(g), _ptr(f), _ptr(c), _ptr(out))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, "vr_partition_order: bad arguments")
+    return out
+
+
+def bench_tex_peak(device: int, dtype: int, hw_filter: bool = True) -> float:
+    r = C.c_double()
+    rc = lib.vr_bench_tex_peak(device, dtype, int(hw_filter), C.byref(r))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, "vr_bench_tex_peak failed")
+    return r.value

@@ -788,3 +788,24 @@ extern "C" int vr_debug_ray_context(const vr_ctx *c, float out[16])
     std::memcpy(out, c->rc, sizeof(float) * 16);
     return VR_OK;
 }
+
+/* Loader without a context (host only): what vr_load_nrrd would upload.  *data is malloc'd,
+ * release with vr_free_host. */
+extern "C" int vr_nrrd_read_host(const char *path, int *dtype, uint32_t dims[3], void **data, char *errbuf, size_t errbuf_len)
+{
+    if (!path || !dtype || !dims || !data) return VR_ERR_INVALID;
+    VrNrrd n;
+    std::string err;
+    const int rc = vr_nrrd_read(path, n, err);
+    if (rc != VR_OK) {
+        if (errbuf && errbuf_len) std::snprintf(errbuf, errbuf_len, "%s", err.c_str());
+        return rc;
+    }
+    void *p = std::malloc(n.bytes.size());
+    if (!p) return VR_ERR_NOMEM;
+    std::memcpy(p, n.bytes.data(), n.bytes.size());
+    *dtype = n.dtype, dims[0] = n.dims[0], dims[1] = n.dims[1], dims[2] = n.dims[2], *data = p;
+    return VR_OK;
+}
+
+extern "C" void vr_free_host(void *p) { std::free(p); }
