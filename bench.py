@@ -126,6 +126,9 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     kind, dname, n, W, H, tfn, desc = WORKLOADS[args.workload]
+    if os.environ.get("VR_BENCH_N"):  # tuning experiments only (changes the workload: not a bench line)
+        n = int(os.environ["VR_BENCH_N"])
+        desc += f" [EXPERIMENT: volume {n}^3]"
     dtype = {"u8": vr.U8, "u16": vr.U16, "f32": vr.F32}[dname]
     esz = {"u8": 1, "u16": 2, "f32": 4}[dname]
     K, Wu = args.steps, args.warmup
@@ -139,8 +142,9 @@ def run_ours(args):
     uniforms = orbit_uniforms(vr, W, H, ORBIT_FRAMES)
     my_frames = [(rank + j * world) % ORBIT_FRAMES for j in range(K)]
     warm_frames = [(rank + j * world) % ORBIT_FRAMES for j in range(Wu)]
-    stream = torch.cuda.Stream()
-    sp = stream.cuda_stream
+    F = max(1, min(args.in_flight, 4))      # frames in flight (the reference keeps MAX_FRAMES_IN_FLIGHT = 2)
+    streams = [torch.cuda.Stream() for _ in range(F)]
+    stream, sp = streams[0], streams[0].cuda_stream
 
     # ---- untimed: work per frame (reference-equivalent samples, executed fetches) ----------------
     n_ref, n_exec = {}, {}
@@ -164,39 +168,53 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---- device-timed: inputs resident, K launches of K1 --------------------------------------------
-    for k in warm_frames:
+    for j, k in enumerate(warm_frames):
         op.set_uniforms(*uniforms[k])
-        op.record(sp)
+        op.record(streams[j % F].cuda_stream, j % F)
     clocks = ClockSampler(physical_gpu_index(local))
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def fork():
+        ev0.record(streams[0])
+        for s in streams[1:]:
+            s.wait_event(ev0)
+
+    def join():
+        for s in streams[1:]:
+            e = torch.cuda.Event()
+            e.record(s)
+            streams[0].wait_event(e)
+        ev1.record(streams[0])
+
     barrier()
     clocks.start()
-    ev0.record(stream)
-    for k in my_frames:
+    fork()
+    for j, k in enumerate(my_frames):
         op.set_uniforms(*uniforms[k])
-        op.record(sp)
-    ev1.record(stream)
+        op.record(streams[j % F].cuda_stream, j % F)
+    join()
     clocks.sample()  # at least one sample while the queue is still draining
     barrier()
     clocks.stop_flag = True
     dev_ms = ev0.elapsed_time(ev1)
 
     # ---- end to end through the public API: host uniforms in, RGBA8 frame out to pinned host memory ---
-    host = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True)
-    for k in warm_frames[:3]:
+    host = [torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(F)]
+    for j, k in enumerate(warm_frames[:3]):
         op.set_uniforms(*uniforms[k])
-        op.record(sp)
-        op.download_async(host.data_ptr(), sp)
-        stream.synchronize()
+        op.record(streams[j % F].cuda_stream, j % F)
+        op.download_async(host[j % F].data_ptr(), streams[j % F].cuda_stream, j % F)
     barrier()
     t0 = time.perf_counter()
-    for k in my_frames:
+    for j, k in enumerate(my_frames):
+        f = j % F
+        streams[f].synchronize()           # frame j-F is in host memory (its buffer may be reused now)
         op.set_uniforms(*uniforms[k])      # 192-byte uniform block: the step's input, goes down with the launch
-        op.record(sp)
-        op.download_async(host.data_ptr(), sp)
-        stream.synchronize()               # the frame is in host memory before the next step starts
-    barrier()
+        op.record(streams[f].cuda_stream, f)
+        op.download_async(host[f].data_ptr(), streams[f].cuda_stream, f)
+    barrier()                              # every frame of the K steps has landed in host memory
     e2e_ms = (time.perf_counter() - t0) * 1e3
+    host = host[(K - 1) % F]
     checksum = int(host.view(torch.int32).sum().item())
 
     t = torch.tensor([dev_ms, e2e_ms, float(total_ref), float(total_exec)], dtype=torch.float64, device="cuda")
@@ -233,6 +251,7 @@ def run_ours(args):
                        "sampler": "exact(8 point fetches + fp32 lerp)" if args.exact else "hw trilinear",
                        "empty_space_skipping": bool(prod["empty_skip"]), "early_ray_termination_eps": prod["early_term_eps"] if prod["early_term"] else 0,
                        "l2": f"inputs larger than L2 ({n ** 3 * esz / 2 ** 20:.0f} MiB volume, no flush)",
+                       "frames_in_flight": F,
                        "parallelism": f"frames of the orbit dealt round-robin to {world} GPU(s), no collective"},
             "executed_samples_per_s": all_exec / (dev_ms * 1e-3),
             "roofline": {"bound": "hbm", "achieved": alg_bytes / step_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
@@ -367,6 +386,7 @@ def main():
     ap.add_argument("--no-ess", action="store_true")
     ap.add_argument("--no-ert", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--in-flight", type=int, default=2, help="frames in flight (streams), 1..4")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

@@ -94,6 +94,14 @@ int vr_abi_version(void);
  * store RGBA8.  Asynchronous on `cuda_stream` like command recording; results are
  * complete after the stream is synchronised (vr_sync / vr_download do that). */
 int vr_render(vr_ctx *ctx, void *cuda_stream);
+/* The same with the reference's frame_index argument: the reference keeps MAX_FRAMES_IN_FLIGHT = 2
+ * frames in flight (src/rendering/vulkan_context.h:17, main_pass.cpp:55-57,:115-117).  Each
+ * frame_index < VR_MAX_FRAMES_IN_FLIGHT has its own RGBA8 target, so frame k+1 can be recorded on
+ * another stream while frame k is still rendering or being downloaded.  vr_render = frame 0. */
+#define VR_MAX_FRAMES_IN_FLIGHT 4
+int vr_render_frame(vr_ctx *ctx, uint32_t frame_index, void *cuda_stream);
+int vr_get_image_frame(vr_ctx *ctx, uint32_t frame_index, void **dev_rgba8, size_t *pitch_bytes);
+int vr_download_frame_async(vr_ctx *ctx, uint32_t frame_index, void *host_rgba8, void *cuda_stream);
 int vr_sync(vr_ctx *ctx);
 
 /* The uniform block the reference fills by pulling the camera inside record()

@@ -133,9 +133,9 @@ class OffscreenPass:
             raise VrError(rc, lib.vr_last_error(self._h).decode())
 
     # ---- the reference's members ------------------------------------------------------
-    def record(self, stream: int | None = None):
+    def record(self, stream: int | None = None, frame_index: int = 0):
         """record(command_buffer, frame_index), offscreen_pass.cpp:163-230 (asynchronous)."""
-        self._check(lib.vr_render(self._h, stream))
+        self._check(lib.vr_render_frame(self._h, frame_index, stream))
 
     def framebuffer_size_changed(self, width: int, height: int):
         self._check(lib.vr_resize(self._h, width, height))
@@ -225,8 +225,8 @@ class OffscreenPass:
         self._check(lib.vr_download(self._h, _ptr(out)))
         return out
 
-    def download_async(self, host_ptr: int, stream: int | None = None):
-        self._check(lib.vr_download_async(self._h, host_ptr, stream))
+    def download_async(self, host_ptr: int, stream: int | None = None, frame_index: int = 0):
+        self._check(lib.vr_download_frame_async(self._h, frame_index, host_ptr, stream))
 
     def download_raw(self) -> np.ndarray:
         w, h = self.size

@@ -37,6 +37,9 @@ SIGNATURES = {
     "vr_last_error": (C.c_char_p, [_P]),
     "vr_abi_version": (C.c_int, []),
     "vr_render": (C.c_int, [_P, _P]),
+    "vr_render_frame": (C.c_int, [_P, C.c_uint32, _P]),
+    "vr_get_image_frame": (C.c_int, [_P, C.c_uint32, C.POINTER(_P), C.POINTER(C.c_size_t)]),
+    "vr_download_frame_async": (C.c_int, [_P, C.c_uint32, _P, _P]),
     "vr_sync": (C.c_int, [_P]),
     "vr_set_camera": (C.c_int, [_P, _P, _P, _P]),
     "vr_resize": (C.c_int, [_P, C.c_uint32, C.c_uint32]),

@@ -8,11 +8,13 @@
  * objects, the decoded LUT, the occupancy grid, and one stream.  Every mutator keeps the
  * reference's semantics (synchronous, copy-in), every failure becomes a status + message.
  */
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <new>
@@ -124,8 +126,18 @@ int upload_lut(vr_ctx *c)
     }
     for (uint32_t k = 0; k < n + 2; k++)
         D[k] = make_float4(P[k + 1].x - P[k].x, P[k + 1].y - P[k].y, P[k + 1].z - P[k].z, P[k + 1].w - P[k].w);
+    /* fp16 staging of the same table: {P.rg, P.ba, D.rg, D.ba}; 0 stays exactly 0 */
+    std::vector<uint4> H(n + 2);
+    for (uint32_t k = 0; k < n + 2; k++) {
+        const __half2 prg = __floats2half2_rn(P[k].x, P[k].y), pba = __floats2half2_rn(P[k].z, P[k].w);
+        const __half2 drg = __floats2half2_rn(D[k].x, D[k].y), dba = __floats2half2_rn(D[k].z, D[k].w);
+        std::memcpy(&H[k].x, &prg, 4), std::memcpy(&H[k].y, &pba, 4), std::memcpy(&H[k].z, &drg, 4), std::memcpy(&H[k].w, &dba, 4);
+    }
     if (c->d_lut_pad) cudaFree(c->d_lut_pad), c->d_lut_pad = nullptr;
     if (c->d_lut_dif) cudaFree(c->d_lut_dif), c->d_lut_dif = nullptr;
+    if (c->d_lut_h16) cudaFree(c->d_lut_h16), c->d_lut_h16 = nullptr;
+    VR_CUDA(c, cudaMalloc(&c->d_lut_h16, sizeof(uint4) * (n + 2)));
+    VR_CUDA(c, cudaMemcpy(c->d_lut_h16, H.data(), sizeof(uint4) * (n + 2), cudaMemcpyHostToDevice));
     VR_CUDA(c, cudaMalloc(&c->d_lut_pad, sizeof(float4) * (n + 3)));
     VR_CUDA(c, cudaMalloc(&c->d_lut_dif, sizeof(float4) * (n + 2)));
     VR_CUDA(c, cudaMemcpy(c->d_lut_pad, P.data(), sizeof(float4) * (n + 3), cudaMemcpyHostToDevice));
@@ -147,6 +159,8 @@ int alloc_target(vr_ctx *c, uint32_t w, uint32_t h)
 {
     if (c->d_image) cudaFree(c->d_image), c->d_image = nullptr;
     if (c->d_raw) cudaFree(c->d_raw), c->d_raw = nullptr;
+    for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
+        if (c->d_image_slot[k]) cudaFree(c->d_image_slot[k]), c->d_image_slot[k] = nullptr;
     c->W = w, c->H = h;
     VR_CUDA(c, cudaMalloc(&c->d_image, (size_t)w * h * sizeof(uchar4)));
     VR_CUDA(c, cudaMemset(c->d_image, 0, (size_t)w * h * sizeof(uchar4)));
@@ -272,6 +286,16 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     c->opt.early_term_eps = 1.0f / 1024.0f;
     c->opt.collect_stats = 0;
     c->opt.write_raw = 0;
+    if (const char *e = std::getenv("VR_BATCH")) c->tune_batch = std::atoi(e);
+    if (const char *e = std::getenv("VR_LUT16")) c->tune_lut16 = std::atoi(e);
+    if (const char *e = std::getenv("VR_CTA_THREADS")) c->tune_threads = std::atoi(e) == 128 ? 128 : 256;
+    if (const char *e = std::getenv("VR_BBOX")) c->tune_bbox = std::atoi(e);
+    if (const char *e = std::getenv("VR_WARP_W")) {
+        const int w = std::atoi(e);
+        if (w == 4 || w == 8 || w == 16) c->tune_warp_w = w;
+    }
+    if (const char *e = std::getenv("VR_CARVEOUT")) c->tune_carveout = std::atoi(e);
+    if (const char *e = std::getenv("VR_L2_GRAN")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(e));
     int rc = VR_OK;
     do {
         if ((e = cudaSetDevice(device)) != cudaSuccess) { rc = cuda_fail(c, e, "cudaSetDevice"); break; }
@@ -300,8 +324,11 @@ extern "C" int vr_destroy(vr_ctx *c)
     release_volume(c);
     if (c->d_lut_pad) cudaFree(c->d_lut_pad);
     if (c->d_lut_dif) cudaFree(c->d_lut_dif);
+    if (c->d_lut_h16) cudaFree(c->d_lut_h16);
     if (c->d_image) cudaFree(c->d_image);
     if (c->d_raw) cudaFree(c->d_raw);
+    for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
+        if (c->d_image_slot[k]) cudaFree(c->d_image_slot[k]);
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -337,7 +364,7 @@ extern "C" int vr_resize(vr_ctx *c, uint32_t width, uint32_t height)
     if (!c) return VR_ERR_INVALID;
     if (width == 0 || height == 0) return VR_OK; /* offscreen_pass.cpp:237-239 */
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->last_stream)); /* vkDeviceWaitIdle, :241 */
+    VR_CUDA(c, cudaDeviceSynchronize()); /* vkDeviceWaitIdle, :241 */
     return alloc_target(c, width, height);
 }
 
@@ -347,7 +374,7 @@ extern "C" int vr_set_volume_device(vr_ctx *c, const void *dev, int dtype, uint3
     if (!c || !dev || dtype < VR_U8 || dtype > VR_F32 || nx == 0 || ny == 0 || nz == 0)
         return fail(c, VR_ERR_INVALID, "vr_set_volume: bad arguments");
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    VR_CUDA(c, cudaDeviceSynchronize());
     return install_volume(c, dev, dtype, nx, ny, nz, mn, mx);
 }
 
@@ -357,7 +384,7 @@ extern "C" int vr_set_volume(vr_ctx *c, const void *data, int dtype, uint32_t nx
     if (!c || !data || dtype < VR_U8 || dtype > VR_F32 || nx == 0 || ny == 0 || nz == 0)
         return fail(c, VR_ERR_INVALID, "vr_set_volume: bad arguments");
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    VR_CUDA(c, cudaDeviceSynchronize());
     const size_t bytes = (size_t)nx * ny * nz * dtype_size(dtype);
     void *stage = nullptr;
     VR_CUDA(c, cudaMalloc(&stage, bytes));
@@ -412,7 +439,7 @@ extern "C" int vr_set_transfer_function(vr_ctx *c, const uint32_t *rgba8, uint32
     if (!c || !rgba8 || n == 0) return fail(c, VR_ERR_INVALID, "vr_set_transfer_function: need n >= 1 texels");
     if (n > 4096) return fail(c, VR_ERR_INVALID, "vr_set_transfer_function: at most 4096 texels (shared-memory staged)");
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->last_stream)); /* wait_till_idle, offscreen_pass.cpp:282 */
+    VR_CUDA(c, cudaDeviceSynchronize()); /* wait_till_idle, offscreen_pass.cpp:282 */
     uint32_t *copy = (uint32_t *)std::malloc(sizeof(uint32_t) * n);
     if (!copy) return fail(c, VR_ERR_NOMEM, "out of host memory");
     std::memcpy(copy, rgba8, sizeof(uint32_t) * n);
@@ -466,6 +493,33 @@ int prepare_occupancy(vr_ctx *c, cudaStream_t s)
     return VR_OK;
 }
 
+/* Pixels the cube can cover: the projections of its 8 corners bound its silhouette when all of
+ * them are in front of the eye; otherwise (camera inside or near the cube) the whole target. */
+void screen_bbox(const vr_ctx *c, uint32_t bbox[4])
+{
+    bbox[0] = 0, bbox[1] = 0, bbox[2] = c->W, bbox[3] = c->H;
+    if (!c->tune_bbox) return;
+    double v[16], p[16], pv[16];
+    for (int i = 0; i < 16; i++) v[i] = (double)c->view[i], p[i] = (double)c->proj[i];
+    mat4_mul_d(p, v, pv);
+    double x0 = 1e30, y0 = 1e30, x1 = -1e30, y1 = -1e30;
+    for (int k = 0; k < 8; k++) {
+        const double q[3] = {(k & 1) ? 0.5 : -0.5, (k & 2) ? 0.5 : -0.5, (k & 4) ? 0.5 : -0.5};
+        double h[4];
+        for (int r = 0; r < 4; r++) h[r] = pv[r] * q[0] + pv[4 + r] * q[1] + pv[8 + r] * q[2] + pv[12 + r];
+        if (!(h[3] > 1e-4)) return;
+        const double px = (h[0] / h[3] + 1.0) * 0.5 * c->W, py = (h[1] / h[3] + 1.0) * 0.5 * c->H;
+        x0 = std::min(x0, px), x1 = std::max(x1, px), y0 = std::min(y0, py), y1 = std::max(y1, py);
+    }
+    if (!(x0 == x0) || !(x1 == x1) || !(y0 == y0) || !(y1 == y1)) return;
+    const double m = 2.0; /* pixels of slack for the fp32 coverage test */
+    const double lx = std::floor(x0 - m), ly = std::floor(y0 - m), hx = std::ceil(x1 + m), hy = std::ceil(y1 + m);
+    bbox[0] = (uint32_t)std::min(std::max(lx, 0.0), (double)c->W);
+    bbox[1] = (uint32_t)std::min(std::max(ly, 0.0), (double)c->H);
+    bbox[2] = (uint32_t)std::min(std::max(hx, 0.0), (double)c->W);
+    bbox[3] = (uint32_t)std::min(std::max(hy, 0.0), (double)c->H);
+}
+
 void fill_params(const vr_ctx *c, MarchParams &p)
 {
     std::memset(&p, 0, sizeof(p));
@@ -492,6 +546,10 @@ void fill_params(const vr_ctx *c, MarchParams &p)
             if (c->own_org[i] > 0) p.own_lo[i] = (float)c->own_org[i] / (float)full;
             if (c->own_org[i] + c->own_dims[i] < full) p.own_hi[i] = (float)(c->own_org[i] + c->own_dims[i]) / (float)full;
         }
+        p.box_lo[i] = std::max(0.0f, std::max(c->min_slice[i], p.own_lo[i]));
+        p.box_hi[i] = std::min(1.0f, std::min(c->max_slice[i], p.own_hi[i]));
+        if (!(c->min_slice[i] == c->min_slice[i]) || !(c->max_slice[i] == c->max_slice[i]))
+            p.box_lo[i] = inf, p.box_hi[i] = -inf; /* NaN slice bound: every strict test fails */
         p.occ_n[i] = c->occ_n[i];
         p.occ_scale[i] = (float)full / (float)c->occ_cell;
         p.occ_off[i] = (float)p.org[i] / (float)c->occ_cell;
@@ -509,13 +567,32 @@ void fill_params(const vr_ctx *c, MarchParams &p)
     p.ert_eps = c->opt.early_term ? c->opt.early_term_eps : -1.0f;
     p.pt_px = c->pt_px, p.pt_rank = c->pt_rank, p.pt_nranks = c->pt_nranks;
     p.pt_nx = (c->W + c->pt_px - 1) / c->pt_px, p.pt_ny = (c->H + c->pt_px - 1) / c->pt_px;
-    p.pt_sub = c->pt_px / VR_TILE;
+    p.warp_w = (uint32_t)c->tune_warp_w;
+    p.carveout = c->tune_carveout;
+    p.tile_h = (uint32_t)c->tune_threads / VR_TILE;
+    p.lut_h16 = c->d_lut_h16;
+    screen_bbox(c, p.bbox);
+    p.ntx = (c->W + VR_TILE - 1) / VR_TILE, p.nty = (c->H + p.tile_h - 1) / p.tile_h;
+    p.rect[0] = (int)(p.bbox[0] / VR_TILE), p.rect[1] = (int)(p.bbox[1] / p.tile_h);
+    p.rect[2] = (int)((p.bbox[2] + VR_TILE - 1) / VR_TILE), p.rect[3] = (int)((p.bbox[3] + p.tile_h - 1) / p.tile_h);
+    if (p.bbox[2] <= p.bbox[0] || p.bbox[3] <= p.bbox[1]) {
+        p.rect[0] = p.rect[1] = p.rect[2] = p.rect[3] = 0;
+        p.sp_count = 0, p.sp_cx = p.sp_cy = 0;
+    } else {
+        const int w = p.rect[2] - p.rect[0], h = p.rect[3] - p.rect[1];
+        const int R = (std::max(w, h) + 1) / 2; /* the (2R+1)^2 spiral square covers the rectangle */
+        p.sp_cx = p.rect[0] + w / 2, p.sp_cy = p.rect[1] + h / 2;
+        p.sp_count = (uint32_t)((2 * R + 1) * (2 * R + 1));
+    }
 }
 }  // namespace
 
-extern "C" int vr_render(vr_ctx *c, void *cuda_stream)
+extern "C" int vr_render(vr_ctx *c, void *cuda_stream) { return vr_render_frame(c, 0, cuda_stream); }
+
+extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_stream)
 {
     if (!c) return VR_ERR_INVALID;
+    if (frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return fail(c, VR_ERR_INVALID, "vr_render_frame: frame_index out of range");
     if (!c->ray_valid) return fail(c, VR_ERR_STATE, "vr_render: no valid camera");
     if (!c->array) return fail(c, VR_ERR_STATE, "vr_render: no volume");
     VR_CUDA(c, cudaSetDevice(c->device));
@@ -531,10 +608,21 @@ extern "C" int vr_render(vr_ctx *c, void *cuda_stream)
         const int rc = prepare_occupancy(c, s);
         if (rc != VR_OK) return rc;
     }
+    uchar4 *target = c->d_image;
+    if (frame_index > 0) {
+        if (!c->d_image_slot[frame_index]) {
+            VR_CUDA(c, cudaMalloc(&c->d_image_slot[frame_index], (size_t)c->W * c->H * sizeof(uchar4)));
+            VR_CUDA(c, cudaMemset(c->d_image_slot[frame_index], 0, (size_t)c->W * c->H * sizeof(uchar4)));
+        }
+        target = c->d_image_slot[frame_index];
+    }
     MarchParams p;
     fill_params(c, p);
+    p.out = target;
+    if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
-    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, s));
+    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, c->tune_batch, c->tune_lut16 != 0,
+                               c->tune_threads, s));
     if (c->opt.collect_stats)
         VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     return VR_OK;
@@ -544,7 +632,7 @@ extern "C" int vr_sync(vr_ctx *c)
 {
     if (!c) return VR_ERR_INVALID;
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    VR_CUDA(c, cudaDeviceSynchronize());
     return VR_OK;
 }
 
@@ -563,6 +651,26 @@ extern "C" int vr_get_image(vr_ctx *c, void **dev, size_t *pitch)
     if (!c || !dev) return VR_ERR_INVALID;
     *dev = c->d_image;
     if (pitch) *pitch = (size_t)c->W * sizeof(uchar4);
+    return VR_OK;
+}
+
+extern "C" int vr_get_image_frame(vr_ctx *c, uint32_t frame_index, void **dev, size_t *pitch)
+{
+    if (!c || !dev || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return VR_ERR_INVALID;
+    *dev = frame_index == 0 ? c->d_image : c->d_image_slot[frame_index];
+    if (!*dev) return fail(c, VR_ERR_STATE, "vr_get_image_frame: that frame was never rendered");
+    if (pitch) *pitch = (size_t)c->W * sizeof(uchar4);
+    return VR_OK;
+}
+
+extern "C" int vr_download_frame_async(vr_ctx *c, uint32_t frame_index, void *host, void *cuda_stream)
+{
+    if (!c || !host || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return fail(c, VR_ERR_INVALID, "vr_download_frame_async: bad arguments");
+    const uchar4 *src = frame_index == 0 ? c->d_image : c->d_image_slot[frame_index];
+    if (!src) return fail(c, VR_ERR_STATE, "vr_download_frame_async: that frame was never rendered");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->last_stream;
+    VR_CUDA(c, cudaMemcpyAsync(host, src, (size_t)c->W * c->H * sizeof(uchar4), cudaMemcpyDeviceToHost, s));
     return VR_OK;
 }
 
@@ -648,7 +756,7 @@ extern "C" int vr_synth_volume(vr_ctx *c, int kind, uint32_t seed, int dtype, ui
         return fail(c, VR_ERR_INVALID, "vr_synth_volume: bad arguments");
     if (c->sort_last) return fail(c, VR_ERR_STATE, "vr_synth_volume: context is sort-last partitioned (use vr_synth_subvolume)");
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    VR_CUDA(c, cudaDeviceSynchronize());
     void *lin = nullptr;
     VR_CUDA(c, cudaMalloc(&lin, (size_t)nx * ny * nz * dtype_size(dtype)));
     const int org[3] = {0, 0, 0};
@@ -668,7 +776,7 @@ extern "C" int vr_synth_subvolume(vr_ctx *c, int kind, uint32_t seed, int dtype)
     if (!c || kind < 0 || kind > 2 || dtype < VR_U8 || dtype > VR_F32) return fail(c, VR_ERR_INVALID, "vr_synth_subvolume: bad arguments");
     if (!c->sort_last) return fail(c, VR_ERR_STATE, "vr_synth_subvolume: call vr_set_partition_sort_last first");
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
+    VR_CUDA(c, cudaDeviceSynchronize());
     uint32_t l[3];
     for (int i = 0; i < 3; i++) {
         const uint32_t end = c->own_org[i] + c->own_dims[i];

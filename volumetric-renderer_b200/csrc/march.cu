@@ -19,6 +19,7 @@
  * bit-identical to the CPU oracle.  Fused multiply-adds are written explicitly (fmaf) where
  * the hardware-sampler path is allowed to differ in rounding.
  */
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
@@ -130,33 +131,217 @@ __device__ __forceinline__ bool cell_occupied(const MarchParams &p, const uint32
     return (sOcc[bit >> 5] >> (bit & 31)) & 1u;
 }
 
-template <bool EXACT, bool ESS, bool STATS, bool PART>
+/* Per-thread state of one ray. */
+struct Ray {
+    float cr, cg, cb, T;   /* volume.frag:22 color (T = color.a = transmittance) */
+    float px, py, pz;      /* ray_pos */
+    float dx, dy, dz;      /* ray_dir * step_size */
+    int i;                 /* loop counter */
+    bool done;
+    uint32_t nb, ns, nf;   /* counters (STATS) */
+};
+
+/* The positions volume.frag:47 accumulates are monotone on every axis, and differ from
+ * tex + i*d by at most steps * ulp(1)/2.  So the steps that pass the bounds test (:34-37), the
+ * strict slice test (:39-40) and the sort-last ownership test form one interval of i, and the
+ * analytic interval shrunk by that error bound and by one step at each end is inside it:
+ * those steps can run without evaluating any of the tests, with identical results. */
+__device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r, int &fast_lo, int &fast_hi)
+{
+    const float eps = (float)(p.steps + 2) * 1.2e-7f;
+    float tlo = 0.0f, thi = (float)(p.steps - 1);
+    const float p0[3] = {r.px, r.py, r.pz}, d[3] = {r.dx, r.dy, r.dz};
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        const float lo = p.box_lo[a] + eps, hi = p.box_hi[a] - eps;
+        if (d[a] != 0.0f) {
+            const float inv = __frcp_rn(d[a]);
+            const float ta = (lo - p0[a]) * inv, tb = (hi - p0[a]) * inv;
+            tlo = fmaxf(tlo, fminf(ta, tb));
+            thi = fminf(thi, fmaxf(ta, tb));
+        } else if (!(p0[a] > lo && p0[a] < hi)) {
+            thi = -1.0f;
+        }
+    }
+    if (tlo == tlo && thi == thi && thi - tlo >= 4.0f && tlo < 1.0e6f) {
+        fast_lo = (int)ceilf(tlo) + 1;
+        fast_hi = (int)floorf(thi) - 1;
+    }
+}
+
+/* U consecutive iterations of volume.frag:33-48: positions first, then all fetches back to
+ * back, then transfer function + compositing.  CHECK = evaluate the per-step tests. */
+template <bool EXACT, bool ESS, bool STATS, bool PART, int U, bool LUT16, bool CHECK>
+__device__ __forceinline__ void march_batch(const MarchParams &p, Ray &r, const float4 *sP, const float4 *sD,
+                                            const uint4 *sH, const uint32_t *sOcc)
+{
+    const float lut_hi = (float)p.nlut;
+    float qx[U], qy[U], qz[U], val[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        bool s;
+        if (CHECK) {
+            /* volume.frag:33-37: loop bound and the strict bounds test */
+            const bool inb = !r.done && r.i < p.steps &&
+                             !(r.px > 1.0f || r.py > 1.0f || r.pz > 1.0f || r.px < 0.0f || r.py < 0.0f || r.pz < 0.0f);
+            if (!inb) r.done = true;
+            /* volume.frag:39-40: strict on both sides */
+            s = inb && r.px < p.max_slice[0] && r.py < p.max_slice[1] && r.pz < p.max_slice[2] &&
+                r.px > p.min_slice[0] && r.py > p.min_slice[1] && r.pz > p.min_slice[2];
+            if (PART)
+                s = s && r.px >= p.own_lo[0] && r.py >= p.own_lo[1] && r.pz >= p.own_lo[2] && r.px < p.own_hi[0] &&
+                    r.py < p.own_hi[1] && r.pz < p.own_hi[2];
+            if (STATS) {
+                r.nb += inb;
+                r.ns += s;
+            }
+        } else {
+            s = !r.done;
+            if (STATS) {
+                r.nb += s;
+                r.ns += s;
+            }
+        }
+        if (ESS) s = s && cell_occupied<PART>(p, sOcc, r.px, r.py, r.pz);
+        ok[u] = s;
+        qx[u] = r.px, qy[u] = r.py, qz[u] = r.pz;
+        /* volume.frag:47 */
+        r.px += r.dx, r.py += r.dy, r.pz += r.dz;
+        r.i++;
+    }
+    /* volume.frag:41: all fetches of the batch are issued before any is consumed */
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        val[u] = 0.0f;
+        if (ok[u]) {
+            if (EXACT) {
+                val[u] = sample_exact(p, qx[u], qy[u], qz[u]);
+            } else if (PART) {
+                val[u] = tex3D<float>(p.tex_lin, (qx[u] * p.dims[0] - p.forg[0]) * p.inv_ldims[0],
+                                      (qy[u] * p.dims[1] - p.forg[1]) * p.inv_ldims[1],
+                                      (qz[u] * p.dims[2] - p.forg[2]) * p.inv_ldims[2]);
+            } else {
+                val[u] = tex3D<float>(p.tex_lin, qx[u], qy[u], qz[u]);
+            }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        if (ok[u]) {
+            if (STATS) r.nf++;
+            float sr, sg, sb, sa;
+            if (EXACT) {
+                /* volume.frag:42-43 and the LINEAR / CLAMP_TO_EDGE 1-D sampler */
+                const float tt = (val[u] - p.min_density) / p.range;
+                float uu = tt * lut_hi - 0.5f;
+                uu = (uu > -1.0f) ? uu : -1.0f; /* NaN -> texel 0 */
+                uu = (uu < lut_hi) ? uu : lut_hi;
+                const float fu = floorf(uu);
+                const int k = (int)fu + 1;
+                const float w = uu - fu;
+                const float4 a = sP[k], b = sP[k + 1];
+                sr = lerp1(a.x, b.x, w), sg = lerp1(a.y, b.y, w), sb = lerp1(a.z, b.z, w), sa = lerp1(a.w, b.w, w);
+                /* volume.frag:44-45 */
+                r.cr += r.T * (sa * sr);
+                r.cg += r.T * (sa * sg);
+                r.cb += r.T * (sa * sb);
+                r.T *= (1.0f - sa);
+            } else {
+                float uu = fmaf(val[u], p.lutA, p.lutB); /* padded LUT coordinate, u + 1 */
+                uu = fminf(fmaxf(uu, 0.0f), lut_hi + 1.0f);
+                const int k = (int)uu;
+                const float w = uu - (float)k;
+                if (LUT16) {
+                    const uint4 h = sH[k];
+                    const float2 prg = __half22float2(*reinterpret_cast<const __half2 *>(&h.x));
+                    const float2 pba = __half22float2(*reinterpret_cast<const __half2 *>(&h.y));
+                    const float2 drg = __half22float2(*reinterpret_cast<const __half2 *>(&h.z));
+                    const float2 dba = __half22float2(*reinterpret_cast<const __half2 *>(&h.w));
+                    sr = fmaf(w, drg.x, prg.x), sg = fmaf(w, drg.y, prg.y), sb = fmaf(w, dba.x, pba.x), sa = fmaf(w, dba.y, pba.y);
+                } else {
+                    const float4 a = sP[k], d = sD[k];
+                    sr = fmaf(w, d.x, a.x), sg = fmaf(w, d.y, a.y), sb = fmaf(w, d.z, a.z), sa = fmaf(w, d.w, a.w);
+                }
+                const float ta = r.T * sa;
+                r.cr = fmaf(ta, sr, r.cr);
+                r.cg = fmaf(ta, sg, r.cg);
+                r.cb = fmaf(ta, sb, r.cb);
+                r.T = fmaf(-r.T, sa, r.T);
+            }
+            if (CHECK || EXACT) {
+                if (r.T < p.ert_eps) {
+                    /* early ray termination: what is left contributes < eps per channel */
+                    r.done = true;
+#pragma unroll
+                    for (int v = u + 1; v < U; v++) ok[v] = false;
+                }
+            }
+        }
+    }
+    /* unchecked batches test for early termination once: the samples composited past the
+     * threshold are real samples, the bound on what is dropped is unchanged */
+    if (!CHECK && !EXACT && r.T < p.ert_eps) r.done = true;
+}
+
+/* EXACT: verification sampler.  ESS: occupancy grid consulted.  STATS: sample counters.
+ * PART: sort-last sub-volume.  UB: fetches in flight per thread (HW sampler).
+ * LUT16: transfer function staged as fp16 {value, difference} pairs, one LDS.128 per sample. */
+template <bool EXACT, bool ESS, bool STATS, bool PART, int UB, bool LUT16>
 __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant__ MarchParams p)
 {
     extern __shared__ float4 smem[];
-    float4 *sP = smem;                 /* nlut + 3 */
-    float4 *sD = sP + (p.nlut + 3);    /* nlut + 2 */
-    uint32_t *sOcc = reinterpret_cast<uint32_t *>(sD + (p.nlut + 2));
+    float4 *sP = smem;                                        /* nlut + 3 (fp32 path) */
+    float4 *sD = sP + (p.nlut + 3);                           /* nlut + 2 */
+    const uint4 *sH = reinterpret_cast<const uint4 *>(smem);  /* nlut + 2 (fp16 path) */
+    uint32_t *sOcc = LUT16 ? reinterpret_cast<uint32_t *>(smem + (p.nlut + 2))
+                           : reinterpret_cast<uint32_t *>(sD + (p.nlut + 2));
 
-    /* which tile: partition tiles dealt round-robin to ranks, 16x16 sub-tiles inside */
-    const uint32_t sub2 = p.pt_sub * p.pt_sub;
-    const uint32_t own_tile = blockIdx.x / sub2, r = blockIdx.x - own_tile * sub2;
-    const uint32_t t = p.pt_rank + own_tile * p.pt_nranks;
-    const uint32_t pty = t / p.pt_nx, ptx = t - pty * p.pt_nx;
-    const uint32_t sy_ = r / p.pt_sub, sx_ = r - sy_ * p.pt_sub;
-    const uint32_t x0 = ptx * p.pt_px + sx_ * VR_TILE, y0 = pty * p.pt_px + sy_ * VR_TILE;
+    /* Which tile.  The first sp_count blocks walk the tiles of the cube's screen bounding box in a
+     * square spiral from its centre: the longest rays (through the middle of the cube) start
+     * first and the short ones at the silhouette fill the tail.  The remaining blocks cover the
+     * rest of the target with the clear colour. */
+    const uint32_t nthreads = blockDim.x;
+    int tx, ty;
+    const bool in_bbox = blockIdx.x < p.sp_count;
+    if (in_bbox) {
+        int ox = 0, oy = 0;
+        const int b = (int)blockIdx.x;
+        if (b > 0) {
+            int r = (int)ceilf((sqrtf((float)(b + 1)) - 1.0f) * 0.5f);
+            while ((2 * r - 1) * (2 * r - 1) > b) r--;
+            while ((2 * r + 1) * (2 * r + 1) <= b) r++;
+            const int k = b - (2 * r - 1) * (2 * r - 1), seg = k / (2 * r), off = k - seg * 2 * r;
+            if (seg == 0) ox = r, oy = -r + 1 + off;
+            else if (seg == 1) ox = r - 1 - off, oy = r;
+            else if (seg == 2) ox = -r, oy = r - 1 - off;
+            else ox = -r + 1 + off, oy = -r;
+        }
+        tx = p.sp_cx + ox, ty = p.sp_cy + oy;
+        if (tx < p.rect[0] || ty < p.rect[1] || tx >= p.rect[2] || ty >= p.rect[3]) return;
+    } else {
+        const uint32_t j = blockIdx.x - p.sp_count;
+        ty = (int)(j / p.ntx), tx = (int)(j - (uint32_t)ty * p.ntx);
+        if (tx >= p.rect[0] && ty >= p.rect[1] && tx < p.rect[2] && ty < p.rect[3]) return;
+    }
+    const uint32_t x0 = (uint32_t)tx * VR_TILE, y0 = (uint32_t)ty * p.tile_h;
     if (x0 >= p.W || y0 >= p.H) return; /* uniform per CTA */
+    /* sort-first: partition tiles of pt_px pixels dealt round-robin to ranks */
+    if (p.pt_nranks > 1 && ((y0 / p.pt_px) * p.pt_nx + x0 / p.pt_px) % p.pt_nranks != p.pt_rank) return;
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t px = x0 + (warp & 1) * 8 + (lane & 7);
-    const uint32_t py = y0 + (warp >> 1) * 4 + (lane >> 3);
+    /* warp footprint ww x (32/ww) pixels, warps tiled across the 16-pixel-wide CTA tile */
+    const uint32_t ww = p.warp_w, wh = 32u / ww, wpr = VR_TILE / ww;
+    const uint32_t px = x0 + (warp % wpr) * ww + (lane % ww);
+    const uint32_t py = y0 + (warp / wpr) * wh + (lane / ww);
     const bool valid = px < p.W && py < p.H;
-
-    Entry e;
-    const bool covered = valid && pixel_entry(p, px, py, e);
     const size_t pix = (size_t)py * p.W + px;
 
-    if (!__syncthreads_or(covered)) {
+    /* tiles outside the screen bounding box of the cube cannot receive a fragment */
+    Entry e;
+    const bool covered = in_bbox && valid && pixel_entry(p, px, py, e);
+
+    if (!in_bbox || !__syncthreads_or(covered)) {
         /* nothing to march in this tile: clear colour only (offscreen_pass.cpp:170-173) */
         if (valid) {
             const unsigned char c = (unsigned char)(VR_CLEAR_RGB * 255.0f + 0.5f);
@@ -166,11 +351,16 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         return;
     }
 
-    for (uint32_t i = threadIdx.x; i < p.nlut + 3; i += VR_CTA_THREADS) sP[i] = p.lut_pad[i];
-    if (!EXACT)
-        for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += VR_CTA_THREADS) sD[i] = p.lut_dif[i];
+    if (LUT16) {
+        uint4 *dst = reinterpret_cast<uint4 *>(smem);
+        for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) dst[i] = p.lut_h16[i];
+    } else {
+        for (uint32_t i = threadIdx.x; i < p.nlut + 3; i += nthreads) sP[i] = p.lut_pad[i];
+        if (!EXACT)
+            for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) sD[i] = p.lut_dif[i];
+    }
     if (ESS)
-        for (int i = threadIdx.x; i < p.occ_words; i += VR_CTA_THREADS) sOcc[i] = p.occ[i];
+        for (int i = threadIdx.x; i < p.occ_words; i += nthreads) sOcc[i] = p.occ[i];
     __syncthreads();
 
     /* volume.frag:22-24 */
@@ -186,97 +376,27 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         posx = e.tex[0], posy = e.tex[1], posz = e.tex[2];
     }
 
-    constexpr int U = EXACT ? 1 : VR_BATCH;
-    const float lut_hi = (float)p.nlut;
-    uint32_t nb = 0, ns = 0, nf = 0;
-    bool done = !covered;
-    int i = 0;
+    Ray ray;
+    ray.cr = cr, ray.cg = cg, ray.cb = cb, ray.T = T;
+    ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
+    ray.i = 0, ray.done = !covered, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
-    while (!done) {
-        float qx[U], qy[U], qz[U], val[U];
-        bool ok[U];
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            /* volume.frag:33-37: loop bound and the strict bounds test */
-            const bool inb = !done && i < p.steps &&
-                             !(posx > 1.0f || posy > 1.0f || posz > 1.0f || posx < 0.0f || posy < 0.0f || posz < 0.0f);
-            if (!inb) done = true;
-            /* volume.frag:39-40: strict on both sides */
-            bool s = inb && posx < p.max_slice[0] && posy < p.max_slice[1] && posz < p.max_slice[2] &&
-                     posx > p.min_slice[0] && posy > p.min_slice[1] && posz > p.min_slice[2];
-            if (PART)
-                s = s && posx >= p.own_lo[0] && posy >= p.own_lo[1] && posz >= p.own_lo[2] && posx < p.own_hi[0] &&
-                    posy < p.own_hi[1] && posz < p.own_hi[2];
-            if (STATS) {
-                nb += inb;
-                ns += s;
-            }
-            if (ESS) s = s && cell_occupied<PART>(p, sOcc, posx, posy, posz);
-            ok[u] = s;
-            qx[u] = posx, qy[u] = posy, qz[u] = posz;
-            /* volume.frag:47 */
-            posx += dx, posy += dy, posz += dz;
-            i++;
-        }
-        /* volume.frag:41: all fetches of the batch are issued before any is consumed */
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            val[u] = 0.0f;
-            if (ok[u]) {
-                if (EXACT) {
-                    val[u] = sample_exact(p, qx[u], qy[u], qz[u]);
-                } else if (PART) {
-                    val[u] = tex3D<float>(p.tex_lin, (qx[u] * p.dims[0] - p.forg[0]) * p.inv_ldims[0],
-                                          (qy[u] * p.dims[1] - p.forg[1]) * p.inv_ldims[1],
-                                          (qz[u] * p.dims[2] - p.forg[2]) * p.inv_ldims[2]);
-                } else {
-                    val[u] = tex3D<float>(p.tex_lin, qx[u], qy[u], qz[u]);
-                }
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            if (ok[u]) {
-                if (STATS) nf++;
-                float sr, sg, sb, sa;
-                if (EXACT) {
-                    /* volume.frag:42-43 and the LINEAR / CLAMP_TO_EDGE 1-D sampler */
-                    const float tt = (val[u] - p.min_density) / p.range;
-                    float uu = tt * lut_hi - 0.5f;
-                    uu = (uu > -1.0f) ? uu : -1.0f; /* NaN -> texel 0 */
-                    uu = (uu < lut_hi) ? uu : lut_hi;
-                    const float fu = floorf(uu);
-                    const int k = (int)fu + 1;
-                    const float w = uu - fu;
-                    const float4 a = sP[k], b = sP[k + 1];
-                    sr = lerp1(a.x, b.x, w), sg = lerp1(a.y, b.y, w), sb = lerp1(a.z, b.z, w), sa = lerp1(a.w, b.w, w);
-                    /* volume.frag:44-45 */
-                    cr += T * (sa * sr);
-                    cg += T * (sa * sg);
-                    cb += T * (sa * sb);
-                    T *= (1.0f - sa);
-                } else {
-                    float uu = fmaf(val[u], p.lutA, p.lutB); /* padded LUT coordinate, u + 1 */
-                    uu = fminf(fmaxf(uu, 0.0f), lut_hi + 1.0f);
-                    const int k = (int)uu;
-                    const float w = uu - (float)k;
-                    const float4 a = sP[k], d = sD[k];
-                    sr = fmaf(w, d.x, a.x), sg = fmaf(w, d.y, a.y), sb = fmaf(w, d.z, a.z), sa = fmaf(w, d.w, a.w);
-                    const float ta = T * sa;
-                    cr = fmaf(ta, sr, cr);
-                    cg = fmaf(ta, sg, cg);
-                    cb = fmaf(ta, sb, cb);
-                    T = fmaf(-T, sa, T);
-                }
-                if (T < p.ert_eps) {
-                    /* early ray termination: what is left contributes < eps per channel */
-                    done = true;
-#pragma unroll
-                    for (int v = u + 1; v < U; v++) ok[v] = false;
-                }
-            }
-        }
+    /* Steps fast_lo..fast_hi need no bounds / slice / ownership test (see safe_interval). */
+    int fast_lo = 0x7fffffff, fast_hi = -1;
+    if (covered && !EXACT) safe_interval(p, ray, fast_lo, fast_hi);
+
+    constexpr int U = EXACT ? 1 : UB;
+    while (__any_sync(0xffffffffu, !ray.done)) {
+        /* warp-uniform choice: the checked batch is always correct, the unchecked one only
+         * where every live lane is inside its safe interval */
+        const bool can_fast = ray.done || (ray.i >= fast_lo && ray.i + U - 1 <= fast_hi);
+        if (!EXACT && __all_sync(0xffffffffu, can_fast))
+            march_batch<EXACT, ESS, STATS, PART, U, LUT16, false>(p, ray, sP, sD, sH, sOcc);
+        else
+            march_batch<EXACT, ESS, STATS, PART, U, LUT16, true>(p, ray, sP, sD, sH, sOcc);
     }
+    cr = ray.cr, cg = ray.cg, cb = ray.cb, T = ray.T;
+    uint32_t nb = ray.nb, ns = ray.ns, nf = ray.nf;
 
     if (valid) {
         uchar4 o;
@@ -320,42 +440,64 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     }
 }
 
-template <bool EXACT, bool ESS, bool STATS, bool PART>
-cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, cudaStream_t s)
+template <bool EXACT, bool ESS, bool STATS, bool PART, int UB, bool LUT16>
+cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, int threads, cudaStream_t s)
 {
-    auto kern = k_march<EXACT, ESS, STATS, PART>;
+    auto kern = k_march<EXACT, ESS, STATS, PART, UB, LUT16>;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    kern<<<grid, VR_CTA_THREADS, smem, s>>>(p);
+    if (p.carveout >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, p.carveout);
+    kern<<<grid, threads, smem, s>>>(p);
     return cudaGetLastError();
 }
 
-template <bool EXACT, bool ESS>
-cudaError_t launch2(const MarchParams &p, bool stats, bool part, size_t smem, dim3 grid, cudaStream_t s)
+template <bool EXACT, bool ESS, int UB, bool LUT16>
+cudaError_t launch2(const MarchParams &p, bool stats, bool part, size_t smem, dim3 grid, int threads, cudaStream_t s)
 {
-    if (stats) return part ? launch<EXACT, ESS, true, true>(p, smem, grid, s) : launch<EXACT, ESS, true, false>(p, smem, grid, s);
-    return part ? launch<EXACT, ESS, false, true>(p, smem, grid, s) : launch<EXACT, ESS, false, false>(p, smem, grid, s);
+    if (stats)
+        return part ? launch<EXACT, ESS, true, true, UB, LUT16>(p, smem, grid, threads, s)
+                    : launch<EXACT, ESS, true, false, UB, LUT16>(p, smem, grid, threads, s);
+    return part ? launch<EXACT, ESS, false, true, UB, LUT16>(p, smem, grid, threads, s)
+                : launch<EXACT, ESS, false, false, UB, LUT16>(p, smem, grid, threads, s);
+}
+
+template <bool ESS>
+cudaError_t launch_hw(const MarchParams &p, bool stats, bool part, int ub, bool lut16, size_t smem, dim3 grid, int threads,
+                      cudaStream_t s)
+{
+#define VR_HW(UB_)                                                                                    \
+    return lut16 ? launch2<false, ESS, UB_, true>(p, stats, part, smem, grid, threads, s)             \
+                 : launch2<false, ESS, UB_, false>(p, stats, part, smem, grid, threads, s)
+    switch (ub) {
+        case 2: VR_HW(2);
+        case 8: VR_HW(8);
+        default: VR_HW(4);
+    }
+#undef VR_HW
 }
 
 }  // namespace
 
-size_t vr_march_smem_bytes(const MarchParams &p, bool ess)
+size_t vr_march_smem_bytes(const MarchParams &p, bool ess, bool lut16)
 {
-    return sizeof(float4) * (size_t)(2 * p.nlut + 5) + (ess ? sizeof(uint32_t) * (size_t)p.occ_words : 0);
+    const size_t lut = lut16 ? sizeof(uint4) * (size_t)(p.nlut + 2) : sizeof(float4) * (size_t)(2 * p.nlut + 5);
+    return lut + (ess ? sizeof(uint32_t) * (size_t)p.occ_words : 0);
 }
 
-cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, cudaStream_t s)
+cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, bool lut16,
+                            int threads, cudaStream_t s)
 {
-    const uint64_t ntiles = (uint64_t)p.pt_nx * p.pt_ny;
-    if (p.pt_rank >= ntiles) return cudaSuccess; /* more ranks than tiles */
-    const uint64_t own = (ntiles - p.pt_rank + p.pt_nranks - 1) / p.pt_nranks;
-    const uint64_t ctas = own * p.pt_sub * p.pt_sub;
+    const uint64_t ctas = (uint64_t)p.sp_count + (uint64_t)p.ntx * p.nty;
     if (ctas == 0) return cudaSuccess;
     if (ctas > 0x7fffffffull) return cudaErrorInvalidConfiguration;
-    const size_t smem = vr_march_smem_bytes(p, ess);
+    if (exact) lut16 = false;
+    const size_t smem = vr_march_smem_bytes(p, ess, lut16);
     const dim3 grid((unsigned)ctas);
-    if (exact) return ess ? launch2<true, true>(p, stats, part, smem, grid, s) : launch2<true, false>(p, stats, part, smem, grid, s);
-    return ess ? launch2<false, true>(p, stats, part, smem, grid, s) : launch2<false, false>(p, stats, part, smem, grid, s);
+    if (exact)
+        return ess ? launch2<true, true, 1, false>(p, stats, part, smem, grid, threads, s)
+                   : launch2<true, false, 1, false>(p, stats, part, smem, grid, threads, s);
+    return ess ? launch_hw<true>(p, stats, part, ub, lut16, smem, grid, threads, s)
+               : launch_hw<false>(p, stats, part, ub, lut16, smem, grid, threads, s);
 }

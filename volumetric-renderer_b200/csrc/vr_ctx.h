@@ -41,6 +41,7 @@ struct MarchParams {
     int dtype;          /* vr_dtype of the texels (point fetches read the element type) */
     /* sort-last ownership, texture space, half-open [lo, hi) */
     float own_lo[3], own_hi[3];
+    float box_lo[3], box_hi[3]; /* bounds, slices and ownership intersected: where a step is sampled */
     /* S6: LUT, decoded to linear fp32, padded: P[k] = L[clamp(k-1, 0, n-1)], k = 0..n+2 (n+3 entries) */
     const float4 *lut_pad;
     const float4 *lut_dif; /* D[k] = P[k+1] - P[k], k = 0..n+1 (n+2 entries) */
@@ -57,7 +58,16 @@ struct MarchParams {
     unsigned long long *counters; /* [4]: covered, n_ref, n_inslice, n_fetch */
     float ert_eps;
     /* screen partition (sort-first): partition tiles of pt_px pixels, round-robin */
-    uint32_t pt_px, pt_nx, pt_ny, pt_rank, pt_nranks, pt_sub; /* pt_sub = pt_px / VR_TILE */
+    uint32_t pt_px, pt_nx, pt_ny, pt_rank, pt_nranks;
+    /* CTA tiles: ntx x nty over the target; rect = tiles that can be covered (x0,y0,x1,y1, exclusive);
+     * the first sp_count blocks spiral out from tile (sp_cx, sp_cy) over the square containing rect */
+    uint32_t ntx, nty, sp_count;
+    int sp_cx, sp_cy, rect[4];
+    int carveout;                                             /* shared-memory carve-out hint in percent, -1 = driver default */
+    uint32_t warp_w;                                          /* warp footprint width: 4, 8 or 16 pixels */
+    uint32_t tile_h;                                          /* CTA tile is VR_TILE x tile_h pixels */
+    uint32_t bbox[4];                                         /* x0, y0, x1, y1 (exclusive): pixels that can be covered */
+    const uint4 *lut_h16; /* fp16 {P.rg, P.ba, D.rg, D.ba}[k], k = 0..n+1 */
 };
 
 struct vr_ctx {
@@ -66,7 +76,8 @@ struct vr_ctx {
     std::string err;
 
     uint32_t W = 0, H = 0;
-    uchar4 *d_image = nullptr;
+    uchar4 *d_image = nullptr;                                       /* frame 0 */
+    uchar4 *d_image_slot[VR_MAX_FRAMES_IN_FLIGHT] = {nullptr, nullptr, nullptr, nullptr}; /* frames 1.. (lazily) */
     float4 *d_raw = nullptr;
     unsigned long long *d_counters = nullptr;
     unsigned long long *h_counters = nullptr; /* pinned */
@@ -94,6 +105,9 @@ struct vr_ctx {
     uint32_t nlut = 0;
     uint32_t *h_lut = nullptr; /* packed, as set */
     float4 *d_lut_pad = nullptr, *d_lut_dif = nullptr;
+    uint4 *d_lut_h16 = nullptr;
+    /* tuning knobs (environment: VR_BATCH, VR_LUT16, VR_CTA_THREADS, VR_BBOX) */
+    int tune_batch = 4, tune_lut16 = 0, tune_threads = 256, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
 
     /* occupancy */
     int occ_n[3] = {0, 0, 0};
@@ -112,8 +126,9 @@ struct vr_ctx {
 /* ---- kernels / device-side stages (each .cu implements its own) ---- */
 
 /* K1 (march.cu) */
-cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, cudaStream_t s);
-size_t vr_march_smem_bytes(const MarchParams &p, bool ess);
+cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, bool lut16,
+                            int threads, cudaStream_t s);
+size_t vr_march_smem_bytes(const MarchParams &p, bool ess, bool lut16);
 
 /* K0 (volume.cu) */
 cudaError_t vr_k0_global_minmax(const void *dev, int dtype, size_t n, float *h_min, float *h_max, cudaStream_t s);
