@@ -8,7 +8,6 @@
  * objects, the decoded LUT, the occupancy grid, and one stream.  Every mutator keeps the
  * reference's semantics (synchronous, copy-in), every failure becomes a status + message.
  */
-#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -126,18 +125,8 @@ int upload_lut(vr_ctx *c)
     }
     for (uint32_t k = 0; k < n + 2; k++)
         D[k] = make_float4(P[k + 1].x - P[k].x, P[k + 1].y - P[k].y, P[k + 1].z - P[k].z, P[k + 1].w - P[k].w);
-    /* fp16 staging of the same table: {P.rg, P.ba, D.rg, D.ba}; 0 stays exactly 0 */
-    std::vector<uint4> H(n + 2);
-    for (uint32_t k = 0; k < n + 2; k++) {
-        const __half2 prg = __floats2half2_rn(P[k].x, P[k].y), pba = __floats2half2_rn(P[k].z, P[k].w);
-        const __half2 drg = __floats2half2_rn(D[k].x, D[k].y), dba = __floats2half2_rn(D[k].z, D[k].w);
-        std::memcpy(&H[k].x, &prg, 4), std::memcpy(&H[k].y, &pba, 4), std::memcpy(&H[k].z, &drg, 4), std::memcpy(&H[k].w, &dba, 4);
-    }
     if (c->d_lut_pad) cudaFree(c->d_lut_pad), c->d_lut_pad = nullptr;
     if (c->d_lut_dif) cudaFree(c->d_lut_dif), c->d_lut_dif = nullptr;
-    if (c->d_lut_h16) cudaFree(c->d_lut_h16), c->d_lut_h16 = nullptr;
-    VR_CUDA(c, cudaMalloc(&c->d_lut_h16, sizeof(uint4) * (n + 2)));
-    VR_CUDA(c, cudaMemcpy(c->d_lut_h16, H.data(), sizeof(uint4) * (n + 2), cudaMemcpyHostToDevice));
     VR_CUDA(c, cudaMalloc(&c->d_lut_pad, sizeof(float4) * (n + 3)));
     VR_CUDA(c, cudaMalloc(&c->d_lut_dif, sizeof(float4) * (n + 2)));
     VR_CUDA(c, cudaMemcpy(c->d_lut_pad, P.data(), sizeof(float4) * (n + 3), cudaMemcpyHostToDevice));
@@ -287,8 +276,8 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     c->opt.collect_stats = 0;
     c->opt.write_raw = 0;
     if (const char *e = std::getenv("VR_BATCH")) c->tune_batch = std::atoi(e);
-    if (const char *e = std::getenv("VR_LUT16")) c->tune_lut16 = std::atoi(e);
-    if (const char *e = std::getenv("VR_CTA_THREADS")) c->tune_threads = std::atoi(e) == 128 ? 128 : 256;
+    if (const char *e = std::getenv("VR_ESS_MIN_EMPTY")) c->tune_ess_min_empty = (float)std::atof(e);
+    if (const char *e = std::getenv("VR_CTA_THREADS")) c->tune_threads = std::atoi(e) == 256 ? 256 : 128;
     if (const char *e = std::getenv("VR_BBOX")) c->tune_bbox = std::atoi(e);
     if (const char *e = std::getenv("VR_WARP_W")) {
         const int w = std::atoi(e);
@@ -324,7 +313,6 @@ extern "C" int vr_destroy(vr_ctx *c)
     release_volume(c);
     if (c->d_lut_pad) cudaFree(c->d_lut_pad);
     if (c->d_lut_dif) cudaFree(c->d_lut_dif);
-    if (c->d_lut_h16) cudaFree(c->d_lut_h16);
     if (c->d_image) cudaFree(c->d_image);
     if (c->d_raw) cudaFree(c->d_raw);
     for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
@@ -570,7 +558,6 @@ void fill_params(const vr_ctx *c, MarchParams &p)
     p.warp_w = (uint32_t)c->tune_warp_w;
     p.carveout = c->tune_carveout;
     p.tile_h = (uint32_t)c->tune_threads / VR_TILE;
-    p.lut_h16 = c->d_lut_h16;
     screen_bbox(c, p.bbox);
     p.ntx = (c->W + VR_TILE - 1) / VR_TILE, p.nty = (c->H + p.tile_h - 1) / p.tile_h;
     p.rect[0] = (int)(p.bbox[0] / VR_TILE), p.rect[1] = (int)(p.bbox[1] / p.tile_h);
@@ -603,10 +590,14 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     /* max_density == min_density divides by zero in volume.frag:42; only the exact path
      * reproduces the oracle's definition of that case */
     const bool exact = c->opt.sampler == VR_SAMPLER_EXACT || !nondegenerate;
-    const bool ess = c->opt.empty_skip && nondegenerate;
+    bool ess = c->opt.empty_skip && nondegenerate;
     if (ess) {
         const int rc = prepare_occupancy(c, s);
         if (rc != VR_OK) return rc;
+        /* skipping is result-identical, so whether to consult the grid is purely a cost question:
+         * with few empty cells the per-sample lookup costs more than the fetches it saves */
+        const double ncells = (double)c->occ_n[0] * c->occ_n[1] * c->occ_n[2];
+        ess = (double)c->occ_empty_cells >= (double)c->tune_ess_min_empty * ncells;
     }
     uchar4 *target = c->d_image;
     if (frame_index > 0) {
@@ -621,8 +612,7 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     p.out = target;
     if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
-    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, c->tune_batch, c->tune_lut16 != 0,
-                               c->tune_threads, s));
+    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, c->tune_batch, c->tune_threads, s));
     if (c->opt.collect_stats)
         VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     return VR_OK;

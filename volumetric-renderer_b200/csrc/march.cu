@@ -19,7 +19,6 @@
  * bit-identical to the CPU oracle.  Fused multiply-adds are written explicitly (fmaf) where
  * the hardware-sampler path is allowed to differ in rounding.
  */
-#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
@@ -137,7 +136,8 @@ struct Ray {
     float px, py, pz;      /* ray_pos */
     float dx, dy, dz;      /* ray_dir * step_size */
     int i;                 /* loop counter */
-    bool done;
+    bool done;             /* no more positions to generate */
+    bool stop;             /* early termination: composite nothing more */
     uint32_t nb, ns, nf;   /* counters (STATS) */
 };
 
@@ -169,15 +169,20 @@ __device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r
     }
 }
 
-/* U consecutive iterations of volume.frag:33-48: positions first, then all fetches back to
- * back, then transfer function + compositing.  CHECK = evaluate the per-step tests. */
-template <bool EXACT, bool ESS, bool STATS, bool PART, int U, bool LUT16, bool CHECK>
-__device__ __forceinline__ void march_batch(const MarchParams &p, Ray &r, const float4 *sP, const float4 *sD,
-                                            const uint4 *sH, const uint32_t *sOcc)
-{
-    const float lut_hi = (float)p.nlut;
-    float qx[U], qy[U], qz[U], val[U];
+/* One batch of U consecutive iterations of volume.frag:33-48, split in two halves so that the
+ * fetches of the next batch can be in flight while this one is composited. */
+template <int U>
+struct Batch {
+    float val[U];
     bool ok[U];
+};
+
+/* First half: positions (volume.frag:33-40,:47), then all U fetches back to back (:41).
+ * CHECK = evaluate the per-step tests; otherwise every step of a live ray is sampled. */
+template <bool EXACT, bool ESS, bool STATS, bool PART, int U, bool CHECK>
+__device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<U> &b, const uint32_t *sOcc)
+{
+    float qx[U], qy[U], qz[U];
 #pragma unroll
     for (int u = 0; u < U; u++) {
         bool s;
@@ -204,98 +209,87 @@ __device__ __forceinline__ void march_batch(const MarchParams &p, Ray &r, const 
             }
         }
         if (ESS) s = s && cell_occupied<PART>(p, sOcc, r.px, r.py, r.pz);
-        ok[u] = s;
+        b.ok[u] = s;
         qx[u] = r.px, qy[u] = r.py, qz[u] = r.pz;
         /* volume.frag:47 */
         r.px += r.dx, r.py += r.dy, r.pz += r.dz;
         r.i++;
     }
-    /* volume.frag:41: all fetches of the batch are issued before any is consumed */
 #pragma unroll
     for (int u = 0; u < U; u++) {
-        val[u] = 0.0f;
-        if (ok[u]) {
+        b.val[u] = 0.0f;
+        if (b.ok[u]) {
             if (EXACT) {
-                val[u] = sample_exact(p, qx[u], qy[u], qz[u]);
+                b.val[u] = sample_exact(p, qx[u], qy[u], qz[u]);
             } else if (PART) {
-                val[u] = tex3D<float>(p.tex_lin, (qx[u] * p.dims[0] - p.forg[0]) * p.inv_ldims[0],
-                                      (qy[u] * p.dims[1] - p.forg[1]) * p.inv_ldims[1],
-                                      (qz[u] * p.dims[2] - p.forg[2]) * p.inv_ldims[2]);
+                b.val[u] = tex3D<float>(p.tex_lin, (qx[u] * p.dims[0] - p.forg[0]) * p.inv_ldims[0],
+                                        (qy[u] * p.dims[1] - p.forg[1]) * p.inv_ldims[1],
+                                        (qz[u] * p.dims[2] - p.forg[2]) * p.inv_ldims[2]);
             } else {
-                val[u] = tex3D<float>(p.tex_lin, qx[u], qy[u], qz[u]);
+                b.val[u] = tex3D<float>(p.tex_lin, qx[u], qy[u], qz[u]);
             }
         }
     }
+}
+
+/* Second half: normalise, transfer function, composite (volume.frag:42-45). */
+template <bool EXACT, bool STATS, int U>
+__device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batch<U> &b, const float4 *sP,
+                                              const float4 *sD)
+{
+    const float lut_hi = (float)p.nlut;
 #pragma unroll
     for (int u = 0; u < U; u++) {
-        if (ok[u]) {
+        if (b.ok[u] && !r.stop) {
             if (STATS) r.nf++;
             float sr, sg, sb, sa;
             if (EXACT) {
                 /* volume.frag:42-43 and the LINEAR / CLAMP_TO_EDGE 1-D sampler */
-                const float tt = (val[u] - p.min_density) / p.range;
+                const float tt = (b.val[u] - p.min_density) / p.range;
                 float uu = tt * lut_hi - 0.5f;
                 uu = (uu > -1.0f) ? uu : -1.0f; /* NaN -> texel 0 */
                 uu = (uu < lut_hi) ? uu : lut_hi;
                 const float fu = floorf(uu);
                 const int k = (int)fu + 1;
                 const float w = uu - fu;
-                const float4 a = sP[k], b = sP[k + 1];
-                sr = lerp1(a.x, b.x, w), sg = lerp1(a.y, b.y, w), sb = lerp1(a.z, b.z, w), sa = lerp1(a.w, b.w, w);
+                const float4 a = sP[k], c = sP[k + 1];
+                sr = lerp1(a.x, c.x, w), sg = lerp1(a.y, c.y, w), sb = lerp1(a.z, c.z, w), sa = lerp1(a.w, c.w, w);
                 /* volume.frag:44-45 */
                 r.cr += r.T * (sa * sr);
                 r.cg += r.T * (sa * sg);
                 r.cb += r.T * (sa * sb);
                 r.T *= (1.0f - sa);
+                /* early ray termination: what is left contributes < eps per channel */
+                if (r.T < p.ert_eps) r.stop = true, r.done = true;
             } else {
-                float uu = fmaf(val[u], p.lutA, p.lutB); /* padded LUT coordinate, u + 1 */
+                float uu = fmaf(b.val[u], p.lutA, p.lutB); /* padded LUT coordinate, u + 1 */
                 uu = fminf(fmaxf(uu, 0.0f), lut_hi + 1.0f);
                 const int k = (int)uu;
                 const float w = uu - (float)k;
-                if (LUT16) {
-                    const uint4 h = sH[k];
-                    const float2 prg = __half22float2(*reinterpret_cast<const __half2 *>(&h.x));
-                    const float2 pba = __half22float2(*reinterpret_cast<const __half2 *>(&h.y));
-                    const float2 drg = __half22float2(*reinterpret_cast<const __half2 *>(&h.z));
-                    const float2 dba = __half22float2(*reinterpret_cast<const __half2 *>(&h.w));
-                    sr = fmaf(w, drg.x, prg.x), sg = fmaf(w, drg.y, prg.y), sb = fmaf(w, dba.x, pba.x), sa = fmaf(w, dba.y, pba.y);
-                } else {
-                    const float4 a = sP[k], d = sD[k];
-                    sr = fmaf(w, d.x, a.x), sg = fmaf(w, d.y, a.y), sb = fmaf(w, d.z, a.z), sa = fmaf(w, d.w, a.w);
-                }
+                const float4 a = sP[k], d = sD[k];
+                sr = fmaf(w, d.x, a.x), sg = fmaf(w, d.y, a.y), sb = fmaf(w, d.z, a.z), sa = fmaf(w, d.w, a.w);
                 const float ta = r.T * sa;
                 r.cr = fmaf(ta, sr, r.cr);
                 r.cg = fmaf(ta, sg, r.cg);
                 r.cb = fmaf(ta, sb, r.cb);
                 r.T = fmaf(-r.T, sa, r.T);
             }
-            if (CHECK || EXACT) {
-                if (r.T < p.ert_eps) {
-                    /* early ray termination: what is left contributes < eps per channel */
-                    r.done = true;
-#pragma unroll
-                    for (int v = u + 1; v < U; v++) ok[v] = false;
-                }
-            }
         }
     }
-    /* unchecked batches test for early termination once: the samples composited past the
-     * threshold are real samples, the bound on what is dropped is unchanged */
-    if (!CHECK && !EXACT && r.T < p.ert_eps) r.done = true;
+    /* the hardware path tests for early termination once per batch: the samples composited past
+     * the threshold are real samples, the bound on what is dropped is unchanged */
+    if (!EXACT && r.T < p.ert_eps) r.stop = true, r.done = true;
 }
 
 /* EXACT: verification sampler.  ESS: occupancy grid consulted.  STATS: sample counters.
- * PART: sort-last sub-volume.  UB: fetches in flight per thread (HW sampler).
- * LUT16: transfer function staged as fp16 {value, difference} pairs, one LDS.128 per sample. */
-template <bool EXACT, bool ESS, bool STATS, bool PART, int UB, bool LUT16>
+ * PART: sort-last sub-volume.  UB: steps per batch (HW sampler; two batches are in flight). */
+template <bool EXACT, bool ESS, bool STATS, bool PART, int UB>
 __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant__ MarchParams p)
 {
     extern __shared__ float4 smem[];
-    float4 *sP = smem;                                        /* nlut + 3 (fp32 path) */
-    float4 *sD = sP + (p.nlut + 3);                           /* nlut + 2 */
-    const uint4 *sH = reinterpret_cast<const uint4 *>(smem);  /* nlut + 2 (fp16 path) */
-    uint32_t *sOcc = LUT16 ? reinterpret_cast<uint32_t *>(smem + (p.nlut + 2))
-                           : reinterpret_cast<uint32_t *>(sD + (p.nlut + 2));
+    float4 *sP = smem;              /* nlut + 3 */
+    float4 *sD = sP + (p.nlut + 3); /* nlut + 2 */
+    uint32_t *sOcc = reinterpret_cast<uint32_t *>(sD + (p.nlut + 2));
 
     /* Which tile.  The first sp_count blocks walk the tiles of the cube's screen bounding box in a
      * square spiral from its centre: the longest rays (through the middle of the cube) start
@@ -351,14 +345,9 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         return;
     }
 
-    if (LUT16) {
-        uint4 *dst = reinterpret_cast<uint4 *>(smem);
-        for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) dst[i] = p.lut_h16[i];
-    } else {
-        for (uint32_t i = threadIdx.x; i < p.nlut + 3; i += nthreads) sP[i] = p.lut_pad[i];
-        if (!EXACT)
-            for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) sD[i] = p.lut_dif[i];
-    }
+    for (uint32_t i = threadIdx.x; i < p.nlut + 3; i += nthreads) sP[i] = p.lut_pad[i];
+    if (!EXACT)
+        for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) sD[i] = p.lut_dif[i];
     if (ESS)
         for (int i = threadIdx.x; i < p.occ_words; i += nthreads) sOcc[i] = p.occ[i];
     __syncthreads();
@@ -379,22 +368,51 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     Ray ray;
     ray.cr = cr, ray.cg = cg, ray.cb = cb, ray.T = T;
     ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
-    ray.i = 0, ray.done = !covered, ray.nb = 0, ray.ns = 0, ray.nf = 0;
+    ray.i = 0, ray.done = !covered, ray.stop = false, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
     /* Steps fast_lo..fast_hi need no bounds / slice / ownership test (see safe_interval). */
     int fast_lo = 0x7fffffff, fast_hi = -1;
     if (covered && !EXACT) safe_interval(p, ray, fast_lo, fast_hi);
 
     constexpr int U = EXACT ? 1 : UB;
-    while (__any_sync(0xffffffffu, !ray.done)) {
-        /* warp-uniform choice: the checked batch is always correct, the unchecked one only
-         * where every live lane is inside its safe interval */
-        const bool can_fast = ray.done || (ray.i >= fast_lo && ray.i + U - 1 <= fast_hi);
-        if (!EXACT && __all_sync(0xffffffffu, can_fast))
-            march_batch<EXACT, ESS, STATS, PART, U, LUT16, false>(p, ray, sP, sD, sH, sOcc);
-        else
-            march_batch<EXACT, ESS, STATS, PART, U, LUT16, true>(p, ray, sP, sD, sH, sOcc);
+    /* warp-uniform choice per batch: the checked form is always correct, the unchecked one only
+     * where every live lane is inside its safe interval */
+#define VR_ISSUE(B_)                                                                                        \
+    do {                                                                                                    \
+        const bool can_fast = ray.done || (ray.i >= fast_lo && ray.i + U - 1 <= fast_hi);                   \
+        if (!EXACT && __all_sync(0xffffffffu, can_fast))                                                    \
+            batch_issue<EXACT, ESS, STATS, PART, U, false>(p, ray, B_, sOcc);                               \
+        else                                                                                                \
+            batch_issue<EXACT, ESS, STATS, PART, U, true>(p, ray, B_, sOcc);                                \
+    } while (0)
+#define VR_CONSUME(B_) batch_consume<EXACT, STATS, U>(p, ray, B_, sP, sD)
+    if (EXACT) {
+        Batch<U> a;
+        while (!ray.done) {
+            VR_ISSUE(a);
+            VR_CONSUME(a);
+        }
+    } else {
+        /* two batches in rotation: the fetches of one are in flight while the other is composited */
+        Batch<U> a, b;
+        VR_ISSUE(a);
+        while (true) {
+            VR_ISSUE(b);
+            VR_CONSUME(a);
+            if (!__any_sync(0xffffffffu, !ray.done)) {
+                VR_CONSUME(b);
+                break;
+            }
+            VR_ISSUE(a);
+            VR_CONSUME(b);
+            if (!__any_sync(0xffffffffu, !ray.done)) {
+                VR_CONSUME(a);
+                break;
+            }
+        }
     }
+#undef VR_ISSUE
+#undef VR_CONSUME
     cr = ray.cr, cg = ray.cg, cb = ray.cb, T = ray.T;
     uint32_t nb = ray.nb, ns = ray.ns, nf = ray.nf;
 
@@ -440,10 +458,10 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     }
 }
 
-template <bool EXACT, bool ESS, bool STATS, bool PART, int UB, bool LUT16>
+template <bool EXACT, bool ESS, bool STATS, bool PART, int UB>
 cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, int threads, cudaStream_t s)
 {
-    auto kern = k_march<EXACT, ESS, STATS, PART, UB, LUT16>;
+    auto kern = k_march<EXACT, ESS, STATS, PART, UB>;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -453,51 +471,45 @@ cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, int threads, cu
     return cudaGetLastError();
 }
 
-template <bool EXACT, bool ESS, int UB, bool LUT16>
+template <bool EXACT, bool ESS, int UB>
 cudaError_t launch2(const MarchParams &p, bool stats, bool part, size_t smem, dim3 grid, int threads, cudaStream_t s)
 {
     if (stats)
-        return part ? launch<EXACT, ESS, true, true, UB, LUT16>(p, smem, grid, threads, s)
-                    : launch<EXACT, ESS, true, false, UB, LUT16>(p, smem, grid, threads, s);
-    return part ? launch<EXACT, ESS, false, true, UB, LUT16>(p, smem, grid, threads, s)
-                : launch<EXACT, ESS, false, false, UB, LUT16>(p, smem, grid, threads, s);
+        return part ? launch<EXACT, ESS, true, true, UB>(p, smem, grid, threads, s)
+                    : launch<EXACT, ESS, true, false, UB>(p, smem, grid, threads, s);
+    return part ? launch<EXACT, ESS, false, true, UB>(p, smem, grid, threads, s)
+                : launch<EXACT, ESS, false, false, UB>(p, smem, grid, threads, s);
 }
 
 template <bool ESS>
-cudaError_t launch_hw(const MarchParams &p, bool stats, bool part, int ub, bool lut16, size_t smem, dim3 grid, int threads,
+cudaError_t launch_hw(const MarchParams &p, bool stats, bool part, int ub, size_t smem, dim3 grid, int threads,
                       cudaStream_t s)
 {
-#define VR_HW(UB_)                                                                                    \
-    return lut16 ? launch2<false, ESS, UB_, true>(p, stats, part, smem, grid, threads, s)             \
-                 : launch2<false, ESS, UB_, false>(p, stats, part, smem, grid, threads, s)
     switch (ub) {
-        case 2: VR_HW(2);
-        case 8: VR_HW(8);
-        default: VR_HW(4);
+        case 4: return launch2<false, ESS, 4>(p, stats, part, smem, grid, threads, s);
+        case 8: return launch2<false, ESS, 8>(p, stats, part, smem, grid, threads, s);
+        default: return launch2<false, ESS, 2>(p, stats, part, smem, grid, threads, s);
     }
-#undef VR_HW
 }
 
 }  // namespace
 
-size_t vr_march_smem_bytes(const MarchParams &p, bool ess, bool lut16)
+size_t vr_march_smem_bytes(const MarchParams &p, bool ess)
 {
-    const size_t lut = lut16 ? sizeof(uint4) * (size_t)(p.nlut + 2) : sizeof(float4) * (size_t)(2 * p.nlut + 5);
-    return lut + (ess ? sizeof(uint32_t) * (size_t)p.occ_words : 0);
+    return sizeof(float4) * (size_t)(2 * p.nlut + 5) + (ess ? sizeof(uint32_t) * (size_t)p.occ_words : 0);
 }
 
-cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, bool lut16,
-                            int threads, cudaStream_t s)
+cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, int threads,
+                            cudaStream_t s)
 {
     const uint64_t ctas = (uint64_t)p.sp_count + (uint64_t)p.ntx * p.nty;
     if (ctas == 0) return cudaSuccess;
     if (ctas > 0x7fffffffull) return cudaErrorInvalidConfiguration;
-    if (exact) lut16 = false;
-    const size_t smem = vr_march_smem_bytes(p, ess, lut16);
+    const size_t smem = vr_march_smem_bytes(p, ess);
     const dim3 grid((unsigned)ctas);
     if (exact)
-        return ess ? launch2<true, true, 1, false>(p, stats, part, smem, grid, threads, s)
-                   : launch2<true, false, 1, false>(p, stats, part, smem, grid, threads, s);
-    return ess ? launch_hw<true>(p, stats, part, ub, lut16, smem, grid, threads, s)
-               : launch_hw<false>(p, stats, part, ub, lut16, smem, grid, threads, s);
+        return ess ? launch2<true, true, 1>(p, stats, part, smem, grid, threads, s)
+                   : launch2<true, false, 1>(p, stats, part, smem, grid, threads, s);
+    return ess ? launch_hw<true>(p, stats, part, ub, smem, grid, threads, s)
+               : launch_hw<false>(p, stats, part, ub, smem, grid, threads, s);
 }

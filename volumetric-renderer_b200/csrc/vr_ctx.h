@@ -67,7 +67,6 @@ struct MarchParams {
     uint32_t warp_w;                                          /* warp footprint width: 4, 8 or 16 pixels */
     uint32_t tile_h;                                          /* CTA tile is VR_TILE x tile_h pixels */
     uint32_t bbox[4];                                         /* x0, y0, x1, y1 (exclusive): pixels that can be covered */
-    const uint4 *lut_h16; /* fp16 {P.rg, P.ba, D.rg, D.ba}[k], k = 0..n+1 */
 };
 
 struct vr_ctx {
@@ -105,9 +104,9 @@ struct vr_ctx {
     uint32_t nlut = 0;
     uint32_t *h_lut = nullptr; /* packed, as set */
     float4 *d_lut_pad = nullptr, *d_lut_dif = nullptr;
-    uint4 *d_lut_h16 = nullptr;
-    /* tuning knobs (environment: VR_BATCH, VR_LUT16, VR_CTA_THREADS, VR_BBOX) */
-    int tune_batch = 4, tune_lut16 = 0, tune_threads = 256, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
+    /* tuning knobs (environment: VR_BATCH, VR_CTA_THREADS, VR_BBOX, VR_WARP_W, VR_CARVEOUT, VR_ESS_MIN_EMPTY) */
+    int tune_batch = 2, tune_threads = 128, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
+    float tune_ess_min_empty = 0.25f; /* consult the occupancy grid only if at least this share of cells is empty */
 
     /* occupancy */
     int occ_n[3] = {0, 0, 0};
@@ -126,9 +125,9 @@ struct vr_ctx {
 /* ---- kernels / device-side stages (each .cu implements its own) ---- */
 
 /* K1 (march.cu) */
-cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, bool lut16,
-                            int threads, cudaStream_t s);
-size_t vr_march_smem_bytes(const MarchParams &p, bool ess, bool lut16);
+cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, int threads,
+                            cudaStream_t s);
+size_t vr_march_smem_bytes(const MarchParams &p, bool ess);
 
 /* K0 (volume.cu) */
 cudaError_t vr_k0_global_minmax(const void *dev, int dtype, size_t n, float *h_min, float *h_max, cudaStream_t s);
