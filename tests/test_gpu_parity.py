@@ -186,3 +186,62 @@ def test_device_minmax_and_synth_match_cpu(vr, port):
                 assert np.abs(g.astype(np.int64) - c.astype(np.int64)).max() <= 1  # libm vs device sin/cos
     finally:
         op.close()
+
+
+# ---- the committed golden vectors (generated from the reference's own sources) -------------------
+
+import glob
+import os
+
+GOLDEN = sorted(g for g in glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz"))
+                if not g.endswith("host_surfaces.npz"))
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_cuda_path_reproduces_golden(vr, path):
+    g = np.load(path)
+    w, h = int(g["width"]), int(g["height"])
+    op = vr.OffscreenPass(w, h)
+    try:
+        op.volume_dataset_changed(vr.Dataset(np.ascontiguousarray(g["volume"]), float(g["min_density"]), float(g["max_density"])))
+        op.transfer_function_changed(g["lut"])
+        op.slicing_changed(g["min_slice"], g["max_slice"])
+        op.set_uniforms(g["view"], g["proj"], g["camera_position"])
+        op.set_options(sampler=vr.SAMPLER_EXACT, write_raw=1, collect_stats=1)
+        op.record()
+        raw, img, st = op.download_raw(), op.download(), op.stats()
+        assert np.array_equal(bits(raw), bits(g["raw"]))
+        assert np.array_equal(img, g["rgba8"])
+        assert [st.covered_pixels, st.n_ref, st.n_inslice] == g["stats"].tolist()
+        op.set_options(sampler=vr.SAMPLER_HW)
+        op.record()
+        assert_within_tolerance(op.download(), g["rgba8"], os.path.basename(path))
+    finally:
+        op.close()
+
+
+def test_frames_in_flight_do_not_interfere(vr, port):
+    """Two frames recorded on two streams into two targets equal the same frames rendered one by one."""
+    import torch
+    lut = tf(port, "B")
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.synth_volume(vr.SYNTH_FBM, 0x5EED0002, vr.U16, 64)
+        op.transfer_function_changed(lut)
+        cams = [vr.Camera().rotate((40.0 * k, 10.0 * k)) for k in range(4)]
+        want = []
+        for c in cams:
+            op.set_camera(c)
+            op.record()
+            want.append(op.download())
+        streams = [torch.cuda.Stream() for _ in range(4)]
+        hosts = [torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(4)]
+        for k, c in enumerate(cams):
+            op.set_camera(c)
+            op.record(streams[k].cuda_stream, k)
+            op.download_async(hosts[k].data_ptr(), streams[k].cuda_stream, k)
+        torch.cuda.synchronize()
+        for k in range(4):
+            assert np.array_equal(hosts[k].numpy(), want[k])
+    finally:
+        op.close()

@@ -1,0 +1,208 @@
+"""CPU tests of the product's host side (no GPU): the C-ABI library loads and exports every symbol
+include/vr.h declares; the input surfaces kept from the app (camera, projection, gradient, NRRD
+loader) give the reference's bits; partition helpers; error behaviour without a device."""
+import os
+import re
+import struct
+
+import numpy as np
+import pytest
+
+from common import bits
+from oracle import pyoracle
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST_GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "host_surfaces.npz")
+
+
+def test_library_exports_every_declared_symbol(vr):
+    hdr = open(os.path.join(ROOT, "include", "vr.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(vr_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 45
+    from volumetric_renderer_b200 import _lib
+    missing = [n for n in sorted(declared) if not hasattr(vr.lib, n)]
+    assert not missing, f"declared in include/vr.h but not exported: {missing}"
+    unbound = [n for n in sorted(declared) if n not in _lib.SIGNATURES]
+    assert not unbound, f"declared but not bound in _lib.py: {unbound}"
+    assert vr.lib.vr_abi_version() == 1
+
+
+def test_no_cpu_fallback_without_device(vr):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(vr.VrError) as e:
+        vr.OffscreenPass(64, 64)
+    assert "no CPU fallback" in str(e.value)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "volumetric-renderer_b200")
+    for dp, _, fns in os.walk(pkg):
+        if "build" in dp:
+            continue
+        for fn in fns:
+            if fn.endswith((".py", ".cu", ".cpp", ".h", "Makefile")):
+                txt = open(os.path.join(dp, fn), errors="ignore").read()
+                assert "oracle/" not in txt and "pyoracle" not in txt and "vr_oracle" not in txt, os.path.join(dp, fn)
+
+
+def test_camera_projection_gradient_match_golden_from_reference(vr):
+    g = np.load(HOST_GOLDEN)
+    cam = vr.Camera()
+    for m, want in zip([(0, 0), (4, 0), (-120, 80), (33.3, -17.7), (400, 5)], g["cameras"]):
+        cam.rotate(m)
+        got = np.concatenate([cam.get_view(), cam.get_position()])
+        assert np.array_equal(bits(got), bits(want))
+    assert np.array_equal(bits(vr.projection(512, 512)), bits(g["proj_512"]))
+    assert np.array_equal(bits(vr.projection(1920, 1080)), bits(g["proj_1080"]))
+    assert np.array_equal(bits(vr.projection(100, 100)), bits(g["proj_100"]))
+    from common import vr_gradient
+    assert np.array_equal(vr.Gradient().discretize(256), g["lut_A"])
+    assert np.array_equal(vr_gradient(vr, "B").discretize(256), g["lut_B"])
+    assert np.array_equal(vr_gradient(vr, "C").discretize(256), g["lut_C"])
+    assert np.array_equal(vr_gradient(vr, "B").discretize(7), g["lut_B_7"])
+
+
+def test_camera_matches_reference_build_on_random_input(vr, ref):
+    rng = np.random.default_rng(3)
+    a, b = vr.Camera(), ref.camera()
+    for _ in range(200):
+        d = tuple(float(x) for x in rng.uniform(-500, 500, 2))
+        a.rotate(d)
+        b.rotate(*d)
+        z = float(rng.uniform(-1, 1))
+        a.zoom(z)
+        b.zoom(z)
+    assert np.array_equal(bits(a.get_view()), bits(b.view))
+    assert np.array_equal(bits(a.get_position()), bits(b.position))
+
+
+def test_gradient_matches_reference_build_on_random_markers(vr, ref):
+    rng = np.random.default_rng(5)
+    for _ in range(20):
+        nc, na = int(rng.integers(1, 6)), int(rng.integers(1, 6))
+        cl, al = np.sort(rng.uniform(0, 1, nc)), np.sort(rng.uniform(0, 1, na))
+        cm = [(float(l), *[float(x) for x in rng.uniform(-0.2, 1.2, 3)]) for l in cl]
+        am = [(float(l), float(rng.uniform(-0.2, 1.2))) for l in al]
+        got = vr.Gradient([(m[0], m[1:]) for m in cm], am).discretize(64)
+        assert np.array_equal(got, ref.discretize(cm, am, count=64))
+
+
+# ---- NRRD loader -------------------------------------------------------------------------------
+
+NRRD_TYPES = [("int8", np.int8), ("uchar", np.uint8), ("short", np.int16), ("ushort", np.uint16), ("int", np.int32),
+              ("uint", np.uint32), ("longlong", np.int64), ("ulonglong", np.uint64), ("float", np.float32),
+              ("double", np.float64)]
+
+
+def write_nrrd(path, arr, tname, encoding="raw", endian="little", detached=False, extra=""):
+    nz, ny, nx = arr.shape
+    hdr = f"NRRD0004\n# test file\ntype: {tname}\ndimension: 3\nsizes: {nx} {ny} {nz}\n{extra}encoding: {encoding}\n"
+    if arr.dtype.itemsize > 1 and encoding != "ascii":
+        hdr += f"endian: {endian}\n"
+    data = arr.astype(arr.dtype.newbyteorder("<" if endian == "little" else ">"))
+    if encoding == "raw":
+        payload = data.tobytes()
+    elif encoding == "ascii":
+        payload = ("\n".join(" ".join(repr(x.item()) for x in row) for row in arr.reshape(-1, nx)) + "\n").encode()
+    else:
+        payload = data.tobytes().hex().encode()
+    if detached:
+        open(str(path) + ".raw", "wb").write(payload)
+        hdr += f"data file: {os.path.basename(str(path))}.raw\n"
+        open(path, "wb").write(hdr.encode())
+    else:
+        open(path, "wb").write(hdr.encode() + b"\n" + payload)
+
+
+@pytest.mark.parametrize("tname,dt", NRRD_TYPES)
+def test_nrrd_reader_matches_reference_parser_all_types(vr, ref, tmp_path, tname, dt):
+    rng = np.random.default_rng(11)
+    info = np.iinfo(dt) if np.issubdtype(dt, np.integer) else None
+    arr = (rng.integers(max(info.min, -2**40), min(info.max, 2**40), (3, 4, 5)).astype(dt) if info
+           else rng.normal(0, 100, (3, 4, 5)).astype(dt))
+    p = tmp_path / f"v_{tname}.nrrd"
+    write_nrrd(p, arr, tname)
+    got = vr.read_nrrd(str(p))
+    want, mn, mx = ref.load_nrrd(str(p))  # NrrdFileParser::parse + NrrdIO
+    assert got.shape == want.shape == (3, 4, 5)
+    if dt in (np.uint8, np.uint16):
+        assert got.dtype == dt and np.array_equal(got, arr)  # native on the device
+    else:
+        assert got.dtype == np.float32
+    assert np.array_equal(got.astype(np.float32), want)      # same floats as the reference's widening
+    assert float(got.min()) == mn and float(got.max()) == mx
+
+
+@pytest.mark.parametrize("encoding,endian,detached", [("raw", "big", False), ("ascii", "little", False),
+                                                      ("hex", "little", False), ("hex", "big", False),
+                                                      ("raw", "little", True)])
+def test_nrrd_reader_encodings(vr, ref, tmp_path, encoding, endian, detached):
+    arr = np.arange(2 * 3 * 4, dtype=np.uint16).reshape(2, 3, 4) * 1000
+    p = tmp_path / ("v.nhdr" if detached else "v.nrrd")
+    write_nrrd(p, arr, "ushort", encoding, endian, detached, extra="spacings: 1 2 3\nkey:=value\n")
+    got = vr.read_nrrd(str(p))
+    want, _, _ = ref.load_nrrd(str(p))
+    assert np.array_equal(got, arr) and np.array_equal(got.astype(np.float32), want)
+
+
+def test_nrrd_reader_rejects_what_the_reference_rejects(vr, ref, tmp_path):
+    p = tmp_path / "two_d.nrrd"
+    open(p, "wb").write(b"NRRD0004\ntype: uchar\ndimension: 2\nsizes: 4 4\nencoding: raw\n\n" + bytes(16))
+    with pytest.raises(vr.VrError) as e:
+        vr.read_nrrd(str(p))
+    assert "Invalid file properties" in str(e.value)  # nrrd_file_parser.cpp:28-30
+    with pytest.raises(RuntimeError):
+        ref.load_nrrd(str(p))
+    with pytest.raises(vr.VrError):
+        vr.read_nrrd(str(tmp_path / "missing.nrrd"))
+    q = tmp_path / "short.nrrd"
+    open(q, "wb").write(b"NRRD0004\ntype: uchar\ndimension: 3\nsizes: 4 4 4\nencoding: raw\n\n" + bytes(10))
+    with pytest.raises(vr.VrError):
+        vr.read_nrrd(str(q))
+    z = tmp_path / "gz.nrrd"
+    open(z, "wb").write(b"NRRD0004\ntype: uchar\ndimension: 3\nsizes: 2 2 2\nencoding: gzip\n\n" + bytes(8))
+    with pytest.raises(vr.VrError):
+        vr.read_nrrd(str(z))
+
+
+# ---- partition helpers -----------------------------------------------------------------------------
+
+def test_partition_boxes_tile_the_grid(vr):
+    for grid, full in [((2, 2, 2), (64, 64, 64)), ((3, 2, 1), (50, 33, 7)), ((1, 1, 1), (5, 5, 5)), ((2, 1, 1), (7, 3, 3))]:
+        seen = np.zeros(full[::-1], np.int32)
+        for b in range(grid[0] * grid[1] * grid[2]):
+            org, dims = vr.partition_box(grid, full, b)
+            seen[org[2]:org[2] + dims[2], org[1]:org[1] + dims[1], org[0]:org[0] + dims[0]] += 1
+        assert (seen == 1).all()
+    with pytest.raises(vr.VrError):
+        vr.partition_box((2, 2, 2), (64, 64, 64), 8)
+
+
+def test_partition_order_is_a_valid_front_to_back_order(vr):
+    """For random cameras and random rays from them: boxes are visited in an order consistent with out[]."""
+    rng = np.random.default_rng(17)
+    for grid in [(2, 2, 2), (3, 2, 1), (4, 1, 2)]:
+        full = (60, 60, 60)
+        nb = grid[0] * grid[1] * grid[2]
+        for _ in range(20):
+            cam = rng.uniform(-3, 3, 3).astype(np.float32)
+            order = vr.partition_order(grid, full, cam).tolist()
+            assert sorted(order) == list(range(nb))
+            rank_of = {b: k for k, b in enumerate(order)}
+            for _ in range(50):
+                target = rng.uniform(-0.5, 0.5, 3)
+                d = target - cam
+                ts = np.linspace(0, 2, 400)
+                pts = cam[None, :] + ts[:, None] * d[None, :] + 0.5  # texture space
+                inside = np.all((pts >= 0) & (pts < 1), axis=1)
+                visited = []
+                for q in pts[inside]:
+                    idx = [max(k for k in range(grid[a]) if q[a] >= (k * full[a] // grid[a]) / full[a]) for a in range(3)]
+                    b = idx[0] + grid[0] * (idx[1] + grid[1] * idx[2])
+                    if not visited or visited[-1] != b:
+                        visited.append(b)
+                ranks = [rank_of[b] for b in visited]
+                assert ranks == sorted(ranks), (grid, cam, visited, order)

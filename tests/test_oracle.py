@@ -1,0 +1,139 @@
+"""CPU tests of the oracle (no GPU): the plain-C port against the golden vectors generated from
+the reference's own sources (tests/golden/make_golden.py), against oracle/_ref itself when it is
+available, and against the closed-form anchors of SURVEY.md section 8(c)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from common import bits, tf
+from oracle import pyoracle
+
+GOLDEN = sorted(g for g in glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz"))
+                if not g.endswith("host_surfaces.npz"))
+
+
+def frame_from_golden(o, g):
+    f = pyoracle.Frame()
+    f.width, f.height = int(g["width"]), int(g["height"])
+    f.view[:] = g["view"].tolist()
+    f.proj[:] = g["proj"].tolist()
+    f.camera_position[:] = g["camera_position"].tolist()
+    f.min_density, f.max_density = float(g["min_density"]), float(g["max_density"])
+    f.min_slice[:] = g["min_slice"].tolist()
+    f.max_slice[:] = g["max_slice"].tolist()
+    f.ray_dist, f.step_size = pyoracle.DEFAULT_RAY_DIST, pyoracle.DEFAULT_STEP
+    return f
+
+
+def test_golden_fixtures_exist():
+    assert len(GOLDEN) >= 8
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_port_reproduces_golden_bit_for_bit(port, path):
+    g = np.load(path)
+    r = port.render(frame_from_golden(port, g), np.ascontiguousarray(g["volume"]), g["lut"], want_raw=True, want_iters=True)
+    assert np.array_equal(bits(r["raw"]), bits(g["raw"]))
+    assert np.array_equal(r["rgba8"], g["rgba8"])
+    assert np.array_equal(r["iters"], g["iters"])
+    assert [r["stats"].covered_pixels, r["stats"].n_ref, r["stats"].n_inslice] == g["stats"].tolist()
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_port_camera_path_reproduces_golden_uniforms(port, path):
+    """The uniform block itself (camera.cpp + update_uniform_buffer) from the recorded mouse input."""
+    g = np.load(path)
+    cam = port.camera()
+    for m in g["moves"]:
+        cam.rotate(float(m[0]), float(m[1]))
+    if float(g["zoom"]):
+        cam.zoom(float(g["zoom"]))
+    f = port.frame(int(g["width"]), int(g["height"]), cam, 0.0, 1.0)
+    assert np.array_equal(bits(np.array(f.view)), bits(g["view"]))
+    assert np.array_equal(bits(np.array(f.proj)), bits(g["proj"]))
+    assert np.array_equal(bits(np.array(f.camera_position)), bits(g["camera_position"]))
+
+
+def test_port_equals_reference_build_on_fresh_inputs(port, ref):
+    """Beyond the fixtures: random cameras, port vs the reference sources compiled here."""
+    rng = np.random.default_rng(7)
+    vol = port.synth(1, 0xABCDEF, np.uint16, 20)
+    lut = ref.discretize(*pyoracle.TF_B_MARKERS)
+    for _ in range(4):
+        mv = [tuple(rng.uniform(-300, 300, 2)) for _ in range(3)]
+        cp, cr = port.camera(), ref.camera()
+        for m in mv:
+            cp.rotate(*m)
+            cr.rotate(*m)
+        z = float(rng.uniform(-2, 2.2))
+        cp.zoom(z)
+        cr.zoom(z)
+        fp = port.frame(80, 60, cp, float(vol.min()), float(vol.max()))
+        fr = ref.frame(80, 60, cr, float(vol.min()), float(vol.max()))
+        assert bytes(fp) == bytes(fr)
+        a, b = port.render(fp, vol, lut, want_raw=True), ref.render(fr, vol, lut, want_raw=True)
+        assert np.array_equal(bits(a["raw"]), bits(b["raw"])) and np.array_equal(a["rgba8"], b["rgba8"])
+        assert a["stats"].n_ref == b["stats"].n_ref and a["stats"].n_inslice == b["stats"].n_inslice
+
+
+def test_row_subset_matches_full_frame(port):
+    vol = port.synth(1, 1, np.uint8, 16)
+    lut = tf(port, "B")
+    f = port.frame(64, 48, port.camera().rotate(-120, 80), 0.0, 255.0)
+    full = port.render(f, vol, lut, want_raw=True)
+    part = port.render(f, vol, lut, want_raw=True, row_start=2, row_stride=5)
+    assert np.array_equal(full["raw"][2::5], part["raw"][2::5])
+    assert (part["rgba8"][0] == 0).all()
+
+
+# ---- closed-form anchors ---------------------------------------------------------
+
+def test_anchor_constant_volume_constant_lut(port):
+    """Constant density, constant LUT (c, a): A = 1 - (1-a)^n, C = c*A with n = in-slice iterations."""
+    vol = np.full((8, 8, 8), 100, np.uint8)
+    lut = np.full(256, 0x40FF8040, np.uint32)  # A = 0x40, B = 0xFF, G = 0x80, R = 0x40
+    f = port.frame(64, 48, port.camera().rotate(-120, 80), 0.0, 255.0, (0.2, 0.2, 0.2), (0.8, 0.8, 0.8))
+    r = port.render(f, vol, lut, want_raw=True, want_iters=True)
+    a = np.float32(0x40) / np.float32(255)
+    # count in-slice iterations per pixel by re-rendering with an opaque LUT? use stats instead:
+    assert r["stats"].n_inslice > 0
+    raw = r["raw"]
+    covered = r["iters"] > 0
+    # inside the sliced region the border never contributes, so density is exactly 100 everywhere:
+    # every in-slice sample adds the same (c, a); check A against (1-a)^n for the n implied by A
+    covered &= raw[..., 3] < 0.999
+    A = raw[..., 3][covered]
+    n = np.round(np.log1p(-A.astype(np.float64)) / np.log1p(-np.float64(a)))
+    assert np.allclose(1.0 - (1.0 - np.float64(a)) ** n, A, atol=2e-5)
+    lin = lambda c8: (c8 / 255.0 / 12.92) if c8 / 255.0 <= 0.04045 else ((c8 / 255.0 + 0.055) / 1.055) ** 2.4
+    for ch, c8 in enumerate((0x40, 0x80, 0xFF)):
+        assert np.allclose(raw[..., ch][covered], lin(c8) * A, atol=3e-5)
+
+
+def test_anchor_startup_state_and_clear_colour(port):
+    """One white opaque texel (offscreen_pass.cpp:119): covered -> (255,255,255,255); else (28,28,28,255)."""
+    f = port.frame(64, 48, port.camera(), 0.0, 0.0)
+    r = port.render(f, np.zeros((1, 1, 1), np.float32), pyoracle.TF_0, want_raw=True)
+    cov = r["raw"][..., 3] > 0
+    assert cov.any() and (~cov).any()
+    assert (r["rgba8"][cov] == 255).all()
+    assert (r["rgba8"][~cov] == (28, 28, 28, 255)).all()
+
+
+def test_anchor_default_gradient_values(port, ref):
+    want = np.array([0xFF000000 | (i * 0x010101) for i in range(256)], np.uint32)
+    assert np.array_equal(port.discretize(*pyoracle.TF_A_MARKERS), want)
+    assert np.array_equal(ref.discretize(*pyoracle.TF_A_MARKERS), want)
+
+
+def test_anchor_opaque_lut_shows_first_inslice_sample(port):
+    """TF-A (alpha 1 everywhere): the pixel is the sRGB-decoded LUT value of the first in-slice sample."""
+    vol = port.synth(0, 0x5EED0000, np.uint8, 24)
+    lut = tf(port, "A")
+    f = port.frame(64, 48, port.camera().rotate(-120, 80), float(vol.min()), float(vol.max()))
+    r = port.render(f, vol, lut, want_raw=True)
+    cov = r["raw"][..., 3] > 0
+    assert np.all(r["raw"][..., 3][cov] == 1.0)
+    assert np.all(r["raw"][..., 0][cov] == r["raw"][..., 1][cov])  # grey ramp
