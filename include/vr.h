@@ -226,6 +226,24 @@ int vr_clear_partition(vr_ctx *ctx);
  * each pointing at that partial's pixel 0. */
 int vr_composite(vr_ctx *ctx, const void *const *parts, uint32_t nparts, uint64_t pixel_begin, uint64_t pixel_end,
                  void *cuda_stream);
+/* vr_composite with an explicit destination (device pointer to the RGBA8 frame, NULL = this
+ * context's image): lets every rank merge its own pixel range straight into the display rank's
+ * image over NVLink. */
+int vr_composite_to(vr_ctx *ctx, const void *const *parts, uint32_t nparts, uint64_t pixel_begin, uint64_t pixel_end,
+                    void *out_rgba8, void *cuda_stream);
+
+/* Peer memory for one-process-per-GPU runs (CUDA IPC; all GPUs of one NVLink/NVSwitch box).
+ * vr_ipc_export: 64-byte handle of this context's RGBA8 image (which = 0) or float4 output
+ * (which = 1).  vr_ipc_open maps a peer's buffer into this process (peer access is enabled on
+ * first use); the pointer can be passed to vr_set_image_target / vr_composite(_to).
+ * vr_set_image_target redirects frame 0 of vr_render into such a pointer (NULL restores): with
+ * sort-first partitioning every rank writes its tiles directly into the display rank's image --
+ * the tile gather is the kernel's own store. */
+int vr_ipc_export(vr_ctx *ctx, int which, unsigned char handle[64]);
+int vr_ipc_open(vr_ctx *ctx, const unsigned char handle[64], void **dev_ptr);
+int vr_ipc_close(vr_ctx *ctx, void *dev_ptr);
+int vr_set_image_target(vr_ctx *ctx, void *dev_rgba8);
+
 /* Regular split of a grid into grid[0]*grid[1]*grid[2] sub-boxes: box `index` (x fastest)
  * owns voxels [org, org+dims) with faces at floor(k * full / grid). */
 int vr_partition_box(const uint32_t grid[3], const uint32_t full_dims[3], uint32_t index, uint32_t org[3],

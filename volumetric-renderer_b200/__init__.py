@@ -269,9 +269,26 @@ class OffscreenPass:
     def clear_partition(self):
         self._check(lib.vr_clear_partition(self._h))
 
-    def composite(self, part_ptrs, pixel_begin: int, pixel_end: int, stream: int | None = None):
+    def composite(self, part_ptrs, pixel_begin: int, pixel_end: int, stream: int | None = None, out_ptr: int | None = None):
         arr = (C.c_void_p * len(part_ptrs))(*part_ptrs)
-        self._check(lib.vr_composite(self._h, arr, len(part_ptrs), pixel_begin, pixel_end, stream))
+        self._check(lib.vr_composite_to(self._h, arr, len(part_ptrs), pixel_begin, pixel_end, out_ptr, stream))
+
+    def ipc_export(self, which: int = 0) -> bytes:
+        buf = (C.c_ubyte * 64)()
+        self._check(lib.vr_ipc_export(self._h, which, buf))
+        return bytes(buf)
+
+    def ipc_open(self, handle: bytes) -> int:
+        buf = (C.c_ubyte * 64)(*handle)
+        p = C.c_void_p()
+        self._check(lib.vr_ipc_open(self._h, buf, C.byref(p)))
+        return p.value
+
+    def ipc_close(self, ptr: int):
+        self._check(lib.vr_ipc_close(self._h, ptr))
+
+    def set_image_target(self, ptr: int | None):
+        self._check(lib.vr_set_image_target(self._h, ptr))
 
 
 def read_nrrd(path: str) -> np.ndarray:

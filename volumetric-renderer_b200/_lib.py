@@ -79,6 +79,11 @@ SIGNATURES = {
     "vr_synth_subvolume": (C.c_int, [_P, C.c_int, C.c_uint32, C.c_int]),
     "vr_clear_partition": (C.c_int, [_P]),
     "vr_composite": (C.c_int, [_P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _P]),
+    "vr_composite_to": (C.c_int, [_P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _P, _P]),
+    "vr_ipc_export": (C.c_int, [_P, C.c_int, _P]),
+    "vr_ipc_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
+    "vr_ipc_close": (C.c_int, [_P, _P]),
+    "vr_set_image_target": (C.c_int, [_P, _P]),
     "vr_partition_box": (C.c_int, [_P, _P, C.c_uint32, _P, _P]),
     "vr_partition_order": (C.c_int, [_P, _P, _P, _P]),
     "vr_bench_tex_peak": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]),

@@ -599,7 +599,7 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
         const double ncells = (double)c->occ_n[0] * c->occ_n[1] * c->occ_n[2];
         ess = (double)c->occ_empty_cells >= (double)c->tune_ess_min_empty * ncells;
     }
-    uchar4 *target = c->d_image;
+    uchar4 *target = c->ext_image ? c->ext_image : c->d_image;
     if (frame_index > 0) {
         if (!c->d_image_slot[frame_index]) {
             VR_CUDA(c, cudaMalloc(&c->d_image_slot[frame_index], (size_t)c->W * c->H * sizeof(uchar4)));
@@ -869,14 +869,7 @@ extern "C" int vr_partition_order(const uint32_t grid[3], const uint32_t full_di
 extern "C" int vr_composite(vr_ctx *c, const void *const *parts, uint32_t nparts, uint64_t pixel_begin, uint64_t pixel_end,
                             void *cuda_stream)
 {
-    if (!c || !parts || nparts == 0) return fail(c, VR_ERR_INVALID, "vr_composite: bad arguments");
-    if (pixel_end > (uint64_t)c->W * c->H || pixel_begin > pixel_end) return fail(c, VR_ERR_INVALID, "vr_composite: pixel range outside the frame");
-    VR_CUDA(c, cudaSetDevice(c->device));
-    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
-    c->last_stream = s;
-    VR_CUDA(c, vr_launch_composite(reinterpret_cast<const float4 *const *>(parts), nparts, pixel_begin, pixel_end, c->d_image,
-                                   nullptr, s));
-    return VR_OK;
+    return vr_composite_to(c, parts, nparts, pixel_begin, pixel_end, nullptr, cuda_stream);
 }
 
 /* test hook: the fp32 columns of inverse(proj*view) the kernel will use */
@@ -907,3 +900,56 @@ extern "C" int vr_nrrd_read_host(const char *path, int *dtype, uint32_t dims[3],
 }
 
 extern "C" void vr_free_host(void *p) { std::free(p); }
+
+/* ============================================== peer memory (one process per GPU) == */
+
+extern "C" int vr_set_image_target(vr_ctx *c, void *dev_rgba8)
+{
+    if (!c) return VR_ERR_INVALID;
+    c->ext_image = reinterpret_cast<uchar4 *>(dev_rgba8);
+    return VR_OK;
+}
+
+extern "C" int vr_ipc_export(vr_ctx *c, int which, unsigned char handle[64])
+{
+    if (!c || !handle || (which != 0 && which != 1)) return fail(c, VR_ERR_INVALID, "vr_ipc_export: bad arguments");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    void *ptr = which == 0 ? (void *)c->d_image : (void *)c->d_raw;
+    if (!ptr) return fail(c, VR_ERR_STATE, "vr_ipc_export: that buffer does not exist (options.write_raw?)");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    VR_CUDA(c, cudaIpcGetMemHandle(&h, ptr));
+    std::memcpy(handle, &h, 64);
+    return VR_OK;
+}
+
+extern "C" int vr_ipc_open(vr_ctx *c, const unsigned char handle[64], void **dev_ptr)
+{
+    if (!c || !handle || !dev_ptr) return fail(c, VR_ERR_INVALID, "vr_ipc_open: bad arguments");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    VR_CUDA(c, cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return VR_OK;
+}
+
+extern "C" int vr_ipc_close(vr_ctx *c, void *dev_ptr)
+{
+    if (!c || !dev_ptr) return VR_ERR_INVALID;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaIpcCloseMemHandle(dev_ptr));
+    return VR_OK;
+}
+
+extern "C" int vr_composite_to(vr_ctx *c, const void *const *parts, uint32_t nparts, uint64_t pixel_begin,
+                               uint64_t pixel_end, void *out_rgba8, void *cuda_stream)
+{
+    if (!c || !parts || nparts == 0) return fail(c, VR_ERR_INVALID, "vr_composite: bad arguments");
+    if (pixel_end > (uint64_t)c->W * c->H || pixel_begin > pixel_end) return fail(c, VR_ERR_INVALID, "vr_composite: pixel range outside the frame");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+    c->last_stream = s;
+    uchar4 *out = out_rgba8 ? reinterpret_cast<uchar4 *>(out_rgba8) : (c->ext_image ? c->ext_image : c->d_image);
+    VR_CUDA(c, vr_launch_composite(reinterpret_cast<const float4 *const *>(parts), nparts, pixel_begin, pixel_end, out, nullptr, s));
+    return VR_OK;
+}

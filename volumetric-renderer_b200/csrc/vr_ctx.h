@@ -78,6 +78,7 @@ struct vr_ctx {
     uchar4 *d_image = nullptr;                                       /* frame 0 */
     uchar4 *d_image_slot[VR_MAX_FRAMES_IN_FLIGHT] = {nullptr, nullptr, nullptr, nullptr}; /* frames 1.. (lazily) */
     float4 *d_raw = nullptr;
+    uchar4 *ext_image = nullptr; /* vr_set_image_target: frame 0 is written there instead (peer memory) */
     unsigned long long *d_counters = nullptr;
     unsigned long long *h_counters = nullptr; /* pinned */
 

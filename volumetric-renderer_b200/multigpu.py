@@ -1,0 +1,213 @@
+"""Multi-GPU partitioning of the ray-march pass: one process per GPU, torch.distributed for the
+plumbing (rendezvous, barriers, the NCCL fallback exchange), the data path in the CUDA library.
+
+The reference is single-GPU; these are the two partitions BASELINE.json names.
+
+SortFirst   image tiles dealt round-robin to ranks, volume replicated.  Every rank's K1 stores its
+            tiles straight into the display rank's RGBA8 image through a CUDA-IPC mapped pointer
+            (NVLink peer writes): the gather is the kernel's own epilogue, there is no collective.
+SortLast    volume split into a regular grid of sub-boxes (one per rank, one ghost voxel towards
+            each neighbour).  Every rank marches the full frame over ITS samples only (global step
+            positions, half-open ownership) into a float4 partial; then rank r merges pixel range r
+            of all partials in view order with K2, reading the peers' partials directly over NVLink
+            and writing into the display rank's image (direct-send; exchange + merge + display
+            blend in one kernel).  mode="nccl" exchanges the ranges with send/recv instead.
+
+Host-side logic that does not need a GPU (ranges, grids, ordering, the exchange schedule) is kept in
+plain functions so it is testable with the gloo backend.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def pixel_ranges(npix: int, world: int):
+    """Contiguous pixel range of every rank for direct-send compositing (multiples of 32 pixels)."""
+    per = -(-npix // world)
+    per = -(-per // 32) * 32
+    return [(min(r * per, npix), min((r + 1) * per, npix)) for r in range(world)]
+
+
+def grid_for_world(world: int):
+    """Sub-box grid for `world` ranks: split the axes as evenly as possible (8 -> 2x2x2, 4 -> 2x2x1)."""
+    g = [1, 1, 1]
+    w, a = world, 0
+    f = 2
+    factors = []
+    while w > 1:
+        while w % f == 0:
+            factors.append(f)
+            w //= f
+        f += 1
+    for f in sorted(factors, reverse=True):
+        a = int(np.argmin(g))
+        g[a] *= f
+    return tuple(g)
+
+
+def exchange_ranges(partial, ranges, rank: int, world: int, group=None):
+    """Direct-send without peer memory: rank r receives pixel range r of every rank's partial.
+    partial: tensor [npix, 4] float32.  Returns tensor [world, len_r, 4] (slot i = rank i's data).
+    Uses batched send/recv so it runs on NCCL and on gloo alike."""
+    import torch
+    import torch.distributed as dist
+
+    b, e = ranges[rank]
+    recv = torch.empty((world, e - b, 4), dtype=partial.dtype, device=partial.device)
+    recv[rank].copy_(partial[b:e])
+    ops = []
+    for peer in range(world):
+        if peer == rank:
+            continue
+        pb, pe = ranges[peer]
+        if pe > pb:
+            ops.append(dist.P2POp(dist.isend, partial[pb:pe].contiguous(), peer, group))
+        if e > b:
+            ops.append(dist.P2POp(dist.irecv, recv[peer], peer, group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    return recv
+
+
+class _DevBuf:
+    """A device pointer as a __cuda_array_interface__ object so torch can wrap it without a copy."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def _gather_handles(handle: bytes, world: int, group=None):
+    import torch.distributed as dist
+    out = [None] * world
+    dist.all_gather_object(out, handle, group=group)
+    return out
+
+
+class SortFirst:
+    """Sort-first image-tile partition (BASELINE.json config 4)."""
+
+    def __init__(self, op, rank: int, world: int, tile_px: int = 64, display_rank: int = 0, group=None):
+        import torch.distributed as dist
+        self.op, self.rank, self.world, self.display, self.group = op, rank, world, display_rank, group
+        op.set_partition_sort_first(rank, world, tile_px)
+        self._peer = None
+        if world > 1:
+            handles = _gather_handles(op.ipc_export(0), world, group)
+            if rank != display_rank:
+                self._peer = op.ipc_open(handles[display_rank])
+                op.set_image_target(self._peer)
+            dist.barrier(group)
+
+    def render(self, stream: int | None = None):
+        """Record this rank's tiles; they land in the display rank's image."""
+        self.op.record(stream)
+
+    def finish(self):
+        """All ranks' tiles are in the display rank's image when this returns."""
+        import torch.distributed as dist
+        self.op.sync()
+        if self.world > 1:
+            dist.barrier(self.group)
+
+    def close(self):
+        if self._peer:
+            self.op.set_image_target(None)
+            self.op.sync()
+            self.op.ipc_close(self._peer)
+            self._peer = None
+
+
+class SortLast:
+    """Sort-last sub-box partition with view-ordered direct-send compositing (BASELINE.json config 5)."""
+
+    def __init__(self, op, rank: int, world: int, full_dims, grid=None, display_rank: int = 0, mode: str = "p2p",
+                 group=None):
+        import torch.distributed as dist
+        from . import partition_box
+        self.op, self.rank, self.world, self.display, self.mode, self.group = op, rank, world, display_rank, mode, group
+        self.full = tuple(int(x) for x in full_dims)
+        self.grid = tuple(grid) if grid else grid_for_world(world)
+        assert self.grid[0] * self.grid[1] * self.grid[2] == world
+        self.org, self.dims = partition_box(self.grid, self.full, rank)
+        op.set_options(write_raw=1)
+        op.set_partition_sort_last(self.full, self.org, self.dims)
+        w, h = op.size
+        self.npix = w * h
+        self.ranges = pixel_ranges(self.npix, world)
+        self._peers_raw, self._peer_img = None, None
+        if world > 1 and mode == "p2p":
+            raws = _gather_handles(op.ipc_export(1), world, group)
+            imgs = _gather_handles(op.ipc_export(0), world, group)
+            self._peers_raw = [op.get_raw() if r == rank else op.ipc_open(raws[r]) for r in range(world)]
+            self._peer_img = None if rank == display_rank else op.ipc_open(imgs[display_rank])
+            dist.barrier(group)
+
+    def set_global_density_range(self):
+        """Reduce the per-rank density range to the global one (ubo.min/max_density are global)."""
+        import torch
+        import torch.distributed as dist
+        _, _, mn, mx = self.op.volume_info()
+        if self.world > 1:
+            t = torch.tensor([-mn, mx], dtype=torch.float64, device="cuda" if dist.get_backend(self.group) == "nccl" else "cpu")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+            mn, mx = -float(t[0]), float(t[1])
+        self.op.set_density_range(mn, mx)
+        return mn, mx
+
+    def render(self, camera_position, stream: int | None = None):
+        """March this rank's samples, then merge.  The frame is complete in the display rank's image
+        after finish()."""
+        import torch
+        import torch.distributed as dist
+        from . import partition_order
+        op, rank, world = self.op, self.rank, self.world
+        op.record(stream)
+        order = [int(b) for b in partition_order(self.grid, self.full, camera_position)]
+        b, e = self.ranges[rank]
+        if world == 1:
+            op.composite([op.get_raw()], 0, self.npix, stream)
+            return
+        op.sync()
+        dist.barrier(self.group)  # every partial is complete before anyone reads it
+        if self.mode == "p2p":
+            if e > b:
+                op.composite([self._peers_raw[r] for r in order], b, e, stream, out_ptr=self._peer_img)
+        else:
+            raw = torch.as_tensor(_DevBuf(op.get_raw(), (self.npix, 4), "<f4"), device="cuda")
+            recv = exchange_ranges(raw, self.ranges, rank, world, self.group)
+            torch.cuda.current_stream().synchronize()  # the merge runs on the context's stream
+            self._recv = recv  # keep alive until the merge has run
+            base = recv.data_ptr()
+            n = e - b
+            # K2 indexes parts[k] + pixel, so shift each slot back by `b` pixels (16 bytes per pixel)
+            ptrs = [base + r * n * 16 - b * 16 for r in order]
+            img = torch.as_tensor(_DevBuf(op.get_image()[0], (self.npix, 4), "|u1"), device="cuda")
+            if e > b:
+                op.composite(ptrs, b, e, None)
+            op.sync()
+            # gather the merged ranges on the display rank
+            per = max(r[1] - r[0] for r in self.ranges)
+            mine = torch.zeros((per, 4), dtype=torch.uint8, device="cuda")
+            mine[: e - b].copy_(img[b:e])
+            out = [torch.empty_like(mine) for _ in range(world)] if rank == self.display else None
+            dist.gather(mine, out, dst=self.display, group=self.group)
+            if rank == self.display:
+                for r, (rb, re_) in enumerate(self.ranges):
+                    img[rb:re_].copy_(out[r][: re_ - rb])
+
+    def finish(self):
+        import torch.distributed as dist
+        self.op.sync()
+        if self.world > 1:
+            dist.barrier(self.group)
+
+    def close(self):
+        if self._peers_raw:
+            self.op.sync()
+            for r, p in enumerate(self._peers_raw):
+                if r != self.rank:
+                    self.op.ipc_close(p)
+            if self._peer_img:
+                self.op.ipc_close(self._peer_img)
+            self._peers_raw, self._peer_img = None, None
