@@ -57,3 +57,32 @@ def test_multi_process_partitions_on_real_gpus():
            "--master-port", "29517", os.path.join(ROOT, "tests", "mgpu_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "MGPU_CHECK OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_cpp_host_mirror_renders_the_same_frames(vr, tmp_path):
+    """host/example_orbit (C++ over host/offscreen_pass.hpp) against the Python mirror: same frames."""
+    exe = os.path.join(ROOT, "volumetric-renderer_b200", "host", "example_orbit")
+    if not os.path.exists(exe):
+        pytest.skip("example_orbit not built")
+    W, H, n, frames = 160, 120, 48, 3
+    out = tmp_path / "o.ppm"
+    r = subprocess.run([exe, str(out), str(W), str(H), str(n), str(frames)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    got_sum = int(r.stdout.split("checksum=")[1].split()[0])
+    op = vr.OffscreenPass(W, H)
+    op.synth_volume(vr.SYNTH_FBM, 0x5EED0002, vr.U16, n)
+    op.transfer_function_changed(vr.Gradient([(0.0, (0, 0, 0.5)), (0.5, (1, 0.5, 0)), (1.0, (1, 1, 1))],
+                                             [(0.0, 0.0), (0.3, 0.0), (1.0, 0.08)]).discretize(256))
+    cam, total, img = vr.Camera(), 0, None
+    for _ in range(frames):
+        op.set_camera(cam)
+        op.record()
+        img = op.download()
+        total += int(img.astype(np.int64).sum())
+        cam.rotate((4.0, 0.0))
+    op.close()
+    assert got_sum == total
+    ppm = open(out, "rb").read()
+    assert ppm.startswith(b"P6\n160 120\n255\n")
+    body = np.frombuffer(ppm[len(b"P6\n160 120\n255\n"):], np.uint8).reshape(H, W, 3)
+    assert np.array_equal(body, img[..., :3])

@@ -206,3 +206,19 @@ def test_partition_order_is_a_valid_front_to_back_order(vr):
                         visited.append(b)
                 ranks = [rank_of[b] for b in visited]
                 assert ranks == sorted(ranks), (grid, cam, visited, order)
+
+
+# ---- C++ host side over the ABI -------------------------------------------------------------------
+
+def test_cpp_mirror_builds_and_fails_loudly_without_a_device(vr):
+    """host/offscreen_pass.hpp (the C++ mirror of the reference's classes) compiles against include/vr.h
+    and links to the library; without a GPU the pass constructor throws like the reference would."""
+    import subprocess
+    import torch
+    pkg = os.path.join(ROOT, "volumetric-renderer_b200")
+    subprocess.run(["make", "-s", "-C", pkg, os.path.join(pkg, "host", "example_orbit")], check=True)
+    exe = os.path.join(pkg, "host", "example_orbit")
+    assert os.path.exists(exe)
+    if not torch.cuda.is_available():
+        r = subprocess.run([exe, "/tmp/_vr_none.ppm", "32", "32", "8", "1"], capture_output=True, text=True)
+        assert r.returncode == 1 and "no CPU fallback" in r.stderr
