@@ -127,7 +127,9 @@ __device__ __forceinline__ bool cell_occupied(const MarchParams &p, const uint32
     cy = min(max(cy, 0), p.occ_n[1] - 1);
     cz = min(max(cz, 0), p.occ_n[2] - 1);
     const int bit = (cz * p.occ_n[1] + cy) * p.occ_n[0] + cx;
-    return (sOcc[bit >> 5] >> (bit & 31)) & 1u;
+    /* fine bits stay in global memory (32 KiB, L1-resident): staging them per CTA would cost
+     * occupancy; shared memory holds the two coarse levels only */
+    return (__ldg(p.occ + (bit >> 5)) >> (bit & 31)) & 1u;
 }
 
 /* Per-thread state of one ray. */
@@ -139,6 +141,8 @@ struct Ray {
     bool done;             /* no more positions to generate */
     bool stop;             /* early termination: composite nothing more */
     uint32_t nb, ns, nf;   /* counters (STATS) */
+    float ifx, ify, ifz;   /* ESS: 1 / (d * occ_scale): steps per fine cell, per axis */
+    bool in_empty;         /* ESS: the last step generated fell into an empty fine cell */
 };
 
 /* The positions volume.frag:47 accumulates are monotone on every axis, and differ from
@@ -169,17 +173,77 @@ __device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r
     }
 }
 
+/* Hierarchical empty-space skipping.  Two coarse levels over the fine occupancy bits (4^3 and 16^3
+ * fine cells per coarse cell, bit = OR).  If the coarse cell holding the current position is empty,
+ * the ray advances to where it leaves that cell with nothing but the position additions of
+ * volume.frag:47 (so positions stay bit-identical): every skipped position lies strictly inside
+ * the empty cell, i.e. is one the fine test would have rejected anyway -- results are unchanged. */
+template <bool STATS, bool PART>
+__device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, const uint32_t *sOcc)
+{
+#pragma unroll 1
+    for (int guard = 0; guard < 4 && !r.done && r.in_empty; guard++) {
+        /* position in fine-cell units */
+        const float fx = PART ? r.px * p.occ_scale[0] - p.occ_off[0] : r.px * p.occ_scale[0];
+        const float fy = PART ? r.py * p.occ_scale[1] - p.occ_off[1] : r.py * p.occ_scale[1];
+        const float fz = PART ? r.pz * p.occ_scale[2] - p.occ_off[2] : r.pz * p.occ_scale[2];
+        if (!(fx >= 0.0f && fy >= 0.0f && fz >= 0.0f && fx < p.occ_f_hi[0] && fy < p.occ_f_hi[1] && fz < p.occ_f_hi[2])) return;
+        const int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+        int shift = 4;
+        int bit = ((iz >> 4) * p.occ_n2[1] + (iy >> 4)) * p.occ_n2[0] + (ix >> 4);
+        bool occupied = (sOcc[(p.occ_l2_off - p.occ_l1_off) + (bit >> 5)] >> (bit & 31)) & 1u;
+        if (occupied) {
+            shift = 2;
+            bit = ((iz >> 2) * p.occ_n1[1] + (iy >> 2)) * p.occ_n1[0] + (ix >> 2);
+            occupied = (sOcc[bit >> 5] >> (bit & 31)) & 1u;
+            if (occupied) return;
+        }
+        /* steps until the ray leaves the cell shrunk by a margin that covers the accumulated
+         * rounding of the positions (<= steps * ulp, far below 2e-3 fine cells) */
+        const float size = (float)(1 << shift), m = 2.0e-3f;
+        const float f[3] = {fx, fy, fz}, inv[3] = {r.ifx, r.ify, r.ifz};
+        const int c[3] = {ix >> shift, iy >> shift, iz >> shift};
+        float t = 1.0e9f;
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            const float lo = (float)c[a] * size + m;
+            const float hi = fminf((float)(c[a] + 1) * size, p.occ_f_hi[a]) - m;
+            /* inv > 0: moving up, leaves through hi; inv < 0: leaves through lo; inv = 0 (d = 0): never */
+            const float ta = inv[a] > 0.0f ? (hi - f[a]) * inv[a] : (inv[a] < 0.0f ? (lo - f[a]) * inv[a] : 1.0e9f);
+            t = fminf(t, ta);
+        }
+        int k = (t >= 1.0f) ? (int)t : 0; /* positions 0..k-1 are inside */
+        k = min(k, p.steps - r.i);
+        if (k <= 0) return;
+        r.i += k;
+        if (STATS) r.nb += (uint32_t)k;
+#pragma unroll 1
+        for (int j = 0; j < k; j++) {
+            if (STATS) {
+                bool s = r.px < p.max_slice[0] && r.py < p.max_slice[1] && r.pz < p.max_slice[2] && r.px > p.min_slice[0] &&
+                         r.py > p.min_slice[1] && r.pz > p.min_slice[2];
+                if (PART)
+                    s = s && r.px >= p.own_lo[0] && r.py >= p.own_lo[1] && r.pz >= p.own_lo[2] && r.px < p.own_hi[0] &&
+                        r.py < p.own_hi[1] && r.pz < p.own_hi[2];
+                r.ns += s;
+            }
+            r.px += r.dx, r.py += r.dy, r.pz += r.dz;
+        }
+    }
+}
+
 /* One batch of U consecutive iterations of volume.frag:33-48, split in two halves so that the
  * fetches of the next batch can be in flight while this one is composited. */
 template <int U>
 struct Batch {
     float val[U];
     bool ok[U];
+    bool pred; /* warp-uniform: ok[] is meaningful (otherwise every lane samples every step) */
 };
 
 /* First half: positions (volume.frag:33-40,:47), then all U fetches back to back (:41).
  * CHECK = evaluate the per-step tests; otherwise every step of a live ray is sampled. */
-template <bool EXACT, bool ESS, bool STATS, bool PART, int U, bool CHECK>
+template <bool EXACT, bool ESS, bool STATS, bool PART, int U, bool CHECK, bool PRED>
 __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<U> &b, const uint32_t *sOcc)
 {
     float qx[U], qy[U], qz[U];
@@ -202,14 +266,18 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
                 r.ns += s;
             }
         } else {
-            s = !r.done;
+            s = PRED ? !r.done : true;
             if (STATS) {
                 r.nb += s;
                 r.ns += s;
             }
         }
-        if (ESS) s = s && cell_occupied<PART>(p, sOcc, r.px, r.py, r.pz);
-        b.ok[u] = s;
+        if (ESS) {
+            const bool occ = !s || cell_occupied<PART>(p, sOcc, r.px, r.py, r.pz);
+            r.in_empty = !occ;
+            s = s && occ;
+        }
+        if (CHECK || PRED) b.ok[u] = s;
         qx[u] = r.px, qy[u] = r.py, qz[u] = r.pz;
         /* volume.frag:47 */
         r.px += r.dx, r.py += r.dy, r.pz += r.dz;
@@ -217,8 +285,8 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
     }
 #pragma unroll
     for (int u = 0; u < U; u++) {
-        b.val[u] = 0.0f;
-        if (b.ok[u]) {
+        if (CHECK || PRED) b.val[u] = 0.0f;
+        if ((CHECK || PRED) ? b.ok[u] : true) {
             if (EXACT) {
                 b.val[u] = sample_exact(p, qx[u], qy[u], qz[u]);
             } else if (PART) {
@@ -230,17 +298,18 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
             }
         }
     }
+    b.pred = CHECK || PRED;
 }
 
 /* Second half: normalise, transfer function, composite (volume.frag:42-45). */
-template <bool EXACT, bool STATS, int U>
+template <bool EXACT, bool STATS, int U, bool PRED>
 __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batch<U> &b, const float4 *sP,
                                               const float4 *sD)
 {
     const float lut_hi = (float)p.nlut;
 #pragma unroll
     for (int u = 0; u < U; u++) {
-        if (b.ok[u] && !r.stop) {
+        if (!PRED || (b.ok[u] && !r.stop)) {
             if (STATS) r.nf++;
             float sr, sg, sb, sa;
             if (EXACT) {
@@ -349,7 +418,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     if (!EXACT)
         for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) sD[i] = p.lut_dif[i];
     if (ESS)
-        for (int i = threadIdx.x; i < p.occ_words; i += nthreads) sOcc[i] = p.occ[i];
+        for (int i = threadIdx.x; i < p.occ_words - p.occ_l1_off; i += nthreads) sOcc[i] = p.occ[p.occ_l1_off + i];
     __syncthreads();
 
     /* volume.frag:22-24 */
@@ -368,24 +437,38 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     Ray ray;
     ray.cr = cr, ray.cg = cg, ray.cb = cb, ray.T = T;
     ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
-    ray.i = 0, ray.done = !covered, ray.stop = false, ray.nb = 0, ray.ns = 0, ray.nf = 0;
+    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
     /* Steps fast_lo..fast_hi need no bounds / slice / ownership test (see safe_interval). */
     int fast_lo = 0x7fffffff, fast_hi = -1;
     if (covered && !EXACT) safe_interval(p, ray, fast_lo, fast_hi);
 
     constexpr int U = EXACT ? 1 : UB;
-    /* warp-uniform choice per batch: the checked form is always correct, the unchecked one only
-     * where every live lane is inside its safe interval */
+    if (ESS) {
+        const float sx_ = ray.dx * p.occ_scale[0], sy_ = ray.dy * p.occ_scale[1], sz_ = ray.dz * p.occ_scale[2];
+        ray.ifx = sx_ != 0.0f ? __frcp_rn(sx_) : 0.0f;
+        ray.ify = sy_ != 0.0f ? __frcp_rn(sy_) : 0.0f;
+        ray.ifz = sz_ != 0.0f ? __frcp_rn(sz_) : 0.0f;
+    }
+    /* Warp-uniform choice per batch.  Checked: every test of volume.frag:34-40 is evaluated (always
+     * correct).  Unchecked: every live lane is inside its safe interval; predicated if some lane is
+     * finished or the occupancy grid is consulted, else no per-lane flag at all. */
 #define VR_ISSUE(B_)                                                                                        \
     do {                                                                                                    \
-        const bool can_fast = ray.done || (ray.i >= fast_lo && ray.i + U - 1 <= fast_hi);                   \
-        if (!EXACT && __all_sync(0xffffffffu, can_fast))                                                    \
-            batch_issue<EXACT, ESS, STATS, PART, U, false>(p, ray, B_, sOcc);                               \
+        if (ESS && !EXACT) skip_empty<STATS, PART>(p, ray, sOcc);                                           \
+        const bool in_safe = ray.i >= fast_lo && ray.i + U - 1 <= fast_hi;                                  \
+        if (!EXACT && !ESS && __all_sync(0xffffffffu, !ray.done && in_safe))                                \
+            batch_issue<EXACT, ESS, STATS, PART, U, false, false>(p, ray, B_, sOcc);                        \
+        else if (!EXACT && __all_sync(0xffffffffu, ray.done || in_safe))                                    \
+            batch_issue<EXACT, ESS, STATS, PART, U, false, true>(p, ray, B_, sOcc);                         \
         else                                                                                                \
-            batch_issue<EXACT, ESS, STATS, PART, U, true>(p, ray, B_, sOcc);                                \
+            batch_issue<EXACT, ESS, STATS, PART, U, true, true>(p, ray, B_, sOcc);                          \
     } while (0)
-#define VR_CONSUME(B_) batch_consume<EXACT, STATS, U>(p, ray, B_, sP, sD)
+#define VR_CONSUME(B_)                                                                                      \
+    do {                                                                                                    \
+        if (B_.pred) batch_consume<EXACT, STATS, U, true>(p, ray, B_, sP, sD);                              \
+        else batch_consume<EXACT, STATS, U, false>(p, ray, B_, sP, sD);                                     \
+    } while (0)
     if (EXACT) {
         Batch<U> a;
         while (!ray.done) {
@@ -496,7 +579,7 @@ cudaError_t launch_hw(const MarchParams &p, bool stats, bool part, int ub, size_
 
 size_t vr_march_smem_bytes(const MarchParams &p, bool ess)
 {
-    return sizeof(float4) * (size_t)(2 * p.nlut + 5) + (ess ? sizeof(uint32_t) * (size_t)p.occ_words : 0);
+    return sizeof(float4) * (size_t)(2 * p.nlut + 5) + (ess ? sizeof(uint32_t) * (size_t)(p.occ_words - p.occ_l1_off) : 0);
 }
 
 cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, int threads,

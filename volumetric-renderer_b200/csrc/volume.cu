@@ -155,6 +155,29 @@ __global__ void __launch_bounds__(256) k_classify(const float2 *__restrict__ ran
     }
 }
 
+/* coarse level: bit = OR of the 4x4x4 finer bits below it (finer cells outside the grid count as empty) */
+__global__ void __launch_bounds__(256) k_coarsen(uint32_t *occ, int fnx, int fny, int fnz, int fine_off, int cnx, int cny,
+                                                 int cnz, int coarse_off)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ncoarse = cnx * cny * cnz;
+    bool any = false;
+    if (c < ncoarse) {
+        const int cx = c % cnx, cy = (c / cnx) % cny, cz = c / (cnx * cny);
+        for (int dz = 0; dz < 4 && !any; dz++)
+            for (int dy = 0; dy < 4 && !any; dy++)
+                for (int dx = 0; dx < 4; dx++) {
+                    const int x = cx * 4 + dx, y = cy * 4 + dy, z = cz * 4 + dz;
+                    if (x < fnx && y < fny && z < fnz) {
+                        const int b = (z * fny + y) * fnx + x;
+                        any = any || ((occ[fine_off + (b >> 5)] >> (b & 31)) & 1u);
+                    }
+                }
+    }
+    const uint32_t word = __ballot_sync(0xffffffffu, any);
+    if ((threadIdx.x & 31) == 0 && (c >> 5) < (ncoarse + 31) / 32) occ[coarse_off + (c >> 5)] = word;
+}
+
 /* ------------------------------------------------------------------ synth -- */
 
 __device__ __forceinline__ uint32_t hash_u32(uint32_t h)
@@ -325,6 +348,15 @@ cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const flo
     const int threads = occ_words * 32;
     k_classify<<<(threads + 255) / 256, 256, 0, s>>>(d_ranges, ncells, d_lut_pad, (int)nlut, min_density, max_density,
                                                      d_occ, d_empty_count);
+    return cudaGetLastError();
+}
+
+cudaError_t vr_k0_coarsen(uint32_t *d_occ, const int fine_n[3], int fine_off, const int coarse_n[3], int coarse_off,
+                          int coarse_words, cudaStream_t s)
+{
+    const int threads = coarse_words * 32;
+    k_coarsen<<<(threads + 255) / 256, 256, 0, s>>>(d_occ, fine_n[0], fine_n[1], fine_n[2], fine_off, coarse_n[0], coarse_n[1],
+                                                    coarse_n[2], coarse_off);
     return cudaGetLastError();
 }
 
