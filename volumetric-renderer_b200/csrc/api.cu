@@ -142,6 +142,8 @@ void release_volume(vr_ctx *c)
     if (c->array) cudaFreeArray(c->array), c->array = nullptr;
     if (c->d_cell_range) cudaFree(c->d_cell_range), c->d_cell_range = nullptr;
     if (c->d_occ) cudaFree(c->d_occ), c->d_occ = nullptr;
+    if (c->d_dist) cudaFree(c->d_dist), c->d_dist = nullptr;
+    if (c->d_dist_tmp) cudaFree(c->d_dist_tmp), c->d_dist_tmp = nullptr;
 }
 
 int alloc_target(vr_ctx *c, uint32_t w, uint32_t h)
@@ -213,13 +215,11 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
     c->occ_n[0] = (int)((nx + cell - 1) / cell), c->occ_n[1] = (int)((ny + cell - 1) / cell),
     c->occ_n[2] = (int)((nz + cell - 1) / cell);
     const int ncells = c->occ_n[0] * c->occ_n[1] * c->occ_n[2];
-    c->occ_fine_words = (ncells + 31) / 32;
-    for (int i = 0; i < 3; i++) c->occ_n1[i] = (c->occ_n[i] + 3) / 4, c->occ_n2[i] = (c->occ_n1[i] + 3) / 4;
-    const int w1 = (c->occ_n1[0] * c->occ_n1[1] * c->occ_n1[2] + 31) / 32, w2 = (c->occ_n2[0] * c->occ_n2[1] * c->occ_n2[2] + 31) / 32;
-    c->occ_l1_off = c->occ_fine_words, c->occ_l2_off = c->occ_fine_words + w1;
-    c->occ_words = c->occ_fine_words + w1 + w2;
+    c->occ_words = (ncells + 31) / 32;
     VR_CUDA(c, cudaMalloc(&c->d_cell_range, sizeof(float2) * ncells));
     VR_CUDA(c, cudaMalloc(&c->d_occ, sizeof(uint32_t) * c->occ_words));
+    VR_CUDA(c, cudaMalloc(&c->d_dist, (size_t)ncells));
+    VR_CUDA(c, cudaMalloc(&c->d_dist_tmp, (size_t)ncells));
     VR_CUDA(c, vr_k0_cell_ranges(dev, dtype, nx, ny, nz, cell, c->occ_n, c->d_cell_range, c->stream));
     c->occ_dirty = true;
     VR_CUDA(c, cudaStreamSynchronize(c->stream)); /* the reference's upload is synchronous too */
@@ -477,9 +477,8 @@ int prepare_occupancy(vr_ctx *c, cudaStream_t s)
 {
     if (!c->occ_dirty) return VR_OK;
     VR_CUDA(c, vr_k0_classify(c->d_cell_range, c->occ_n, c->d_lut_pad, c->nlut, c->min_density, c->max_density, c->d_occ,
-                              c->occ_fine_words, c->d_counters + 4, s));
-    VR_CUDA(c, vr_k0_coarsen(c->d_occ, c->occ_n, 0, c->occ_n1, c->occ_l1_off, c->occ_l2_off - c->occ_l1_off, s));
-    VR_CUDA(c, vr_k0_coarsen(c->d_occ, c->occ_n1, c->occ_l1_off, c->occ_n2, c->occ_l2_off, c->occ_words - c->occ_l2_off, s));
+                              c->occ_words, c->d_counters + 4, s));
+    VR_CUDA(c, vr_k0_distance(c->d_occ, c->occ_n, c->d_dist, c->d_dist_tmp, s));
     VR_CUDA(c, cudaMemcpyAsync(&c->h_counters[4], c->d_counters + 4, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     VR_CUDA(c, cudaStreamSynchronize(s));
     c->occ_empty_cells = c->h_counters[4];
@@ -545,7 +544,6 @@ void fill_params(const vr_ctx *c, MarchParams &p)
         if (!(c->min_slice[i] == c->min_slice[i]) || !(c->max_slice[i] == c->max_slice[i]))
             p.box_lo[i] = inf, p.box_hi[i] = -inf; /* NaN slice bound: every strict test fails */
         p.occ_n[i] = c->occ_n[i];
-        p.occ_n1[i] = c->occ_n1[i], p.occ_n2[i] = c->occ_n2[i];
         p.occ_f_hi[i] = (float)ldims[i] / (float)c->occ_cell;
         p.occ_scale[i] = (float)full / (float)c->occ_cell;
         p.occ_off[i] = (float)p.org[i] / (float)c->occ_cell;
@@ -557,7 +555,7 @@ void fill_params(const vr_ctx *c, MarchParams &p)
     p.lutA = (float)((double)p.dscale * n / range);
     p.lutB = (float)(0.5 - (double)c->min_density * n / range);
     p.occ = c->d_occ, p.occ_words = c->occ_words;
-    p.occ_l1_off = c->occ_l1_off, p.occ_l2_off = c->occ_l2_off;
+    p.dist = c->d_dist;
     p.out = c->d_image;
     p.raw = c->opt.write_raw ? c->d_raw : nullptr;
     p.counters = c->d_counters;

@@ -115,21 +115,20 @@ __device__ __forceinline__ float sample_exact(const MarchParams &p, float s, flo
     return lerp1(lerp1(x00, x10, b), lerp1(x01, x11, b), c);
 }
 
-/* Is the occupancy bit of the cell holding this position set? */
+/* Chebyshev distance (in cells, capped) from the cell holding this position to the nearest cell
+ * that may contribute: 0 = sample here; d >= 1 = every cell within d-1 cells is empty.
+ * A one-ulp slip across a cell face is harmless: every cell's range includes a 1-voxel apron. */
 template <bool PART>
-__device__ __forceinline__ bool cell_occupied(const MarchParams &p, const uint32_t *sOcc, float x, float y, float z)
+__device__ __forceinline__ int cell_distance(const MarchParams &p, float x, float y, float z)
 {
-    /* a one-ulp slip across a cell face is harmless: every cell's range includes a 1-voxel apron */
     int cx = PART ? (int)(x * p.occ_scale[0] - p.occ_off[0]) : (int)(x * p.occ_scale[0]);
     int cy = PART ? (int)(y * p.occ_scale[1] - p.occ_off[1]) : (int)(y * p.occ_scale[1]);
     int cz = PART ? (int)(z * p.occ_scale[2] - p.occ_off[2]) : (int)(z * p.occ_scale[2]);
     cx = min(max(cx, 0), p.occ_n[0] - 1);
     cy = min(max(cy, 0), p.occ_n[1] - 1);
     cz = min(max(cz, 0), p.occ_n[2] - 1);
-    const int bit = (cz * p.occ_n[1] + cy) * p.occ_n[0] + cx;
-    /* fine bits stay in global memory (32 KiB, L1-resident): staging them per CTA would cost
-     * occupancy; shared memory holds the two coarse levels only */
-    return (__ldg(p.occ + (bit >> 5)) >> (bit & 31)) & 1u;
+    /* 256 KiB at most, read through L1 (no shared-memory staging: it would cost occupancy) */
+    return (int)__ldg(p.dist + ((cz * p.occ_n[1] + cy) * p.occ_n[0] + cx));
 }
 
 /* Per-thread state of one ray. */
@@ -173,46 +172,42 @@ __device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r
     }
 }
 
-/* Hierarchical empty-space skipping.  Two coarse levels over the fine occupancy bits (4^3 and 16^3
- * fine cells per coarse cell, bit = OR).  If the coarse cell holding the current position is empty,
- * the ray advances to where it leaves that cell with nothing but the position additions of
- * volume.frag:47 (so positions stay bit-identical): every skipped position lies strictly inside
- * the empty cell, i.e. is one the fine test would have rejected anyway -- results are unchanged. */
+/* Empty-space skipping by distance map.  If the cell holding the current position is empty with
+ * distance d, the cube of 2d-1 cells around it is empty: the ray advances to where it leaves that
+ * cube with nothing but the position additions of volume.frag:47 (positions stay bit-identical).
+ * Every skipped position lies strictly inside the cube, i.e. is one the per-step test would have
+ * rejected anyway -- results are unchanged. */
 template <bool STATS, bool PART>
-__device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, const uint32_t *sOcc)
+__device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r)
 {
 #pragma unroll 1
-    for (int guard = 0; guard < 4 && !r.done && r.in_empty; guard++) {
-        /* position in fine-cell units */
+    for (int guard = 0; guard < 8 && !r.done && r.in_empty; guard++) {
+        /* position in cell units */
         const float fx = PART ? r.px * p.occ_scale[0] - p.occ_off[0] : r.px * p.occ_scale[0];
         const float fy = PART ? r.py * p.occ_scale[1] - p.occ_off[1] : r.py * p.occ_scale[1];
         const float fz = PART ? r.pz * p.occ_scale[2] - p.occ_off[2] : r.pz * p.occ_scale[2];
         if (!(fx >= 0.0f && fy >= 0.0f && fz >= 0.0f && fx < p.occ_f_hi[0] && fy < p.occ_f_hi[1] && fz < p.occ_f_hi[2])) return;
-        const int ix = (int)fx, iy = (int)fy, iz = (int)fz;
-        int shift = 4;
-        int bit = ((iz >> 4) * p.occ_n2[1] + (iy >> 4)) * p.occ_n2[0] + (ix >> 4);
-        bool occupied = (sOcc[(p.occ_l2_off - p.occ_l1_off) + (bit >> 5)] >> (bit & 31)) & 1u;
-        if (occupied) {
-            shift = 2;
-            bit = ((iz >> 2) * p.occ_n1[1] + (iy >> 2)) * p.occ_n1[0] + (ix >> 2);
-            occupied = (sOcc[bit >> 5] >> (bit & 31)) & 1u;
-            if (occupied) return;
+        const int c[3] = {(int)fx, (int)fy, (int)fz};
+        const int d = (int)__ldg(p.dist + ((c[2] * p.occ_n[1] + c[1]) * p.occ_n[0] + c[0]));
+        if (d == 0) {
+            r.in_empty = false;
+            return;
         }
-        /* steps until the ray leaves the cell shrunk by a margin that covers the accumulated
-         * rounding of the positions (<= steps * ulp, far below 2e-3 fine cells) */
-        const float size = (float)(1 << shift), m = 2.0e-3f;
+        /* steps until the ray leaves the cube, shrunk by a margin that covers the accumulated
+         * rounding of the positions (<= steps * ulp, far below 2e-3 cells) */
+        const float m = 2.0e-3f, rad = (float)(d - 1);
         const float f[3] = {fx, fy, fz}, inv[3] = {r.ifx, r.ify, r.ifz};
-        const int c[3] = {ix >> shift, iy >> shift, iz >> shift};
         float t = 1.0e9f;
 #pragma unroll
         for (int a = 0; a < 3; a++) {
-            const float lo = (float)c[a] * size + m;
-            const float hi = fminf((float)(c[a] + 1) * size, p.occ_f_hi[a]) - m;
+            const float lo = fmaxf((float)c[a] - rad, 0.0f) + m;
+            const float hi = fminf((float)(c[a] + 1) + rad, p.occ_f_hi[a]) - m;
             /* inv > 0: moving up, leaves through hi; inv < 0: leaves through lo; inv = 0 (d = 0): never */
             const float ta = inv[a] > 0.0f ? (hi - f[a]) * inv[a] : (inv[a] < 0.0f ? (lo - f[a]) * inv[a] : 1.0e9f);
             t = fminf(t, ta);
         }
-        int k = (t >= 1.0f) ? (int)t : 0; /* positions 0..k-1 are inside */
+        /* positions 0..k-1 are inside the cube; position 0 is the current one, known to be empty */
+        int k = (t >= 1.0f) ? (int)fminf(t, 65536.0f) : 1;
         k = min(k, p.steps - r.i);
         if (k <= 0) return;
         r.i += k;
@@ -244,7 +239,7 @@ struct Batch {
 /* First half: positions (volume.frag:33-40,:47), then all U fetches back to back (:41).
  * CHECK = evaluate the per-step tests; otherwise every step of a live ray is sampled. */
 template <bool EXACT, bool ESS, bool STATS, bool PART, int U, bool CHECK, bool PRED>
-__device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<U> &b, const uint32_t *sOcc)
+__device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<U> &b)
 {
     float qx[U], qy[U], qz[U];
 #pragma unroll
@@ -273,7 +268,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
             }
         }
         if (ESS) {
-            const bool occ = !s || cell_occupied<PART>(p, sOcc, r.px, r.py, r.pz);
+            const bool occ = !s || cell_distance<PART>(p, r.px, r.py, r.pz) == 0;
             r.in_empty = !occ;
             s = s && occ;
         }
@@ -358,7 +353,6 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     extern __shared__ float4 smem[];
     float4 *sP = smem;              /* nlut + 3 */
     float4 *sD = sP + (p.nlut + 3); /* nlut + 2 */
-    uint32_t *sOcc = reinterpret_cast<uint32_t *>(sD + (p.nlut + 2));
 
     /* Which tile.  The first sp_count blocks walk the tiles of the cube's screen bounding box in a
      * square spiral from its centre: the longest rays (through the middle of the cube) start
@@ -417,8 +411,6 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     for (uint32_t i = threadIdx.x; i < p.nlut + 3; i += nthreads) sP[i] = p.lut_pad[i];
     if (!EXACT)
         for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) sD[i] = p.lut_dif[i];
-    if (ESS)
-        for (int i = threadIdx.x; i < p.occ_words - p.occ_l1_off; i += nthreads) sOcc[i] = p.occ[p.occ_l1_off + i];
     __syncthreads();
 
     /* volume.frag:22-24 */
@@ -455,14 +447,14 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
      * finished or the occupancy grid is consulted, else no per-lane flag at all. */
 #define VR_ISSUE(B_)                                                                                        \
     do {                                                                                                    \
-        if (ESS && !EXACT) skip_empty<STATS, PART>(p, ray, sOcc);                                           \
+        if (ESS && !EXACT) skip_empty<STATS, PART>(p, ray);                                           \
         const bool in_safe = ray.i >= fast_lo && ray.i + U - 1 <= fast_hi;                                  \
         if (!EXACT && !ESS && __all_sync(0xffffffffu, !ray.done && in_safe))                                \
-            batch_issue<EXACT, ESS, STATS, PART, U, false, false>(p, ray, B_, sOcc);                        \
+            batch_issue<EXACT, ESS, STATS, PART, U, false, false>(p, ray, B_);                        \
         else if (!EXACT && __all_sync(0xffffffffu, ray.done || in_safe))                                    \
-            batch_issue<EXACT, ESS, STATS, PART, U, false, true>(p, ray, B_, sOcc);                         \
+            batch_issue<EXACT, ESS, STATS, PART, U, false, true>(p, ray, B_);                         \
         else                                                                                                \
-            batch_issue<EXACT, ESS, STATS, PART, U, true, true>(p, ray, B_, sOcc);                          \
+            batch_issue<EXACT, ESS, STATS, PART, U, true, true>(p, ray, B_);                          \
     } while (0)
 #define VR_CONSUME(B_)                                                                                      \
     do {                                                                                                    \
@@ -579,7 +571,8 @@ cudaError_t launch_hw(const MarchParams &p, bool stats, bool part, int ub, size_
 
 size_t vr_march_smem_bytes(const MarchParams &p, bool ess)
 {
-    return sizeof(float4) * (size_t)(2 * p.nlut + 5) + (ess ? sizeof(uint32_t) * (size_t)(p.occ_words - p.occ_l1_off) : 0);
+    (void)ess; /* the distance map is read from global memory */
+    return sizeof(float4) * (size_t)(2 * p.nlut + 5);
 }
 
 cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, int threads,

@@ -155,27 +155,28 @@ __global__ void __launch_bounds__(256) k_classify(const float2 *__restrict__ ran
     }
 }
 
-/* coarse level: bit = OR of the 4x4x4 finer bits below it (finer cells outside the grid count as empty) */
-__global__ void __launch_bounds__(256) k_coarsen(uint32_t *occ, int fnx, int fny, int fnz, int fine_off, int cnx, int cny,
-                                                 int cnz, int coarse_off)
+/* Chebyshev distance transform of the occupancy bits, one separable pass per axis:
+ * pass 0 reads the bits (0 where occupied, else "far"), each pass replaces D by
+ * min over the line of max(|i - i'|, D(i')).  After the three passes D = number of cells to the
+ * nearest occupied cell in the max-norm, capped at VR_DIST_CAP. */
+#define VR_DIST_CAP 64
+__global__ void __launch_bounds__(256) k_chebyshev_pass(const uint32_t *__restrict__ occ, const unsigned char *__restrict__ in,
+                                                        unsigned char *__restrict__ out, int nx, int ny, int nz, int axis)
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    const int ncoarse = cnx * cny * cnz;
-    bool any = false;
-    if (c < ncoarse) {
-        const int cx = c % cnx, cy = (c / cnx) % cny, cz = c / (cnx * cny);
-        for (int dz = 0; dz < 4 && !any; dz++)
-            for (int dy = 0; dy < 4 && !any; dy++)
-                for (int dx = 0; dx < 4; dx++) {
-                    const int x = cx * 4 + dx, y = cy * 4 + dy, z = cz * 4 + dz;
-                    if (x < fnx && y < fny && z < fnz) {
-                        const int b = (z * fny + y) * fnx + x;
-                        any = any || ((occ[fine_off + (b >> 5)] >> (b & 31)) & 1u);
-                    }
-                }
+    if (c >= nx * ny * nz) return;
+    const int x = c % nx, y = (c / nx) % ny, z = c / (nx * ny);
+    const int n = axis == 0 ? nx : (axis == 1 ? ny : nz);
+    const int stride = axis == 0 ? 1 : (axis == 1 ? nx : nx * ny);
+    const int i0 = axis == 0 ? x : (axis == 1 ? y : z);
+    const int base = c - i0 * stride;
+    int best = VR_DIST_CAP;
+    for (int i = max(0, i0 - VR_DIST_CAP); i < min(n, i0 + VR_DIST_CAP + 1); i++) {
+        const int q = base + i * stride;
+        const int dq = in ? (int)in[q] : (((occ[q >> 5] >> (q & 31)) & 1u) ? 0 : VR_DIST_CAP);
+        best = min(best, max(abs(i - i0), dq));
     }
-    const uint32_t word = __ballot_sync(0xffffffffu, any);
-    if ((threadIdx.x & 31) == 0 && (c >> 5) < (ncoarse + 31) / 32) occ[coarse_off + (c >> 5)] = word;
+    out[c] = (unsigned char)best;
 }
 
 /* ------------------------------------------------------------------ synth -- */
@@ -351,12 +352,13 @@ cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const flo
     return cudaGetLastError();
 }
 
-cudaError_t vr_k0_coarsen(uint32_t *d_occ, const int fine_n[3], int fine_off, const int coarse_n[3], int coarse_off,
-                          int coarse_words, cudaStream_t s)
+cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, unsigned char *d_tmp,
+                           cudaStream_t s)
 {
-    const int threads = coarse_words * 32;
-    k_coarsen<<<(threads + 255) / 256, 256, 0, s>>>(d_occ, fine_n[0], fine_n[1], fine_n[2], fine_off, coarse_n[0], coarse_n[1],
-                                                    coarse_n[2], coarse_off);
+    const int n = occ_n[0] * occ_n[1] * occ_n[2], blocks = (n + 255) / 256;
+    k_chebyshev_pass<<<blocks, 256, 0, s>>>(d_occ, nullptr, d_dist, occ_n[0], occ_n[1], occ_n[2], 0);
+    k_chebyshev_pass<<<blocks, 256, 0, s>>>(d_occ, d_dist, d_tmp, occ_n[0], occ_n[1], occ_n[2], 1);
+    k_chebyshev_pass<<<blocks, 256, 0, s>>>(d_occ, d_tmp, d_dist, occ_n[0], occ_n[1], occ_n[2], 2);
     return cudaGetLastError();
 }
 

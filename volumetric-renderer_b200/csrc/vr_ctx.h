@@ -52,8 +52,7 @@ struct MarchParams {
     int occ_n[3];
     int occ_words;
     float occ_scale[3], occ_off[3]; /* cell = int(pos * occ_scale - occ_off) */
-    /* coarse levels (4^3 and 16^3 fine cells per bit) stored after the fine bits */
-    int occ_n1[3], occ_n2[3], occ_l1_off, occ_l2_off;
+    const unsigned char *dist; /* per cell: Chebyshev distance (cells) to the nearest occupied cell, 0 = occupied */
     float occ_f_hi[3]; /* extent of the volume in fine-cell units (local texture) */
     /* outputs */
     uchar4 *out;
@@ -117,8 +116,8 @@ struct vr_ctx {
     int occ_cell = 0; /* voxels per cell edge (power of two) */
     float2 *d_cell_range = nullptr; /* per cell (min,max) incl. 1-voxel apron and border zeros */
     uint32_t *d_occ = nullptr;
-    int occ_words = 0; /* fine + coarse levels */
-    int occ_fine_words = 0, occ_n1[3] = {0, 0, 0}, occ_n2[3] = {0, 0, 0}, occ_l1_off = 0, occ_l2_off = 0;
+    int occ_words = 0;
+    unsigned char *d_dist = nullptr, *d_dist_tmp = nullptr;
     bool occ_dirty = true;
     uint64_t occ_empty_cells = 0;
 
@@ -141,8 +140,8 @@ cudaError_t vr_k0_cell_ranges(const void *dev, int dtype, uint32_t nx, uint32_t 
 cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const float4 *d_lut_pad, uint32_t nlut,
                            float min_density, float max_density, uint32_t *d_occ, int occ_words,
                            unsigned long long *d_empty_count, cudaStream_t s);
-cudaError_t vr_k0_coarsen(uint32_t *d_occ, const int fine_n[3], int fine_off, const int coarse_n[3], int coarse_off,
-                          int coarse_words, cudaStream_t s);
+cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, unsigned char *d_tmp,
+                           cudaStream_t s);
 cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
                         const int org[3], const uint32_t full[3], cudaStream_t s);
 
