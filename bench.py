@@ -134,6 +134,7 @@ def run_ours(args):
     K, Wu = args.steps, args.warmup
 
     op = vr.OffscreenPass(W, H, device=local)
+    op.set_volume_layout({"auto": vr.LAYOUT_AUTO, "3d": vr.LAYOUT_ARRAY3D, "paired": vr.LAYOUT_PAIRED}[args.layout])
     op.synth_volume(kind, {"c1": 0x5EED0001, "c2": 0x5EED0002, "c3": 0x5EED0003}[args.workload], dtype, n)
     lut = product_lut(vr, tfn)
     op.transfer_function_changed(lut)
@@ -240,7 +241,8 @@ def run_ours(args):
         occ_frac = (ncell - empty) / ncell if prod["empty_skip"] else 1.0
         alg_bytes = n ** 3 * esz * occ_frac + W * H * 4 + 1024   # touched bricks once + RGBA8 out + LUT
         step_s = dev_ms * 1e-3 / K                                # one launch per step
-        tex_peak = vr.bench_tex_peak(local, dtype, True)
+        paired = op.volume_layout() == vr.LAYOUT_PAIRED and not args.exact
+        tex_peak = vr.bench_tex_peak(local, dtype, 2 if paired else 1)
         exec_rate = (total_exec / K) / step_s
         line = {
             "metric": "ray samples/s @1920x1080, 512^3 u16" if args.workload == "c2" else f"ray samples/s ({args.workload})",
@@ -252,6 +254,7 @@ def run_ours(args):
                        "empty_space_skipping": bool(prod["empty_skip"]), "early_ray_termination_eps": prod["early_term_eps"] if prod["early_term"] else 0,
                        "l2": f"inputs larger than L2 ({n ** 3 * esz / 2 ** 20:.0f} MiB volume, no flush)",
                        "frames_in_flight": F,
+                       "layout": "paired z-slices, 2-D layered array (+ the 3-D array kept for the exact sampler)" if paired else "3-D array",
                        "parallelism": f"frames of the orbit dealt round-robin to {world} GPU(s), no collective"},
             "executed_samples_per_s": all_exec / (dev_ms * 1e-3),
             "roofline": {"bound": "hbm", "achieved": alg_bytes / step_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
@@ -260,7 +263,7 @@ def run_ours(args):
                          "algorithmic_bytes_per_launch": alg_bytes},
             "roofline_tex": {"bound": "tex", "achieved": exec_rate / 1e9, "peak": tex_peak / 1e9, "unit": "Gfetch/s",
                              "frac": exec_rate / tex_peak,
-                             "peak_source": "vr_bench_tex_peak: L1-resident 3-D trilinear fetches, measured in this run"},
+                             "peak_source": "vr_bench_tex_peak: L1-resident " + ("paired-layout bilinear fetches (2-D layered, two z-slices per texel)" if paired else "3-D trilinear fetches") + ", measured in this run"},
             "e2e": {"value": all_ref / (e2e_ms * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": 192,
                     "d2h_bytes_per_step": W * H * 4, "ms_per_step": e2e_ms / K, "fps": world * K / (e2e_ms * 1e-3),
                     "frame_checksum": checksum},
@@ -503,7 +506,8 @@ def main():
     ap.add_argument("--no-ess", action="store_true")
     ap.add_argument("--no-ert", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--in-flight", type=int, default=2, help="frames in flight (streams), 1..4")
+    ap.add_argument("--in-flight", type=int, default=3, help="frames in flight (streams), 1..4")
+    ap.add_argument("--layout", choices=["auto", "3d", "paired"], default="auto", help="volume layout (vr_set_volume_layout)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.workload in ("c4", "c5"):

@@ -55,6 +55,16 @@ typedef enum vr_sampler {
                              bit-exact with the CPU oracle; the verification mode */
 } vr_sampler;
 
+/* How the volume is laid out in HBM for the hardware sampler.  The reference has one layout
+ * (an optimal-tiling VK_IMAGE_TYPE_3D image, offscreen_pass.cpp:943-989); here the loader may add a
+ * second one.  Results of VR_SAMPLER_EXACT do not depend on it. */
+typedef enum vr_layout {
+    VR_LAYOUT_AUTO = 0,    /* PAIRED when the volume qualifies (u8/u16, nz <= 2047, within the memory budget) */
+    VR_LAYOUT_ARRAY3D = 1, /* 3-D block-linear array, hardware trilinear fetch (half texture rate) */
+    VR_LAYOUT_PAIRED = 2   /* + a 2-D layered array whose texel l holds (v[z=l-1], v[z=l]): one full-rate
+                              bilinear fetch returns both z-slices, the z-lerp is one fp32 FMA */
+} vr_layout;
+
 typedef struct vr_ctx vr_ctx;
 
 typedef struct vr_options {
@@ -148,6 +158,12 @@ int vr_set_transfer_function(vr_ctx *ctx, const uint32_t *rgba8_srgb, uint32_t n
 /* The two shader literals ray_dist = 1.8, step_size = 0.005 (res/shaders/volume.frag:29-30)
  * as parameters; steps = int(ray_dist / step_size) in fp32 (:31). */
 int vr_set_march(vr_ctx *ctx, float ray_dist, float step_size);
+
+/* Layout used by the NEXT volume upload (vr_set_volume*, vr_load_nrrd, vr_synth_*); default AUTO.
+ * VR_LAYOUT_PAIRED on a volume that does not qualify makes that upload fail with VR_ERR_INVALID. */
+int vr_set_volume_layout(vr_ctx *ctx, int layout);
+/* Layout of the current volume: VR_LAYOUT_ARRAY3D or VR_LAYOUT_PAIRED. */
+int vr_get_volume_layout(const vr_ctx *ctx, int *layout);
 
 int vr_get_options(const vr_ctx *ctx, vr_options *out);
 int vr_set_options(vr_ctx *ctx, const vr_options *opt);
@@ -255,8 +271,9 @@ int vr_partition_order(const uint32_t grid[3], const uint32_t full_dims[3], cons
 
 /* ---- measurement ----------------------------------------------------------------------- */
 
-/* Texture-fetch roofline micro-benchmark: trilinear tex3D fetches of an L1-resident
- * volume of `dtype` from all SMs; returns fetches per second (device-timed). */
+/* Texture-fetch roofline micro-benchmark: filtered fetches of an L1-resident volume of `dtype` from all
+ * SMs; returns fetches per second (device-timed).  hw_filter: 0 = point tex3D, 1 = trilinear tex3D
+ * (VR_LAYOUT_ARRAY3D's fetch), 2 = bilinear fetch of the paired layered array (VR_LAYOUT_PAIRED's fetch). */
 int vr_bench_tex_peak(int device, int dtype, int hw_filter, double *fetches_per_s);
 /* Test hook: the 16 floats (4 columns) of inverse(proj * view) the kernel uses. */
 int vr_debug_ray_context(const vr_ctx *ctx, float out[16]);

@@ -22,8 +22,8 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _lib
-from ._lib import (F32, U8, U16, SAMPLER_EXACT, SAMPLER_HW, SYNTH_BLOBS, SYNTH_FBM, SYNTH_MARSCHNER_LOBB,
-                   Options, Stats)
+from ._lib import (F32, U8, U16, LAYOUT_ARRAY3D, LAYOUT_AUTO, LAYOUT_PAIRED, SAMPLER_EXACT, SAMPLER_HW, SYNTH_BLOBS,
+                   SYNTH_FBM, SYNTH_MARSCHNER_LOBB, Options, Stats)
 
 lib = _lib.load()
 
@@ -177,6 +177,15 @@ class OffscreenPass:
         nx, ny, nz = (n, n, n) if isinstance(n, int) else n
         self._check(lib.vr_synth_volume(self._h, kind, seed & 0xFFFFFFFF, dtype, nx, ny, nz))
 
+    def set_volume_layout(self, layout: int):
+        """Layout of the NEXT volume upload: LAYOUT_AUTO / LAYOUT_ARRAY3D / LAYOUT_PAIRED."""
+        self._check(lib.vr_set_volume_layout(self._h, int(layout)))
+
+    def volume_layout(self) -> int:
+        v = C.c_int(0)
+        self._check(lib.vr_get_volume_layout(self._h, C.byref(v)))
+        return v.value
+
     def set_march(self, ray_dist: float, step_size: float):
         self._check(lib.vr_set_march(self._h, ray_dist, step_size))
 
@@ -326,7 +335,8 @@ def partition_order(grid, full_dims, camera_position) -> np.ndarray:
     return out
 
 
-def bench_tex_peak(device: int, dtype: int, hw_filter: bool = True) -> float:
+def bench_tex_peak(device: int, dtype: int, hw_filter=True) -> float:
+    """hw_filter: 0 point, 1 trilinear tex3D (LAYOUT_ARRAY3D's fetch), 2 paired bilinear (LAYOUT_PAIRED's fetch)."""
     r = C.c_double()
     rc = lib.vr_bench_tex_peak(device, dtype, int(hw_filter), C.byref(r))
     if rc != _lib.VR_OK:

@@ -15,6 +15,7 @@ VR_OK = 0
 U8, U16, F32 = 0, 1, 2
 SAMPLER_HW, SAMPLER_EXACT = 0, 1
 SYNTH_MARSCHNER_LOBB, SYNTH_FBM, SYNTH_BLOBS = 0, 1, 2
+LAYOUT_AUTO, LAYOUT_ARRAY3D, LAYOUT_PAIRED = 0, 1, 2
 
 
 class Options(C.Structure):
@@ -53,6 +54,8 @@ SIGNATURES = {
     "vr_set_slicing": (C.c_int, [_P, _P, _P]),
     "vr_set_transfer_function": (C.c_int, [_P, _P, C.c_uint32]),
     "vr_set_march": (C.c_int, [_P, C.c_float, C.c_float]),
+    "vr_set_volume_layout": (C.c_int, [_P, C.c_int]),
+    "vr_get_volume_layout": (C.c_int, [_P, C.POINTER(C.c_int)]),
     "vr_get_options": (C.c_int, [_P, C.POINTER(Options)]),
     "vr_set_options": (C.c_int, [_P, C.POINTER(Options)]),
     "vr_get_image": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_size_t)]),

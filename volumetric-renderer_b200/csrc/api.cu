@@ -8,6 +8,7 @@
  * objects, the decoded LUT, the occupancy grid, and one stream.  Every mutator keeps the
  * reference's semantics (synchronous, copy-in), every failure becomes a status + message.
  */
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -125,8 +126,24 @@ int upload_lut(vr_ctx *c)
     }
     for (uint32_t k = 0; k < n + 2; k++)
         D[k] = make_float4(P[k + 1].x - P[k].x, P[k + 1].y - P[k].y, P[k + 1].z - P[k].z, P[k + 1].w - P[k].w);
+    /* hardware-sampler table: one 16-byte entry {P[k] + D[k]/2, D[k]} of eight fp16 -> one LDS.128 per sample (march.cu: lut_eval) */
+    std::vector<uint4> Hh(n + 2);
+    for (uint32_t k = 0; k < n + 2; k++) {
+        const float e[8] = {P[k].x + 0.5f * D[k].x, P[k].y + 0.5f * D[k].y, P[k].z + 0.5f * D[k].z, P[k].w + 0.5f * D[k].w,
+                            D[k].x, D[k].y, D[k].z, D[k].w};
+        unsigned short hb[8];
+        for (int j = 0; j < 8; j++) {
+            const __half hv = __float2half_rn(e[j]);
+            std::memcpy(&hb[j], &hv, 2);
+        }
+        Hh[k] = make_uint4(hb[0] | ((uint32_t)hb[1] << 16), hb[2] | ((uint32_t)hb[3] << 16), hb[4] | ((uint32_t)hb[5] << 16),
+                           hb[6] | ((uint32_t)hb[7] << 16));
+    }
     if (c->d_lut_pad) cudaFree(c->d_lut_pad), c->d_lut_pad = nullptr;
     if (c->d_lut_dif) cudaFree(c->d_lut_dif), c->d_lut_dif = nullptr;
+    if (c->d_lut_h) cudaFree(c->d_lut_h), c->d_lut_h = nullptr;
+    VR_CUDA(c, cudaMalloc(&c->d_lut_h, sizeof(uint4) * (n + 2)));
+    VR_CUDA(c, cudaMemcpy(c->d_lut_h, Hh.data(), sizeof(uint4) * (n + 2), cudaMemcpyHostToDevice));
     VR_CUDA(c, cudaMalloc(&c->d_lut_pad, sizeof(float4) * (n + 3)));
     VR_CUDA(c, cudaMalloc(&c->d_lut_dif, sizeof(float4) * (n + 2)));
     VR_CUDA(c, cudaMemcpy(c->d_lut_pad, P.data(), sizeof(float4) * (n + 3), cudaMemcpyHostToDevice));
@@ -139,6 +156,8 @@ void release_volume(vr_ctx *c)
 {
     if (c->tex_lin) cudaDestroyTextureObject(c->tex_lin), c->tex_lin = 0;
     if (c->tex_pt) cudaDestroyTextureObject(c->tex_pt), c->tex_pt = 0;
+    if (c->tex_pair) cudaDestroyTextureObject(c->tex_pair), c->tex_pair = 0;
+    if (c->pair_array) cudaFreeArray(c->pair_array), c->pair_array = nullptr;
     if (c->array) cudaFreeArray(c->array), c->array = nullptr;
     if (c->d_cell_range) cudaFree(c->d_cell_range), c->d_cell_range = nullptr;
     if (c->d_occ) cudaFree(c->d_occ), c->d_occ = nullptr;
@@ -196,6 +215,27 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
     tp.normalizedCoords = 0;
     VR_CUDA(c, cudaCreateTextureObject(&c->tex_pt, &rd, &tp, nullptr));
 
+    /* second layout for the hardware sampler (vr_layout): z-pairs in a 2-D layered array */
+    const bool can_pair = (dtype == VR_U8 || dtype == VR_U16) && nz + 1 <= 2048 && nx <= 32768 && ny <= 32768;
+    const size_t pair_bytes = (size_t)nx * ny * ((size_t)nz + 1) * 2 * dtype_size(dtype);
+    if (c->layout_req == VR_LAYOUT_PAIRED && !can_pair)
+        return fail(c, VR_ERR_INVALID, "VR_LAYOUT_PAIRED needs a u8/u16 volume with nz <= 2047 and nx, ny <= 32768");
+    if (c->layout_req == VR_LAYOUT_PAIRED || (c->layout_req == VR_LAYOUT_AUTO && can_pair && pair_bytes <= c->tune_pair_max_bytes)) {
+        cudaChannelFormatDesc cd2 = dtype == VR_U8 ? cudaCreateChannelDesc<uchar2>() : cudaCreateChannelDesc<ushort2>();
+        VR_CUDA(c, cudaMalloc3DArray(&c->pair_array, &cd2, make_cudaExtent(nx, ny, (size_t)nz + 1),
+                                     cudaArrayLayered | cudaArraySurfaceLoadStore));
+        VR_CUDA(c, vr_k0_pack_pairs(dev, dtype, nx, ny, nz, c->pair_array, c->stream));
+        cudaResourceDesc rp = {};
+        rp.resType = cudaResourceTypeArray;
+        rp.res.array.array = c->pair_array;
+        cudaTextureDesc tq = {};
+        tq.addressMode[0] = tq.addressMode[1] = tq.addressMode[2] = cudaAddressModeBorder;
+        tq.filterMode = cudaFilterModeLinear;
+        tq.readMode = cudaReadModeNormalizedFloat;
+        tq.normalizedCoords = 1;
+        VR_CUDA(c, cudaCreateTextureObject(&c->tex_pair, &rp, &tq, nullptr));
+    }
+
     /* ubo.min_density / max_density = dataset.min / max (offscreen_pass.cpp:265-266) */
     if (mn && mx) {
         c->min_density = *mn, c->max_density = *mx;
@@ -233,7 +273,10 @@ int default_state(vr_ctx *c)
     VR_CUDA(c, cudaMalloc(&d0, sizeof(float)));
     VR_CUDA(c, cudaMemset(d0, 0, sizeof(float)));
     const float zero = 0.0f;
+    const int want = c->layout_req; /* the start-up volume is f32: never paired */
+    c->layout_req = VR_LAYOUT_AUTO;
     int rc = install_volume(c, d0, VR_F32, 1, 1, 1, &zero, &zero);
+    c->layout_req = want;
     cudaFree(d0);
     if (rc != VR_OK) return rc;
     c->nlut = 1;
@@ -288,6 +331,8 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
         if (w == 4 || w == 8 || w == 16) c->tune_warp_w = w;
     }
     if (const char *e = std::getenv("VR_CARVEOUT")) c->tune_carveout = std::atoi(e);
+    if (const char *e = std::getenv("VR_LAYOUT")) c->layout_req = std::atoi(e) == 1 ? VR_LAYOUT_ARRAY3D : (std::atoi(e) == 2 ? VR_LAYOUT_PAIRED : VR_LAYOUT_AUTO);
+    if (const char *e = std::getenv("VR_PAIR_MAX_MB")) c->tune_pair_max_bytes = (size_t)std::atoll(e) << 20;
     if (const char *e = std::getenv("VR_L2_GRAN")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(e));
     int rc = VR_OK;
     do {
@@ -317,6 +362,7 @@ extern "C" int vr_destroy(vr_ctx *c)
     release_volume(c);
     if (c->d_lut_pad) cudaFree(c->d_lut_pad);
     if (c->d_lut_dif) cudaFree(c->d_lut_dif);
+    if (c->d_lut_h) cudaFree(c->d_lut_h);
     if (c->d_image) cudaFree(c->d_image);
     if (c->d_raw) cudaFree(c->d_raw);
     for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
@@ -447,6 +493,20 @@ extern "C" int vr_set_march(vr_ctx *c, float ray_dist, float step_size)
     return VR_OK;
 }
 
+extern "C" int vr_set_volume_layout(vr_ctx *c, int layout)
+{
+    if (!c || layout < VR_LAYOUT_AUTO || layout > VR_LAYOUT_PAIRED) return fail(c, VR_ERR_INVALID, "vr_set_volume_layout: bad layout");
+    c->layout_req = layout;
+    return VR_OK;
+}
+
+extern "C" int vr_get_volume_layout(const vr_ctx *c, int *layout)
+{
+    if (!c || !layout) return VR_ERR_INVALID;
+    *layout = c->tex_pair ? VR_LAYOUT_PAIRED : VR_LAYOUT_ARRAY3D;
+    return VR_OK;
+}
+
 extern "C" int vr_get_options(const vr_ctx *c, vr_options *out)
 {
     if (!c || !out) return VR_ERR_INVALID;
@@ -550,10 +610,19 @@ void fill_params(const vr_ctx *c, MarchParams &p)
     }
     p.dtype = c->dtype;
     p.dscale = c->dtype == VR_U8 ? 255.0f : (c->dtype == VR_U16 ? 65535.0f : 1.0f);
-    p.lut_pad = c->d_lut_pad, p.lut_dif = c->d_lut_dif, p.nlut = c->nlut;
+    p.lut_pad = c->d_lut_pad, p.lut_dif = c->d_lut_dif, p.lut_h = c->d_lut_h, p.nlut = c->nlut;
+    p.tex_pair = c->tex_pair;
+    for (int i = 0; i < 2; i++) {
+        p.pair_a[i] = p.dims[i] * p.inv_ldims[i];
+        p.pair_b[i] = -p.forg[i] * p.inv_ldims[i];
+    }
+    p.pair_a[2] = p.dims[2];
+    p.pair_b[2] = 12582912.0f - p.forg[2]; /* 1.5 * 2^23: the FMA rounds the local z texel coordinate to an integer = floor(w) + 1 */
+    p.pair_zc = 0.5f - p.forg[2];          /* w - floor(w) = q_z * dims_z + (pair_zc - (floor(w) + 1)) */
     const double range = (double)p.range, n = (double)c->nlut;
     p.lutA = (float)((double)p.dscale * n / range);
     p.lutB = (float)(0.5 - (double)c->min_density * n / range);
+    p.lutBh = (float)(0.0 - (double)c->min_density * n / range);
     p.occ = c->d_occ, p.occ_words = c->occ_words;
     p.dist = c->d_dist;
     p.out = c->d_image;
@@ -619,7 +688,8 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     p.out = target;
     if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
-    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, c->tune_batch, c->tune_threads, s));
+    const bool pair = !exact && c->tex_pair != 0;
+    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, pair, c->tune_batch, c->tune_threads, s));
     if (c->opt.collect_stats)
         VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     return VR_OK;

@@ -19,6 +19,7 @@
  * bit-identical to the CPU oracle.  Fused multiply-adds are written explicitly (fmaf) where
  * the hardware-sampler path is allowed to differ in rounding.
  */
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
@@ -131,6 +132,46 @@ __device__ __forceinline__ int cell_distance(const MarchParams &p, float x, floa
     return (int)__ldg(p.dist + ((cz * p.occ_n[1] + cy) * p.occ_n[0] + cx));
 }
 
+#define VR_MAGIC 12582912.0f /* 1.5 * 2^23: x + VR_MAGIC rounds x to an integer held in the low mantissa bits */
+#define VR_MAGIC_BITS 0x4B400000u
+
+/* Paired layout, one sample: the layer holding (v[fl], v[fl+1]) with fl = floor(w), w = z texel coordinate
+ * - 0.5, is fl + 1 = round(w + 0.5), read from the mantissa of q_z * a + b (b carries 1.5*2^23; at a tie
+ * either neighbour gives the same value because the z weight is then 0 or 1).  Returns the pair, and the
+ * z weight w - fl evaluated with a single rounding. */
+template <bool PART>
+__device__ __forceinline__ float2 fetch_pair(const MarchParams &p, float qx, float qy, float qz, float &frac)
+{
+    const float tm = fmaf(qz, p.pair_a[2], p.pair_b[2]);
+    const float fl1 = tm - VR_MAGIC;                        /* fl + 1 */
+    const int layer = (int)(__float_as_uint(tm) & 0xffffu); /* 0 .. nz (nz <= 2047) */
+    frac = fmaf(qz, p.pair_a[2], p.pair_zc - fl1);
+    return PART ? tex2DLayered<float2>(p.tex_pair, fmaf(qx, p.pair_a[0], p.pair_b[0]), fmaf(qy, p.pair_a[1], p.pair_b[1]), layer)
+                : tex2DLayered<float2>(p.tex_pair, qx, qy, layer);
+}
+
+/* Hardware-sampler transfer function.  Table entry k (shared memory, 16 bytes = eight fp16) holds
+ * M[k] = P[k] + D[k]/2 and D[k] = P[k+1] - P[k] of the edge-padded LUT, so with k = round(u - 1/2) and
+ * wm = u - 1/2 - k in [-1/2, 1/2] the CLAMP_TO_EDGE / LINEAR result is M[k] + wm * D[k]: one LDS.128 and
+ * two HFMA2, no float<->int conversion (k comes from the mantissa of u - 1/2 + 1.5*2^23). */
+struct LutH {
+    uint32_t base; /* shared-window address of entry 0, minus (VR_MAGIC_BITS << 4) */
+    float A, Bh, hi;
+};
+__device__ __forceinline__ void lut_eval(const LutH &L, float dens, float &sr, float &sg, float &sb, float &sa)
+{
+    float uh = fmaf(dens, L.A, L.Bh); /* padded LUT coordinate - 1/2 */
+    uh = fminf(fmaxf(uh, -0.5f), L.hi);
+    const float tk = uh + VR_MAGIC;
+    const float wm = uh - (tk - VR_MAGIC);
+    uint4 e;
+    asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(e.x), "=r"(e.y), "=r"(e.z), "=r"(e.w) : "r"((__float_as_uint(tk) << 4) + L.base));
+    const __half2 w2 = __float2half2_rn(wm);
+    const float2 rg = __half22float2(__hfma2(w2, *reinterpret_cast<const __half2 *>(&e.z), *reinterpret_cast<const __half2 *>(&e.x)));
+    const float2 ba = __half22float2(__hfma2(w2, *reinterpret_cast<const __half2 *>(&e.w), *reinterpret_cast<const __half2 *>(&e.y)));
+    sr = rg.x, sg = rg.y, sb = ba.x, sa = ba.y;
+}
+
 /* Per-thread state of one ray. */
 struct Ray {
     float cr, cg, cb, T;   /* volume.frag:22 color (T = color.a = transmittance) */
@@ -232,13 +273,14 @@ __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r)
 template <int U>
 struct Batch {
     float val[U];
+    float val2[U], frac[U]; /* paired layout: second slice of the pair and the z weight */
     bool ok[U];
     bool pred; /* warp-uniform: ok[] is meaningful (otherwise every lane samples every step) */
 };
 
 /* First half: positions (volume.frag:33-40,:47), then all U fetches back to back (:41).
  * CHECK = evaluate the per-step tests; otherwise every step of a live ray is sampled. */
-template <bool EXACT, bool ESS, bool STATS, bool PART, int U, bool CHECK, bool PRED>
+template <bool EXACT, bool ESS, bool STATS, bool PART, bool PAIR, int U, bool CHECK, bool PRED>
 __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<U> &b)
 {
     float qx[U], qy[U], qz[U];
@@ -263,8 +305,8 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
         } else {
             s = PRED ? !r.done : true;
             if (STATS) {
-                r.nb += s;
-                r.ns += s;
+                r.nb += !r.done;
+                r.ns += !r.done;
             }
         }
         if (ESS) {
@@ -281,9 +323,13 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
 #pragma unroll
     for (int u = 0; u < U; u++) {
         if (CHECK || PRED) b.val[u] = 0.0f;
+        if (PAIR && (CHECK || PRED)) b.val2[u] = 0.0f, b.frac[u] = 0.0f;
         if ((CHECK || PRED) ? b.ok[u] : true) {
             if (EXACT) {
                 b.val[u] = sample_exact(p, qx[u], qy[u], qz[u]);
+            } else if (PAIR) {
+                const float2 t = fetch_pair<PART>(p, qx[u], qy[u], qz[u], b.frac[u]);
+                b.val[u] = t.x, b.val2[u] = t.y;
             } else if (PART) {
                 b.val[u] = tex3D<float>(p.tex_lin, (qx[u] * p.dims[0] - p.forg[0]) * p.inv_ldims[0],
                                         (qy[u] * p.dims[1] - p.forg[1]) * p.inv_ldims[1],
@@ -297,15 +343,15 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
 }
 
 /* Second half: normalise, transfer function, composite (volume.frag:42-45). */
-template <bool EXACT, bool STATS, int U, bool PRED>
+template <bool EXACT, bool STATS, bool PAIR, int U, bool PRED>
 __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batch<U> &b, const float4 *sP,
-                                              const float4 *sD)
+                                              const LutH &L)
 {
     const float lut_hi = (float)p.nlut;
 #pragma unroll
     for (int u = 0; u < U; u++) {
         if (!PRED || (b.ok[u] && !r.stop)) {
-            if (STATS) r.nf++;
+            if (STATS) r.nf += PRED ? 1u : (r.done ? 0u : 1u);
             float sr, sg, sb, sa;
             if (EXACT) {
                 /* volume.frag:42-43 and the LINEAR / CLAMP_TO_EDGE 1-D sampler */
@@ -326,12 +372,8 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
                 /* early ray termination: what is left contributes < eps per channel */
                 if (r.T < p.ert_eps) r.stop = true, r.done = true;
             } else {
-                float uu = fmaf(b.val[u], p.lutA, p.lutB); /* padded LUT coordinate, u + 1 */
-                uu = fminf(fmaxf(uu, 0.0f), lut_hi + 1.0f);
-                const int k = (int)uu;
-                const float w = uu - (float)k;
-                const float4 a = sP[k], d = sD[k];
-                sr = fmaf(w, d.x, a.x), sg = fmaf(w, d.y, a.y), sb = fmaf(w, d.z, a.z), sa = fmaf(w, d.w, a.w);
+                const float dens = PAIR ? fmaf(b.frac[u], b.val2[u] - b.val[u], b.val[u]) : b.val[u];
+                lut_eval(L, dens, sr, sg, sb, sa);
                 const float ta = r.T * sa;
                 r.cr = fmaf(ta, sr, r.cr);
                 r.cg = fmaf(ta, sg, r.cg);
@@ -347,12 +389,12 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
 
 /* EXACT: verification sampler.  ESS: occupancy grid consulted.  STATS: sample counters.
  * PART: sort-last sub-volume.  UB: steps per batch (HW sampler; two batches are in flight). */
-template <bool EXACT, bool ESS, bool STATS, bool PART, int UB>
+template <bool EXACT, bool ESS, bool STATS, bool PART, bool PAIR, int UB>
 __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant__ MarchParams p)
 {
     extern __shared__ float4 smem[];
-    float4 *sP = smem;              /* nlut + 3 */
-    float4 *sD = sP + (p.nlut + 3); /* nlut + 2 */
+    float4 *sP = smem;                              /* EXACT: nlut + 3 decoded texels */
+    uint4 *sH = reinterpret_cast<uint4 *>(smem);    /* HW: nlut + 2 packed fp16 entries */
 
     /* Which tile.  The first sp_count blocks walk the tiles of the cube's screen bounding box in a
      * square spiral from its centre: the longest rays (through the middle of the cube) start
@@ -408,9 +450,10 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         return;
     }
 
-    for (uint32_t i = threadIdx.x; i < p.nlut + 3; i += nthreads) sP[i] = p.lut_pad[i];
-    if (!EXACT)
-        for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) sD[i] = p.lut_dif[i];
+    if (EXACT)
+        for (uint32_t i = threadIdx.x; i < p.nlut + 3; i += nthreads) sP[i] = p.lut_pad[i];
+    else
+        for (uint32_t i = threadIdx.x; i < p.nlut + 2; i += nthreads) sH[i] = p.lut_h[i];
     __syncthreads();
 
     /* volume.frag:22-24 */
@@ -431,11 +474,16 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
     ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
+    bool parked = false; /* fast phase: this lane only keeps its warp company */
+    float t_saved = 1.0f;
     /* Steps fast_lo..fast_hi need no bounds / slice / ownership test (see safe_interval). */
     int fast_lo = 0x7fffffff, fast_hi = -1;
     if (covered && !EXACT) safe_interval(p, ray, fast_lo, fast_hi);
 
     constexpr int U = EXACT ? 1 : UB;
+    LutH L;
+    L.base = (uint32_t)__cvta_generic_to_shared(sH) - (VR_MAGIC_BITS << 4);
+    L.A = p.lutA, L.Bh = p.lutBh, L.hi = (float)p.nlut + 0.5f;
     if (ESS) {
         const float sx_ = ray.dx * p.occ_scale[0], sy_ = ray.dy * p.occ_scale[1], sz_ = ray.dz * p.occ_scale[2];
         ray.ifx = sx_ != 0.0f ? __frcp_rn(sx_) : 0.0f;
@@ -450,22 +498,59 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         if (ESS && !EXACT) skip_empty<STATS, PART>(p, ray);                                           \
         const bool in_safe = ray.i >= fast_lo && ray.i + U - 1 <= fast_hi;                                  \
         if (!EXACT && !ESS && __all_sync(0xffffffffu, !ray.done && in_safe))                                \
-            batch_issue<EXACT, ESS, STATS, PART, U, false, false>(p, ray, B_);                        \
+            batch_issue<EXACT, ESS, STATS, PART, PAIR, U, false, false>(p, ray, B_);                        \
         else if (!EXACT && __all_sync(0xffffffffu, ray.done || in_safe))                                    \
-            batch_issue<EXACT, ESS, STATS, PART, U, false, true>(p, ray, B_);                         \
+            batch_issue<EXACT, ESS, STATS, PART, PAIR, U, false, true>(p, ray, B_);                         \
         else                                                                                                \
-            batch_issue<EXACT, ESS, STATS, PART, U, true, true>(p, ray, B_);                          \
+            batch_issue<EXACT, ESS, STATS, PART, PAIR, U, true, true>(p, ray, B_);                          \
     } while (0)
 #define VR_CONSUME(B_)                                                                                      \
     do {                                                                                                    \
-        if (B_.pred) batch_consume<EXACT, STATS, U, true>(p, ray, B_, sP, sD);                              \
-        else batch_consume<EXACT, STATS, U, false>(p, ray, B_, sP, sD);                                     \
+        if (B_.pred) batch_consume<EXACT, STATS, PAIR, U, true>(p, ray, B_, sP, L);                         \
+        else batch_consume<EXACT, STATS, PAIR, U, false>(p, ray, B_, sP, L);                                \
     } while (0)
     if (EXACT) {
         Batch<U> a;
         while (!ray.done) {
             VR_ISSUE(a);
             VR_CONSUME(a);
+        }
+    } else if (!ESS) {
+        /* Fast phase.  While every lane of the warp is inside its safe interval (or has nothing left to
+         * do), the warp runs `nb` double-batches with no test, no predicate and no vote except the
+         * early-termination one.  Lanes that are finished (or never had a fragment) are parked: their
+         * transmittance is saved and set to 0, so the unpredicated compositing adds exactly 0 to their
+         * colour, and they step in place at the volume centre.  A lane that drops below the early-
+         * termination threshold inside the phase keeps compositing real samples until the phase ends:
+         * its result only gets closer to the unterminated one, the error bound is unchanged. */
+        Batch<U> a, b;
+        while (true) {
+            const int room = ray.done ? 0x7fffffff : (ray.i >= fast_lo ? fast_hi - ray.i + 1 : 0);
+            const int nmin = __reduce_min_sync(0xffffffffu, room);
+            if (nmin == 0x7fffffff) break; /* every lane is done */
+            const int nb = (nmin / U - 1) / 2;
+            if (nb >= 1) {
+                if (ray.done && !parked) {
+                    parked = true, t_saved = ray.T, ray.T = 0.0f;
+                    ray.px = ray.py = ray.pz = 0.5f, ray.dx = ray.dy = ray.dz = 0.0f;
+                }
+                batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, a);
+#pragma unroll 1
+                for (int it = 0; it < nb; it++) {
+                    batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, b);
+                    batch_consume<false, STATS, PAIR, U, false>(p, ray, a, sP, L);
+                    batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, a);
+                    batch_consume<false, STATS, PAIR, U, false>(p, ray, b, sP, L);
+                    if (__all_sync(0xffffffffu, ray.done)) break;
+                }
+                batch_consume<false, STATS, PAIR, U, false>(p, ray, a, sP, L);
+                continue;
+            }
+            /* head / tail: one double-batch with the tests the lanes need */
+            VR_ISSUE(a);
+            VR_ISSUE(b);
+            VR_CONSUME(a);
+            VR_CONSUME(b);
         }
     } else {
         /* two batches in rotation: the fetches of one are in flight while the other is composited */
@@ -488,7 +573,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     }
 #undef VR_ISSUE
 #undef VR_CONSUME
-    cr = ray.cr, cg = ray.cg, cb = ray.cb, T = ray.T;
+    cr = ray.cr, cg = ray.cg, cb = ray.cb, T = parked ? t_saved : ray.T;
     uint32_t nb = ray.nb, ns = ray.ns, nf = ray.nf;
 
     if (valid) {
@@ -533,10 +618,10 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     }
 }
 
-template <bool EXACT, bool ESS, bool STATS, bool PART, int UB>
+template <bool EXACT, bool ESS, bool STATS, bool PART, bool PAIR, int UB>
 cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, int threads, cudaStream_t s)
 {
-    auto kern = k_march<EXACT, ESS, STATS, PART, UB>;
+    auto kern = k_march<EXACT, ESS, STATS, PART, PAIR, UB>;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -546,46 +631,48 @@ cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, int threads, cu
     return cudaGetLastError();
 }
 
-template <bool EXACT, bool ESS, int UB>
+template <bool EXACT, bool ESS, bool PAIR, int UB>
 cudaError_t launch2(const MarchParams &p, bool stats, bool part, size_t smem, dim3 grid, int threads, cudaStream_t s)
 {
     if (stats)
-        return part ? launch<EXACT, ESS, true, true, UB>(p, smem, grid, threads, s)
-                    : launch<EXACT, ESS, true, false, UB>(p, smem, grid, threads, s);
-    return part ? launch<EXACT, ESS, false, true, UB>(p, smem, grid, threads, s)
-                : launch<EXACT, ESS, false, false, UB>(p, smem, grid, threads, s);
+        return part ? launch<EXACT, ESS, true, true, PAIR, UB>(p, smem, grid, threads, s)
+                    : launch<EXACT, ESS, true, false, PAIR, UB>(p, smem, grid, threads, s);
+    return part ? launch<EXACT, ESS, false, true, PAIR, UB>(p, smem, grid, threads, s)
+                : launch<EXACT, ESS, false, false, PAIR, UB>(p, smem, grid, threads, s);
 }
 
-template <bool ESS>
+template <bool ESS, bool PAIR>
 cudaError_t launch_hw(const MarchParams &p, bool stats, bool part, int ub, size_t smem, dim3 grid, int threads,
                       cudaStream_t s)
 {
     switch (ub) {
-        case 4: return launch2<false, ESS, 4>(p, stats, part, smem, grid, threads, s);
-        case 8: return launch2<false, ESS, 8>(p, stats, part, smem, grid, threads, s);
-        default: return launch2<false, ESS, 2>(p, stats, part, smem, grid, threads, s);
+        case 4: return launch2<false, ESS, PAIR, 4>(p, stats, part, smem, grid, threads, s);
+        default: return launch2<false, ESS, PAIR, 2>(p, stats, part, smem, grid, threads, s);
     }
 }
 
 }  // namespace
 
-size_t vr_march_smem_bytes(const MarchParams &p, bool ess)
+size_t vr_march_smem_bytes(const MarchParams &p, bool exact)
 {
-    (void)ess; /* the distance map is read from global memory */
-    return sizeof(float4) * (size_t)(2 * p.nlut + 5);
+    /* EXACT: nlut + 3 float4 texels; HW: nlut + 2 packed fp16 entries.  The distance map is read from global memory. */
+    return exact ? sizeof(float4) * (size_t)(p.nlut + 3) : sizeof(uint4) * (size_t)(p.nlut + 2);
 }
 
-cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, int threads,
-                            cudaStream_t s)
+cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, bool pair, int ub,
+                            int threads, cudaStream_t s)
 {
     const uint64_t ctas = (uint64_t)p.sp_count + (uint64_t)p.ntx * p.nty;
     if (ctas == 0) return cudaSuccess;
     if (ctas > 0x7fffffffull) return cudaErrorInvalidConfiguration;
-    const size_t smem = vr_march_smem_bytes(p, ess);
+    const size_t smem = vr_march_smem_bytes(p, exact);
     const dim3 grid((unsigned)ctas);
     if (exact)
-        return ess ? launch2<true, true, 1>(p, stats, part, smem, grid, threads, s)
-                   : launch2<true, false, 1>(p, stats, part, smem, grid, threads, s);
-    return ess ? launch_hw<true>(p, stats, part, ub, smem, grid, threads, s)
-               : launch_hw<false>(p, stats, part, ub, smem, grid, threads, s);
+        return ess ? launch2<true, true, false, 1>(p, stats, part, smem, grid, threads, s)
+                   : launch2<true, false, false, 1>(p, stats, part, smem, grid, threads, s);
+    if (pair)
+        return ess ? launch_hw<true, true>(p, stats, part, ub, smem, grid, threads, s)
+                   : launch_hw<false, true>(p, stats, part, ub, smem, grid, threads, s);
+    return ess ? launch_hw<true, false>(p, stats, part, ub, smem, grid, threads, s)
+               : launch_hw<false, false>(p, stats, part, ub, smem, grid, threads, s);
 }

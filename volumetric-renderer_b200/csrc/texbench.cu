@@ -15,6 +15,7 @@
 
 namespace
 {
+template <bool PAIR>
 __global__ void __launch_bounds__(256) k_texbench(cudaTextureObject_t tex, int iters, float step, float *sink)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -27,7 +28,14 @@ __global__ void __launch_bounds__(256) k_texbench(cudaTextureObject_t tex, int i
     for (int i = 0; i < iters; i++) {
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            acc[k] += tex3D<float>(tex, x, y, z);
+            if (PAIR) {
+                /* the paired layout's fetch: one bilinear fetch of a two-channel layered texel + the z-lerp */
+                const float w = z * 31.0f, fl = floorf(w);
+                const float2 t = tex2DLayered<float2>(tex, x, y, (int)fl);
+                acc[k] += fmaf(w - fl, t.y - t.x, t.x);
+            } else {
+                acc[k] += tex3D<float>(tex, x, y, z);
+            }
             z += step;
             if (z > 1.0f) z -= 1.0f;
         }
@@ -41,13 +49,15 @@ __global__ void __launch_bounds__(256) k_texbench(cudaTextureObject_t tex, int i
 
 extern "C" int vr_bench_tex_peak(int device, int dtype, int hw_filter, double *fetches_per_s)
 {
-    if (!fetches_per_s || dtype < VR_U8 || dtype > VR_F32) return VR_ERR_INVALID;
+    if (!fetches_per_s || dtype < VR_U8 || dtype > VR_F32 || hw_filter < 0 || hw_filter > 2) return VR_ERR_INVALID;
+    const bool pair = hw_filter == 2;
+    if (pair && dtype == VR_F32) return VR_ERR_INVALID;
     if (cudaSetDevice(device) != cudaSuccess) return VR_ERR_CUDA;
     const int N = 32;
-    const size_t esz = dtype == VR_U8 ? 1 : (dtype == VR_U16 ? 2 : 4);
+    const size_t esz = (dtype == VR_U8 ? 1 : (dtype == VR_U16 ? 2 : 4)) * (pair ? 2 : 1);
     std::vector<unsigned char> host((size_t)N * N * N * esz);
     uint32_t h = 0x1234567u;
-    for (size_t i = 0; i < (size_t)N * N * N; i++) {
+    for (size_t i = 0; i < (size_t)N * N * N * (pair ? 2 : 1); i++) {
         h = h * 1664525u + 1013904223u;
         if (dtype == VR_U8) host[i] = (unsigned char)(h >> 24);
         else if (dtype == VR_U16) reinterpret_cast<unsigned short *>(host.data())[i] = (unsigned short)(h >> 16);
@@ -56,13 +66,14 @@ extern "C" int vr_bench_tex_peak(int device, int dtype, int hw_filter, double *f
     cudaChannelFormatDesc cd = dtype == VR_U8    ? cudaCreateChannelDesc<unsigned char>()
                                : dtype == VR_U16 ? cudaCreateChannelDesc<unsigned short>()
                                                  : cudaCreateChannelDesc<float>();
+    if (pair) cd = dtype == VR_U8 ? cudaCreateChannelDesc<uchar2>() : cudaCreateChannelDesc<ushort2>();
     cudaArray_t arr = nullptr;
     cudaTextureObject_t tex = 0;
     float *sink = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     int rc = VR_ERR_CUDA;
     do {
-        if (cudaMalloc3DArray(&arr, &cd, make_cudaExtent(N, N, N)) != cudaSuccess) break;
+        if (cudaMalloc3DArray(&arr, &cd, make_cudaExtent(N, N, N), pair ? cudaArrayLayered : 0) != cudaSuccess) break;
         cudaMemcpy3DParms cp = {};
         cp.srcPtr = make_cudaPitchedPtr(host.data(), N * esz, N, N);
         cp.dstArray = arr;
@@ -84,11 +95,12 @@ extern "C" int vr_bench_tex_peak(int device, int dtype, int hw_filter, double *f
         const int blocks = sms * 8, iters = 2048;
         const float step = 2.56f / 32.0f * 0.125f;
         cudaEventCreate(&e0), cudaEventCreate(&e1);
-        k_texbench<<<blocks, 256>>>(tex, 64, step, sink); /* warm-up */
+        auto kern = pair ? k_texbench<true> : k_texbench<false>;
+        kern<<<blocks, 256>>>(tex, 64, step, sink); /* warm-up */
         double best = 0.0;
         for (int rep = 0; rep < 5; rep++) {
             cudaEventRecord(e0);
-            k_texbench<<<blocks, 256>>>(tex, iters, step, sink);
+            kern<<<blocks, 256>>>(tex, iters, step, sink);
             cudaEventRecord(e1);
             if (cudaEventSynchronize(e1) != cudaSuccess) break;
             float ms = 0.f;

@@ -179,6 +179,20 @@ __global__ void __launch_bounds__(256) k_chebyshev_pass(const uint32_t *__restri
     out[c] = (unsigned char)best;
 }
 
+/* Paired layout: texel (x, y) of layer l = (v[x, y, l-1], v[x, y, l]), zero outside the volume (that is
+ * the sampler's transparent-black border, offscreen_pass.cpp:1020-1026, on the z axis).  Written
+ * through a surface so the block-linear array is filled in place, without a linear staging copy. */
+template <typename T, typename T2>
+__global__ void __launch_bounds__(256) k_pack_pairs(const T *__restrict__ v, int nx, int ny, int nz, cudaSurfaceObject_t surf)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, l = blockIdx.z;
+    if (x >= nx) return;
+    T2 t;
+    t.x = l > 0 ? __ldg(v + ((size_t)(l - 1) * ny + y) * nx + x) : (T)0;
+    t.y = l < nz ? __ldg(v + ((size_t)l * ny + y) * nx + x) : (T)0;
+    surf2DLayeredwrite(t, surf, x * (int)sizeof(T2), y, l);
+}
+
 /* ------------------------------------------------------------------ synth -- */
 
 __device__ __forceinline__ uint32_t hash_u32(uint32_t h)
@@ -360,6 +374,28 @@ cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned c
     k_chebyshev_pass<<<blocks, 256, 0, s>>>(d_occ, d_dist, d_tmp, occ_n[0], occ_n[1], occ_n[2], 1);
     k_chebyshev_pass<<<blocks, 256, 0, s>>>(d_occ, d_tmp, d_dist, occ_n[0], occ_n[1], occ_n[2], 2);
     return cudaGetLastError();
+}
+
+cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, cudaArray_t pair_array,
+                             cudaStream_t s)
+{
+    if (dtype != VR_U8 && dtype != VR_U16) return cudaErrorInvalidValue;
+    if (ny > 65535u || nz + 1 > 65535u) return cudaErrorInvalidConfiguration;
+    cudaResourceDesc rd = {};
+    rd.resType = cudaResourceTypeArray;
+    rd.res.array.array = pair_array;
+    cudaSurfaceObject_t surf = 0;
+    cudaError_t e = cudaCreateSurfaceObject(&surf, &rd);
+    if (e != cudaSuccess) return e;
+    const dim3 grid((nx + 255) / 256, ny, nz + 1);
+    if (dtype == VR_U8)
+        k_pack_pairs<unsigned char, uchar2><<<grid, 256, 0, s>>>((const unsigned char *)dev, (int)nx, (int)ny, (int)nz, surf);
+    else
+        k_pack_pairs<unsigned short, ushort2><<<grid, 256, 0, s>>>((const unsigned short *)dev, (int)nx, (int)ny, (int)nz, surf);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaDestroySurfaceObject(surf);
+    return e;
 }
 
 cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,

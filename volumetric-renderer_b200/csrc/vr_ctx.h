@@ -33,6 +33,11 @@ struct MarchParams {
     /* S4: volume */
     cudaTextureObject_t tex_lin; /* normalised coords, linear, border 0, normalised-float read for u8/u16 */
     cudaTextureObject_t tex_pt;  /* texel coords, point, border 0, element read */
+    /* paired layout: 2-D layered array, layer l holds the texel pair (v[z = l-1], v[z = l]) (zero outside);
+     * normalised x/y, linear, border 0, normalised-float read.  One bilinear fetch + one lerp = one sample. */
+    cudaTextureObject_t tex_pair;
+    float pair_a[3], pair_b[3]; /* x, y: local normalised coord = q * a + b;  z: local texel coord + MAGIC - 1 = q * a + b */
+    float pair_zc;              /* -0.5 - forg[2]: frac = q_z * dims[2] + (pair_zc - floor) */
     float dims[3];      /* GLOBAL grid size as float */
     int org[3];         /* global voxel index of local texel 0 (0 unless sort-last) */
     float forg[3];      /* same as float */
@@ -45,8 +50,10 @@ struct MarchParams {
     /* S6: LUT, decoded to linear fp32, padded: P[k] = L[clamp(k-1, 0, n-1)], k = 0..n+2 (n+3 entries) */
     const float4 *lut_pad;
     const float4 *lut_dif; /* D[k] = P[k+1] - P[k], k = 0..n+1 (n+2 entries) */
+    const uint4 *lut_h;    /* HW sampler: entry k = {P[k] rgba, D[k] rgba} as eight fp16 (n+2 entries, 16 B each) */
     uint32_t nlut;
     float lutA, lutB; /* HW sampler: padded LUT coordinate = texel * lutA + lutB */
+    float lutBh;      /* lutB - 1/2 */
     /* empty-space skipping: bit per cell, x fastest */
     const uint32_t *occ;
     int occ_n[3];
@@ -97,6 +104,9 @@ struct vr_ctx {
     uint32_t nx = 0, ny = 0, nz = 0; /* local texture size */
     cudaArray_t array = nullptr;
     cudaTextureObject_t tex_lin = 0, tex_pt = 0;
+    int layout_req = VR_LAYOUT_AUTO;  /* vr_set_volume_layout: applies to the next upload */
+    cudaArray_t pair_array = nullptr; /* paired layout (see MarchParams::tex_pair), resident next to `array` */
+    cudaTextureObject_t tex_pair = 0;
 
     /* sort-last */
     bool sort_last = false;
@@ -107,8 +117,10 @@ struct vr_ctx {
     uint32_t nlut = 0;
     uint32_t *h_lut = nullptr; /* packed, as set */
     float4 *d_lut_pad = nullptr, *d_lut_dif = nullptr;
+    uint4 *d_lut_h = nullptr;
     /* tuning knobs (environment: VR_BATCH, VR_CTA_THREADS, VR_BBOX, VR_WARP_W, VR_CARVEOUT, VR_ESS_MIN_EMPTY) */
     int tune_batch = 2, tune_threads = 128, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
+    size_t tune_pair_max_bytes = (size_t)8 << 30; /* AUTO layout: pair only if the paired copy fits this (VR_PAIR_MAX_MB) */
     float tune_ess_min_empty = 0.25f; /* consult the occupancy grid only if at least this share of cells is empty */
 
     /* occupancy */
@@ -129,8 +141,8 @@ struct vr_ctx {
 /* ---- kernels / device-side stages (each .cu implements its own) ---- */
 
 /* K1 (march.cu) */
-cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, int ub, int threads,
-                            cudaStream_t s);
+cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, bool pair, int ub,
+                            int threads, cudaStream_t s);
 size_t vr_march_smem_bytes(const MarchParams &p, bool ess);
 
 /* K0 (volume.cu) */
@@ -142,6 +154,9 @@ cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const flo
                            unsigned long long *d_empty_count, cudaStream_t s);
 cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, unsigned char *d_tmp,
                            cudaStream_t s);
+/* fill the paired layered array (nx, ny, nz + 1 layers) from the linear volume; dtype u8 or u16 */
+cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, cudaArray_t pair_array,
+                             cudaStream_t s);
 cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
                         const int org[3], const uint32_t full[3], cudaStream_t s);
 
