@@ -59,10 +59,12 @@ typedef enum vr_sampler {
  * (an optimal-tiling VK_IMAGE_TYPE_3D image, offscreen_pass.cpp:943-989); here the loader may add a
  * second one.  Results of VR_SAMPLER_EXACT do not depend on it. */
 typedef enum vr_layout {
-    VR_LAYOUT_AUTO = 0,    /* PAIRED when the volume qualifies (u8/u16, nz <= 2047, within the memory budget) */
-    VR_LAYOUT_ARRAY3D = 1, /* 3-D block-linear array, hardware trilinear fetch (half texture rate) */
+    VR_LAYOUT_AUTO = 0,    /* both layouts when the volume qualifies (u8/u16, nz <= 2047, within the memory
+                              budget); each frame samples the one that is cheaper for it (vr_render_frame) */
+    VR_LAYOUT_ARRAY3D = 1, /* 3-D block-linear array only, hardware trilinear fetch (half texture rate) */
     VR_LAYOUT_PAIRED = 2   /* + a 2-D layered array whose texel l holds (v[z=l-1], v[z=l]): one full-rate
-                              bilinear fetch returns both z-slices, the z-lerp is one fp32 FMA */
+                              bilinear fetch returns both z-slices, the z-lerp is one fp32 FMA; the hardware
+                              sampler always uses it */
 } vr_layout;
 
 typedef struct vr_ctx vr_ctx;
@@ -162,8 +164,9 @@ int vr_set_march(vr_ctx *ctx, float ray_dist, float step_size);
 /* Layout used by the NEXT volume upload (vr_set_volume*, vr_load_nrrd, vr_synth_*); default AUTO.
  * VR_LAYOUT_PAIRED on a volume that does not qualify makes that upload fail with VR_ERR_INVALID. */
 int vr_set_volume_layout(vr_ctx *ctx, int layout);
-/* Layout of the current volume: VR_LAYOUT_ARRAY3D or VR_LAYOUT_PAIRED. */
-int vr_get_volume_layout(const vr_ctx *ctx, int *layout);
+/* Layouts resident for the current volume: VR_LAYOUT_ARRAY3D (only that) or VR_LAYOUT_PAIRED (both).
+ * last_frame_paired (may be NULL): 1 if the last vr_render* sampled the paired layout. */
+int vr_get_volume_layout(const vr_ctx *ctx, int *layout, int *last_frame_paired);
 
 int vr_get_options(const vr_ctx *ctx, vr_options *out);
 int vr_set_options(vr_ctx *ctx, const vr_options *opt);

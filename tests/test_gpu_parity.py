@@ -23,18 +23,22 @@ def small_volume(port, kind, dtype, n):
 
 
 def render_both(vr, port, vol, lut, moves=(), zoom=0.0, w=W, h=H, min_slice=(0, 0, 0), max_slice=(1, 1, 1),
-                minmax=None, **opts):
+                minmax=None, layout=None, **opts):
     cam, ocam = twin_cameras(vr, port, moves, zoom)
     mn, mx = minmax if minmax is not None else (float(vol.min()), float(vol.max()))
     op = vr.OffscreenPass(w, h)
     try:
         op.set_options(write_raw=1, collect_stats=1, **opts)
+        if layout is not None:
+            op.set_volume_layout(layout)
         op.volume_dataset_changed(vr.Dataset(vol, mn, mx))
         op.transfer_function_changed(lut)
         op.slicing_changed(min_slice, max_slice)
         op.set_camera(cam)
         op.record()
         img, raw, st = op.download(), op.download_raw(), op.stats()
+        if layout is not None and opts.get("sampler", vr.SAMPLER_HW) == vr.SAMPLER_HW and mx > mn:
+            assert op.last_frame_paired() == (layout == vr.LAYOUT_PAIRED)
     finally:
         op.close()
     o = port.render(oracle_frame(port, ocam, w, h, mn, mx, min_slice, max_slice), vol, lut, want_raw=True)
@@ -75,22 +79,30 @@ def test_exact_sampler_is_bit_identical(vr, port, case, ess):
 
 
 @pytest.mark.parametrize("case", range(len(CASES)))
-def test_hw_sampler_within_tolerance(vr, port, case):
+@pytest.mark.parametrize("layout", ["array3d", "paired"])
+def test_hw_sampler_within_tolerance(vr, port, case, layout):
+    """Both volume layouts of the hardware sampler (vr_layout): the 3-D array (one trilinear fetch) and the
+    paired 2-D layered array (one bilinear fetch + fp32 z-lerp) meet the same bar against the oracle."""
     kind, dtype, n, tfn, moves, zoom, slices = CASES[case]
+    if layout == "paired" and dtype == np.float32:
+        pytest.skip("f32 volumes have no paired layout")
     vol = small_volume(port, kind, dtype, n)
     lut = tf(port, tfn)
     kw = dict(min_slice=slices[0], max_slice=slices[1]) if slices else {}
-    img, raw, st, o = render_both(vr, port, vol, lut, moves, zoom, sampler=vr.SAMPLER_HW, empty_skip=1, **kw)
+    lay = vr.LAYOUT_PAIRED if layout == "paired" else vr.LAYOUT_ARRAY3D
+    img, raw, st, o = render_both(vr, port, vol, lut, moves, zoom, sampler=vr.SAMPLER_HW, empty_skip=1, layout=lay, **kw)
     assert st.covered_pixels == o["stats"].covered_pixels
     assert st.n_ref == o["stats"].n_ref  # positions are bit-exact in both modes
     assert_within_tolerance(img, o["rgba8"], f"case {case}")
 
 
-def test_empty_space_skipping_skips_and_changes_nothing(vr, port):
+@pytest.mark.parametrize("layout", ["array3d", "paired"])
+def test_empty_space_skipping_skips_and_changes_nothing(vr, port, layout):
     vol = small_volume(port, 2, np.uint16, 64)
     lut = tf(port, "C")
-    a = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=0)
-    b = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=1)
+    lay = vr.LAYOUT_PAIRED if layout == "paired" else vr.LAYOUT_ARRAY3D
+    a = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=0, layout=lay)
+    b = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=1, layout=lay)
     assert np.array_equal(bits(a[1]), bits(b[1]))
     assert np.array_equal(a[0], b[0])
     assert b[2].n_fetch < a[2].n_fetch * 0.7, (a[2].n_fetch, b[2].n_fetch)
@@ -105,6 +117,69 @@ def test_early_termination_error_is_bounded(vr, port):
     assert np.abs(a[1] - b[1]).max() < eps
     assert np.abs(a[0].astype(int) - b[0].astype(int)).max() <= 1
     assert b[2].n_fetch < a[2].n_fetch
+
+
+@pytest.mark.parametrize("layout", ["array3d", "paired"])
+def test_hw_early_termination_error_is_bounded(vr, port, layout):
+    """The hardware path tests the threshold once per batch (and once per double-batch in the unchecked
+    phase): it composites a few more real samples than the per-sample test would, never fewer."""
+    vol = small_volume(port, 1, np.uint16, 64)
+    lut = tf(port, "B")
+    eps = 1.0 / 256.0
+    lay = vr.LAYOUT_PAIRED if layout == "paired" else vr.LAYOUT_ARRAY3D
+    a = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=0, layout=lay)
+    b = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=0, early_term=1, early_term_eps=eps, layout=lay)
+    assert np.abs(a[1] - b[1]).max() < eps
+    assert b[2].n_fetch <= a[2].n_fetch
+
+
+def test_layouts_agree_and_paired_needs_integer_texels(vr, port):
+    """The two layouts sample the same voxels with different fixed-point weights (x, y, z: 8 fractional
+    bits in hardware for the 3-D array; x, y in hardware and z in fp32 for the pairs)."""
+    vol = small_volume(port, 1, np.uint16, 48)
+    lut = tf(port, "B")
+    a = render_both(vr, port, vol, lut, [(-120, 80)], sampler=vr.SAMPLER_HW, layout=vr.LAYOUT_ARRAY3D)
+    b = render_both(vr, port, vol, lut, [(-120, 80)], sampler=vr.SAMPLER_HW, layout=vr.LAYOUT_PAIRED)
+    assert np.abs(a[0].astype(int) - b[0].astype(int)).max() <= 2
+    assert a[2].n_ref == b[2].n_ref and a[2].n_fetch == b[2].n_fetch
+    op = vr.OffscreenPass(32, 32)
+    try:
+        op.set_volume_layout(vr.LAYOUT_PAIRED)
+        with pytest.raises(vr.VrError):
+            op.volume_dataset_changed(vr.Dataset(np.zeros((4, 4, 4), np.float32), 0.0, 1.0))
+        op.set_volume_layout(vr.LAYOUT_AUTO)
+        op.volume_dataset_changed(vr.Dataset(np.zeros((4, 4, 4), np.float32), 0.0, 1.0))
+        assert op.volume_layout() == vr.LAYOUT_ARRAY3D
+        op.volume_dataset_changed(vr.Dataset(np.zeros((4, 4, 4), np.uint16), 0.0, 1.0))
+        assert op.volume_layout() == vr.LAYOUT_PAIRED
+        op.set_volume_layout(vr.LAYOUT_ARRAY3D)
+        op.volume_dataset_changed(vr.Dataset(np.zeros((4, 4, 4), np.uint16), 0.0, 1.0))
+        assert op.volume_layout() == vr.LAYOUT_ARRAY3D
+    finally:
+        op.close()
+
+
+def test_auto_layout_is_chosen_per_frame(vr, port):
+    """AUTO keeps both layouts resident and samples the pairs only when the cube's screen bounding box
+    fills the GPU (vr_render_frame); the result meets the bar either way."""
+    vol = small_volume(port, 1, np.uint16, 64)
+    lut = tf(port, "B")
+    cam, ocam = twin_cameras(vr, port, [(30, 20)], 0.0)
+    for (w, h), want in (((160, 120), False), ((1280, 960), True)):
+        op = vr.OffscreenPass(w, h)
+        try:
+            op.set_options(empty_skip=0)
+            op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+            op.transfer_function_changed(lut)
+            op.set_camera(cam)
+            op.record()
+            img = op.download()
+            assert op.volume_layout() == vr.LAYOUT_PAIRED
+            assert op.last_frame_paired() == want, (w, h)
+        finally:
+            op.close()
+        o = port.render(oracle_frame(port, ocam, w, h, float(vol.min()), float(vol.max()), (0, 0, 0), (1, 1, 1)), vol, lut)
+        assert_within_tolerance(img, o["rgba8"], f"auto {w}x{h}")
 
 
 def test_startup_state_matches_reference_defaults(vr, port):

@@ -182,9 +182,15 @@ class OffscreenPass:
         self._check(lib.vr_set_volume_layout(self._h, int(layout)))
 
     def volume_layout(self) -> int:
+        """LAYOUT_PAIRED if the paired copy is resident next to the 3-D array, else LAYOUT_ARRAY3D."""
         v = C.c_int(0)
-        self._check(lib.vr_get_volume_layout(self._h, C.byref(v)))
+        self._check(lib.vr_get_volume_layout(self._h, C.byref(v), None))
         return v.value
+
+    def last_frame_paired(self) -> bool:
+        v, f = C.c_int(0), C.c_int(0)
+        self._check(lib.vr_get_volume_layout(self._h, C.byref(v), C.byref(f)))
+        return bool(f.value)
 
     def set_march(self, ray_dist: float, step_size: float):
         self._check(lib.vr_set_march(self._h, ray_dist, step_size))

@@ -55,7 +55,7 @@ SIGNATURES = {
     "vr_set_transfer_function": (C.c_int, [_P, _P, C.c_uint32]),
     "vr_set_march": (C.c_int, [_P, C.c_float, C.c_float]),
     "vr_set_volume_layout": (C.c_int, [_P, C.c_int]),
-    "vr_get_volume_layout": (C.c_int, [_P, C.POINTER(C.c_int)]),
+    "vr_get_volume_layout": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "vr_get_options": (C.c_int, [_P, C.POINTER(Options)]),
     "vr_set_options": (C.c_int, [_P, C.POINTER(Options)]),
     "vr_get_image": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_size_t)]),

@@ -187,6 +187,7 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
 {
     release_volume(c);
     c->dtype = dtype, c->nx = nx, c->ny = ny, c->nz = nz;
+    c->layout_used = c->layout_req;
     cudaChannelFormatDesc cd = dtype == VR_U8    ? cudaCreateChannelDesc<unsigned char>()
                                : dtype == VR_U16 ? cudaCreateChannelDesc<unsigned short>()
                                                  : cudaCreateChannelDesc<float>();
@@ -332,6 +333,7 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     }
     if (const char *e = std::getenv("VR_CARVEOUT")) c->tune_carveout = std::atoi(e);
     if (const char *e = std::getenv("VR_LAYOUT")) c->layout_req = std::atoi(e) == 1 ? VR_LAYOUT_ARRAY3D : (std::atoi(e) == 2 ? VR_LAYOUT_PAIRED : VR_LAYOUT_AUTO);
+    if (const char *e = std::getenv("VR_PAIR_POLICY")) c->tune_pair_policy = std::atoi(e);
     if (const char *e = std::getenv("VR_PAIR_MAX_MB")) c->tune_pair_max_bytes = (size_t)std::atoll(e) << 20;
     if (const char *e = std::getenv("VR_L2_GRAN")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(e));
     int rc = VR_OK;
@@ -500,10 +502,11 @@ extern "C" int vr_set_volume_layout(vr_ctx *c, int layout)
     return VR_OK;
 }
 
-extern "C" int vr_get_volume_layout(const vr_ctx *c, int *layout)
+extern "C" int vr_get_volume_layout(const vr_ctx *c, int *layout, int *last_frame_paired)
 {
     if (!c || !layout) return VR_ERR_INVALID;
     *layout = c->tex_pair ? VR_LAYOUT_PAIRED : VR_LAYOUT_ARRAY3D;
+    if (last_frame_paired) *last_frame_paired = c->last_pair ? 1 : 0;
     return VR_OK;
 }
 
@@ -636,6 +639,7 @@ void fill_params(const vr_ctx *c, MarchParams &p)
     p.tile_h = (uint32_t)c->tune_threads / VR_TILE;
     screen_bbox(c, p.bbox);
     p.ntx = (c->W + VR_TILE - 1) / VR_TILE, p.nty = (c->H + p.tile_h - 1) / p.tile_h;
+    p.nclr_x = (c->W + 63) / 64, p.nclr_y = (c->H + 31) / 32;
     p.rect[0] = (int)(p.bbox[0] / VR_TILE), p.rect[1] = (int)(p.bbox[1] / p.tile_h);
     p.rect[2] = (int)((p.bbox[2] + VR_TILE - 1) / VR_TILE), p.rect[3] = (int)((p.bbox[3] + p.tile_h - 1) / p.tile_h);
     if (p.bbox[2] <= p.bbox[0] || p.bbox[3] <= p.bbox[1]) {
@@ -688,7 +692,22 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     p.out = target;
     if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
-    const bool pair = !exact && c->tex_pair != 0;
+    /* Both layouts are resident; which one this frame samples is a cost question (the images agree within
+     * the hardware-sampler tolerance either way).  The paired fetch doubles the texture rate but adds
+     * dependent ALU work per step and DRAM bytes: it pays when the frame is throughput-bound, i.e. the
+     * cube's screen bounding box fills the GPU with at least one wave of CTAs and the occupancy grid is
+     * not consulted.  Small frames are latency-bound and sparse volumes are bound by the skipping. */
+    bool pair = !exact && c->tex_pair != 0;
+    const int policy = c->layout_used == VR_LAYOUT_PAIRED ? 1 : c->tune_pair_policy; /* asked for by name: always */
+    if (pair && policy == 2) {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+        const int64_t bw = (int64_t)p.bbox[2] - (int64_t)p.bbox[0], bh = (int64_t)p.bbox[3] - (int64_t)p.bbox[1];
+        pair = !ess && bw > 0 && bh > 0 && bw * bh >= (int64_t)sms * 10 * 128;
+    } else if (pair && policy == 0) {
+        pair = false;
+    }
+    c->last_pair = pair;
     VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, pair, c->tune_batch, c->tune_threads, s));
     if (c->opt.collect_stats)
         VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));

@@ -181,7 +181,8 @@ struct Ray {
     bool done;             /* no more positions to generate */
     bool stop;             /* early termination: composite nothing more */
     uint32_t nb, ns, nf;   /* counters (STATS) */
-    float ifx, ify, ifz;   /* ESS: 1 / (d * occ_scale): steps per fine cell, per axis */
+    float ifx, ify, ifz;   /* ESS: 1 / (d * occ_scale): steps per cell, per axis (1e30 where d = 0) */
+    float sgx, sgy, sgz;   /* ESS: sign of the direction, per axis */
     bool in_empty;         /* ESS: the last step generated fell into an empty fine cell */
 };
 
@@ -217,54 +218,47 @@ __device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r
  * distance d, the cube of 2d-1 cells around it is empty: the ray advances to where it leaves that
  * cube with nothing but the position additions of volume.frag:47 (positions stay bit-identical).
  * Every skipped position lies strictly inside the cube, i.e. is one the per-step test would have
- * rejected anyway -- results are unchanged. */
+ * rejected anyway -- results are unchanged.  Jumps are taken only inside the ray's safe interval
+ * (see safe_interval), where every position is inside the volume, the slices and the rank's own
+ * box: no clipping of the cube, and every skipped step counts as visited for the statistics. */
 template <bool STATS, bool PART>
-__device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r)
+__device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fast_lo, int fast_hi)
 {
 #pragma unroll 1
-    for (int guard = 0; guard < 8 && !r.done && r.in_empty; guard++) {
-        /* position in cell units */
-        const float fx = PART ? r.px * p.occ_scale[0] - p.occ_off[0] : r.px * p.occ_scale[0];
-        const float fy = PART ? r.py * p.occ_scale[1] - p.occ_off[1] : r.py * p.occ_scale[1];
-        const float fz = PART ? r.pz * p.occ_scale[2] - p.occ_off[2] : r.pz * p.occ_scale[2];
-        if (!(fx >= 0.0f && fy >= 0.0f && fz >= 0.0f && fx < p.occ_f_hi[0] && fy < p.occ_f_hi[1] && fz < p.occ_f_hi[2])) return;
-        const int c[3] = {(int)fx, (int)fy, (int)fz};
-        const int d = (int)__ldg(p.dist + ((c[2] * p.occ_n[1] + c[1]) * p.occ_n[0] + c[0]));
+    for (int guard = 0; guard < 8; guard++) {
+        if (r.done || !r.in_empty || r.i < fast_lo || r.i > fast_hi) return;
+        /* position in cell units (> 0 and inside the grid: the safe interval is inside the box) */
+        const float fx = PART ? fmaf(r.px, p.occ_scale[0], -p.occ_off[0]) : r.px * p.occ_scale[0];
+        const float fy = PART ? fmaf(r.py, p.occ_scale[1], -p.occ_off[1]) : r.py * p.occ_scale[1];
+        const float fz = PART ? fmaf(r.pz, p.occ_scale[2], -p.occ_off[2]) : r.pz * p.occ_scale[2];
+        const int cx = min((int)fx, p.occ_n[0] - 1), cy = min((int)fy, p.occ_n[1] - 1), cz = min((int)fz, p.occ_n[2] - 1);
+        const int d = (int)__ldg(p.dist + ((cz * p.occ_n[1] + cy) * p.occ_n[0] + cx));
         if (d == 0) {
             r.in_empty = false;
             return;
         }
-        /* steps until the ray leaves the cube, shrunk by a margin that covers the accumulated
-         * rounding of the positions (<= steps * ulp, far below 2e-3 cells) */
-        const float m = 2.0e-3f, rad = (float)(d - 1);
-        const float f[3] = {fx, fy, fz}, inv[3] = {r.ifx, r.ify, r.ifz};
-        float t = 1.0e9f;
-#pragma unroll
-        for (int a = 0; a < 3; a++) {
-            const float lo = fmaxf((float)c[a] - rad, 0.0f) + m;
-            const float hi = fminf((float)(c[a] + 1) + rad, p.occ_f_hi[a]) - m;
-            /* inv > 0: moving up, leaves through hi; inv < 0: leaves through lo; inv = 0 (d = 0): never */
-            const float ta = inv[a] > 0.0f ? (hi - f[a]) * inv[a] : (inv[a] < 0.0f ? (lo - f[a]) * inv[a] : 1.0e9f);
-            t = fminf(t, ta);
-        }
+        /* steps until the ray leaves the cube: per axis the exit plane is the cell centre +- (d - 1/2),
+         * pulled in by a margin that covers the accumulated rounding of the positions (<= steps * ulp,
+         * far below 2e-3 cells); sg = direction sign, if = steps per cell (1e30 on a zero component) */
+        const float R = (float)(d - 1) + (0.5f - 2.0e-3f);
+        const float tx = (fmaf(r.sgx, R, (float)cx + 0.5f) - fx) * r.ifx;
+        const float ty = (fmaf(r.sgy, R, (float)cy + 0.5f) - fy) * r.ify;
+        const float tz = (fmaf(r.sgz, R, (float)cz + 0.5f) - fz) * r.ifz;
         /* positions 0..k-1 are inside the cube; position 0 is the current one, known to be empty */
-        int k = (t >= 1.0f) ? (int)fminf(t, 65536.0f) : 1;
-        k = min(k, p.steps - r.i);
-        if (k <= 0) return;
+        int k = (int)fminf(fminf(fminf(tx, ty), tz), 65536.0f);
+        k = min(max(k, 1), fast_hi - r.i + 1);
         r.i += k;
-        if (STATS) r.nb += (uint32_t)k;
+        if (STATS) r.nb += (uint32_t)k, r.ns += (uint32_t)k;
 #pragma unroll 1
-        for (int j = 0; j < k; j++) {
-            if (STATS) {
-                bool s = r.px < p.max_slice[0] && r.py < p.max_slice[1] && r.pz < p.max_slice[2] && r.px > p.min_slice[0] &&
-                         r.py > p.min_slice[1] && r.pz > p.min_slice[2];
-                if (PART)
-                    s = s && r.px >= p.own_lo[0] && r.py >= p.own_lo[1] && r.pz >= p.own_lo[2] && r.px < p.own_hi[0] &&
-                        r.py < p.own_hi[1] && r.pz < p.own_hi[2];
-                r.ns += s;
-            }
+        for (; k >= 4; k -= 4) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) r.px += r.dx, r.py += r.dy, r.pz += r.dz;
+        }
+        if (k & 2) {
+            r.px += r.dx, r.py += r.dy, r.pz += r.dz;
             r.px += r.dx, r.py += r.dy, r.pz += r.dz;
         }
+        if (k & 1) r.px += r.dx, r.py += r.dy, r.pz += r.dz;
     }
 }
 
@@ -343,7 +337,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
 }
 
 /* Second half: normalise, transfer function, composite (volume.frag:42-45). */
-template <bool EXACT, bool STATS, bool PAIR, int U, bool PRED>
+template <bool EXACT, bool STATS, bool PAIR, int U, bool PRED, bool ERT = true>
 __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batch<U> &b, const float4 *sP,
                                               const LutH &L)
 {
@@ -384,7 +378,7 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
     }
     /* the hardware path tests for early termination once per batch: the samples composited past
      * the threshold are real samples, the bound on what is dropped is unchanged */
-    if (!EXACT && r.T < p.ert_eps) r.stop = true, r.done = true;
+    if (!EXACT && ERT && r.T < p.ert_eps) r.stop = true, r.done = true;
 }
 
 /* EXACT: verification sampler.  ESS: occupancy grid consulted.  STATS: sample counters.
@@ -419,9 +413,28 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         tx = p.sp_cx + ox, ty = p.sp_cy + oy;
         if (tx < p.rect[0] || ty < p.rect[1] || tx >= p.rect[2] || ty >= p.rect[3]) return;
     } else {
+        /* clear colour only (offscreen_pass.cpp:170-173): a block clears a 64x32 pixel region in groups of
+         * four pixels (one 16-byte store), leaving out the tiles the spiral blocks own */
         const uint32_t j = blockIdx.x - p.sp_count;
-        ty = (int)(j / p.ntx), tx = (int)(j - (uint32_t)ty * p.ntx);
-        if (tx >= p.rect[0] && ty >= p.rect[1] && tx < p.rect[2] && ty < p.rect[3]) return;
+        const uint32_t ry = (j / p.nclr_x) * 32u, rx = (j % p.nclr_x) * 64u;
+        const uint32_t c8 = (uint32_t)(VR_CLEAR_RGB * 255.0f + 0.5f), cw = c8 | (c8 << 8) | (c8 << 16) | 0xff000000u;
+        const bool wide = (p.W & 3u) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;
+        for (uint32_t g = threadIdx.x; g < 512u; g += nthreads) {
+            const uint32_t gx = rx + (g & 15u) * 4u, gy = ry + (g >> 4);
+            if (gx >= p.W || gy >= p.H) continue;
+            const int ttx = (int)(gx / VR_TILE), tty = (int)(gy / p.tile_h);
+            if (ttx >= p.rect[0] && tty >= p.rect[1] && ttx < p.rect[2] && tty < p.rect[3]) continue;
+            if (p.pt_nranks > 1 && ((gy / p.pt_px) * p.pt_nx + gx / p.pt_px) % p.pt_nranks != p.pt_rank) continue;
+            const size_t gp = (size_t)gy * p.W + gx;
+            if (wide) {
+                *reinterpret_cast<uint4 *>(p.out + gp) = make_uint4(cw, cw, cw, cw);
+            } else {
+                for (uint32_t k = 0; k < 4u && gx + k < p.W; k++) p.out[gp + k] = make_uchar4(c8, c8, c8, 255);
+            }
+            if (p.raw)
+                for (uint32_t k = 0; k < 4u && gx + k < p.W; k++) p.raw[gp + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        return;
     }
     const uint32_t x0 = (uint32_t)tx * VR_TILE, y0 = (uint32_t)ty * p.tile_h;
     if (x0 >= p.W || y0 >= p.H) return; /* uniform per CTA */
@@ -436,11 +449,10 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     const bool valid = px < p.W && py < p.H;
     const size_t pix = (size_t)py * p.W + px;
 
-    /* tiles outside the screen bounding box of the cube cannot receive a fragment */
     Entry e;
-    const bool covered = in_bbox && valid && pixel_entry(p, px, py, e);
+    const bool covered = valid && pixel_entry(p, px, py, e);
 
-    if (!in_bbox || !__syncthreads_or(covered)) {
+    if (!__syncthreads_or(covered)) {
         /* nothing to march in this tile: clear colour only (offscreen_pass.cpp:170-173) */
         if (valid) {
             const unsigned char c = (unsigned char)(VR_CLEAR_RGB * 255.0f + 0.5f);
@@ -472,7 +484,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     Ray ray;
     ray.cr = cr, ray.cg = cg, ray.cb = cb, ray.T = T;
     ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
-    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
+    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.sgx = ray.sgy = ray.sgz = 1.0f, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
     bool parked = false; /* fast phase: this lane only keeps its warp company */
     float t_saved = 1.0f;
@@ -483,19 +495,21 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     constexpr int U = EXACT ? 1 : UB;
     LutH L;
     L.base = (uint32_t)__cvta_generic_to_shared(sH) - (VR_MAGIC_BITS << 4);
+    asm volatile("" : "+r"(L.base)); /* keep it one register: the lookup address is a single shift-add */
     L.A = p.lutA, L.Bh = p.lutBh, L.hi = (float)p.nlut + 0.5f;
     if (ESS) {
         const float sx_ = ray.dx * p.occ_scale[0], sy_ = ray.dy * p.occ_scale[1], sz_ = ray.dz * p.occ_scale[2];
-        ray.ifx = sx_ != 0.0f ? __frcp_rn(sx_) : 0.0f;
-        ray.ify = sy_ != 0.0f ? __frcp_rn(sy_) : 0.0f;
-        ray.ifz = sz_ != 0.0f ? __frcp_rn(sz_) : 0.0f;
+        ray.ifx = sx_ != 0.0f ? __frcp_rn(sx_) : 1.0e30f;
+        ray.ify = sy_ != 0.0f ? __frcp_rn(sy_) : 1.0e30f;
+        ray.ifz = sz_ != 0.0f ? __frcp_rn(sz_) : 1.0e30f;
+        ray.sgx = ray.ifx < 0.0f ? -1.0f : 1.0f, ray.sgy = ray.ify < 0.0f ? -1.0f : 1.0f, ray.sgz = ray.ifz < 0.0f ? -1.0f : 1.0f;
     }
     /* Warp-uniform choice per batch.  Checked: every test of volume.frag:34-40 is evaluated (always
      * correct).  Unchecked: every live lane is inside its safe interval; predicated if some lane is
      * finished or the occupancy grid is consulted, else no per-lane flag at all. */
 #define VR_ISSUE(B_)                                                                                        \
     do {                                                                                                    \
-        if (ESS && !EXACT) skip_empty<STATS, PART>(p, ray);                                           \
+        if (ESS && !EXACT) skip_empty<STATS, PART>(p, ray, fast_lo, fast_hi);                               \
         const bool in_safe = ray.i >= fast_lo && ray.i + U - 1 <= fast_hi;                                  \
         if (!EXACT && !ESS && __all_sync(0xffffffffu, !ray.done && in_safe))                                \
             batch_issue<EXACT, ESS, STATS, PART, PAIR, U, false, false>(p, ray, B_);                        \
@@ -538,12 +552,13 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
 #pragma unroll 1
                 for (int it = 0; it < nb; it++) {
                     batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, b);
-                    batch_consume<false, STATS, PAIR, U, false>(p, ray, a, sP, L);
+                    batch_consume<false, STATS, PAIR, U, false, false>(p, ray, a, sP, L);
                     batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, a);
-                    batch_consume<false, STATS, PAIR, U, false>(p, ray, b, sP, L);
-                    if (__all_sync(0xffffffffu, ray.done)) break;
+                    batch_consume<false, STATS, PAIR, U, false, false>(p, ray, b, sP, L);
+                    if (__all_sync(0xffffffffu, ray.T < p.ert_eps)) break; /* parked lanes: T = 0 (never true when ERT is off: nb bounds the loop) */
                 }
-                batch_consume<false, STATS, PAIR, U, false>(p, ray, a, sP, L);
+                batch_consume<false, STATS, PAIR, U, false, false>(p, ray, a, sP, L);
+                if (!ray.done && ray.T < p.ert_eps) ray.stop = true, ray.done = true;
                 continue;
             }
             /* head / tail: one double-batch with the tests the lanes need */
@@ -662,7 +677,7 @@ size_t vr_march_smem_bytes(const MarchParams &p, bool exact)
 cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, bool pair, int ub,
                             int threads, cudaStream_t s)
 {
-    const uint64_t ctas = (uint64_t)p.sp_count + (uint64_t)p.ntx * p.nty;
+    const uint64_t ctas = (uint64_t)p.sp_count + (uint64_t)p.nclr_x * p.nclr_y;
     if (ctas == 0) return cudaSuccess;
     if (ctas > 0x7fffffffull) return cudaErrorInvalidConfiguration;
     const size_t smem = vr_march_smem_bytes(p, exact);

@@ -71,6 +71,7 @@ struct MarchParams {
     /* CTA tiles: ntx x nty over the target; rect = tiles that can be covered (x0,y0,x1,y1, exclusive);
      * the first sp_count blocks spiral out from tile (sp_cx, sp_cy) over the square containing rect */
     uint32_t ntx, nty, sp_count;
+    uint32_t nclr_x, nclr_y; /* clear-colour blocks: 64x32 pixel regions over the target */
     int sp_cx, sp_cy, rect[4];
     int carveout;                                             /* shared-memory carve-out hint in percent, -1 = driver default */
     uint32_t warp_w;                                          /* warp footprint width: 4, 8 or 16 pixels */
@@ -105,6 +106,8 @@ struct vr_ctx {
     cudaArray_t array = nullptr;
     cudaTextureObject_t tex_lin = 0, tex_pt = 0;
     int layout_req = VR_LAYOUT_AUTO;  /* vr_set_volume_layout: applies to the next upload */
+    int layout_used = VR_LAYOUT_AUTO; /* the request the current volume was uploaded under */
+    bool last_pair = false;           /* the last frame sampled the paired layout */
     cudaArray_t pair_array = nullptr; /* paired layout (see MarchParams::tex_pair), resident next to `array` */
     cudaTextureObject_t tex_pair = 0;
 
@@ -120,6 +123,7 @@ struct vr_ctx {
     uint4 *d_lut_h = nullptr;
     /* tuning knobs (environment: VR_BATCH, VR_CTA_THREADS, VR_BBOX, VR_WARP_W, VR_CARVEOUT, VR_ESS_MIN_EMPTY) */
     int tune_batch = 2, tune_threads = 128, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
+    int tune_pair_policy = 2; /* VR_PAIR_POLICY: 0 never sample the paired layout, 1 always, 2 per frame (vr_render_frame) */
     size_t tune_pair_max_bytes = (size_t)8 << 30; /* AUTO layout: pair only if the paired copy fits this (VR_PAIR_MAX_MB) */
     float tune_ess_min_empty = 0.25f; /* consult the occupancy grid only if at least this share of cells is empty */
 
