@@ -101,6 +101,15 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
+def measured_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_march launch of this workload, from the committed
+    ncu --set full capture (profiles/traffic.json names the summary it was read from); None if not captured."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[workload]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def physical_gpu_index(local_rank):
     vis = os.environ.get("CUDA_VISIBLE_DEVICES")
     if vis:
@@ -258,7 +267,7 @@ def run_ours(args):
                        "parallelism": f"frames of the orbit dealt round-robin to {world} GPU(s), no collective"},
             "executed_samples_per_s": all_exec / (dev_ms * 1e-3),
             "roofline": {"bound": "hbm", "achieved": alg_bytes / step_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": alg_bytes / step_s / 1e9 / hbm_peak, "traffic": None,
+                         "frac": alg_bytes / step_s / 1e9 / hbm_peak, "traffic": measured_traffic(args.workload),
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback",
                          "algorithmic_bytes_per_launch": alg_bytes},
             "roofline_tex": {"bound": "tex", "achieved": exec_rate / 1e9, "peak": tex_peak / 1e9, "unit": "Gfetch/s",

@@ -62,9 +62,9 @@ typedef enum vr_layout {
     VR_LAYOUT_AUTO = 0,    /* both layouts when the volume qualifies (u8/u16, nz <= 2047, within the memory
                               budget); each frame samples the one that is cheaper for it (vr_render_frame) */
     VR_LAYOUT_ARRAY3D = 1, /* 3-D block-linear array only, hardware trilinear fetch (half texture rate) */
-    VR_LAYOUT_PAIRED = 2   /* + a 2-D layered array whose texel l holds (v[z=l-1], v[z=l]): one full-rate
-                              bilinear fetch returns both z-slices, the z-lerp is one fp32 FMA; the hardware
-                              sampler always uses it */
+    VR_LAYOUT_PAIRED = 2   /* + per axis w a 2-D layered array whose layer l holds the texel pairs (v[w=l-1], v[w=l]):
+                              one full-rate bilinear fetch returns both slices, the lerp along w is one fp32
+                              FMA; the hardware sampler always uses them (7x the volume's bytes in HBM) */
 } vr_layout;
 
 typedef struct vr_ctx vr_ctx;
@@ -165,7 +165,9 @@ int vr_set_march(vr_ctx *ctx, float ray_dist, float step_size);
  * VR_LAYOUT_PAIRED on a volume that does not qualify makes that upload fail with VR_ERR_INVALID. */
 int vr_set_volume_layout(vr_ctx *ctx, int layout);
 /* Layouts resident for the current volume: VR_LAYOUT_ARRAY3D (only that) or VR_LAYOUT_PAIRED (both).
- * last_frame_paired (may be NULL): 1 if the last vr_render* sampled the paired layout. */
+ * last_frame_paired (may be NULL): 0 if the last vr_render* sampled the 3-D array, else 1 + the model
+ * axis (0 x, 1 y, 2 z) its pairs ran along -- the axis that keeps a warp's fetch in the fewest layers
+ * (the axis the camera looks down, or the third axis for a view between two axes). */
 int vr_get_volume_layout(const vr_ctx *ctx, int *layout, int *last_frame_paired);
 
 int vr_get_options(const vr_ctx *ctx, vr_options *out);

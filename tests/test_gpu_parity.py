@@ -159,6 +159,35 @@ def test_layouts_agree_and_paired_needs_integer_texels(vr, port):
         op.close()
 
 
+@pytest.mark.parametrize("moves,axis", [([], 1), ([(360, 0)], 0), ([(40, 320)], 2), ([(-300, -60)], 0)])
+@pytest.mark.parametrize("ess", [0, 1])
+def test_pair_axis_follows_the_camera(vr, port, moves, axis, ess):
+    """The pairs run along the axis the camera looks down most; the march then works in a permuted
+    sampling space (slices, occupancy grid and bounds follow).  Non-cubic volume, asymmetric slices."""
+    vol = port.synth(2 if ess else 1, 0x5EED0042, np.uint16, (56, 24, 40))  # (nx, ny, nz)
+    lut = tf(port, "C" if ess else "B")
+    cam, ocam = twin_cameras(vr, port, moves, 0.0)
+    mn, mx = float(vol.min()), float(vol.max())
+    lo, hi = (0.1, 0.0, 0.2), (0.95, 0.8, 1.0)
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_options(write_raw=1, collect_stats=1, sampler=vr.SAMPLER_HW, empty_skip=ess)
+        op.set_volume_layout(vr.LAYOUT_PAIRED)
+        op.volume_dataset_changed(vr.Dataset(vol, mn, mx))
+        op.transfer_function_changed(lut)
+        op.slicing_changed(lo, hi)
+        op.set_camera(cam)
+        op.record()
+        img, st = op.download(), op.stats()
+        assert op.last_frame_pair_axis() == axis
+    finally:
+        op.close()
+    o = port.render(oracle_frame(port, ocam, W, H, mn, mx, lo, hi), vol, lut)
+    assert st.covered_pixels == o["stats"].covered_pixels
+    assert st.n_ref == o["stats"].n_ref and st.n_inslice == o["stats"].n_inslice
+    assert_within_tolerance(img, o["rgba8"], f"pair axis {axis}")
+
+
 def test_auto_layout_is_chosen_per_frame(vr, port):
     """AUTO keeps both layouts resident and samples the pairs only when the cube's screen bounding box
     fills the GPU (vr_render_frame); the result meets the bar either way."""

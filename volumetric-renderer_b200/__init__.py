@@ -192,6 +192,12 @@ class OffscreenPass:
         self._check(lib.vr_get_volume_layout(self._h, C.byref(v), C.byref(f)))
         return bool(f.value)
 
+    def last_frame_pair_axis(self) -> int | None:
+        """Model axis (0 x, 1 y, 2 z) the last frame's pairs ran along; None if it sampled the 3-D array."""
+        v, f = C.c_int(0), C.c_int(0)
+        self._check(lib.vr_get_volume_layout(self._h, C.byref(v), C.byref(f)))
+        return f.value - 1 if f.value else None
+
     def set_march(self, ray_dist: float, step_size: float):
         self._check(lib.vr_set_march(self._h, ray_dist, step_size))
 

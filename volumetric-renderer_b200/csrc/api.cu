@@ -156,8 +156,10 @@ void release_volume(vr_ctx *c)
 {
     if (c->tex_lin) cudaDestroyTextureObject(c->tex_lin), c->tex_lin = 0;
     if (c->tex_pt) cudaDestroyTextureObject(c->tex_pt), c->tex_pt = 0;
-    if (c->tex_pair) cudaDestroyTextureObject(c->tex_pair), c->tex_pair = 0;
-    if (c->pair_array) cudaFreeArray(c->pair_array), c->pair_array = nullptr;
+    for (int a = 0; a < 3; a++) {
+        if (c->tex_pair[a]) cudaDestroyTextureObject(c->tex_pair[a]), c->tex_pair[a] = 0;
+        if (c->pair_array[a]) cudaFreeArray(c->pair_array[a]), c->pair_array[a] = nullptr;
+    }
     if (c->array) cudaFreeArray(c->array), c->array = nullptr;
     if (c->d_cell_range) cudaFree(c->d_cell_range), c->d_cell_range = nullptr;
     if (c->d_occ) cudaFree(c->d_occ), c->d_occ = nullptr;
@@ -216,25 +218,34 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
     tp.normalizedCoords = 0;
     VR_CUDA(c, cudaCreateTextureObject(&c->tex_pt, &rd, &tp, nullptr));
 
-    /* second layout for the hardware sampler (vr_layout): z-pairs in a 2-D layered array */
-    const bool can_pair = (dtype == VR_U8 || dtype == VR_U16) && nz + 1 <= 2048 && nx <= 32768 && ny <= 32768;
-    const size_t pair_bytes = (size_t)nx * ny * ((size_t)nz + 1) * 2 * dtype_size(dtype);
+    /* second layout for the hardware sampler (vr_layout): pairs along each axis in 2-D layered arrays */
+    const uint32_t nd[3] = {nx, ny, nz};
+    bool can_pair = dtype == VR_U8 || dtype == VR_U16;
+    size_t pair_bytes = 0;
+    for (int a = 0; a < 3; a++) {
+        can_pair = can_pair && nd[a] + 1 <= 2048 && nd[a] <= 32768;
+        pair_bytes += (size_t)nx * ny * nz / nd[a] * ((size_t)nd[a] + 1) * 2 * dtype_size(dtype);
+    }
     if (c->layout_req == VR_LAYOUT_PAIRED && !can_pair)
-        return fail(c, VR_ERR_INVALID, "VR_LAYOUT_PAIRED needs a u8/u16 volume with nz <= 2047 and nx, ny <= 32768");
+        return fail(c, VR_ERR_INVALID, "VR_LAYOUT_PAIRED needs a u8/u16 volume of at most 2047 voxels per axis");
     if (c->layout_req == VR_LAYOUT_PAIRED || (c->layout_req == VR_LAYOUT_AUTO && can_pair && pair_bytes <= c->tune_pair_max_bytes)) {
         cudaChannelFormatDesc cd2 = dtype == VR_U8 ? cudaCreateChannelDesc<uchar2>() : cudaCreateChannelDesc<ushort2>();
-        VR_CUDA(c, cudaMalloc3DArray(&c->pair_array, &cd2, make_cudaExtent(nx, ny, (size_t)nz + 1),
-                                     cudaArrayLayered | cudaArraySurfaceLoadStore));
-        VR_CUDA(c, vr_k0_pack_pairs(dev, dtype, nx, ny, nz, c->pair_array, c->stream));
-        cudaResourceDesc rp = {};
-        rp.resType = cudaResourceTypeArray;
-        rp.res.array.array = c->pair_array;
-        cudaTextureDesc tq = {};
-        tq.addressMode[0] = tq.addressMode[1] = tq.addressMode[2] = cudaAddressModeBorder;
-        tq.filterMode = cudaFilterModeLinear;
-        tq.readMode = cudaReadModeNormalizedFloat;
-        tq.normalizedCoords = 1;
-        VR_CUDA(c, cudaCreateTextureObject(&c->tex_pair, &rp, &tq, nullptr));
+        for (int a = 0; a < 3; a++) {
+            /* in-plane extent (u, v), layers along a: a = 2 -> (x, y), a = 1 -> (x, z), a = 0 -> (y, z) */
+            const uint32_t eu = a == 0 ? ny : nx, ev = a == 2 ? ny : nz;
+            VR_CUDA(c, cudaMalloc3DArray(&c->pair_array[a], &cd2, make_cudaExtent(eu, ev, (size_t)nd[a] + 1),
+                                         cudaArrayLayered | cudaArraySurfaceLoadStore));
+            VR_CUDA(c, vr_k0_pack_pairs(dev, dtype, nx, ny, nz, a, c->pair_array[a], c->stream));
+            cudaResourceDesc rp = {};
+            rp.resType = cudaResourceTypeArray;
+            rp.res.array.array = c->pair_array[a];
+            cudaTextureDesc tq = {};
+            tq.addressMode[0] = tq.addressMode[1] = tq.addressMode[2] = cudaAddressModeBorder;
+            tq.filterMode = cudaFilterModeLinear;
+            tq.readMode = cudaReadModeNormalizedFloat;
+            tq.normalizedCoords = 1;
+            VR_CUDA(c, cudaCreateTextureObject(&c->tex_pair[a], &rp, &tq, nullptr));
+        }
     }
 
     /* ubo.min_density / max_density = dataset.min / max (offscreen_pass.cpp:265-266) */
@@ -334,6 +345,7 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     if (const char *e = std::getenv("VR_CARVEOUT")) c->tune_carveout = std::atoi(e);
     if (const char *e = std::getenv("VR_LAYOUT")) c->layout_req = std::atoi(e) == 1 ? VR_LAYOUT_ARRAY3D : (std::atoi(e) == 2 ? VR_LAYOUT_PAIRED : VR_LAYOUT_AUTO);
     if (const char *e = std::getenv("VR_PAIR_POLICY")) c->tune_pair_policy = std::atoi(e);
+    if (const char *e = std::getenv("VR_PAIR_AXIS")) c->tune_pair_axis = std::atoi(e) >= 0 && std::atoi(e) <= 2 ? std::atoi(e) : -1;
     if (const char *e = std::getenv("VR_PAIR_MAX_MB")) c->tune_pair_max_bytes = (size_t)std::atoll(e) << 20;
     if (const char *e = std::getenv("VR_L2_GRAN")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(e));
     int rc = VR_OK;
@@ -505,8 +517,8 @@ extern "C" int vr_set_volume_layout(vr_ctx *c, int layout)
 extern "C" int vr_get_volume_layout(const vr_ctx *c, int *layout, int *last_frame_paired)
 {
     if (!c || !layout) return VR_ERR_INVALID;
-    *layout = c->tex_pair ? VR_LAYOUT_PAIRED : VR_LAYOUT_ARRAY3D;
-    if (last_frame_paired) *last_frame_paired = c->last_pair ? 1 : 0;
+    *layout = c->tex_pair[2] ? VR_LAYOUT_PAIRED : VR_LAYOUT_ARRAY3D;
+    if (last_frame_paired) *last_frame_paired = c->last_pair ? 1 + c->last_pair_axis : 0;
     return VR_OK;
 }
 
@@ -576,7 +588,15 @@ void screen_bbox(const vr_ctx *c, uint32_t bbox[4])
     bbox[3] = (uint32_t)std::min(std::max(hy, 0.0), (double)c->H);
 }
 
-void fill_params(const vr_ctx *c, MarchParams &p)
+template <typename T>
+void permute3(T *v, const int perm[3])
+{
+    const T t[3] = {v[0], v[1], v[2]};
+    for (int j = 0; j < 3; j++) v[j] = t[perm[j]];
+}
+
+/* pair_axis < 0: the frame samples the 3-D array; else the model axis the pairs run along */
+void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
 {
     std::memset(&p, 0, sizeof(p));
     for (int r = 0; r < 4; r++) p.c0[r] = c->rc[0][r], p.c1[r] = c->rc[1][r], p.c2[r] = c->rc[2][r], p.c3[r] = c->rc[3][r];
@@ -614,7 +634,21 @@ void fill_params(const vr_ctx *c, MarchParams &p)
     p.dtype = c->dtype;
     p.dscale = c->dtype == VR_U8 ? 255.0f : (c->dtype == VR_U16 ? 65535.0f : 1.0f);
     p.lut_pad = c->d_lut_pad, p.lut_dif = c->d_lut_dif, p.lut_h = c->d_lut_h, p.nlut = c->nlut;
-    p.tex_pair = c->tex_pair;
+    p.occ_stride[0] = 1, p.occ_stride[1] = c->occ_n[0], p.occ_stride[2] = c->occ_n[0] * c->occ_n[1];
+    p.pair_axis = 2;
+    p.tex_pair = 0;
+    if (pair_axis >= 0) {
+        /* sampling space (u, v, w) = model axes perm[0..2], w = the pair axis: every per-axis field is
+         * stored in that order; the kernel permutes the ray once (march.cu) */
+        const int perm[3] = {pair_axis == 0 ? 1 : 0, pair_axis == 2 ? 1 : 2, pair_axis};
+        p.pair_axis = pair_axis;
+        p.tex_pair = c->tex_pair[pair_axis];
+        permute3(p.min_slice, perm), permute3(p.max_slice, perm);
+        permute3(p.dims, perm), permute3(p.org, perm), permute3(p.forg, perm), permute3(p.inv_ldims, perm);
+        permute3(p.own_lo, perm), permute3(p.own_hi, perm), permute3(p.box_lo, perm), permute3(p.box_hi, perm);
+        permute3(p.occ_n, perm), permute3(p.occ_stride, perm), permute3(p.occ_scale, perm), permute3(p.occ_off, perm);
+        permute3(p.occ_f_hi, perm);
+    }
     for (int i = 0; i < 2; i++) {
         p.pair_a[i] = p.dims[i] * p.inv_ldims[i];
         p.pair_b[i] = -p.forg[i] * p.inv_ldims[i];
@@ -687,27 +721,47 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
         }
         target = c->d_image_slot[frame_index];
     }
-    MarchParams p;
-    fill_params(c, p);
-    p.out = target;
-    if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
-    if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
     /* Both layouts are resident; which one this frame samples is a cost question (the images agree within
      * the hardware-sampler tolerance either way).  The paired fetch doubles the texture rate but adds
-     * dependent ALU work per step and DRAM bytes: it pays when the frame is throughput-bound, i.e. the
-     * cube's screen bounding box fills the GPU with at least one wave of CTAs and the occupancy grid is
-     * not consulted.  Small frames are latency-bound and sparse volumes are bound by the skipping. */
-    bool pair = !exact && c->tex_pair != 0;
+     * dependent ALU work per step: it pays when the frame is throughput-bound, i.e. the cube's screen
+     * bounding box fills the GPU with at least one wave of CTAs and the occupancy grid is not consulted.
+     * Small frames are latency-bound and sparse volumes are bound by the skipping.
+     * The pair axis w is the one that keeps a warp's fetch in the fewest layers: a warp is ww x wh
+     * neighbouring pixels, so with r, s the model-space directions of screen x and y (columns 0 and 1 of
+     * inverse(proj * view)) one fetch instruction spans about 1 + ww |r_w| + wh |s_w| layers.  That is
+     * minimal for the axis the camera looks down (then consecutive samples of a ray also fall into
+     * different layers and only every step-th layer is read from HBM); for a view between two axes it
+     * is the third axis.  Measured (profiles/r1_exp_axis.txt): the wrong axis costs up to 2x. */
+    bool pair = !exact && c->tex_pair[2] != 0;
+    int pair_axis = 2;
+    if (pair && c->tune_pair_axis < 0) {
+        const float *r = c->rc[0], *u = c->rc[1];
+        const double rn = std::sqrt((double)r[0] * r[0] + (double)r[1] * r[1] + (double)r[2] * r[2]);
+        const double un = std::sqrt((double)u[0] * u[0] + (double)u[1] * u[1] + (double)u[2] * u[2]);
+        const double ww = (double)c->tune_warp_w, wh = 32.0 / ww;
+        double best = 1e30;
+        for (int a = 2; a >= 0; a--) { /* ties go to z, then y */
+            const double layers = 1.0 + (rn > 0 ? ww * std::fabs(r[a]) / rn : 0.0) + (un > 0 ? wh * std::fabs(u[a]) / un : 0.0);
+            if (layers < best - 1e-9) best = layers, pair_axis = a;
+        }
+    } else if (pair) {
+        pair_axis = c->tune_pair_axis;
+    }
     const int policy = c->layout_used == VR_LAYOUT_PAIRED ? 1 : c->tune_pair_policy; /* asked for by name: always */
+    if (pair && policy == 0) pair = false;
+    MarchParams p;
+    fill_params(c, p, -1);
     if (pair && policy == 2) {
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
         const int64_t bw = (int64_t)p.bbox[2] - (int64_t)p.bbox[0], bh = (int64_t)p.bbox[3] - (int64_t)p.bbox[1];
         pair = !ess && bw > 0 && bh > 0 && bw * bh >= (int64_t)sms * 10 * 128;
-    } else if (pair && policy == 0) {
-        pair = false;
     }
-    c->last_pair = pair;
+    if (pair) fill_params(c, p, pair_axis);
+    c->last_pair = pair, c->last_pair_axis = pair_axis;
+    p.out = target;
+    if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
+    if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
     VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, pair, c->tune_batch, c->tune_threads, s));
     if (c->opt.collect_stats)
         VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));

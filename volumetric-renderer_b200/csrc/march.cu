@@ -129,7 +129,7 @@ __device__ __forceinline__ int cell_distance(const MarchParams &p, float x, floa
     cy = min(max(cy, 0), p.occ_n[1] - 1);
     cz = min(max(cz, 0), p.occ_n[2] - 1);
     /* 256 KiB at most, read through L1 (no shared-memory staging: it would cost occupancy) */
-    return (int)__ldg(p.dist + ((cz * p.occ_n[1] + cy) * p.occ_n[0] + cx));
+    return (int)__ldg(p.dist + (cz * p.occ_stride[2] + cy * p.occ_stride[1] + cx * p.occ_stride[0]));
 }
 
 #define VR_MAGIC 12582912.0f /* 1.5 * 2^23: x + VR_MAGIC rounds x to an integer held in the low mantissa bits */
@@ -232,7 +232,7 @@ __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fas
         const float fy = PART ? fmaf(r.py, p.occ_scale[1], -p.occ_off[1]) : r.py * p.occ_scale[1];
         const float fz = PART ? fmaf(r.pz, p.occ_scale[2], -p.occ_off[2]) : r.pz * p.occ_scale[2];
         const int cx = min((int)fx, p.occ_n[0] - 1), cy = min((int)fy, p.occ_n[1] - 1), cz = min((int)fz, p.occ_n[2] - 1);
-        const int d = (int)__ldg(p.dist + ((cz * p.occ_n[1] + cy) * p.occ_n[0] + cx));
+        const int d = (int)__ldg(p.dist + (cz * p.occ_stride[2] + cy * p.occ_stride[1] + cx * p.occ_stride[0]));
         if (d == 0) {
             r.in_empty = false;
             return;
@@ -479,6 +479,17 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         dy = (vy * inv) * p.step_size;
         dz = (vz * inv) * p.step_size;
         posx = e.tex[0], posy = e.tex[1], posz = e.tex[2];
+    }
+    if (PAIR && p.pair_axis != 2) {
+        /* sampling space (u, v, w) with w = the pair axis: (x, z, y) or (y, z, x).  Everything the march
+         * tests or looks up per axis was stored in this order by the host. */
+        float t = posy;
+        posy = posz, posz = t;
+        t = dy, dy = dz, dz = t;
+        if (p.pair_axis == 0) {
+            t = posx, posx = posz, posz = t; /* (x, z, y) -> (y, z, x) */
+            t = dx, dx = dz, dz = t;
+        }
     }
 
     Ray ray;

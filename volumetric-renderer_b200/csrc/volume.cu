@@ -179,18 +179,51 @@ __global__ void __launch_bounds__(256) k_chebyshev_pass(const uint32_t *__restri
     out[c] = (unsigned char)best;
 }
 
-/* Paired layout: texel (x, y) of layer l = (v[x, y, l-1], v[x, y, l]), zero outside the volume (that is
- * the sampler's transparent-black border, offscreen_pass.cpp:1020-1026, on the z axis).  Written
- * through a surface so the block-linear array is filled in place, without a linear staging copy. */
+/* Paired layout along axis `ax`: the 2-D layered array has one layer per position l = 0..n_ax on that
+ * axis and texel (a, b) of layer l = (v[.., ax = l-1, ..], v[.., ax = l, ..]), zero outside the volume
+ * (that is the sampler's transparent-black border, offscreen_pass.cpp:1020-1026, on the pair axis).
+ * In-plane axes (a, b): ax = 2 -> (x, y), ax = 1 -> (x, z), ax = 0 -> (y, z).
+ * Written through a surface so the block-linear array is filled in place, without a staging copy. */
 template <typename T, typename T2>
-__global__ void __launch_bounds__(256) k_pack_pairs(const T *__restrict__ v, int nx, int ny, int nz, cudaSurfaceObject_t surf)
+__global__ void __launch_bounds__(256) k_pack_pairs(const T *__restrict__ v, int nx, int ny, int nz, int ax,
+                                                    cudaSurfaceObject_t surf)
 {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, l = blockIdx.z;
-    if (x >= nx) return;
-    T2 t;
-    t.x = l > 0 ? __ldg(v + ((size_t)(l - 1) * ny + y) * nx + x) : (T)0;
-    t.y = l < nz ? __ldg(v + ((size_t)l * ny + y) * nx + x) : (T)0;
-    surf2DLayeredwrite(t, surf, x * (int)sizeof(T2), y, l);
+    if (ax != 0) {
+        /* a = x: consecutive threads read consecutive voxels */
+        const int x = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y, l = blockIdx.z;
+        if (x >= nx) return;
+        T2 t;
+        if (ax == 2) {
+            t.x = l > 0 ? __ldg(v + ((size_t)(l - 1) * ny + b) * nx + x) : (T)0;
+            t.y = l < nz ? __ldg(v + ((size_t)l * ny + b) * nx + x) : (T)0;
+        } else {
+            t.x = l > 0 ? __ldg(v + ((size_t)b * ny + (l - 1)) * nx + x) : (T)0;
+            t.y = l < ny ? __ldg(v + ((size_t)b * ny + l) * nx + x) : (T)0;
+        }
+        surf2DLayeredwrite(t, surf, x * (int)sizeof(T2), b, l);
+    } else {
+        /* layers along x, a = y: a 32 (y) x 33 (x) tile of one z-slice goes through shared memory so that
+         * both the reads (along x) and the writes (along y) are contiguous */
+        __shared__ T tile[32][34];
+        const int z = blockIdx.z, y0 = blockIdx.y * 32, l0 = blockIdx.x * 32; /* layers l0 .. l0+31 need x = l0-1 .. l0+31 */
+        const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;               /* 32 x 8 threads */
+        for (int r = ty; r < 32; r += 8) {
+            const int y = y0 + r;
+            for (int c = tx; c < 33; c += 32) {
+                const int x = l0 - 1 + c;
+                tile[r][c] = (y < ny && x >= 0 && x < nx) ? __ldg(v + ((size_t)z * ny + y) * nx + x) : (T)0;
+            }
+        }
+        __syncthreads();
+        for (int r = ty; r < 32; r += 8) { /* r: layer within the tile, tx: y within the tile */
+            const int l = l0 + r, y = y0 + tx;
+            if (l <= nx && y < ny) {
+                T2 t;
+                t.x = tile[tx][r], t.y = tile[tx][r + 1];
+                surf2DLayeredwrite(t, surf, y * (int)sizeof(T2), z, l);
+            }
+        }
+    }
 }
 
 /* ------------------------------------------------------------------ synth -- */
@@ -376,22 +409,25 @@ cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned c
     return cudaGetLastError();
 }
 
-cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, cudaArray_t pair_array,
-                             cudaStream_t s)
+cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int axis,
+                             cudaArray_t pair_array, cudaStream_t s)
 {
-    if (dtype != VR_U8 && dtype != VR_U16) return cudaErrorInvalidValue;
-    if (ny > 65535u || nz + 1 > 65535u) return cudaErrorInvalidConfiguration;
+    if ((dtype != VR_U8 && dtype != VR_U16) || axis < 0 || axis > 2) return cudaErrorInvalidValue;
+    if (nx > 65535u * 32u || ny > 65535u || nz > 65535u) return cudaErrorInvalidConfiguration;
     cudaResourceDesc rd = {};
     rd.resType = cudaResourceTypeArray;
     rd.res.array.array = pair_array;
     cudaSurfaceObject_t surf = 0;
     cudaError_t e = cudaCreateSurfaceObject(&surf, &rd);
     if (e != cudaSuccess) return e;
-    const dim3 grid((nx + 255) / 256, ny, nz + 1);
+    /* axis 2: (x blocks, y, layers z); axis 1: (x blocks, z, layers y); axis 0: (layer tiles, y tiles, z) */
+    const dim3 grid = axis == 2   ? dim3((nx + 255) / 256, ny, nz + 1)
+                      : axis == 1 ? dim3((nx + 255) / 256, nz, ny + 1)
+                                  : dim3((nx + 1 + 31) / 32, (ny + 31) / 32, nz);
     if (dtype == VR_U8)
-        k_pack_pairs<unsigned char, uchar2><<<grid, 256, 0, s>>>((const unsigned char *)dev, (int)nx, (int)ny, (int)nz, surf);
+        k_pack_pairs<unsigned char, uchar2><<<grid, 256, 0, s>>>((const unsigned char *)dev, (int)nx, (int)ny, (int)nz, axis, surf);
     else
-        k_pack_pairs<unsigned short, ushort2><<<grid, 256, 0, s>>>((const unsigned short *)dev, (int)nx, (int)ny, (int)nz, surf);
+        k_pack_pairs<unsigned short, ushort2><<<grid, 256, 0, s>>>((const unsigned short *)dev, (int)nx, (int)ny, (int)nz, axis, surf);
     e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     cudaDestroySurfaceObject(surf);

@@ -33,11 +33,17 @@ struct MarchParams {
     /* S4: volume */
     cudaTextureObject_t tex_lin; /* normalised coords, linear, border 0, normalised-float read for u8/u16 */
     cudaTextureObject_t tex_pt;  /* texel coords, point, border 0, element read */
-    /* paired layout: 2-D layered array, layer l holds the texel pair (v[z = l-1], v[z = l]) (zero outside);
-     * normalised x/y, linear, border 0, normalised-float read.  One bilinear fetch + one lerp = one sample. */
+    /* paired layout: 2-D layered array, layer l holds the texel pair (v[w = l-1], v[w = l]) along the pair
+     * axis w (zero outside); normalised in-plane coords, linear, border 0, normalised-float read.  One
+     * bilinear fetch + one lerp = one sample.  The pair axis is chosen per frame (the axis the view
+     * direction is closest to: consecutive samples of a ray then fall into different layers and only
+     * 1/step of the layers is read from HBM).  When it is not z, the march runs in a permuted sampling
+     * space (u, v, w): every per-axis field of this block is stored in that order by the host, and the
+     * kernel permutes the ray's entry position and direction once (pair_axis). */
     cudaTextureObject_t tex_pair;
-    float pair_a[3], pair_b[3]; /* x, y: local normalised coord = q * a + b;  z: local texel coord + MAGIC - 1 = q * a + b */
-    float pair_zc;              /* -0.5 - forg[2]: frac = q_z * dims[2] + (pair_zc - floor) */
+    int pair_axis;              /* model axis of w: 2 (identity), 1: (u,v,w) = (x,z,y), 0: (u,v,w) = (y,z,x) */
+    float pair_a[3], pair_b[3]; /* u, v: local normalised coord = q * a + b;  w: local texel coord + 1.5*2^23 = q * a + b */
+    float pair_zc;              /* 0.5 - forg[w]: frac = q_w * dims[w] + (pair_zc - (floor + 1)) */
     float dims[3];      /* GLOBAL grid size as float */
     int org[3];         /* global voxel index of local texel 0 (0 unless sort-last) */
     float forg[3];      /* same as float */
@@ -57,6 +63,7 @@ struct MarchParams {
     /* empty-space skipping: bit per cell, x fastest */
     const uint32_t *occ;
     int occ_n[3];
+    int occ_stride[3]; /* distance-map index = sum c[a] * occ_stride[a] (sampling-space order) */
     int occ_words;
     float occ_scale[3], occ_off[3]; /* cell = int(pos * occ_scale - occ_off) */
     const unsigned char *dist; /* per cell: Chebyshev distance (cells) to the nearest occupied cell, 0 = occupied */
@@ -108,8 +115,9 @@ struct vr_ctx {
     int layout_req = VR_LAYOUT_AUTO;  /* vr_set_volume_layout: applies to the next upload */
     int layout_used = VR_LAYOUT_AUTO; /* the request the current volume was uploaded under */
     bool last_pair = false;           /* the last frame sampled the paired layout */
-    cudaArray_t pair_array = nullptr; /* paired layout (see MarchParams::tex_pair), resident next to `array` */
-    cudaTextureObject_t tex_pair = 0;
+    cudaArray_t pair_array[3] = {nullptr, nullptr, nullptr}; /* paired layouts along x, y, z (see MarchParams::tex_pair), resident next to `array` */
+    cudaTextureObject_t tex_pair[3] = {0, 0, 0};
+    int last_pair_axis = 2;
 
     /* sort-last */
     bool sort_last = false;
@@ -123,8 +131,9 @@ struct vr_ctx {
     uint4 *d_lut_h = nullptr;
     /* tuning knobs (environment: VR_BATCH, VR_CTA_THREADS, VR_BBOX, VR_WARP_W, VR_CARVEOUT, VR_ESS_MIN_EMPTY) */
     int tune_batch = 2, tune_threads = 128, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
+    int tune_pair_axis = -1;  /* VR_PAIR_AXIS: force the pair axis (experiments); -1 = the axis the camera looks down most */
     int tune_pair_policy = 2; /* VR_PAIR_POLICY: 0 never sample the paired layout, 1 always, 2 per frame (vr_render_frame) */
-    size_t tune_pair_max_bytes = (size_t)8 << 30; /* AUTO layout: pair only if the paired copy fits this (VR_PAIR_MAX_MB) */
+    size_t tune_pair_max_bytes = (size_t)24 << 30; /* AUTO layout: pair only if the paired copy fits this (VR_PAIR_MAX_MB) */
     float tune_ess_min_empty = 0.25f; /* consult the occupancy grid only if at least this share of cells is empty */
 
     /* occupancy */
@@ -158,9 +167,9 @@ cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const flo
                            unsigned long long *d_empty_count, cudaStream_t s);
 cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, unsigned char *d_tmp,
                            cudaStream_t s);
-/* fill the paired layered array (nx, ny, nz + 1 layers) from the linear volume; dtype u8 or u16 */
-cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, cudaArray_t pair_array,
-                             cudaStream_t s);
+/* fill the layered array paired along `axis` (n_axis + 1 layers) from the linear volume; dtype u8 or u16 */
+cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int axis,
+                             cudaArray_t pair_array, cudaStream_t s);
 cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
                         const int org[3], const uint32_t full[3], cudaStream_t s);
 
