@@ -187,6 +187,10 @@ int vr_download_async(vr_ctx *ctx, void *host_rgba8, void *cuda_stream);
  * and alpha = 1 - transmittance, (0,0,0,0) where no fragment.  Needs options.write_raw. */
 int vr_get_raw(vr_ctx *ctx, void **dev_rgba_f32);
 int vr_download_raw(vr_ctx *ctx, float *host_rgba_f32);
+/* The display image as a file: binary PPM (P6, the alpha channel is dropped) or, if `path` ends in
+ * ".pam", PAM with all four channels.  Stands where the reference hands the image to ImGui for display
+ * (src/ui/main_window.cpp:159-165); there is no window on a headless box.  Synchronises. */
+int vr_write_image(vr_ctx *ctx, const char *path);
 int vr_get_stats(vr_ctx *ctx, vr_stats *out);
 int vr_get_size(const vr_ctx *ctx, uint32_t *width, uint32_t *height);
 /* Empty-space-skipping grid: cells per axis, voxels per cell edge, cells whose samples are all
@@ -275,6 +279,23 @@ int vr_partition_order(const uint32_t grid[3], const uint32_t full_dims[3], cons
                        uint32_t *out);
 
 /* ---- measurement ----------------------------------------------------------------------- */
+
+/* ---- stream-ordered frame hand-off between ranks (one process per GPU) --------------------
+ * The reference orders its two frames in flight with per-frame fences (src/rendering/main_pass.cpp:55-57,
+ * :115-117); across GPUs the same ordering is kept by 32-bit counters in device memory, written and
+ * awaited in stream order by one-warp kernels: no host synchronisation and no collective per frame. */
+#define VR_FLAG_COUNT 256
+/* The context's block of VR_FLAG_COUNT zero-initialised uint32 counters (export with vr_ipc_export(ctx, 2, ..)). */
+int vr_get_flags(vr_ctx *ctx, void **dev_u32);
+/* After everything enqueued so far on the stream: store `value` into the n <= 32 counters `flags[i]`
+ * (device pointers, local or peer-mapped), with system-scope release semantics. */
+int vr_stream_signal(vr_ctx *ctx, void *const *flags, uint32_t n, uint32_t value, void *cuda_stream);
+/* Hold the stream until the n <= 256 consecutive LOCAL counters at `flags` have all reached `value`
+ * (counters only grow).  After timeout_ms the wait gives up and the next vr_sync fails with VR_ERR_STATE. */
+int vr_stream_wait(vr_ctx *ctx, const void *flags, uint32_t n, uint32_t value, uint32_t timeout_ms, void *cuda_stream);
+/* vr_set_image_target for any frame in flight; vr_ipc_export accepts which = 16 + frame_index for those
+ * targets (allocated on first use). */
+int vr_set_image_target_frame(vr_ctx *ctx, uint32_t frame_index, void *dev_rgba8);
 
 /* Texture-fetch roofline micro-benchmark: filtered fetches of an L1-resident volume of `dtype` from all
  * SMs; returns fetches per second (device-timed).  hw_filter: 0 = point tex3D, 1 = trilinear tex3D

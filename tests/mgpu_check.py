@@ -55,6 +55,30 @@ def main():
         if not np.array_equal(got, want):
             failures.append(f"sort-first differs in {(got != want).any(axis=-1).sum()} pixels")
     dist.barrier()
+    # pipelined: 9 more frames with a moving camera and no host synchronisation in between; the two
+    # image slots then hold the last two frames, each complete and bit-identical to one GPU
+    cams = []
+    for k in range(9):
+        c = vr.Camera().rotate((-120.0 + 40.0 * k, 80.0 - 10.0 * k))
+        cams.append(c)
+        op.set_camera(c)
+        slot = sf.render()
+    sf.finish()
+    if rank == 0:
+        for k in (7, 8):
+            ref = vr.OffscreenPass(W, H, device=local)
+            ref.synth_volume(vr.SYNTH_FBM, 0x5EED0004, vr.U16, n)
+            ref.transfer_function_changed(lut)
+            ref.set_camera(cams[k])
+            ref.record()
+            w_k = ref.download()
+            ref.close()
+            got = np.empty((H, W, 4), np.uint8)
+            op.download_async(got.ctypes.data, None, (2 + k) % 2)
+            op.sync()
+            if not np.array_equal(got, w_k):
+                failures.append(f"sort-first pipelined frame {k} differs in {(got != w_k).any(axis=-1).sum()} pixels")
+    dist.barrier()
     sf.close()
     op.close()
 
@@ -71,6 +95,9 @@ def main():
         for _ in range(2):
             sl.render(cam.get_position())
             sl.finish()
+        for _ in range(5):  # back to back: ordered by the counters only (p2p) / by the collectives (nccl)
+            sl.render(cam.get_position())
+        sl.finish()
         if rank == 0:
             got = op.download()
             d = np.abs(got.astype(int) - want.astype(int))

@@ -47,6 +47,42 @@ def test_sort_first_ranks_write_into_one_image(vr, port):
     assert np.array_equal(got, want)
 
 
+def test_stream_flags_signal_wait_and_time_out(vr):
+    """vr_stream_signal stores into local or foreign counters in stream order; vr_stream_wait holds a stream
+    until its counters reach the value; a wait nobody answers gives up and makes the next vr_sync fail
+    instead of hanging the GPU.  (Here the counter is raised from the host: two compute streams of ONE
+    process may share a hardware queue, so a signal kernel could sit behind the held stream; between
+    processes -- tests/mgpu_check.py -- the signals come from other GPUs.)"""
+    import torch
+    from volumetric_renderer_b200.multigpu import _DevBuf
+    a, b = vr.OffscreenPass(64, 64), vr.OffscreenPass(64, 64)
+    try:
+        fa = torch.as_tensor(_DevBuf(a.flags(), (256,), "<u4"), device="cuda")
+        fb = torch.as_tensor(_DevBuf(b.flags(), (256,), "<u4"), device="cuda")
+        assert int(fa.sum()) == 0 and int(fb.sum()) == 0
+        b.stream_signal([a.flags() + 4 * 7, b.flags() + 4 * 200], 41)   # one foreign, one own counter
+        b.sync()
+        assert int(fa[7]) == 41 and int(fb[200]) == 41 and int(fa.sum()) == 41
+        sa = torch.cuda.Stream()
+        a.stream_wait(a.flags() + 4 * 5, 2, 3, sa.cuda_stream)          # counters 5 and 6 of `a` must reach 3
+        done = torch.cuda.Event()
+        done.record(sa)
+        fa[5:7] = torch.tensor([3, 2], dtype=fa.dtype, device="cuda")
+        torch.cuda.current_stream().synchronize()
+        assert not done.query()
+        fa[6] = 7                                                       # counters only grow: 7 >= 3
+        sa.synchronize()
+        assert done.query()
+        a.sync()
+        b.stream_wait(b.flags() + 4 * 9, 2, 1, None, timeout_ms=50)
+        with pytest.raises(vr.VrError, match="timed out"):
+            b.sync()
+        b.sync()                                                        # the error is reported once
+    finally:
+        a.close()
+        b.close()
+
+
 def test_multi_process_partitions_on_real_gpus():
     import torch
     n = torch.cuda.device_count()

@@ -211,6 +211,28 @@ def test_auto_layout_is_chosen_per_frame(vr, port):
         assert_within_tolerance(img, o["rgba8"], f"auto {w}x{h}")
 
 
+def test_write_image_round_trips(vr, port, tmp_path):
+    op = vr.OffscreenPass(37, 21)
+    try:
+        op.synth_volume(vr.SYNTH_MARSCHNER_LOBB, 1, vr.U8, 16)
+        op.transfer_function_changed(tf(port, "A"))
+        op.set_camera(vr.Camera().rotate((-120.0, 80.0)))
+        op.record()
+        img = op.download()
+        op.write_image(tmp_path / "f.ppm")
+        op.write_image(tmp_path / "f.pam")
+        with pytest.raises(vr.VrError):
+            op.write_image(tmp_path / "no_such_dir" / "f.ppm")
+    finally:
+        op.close()
+    raw = (tmp_path / "f.ppm").read_bytes()
+    assert raw.startswith(b"P6\n37 21\n255\n")
+    assert np.array_equal(np.frombuffer(raw[len(b"P6\n37 21\n255\n"):], np.uint8).reshape(21, 37, 3), img[..., :3])
+    raw = (tmp_path / "f.pam").read_bytes()
+    body = raw[raw.index(b"ENDHDR\n") + 7:]
+    assert np.array_equal(np.frombuffer(body, np.uint8).reshape(21, 37, 4), img)
+
+
 def test_startup_state_matches_reference_defaults(vr, port):
     """1x1x1 zero volume + one white opaque texel (offscreen_pass.cpp:118-119): every covered pixel
     is white; min == max divides by zero in volume.frag:42 (NaN -> texel 0 by the oracle's definition)."""

@@ -246,6 +246,10 @@ class OffscreenPass:
         self._check(lib.vr_download(self._h, _ptr(out)))
         return out
 
+    def write_image(self, path: str):
+        """The display image as binary PPM (or 4-channel PAM if the name ends in .pam)."""
+        self._check(lib.vr_write_image(self._h, str(path).encode()))
+
     def download_async(self, host_ptr: int, stream: int | None = None, frame_index: int = 0):
         self._check(lib.vr_download_frame_async(self._h, frame_index, host_ptr, stream))
 
@@ -308,8 +312,22 @@ class OffscreenPass:
     def ipc_close(self, ptr: int):
         self._check(lib.vr_ipc_close(self._h, ptr))
 
-    def set_image_target(self, ptr: int | None):
-        self._check(lib.vr_set_image_target(self._h, ptr))
+    def set_image_target(self, ptr: int | None, frame_index: int = 0):
+        self._check(lib.vr_set_image_target_frame(self._h, frame_index, ptr))
+
+    # ---- stream-ordered hand-off between ranks (include/vr.h: vr_stream_signal / vr_stream_wait) ----
+    def flags(self) -> int:
+        """Device pointer of this context's block of 256 uint32 counters (ipc_export(2) shares it)."""
+        p = C.c_void_p()
+        self._check(lib.vr_get_flags(self._h, C.byref(p)))
+        return p.value
+
+    def stream_signal(self, flag_ptrs, value: int, stream: int | None = None):
+        arr = (C.c_void_p * len(flag_ptrs))(*flag_ptrs)
+        self._check(lib.vr_stream_signal(self._h, arr, len(flag_ptrs), value & 0xFFFFFFFF, stream))
+
+    def stream_wait(self, flags_ptr: int, n: int, value: int, stream: int | None = None, timeout_ms: int = 10000):
+        self._check(lib.vr_stream_wait(self._h, flags_ptr, n, value & 0xFFFFFFFF, timeout_ms, stream))
 
 
 def read_nrrd(path: str) -> np.ndarray:

@@ -63,6 +63,7 @@ SIGNATURES = {
     "vr_download_async": (C.c_int, [_P, _P, _P]),
     "vr_get_raw": (C.c_int, [_P, C.POINTER(_P)]),
     "vr_download_raw": (C.c_int, [_P, _P]),
+    "vr_write_image": (C.c_int, [_P, C.c_char_p]),
     "vr_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),
     "vr_get_size": (C.c_int, [_P, _U, _U]),
     "vr_get_occupancy_info": (C.c_int, [_P, _U, _U, C.POINTER(C.c_uint64)]),
@@ -83,6 +84,10 @@ SIGNATURES = {
     "vr_clear_partition": (C.c_int, [_P]),
     "vr_composite": (C.c_int, [_P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _P]),
     "vr_composite_to": (C.c_int, [_P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _P, _P]),
+    "vr_get_flags": (C.c_int, [_P, C.POINTER(_P)]),
+    "vr_stream_signal": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, _P]),
+    "vr_stream_wait": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32, _P]),
+    "vr_set_image_target_frame": (C.c_int, [_P, C.c_uint32, _P]),
     "vr_ipc_export": (C.c_int, [_P, C.c_int, _P]),
     "vr_ipc_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
     "vr_ipc_close": (C.c_int, [_P, _P]),

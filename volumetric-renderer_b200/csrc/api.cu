@@ -355,6 +355,8 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
         if ((e = cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(c, e, "cudaMalloc"); break; }
         if ((e = cudaMallocHost(&c->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(c, e, "cudaMallocHost"); break; }
         std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
+        if ((e = cudaMalloc(&c->d_flags, VR_FLAG_COUNT * sizeof(uint32_t))) != cudaSuccess) { rc = cuda_fail(c, e, "cudaMalloc"); break; }
+        if ((e = cudaMemset(c->d_flags, 0, VR_FLAG_COUNT * sizeof(uint32_t))) != cudaSuccess) { rc = cuda_fail(c, e, "cudaMemset"); break; }
         if ((rc = alloc_target(c, width, height)) != VR_OK) break;
         if ((rc = default_state(c)) != VR_OK) break;
     } while (0);
@@ -382,6 +384,7 @@ extern "C" int vr_destroy(vr_ctx *c)
     for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
         if (c->d_image_slot[k]) cudaFree(c->d_image_slot[k]);
     if (c->d_counters) cudaFree(c->d_counters);
+    if (c->d_flags) cudaFree(c->d_flags);
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->stream) cudaStreamDestroy(c->stream);
     std::free(c->h_lut);
@@ -561,6 +564,14 @@ int prepare_occupancy(vr_ctx *c, cudaStream_t s)
     return VR_OK;
 }
 
+int ensure_slot(vr_ctx *c, uint32_t frame_index)
+{
+    if (frame_index == 0 || c->d_image_slot[frame_index]) return VR_OK;
+    VR_CUDA(c, cudaMalloc(&c->d_image_slot[frame_index], (size_t)c->W * c->H * sizeof(uchar4)));
+    VR_CUDA(c, cudaMemset(c->d_image_slot[frame_index], 0, (size_t)c->W * c->H * sizeof(uchar4)));
+    return VR_OK;
+}
+
 /* Pixels the cube can cover: the projections of its 8 corners bound its silhouette when all of
  * them are in front of the eye; otherwise (camera inside or near the cube) the whole target. */
 void screen_bbox(const vr_ctx *c, uint32_t bbox[4])
@@ -715,11 +726,13 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     }
     uchar4 *target = c->ext_image ? c->ext_image : c->d_image;
     if (frame_index > 0) {
-        if (!c->d_image_slot[frame_index]) {
-            VR_CUDA(c, cudaMalloc(&c->d_image_slot[frame_index], (size_t)c->W * c->H * sizeof(uchar4)));
-            VR_CUDA(c, cudaMemset(c->d_image_slot[frame_index], 0, (size_t)c->W * c->H * sizeof(uchar4)));
+        if (c->ext_image_slot[frame_index]) {
+            target = c->ext_image_slot[frame_index];
+        } else {
+            const int rc = ensure_slot(c, frame_index);
+            if (rc != VR_OK) return rc;
+            target = c->d_image_slot[frame_index];
         }
-        target = c->d_image_slot[frame_index];
     }
     /* Both layouts are resident; which one this frame samples is a cost question (the images agree within
      * the hardware-sampler tolerance either way).  The paired fetch doubles the texture rate but adds
@@ -773,6 +786,11 @@ extern "C" int vr_sync(vr_ctx *c)
     if (!c) return VR_ERR_INVALID;
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaDeviceSynchronize());
+    if (c->h_counters[7]) { /* raised by a vr_stream_wait that gave up (sync.cu) */
+        const unsigned long long which = c->h_counters[7] - 1;
+        c->h_counters[7] = 0;
+        return fail(c, VR_ERR_STATE, "vr_stream_wait timed out waiting for counter " + std::to_string(which) + " of its range");
+    }
     return VR_OK;
 }
 
@@ -829,6 +847,29 @@ extern "C" int vr_download(vr_ctx *c, void *host)
     if (rc != VR_OK) return rc;
     VR_CUDA(c, cudaStreamSynchronize(c->last_stream));
     return VR_OK;
+}
+
+extern "C" int vr_write_image(vr_ctx *c, const char *path)
+{
+    if (!c || !path) return fail(c, VR_ERR_INVALID, "vr_write_image: null argument");
+    std::vector<unsigned char> img((size_t)c->W * c->H * 4);
+    const int rc = vr_download(c, img.data());
+    if (rc != VR_OK) return rc;
+    const size_t len = std::strlen(path);
+    const bool pam = len >= 4 && std::strcmp(path + len - 4, ".pam") == 0;
+    std::FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(c, VR_ERR_IO, std::string("vr_write_image: cannot open ") + path);
+    bool ok;
+    if (pam) {
+        ok = std::fprintf(f, "P7\nWIDTH %u\nHEIGHT %u\nDEPTH 4\nMAXVAL 255\nTUPLTYPE RGB_ALPHA\nENDHDR\n", c->W, c->H) > 0 &&
+             std::fwrite(img.data(), 1, img.size(), f) == img.size();
+    } else {
+        std::vector<unsigned char> rgb((size_t)c->W * c->H * 3);
+        for (size_t i = 0; i < (size_t)c->W * c->H; i++) rgb[3 * i] = img[4 * i], rgb[3 * i + 1] = img[4 * i + 1], rgb[3 * i + 2] = img[4 * i + 2];
+        ok = std::fprintf(f, "P6\n%u %u\n255\n", c->W, c->H) > 0 && std::fwrite(rgb.data(), 1, rgb.size(), f) == rgb.size();
+    }
+    ok = (std::fclose(f) == 0) && ok;
+    return ok ? VR_OK : fail(c, VR_ERR_IO, std::string("vr_write_image: write failed: ") + path);
 }
 
 extern "C" int vr_get_raw(vr_ctx *c, void **dev)
@@ -1053,18 +1094,54 @@ extern "C" void vr_free_host(void *p) { std::free(p); }
 
 /* ============================================== peer memory (one process per GPU) == */
 
-extern "C" int vr_set_image_target(vr_ctx *c, void *dev_rgba8)
+extern "C" int vr_set_image_target(vr_ctx *c, void *dev_rgba8) { return vr_set_image_target_frame(c, 0, dev_rgba8); }
+
+extern "C" int vr_set_image_target_frame(vr_ctx *c, uint32_t frame_index, void *dev_rgba8)
 {
-    if (!c) return VR_ERR_INVALID;
-    c->ext_image = reinterpret_cast<uchar4 *>(dev_rgba8);
+    if (!c || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return fail(c, VR_ERR_INVALID, "vr_set_image_target_frame: bad arguments");
+    if (frame_index == 0) c->ext_image = reinterpret_cast<uchar4 *>(dev_rgba8);
+    else c->ext_image_slot[frame_index] = reinterpret_cast<uchar4 *>(dev_rgba8);
+    return VR_OK;
+}
+
+extern "C" int vr_get_flags(vr_ctx *c, void **dev_u32)
+{
+    if (!c || !dev_u32) return VR_ERR_INVALID;
+    *dev_u32 = c->d_flags;
+    return VR_OK;
+}
+
+extern "C" int vr_stream_signal(vr_ctx *c, void *const *flags, uint32_t n, uint32_t value, void *cuda_stream)
+{
+    if (!c || !flags || n == 0 || n > VR_SIGNAL_MAX) return fail(c, VR_ERR_INVALID, "vr_stream_signal: need 1..32 flags");
+    for (uint32_t i = 0; i < n; i++)
+        if (!flags[i]) return fail(c, VR_ERR_INVALID, "vr_stream_signal: null flag pointer");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+    VR_CUDA(c, vr_launch_signal(flags, (int)n, value, s));
+    return VR_OK;
+}
+
+extern "C" int vr_stream_wait(vr_ctx *c, const void *flags, uint32_t n, uint32_t value, uint32_t timeout_ms, void *cuda_stream)
+{
+    if (!c || !flags || n == 0 || n > 256) return fail(c, VR_ERR_INVALID, "vr_stream_wait: need 1..256 flags");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+    VR_CUDA(c, vr_launch_wait(flags, (int)n, value, timeout_ms ? timeout_ms : 10000u, &c->h_counters[7], s));
     return VR_OK;
 }
 
 extern "C" int vr_ipc_export(vr_ctx *c, int which, unsigned char handle[64])
 {
-    if (!c || !handle || (which != 0 && which != 1)) return fail(c, VR_ERR_INVALID, "vr_ipc_export: bad arguments");
+    const bool frame_slot = which >= 16 && which < 16 + VR_MAX_FRAMES_IN_FLIGHT;
+    if (!c || !handle || (which != 0 && which != 1 && which != 2 && !frame_slot)) return fail(c, VR_ERR_INVALID, "vr_ipc_export: bad arguments");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
-    void *ptr = which == 0 ? (void *)c->d_image : (void *)c->d_raw;
+    if (frame_slot) {
+        const int rc = ensure_slot(c, (uint32_t)(which - 16));
+        if (rc != VR_OK) return rc;
+    }
+    void *ptr = which == 0 ? (void *)c->d_image : (which == 1 ? (void *)c->d_raw : (which == 2 ? (void *)c->d_flags : nullptr));
+    if (frame_slot) ptr = which == 16 ? (void *)c->d_image : (void *)c->d_image_slot[which - 16];
     if (!ptr) return fail(c, VR_ERR_STATE, "vr_ipc_export: that buffer does not exist (options.write_raw?)");
     VR_CUDA(c, cudaSetDevice(c->device));
     cudaIpcMemHandle_t h;

@@ -17,6 +17,7 @@
 #define VR_BATCH 4        /* steps whose fetches are issued back to back before compositing */
 #define VR_OCC_MAX_AXIS 64 /* occupancy grid is at most 64^3 cells = 32 KiB of bits in shared memory */
 #define VR_CLEAR_RGB 0.11f /* offscreen_pass.cpp:171 */
+#define VR_SIGNAL_MAX 32   /* flags one vr_stream_signal writes */
 
 /* Everything K1 needs, passed by value as a __grid_constant__ kernel parameter. */
 struct MarchParams {
@@ -96,6 +97,8 @@ struct vr_ctx {
     uchar4 *d_image_slot[VR_MAX_FRAMES_IN_FLIGHT] = {nullptr, nullptr, nullptr, nullptr}; /* frames 1.. (lazily) */
     float4 *d_raw = nullptr;
     uchar4 *ext_image = nullptr; /* vr_set_image_target: frame 0 is written there instead (peer memory) */
+    uchar4 *ext_image_slot[VR_MAX_FRAMES_IN_FLIGHT] = {nullptr, nullptr, nullptr, nullptr}; /* same for frames 1.. */
+    uint32_t *d_flags = nullptr; /* VR_FLAG_COUNT counters for stream-ordered hand-off between ranks (sync.cu) */
     unsigned long long *d_counters = nullptr;
     unsigned long long *h_counters = nullptr; /* pinned */
 
@@ -172,6 +175,11 @@ cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t n
                              cudaArray_t pair_array, cudaStream_t s);
 cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
                         const int org[3], const uint32_t full[3], cudaStream_t s);
+
+/* stream-ordered flags (sync.cu) */
+cudaError_t vr_launch_signal(void *const *flags, int n, uint32_t value, cudaStream_t s);
+cudaError_t vr_launch_wait(const void *flags, int n, uint32_t value, uint32_t timeout_ms, unsigned long long *error_word,
+                           cudaStream_t s);
 
 /* K2 (composite.cu) */
 cudaError_t vr_launch_composite(const float4 *const *d_parts_table, uint32_t nparts, uint64_t begin, uint64_t end,

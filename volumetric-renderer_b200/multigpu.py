@@ -84,45 +84,110 @@ def _gather_handles(handle: bytes, world: int, group=None):
     return out
 
 
-class SortFirst:
-    """Sort-first image-tile partition (BASELINE.json config 4)."""
+# flag block layout (uint32 index) used by the partitions below; world <= 31
+_F_ARRIVE = 0      # display rank: [slot * 32 + r] = frames rank r has stored into image slot `slot`
+_F_READY = 0       # sort-last, every rank: [r] = frames whose partial rank r has finished
+_F_READ_DONE = 32  # sort-last, every rank: [r] = frames rank r has finished merging (my partial is free again)
+_F_RANGE_DONE = 64 # sort-last, display rank: [r] = frames whose pixel range r is merged into the image
+_F_CONSUMED = 128  # every rank: [slot] = frames presented out of image slot `slot` (the slot is free again)
 
-    def __init__(self, op, rank: int, world: int, tile_px: int = 64, display_rank: int = 0, group=None):
+
+class _PeerFlags:
+    """Every rank's flag block mapped into this process."""
+
+    def __init__(self, op, rank: int, world: int, group=None):
+        self.op, self.rank = op, rank
+        handles = _gather_handles(op.ipc_export(2), world, group)
+        self.base = [op.flags() if r == rank else op.ipc_open(handles[r]) for r in range(world)]
+
+    def ptr(self, r: int, index: int) -> int:
+        return self.base[r] + 4 * index
+
+    def close(self):
+        for r, p in enumerate(self.base):
+            if r != self.rank:
+                self.op.ipc_close(p)
+        self.base = []
+
+
+class SortFirst:
+    """Sort-first image-tile partition (BASELINE.json config 4).
+
+    Frames are handed off in stream order, without a host synchronisation or a collective per frame
+    (include/vr.h: vr_stream_signal / vr_stream_wait): every rank stores its tiles into image slot
+    k % slots of the display rank and then raises its arrival counter there; the display rank, on a
+    second stream, waits for all arrivals of frame k, runs `on_frame(slot, stream)` (e.g. a download)
+    and raises the slot's consumed counter on every rank, which is what a rank waits for before it
+    overwrites that slot with frame k + slots."""
+
+    def __init__(self, op, rank: int, world: int, tile_px: int = 64, display_rank: int = 0, group=None, slots: int = 2,
+                 on_frame=None):
         import torch.distributed as dist
+        assert 1 <= slots <= 4 and world <= 31
         self.op, self.rank, self.world, self.display, self.group = op, rank, world, display_rank, group
+        self.slots, self.on_frame, self._k = slots, on_frame, 0
         op.set_partition_sort_first(rank, world, tile_px)
-        self._peer = None
+        self._peer_imgs, self._flags, self._present = [], None, None
         if world > 1:
-            handles = _gather_handles(op.ipc_export(0), world, group)
-            if rank != display_rank:
-                self._peer = op.ipc_open(handles[display_rank])
-                op.set_image_target(self._peer)
+            for s in range(slots):
+                handles = _gather_handles(op.ipc_export(16 + s) if rank == display_rank else b"", world, group)
+                if rank != display_rank:
+                    p = op.ipc_open(handles[display_rank])
+                    self._peer_imgs.append(p)
+                    op.set_image_target(p, s)
+            self._flags = _PeerFlags(op, rank, world, group)
+            if rank == display_rank:
+                import torch
+                self._present = torch.cuda.Stream()
             dist.barrier(group)
 
-    def render(self, stream: int | None = None):
-        """Record this rank's tiles; they land in the display rank's image."""
-        self.op.record(stream)
+    def render(self, stream: int | None = None) -> int:
+        """Enqueue this rank's tiles of the next frame (and, on the display rank, its presentation).
+        Returns the image slot the frame lands in."""
+        op, k = self.op, self._k
+        s = k % self.slots if self.world > 1 else 0
+        self._k += 1
+        if self.world == 1:
+            op.record(stream)
+            if self.on_frame:
+                self.on_frame(0, stream)
+            return 0
+        f = self._flags
+        if k >= self.slots:
+            op.stream_wait(f.ptr(self.rank, _F_CONSUMED + s), 1, k - self.slots + 1, stream)
+        op.record(stream, s)
+        op.stream_signal([f.ptr(self.display, _F_ARRIVE + s * 32 + self.rank)], k + 1, stream)
+        if self.rank == self.display:
+            ps = self._present.cuda_stream
+            op.stream_wait(f.ptr(self.rank, _F_ARRIVE + s * 32), self.world, k + 1, ps)
+            if self.on_frame:
+                self.on_frame(s, ps)
+            op.stream_signal([f.ptr(r, _F_CONSUMED + s) for r in range(self.world)], k + 1, ps)
+        return s
 
     def finish(self):
-        """All ranks' tiles are in the display rank's image when this returns."""
+        """Every enqueued frame is complete in the display rank's image slots when this returns."""
         import torch.distributed as dist
         self.op.sync()
         if self.world > 1:
             dist.barrier(self.group)
 
     def close(self):
-        if self._peer:
-            self.op.set_image_target(None)
-            self.op.sync()
-            self.op.ipc_close(self._peer)
-            self._peer = None
+        self.op.sync()
+        for s, p in enumerate(self._peer_imgs):
+            self.op.set_image_target(None, s)
+            self.op.ipc_close(p)
+        self._peer_imgs = []
+        if self._flags:
+            self._flags.close()
+            self._flags = None
 
 
 class SortLast:
     """Sort-last sub-box partition with view-ordered direct-send compositing (BASELINE.json config 5)."""
 
     def __init__(self, op, rank: int, world: int, full_dims, grid=None, display_rank: int = 0, mode: str = "p2p",
-                 group=None):
+                 group=None, on_frame=None):
         import torch.distributed as dist
         from . import partition_box
         self.op, self.rank, self.world, self.display, self.mode, self.group = op, rank, world, display_rank, mode, group
@@ -136,11 +201,17 @@ class SortLast:
         self.npix = w * h
         self.ranges = pixel_ranges(self.npix, world)
         self._peers_raw, self._peer_img = None, None
+        self._flags, self._present, self._k, self.on_frame = None, None, 0, on_frame
+        assert world <= 31
         if world > 1 and mode == "p2p":
             raws = _gather_handles(op.ipc_export(1), world, group)
             imgs = _gather_handles(op.ipc_export(0), world, group)
             self._peers_raw = [op.get_raw() if r == rank else op.ipc_open(raws[r]) for r in range(world)]
             self._peer_img = None if rank == display_rank else op.ipc_open(imgs[display_rank])
+            self._flags = _PeerFlags(op, rank, world, group)
+            if rank == display_rank:
+                import torch
+                self._present = torch.cuda.Stream()
             dist.barrier(group)
 
     def set_global_density_range(self):
@@ -162,18 +233,43 @@ class SortLast:
         import torch.distributed as dist
         from . import partition_order
         op, rank, world = self.op, self.rank, self.world
-        op.record(stream)
         order = [int(b) for b in partition_order(self.grid, self.full, camera_position)]
         b, e = self.ranges[rank]
         if world == 1:
+            op.record(stream)
             op.composite([op.get_raw()], 0, self.npix, stream)
+            if self.on_frame:
+                self.on_frame(0, stream)
             return
-        op.sync()
-        dist.barrier(self.group)  # every partial is complete before anyone reads it
         if self.mode == "p2p":
+            # Stream-ordered hand-off (include/vr.h: vr_stream_signal / vr_stream_wait): no host
+            # synchronisation and no collective per frame.  Frame k (counters hold k + 1 when done):
+            f, k, disp = self._flags, self._k, self.display
+            self._k += 1
+            if k >= 1:
+                op.stream_wait(f.ptr(rank, _F_READ_DONE), world, k, stream)   # everyone has merged my partial of frame k-1
+                if rank == disp:
+                    op.stream_wait(f.ptr(rank, _F_CONSUMED), 1, k, stream)    # K1 also stores into the image being presented
+            op.record(stream)
+            op.stream_signal([f.ptr(r, _F_READY + rank) for r in range(world)], k + 1, stream)
+            op.stream_wait(f.ptr(rank, _F_READY), world, k + 1, stream)        # every partial of frame k is complete
+            if k >= 1 and rank != disp:
+                op.stream_wait(f.ptr(rank, _F_CONSUMED), 1, k, stream)        # frame k-1 has left the display image
             if e > b:
                 op.composite([self._peers_raw[r] for r in order], b, e, stream, out_ptr=self._peer_img)
-        else:
+            op.stream_signal([f.ptr(r, _F_READ_DONE + rank) for r in range(world)] + [f.ptr(disp, _F_RANGE_DONE + rank)],
+                             k + 1, stream)
+            if rank == disp:
+                ps = self._present.cuda_stream
+                op.stream_wait(f.ptr(rank, _F_RANGE_DONE), world, k + 1, ps)  # the frame is complete in the image
+                if self.on_frame:
+                    self.on_frame(0, ps)
+                op.stream_signal([f.ptr(r, _F_CONSUMED) for r in range(world)], k + 1, ps)
+            return
+        op.record(stream)
+        op.sync()
+        dist.barrier(self.group)  # every partial is complete before anyone reads it
+        if True:
             raw = torch.as_tensor(_DevBuf(op.get_raw(), (self.npix, 4), "<f4"), device="cuda")
             recv = exchange_ranges(raw, self.ranges, rank, world, self.group)
             torch.cuda.current_stream().synchronize()  # the merge runs on the context's stream
@@ -211,3 +307,6 @@ class SortLast:
             if self._peer_img:
                 self.op.ipc_close(self._peer_img)
             self._peers_raw, self._peer_img = None, None
+        if self._flags:
+            self._flags.close()
+            self._flags = None
