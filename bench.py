@@ -484,9 +484,13 @@ def run_partitioned(args):
         except Exception:
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
-        # every rank streams its (sub-)volume once per frame: c4 its tiles' share of the replicated volume
-        alg = (n ** 3 * 2 / (1 if c4 else world)) + W * H * (4 if c4 else 20) / world
+        # algorithmic bytes per GPU and frame.  c4: the 1/N of the replicated volume its tiles' rays cross, once,
+        # + its share of the RGBA8 image.  c5: its sub-box once, but never more than the 8 texels (16 B) each of
+        # its executed samples needs (at 4096^3 the rays are 2.7 voxels and the steps 20 voxels apart: most
+        # voxels are never touched) + its float4 partial and its share of the merge.
         step_s = dt / K
+        exec_per_gpu = counts[1].item() / K / world
+        alg = (n ** 3 * 2 / world if c4 else min(n ** 3 * 2 / world, exec_per_gpu * 16)) + W * H * (4 if c4 else 20) / world
         print(json.dumps({
             "metric": f"ray samples/s ({args.workload})", "value": counts[0].item() / dt, "unit": "samples/s",
             "n_gpus": world, "steps": K, "warmup": Wu, "ms_per_step": step_s * 1e3, "fps": K / dt,
