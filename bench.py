@@ -484,13 +484,13 @@ def run_partitioned(args):
         except Exception:
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
-        # algorithmic bytes per GPU and frame.  c4: the 1/N of the replicated volume its tiles' rays cross, once,
-        # + its share of the RGBA8 image.  c5: its sub-box once, but never more than the 8 texels (16 B) each of
-        # its executed samples needs (at 4096^3 the rays are 2.7 voxels and the steps 20 voxels apart: most
-        # voxels are never touched) + its float4 partial and its share of the merge.
+        # algorithmic bytes per GPU and frame: its share of the volume once (c4: the 1/N of the replicated volume
+        # its tiles' rays cross; c5: its sub-box), but never more than the 8 texels (16 B) each of its executed
+        # samples needs (steps are 10 voxels apart at 2048^3 and 20 at 4096^3: most voxels are never touched),
+        # + its share of the RGBA8 image (c4) or its float4 partial and its share of the merge (c5).
         step_s = dt / K
         exec_per_gpu = counts[1].item() / K / world
-        alg = (n ** 3 * 2 / world if c4 else min(n ** 3 * 2 / world, exec_per_gpu * 16)) + W * H * (4 if c4 else 20) / world
+        alg = min(n ** 3 * 2 / world, exec_per_gpu * 16) + W * H * (4 if c4 else 20) / world
         print(json.dumps({
             "metric": f"ray samples/s ({args.workload})", "value": counts[0].item() / dt, "unit": "samples/s",
             "n_gpus": world, "steps": K, "warmup": Wu, "ms_per_step": step_s * 1e3, "fps": K / dt,

@@ -159,11 +159,14 @@ def test_layouts_agree_and_paired_needs_integer_texels(vr, port):
         op.close()
 
 
-@pytest.mark.parametrize("moves,axis", [([], 1), ([(360, 0)], 0), ([(40, 320)], 2), ([(-300, -60)], 0)])
+@pytest.mark.parametrize("moves", [[], [(360, 0)], [(40, 320)], [(-300, -60)]])
+@pytest.mark.parametrize("axis", [0, 1, 2])
 @pytest.mark.parametrize("ess", [0, 1])
-def test_pair_axis_follows_the_camera(vr, port, moves, axis, ess):
-    """The pairs run along the axis the camera looks down most; the march then works in a permuted
-    sampling space (slices, occupancy grid and bounds follow).  Non-cubic volume, asymmetric slices."""
+def test_every_pair_axis_with_every_camera(vr, port, moves, axis, ess, monkeypatch):
+    """Pairs along x, y or z: the march works in a permuted sampling space (slices, occupancy grid and
+    bounds follow).  Non-cubic volume, asymmetric slices; the axis is forced (VR_PAIR_AXIS is read when
+    the context is created), the policy is tested below."""
+    monkeypatch.setenv("VR_PAIR_AXIS", str(axis))
     vol = port.synth(2 if ess else 1, 0x5EED0042, np.uint16, (56, 24, 40))  # (nx, ny, nz)
     lut = tf(port, "C" if ess else "B")
     cam, ocam = twin_cameras(vr, port, moves, 0.0)
@@ -186,6 +189,40 @@ def test_pair_axis_follows_the_camera(vr, port, moves, axis, ess):
     assert st.covered_pixels == o["stats"].covered_pixels
     assert st.n_ref == o["stats"].n_ref and st.n_inslice == o["stats"].n_inslice
     assert_within_tolerance(img, o["rgba8"], f"pair axis {axis}")
+
+
+@pytest.mark.parametrize("split", [25, 30])
+def test_pair_copies_split_over_two_layered_arrays(vr, port, split, monkeypatch):
+    """Axes longer than 2047 voxels need two layered arrays per copy (2048-layer limit); VR_PAIR_SPLIT forces
+    the split on a small volume.  The frames must not change by a bit."""
+    vol = small_volume(port, 1, np.uint16, 48)
+    lut = tf(port, "B")
+    frames = {}
+    for s in (2048, split):
+        monkeypatch.setenv("VR_PAIR_SPLIT", str(s))
+        for moves in ([], [(360, 0)], [(40, 320)]):
+            frames[(s, str(moves))] = render_both(vr, port, vol, lut, moves, sampler=vr.SAMPLER_HW, layout=vr.LAYOUT_PAIRED)[1]
+    for moves in ([], [(360, 0)], [(40, 320)]):
+        assert np.array_equal(bits(frames[(2048, str(moves))]), bits(frames[(split, str(moves))])), moves
+
+
+def test_pair_axis_policy_prefers_the_axis_the_camera_looks_down(vr, port):
+    """vr_render_frame's cost estimate: for a view along a volume axis the pairs run along that axis (one
+    layer per warp fetch, fewest layers read)."""
+    vol = small_volume(port, 1, np.uint16, 64)
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_volume_layout(vr.LAYOUT_PAIRED)
+        op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+        op.transfer_function_changed(tf(port, "B"))
+        for moves, axis in (([], 1), ([(360, 0)], 0), ([(0, 350)], 2)):
+            cam, _ = twin_cameras(vr, port, moves, 0.0)
+            op.set_camera(cam)
+            op.record()
+            op.sync()
+            assert op.last_frame_pair_axis() == axis, moves
+    finally:
+        op.close()
 
 
 def test_auto_layout_is_chosen_per_frame(vr, port):

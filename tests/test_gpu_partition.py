@@ -15,8 +15,10 @@ pytestmark = pytest.mark.gpu
 W, H = 200, 136  # not a multiple of the tile size on purpose
 
 
-def setup_pass(vr, w, h, lut, cam, **opts):
+def setup_pass(vr, w, h, lut, cam, layout=None, **opts):
     op = vr.OffscreenPass(w, h)
+    if layout is not None:
+        op.set_volume_layout(layout)
     op.set_options(write_raw=1, collect_stats=1, **opts)
     op.transfer_function_changed(lut)
     op.set_camera(cam)
@@ -55,7 +57,7 @@ def test_sort_first_tiles_reassemble(vr, port, nranks):
 
 
 @pytest.mark.parametrize("grid", [(2, 1, 1), (2, 2, 1), (2, 2, 2), (3, 2, 1)])
-@pytest.mark.parametrize("sampler", ["exact", "hw"])
+@pytest.mark.parametrize("sampler", ["exact", "hw", "hw-pairs"])
 def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, sampler):
     import torch  # device memory plumbing only
 
@@ -64,7 +66,8 @@ def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, sampler)
     moves = [(-120, 80)]
     cam, ocam = twin_cameras(vr, port, moves)
     smp = vr.SAMPLER_EXACT if sampler == "exact" else vr.SAMPLER_HW
-    single = setup_pass(vr, W, H, lut, cam, sampler=smp)
+    lay = vr.LAYOUT_PAIRED if sampler == "hw-pairs" else vr.LAYOUT_ARRAY3D   # pairs: every rank's sub-box in the paired layout
+    single = setup_pass(vr, W, H, lut, cam, layout=lay, sampler=smp)
     single.synth_volume(vr.SYNTH_FBM, 0x5EED0005, vr.U16, n)
     _, _, mn, mx = single.volume_info()
     single.record()
@@ -74,12 +77,13 @@ def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, sampler)
     parts, passes, n_inslice = [], [], 0
     for b in range(nbox):
         org, dims = vr.partition_box(grid, (n, n, n), b)
-        op = setup_pass(vr, W, H, lut, cam, sampler=smp)
+        op = setup_pass(vr, W, H, lut, cam, layout=lay, sampler=smp)
         op.set_partition_sort_last((n, n, n), org, dims)
         op.synth_subvolume(vr.SYNTH_FBM, 0x5EED0005, vr.U16)
         op.set_density_range(mn, mx)
         op.record()
         op.sync()
+        assert op.last_frame_paired() == (sampler == "hw-pairs")
         n_inslice += op.stats().n_inslice
         parts.append(op.get_raw())
         passes.append(op)

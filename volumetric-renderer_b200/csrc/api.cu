@@ -158,7 +158,10 @@ void release_volume(vr_ctx *c)
     if (c->tex_pt) cudaDestroyTextureObject(c->tex_pt), c->tex_pt = 0;
     for (int a = 0; a < 3; a++) {
         if (c->tex_pair[a]) cudaDestroyTextureObject(c->tex_pair[a]), c->tex_pair[a] = 0;
+        if (c->tex_pair_hi[a]) cudaDestroyTextureObject(c->tex_pair_hi[a]), c->tex_pair_hi[a] = 0;
         if (c->pair_array[a]) cudaFreeArray(c->pair_array[a]), c->pair_array[a] = nullptr;
+        if (c->pair_array_hi[a]) cudaFreeArray(c->pair_array_hi[a]), c->pair_array_hi[a] = nullptr;
+        c->pair_split[a] = 0x10000;
     }
     if (c->array) cudaFreeArray(c->array), c->array = nullptr;
     if (c->d_cell_range) cudaFree(c->d_cell_range), c->d_cell_range = nullptr;
@@ -218,33 +221,50 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
     tp.normalizedCoords = 0;
     VR_CUDA(c, cudaCreateTextureObject(&c->tex_pt, &rd, &tp, nullptr));
 
-    /* second layout for the hardware sampler (vr_layout): pairs along each axis in 2-D layered arrays */
+    /* second layout for the hardware sampler (vr_layout): pairs along each axis in 2-D layered arrays;
+     * a layered array holds at most 2048 layers, so an axis longer than 2047 voxels is split over two */
     const uint32_t nd[3] = {nx, ny, nz};
+    const int split = std::min(std::max(c->tune_pair_split, 2), 2048);
     bool can_pair = dtype == VR_U8 || dtype == VR_U16;
     size_t pair_bytes = 0;
     for (int a = 0; a < 3; a++) {
-        can_pair = can_pair && nd[a] + 1 <= 2048 && nd[a] <= 32768;
+        can_pair = can_pair && nd[a] + 1 <= 2u * (uint32_t)split && nd[a] <= 32768;
         pair_bytes += (size_t)nx * ny * nz / nd[a] * ((size_t)nd[a] + 1) * 2 * dtype_size(dtype);
     }
     if (c->layout_req == VR_LAYOUT_PAIRED && !can_pair)
-        return fail(c, VR_ERR_INVALID, "VR_LAYOUT_PAIRED needs a u8/u16 volume of at most 2047 voxels per axis");
-    if (c->layout_req == VR_LAYOUT_PAIRED || (c->layout_req == VR_LAYOUT_AUTO && can_pair && pair_bytes <= c->tune_pair_max_bytes)) {
+        return fail(c, VR_ERR_INVALID, "VR_LAYOUT_PAIRED needs a u8/u16 volume of at most 4095 voxels per axis");
+    bool want_pairs = c->layout_req == VR_LAYOUT_PAIRED;
+    if (c->layout_req == VR_LAYOUT_AUTO && can_pair && pair_bytes <= c->tune_pair_max_bytes) {
+        size_t free_b = 0, total_b = 0;
+        VR_CUDA(c, cudaMemGetInfo(&free_b, &total_b));
+        want_pairs = pair_bytes + ((size_t)6 << 30) <= free_b; /* leave room for targets, partials and the caller */
+    }
+    if (want_pairs) {
         cudaChannelFormatDesc cd2 = dtype == VR_U8 ? cudaCreateChannelDesc<uchar2>() : cudaCreateChannelDesc<ushort2>();
         for (int a = 0; a < 3; a++) {
             /* in-plane extent (u, v), layers along a: a = 2 -> (x, y), a = 1 -> (x, z), a = 0 -> (y, z) */
             const uint32_t eu = a == 0 ? ny : nx, ev = a == 2 ? ny : nz;
-            VR_CUDA(c, cudaMalloc3DArray(&c->pair_array[a], &cd2, make_cudaExtent(eu, ev, (size_t)nd[a] + 1),
-                                         cudaArrayLayered | cudaArraySurfaceLoadStore));
-            VR_CUDA(c, vr_k0_pack_pairs(dev, dtype, nx, ny, nz, a, c->pair_array[a], c->stream));
-            cudaResourceDesc rp = {};
-            rp.resType = cudaResourceTypeArray;
-            rp.res.array.array = c->pair_array[a];
-            cudaTextureDesc tq = {};
-            tq.addressMode[0] = tq.addressMode[1] = tq.addressMode[2] = cudaAddressModeBorder;
-            tq.filterMode = cudaFilterModeLinear;
-            tq.readMode = cudaReadModeNormalizedFloat;
-            tq.normalizedCoords = 1;
-            VR_CUDA(c, cudaCreateTextureObject(&c->tex_pair[a], &rp, &tq, nullptr));
+            const uint32_t layers = nd[a] + 1, lo = std::min(layers, (uint32_t)split), hi = layers - lo;
+            c->pair_split[a] = hi ? (int)lo : 0x10000;
+            cudaArray_t *arrs[2] = {&c->pair_array[a], &c->pair_array_hi[a]};
+            cudaTextureObject_t *texs[2] = {&c->tex_pair[a], &c->tex_pair_hi[a]};
+            const uint32_t cnt[2] = {lo, hi};
+            for (int k = 0; k < 2; k++)
+                if (cnt[k])
+                    VR_CUDA(c, cudaMalloc3DArray(arrs[k], &cd2, make_cudaExtent(eu, ev, cnt[k]), cudaArrayLayered | cudaArraySurfaceLoadStore));
+            VR_CUDA(c, vr_k0_pack_pairs(dev, dtype, nx, ny, nz, a, c->pair_array[a], c->pair_array_hi[a], c->pair_split[a], c->stream));
+            for (int k = 0; k < 2; k++) {
+                if (!cnt[k]) continue;
+                cudaResourceDesc rp = {};
+                rp.resType = cudaResourceTypeArray;
+                rp.res.array.array = *arrs[k];
+                cudaTextureDesc tq = {};
+                tq.addressMode[0] = tq.addressMode[1] = tq.addressMode[2] = cudaAddressModeBorder;
+                tq.filterMode = cudaFilterModeLinear;
+                tq.readMode = cudaReadModeNormalizedFloat;
+                tq.normalizedCoords = 1;
+                VR_CUDA(c, cudaCreateTextureObject(texs[k], &rp, &tq, nullptr));
+            }
         }
     }
 
@@ -345,6 +365,7 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     if (const char *e = std::getenv("VR_CARVEOUT")) c->tune_carveout = std::atoi(e);
     if (const char *e = std::getenv("VR_LAYOUT")) c->layout_req = std::atoi(e) == 1 ? VR_LAYOUT_ARRAY3D : (std::atoi(e) == 2 ? VR_LAYOUT_PAIRED : VR_LAYOUT_AUTO);
     if (const char *e = std::getenv("VR_PAIR_POLICY")) c->tune_pair_policy = std::atoi(e);
+    if (const char *e = std::getenv("VR_PAIR_SPLIT")) c->tune_pair_split = std::atoi(e);
     if (const char *e = std::getenv("VR_PAIR_AXIS")) c->tune_pair_axis = std::atoi(e) >= 0 && std::atoi(e) <= 2 ? std::atoi(e) : -1;
     if (const char *e = std::getenv("VR_PAIR_MAX_MB")) c->tune_pair_max_bytes = (size_t)std::atoll(e) << 20;
     if (const char *e = std::getenv("VR_L2_GRAN")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(e));
@@ -647,13 +668,15 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
     p.lut_pad = c->d_lut_pad, p.lut_dif = c->d_lut_dif, p.lut_h = c->d_lut_h, p.nlut = c->nlut;
     p.occ_stride[0] = 1, p.occ_stride[1] = c->occ_n[0], p.occ_stride[2] = c->occ_n[0] * c->occ_n[1];
     p.pair_axis = 2;
-    p.tex_pair = 0;
+    p.tex_pair = 0, p.tex_pair_hi = 0, p.pair_split = 0x10000;
     if (pair_axis >= 0) {
         /* sampling space (u, v, w) = model axes perm[0..2], w = the pair axis: every per-axis field is
          * stored in that order; the kernel permutes the ray once (march.cu) */
         const int perm[3] = {pair_axis == 0 ? 1 : 0, pair_axis == 2 ? 1 : 2, pair_axis};
         p.pair_axis = pair_axis;
         p.tex_pair = c->tex_pair[pair_axis];
+        p.tex_pair_hi = c->tex_pair_hi[pair_axis] ? c->tex_pair_hi[pair_axis] : c->tex_pair[pair_axis];
+        p.pair_split = c->pair_split[pair_axis];
         permute3(p.min_slice, perm), permute3(p.max_slice, perm);
         permute3(p.dims, perm), permute3(p.org, perm), permute3(p.forg, perm), permute3(p.inv_ldims, perm);
         permute3(p.own_lo, perm), permute3(p.own_hi, perm), permute3(p.box_lo, perm), permute3(p.box_hi, perm);
@@ -735,40 +758,54 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
         }
     }
     /* Both layouts are resident; which one this frame samples is a cost question (the images agree within
-     * the hardware-sampler tolerance either way).  The paired fetch doubles the texture rate but adds
-     * dependent ALU work per step: it pays when the frame is throughput-bound, i.e. the cube's screen
-     * bounding box fills the GPU with at least one wave of CTAs and the occupancy grid is not consulted.
-     * Small frames are latency-bound and sparse volumes are bound by the skipping.
-     * The pair axis w is the one that keeps a warp's fetch in the fewest layers: a warp is ww x wh
-     * neighbouring pixels, so with r, s the model-space directions of screen x and y (columns 0 and 1 of
-     * inverse(proj * view)) one fetch instruction spans about 1 + ww |r_w| + wh |s_w| layers.  That is
-     * minimal for the axis the camera looks down (then consecutive samples of a ray also fall into
-     * different layers and only every step-th layer is read from HBM); for a view between two axes it
-     * is the third axis.  Measured (profiles/r1_exp_axis.txt): the wrong axis costs up to 2x. */
+     * the hardware-sampler tolerance either way).  Small frames (the cube's screen bounding box holds less
+     * than one wave of CTAs) are latency-bound and sparse volumes are bound by the skipping: both measured
+     * faster on the 3-D array.  Otherwise a two-term estimate per candidate, calibrated on
+     * profiles/r1_exp_axis.txt / r1_exp_stream_layouts.txt (the DRAM term is only partly hidden):
+     *   t = max(tex, dram) + 0.3 min(tex, dram)
+     *   3-D array:      tex = S / 3.6e11,              dram = V / 5e12
+     *   pairs along w:  tex = S / 5.7e11 * pen(L_w),   dram = 2 V f_w / 5e12
+     * S = samples of the frame (0.37 * bounding-box pixels * steps), V = bytes of the volume (this rank's share),
+     * L_w = layers one warp fetch spans = 1 + pitch (ww |r_w| + wh |s_w|) with r, s the model-space directions
+     * of screen x, y (columns 0, 1 of inverse(proj * view)) and pitch the voxels per pixel,
+     * pen(L) = 1 + 0.2 max(0, L - 4.5), and f_w = min(1, 1 / (step in voxels along w)) the share of the layers
+     * a ray touches: looking down w, consecutive samples fall into different layers and only every
+     * step-th layer is read from HBM. */
     bool pair = !exact && c->tex_pair[2] != 0;
     int pair_axis = 2;
-    if (pair && c->tune_pair_axis < 0) {
-        const float *r = c->rc[0], *u = c->rc[1];
-        const double rn = std::sqrt((double)r[0] * r[0] + (double)r[1] * r[1] + (double)r[2] * r[2]);
-        const double un = std::sqrt((double)u[0] * u[0] + (double)u[1] * u[1] + (double)u[2] * u[2]);
-        const double ww = (double)c->tune_warp_w, wh = 32.0 / ww;
-        double best = 1e30;
-        for (int a = 2; a >= 0; a--) { /* ties go to z, then y */
-            const double layers = 1.0 + (rn > 0 ? ww * std::fabs(r[a]) / rn : 0.0) + (un > 0 ? wh * std::fabs(u[a]) / un : 0.0);
-            if (layers < best - 1e-9) best = layers, pair_axis = a;
-        }
-    } else if (pair) {
-        pair_axis = c->tune_pair_axis;
-    }
     const int policy = c->layout_used == VR_LAYOUT_PAIRED ? 1 : c->tune_pair_policy; /* asked for by name: always */
     if (pair && policy == 0) pair = false;
     MarchParams p;
     fill_params(c, p, -1);
-    if (pair && policy == 2) {
+    if (pair) {
+        const int64_t bw = std::max<int64_t>((int64_t)p.bbox[2] - (int64_t)p.bbox[0], 0), bh = std::max<int64_t>((int64_t)p.bbox[3] - (int64_t)p.bbox[1], 0);
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
-        const int64_t bw = (int64_t)p.bbox[2] - (int64_t)p.bbox[0], bh = (int64_t)p.bbox[3] - (int64_t)p.bbox[1];
-        pair = !ess && bw > 0 && bh > 0 && bw * bh >= (int64_t)sms * 10 * 128;
+        const uint32_t nd[3] = {c->nx, c->ny, c->nz};
+        double share = 1.0 / (double)std::max(1u, c->pt_nranks); /* this rank's part of the frame's work */
+        if (c->sort_last) share *= ((double)c->own_dims[0] * c->own_dims[1] * c->own_dims[2]) / ((double)c->full[0] * c->full[1] * c->full[2]);
+        const double S = 0.37 * (double)(bw * bh) * (double)p.steps * share;
+        const double V = (double)nd[0] * nd[1] * nd[2] * (double)dtype_size(c->dtype) / (double)std::max(1u, c->pt_nranks);
+        auto combine = [](double a, double b) { return std::max(a, b) + 0.3 * std::min(a, b); };
+        const double t3d = combine(S / 3.6e11, V / 5.0e12);
+        const float *r = c->rc[0], *u = c->rc[1];
+        const double rn = std::sqrt((double)r[0] * r[0] + (double)r[1] * r[1] + (double)r[2] * r[2]);
+        const double un = std::sqrt((double)u[0] * u[0] + (double)u[1] * u[1] + (double)u[2] * u[2]);
+        const double dn = std::sqrt((double)c->cam_pos[0] * c->cam_pos[0] + (double)c->cam_pos[1] * c->cam_pos[1] + (double)c->cam_pos[2] * c->cam_pos[2]);
+        const double ww = (double)c->tune_warp_w, wh = 32.0 / ww;
+        double best = 1e30;
+        for (int a = 2; a >= 0; a--) { /* ties go to z, then y */
+            const double full_a = c->sort_last ? (double)c->full[a] : (double)nd[a];
+            const double pitch = 1.2 * full_a / (double)std::max<int64_t>(std::max(bw, bh), 1); /* voxels per pixel along a */
+            const double L = 1.0 + pitch * ((rn > 0 ? ww * std::fabs(r[a]) / rn : 0.0) + (un > 0 ? wh * std::fabs(u[a]) / un : 0.0));
+            const double step_vox = (double)c->step_size * full_a * (dn > 0 ? std::fabs(c->cam_pos[a]) / dn : 0.0);
+            const double f = step_vox > 1.0 ? 1.0 / step_vox : 1.0;
+            const double t = combine(S / 5.7e11 * (1.0 + 0.2 * std::max(0.0, L - 4.5)), 2.0 * V * f / 5.0e12) *
+                             (1.0 + 1e-6 * L); /* equal cost: the axis with fewer layers per fetch */
+            if (t < best - 1e-12) best = t, pair_axis = a;
+        }
+        if (c->tune_pair_axis >= 0) pair_axis = c->tune_pair_axis;
+        if (policy == 2) pair = !ess && bw * bh >= (int64_t)sms * 10 * 128 && best < t3d;
     }
     if (pair) fill_params(c, p, pair_axis);
     c->last_pair = pair, c->last_pair_axis = pair_axis;

@@ -139,15 +139,18 @@ __device__ __forceinline__ int cell_distance(const MarchParams &p, float x, floa
  * - 0.5, is fl + 1 = round(w + 0.5), read from the mantissa of q_z * a + b (b carries 1.5*2^23; at a tie
  * either neighbour gives the same value because the z weight is then 0 or 1).  Returns the pair, and the
  * z weight w - fl evaluated with a single rounding. */
-template <bool PART>
+template <bool PART, bool SPLIT>
 __device__ __forceinline__ float2 fetch_pair(const MarchParams &p, float qx, float qy, float qz, float &frac)
 {
     const float tm = fmaf(qz, p.pair_a[2], p.pair_b[2]);
     const float fl1 = tm - VR_MAGIC;                        /* fl + 1 */
-    const int layer = (int)(__float_as_uint(tm) & 0xffffu); /* 0 .. nz (nz <= 2047) */
+    const int layer = (int)(__float_as_uint(tm) & 0xffffu); /* 0 .. n_w (n_w <= 4095) */
     frac = fmaf(qz, p.pair_a[2], p.pair_zc - fl1);
-    return PART ? tex2DLayered<float2>(p.tex_pair, fmaf(qx, p.pair_a[0], p.pair_b[0]), fmaf(qy, p.pair_a[1], p.pair_b[1]), layer)
-                : tex2DLayered<float2>(p.tex_pair, qx, qy, layer);
+    const float u = PART ? fmaf(qx, p.pair_a[0], p.pair_b[0]) : qx, v = PART ? fmaf(qy, p.pair_a[1], p.pair_b[1]) : qy;
+    /* axes longer than 2047 voxels: the layers from pair_split on live in a second array */
+    if (!SPLIT) return tex2DLayered<float2>(p.tex_pair, u, v, layer);
+    return layer < p.pair_split ? tex2DLayered<float2>(p.tex_pair, u, v, layer)
+                                : tex2DLayered<float2>(p.tex_pair_hi, u, v, layer - p.pair_split);
 }
 
 /* Hardware-sampler transfer function.  Table entry k (shared memory, 16 bytes = eight fp16) holds
@@ -274,7 +277,7 @@ struct Batch {
 
 /* First half: positions (volume.frag:33-40,:47), then all U fetches back to back (:41).
  * CHECK = evaluate the per-step tests; otherwise every step of a live ray is sampled. */
-template <bool EXACT, bool ESS, bool STATS, bool PART, bool PAIR, int U, bool CHECK, bool PRED>
+template <bool EXACT, bool ESS, bool STATS, bool PART, int PAIR, int U, bool CHECK, bool PRED>
 __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<U> &b)
 {
     float qx[U], qy[U], qz[U];
@@ -322,7 +325,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
             if (EXACT) {
                 b.val[u] = sample_exact(p, qx[u], qy[u], qz[u]);
             } else if (PAIR) {
-                const float2 t = fetch_pair<PART>(p, qx[u], qy[u], qz[u], b.frac[u]);
+                const float2 t = fetch_pair<PART, PAIR == 2>(p, qx[u], qy[u], qz[u], b.frac[u]);
                 b.val[u] = t.x, b.val2[u] = t.y;
             } else if (PART) {
                 b.val[u] = tex3D<float>(p.tex_lin, (qx[u] * p.dims[0] - p.forg[0]) * p.inv_ldims[0],
@@ -337,7 +340,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
 }
 
 /* Second half: normalise, transfer function, composite (volume.frag:42-45). */
-template <bool EXACT, bool STATS, bool PAIR, int U, bool PRED, bool ERT = true>
+template <bool EXACT, bool STATS, int PAIR, int U, bool PRED, bool ERT = true>
 __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batch<U> &b, const float4 *sP,
                                               const LutH &L)
 {
@@ -382,8 +385,9 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
 }
 
 /* EXACT: verification sampler.  ESS: occupancy grid consulted.  STATS: sample counters.
- * PART: sort-last sub-volume.  UB: steps per batch (HW sampler; two batches are in flight). */
-template <bool EXACT, bool ESS, bool STATS, bool PART, bool PAIR, int UB>
+ * PART: sort-last sub-volume.  PAIR: 0 = 3-D array, 1 = paired layout, 2 = paired layout whose copy spans
+ * two layered arrays.  UB: steps per batch (HW sampler; two batches are in flight). */
+template <bool EXACT, bool ESS, bool STATS, bool PART, int PAIR, int UB>
 __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant__ MarchParams p)
 {
     extern __shared__ float4 smem[];
@@ -644,7 +648,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     }
 }
 
-template <bool EXACT, bool ESS, bool STATS, bool PART, bool PAIR, int UB>
+template <bool EXACT, bool ESS, bool STATS, bool PART, int PAIR, int UB>
 cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, int threads, cudaStream_t s)
 {
     auto kern = k_march<EXACT, ESS, STATS, PART, PAIR, UB>;
@@ -657,7 +661,7 @@ cudaError_t launch(const MarchParams &p, size_t smem, dim3 grid, int threads, cu
     return cudaGetLastError();
 }
 
-template <bool EXACT, bool ESS, bool PAIR, int UB>
+template <bool EXACT, bool ESS, int PAIR, int UB>
 cudaError_t launch2(const MarchParams &p, bool stats, bool part, size_t smem, dim3 grid, int threads, cudaStream_t s)
 {
     if (stats)
@@ -667,7 +671,7 @@ cudaError_t launch2(const MarchParams &p, bool stats, bool part, size_t smem, di
                 : launch<EXACT, ESS, false, false, PAIR, UB>(p, smem, grid, threads, s);
 }
 
-template <bool ESS, bool PAIR>
+template <bool ESS, int PAIR>
 cudaError_t launch_hw(const MarchParams &p, bool stats, bool part, int ub, size_t smem, dim3 grid, int threads,
                       cudaStream_t s)
 {
@@ -694,11 +698,14 @@ cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool sta
     const size_t smem = vr_march_smem_bytes(p, exact);
     const dim3 grid((unsigned)ctas);
     if (exact)
-        return ess ? launch2<true, true, false, 1>(p, stats, part, smem, grid, threads, s)
-                   : launch2<true, false, false, 1>(p, stats, part, smem, grid, threads, s);
+        return ess ? launch2<true, true, 0, 1>(p, stats, part, smem, grid, threads, s)
+                   : launch2<true, false, 0, 1>(p, stats, part, smem, grid, threads, s);
+    if (pair && p.pair_split != 0x10000)
+        return ess ? launch_hw<true, 2>(p, stats, part, ub, smem, grid, threads, s)
+                   : launch_hw<false, 2>(p, stats, part, ub, smem, grid, threads, s);
     if (pair)
-        return ess ? launch_hw<true, true>(p, stats, part, ub, smem, grid, threads, s)
-                   : launch_hw<false, true>(p, stats, part, ub, smem, grid, threads, s);
-    return ess ? launch_hw<true, false>(p, stats, part, ub, smem, grid, threads, s)
-               : launch_hw<false, false>(p, stats, part, ub, smem, grid, threads, s);
+        return ess ? launch_hw<true, 1>(p, stats, part, ub, smem, grid, threads, s)
+                   : launch_hw<false, 1>(p, stats, part, ub, smem, grid, threads, s);
+    return ess ? launch_hw<true, 0>(p, stats, part, ub, smem, grid, threads, s)
+               : launch_hw<false, 0>(p, stats, part, ub, smem, grid, threads, s);
 }

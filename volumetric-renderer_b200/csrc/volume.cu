@@ -184,9 +184,17 @@ __global__ void __launch_bounds__(256) k_chebyshev_pass(const uint32_t *__restri
  * (that is the sampler's transparent-black border, offscreen_pass.cpp:1020-1026, on the pair axis).
  * In-plane axes (a, b): ax = 2 -> (x, y), ax = 1 -> (x, z), ax = 0 -> (y, z).
  * Written through a surface so the block-linear array is filled in place, without a staging copy. */
+/* CUDA layered arrays hold at most 2048 layers: layers >= split go to a second array (surf1). */
+template <typename T2>
+__device__ __forceinline__ void put_pair(T2 t, cudaSurfaceObject_t surf0, cudaSurfaceObject_t surf1, int split, int a, int b, int l)
+{
+    if (l < split) surf2DLayeredwrite(t, surf0, a * (int)sizeof(T2), b, l);
+    else surf2DLayeredwrite(t, surf1, a * (int)sizeof(T2), b, l - split);
+}
+
 template <typename T, typename T2>
 __global__ void __launch_bounds__(256) k_pack_pairs(const T *__restrict__ v, int nx, int ny, int nz, int ax,
-                                                    cudaSurfaceObject_t surf)
+                                                    cudaSurfaceObject_t surf, cudaSurfaceObject_t surf1, int split)
 {
     if (ax != 0) {
         /* a = x: consecutive threads read consecutive voxels */
@@ -200,7 +208,7 @@ __global__ void __launch_bounds__(256) k_pack_pairs(const T *__restrict__ v, int
             t.x = l > 0 ? __ldg(v + ((size_t)b * ny + (l - 1)) * nx + x) : (T)0;
             t.y = l < ny ? __ldg(v + ((size_t)b * ny + l) * nx + x) : (T)0;
         }
-        surf2DLayeredwrite(t, surf, x * (int)sizeof(T2), b, l);
+        put_pair(t, surf, surf1, split, x, b, l);
     } else {
         /* layers along x, a = y: a 32 (y) x 33 (x) tile of one z-slice goes through shared memory so that
          * both the reads (along x) and the writes (along y) are contiguous */
@@ -220,7 +228,7 @@ __global__ void __launch_bounds__(256) k_pack_pairs(const T *__restrict__ v, int
             if (l <= nx && y < ny) {
                 T2 t;
                 t.x = tile[tx][r], t.y = tile[tx][r + 1];
-                surf2DLayeredwrite(t, surf, y * (int)sizeof(T2), z, l);
+                put_pair(t, surf, surf1, split, y, z, l);
             }
         }
     }
@@ -410,27 +418,36 @@ cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned c
 }
 
 cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int axis,
-                             cudaArray_t pair_array, cudaStream_t s)
+                             cudaArray_t pair_array, cudaArray_t pair_array_hi, int split, cudaStream_t s)
 {
     if ((dtype != VR_U8 && dtype != VR_U16) || axis < 0 || axis > 2) return cudaErrorInvalidValue;
     if (nx > 65535u * 32u || ny > 65535u || nz > 65535u) return cudaErrorInvalidConfiguration;
-    cudaResourceDesc rd = {};
-    rd.resType = cudaResourceTypeArray;
-    rd.res.array.array = pair_array;
-    cudaSurfaceObject_t surf = 0;
-    cudaError_t e = cudaCreateSurfaceObject(&surf, &rd);
-    if (e != cudaSuccess) return e;
-    /* axis 2: (x blocks, y, layers z); axis 1: (x blocks, z, layers y); axis 0: (layer tiles, y tiles, z) */
-    const dim3 grid = axis == 2   ? dim3((nx + 255) / 256, ny, nz + 1)
-                      : axis == 1 ? dim3((nx + 255) / 256, nz, ny + 1)
-                                  : dim3((nx + 1 + 31) / 32, (ny + 31) / 32, nz);
-    if (dtype == VR_U8)
-        k_pack_pairs<unsigned char, uchar2><<<grid, 256, 0, s>>>((const unsigned char *)dev, (int)nx, (int)ny, (int)nz, axis, surf);
-    else
-        k_pack_pairs<unsigned short, ushort2><<<grid, 256, 0, s>>>((const unsigned short *)dev, (int)nx, (int)ny, (int)nz, axis, surf);
-    e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
-    cudaDestroySurfaceObject(surf);
+    cudaSurfaceObject_t surf[2] = {0, 0};
+    cudaArray_t arrs[2] = {pair_array, pair_array_hi};
+    cudaError_t e = cudaSuccess;
+    for (int k = 0; k < 2 && e == cudaSuccess; k++) {
+        if (!arrs[k]) continue;
+        cudaResourceDesc rd = {};
+        rd.resType = cudaResourceTypeArray;
+        rd.res.array.array = arrs[k];
+        e = cudaCreateSurfaceObject(&surf[k], &rd);
+    }
+    if (e == cudaSuccess) {
+        /* axis 2: (x blocks, y, layers z); axis 1: (x blocks, z, layers y); axis 0: (layer tiles, y tiles, z) */
+        const dim3 grid = axis == 2   ? dim3((nx + 255) / 256, ny, nz + 1)
+                          : axis == 1 ? dim3((nx + 255) / 256, nz, ny + 1)
+                                      : dim3((nx + 1 + 31) / 32, (ny + 31) / 32, nz);
+        if (dtype == VR_U8)
+            k_pack_pairs<unsigned char, uchar2><<<grid, 256, 0, s>>>((const unsigned char *)dev, (int)nx, (int)ny, (int)nz, axis,
+                                                                     surf[0], surf[1], split);
+        else
+            k_pack_pairs<unsigned short, ushort2><<<grid, 256, 0, s>>>((const unsigned short *)dev, (int)nx, (int)ny, (int)nz, axis,
+                                                                       surf[0], surf[1], split);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    }
+    for (int k = 0; k < 2; k++)
+        if (surf[k]) cudaDestroySurfaceObject(surf[k]);
     return e;
 }
 

@@ -42,6 +42,8 @@ struct MarchParams {
      * space (u, v, w): every per-axis field of this block is stored in that order by the host, and the
      * kernel permutes the ray's entry position and direction once (pair_axis). */
     cudaTextureObject_t tex_pair;
+    cudaTextureObject_t tex_pair_hi; /* layers >= pair_split live in a second array (2048-layer limit of layered arrays) */
+    int pair_split;                  /* 0x10000 when one array holds them all */
     int pair_axis;              /* model axis of w: 2 (identity), 1: (u,v,w) = (x,z,y), 0: (u,v,w) = (y,z,x) */
     float pair_a[3], pair_b[3]; /* u, v: local normalised coord = q * a + b;  w: local texel coord + 1.5*2^23 = q * a + b */
     float pair_zc;              /* 0.5 - forg[w]: frac = q_w * dims[w] + (pair_zc - (floor + 1)) */
@@ -119,7 +121,10 @@ struct vr_ctx {
     int layout_used = VR_LAYOUT_AUTO; /* the request the current volume was uploaded under */
     bool last_pair = false;           /* the last frame sampled the paired layout */
     cudaArray_t pair_array[3] = {nullptr, nullptr, nullptr}; /* paired layouts along x, y, z (see MarchParams::tex_pair), resident next to `array` */
-    cudaTextureObject_t tex_pair[3] = {0, 0, 0};
+    cudaArray_t pair_array_hi[3] = {nullptr, nullptr, nullptr}; /* their layers >= pair_split[axis], if any */
+    cudaTextureObject_t tex_pair[3] = {0, 0, 0}, tex_pair_hi[3] = {0, 0, 0};
+    int pair_split[3] = {0x10000, 0x10000, 0x10000};
+    int tune_pair_split = 2048; /* VR_PAIR_SPLIT: layers per layered array (tests force small values) */
     int last_pair_axis = 2;
 
     /* sort-last */
@@ -136,7 +141,7 @@ struct vr_ctx {
     int tune_batch = 2, tune_threads = 128, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
     int tune_pair_axis = -1;  /* VR_PAIR_AXIS: force the pair axis (experiments); -1 = the axis the camera looks down most */
     int tune_pair_policy = 2; /* VR_PAIR_POLICY: 0 never sample the paired layout, 1 always, 2 per frame (vr_render_frame) */
-    size_t tune_pair_max_bytes = (size_t)24 << 30; /* AUTO layout: pair only if the paired copy fits this (VR_PAIR_MAX_MB) */
+    size_t tune_pair_max_bytes = (size_t)160 << 30; /* and never more than the free memory minus a reserve */ /* AUTO layout: pair only if the paired copy fits this (VR_PAIR_MAX_MB) */
     float tune_ess_min_empty = 0.25f; /* consult the occupancy grid only if at least this share of cells is empty */
 
     /* occupancy */
@@ -172,7 +177,7 @@ cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned c
                            cudaStream_t s);
 /* fill the layered array paired along `axis` (n_axis + 1 layers) from the linear volume; dtype u8 or u16 */
 cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int axis,
-                             cudaArray_t pair_array, cudaStream_t s);
+                             cudaArray_t pair_array, cudaArray_t pair_array_hi, int split, cudaStream_t s);
 cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
                         const int org[3], const uint32_t full[3], cudaStream_t s);
 
