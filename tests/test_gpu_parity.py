@@ -248,6 +248,51 @@ def test_auto_layout_is_chosen_per_frame(vr, port):
         assert_within_tolerance(img, o["rgba8"], f"auto {w}x{h}")
 
 
+def _write_nrrd(path, arr, endian="little", detached=None, byte_skip=None, prefix=b""):
+    tname = {np.dtype(np.uint8): "uchar", np.dtype(np.uint16): "ushort", np.dtype(np.float32): "float"}[arr.dtype]
+    nz, ny, nx = arr.shape
+    hdr = f"NRRD0004\n# test\ntype: {tname}\ndimension: 3\nsizes: {nx} {ny} {nz}\nencoding: raw\n"
+    if arr.dtype.itemsize > 1:
+        hdr += f"endian: {endian}\n"
+    if byte_skip is not None:
+        hdr += f"byte skip: {byte_skip}\n"
+    data = arr.astype(arr.dtype.newbyteorder(">" if endian == "big" else "<")).tobytes()
+    if detached:
+        hdr += f"data file: {detached}\n"
+        (path.parent / detached).write_bytes(prefix + data)
+        path.write_bytes(hdr.encode())
+    else:
+        path.write_bytes(hdr.encode() + b"\n" + prefix + data)
+
+
+def test_nrrd_loader_fast_path_and_general_path_agree(vr, port, tmp_path):
+    """vr_load_nrrd streams raw u8/u16/f32 payloads in host byte order through pinned memory straight to the
+    device; everything else goes through the general reader.  Either way the device holds the file's
+    voxels and the data range (nrrd_file_parser.cpp:39-40)."""
+    rng = np.random.default_rng(7)
+    cases = [
+        ("a.nrrd", rng.integers(0, 65535, (9, 20, 33), dtype=np.uint16), dict()),
+        ("b.nhdr", rng.integers(0, 255, (17, 5, 12), dtype=np.uint8), dict(detached="b.raw", byte_skip=-1, prefix=b"junkjunk")),
+        ("c.nrrd", rng.random((6, 7, 8), dtype=np.float32), dict(byte_skip=5, prefix=b"12345")),
+        ("d.nrrd", rng.integers(0, 65535, (4, 6, 10), dtype=np.uint16), dict(endian="big")),   # general path (byte swap)
+    ]
+    op = vr.OffscreenPass(32, 32)
+    try:
+        for name, arr, kw in cases:
+            _write_nrrd(tmp_path / name, arr, **kw)
+            op.import_nrrd(str(tmp_path / name))
+            dt, dims, mn, mx = op.volume_info()
+            assert dims == (arr.shape[2], arr.shape[1], arr.shape[0])
+            assert np.array_equal(op.download_volume(), arr), name
+            assert (mn, mx) == (float(arr.min()), float(arr.max())), name
+            assert np.array_equal(vr.read_nrrd(str(tmp_path / name)), arr), name
+        (tmp_path / "t.nrrd").write_bytes((tmp_path / "a.nrrd").read_bytes()[:-10])
+        with pytest.raises(vr.VrError, match="truncated"):
+            op.import_nrrd(str(tmp_path / "t.nrrd"))
+    finally:
+        op.close()
+
+
 def test_write_image_round_trips(vr, port, tmp_path):
     op = vr.OffscreenPass(37, 21)
     try:

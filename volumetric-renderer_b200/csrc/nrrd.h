@@ -14,6 +14,17 @@ struct VrNrrd {
     std::vector<uint8_t> bytes;
 };
 
-/* Returns a vr_status; on failure `err` holds the message. */
-int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err);
+/* Where the payload of a file lies when it can go to the device as it is: raw encoding, a type the
+ * device keeps natively (u8, u16, f32) and the host's byte order. */
+struct VrNrrdPayload {
+    bool direct = false;
+    std::string path;    /* the file holding the data (the header itself, or its detached data file) */
+    uint64_t offset = 0; /* first byte of the payload in that file */
+    uint64_t bytes = 0;
+};
+
+/* Returns a vr_status; on failure `err` holds the message.  With `payload` given and the file qualifying
+ * (see VrNrrdPayload) the data is NOT read: out.dtype / out.dims are set, out.bytes stays empty and
+ * *payload says where to stream it from (vr_load_nrrd does that through pinned memory). */
+int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err, VrNrrdPayload *payload = nullptr);
 #endif
