@@ -286,7 +286,7 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
     uint32_t maxdim = nx > ny ? nx : ny;
     maxdim = maxdim > nz ? maxdim : nz;
     int cell = 4;
-    while ((maxdim + cell - 1) / cell > VR_OCC_MAX_AXIS) cell *= 2;
+    while ((maxdim + cell - 1) / cell > (uint32_t)c->tune_occ_max_axis) cell *= 2;
     c->occ_cell = cell;
     c->occ_n[0] = (int)((nx + cell - 1) / cell), c->occ_n[1] = (int)((ny + cell - 1) / cell),
     c->occ_n[2] = (int)((nz + cell - 1) / cell);
@@ -370,6 +370,7 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     if (const char *e = std::getenv("VR_LAYOUT")) c->layout_req = std::atoi(e) == 1 ? VR_LAYOUT_ARRAY3D : (std::atoi(e) == 2 ? VR_LAYOUT_PAIRED : VR_LAYOUT_AUTO);
     if (const char *e = std::getenv("VR_PAIR_POLICY")) c->tune_pair_policy = std::atoi(e);
     if (const char *e = std::getenv("VR_PAIR_SPLIT")) c->tune_pair_split = std::atoi(e);
+    if (const char *e = std::getenv("VR_OCC_MAX_AXIS")) c->tune_occ_max_axis = std::min(std::max(std::atoi(e), 8), 256);
     if (const char *e = std::getenv("VR_PAIR_AXIS")) c->tune_pair_axis = std::atoi(e) >= 0 && std::atoi(e) <= 2 ? std::atoi(e) : -1;
     if (const char *e = std::getenv("VR_PAIR_MAX_MB")) c->tune_pair_max_bytes = (size_t)std::atoll(e) << 20;
     if (const char *e = std::getenv("VR_L2_GRAN")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(e));
