@@ -92,19 +92,46 @@ def test_hw_sampler_within_tolerance(vr, port, case, layout):
     lay = vr.LAYOUT_PAIRED if layout == "paired" else vr.LAYOUT_ARRAY3D
     img, raw, st, o = render_both(vr, port, vol, lut, moves, zoom, sampler=vr.SAMPLER_HW, empty_skip=1, layout=lay, **kw)
     assert st.covered_pixels == o["stats"].covered_pixels
-    assert st.n_ref == o["stats"].n_ref  # positions are bit-exact in both modes
+    # positions are bit-exact in both modes except after an empty-space jump (see skip_empty in march.cu)
+    assert abs(st.n_ref - o["stats"].n_ref) <= 1e-3 * o["stats"].n_ref
     assert_within_tolerance(img, o["rgba8"], f"case {case}")
 
 
+# one camera per sign octant of the view direction (the distance maps are per octant), plus axis-aligned views
+ESS_VIEWS = [(45, 30), (135, 30), (225, 30), (315, 30), (45, -30), (135, -30), (225, -30), (315, -30), (0, 0), (90, 0), (0, 89)]
+
+
 @pytest.mark.parametrize("layout", ["array3d", "paired"])
-def test_empty_space_skipping_skips_and_changes_nothing(vr, port, layout):
+@pytest.mark.parametrize("view", ESS_VIEWS)
+def test_empty_space_skipping_skips_and_changes_nothing(vr, port, layout, view):
+    """Hardware sampler: a jump of k steps is one fused multiply-add per axis where the shader makes k
+    additions, so the positions after a jump differ from the reference's by the rounding those additions
+    accumulate (<= 2e-5 texture units): the frame changes by less than one 8-bit level, the visited-step
+    count by at most the rays whose last step sits within that distance of the exit face."""
     vol = small_volume(port, 2, np.uint16, 64)
     lut = tf(port, "C")
     lay = vr.LAYOUT_PAIRED if layout == "paired" else vr.LAYOUT_ARRAY3D
-    a = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=0, layout=lay)
-    b = render_both(vr, port, vol, lut, [(45, 30)], sampler=vr.SAMPLER_HW, empty_skip=1, layout=lay)
+    a = render_both(vr, port, vol, lut, [view], sampler=vr.SAMPLER_HW, empty_skip=0, layout=lay)
+    b = render_both(vr, port, vol, lut, [view], sampler=vr.SAMPLER_HW, empty_skip=1, layout=lay)
+    assert np.abs(a[1] - b[1]).max() < 1.0 / 255.0
+    assert np.abs(a[0].astype(int) - b[0].astype(int)).max() <= 1
+    assert (a[0] != b[0]).mean() < 0.01
+    assert a[2].covered_pixels == b[2].covered_pixels
+    assert abs(a[2].n_ref - b[2].n_ref) <= 1e-3 * a[2].n_ref
+    assert b[2].n_fetch < a[2].n_fetch * 0.7, (a[2].n_fetch, b[2].n_fetch)
+    assert_within_tolerance(b[0], b[3]["rgba8"], f"view {view}")
+
+
+@pytest.mark.parametrize("view", ESS_VIEWS[:8])
+def test_empty_space_skipping_exact_sampler_changes_nothing(vr, port, view):
+    """The exact sampler consults the same per-octant maps step by step and never jumps: bit-identical."""
+    vol = small_volume(port, 2, np.uint16, 64)
+    lut = tf(port, "C")
+    a = render_both(vr, port, vol, lut, [view], sampler=vr.SAMPLER_EXACT, empty_skip=0)
+    b = render_both(vr, port, vol, lut, [view], sampler=vr.SAMPLER_EXACT, empty_skip=1)
     assert np.array_equal(bits(a[1]), bits(b[1]))
     assert np.array_equal(a[0], b[0])
+    assert a[2].n_ref == b[2].n_ref and a[2].n_inslice == b[2].n_inslice
     assert b[2].n_fetch < a[2].n_fetch * 0.7, (a[2].n_fetch, b[2].n_fetch)
 
 
@@ -187,7 +214,11 @@ def test_every_pair_axis_with_every_camera(vr, port, moves, axis, ess, monkeypat
         op.close()
     o = port.render(oracle_frame(port, ocam, W, H, mn, mx, lo, hi), vol, lut)
     assert st.covered_pixels == o["stats"].covered_pixels
-    assert st.n_ref == o["stats"].n_ref and st.n_inslice == o["stats"].n_inslice
+    if ess:  # positions after an empty-space jump differ from the shader's by a few ulp (skip_empty, march.cu)
+        assert abs(st.n_ref - o["stats"].n_ref) <= 1e-3 * o["stats"].n_ref
+        assert abs(st.n_inslice - o["stats"].n_inslice) <= 1e-3 * o["stats"].n_ref
+    else:
+        assert st.n_ref == o["stats"].n_ref and st.n_inslice == o["stats"].n_inslice
     assert_within_tolerance(img, o["rgba8"], f"pair axis {axis}")
 
 

@@ -171,7 +171,7 @@ void release_volume(vr_ctx *c)
     if (c->d_cell_range) cudaFree(c->d_cell_range), c->d_cell_range = nullptr;
     if (c->d_occ) cudaFree(c->d_occ), c->d_occ = nullptr;
     if (c->d_dist) cudaFree(c->d_dist), c->d_dist = nullptr;
-    if (c->d_dist_tmp) cudaFree(c->d_dist_tmp), c->d_dist_tmp = nullptr;
+    if (c->d_sat) cudaFree(c->d_sat), c->d_sat = nullptr;
 }
 
 int alloc_target(vr_ctx *c, uint32_t w, uint32_t h)
@@ -282,7 +282,7 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
         c->max_density = mx ? *mx : b;
     }
 
-    /* occupancy grid: power-of-two cells, at most 64 per axis */
+    /* occupancy grid: power-of-two cells, at most tune_occ_max_axis (128) per axis */
     uint32_t maxdim = nx > ny ? nx : ny;
     maxdim = maxdim > nz ? maxdim : nz;
     int cell = 4;
@@ -294,8 +294,8 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
     c->occ_words = (ncells + 31) / 32;
     VR_CUDA(c, cudaMalloc(&c->d_cell_range, sizeof(float2) * ncells));
     VR_CUDA(c, cudaMalloc(&c->d_occ, sizeof(uint32_t) * c->occ_words));
-    VR_CUDA(c, cudaMalloc(&c->d_dist, (size_t)ncells));
-    VR_CUDA(c, cudaMalloc(&c->d_dist_tmp, (size_t)ncells));
+    VR_CUDA(c, cudaMalloc(&c->d_dist, (size_t)ncells * 8));
+    VR_CUDA(c, cudaMalloc(&c->d_sat, sizeof(uint32_t) * (size_t)(c->occ_n[0] + 1) * (c->occ_n[1] + 1) * (c->occ_n[2] + 1)));
     VR_CUDA(c, vr_k0_cell_ranges(dev, dtype, nx, ny, nz, cell, c->occ_n, c->d_cell_range, c->stream));
     c->occ_dirty = true;
     VR_CUDA(c, cudaStreamSynchronize(c->stream)); /* the reference's upload is synchronous too */
@@ -619,7 +619,7 @@ int prepare_occupancy(vr_ctx *c, cudaStream_t s)
     if (!c->occ_dirty) return VR_OK;
     VR_CUDA(c, vr_k0_classify(c->d_cell_range, c->occ_n, c->d_lut_pad, c->nlut, c->min_density, c->max_density, c->d_occ,
                               c->occ_words, c->d_counters + 4, s));
-    VR_CUDA(c, vr_k0_distance(c->d_occ, c->occ_n, c->d_dist, c->d_dist_tmp, s));
+    VR_CUDA(c, vr_k0_distance(c->d_occ, c->occ_n, c->d_dist, c->d_sat, s));
     VR_CUDA(c, cudaMemcpyAsync(&c->h_counters[4], c->d_counters + 4, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     VR_CUDA(c, cudaStreamSynchronize(s));
     c->occ_empty_cells = c->h_counters[4];
@@ -709,6 +709,7 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
     p.dscale = c->dtype == VR_U8 ? 255.0f : (c->dtype == VR_U16 ? 65535.0f : 1.0f);
     p.lut_pad = c->d_lut_pad, p.lut_dif = c->d_lut_dif, p.lut_h = c->d_lut_h, p.nlut = c->nlut;
     p.occ_stride[0] = 1, p.occ_stride[1] = c->occ_n[0], p.occ_stride[2] = c->occ_n[0] * c->occ_n[1];
+    for (int i = 0; i < 3; i++) p.occ_oct[i] = (uint32_t)(c->occ_n[0] * c->occ_n[1] * c->occ_n[2]) << i;
     p.pair_axis = 2;
     p.tex_pair = 0, p.tex_pair_hi = 0, p.pair_split = 0x10000;
     if (pair_axis >= 0) {
@@ -723,7 +724,7 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
         permute3(p.dims, perm), permute3(p.org, perm), permute3(p.forg, perm), permute3(p.inv_ldims, perm);
         permute3(p.own_lo, perm), permute3(p.own_hi, perm), permute3(p.box_lo, perm), permute3(p.box_hi, perm);
         permute3(p.occ_n, perm), permute3(p.occ_stride, perm), permute3(p.occ_scale, perm), permute3(p.occ_off, perm);
-        permute3(p.occ_f_hi, perm);
+        permute3(p.occ_f_hi, perm), permute3(p.occ_oct, perm);
     }
     for (int i = 0; i < 2; i++) {
         p.pair_a[i] = p.dims[i] * p.inv_ldims[i];

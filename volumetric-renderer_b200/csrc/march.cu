@@ -116,11 +116,12 @@ __device__ __forceinline__ float sample_exact(const MarchParams &p, float s, flo
     return lerp1(lerp1(x00, x10, b), lerp1(x01, x11, b), c);
 }
 
-/* Chebyshev distance (in cells, capped) from the cell holding this position to the nearest cell
- * that may contribute: 0 = sample here; d >= 1 = every cell within d-1 cells is empty.
+/* Directional distance (in cells) of the cell holding this position, from the map of the ray's direction
+ * octant (doff): 0 = the cell may contribute, sample here; d >= 1 = the cube of d cells that starts at this
+ * cell and extends along the ray's octant is empty (volume.cu k_octant_distance).
  * A one-ulp slip across a cell face is harmless: every cell's range includes a 1-voxel apron. */
 template <bool PART>
-__device__ __forceinline__ int cell_distance(const MarchParams &p, float x, float y, float z)
+__device__ __forceinline__ int cell_distance(const MarchParams &p, uint32_t doff, float x, float y, float z)
 {
     int cx = PART ? (int)(x * p.occ_scale[0] - p.occ_off[0]) : (int)(x * p.occ_scale[0]);
     int cy = PART ? (int)(y * p.occ_scale[1] - p.occ_off[1]) : (int)(y * p.occ_scale[1]);
@@ -128,8 +129,8 @@ __device__ __forceinline__ int cell_distance(const MarchParams &p, float x, floa
     cx = min(max(cx, 0), p.occ_n[0] - 1);
     cy = min(max(cy, 0), p.occ_n[1] - 1);
     cz = min(max(cz, 0), p.occ_n[2] - 1);
-    /* 256 KiB at most, read through L1 (no shared-memory staging: it would cost occupancy) */
-    return (int)__ldg(p.dist + (cz * p.occ_stride[2] + cy * p.occ_stride[1] + cx * p.occ_stride[0]));
+    /* 2 MiB per octant at most, read through L1 / L2 */
+    return (int)__ldg(p.dist + doff + (cz * p.occ_stride[2] + cy * p.occ_stride[1] + cx * p.occ_stride[0]));
 }
 
 #define VR_MAGIC 12582912.0f /* 1.5 * 2^23: x + VR_MAGIC rounds x to an integer held in the low mantissa bits */
@@ -186,6 +187,7 @@ struct Ray {
     uint32_t nb, ns, nf;   /* counters (STATS) */
     float ifx, ify, ifz;   /* ESS: 1 / (d * occ_scale): steps per cell, per axis (1e30 where d = 0) */
     float sgx, sgy, sgz;   /* ESS: sign of the direction, per axis */
+    uint32_t doff;         /* ESS: offset of the distance map of the direction's octant */
     bool in_empty;         /* ESS: the last step generated fell into an empty fine cell */
 };
 
@@ -217,13 +219,16 @@ __device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r
     }
 }
 
-/* Empty-space skipping by distance map.  If the cell holding the current position is empty with
- * distance d, the cube of 2d-1 cells around it is empty: the ray advances to where it leaves that
- * cube with nothing but the position additions of volume.frag:47 (positions stay bit-identical).
- * Every skipped position lies strictly inside the cube, i.e. is one the per-step test would have
- * rejected anyway -- results are unchanged.  Jumps are taken only inside the ray's safe interval
- * (see safe_interval), where every position is inside the volume, the slices and the rank's own
- * box: no clipping of the cube, and every skipped step counts as visited for the statistics. */
+/* Empty-space skipping by directional distance map (hardware sampler only).  If the cell holding the
+ * current position is empty with distance d, the cube of d cells that starts at this cell and extends along
+ * the ray's octant is empty: the ray jumps k steps, to the first position that may lie outside the cube.
+ * Every skipped position lies strictly inside the cube, i.e. is one the per-step test would have rejected
+ * anyway.  The jump is one fused multiply-add per axis, pos += k * d, where volume.frag:47 makes k
+ * additions: the positions after a jump differ from the reference's by the accumulated rounding of those
+ * additions (< steps * ulp(1)/2 ~ 2e-5 texture units, far below the 1/256-texel weight resolution of the
+ * filter) -- the exact sampler never jumps.  Jumps are taken only inside the ray's safe interval (see
+ * safe_interval), where every position is inside the volume, the slices and the rank's own box: no
+ * clipping of the cube, and every skipped step counts as visited for the statistics. */
 template <bool STATS, bool PART>
 __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fast_lo, int fast_hi)
 {
@@ -235,15 +240,16 @@ __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fas
         const float fy = PART ? fmaf(r.py, p.occ_scale[1], -p.occ_off[1]) : r.py * p.occ_scale[1];
         const float fz = PART ? fmaf(r.pz, p.occ_scale[2], -p.occ_off[2]) : r.pz * p.occ_scale[2];
         const int cx = min((int)fx, p.occ_n[0] - 1), cy = min((int)fy, p.occ_n[1] - 1), cz = min((int)fz, p.occ_n[2] - 1);
-        const int d = (int)__ldg(p.dist + (cz * p.occ_stride[2] + cy * p.occ_stride[1] + cx * p.occ_stride[0]));
+        const int d = (int)__ldg(p.dist + r.doff + (cz * p.occ_stride[2] + cy * p.occ_stride[1] + cx * p.occ_stride[0]));
         if (d == 0) {
             r.in_empty = false;
             return;
         }
-        /* steps until the ray leaves the cube: per axis the exit plane is the cell centre +- (d - 1/2),
-         * pulled in by a margin that covers the accumulated rounding of the positions (<= steps * ulp,
-         * far below 2e-3 cells); sg = direction sign, if = steps per cell (1e30 on a zero component) */
-        const float R = (float)(d - 1) + (0.5f - 2.0e-3f);
+        /* steps until the ray leaves the cube: per axis the exit plane is the cell's entry face + d cells
+         * along the direction, i.e. the cell centre +- (d - 1/2), pulled in by a margin that covers the
+         * rounding of the positions (<= steps * ulp, far below 2e-3 cells); sg = direction sign,
+         * if = steps per cell (1e30 on a zero component) */
+        const float R = (float)d - (0.5f + 2.0e-3f);
         const float tx = (fmaf(r.sgx, R, (float)cx + 0.5f) - fx) * r.ifx;
         const float ty = (fmaf(r.sgy, R, (float)cy + 0.5f) - fy) * r.ify;
         const float tz = (fmaf(r.sgz, R, (float)cz + 0.5f) - fz) * r.ifz;
@@ -252,16 +258,8 @@ __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fas
         k = min(max(k, 1), fast_hi - r.i + 1);
         r.i += k;
         if (STATS) r.nb += (uint32_t)k, r.ns += (uint32_t)k;
-#pragma unroll 1
-        for (; k >= 4; k -= 4) {
-#pragma unroll
-            for (int j = 0; j < 4; j++) r.px += r.dx, r.py += r.dy, r.pz += r.dz;
-        }
-        if (k & 2) {
-            r.px += r.dx, r.py += r.dy, r.pz += r.dz;
-            r.px += r.dx, r.py += r.dy, r.pz += r.dz;
-        }
-        if (k & 1) r.px += r.dx, r.py += r.dy, r.pz += r.dz;
+        const float kf = (float)k;
+        r.px = fmaf(kf, r.dx, r.px), r.py = fmaf(kf, r.dy, r.py), r.pz = fmaf(kf, r.dz, r.pz);
     }
 }
 
@@ -307,7 +305,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
             }
         }
         if (ESS) {
-            const bool occ = !s || cell_distance<PART>(p, r.px, r.py, r.pz) == 0;
+            const bool occ = !s || cell_distance<PART>(p, r.doff, r.px, r.py, r.pz) == 0;
             r.in_empty = !occ;
             s = s && occ;
         }
@@ -499,7 +497,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     Ray ray;
     ray.cr = cr, ray.cg = cg, ray.cb = cb, ray.T = T;
     ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
-    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.sgx = ray.sgy = ray.sgz = 1.0f, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
+    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.sgx = ray.sgy = ray.sgz = 1.0f, ray.doff = 0u, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
     bool parked = false; /* fast phase: this lane only keeps its warp company */
     float t_saved = 1.0f;
@@ -518,6 +516,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         ray.ify = sy_ != 0.0f ? __frcp_rn(sy_) : 1.0e30f;
         ray.ifz = sz_ != 0.0f ? __frcp_rn(sz_) : 1.0e30f;
         ray.sgx = ray.ifx < 0.0f ? -1.0f : 1.0f, ray.sgy = ray.ify < 0.0f ? -1.0f : 1.0f, ray.sgz = ray.ifz < 0.0f ? -1.0f : 1.0f;
+        ray.doff = (ray.ifx < 0.0f ? p.occ_oct[0] : 0u) + (ray.ify < 0.0f ? p.occ_oct[1] : 0u) + (ray.ifz < 0.0f ? p.occ_oct[2] : 0u);
     }
     /* Warp-uniform choice per batch.  Checked: every test of volume.frag:34-40 is evaluated (always
      * correct).  Unchecked: every live lane is inside its safe interval; predicated if some lane is

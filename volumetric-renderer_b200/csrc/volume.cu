@@ -155,28 +155,80 @@ __global__ void __launch_bounds__(256) k_classify(const float2 *__restrict__ ran
     }
 }
 
-/* Chebyshev distance transform of the occupancy bits, one separable pass per axis:
- * pass 0 reads the bits (0 where occupied, else "far"), each pass replaces D by
- * min over the line of max(|i - i'|, D(i')).  After the three passes D = number of cells to the
- * nearest occupied cell in the max-norm, capped at VR_DIST_CAP. */
-#define VR_DIST_CAP 64
-__global__ void __launch_bounds__(256) k_chebyshev_pass(const uint32_t *__restrict__ occ, const unsigned char *__restrict__ in,
-                                                        unsigned char *__restrict__ out, int nx, int ny, int nz, int axis)
+/* Directional distance maps.  For each of the eight sign octants (sx, sy, sz) of a ray direction and each
+ * empty cell c, D = edge length (in cells) of the largest cube of empty cells that has c at its corner and
+ * extends towards (sx, sy, sz); cells outside the grid count as empty; occupied cells get 0; capped at
+ * VR_DIST_CAP.  A ray in c whose direction lies in that octant cannot meet an occupied cell before it
+ * leaves the cube.  Unlike a centred (Chebyshev) distance this ignores what lies behind the ray, so a ray
+ * leaving or passing a surface takes long jumps at once.
+ *
+ * Built from a summed-volume table S of the occupancy bits (S[x][y][z] = occupied cells in
+ * [0,x) x [0,y) x [0,z), (n+1)^3 entries): a cube is empty iff its clipped box sum is 0, which is monotone
+ * in the edge length -> binary search, 8 table reads per probe. */
+#define VR_DIST_CAP 255
+__global__ void __launch_bounds__(256) k_sat_init(const uint32_t *__restrict__ occ, uint32_t *__restrict__ S, int nx, int ny, int nz)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int mx = nx + 1, my = ny + 1;
+    if (i >= mx * my * (nz + 1)) return;
+    const int x = i % mx, y = (i / mx) % my, z = i / (mx * my);
+    uint32_t v = 0;
+    if (x > 0 && y > 0 && z > 0) {
+        const int q = ((z - 1) * ny + (y - 1)) * nx + (x - 1);
+        v = (occ[q >> 5] >> (q & 31)) & 1u;
+    }
+    S[i] = v;
+}
+
+/* running sum along one axis of the (mx, my, mz) table, one thread per line */
+__global__ void __launch_bounds__(128) k_sat_scan(uint32_t *__restrict__ S, int mx, int my, int mz, int axis)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = axis == 0 ? mx : (axis == 1 ? my : mz);
+    const int na = axis == 0 ? my : mx, nb = axis == 2 ? my : mz; /* the two other extents, fastest first */
+    if (t >= na * nb) return;
+    const int a = t % na, b = t / na;
+    size_t base, stride;
+    if (axis == 0) base = ((size_t)b * my + a) * mx, stride = 1;
+    else if (axis == 1) base = (size_t)b * my * mx + a, stride = (size_t)mx;
+    else base = (size_t)b * mx + a, stride = (size_t)mx * my;
+    uint32_t acc = 0;
+    for (int i = 0; i < n; i++) {
+        acc += S[base + i * stride];
+        S[base + i * stride] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_octant_distance(const uint32_t *__restrict__ occ, const uint32_t *__restrict__ S,
+                                                         unsigned char *__restrict__ out, int nx, int ny, int nz)
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= nx * ny * nz) return;
+    const int ncells = nx * ny * nz;
+    if (c >= ncells) return;
+    const int oct = blockIdx.y;
     const int x = c % nx, y = (c / nx) % ny, z = c / (nx * ny);
-    const int n = axis == 0 ? nx : (axis == 1 ? ny : nz);
-    const int stride = axis == 0 ? 1 : (axis == 1 ? nx : nx * ny);
-    const int i0 = axis == 0 ? x : (axis == 1 ? y : z);
-    const int base = c - i0 * stride;
-    int best = VR_DIST_CAP;
-    for (int i = max(0, i0 - VR_DIST_CAP); i < min(n, i0 + VR_DIST_CAP + 1); i++) {
-        const int q = base + i * stride;
-        const int dq = in ? (int)in[q] : (((occ[q >> 5] >> (q & 31)) & 1u) ? 0 : VR_DIST_CAP);
-        best = min(best, max(abs(i - i0), dq));
+    int d = 0;
+    if (!((occ[c >> 5] >> (c & 31)) & 1u)) {
+        const int mx = nx + 1, my = ny + 1;
+        const bool negx = oct & 1, negy = oct & 2, negz = oct & 4;
+        auto at = [&](int xx, int yy, int zz) { return S[((size_t)zz * my + yy) * mx + xx]; };
+        auto empty = [&](int s) {
+            const int x0 = max(negx ? x - s + 1 : x, 0), x1 = min(negx ? x + 1 : x + s, nx);
+            const int y0 = max(negy ? y - s + 1 : y, 0), y1 = min(negy ? y + 1 : y + s, ny);
+            const int z0 = max(negz ? z - s + 1 : z, 0), z1 = min(negz ? z + 1 : z + s, nz);
+            const uint32_t n = at(x1, y1, z1) - at(x0, y1, z1) - at(x1, y0, z1) - at(x1, y1, z0) + at(x0, y0, z1) +
+                               at(x0, y1, z0) + at(x1, y0, z0) - at(x0, y0, z0);
+            return n == 0u;
+        };
+        int lo = 1, hi = VR_DIST_CAP; /* size 1 = the cell itself, known empty */
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (empty(mid)) lo = mid;
+            else hi = mid - 1;
+        }
+        d = lo;
     }
-    out[c] = (unsigned char)best;
+    out[(size_t)oct * ncells + c] = (unsigned char)d;
 }
 
 /* Paired layout along axis `ax`: the 2-D layered array has one layer per position l = 0..n_ax on that
@@ -407,13 +459,17 @@ cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const flo
     return cudaGetLastError();
 }
 
-cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, unsigned char *d_tmp,
+cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, uint32_t *d_sat,
                            cudaStream_t s)
 {
-    const int n = occ_n[0] * occ_n[1] * occ_n[2], blocks = (n + 255) / 256;
-    k_chebyshev_pass<<<blocks, 256, 0, s>>>(d_occ, nullptr, d_dist, occ_n[0], occ_n[1], occ_n[2], 0);
-    k_chebyshev_pass<<<blocks, 256, 0, s>>>(d_occ, d_dist, d_tmp, occ_n[0], occ_n[1], occ_n[2], 1);
-    k_chebyshev_pass<<<blocks, 256, 0, s>>>(d_occ, d_tmp, d_dist, occ_n[0], occ_n[1], occ_n[2], 2);
+    const int nx = occ_n[0], ny = occ_n[1], nz = occ_n[2];
+    const int mx = nx + 1, my = ny + 1, mz = nz + 1;
+    const int n = nx * ny * nz, m = mx * my * mz;
+    k_sat_init<<<(m + 255) / 256, 256, 0, s>>>(d_occ, d_sat, nx, ny, nz);
+    k_sat_scan<<<(my * mz + 127) / 128, 128, 0, s>>>(d_sat, mx, my, mz, 0);
+    k_sat_scan<<<(mx * mz + 127) / 128, 128, 0, s>>>(d_sat, mx, my, mz, 1);
+    k_sat_scan<<<(mx * my + 127) / 128, 128, 0, s>>>(d_sat, mx, my, mz, 2);
+    k_octant_distance<<<dim3((n + 255) / 256, 8), 256, 0, s>>>(d_occ, d_sat, d_dist, nx, ny, nz);
     return cudaGetLastError();
 }
 

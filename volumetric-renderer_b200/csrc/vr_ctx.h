@@ -71,7 +71,9 @@ struct MarchParams {
     int occ_stride[3]; /* distance-map index = sum c[a] * occ_stride[a] (sampling-space order) */
     int occ_words;
     float occ_scale[3], occ_off[3]; /* cell = int(pos * occ_scale - occ_off) */
-    const unsigned char *dist; /* per cell: Chebyshev distance (cells) to the nearest occupied cell, 0 = occupied */
+    const unsigned char *dist; /* 8 maps (one per direction octant) x cells: edge of the largest empty cube with the cell at
+                                * its corner, extending along the octant; 0 = occupied (volume.cu k_octant_distance) */
+    uint32_t occ_oct[3];       /* offset of the octant's map contributed by a negative direction on sampling axis a */
     float occ_f_hi[3]; /* extent of the volume in fine-cell units (local texture) */
     /* outputs */
     uchar4 *out;
@@ -153,7 +155,8 @@ struct vr_ctx {
     float2 *d_cell_range = nullptr; /* per cell (min,max) incl. 1-voxel apron and border zeros */
     uint32_t *d_occ = nullptr;
     int occ_words = 0;
-    unsigned char *d_dist = nullptr, *d_dist_tmp = nullptr;
+    unsigned char *d_dist = nullptr; /* 8 x cells */
+    uint32_t *d_sat = nullptr;       /* summed-volume table of the occupancy bits, (n+1)^3 */
     bool occ_dirty = true;
     uint64_t occ_empty_cells = 0;
 
@@ -176,7 +179,7 @@ cudaError_t vr_k0_cell_ranges(const void *dev, int dtype, uint32_t nx, uint32_t 
 cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const float4 *d_lut_pad, uint32_t nlut,
                            float min_density, float max_density, uint32_t *d_occ, int occ_words,
                            unsigned long long *d_empty_count, cudaStream_t s);
-cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, unsigned char *d_tmp,
+cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, uint32_t *d_sat,
                            cudaStream_t s);
 /* fill the layered array paired along `axis` (n_axis + 1 layers) from the linear volume; dtype u8 or u16 */
 cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int axis,
