@@ -227,6 +227,29 @@ def run_ours(args):
     host = host[(K - 1) % F]
     checksum = int(host.view(torch.int32).sum().item())
 
+    # ---- what the memory system alone allows: the same frames through the fetch-only build of the kernel ---
+    # (vr_bench_fetch_only: ray setup, stepping and every volume fetch of the frame, no transfer function and
+    # no compositing; a measurement aid, reported beside the rooflines, not part of `value`)
+    fetch_only_ms = None
+    if world == 1 and not args.exact:
+        try:
+            op.bench_fetch_only(True)
+            for j, k in enumerate(warm_frames[:3]):
+                op.set_uniforms(*uniforms[k])
+                op.record(streams[j % F].cuda_stream, j % F)
+            barrier()
+            fork()
+            for j, k in enumerate(my_frames):
+                op.set_uniforms(*uniforms[k])
+                op.record(streams[j % F].cuda_stream, j % F)
+            join()
+            barrier()
+            fetch_only_ms = ev0.elapsed_time(ev1) / K
+        except vr.VrError:
+            fetch_only_ms = None     # empty-space skipping is active for this data: no fetch-only build
+        finally:
+            op.bench_fetch_only(False)
+
     t = torch.tensor([dev_ms, e2e_ms, float(total_ref), float(total_exec)], dtype=torch.float64, device="cuda")
     if world > 1:
         mx = t.clone()
@@ -252,6 +275,7 @@ def run_ours(args):
         step_s = dev_ms * 1e-3 / K                                # one launch per step
         paired = op.last_frame_paired()
         tex_peak = vr.bench_tex_peak(local, dtype, 2 if paired else 1)
+        tex3d_peak = vr.bench_tex_peak(local, dtype, 1) if paired else tex_peak   # one 3-D trilinear fetch per sample
         exec_rate = (total_exec / K) / step_s
         line = {
             "metric": "ray samples/s @1920x1080, 512^3 u16" if args.workload == "c2" else f"ray samples/s ({args.workload})",
@@ -272,7 +296,10 @@ def run_ours(args):
                          "algorithmic_bytes_per_launch": alg_bytes},
             "roofline_tex": {"bound": "tex", "achieved": exec_rate / 1e9, "peak": tex_peak / 1e9, "unit": "Gfetch/s",
                              "frac": exec_rate / tex_peak,
-                             "peak_source": "vr_bench_tex_peak: L1-resident " + ("paired-layout bilinear fetches (2-D layered, two z-slices per texel)" if paired else "3-D trilinear fetches") + ", measured in this run"},
+                             "peak_source": "vr_bench_tex_peak: L1-resident " + ("paired-layout bilinear fetches (2-D layered, two z-slices per texel)" if paired else "3-D trilinear fetches") + ", measured in this run",
+                             "frac_of_3d_trilinear_peak": exec_rate / tex3d_peak,
+                             "fetch_only_ms_per_step": fetch_only_ms,
+                             "fetch_only_share_of_step": (fetch_only_ms / (dev_ms / K)) if fetch_only_ms else None},
             "e2e": {"value": all_ref / (e2e_ms * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": 192,
                     "d2h_bytes_per_step": W * H * 4, "ms_per_step": e2e_ms / K, "fps": world * K / (e2e_ms * 1e-3),
                     "frame_checksum": checksum},

@@ -301,6 +301,14 @@ int vr_set_image_target_frame(vr_ctx *ctx, uint32_t frame_index, void *dev_rgba8
  * SMs; returns fetches per second (device-timed).  hw_filter: 0 = point tex3D, 1 = trilinear tex3D
  * (VR_LAYOUT_ARRAY3D's fetch), 2 = bilinear fetch of the paired layered array (VR_LAYOUT_PAIRED's fetch). */
 int vr_bench_tex_peak(int device, int dtype, int hw_filter, double *fetches_per_s);
+/* Measurement aid (bench.py, roofline_tex.fetch_only): while on, vr_render / vr_render_frame run a build of
+ * the march kernel that does everything up to and including the volume fetches of the frame (ray setup,
+ * stepping, the same fetches in the same order) and then only sums the fetched values: no transfer function,
+ * no compositing, no early termination.  Its frame time is what the memory system alone allows for this
+ * frame with this layout.  The image holds no picture while on.  Requires the hardware sampler with
+ * empty-space skipping and statistics off, and a whole (not sort-last) volume; otherwise vr_render fails
+ * with VR_ERR_STATE.  Not part of the reference interface. */
+int vr_bench_fetch_only(vr_ctx *ctx, int on);
 /* Test hook: the 16 floats (4 columns) of inverse(proj * view) the kernel uses. */
 int vr_debug_ray_context(const vr_ctx *ctx, float out[16]);
 

@@ -250,6 +250,10 @@ class OffscreenPass:
         """The display image as binary PPM (or 4-channel PAM if the name ends in .pam)."""
         self._check(lib.vr_write_image(self._h, str(path).encode()))
 
+    def bench_fetch_only(self, on: bool):
+        """Measurement aid (include/vr.h vr_bench_fetch_only): frames run the fetch-only build of the march kernel."""
+        self._check(lib.vr_bench_fetch_only(self._h, int(bool(on))))
+
     def download_async(self, host_ptr: int, stream: int | None = None, frame_index: int = 0):
         self._check(lib.vr_download_frame_async(self._h, frame_index, host_ptr, stream))
 

@@ -95,6 +95,7 @@ SIGNATURES = {
     "vr_partition_box": (C.c_int, [_P, _P, C.c_uint32, _P, _P]),
     "vr_partition_order": (C.c_int, [_P, _P, _P, _P]),
     "vr_bench_tex_peak": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]),
+    "vr_bench_fetch_only": (C.c_int, [_P, C.c_int]),
     "vr_debug_ray_context": (C.c_int, [_P, _P]),
 }
 

@@ -855,9 +855,22 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     p.out = target;
     if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
+    if (c->bench_fetch_only) {
+        if (exact || ess || c->opt.collect_stats || c->sort_last || (pair && p.pair_split != 0x10000))
+            return fail(c, VR_ERR_STATE, "vr_bench_fetch_only: hardware sampler, no skipping, no statistics, whole volume, pair copy in one array");
+        VR_CUDA(c, vr_launch_march_probe(p, pair, c->tune_threads, s));
+        return VR_OK;
+    }
     VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, pair, c->tune_batch, c->tune_threads, s));
     if (c->opt.collect_stats)
         VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    return VR_OK;
+}
+
+extern "C" int vr_bench_fetch_only(vr_ctx *c, int on)
+{
+    if (!c) return VR_ERR_INVALID;
+    c->bench_fetch_only = on != 0;
     return VR_OK;
 }
 

@@ -8,11 +8,15 @@
  * and the fixed-function blend over the clear colour into RGBA8 (offscreen_pass.cpp:170-173,
  * :715-725,:293).
  *
- * Mapping: a CTA of 256 threads owns a 16x16 pixel tile; each warp an 8x4 block of it, so the
- * 32 rays of a warp stay within a few voxels of one another at every step and share texture
- * cache lines.  The transfer function (decoded sRGB -> linear fp32, edge-padded so the two
- * taps need no clamp) and the occupancy bit grid are staged in shared memory.  The volume is
- * a 3-D CUDA array (hardware block-linear = bricked layout) read through texture objects.
+ * Mapping: a CTA of 128 threads (tunable, at most VR_CTA_THREADS) owns a 16x8 pixel tile (tiles are walked in a spiral from the
+ * centre of the cube's screen bounding box, the remaining CTAs clear the rest of the target); each warp an
+ * 8x4 block of it, so the 32 rays of a warp stay within a few voxels of one another at every step and share
+ * texture cache lines.  The transfer function is staged in shared memory (exact sampler: decoded sRGB ->
+ * linear fp32, edge-padded so the two taps need no clamp; hardware sampler: fp16 midpoint/difference pairs,
+ * see lut_eval).  The volume is read through texture objects: a 3-D CUDA array (hardware block-linear =
+ * bricked layout, one trilinear fetch per sample) or one of the paired 2-D layered copies (one bilinear
+ * fetch + one fp32 lerp per sample, see fetch_pair).  Empty-space skipping reads per-octant distance maps
+ * from global memory (see skip_empty).
  *
  * This file is compiled with -fmad=false: every fp32 operation rounds once, in the order
  * written, so ray entry and the sample positions (volume.frag:47 accumulates them) are
@@ -338,7 +342,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
 }
 
 /* Second half: normalise, transfer function, composite (volume.frag:42-45). */
-template <bool EXACT, bool STATS, int PAIR, int U, bool PRED, bool ERT = true>
+template <bool EXACT, bool STATS, int PAIR, int U, bool PRED, bool ERT = true, bool PROBE = false>
 __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batch<U> &b, const float4 *sP,
                                               const LutH &L)
 {
@@ -368,6 +372,10 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
                 if (r.T < p.ert_eps) r.stop = true, r.done = true;
             } else {
                 const float dens = PAIR ? fmaf(b.frac[u], b.val2[u] - b.val[u], b.val[u]) : b.val[u];
+                if (PROBE) { /* measurement build: the fetched value is consumed, nothing else (vr_bench_fetch_only) */
+                    r.cr += dens;
+                    continue;
+                }
                 lut_eval(L, dens, sr, sg, sb, sa);
                 const float ta = r.T * sa;
                 r.cr = fmaf(ta, sr, r.cr);
@@ -385,7 +393,7 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
 /* EXACT: verification sampler.  ESS: occupancy grid consulted.  STATS: sample counters.
  * PART: sort-last sub-volume.  PAIR: 0 = 3-D array, 1 = paired layout, 2 = paired layout whose copy spans
  * two layered arrays.  UB: steps per batch (HW sampler; two batches are in flight). */
-template <bool EXACT, bool ESS, bool STATS, bool PART, int PAIR, int UB>
+template <bool EXACT, bool ESS, bool STATS, bool PART, int PAIR, int UB, bool PROBE = false>
 __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant__ MarchParams p)
 {
     extern __shared__ float4 smem[];
@@ -406,7 +414,9 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
             int r = (int)ceilf((sqrtf((float)(b + 1)) - 1.0f) * 0.5f);
             while ((2 * r - 1) * (2 * r - 1) > b) r--;
             while ((2 * r + 1) * (2 * r + 1) <= b) r++;
-            const int k = b - (2 * r - 1) * (2 * r - 1), seg = k / (2 * r), off = k - seg * 2 * r;
+            /* ring r holds 8r tiles, four sides of 2r: no integer division */
+            const int k = b - (2 * r - 1) * (2 * r - 1), r2 = 2 * r;
+            const int seg = (k >= r2) + (k >= 2 * r2) + (k >= 3 * r2), off = k - seg * r2;
             if (seg == 0) ox = r, oy = -r + 1 + off;
             else if (seg == 1) ox = r - 1 - off, oy = r;
             else if (seg == 2) ox = -r, oy = r - 1 - off;
@@ -418,14 +428,16 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         /* clear colour only (offscreen_pass.cpp:170-173): a block clears a 64x32 pixel region in groups of
          * four pixels (one 16-byte store), leaving out the tiles the spiral blocks own */
         const uint32_t j = blockIdx.x - p.sp_count;
-        const uint32_t ry = (j / p.nclr_x) * 32u, rx = (j % p.nclr_x) * 64u;
+        const uint32_t jy = j / p.nclr_x;
+        const uint32_t ry = jy * 32u, rx = (j - jy * p.nclr_x) * 64u;
         const uint32_t c8 = (uint32_t)(VR_CLEAR_RGB * 255.0f + 0.5f), cw = c8 | (c8 << 8) | (c8 << 16) | 0xff000000u;
         const bool wide = (p.W & 3u) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;
+        /* the spiral blocks' rectangle in pixels (a group of four pixels never straddles a 16-pixel tile column) */
+        const int rpx0 = p.rect[0] * VR_TILE, rpx1 = p.rect[2] * VR_TILE, rpy0 = p.rect[1] * (int)p.tile_h, rpy1 = p.rect[3] * (int)p.tile_h;
         for (uint32_t g = threadIdx.x; g < 512u; g += nthreads) {
             const uint32_t gx = rx + (g & 15u) * 4u, gy = ry + (g >> 4);
             if (gx >= p.W || gy >= p.H) continue;
-            const int ttx = (int)(gx / VR_TILE), tty = (int)(gy / p.tile_h);
-            if (ttx >= p.rect[0] && tty >= p.rect[1] && ttx < p.rect[2] && tty < p.rect[3]) continue;
+            if ((int)gx >= rpx0 && (int)gy >= rpy0 && (int)gx < rpx1 && (int)gy < rpy1) continue;
             if (p.pt_nranks > 1 && ((gy / p.pt_px) * p.pt_nx + gx / p.pt_px) % p.pt_nranks != p.pt_rank) continue;
             const size_t gp = (size_t)gy * p.W + gx;
             if (wide) {
@@ -445,9 +457,10 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     /* warp footprint ww x (32/ww) pixels, warps tiled across the 16-pixel-wide CTA tile */
-    const uint32_t ww = p.warp_w, wh = 32u / ww, wpr = VR_TILE / ww;
-    const uint32_t px = x0 + (warp % wpr) * ww + (lane % ww);
-    const uint32_t py = y0 + (warp / wpr) * wh + (lane / ww);
+    /* ww is 4, 8 or 16 (api.cu): shifts and masks, no integer division */
+    const uint32_t ws = 31u - (uint32_t)__clz((int)p.warp_w), ww = 1u << ws, wh = 32u >> ws, wprs = 4u - ws;
+    const uint32_t px = x0 + ((warp & ((1u << wprs) - 1u)) << ws) + (lane & (ww - 1u));
+    const uint32_t py = y0 + (warp >> wprs) * wh + (lane >> ws);
     const bool valid = px < p.W && py < p.H;
     const size_t pix = (size_t)py * p.W + px;
 
@@ -534,8 +547,8 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     } while (0)
 #define VR_CONSUME(B_)                                                                                      \
     do {                                                                                                    \
-        if (B_.pred) batch_consume<EXACT, STATS, PAIR, U, true>(p, ray, B_, sP, L);                         \
-        else batch_consume<EXACT, STATS, PAIR, U, false>(p, ray, B_, sP, L);                                \
+        if (B_.pred) batch_consume<EXACT, STATS, PAIR, U, true, true, PROBE>(p, ray, B_, sP, L);            \
+        else batch_consume<EXACT, STATS, PAIR, U, false, true, PROBE>(p, ray, B_, sP, L);                   \
     } while (0)
     if (EXACT) {
         Batch<U> a;
@@ -566,12 +579,12 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
 #pragma unroll 1
                 for (int it = 0; it < nb; it++) {
                     batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, b);
-                    batch_consume<false, STATS, PAIR, U, false, false>(p, ray, a, sP, L);
+                    batch_consume<false, STATS, PAIR, U, false, false, PROBE>(p, ray, a, sP, L);
                     batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, a);
-                    batch_consume<false, STATS, PAIR, U, false, false>(p, ray, b, sP, L);
+                    batch_consume<false, STATS, PAIR, U, false, false, PROBE>(p, ray, b, sP, L);
                     if (__all_sync(0xffffffffu, ray.T < p.ert_eps)) break; /* parked lanes: T = 0 (never true when ERT is off: nb bounds the loop) */
                 }
-                batch_consume<false, STATS, PAIR, U, false, false>(p, ray, a, sP, L);
+                batch_consume<false, STATS, PAIR, U, false, false, PROBE>(p, ray, a, sP, L);
                 if (!ray.done && ray.T < p.ert_eps) ray.stop = true, ray.done = true;
                 continue;
             }
@@ -686,6 +699,17 @@ size_t vr_march_smem_bytes(const MarchParams &p, bool exact)
 {
     /* EXACT: nlut + 3 float4 texels; HW: nlut + 2 packed fp16 entries.  The distance map is read from global memory. */
     return exact ? sizeof(float4) * (size_t)(p.nlut + 3) : sizeof(uint4) * (size_t)(p.nlut + 2);
+}
+
+cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int threads, cudaStream_t s)
+{
+    const uint64_t ctas = (uint64_t)p.sp_count + (uint64_t)p.nclr_x * p.nclr_y;
+    if (ctas == 0) return cudaSuccess;
+    if (ctas > 0x7fffffffull || (pair && p.pair_split != 0x10000)) return cudaErrorInvalidConfiguration;
+    const size_t smem = vr_march_smem_bytes(p, false);
+    if (pair) k_march<false, false, false, false, 1, 4, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+    else k_march<false, false, false, false, 0, 4, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+    return cudaGetLastError();
 }
 
 cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, bool pair, int ub,

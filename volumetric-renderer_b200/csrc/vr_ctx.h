@@ -156,6 +156,7 @@ struct vr_ctx {
     uint32_t *d_occ = nullptr;
     int occ_words = 0;
     unsigned char *d_dist = nullptr; /* 8 x cells */
+    bool bench_fetch_only = false;   /* vr_bench_fetch_only: frames run the fetch-only build of K1 */
     uint32_t *d_sat = nullptr;       /* summed-volume table of the occupancy bits, (n+1)^3 */
     bool occ_dirty = true;
     uint64_t occ_empty_cells = 0;
@@ -168,6 +169,7 @@ struct vr_ctx {
 /* ---- kernels / device-side stages (each .cu implements its own) ---- */
 
 /* K1 (march.cu) */
+cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int threads, cudaStream_t s);
 cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, bool pair, int ub,
                             int threads, cudaStream_t s);
 size_t vr_march_smem_bytes(const MarchParams &p, bool ess);
