@@ -858,7 +858,7 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     if (c->bench_fetch_only) {
         if (exact || ess || c->opt.collect_stats || c->sort_last || (pair && p.pair_split != 0x10000))
             return fail(c, VR_ERR_STATE, "vr_bench_fetch_only: hardware sampler, no skipping, no statistics, whole volume, pair copy in one array");
-        VR_CUDA(c, vr_launch_march_probe(p, pair, c->tune_threads, s));
+        VR_CUDA(c, vr_launch_march_probe(p, pair, c->tune_batch, c->tune_threads, s));
         return VR_OK;
     }
     VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, pair, c->tune_batch, c->tune_threads, s));

@@ -701,14 +701,20 @@ size_t vr_march_smem_bytes(const MarchParams &p, bool exact)
     return exact ? sizeof(float4) * (size_t)(p.nlut + 3) : sizeof(uint4) * (size_t)(p.nlut + 2);
 }
 
-cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int threads, cudaStream_t s)
+cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int ub, int threads, cudaStream_t s)
 {
     const uint64_t ctas = (uint64_t)p.sp_count + (uint64_t)p.nclr_x * p.nclr_y;
     if (ctas == 0) return cudaSuccess;
     if (ctas > 0x7fffffffull || (pair && p.pair_split != 0x10000)) return cudaErrorInvalidConfiguration;
     const size_t smem = vr_march_smem_bytes(p, false);
-    if (pair) k_march<false, false, false, false, 1, 4, true><<<(unsigned)ctas, threads, smem, s>>>(p);
-    else k_march<false, false, false, false, 0, 4, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+    /* same steps per batch as the product launch */
+    if (ub == 4) {
+        if (pair) k_march<false, false, false, false, 1, 4, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+        else k_march<false, false, false, false, 0, 4, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+    } else {
+        if (pair) k_march<false, false, false, false, 1, 2, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+        else k_march<false, false, false, false, 0, 2, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+    }
     return cudaGetLastError();
 }
 

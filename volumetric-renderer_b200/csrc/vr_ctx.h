@@ -169,7 +169,7 @@ struct vr_ctx {
 /* ---- kernels / device-side stages (each .cu implements its own) ---- */
 
 /* K1 (march.cu) */
-cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int threads, cudaStream_t s);
+cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int ub, int threads, cudaStream_t s);
 cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, bool pair, int ub,
                             int threads, cudaStream_t s);
 size_t vr_march_smem_bytes(const MarchParams &p, bool ess);
