@@ -145,6 +145,14 @@ int vr_load_nrrd(vr_ctx *ctx, const char *path);
  * *data is malloc'd (release with vr_free_host); errbuf receives the message on failure. */
 int vr_nrrd_read_host(const char *path, int *dtype, uint32_t dims[3], void **data, char *errbuf, size_t errbuf_len);
 void vr_free_host(void *p);
+/* CsvFileParser::parse + volume_dataset_changed (src/data/importer.cpp:30-46, src/data/csv_file_parser.cpp:14-50):
+ * one CSV file per z slice, one line per y row, comma-separated floats along x.  min/max are the
+ * reference's (they start at 0, so min <= 0 <= max).  Errors: VR_ERR_FORMAT with the reference's message
+ * ("Inconsistant dimensions", or std::stof's for a field that is not a number). */
+int vr_load_csv(vr_ctx *ctx, const char *const *paths, uint32_t npaths);
+/* The parser alone, no context and no GPU.  *data is malloc'd (release with vr_free_host). */
+int vr_csv_read_host(const char *const *paths, uint32_t npaths, uint32_t dims[3], float **data, float *min_density,
+                     float *max_density, char *errbuf, size_t errbuf_len);
 int vr_get_volume_info(const vr_ctx *ctx, int *dtype, uint32_t dims[3], float *min_density, float *max_density);
 /* Overwrite ubo.min_density / max_density (offscreen_pass.cpp:265-266), e.g. with the global
  * range after each sort-last rank measured its own sub-volume. */

@@ -154,6 +154,24 @@ class Oracle:
         self.lib.vro_free(ptr)
         return arr.reshape(dims[2], dims[1], dims[0]), mn.value, mx.value
 
+    def load_csv(self, paths):
+        """CsvFileParser(paths).parse() of the reference build; raises RuntimeError(e.what()) like the importer's popup."""
+        arr = (C.c_char_p * len(paths))(*[str(p).encode() for p in paths])
+        dims = (C.c_uint32 * 3)()
+        mn, mx = C.c_float(), C.c_float()
+        ptr = C.c_void_p()
+        msg = C.create_string_buffer(256)
+        self.lib.vro_load_csv.restype = C.c_int
+        self.lib.vro_load_csv.argtypes = [C.POINTER(C.c_char_p), C.c_uint32, C.c_void_p, C.POINTER(C.c_float),
+                                          C.POINTER(C.c_float), C.POINTER(C.c_void_p), C.c_char_p, C.c_size_t]
+        rc = self.lib.vro_load_csv(arr, len(paths), dims, C.byref(mn), C.byref(mx), C.byref(ptr), msg, len(msg))
+        if rc != 0:
+            raise RuntimeError(msg.value.decode() or f"vro_load_csv failed: {rc}")
+        n = dims[0] * dims[1] * dims[2]
+        a = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float)), shape=(max(n, 1),))[:n].copy()
+        self.lib.vro_free(ptr)
+        return a.reshape(dims[2], dims[1], dims[0]), mn.value, mx.value
+
     def synth(self, kind: int, seed: int, dtype, n, nthreads=0) -> np.ndarray:
         nx, ny, nz = (n, n, n) if isinstance(n, int) else n
         code = dtype if isinstance(dtype, int) else _DTYPE_OF[np.dtype(dtype)]

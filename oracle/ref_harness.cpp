@@ -20,6 +20,7 @@
 #include <glm/gtc/matrix_transform.hpp>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <filesystem>
@@ -29,6 +30,7 @@
 #include <omp.h>
 #endif
 
+#include "data/csv_file_parser.h"
 #include "data/nrrd_file_parser.h"
 #include "scene/camera.h"
 #include "ui/components/gradient.h"
@@ -188,6 +190,30 @@ extern "C" int vro_load_nrrd(const char *path, uint32_t dims[3], float *min, flo
         return 0;
     } catch (const std::exception &) {
         return -1; /* importer.cpp:47-49 shows a popup; here: error code */
+    }
+}
+
+/* ------------------------------------------------------------------- csv -- */
+
+/* The reference's own CsvFileParser (src/data/csv_file_parser.cpp).  msg receives e.what() on failure. */
+extern "C" int vro_load_csv(const char *const *paths, uint32_t npaths, uint32_t dims[3], float *min, float *max,
+                            float **data, char *msg, size_t msg_len)
+{
+    try {
+        std::vector<std::filesystem::path> v;
+        for (uint32_t i = 0; i < npaths; i++) v.emplace_back(paths[i]);
+        Vol::Data::CsvFileParser parser{v};
+        Vol::Data::Dataset ds = parser.parse();
+        dims[0] = ds.dimensions.x, dims[1] = ds.dimensions.y, dims[2] = ds.dimensions.z;
+        *min = ds.min;
+        *max = ds.max;
+        *data = static_cast<float *>(std::malloc(sizeof(float) * (ds.data.size() + 1)));
+        if (!*data) return -3;
+        if (!ds.data.empty()) std::memcpy(*data, ds.data.data(), sizeof(float) * ds.data.size());
+        return 0;
+    } catch (const std::exception &e) {
+        if (msg && msg_len) std::snprintf(msg, msg_len, "%s", e.what());
+        return -1; /* importer.cpp:47-49 shows a popup with this text */
     }
 }
 

@@ -358,4 +358,11 @@ int vro_load_nrrd(const char *path, uint32_t dims[3], float *min, float *max, fl
     return -1; /* reference build only */
 }
 
+int vro_load_csv(const char *const *paths, uint32_t npaths, uint32_t dims[3], float *min, float *max, float **data,
+                 char *msg, size_t msg_len)
+{
+    (void)paths, (void)npaths, (void)dims, (void)min, (void)max, (void)data, (void)msg, (void)msg_len;
+    return -1; /* reference build only */
+}
+
 void vro_free(void *p) { free(p); }

@@ -100,6 +100,9 @@ void vro_gradient_discretize(const float *color_markers, uint32_t nc, const floa
  * NrrdFileParser::parse (src/data/nrrd_file_parser.cpp:21-47).  On success *data is a
  * malloc'd float array (caller frees with vro_free). */
 int vro_load_nrrd(const char *path, uint32_t dims[3], float *min, float *max, float **data);
+/* reference build only (port: -1): CsvFileParser::parse, src/data/csv_file_parser.cpp:14-50 */
+int vro_load_csv(const char *const *paths, uint32_t npaths, uint32_t dims[3], float *min, float *max, float **data,
+                 char *msg, size_t msg_len);
 void vro_free(void *);
 
 /* Synthetic volumes of SURVEY.md section 8(d) (port build only; reference returns -1).

@@ -484,3 +484,37 @@ def test_frames_in_flight_do_not_interfere(vr, port):
             assert np.array_equal(hosts[k].numpy(), want[k])
     finally:
         op.close()
+
+
+def test_csv_import_renders_like_the_same_dataset_set_directly(vr, port, tmp_path):
+    """vr_load_csv = CsvFileParser::parse + volume_dataset_changed (importer.cpp:30-46): float voxels, the
+    reference's min <= 0 <= max as the density range."""
+    vol = small_volume(port, 1, np.uint16, 24).astype(np.float32) / 7.0 + 3.0
+    paths = []
+    for z, sl in enumerate(vol):
+        p = tmp_path / f"z{z:02d}.csv"
+        p.write_text("\n".join(",".join("%.9g" % v for v in row) for row in sl) + "\n")
+        paths.append(str(p))
+    lut = tf(port, "B")
+    cam, ocam = twin_cameras(vr, port, [(30, 20)])
+    imgs = []
+    for how in ("csv", "direct"):
+        op = vr.OffscreenPass(W, H)
+        try:
+            op.set_options(sampler=vr.SAMPLER_EXACT, write_raw=1)
+            if how == "csv":
+                op.load_csv(paths)
+                dtype, dims, mn, mx = op.volume_info()
+                assert dtype == vr.F32 and tuple(dims) == (24, 24, 24)
+                assert mn == 0.0 and mx == float(vol.max())
+            else:
+                op.volume_dataset_changed(vr.Dataset(vol, 0.0, float(vol.max())))
+            op.transfer_function_changed(lut)
+            op.set_camera(cam)
+            op.record()
+            imgs.append((op.download(), op.download_raw()))
+        finally:
+            op.close()
+    assert np.array_equal(imgs[0][0], imgs[1][0]) and np.array_equal(bits(imgs[0][1]), bits(imgs[1][1]))
+    o = port.render(oracle_frame(port, ocam, W, H, 0.0, float(vol.max()), (0, 0, 0), (1, 1, 1)), vol, lut, want_raw=True)
+    assert np.array_equal(bits(imgs[0][1]), bits(o["raw"]))

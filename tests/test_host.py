@@ -170,6 +170,77 @@ def test_nrrd_reader_rejects_what_the_reference_rejects(vr, ref, tmp_path):
 
 # ---- partition helpers -----------------------------------------------------------------------------
 
+def write_csv_stack(tmp_path, vol, fmt="%.9g", eol="\n", last_eol=True, name="s"):
+    paths = []
+    for z, sl in enumerate(vol):
+        text = eol.join(",".join(fmt % v for v in row) for row in sl) + (eol if last_eol else "")
+        p = tmp_path / f"{name}{z:03d}.csv"
+        p.write_bytes(text.encode())
+        paths.append(str(p))
+    return paths
+
+
+@pytest.mark.parametrize("eol,last_eol", [("\n", True), ("\n", False), ("\r\n", True)])
+def test_csv_reader_matches_reference_parser(vr, ref, tmp_path, eol, last_eol):
+    """src/data/csv_file_parser.cpp:14-50 compiled as it lies (oracle/_ref) against the product's reader."""
+    rng = np.random.default_rng(5)
+    vol = rng.normal(3.0, 50.0, (4, 5, 7)).astype(np.float32)
+    vol[1, 2, 3] = 1e-3
+    paths = write_csv_stack(tmp_path, vol, eol=eol, last_eol=last_eol)
+    got = vr.read_csv(paths)
+    want, mn, mx = ref.load_csv(paths)
+    assert got.data.shape == want.shape == vol.shape
+    assert np.array_equal(bits(got.data), bits(want))
+    assert np.array_equal(bits(got.data), bits(vol))  # %.9g round-trips a float
+    assert (got.min, got.max) == (mn, mx)
+    # all-positive data: the reference's minimum is still 0 (value-initialised Dataset)
+    pos = np.abs(vol) + 1.0
+    q = write_csv_stack(tmp_path, pos, name="p")
+    g2, (w2, mn2, mx2) = vr.read_csv(q), ref.load_csv(q)
+    assert g2.min == mn2 == 0.0 and g2.max == mx2 == float(pos.max())
+
+
+def test_csv_reader_field_and_line_rules(vr, ref, tmp_path):
+    """Trailing separators, blanks, exponents, inf/nan, trailing characters: whatever std::getline + std::stof accept."""
+    a, b = tmp_path / "a.csv", tmp_path / "b.csv"
+    a.write_bytes(b" 1.5, -2e3 ,0x10,\n7abc,nan,inf,\n")
+    b.write_bytes(b"1,2,3\n4,5,6")
+    got = vr.read_csv([str(a), str(b)])
+    want, mn, mx = ref.load_csv([str(a), str(b)])
+    assert got.data.shape == want.shape == (2, 2, 3)
+    assert np.array_equal(bits(got.data), bits(want))
+    assert np.array_equal(bits(np.float32([got.min, got.max])), bits(np.float32([mn, mx])))
+    assert got.data[0, 0].tolist() == [1.5, -2000.0, 16.0] and got.data[0, 1, 0] == 7.0 and np.isnan(got.data[0, 1, 1])
+    # no files at all / an unreadable file: zero extents, no error (the reference never checks the stream)
+    for paths in ([], [str(tmp_path / "missing.csv")]):
+        g, (w, _, _) = vr.read_csv(paths), ref.load_csv(paths)
+        assert g.data.shape == w.shape and g.data.size == 0
+
+
+@pytest.mark.parametrize("files,message", [
+    ([b"1,2,3\n4,5\n"], "Inconsistant dimensions"),               # ragged line
+    ([b"1,2\n3,4\n", b"1,2\n"], "Inconsistant dimensions"),       # slice with fewer lines
+    ([b"1,2\n3,4\n", b"1,2\n3,4\n5,6\n"], "Inconsistant dimensions"),
+    ([b"1,2\n\n3,4\n"], "Inconsistant dimensions"),               # blank line = zero fields
+    ([b"1,,3\n"], "stof"),                                         # empty field
+    ([b"1,x,3\n"], "stof"),
+    ([b"1,1e99,3\n"], "stof"),                                     # out of float range
+    ([b"1,2\r\n\r\n"], "stof"),                                   # a line holding only a carriage return
+])
+def test_csv_reader_rejects_what_the_reference_rejects(vr, ref, tmp_path, files, message):
+    paths = []
+    for i, content in enumerate(files):
+        p = tmp_path / f"e{i}.csv"
+        p.write_bytes(content)
+        paths.append(str(p))
+    with pytest.raises(RuntimeError) as want:
+        ref.load_csv(paths)
+    with pytest.raises(vr.VrError) as got:
+        vr.read_csv(paths)
+    assert message in str(want.value) and message in str(got.value)
+    assert str(want.value) in str(got.value)  # the text the reference's error popup would show
+
+
 def test_partition_boxes_tile_the_grid(vr):
     for grid, full in [((2, 2, 2), (64, 64, 64)), ((3, 2, 1), (50, 33, 7)), ((1, 1, 1), (5, 5, 5)), ((2, 1, 1), (7, 3, 3))]:
         seen = np.zeros(full[::-1], np.int32)

@@ -140,6 +140,11 @@ class OffscreenPass:
     def framebuffer_size_changed(self, width: int, height: int):
         self._check(lib.vr_resize(self._h, width, height))
 
+    def load_csv(self, paths):
+        """Importer::import(FileFormat::CSV) without the dialog (src/data/importer.cpp:30-46)."""
+        arr = (C.c_char_p * len(paths))(*[str(p).encode() for p in paths])
+        self._check(lib.vr_load_csv(self._h, arr, len(paths)))
+
     def volume_dataset_changed(self, dataset: Dataset):
         a = dataset.data
         if a.dtype not in _CODE:
@@ -346,6 +351,24 @@ def read_nrrd(path: str) -> np.ndarray:
         np_dt = np.dtype(_NP[dt.value])
         buf = (C.c_char * (n * np_dt.itemsize)).from_address(data.value)
         return np.frombuffer(buf, np_dt).reshape(dims[2], dims[1], dims[0]).copy()
+    finally:
+        lib.vr_free_host(data)
+
+
+def read_csv(paths) -> "Dataset":
+    """CsvFileParser(paths).parse() of the reference (src/data/csv_file_parser.cpp:14-50), host only: one CSV file
+    per z slice -> Dataset(float32 [nz, ny, nx], min, max) with the reference's min <= 0 <= max."""
+    arr = (C.c_char_p * len(paths))(*[str(p).encode() for p in paths])
+    dims, data, mn, mx = (C.c_uint32 * 3)(), C.c_void_p(), C.c_float(), C.c_float()
+    err = C.create_string_buffer(512)
+    rc = lib.vr_csv_read_host(arr, len(paths), dims, C.byref(data), C.byref(mn), C.byref(mx), err, len(err))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, err.value.decode())
+    try:
+        n = dims[0] * dims[1] * dims[2]
+        buf = (C.c_float * n).from_address(data.value) if n else []
+        a = np.array(buf, np.float32).reshape(dims[2], dims[1], dims[0])
+        return Dataset(a, mn.value, mx.value)
     finally:
         lib.vr_free_host(data)
 

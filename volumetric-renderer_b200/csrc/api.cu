@@ -1185,6 +1185,37 @@ extern "C" int vr_nrrd_read_host(const char *path, int *dtype, uint32_t dims[3],
 
 extern "C" void vr_free_host(void *p) { std::free(p); }
 
+/* CSV slices (src/data/csv_file_parser.cpp:14-50 through src/data/importer.cpp:30-46) */
+extern "C" int vr_csv_read_host(const char *const *paths, uint32_t npaths, uint32_t dims[3], float **data, float *mn, float *mx,
+                                char *errbuf, size_t errbuf_len)
+{
+    if (!paths || !dims || !data || !mn || !mx) return VR_ERR_INVALID;
+    VrCsv v;
+    std::string err;
+    const int rc = vr_csv_read(paths, npaths, v, err);
+    if (rc != VR_OK) {
+        if (errbuf && errbuf_len) std::snprintf(errbuf, errbuf_len, "%s", err.c_str());
+        return rc;
+    }
+    float *p = static_cast<float *>(std::malloc(std::max<size_t>(v.data.size(), 1) * sizeof(float)));
+    if (!p) return VR_ERR_NOMEM;
+    if (!v.data.empty()) std::memcpy(p, v.data.data(), v.data.size() * sizeof(float));
+    dims[0] = v.dims[0], dims[1] = v.dims[1], dims[2] = v.dims[2], *data = p, *mn = v.min, *mx = v.max;
+    return VR_OK;
+}
+
+extern "C" int vr_load_csv(vr_ctx *c, const char *const *paths, uint32_t npaths)
+{
+    if (!c || !paths) return fail(c, VR_ERR_INVALID, "vr_load_csv: null argument");
+    VrCsv v;
+    std::string err;
+    const int rc = vr_csv_read(paths, npaths, v, err);
+    if (rc != VR_OK) return fail(c, rc, err);
+    if (!v.dims[0] || !v.dims[1] || !v.dims[2] || v.data.size() != (size_t)v.dims[0] * v.dims[1] * v.dims[2])
+        return fail(c, VR_ERR_FORMAT, "vr_load_csv: empty dataset"); /* the reference would ask Vulkan for a zero-sized image */
+    return vr_set_volume(c, v.data.data(), VR_F32, v.dims[0], v.dims[1], v.dims[2], &v.min, &v.max);
+}
+
 /* ============================================== peer memory (one process per GPU) == */
 
 extern "C" int vr_set_image_target(vr_ctx *c, void *dev_rgba8) { return vr_set_image_target_frame(c, 0, dev_rgba8); }

@@ -28,3 +28,11 @@ struct VrNrrdPayload {
  * *payload says where to stream it from (vr_load_nrrd does that through pinned memory). */
 int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err, VrNrrdPayload *payload = nullptr);
 #endif
+
+/* Stack of CSV slices (csv.cpp): what the reference's CsvFileParser::parse returns. */
+struct VrCsv {
+    uint32_t dims[3] = {0, 0, 0}; /* x = fields per line, y = lines per file, z = files */
+    float min = 0.0f, max = 0.0f; /* both start at 0, like the reference's value-initialised Dataset */
+    std::vector<float> data;      /* x fastest */
+};
+int vr_csv_read(const char *const *paths, uint32_t npaths, VrCsv &out, std::string &err);

@@ -146,6 +146,13 @@ class OffscreenPass
 
     // Importer::import(FileFormat::Nrrd) without the dialog (importer.cpp:36-46)
     void import_nrrd(const std::string &path) { check(vr_load_nrrd(ctx, path.c_str())); }
+    // Importer::import(FileFormat::CSV) without the dialog (importer.cpp:30-46): one file per z slice
+    void import_csv(const std::vector<std::string> &paths)
+    {
+        std::vector<const char *> p;
+        for (const std::string &s : paths) p.push_back(s.c_str());
+        check(vr_load_csv(ctx, p.data(), (uint32_t)p.size()));
+    }
     void set_uniforms(const mat4 &view, const mat4 &proj, const vec3 &camera_position)
     {
         check(vr_set_camera(ctx, view.data(), proj.data(), camera_position.data()));
