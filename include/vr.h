@@ -198,6 +198,12 @@ int vr_download_raw(vr_ctx *ctx, float *host_rgba_f32);
 /* The display image as a file: binary PPM (P6, the alpha channel is dropped) or, if `path` ends in
  * ".pam", PAM with all four channels.  Stands where the reference hands the image to ImGui for display
  * (src/ui/main_window.cpp:159-165); there is no window on a headless box.  Synchronises. */
+/* The step after the path: the viewport samples the offscreen image with LINEAR filters and CLAMP_TO_EDGE
+ * addressing (offscreen_pass.cpp:361-375, main_window.cpp:157-165).  Resamples frame `frame_index` into a
+ * device RGBA8 buffer of dst_width x dst_height (dst_pitch_bytes = 0: tightly packed) with that filter, on
+ * cuda_stream (NULL: the stream of the last render).  Same size = copy.  Zero size = no-op. */
+int vr_present_frame(vr_ctx *ctx, uint32_t frame_index, void *dst_dev_rgba8, uint32_t dst_width, uint32_t dst_height,
+                     size_t dst_pitch_bytes, void *cuda_stream);
 int vr_write_image(vr_ctx *ctx, const char *path);
 int vr_get_stats(vr_ctx *ctx, vr_stats *out);
 int vr_get_size(const vr_ctx *ctx, uint32_t *width, uint32_t *height);

@@ -154,6 +154,17 @@ class Oracle:
         self.lib.vro_free(ptr)
         return arr.reshape(dims[2], dims[1], dims[0]), mn.value, mx.value
 
+    def present_bilinear(self, src: np.ndarray, width: int, height: int) -> np.ndarray:
+        """The viewport sampler (LINEAR, CLAMP_TO_EDGE) applied to an RGBA8 frame [h, w, 4] -> [height, width, 4]."""
+        src = np.ascontiguousarray(src, np.uint8)
+        dst = np.empty((height, width, 4), np.uint8)
+        self.lib.vro_present_bilinear.restype = C.c_int
+        self.lib.vro_present_bilinear.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32]
+        rc = self.lib.vro_present_bilinear(src.ctypes.data, src.shape[1], src.shape[0], dst.ctypes.data, width, height)
+        if rc != 0:
+            raise RuntimeError(f"vro_present_bilinear failed: {rc}")
+        return dst
+
     def load_csv(self, paths):
         """CsvFileParser(paths).parse() of the reference build; raises RuntimeError(e.what()) like the importer's popup."""
         arr = (C.c_char_p * len(paths))(*[str(p).encode() for p in paths])

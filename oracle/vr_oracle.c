@@ -352,6 +352,35 @@ void vro_gradient_discretize(const float *color_markers, uint32_t nc, const floa
     }
 }
 
+/* offscreen_pass.cpp:361-375: magFilter = minFilter = LINEAR, CLAMP_TO_EDGE; image format :293 */
+int vro_present_bilinear(const uint8_t *src, uint32_t sw, uint32_t sh, uint8_t *dst, uint32_t dw, uint32_t dh)
+{
+    if (!src || !dst || !sw || !sh) return -1;
+    const float kx = (float)sw / (float)dw, ky = (float)sh / (float)dh;
+    for (uint32_t y = 0; y < dh; y++) {
+        for (uint32_t x = 0; x < dw; x++) {
+            const float u = ((float)x + 0.5f) * kx - 0.5f, v = ((float)y + 0.5f) * ky - 0.5f;
+            const float fu = floorf(u), fv = floorf(v);
+            const float a = u - fu, b = v - fv;
+            int i0 = (int)fu, i1 = i0 + 1, j0 = (int)fv, j1 = j0 + 1;
+            i0 = i0 < 0 ? 0 : (i0 > (int)sw - 1 ? (int)sw - 1 : i0);
+            i1 = i1 < 0 ? 0 : (i1 > (int)sw - 1 ? (int)sw - 1 : i1);
+            j0 = j0 < 0 ? 0 : (j0 > (int)sh - 1 ? (int)sh - 1 : j0);
+            j1 = j1 < 0 ? 0 : (j1 > (int)sh - 1 ? (int)sh - 1 : j1);
+            const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
+            for (int c = 0; c < 4; c++) {
+                float t = w00 * ((float)src[((size_t)j0 * sw + i0) * 4 + c] / 255.0f);
+                t = t + w10 * ((float)src[((size_t)j0 * sw + i1) * 4 + c] / 255.0f);
+                t = t + w01 * ((float)src[((size_t)j1 * sw + i0) * 4 + c] / 255.0f);
+                t = t + w11 * ((float)src[((size_t)j1 * sw + i1) * 4 + c] / 255.0f);
+                t = t < 0.0f ? 0.0f : (t > 1.0f ? 1.0f : t);
+                dst[((size_t)y * dw + x) * 4 + c] = (uint8_t)(t * 255.0f + 0.5f);
+            }
+        }
+    }
+    return 0;
+}
+
 int vro_load_nrrd(const char *path, uint32_t dims[3], float *min, float *max, float **data)
 {
     (void)path, (void)dims, (void)min, (void)max, (void)data;

@@ -99,6 +99,9 @@ void vro_gradient_discretize(const float *color_markers, uint32_t nc, const floa
 /* NRRD load through the reference loader (reference build only; the port returns -1):
  * NrrdFileParser::parse (src/data/nrrd_file_parser.cpp:21-47).  On success *data is a
  * malloc'd float array (caller frees with vro_free). */
+/* Display side: LINEAR / CLAMP_TO_EDGE resample of an R8G8B8A8_UNORM image (the viewport sampler,
+ * src/rendering/offscreen_pass.cpp:361-375; filter equation: Vulkan 1.0 section 15.8.3), fp32, single roundings. */
+int vro_present_bilinear(const uint8_t *src_rgba8, uint32_t sw, uint32_t sh, uint8_t *dst_rgba8, uint32_t dw, uint32_t dh);
 int vro_load_nrrd(const char *path, uint32_t dims[3], float *min, float *max, float **data);
 /* reference build only (port: -1): CsvFileParser::parse, src/data/csv_file_parser.cpp:14-50 */
 int vro_load_csv(const char *const *paths, uint32_t npaths, uint32_t dims[3], float *min, float *max, float **data,

@@ -518,3 +518,39 @@ def test_csv_import_renders_like_the_same_dataset_set_directly(vr, port, tmp_pat
     assert np.array_equal(imgs[0][0], imgs[1][0]) and np.array_equal(bits(imgs[0][1]), bits(imgs[1][1]))
     o = port.render(oracle_frame(port, ocam, W, H, 0.0, float(vol.max()), (0, 0, 0), (1, 1, 1)), vol, lut, want_raw=True)
     assert np.array_equal(bits(imgs[0][1]), bits(o["raw"]))
+
+
+@pytest.mark.parametrize("size", [(W, H), (2 * W, 2 * H), (W // 2 + 3, H // 3), (1, 1), (W + 1, H), (3 * W - 1, 7)])
+def test_present_resamples_like_the_viewport_sampler(vr, port, size):
+    """K3 (present.cu): LINEAR / CLAMP_TO_EDGE sampling of the RGBA8 frame (offscreen_pass.cpp:361-375),
+    bit-exact against the oracle's restatement; same size in and out is the identity."""
+    import torch
+    vol = small_volume(port, 1, np.uint16, 32)
+    cam, _ = twin_cameras(vr, port, [(25, 40)])
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+        op.transfer_function_changed(tf(port, "B"))
+        op.set_camera(cam)
+        op.record()
+        frame = op.download()
+        dw, dh = size
+        dst = torch.zeros((dh, dw, 4), dtype=torch.uint8, device="cuda")
+        op.present(dst.data_ptr(), dw, dh)
+        torch.cuda.synchronize()
+        got = dst.cpu().numpy()
+        want = port.present_bilinear(frame, dw, dh)
+        assert np.array_equal(got, want)
+        if size == (W, H):
+            assert np.array_equal(got, frame)
+        # pitched destination: rows 16 pixels apart wider than the image
+        pitched = torch.zeros((dh, dw + 16, 4), dtype=torch.uint8, device="cuda")
+        op.present(pitched.data_ptr(), dw, dh, pitch_bytes=(dw + 16) * 4)
+        torch.cuda.synchronize()
+        assert np.array_equal(pitched[:, :dw].cpu().numpy(), want) and int(pitched[:, dw:].max()) == 0
+        if dw > 1:  # a pitch of 0 means tightly packed
+            with pytest.raises(vr.VrError):
+                op.present(dst.data_ptr(), dw, dh, pitch_bytes=4 * dw - 4)
+        op.present(0, 0, 0)  # zero size: no-op, like framebuffer_size_changed(0, 0)
+    finally:
+        op.close()

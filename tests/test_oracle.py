@@ -137,3 +137,30 @@ def test_anchor_opaque_lut_shows_first_inslice_sample(port):
     cov = r["raw"][..., 3] > 0
     assert np.all(r["raw"][..., 3][cov] == 1.0)
     assert np.all(r["raw"][..., 0][cov] == r["raw"][..., 1][cov])  # grey ramp
+
+
+def test_viewport_sampler_restatement(port):
+    """vro_present_bilinear (offscreen_pass.cpp:361-375: LINEAR, CLAMP_TO_EDGE): identity at equal size, a constant
+    image stays constant, and fp32 agrees with a float64 evaluation of the Vulkan filter equation to one level."""
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, (7, 9, 4)).astype(np.uint8)
+    assert np.array_equal(port.present_bilinear(img, 9, 7), img)
+    flat = np.full((5, 6, 4), 137, np.uint8)
+    assert (port.present_bilinear(flat, 17, 11) == 137).all()
+
+    def f64(dw, dh):
+        sh, sw = img.shape[:2]
+        x, y = np.meshgrid(np.arange(dw), np.arange(dh))
+        u, v = (x + 0.5) * sw / dw - 0.5, (y + 0.5) * sh / dh - 0.5
+        i0, j0 = np.floor(u).astype(int), np.floor(v).astype(int)
+        a, b = (u - i0)[..., None], (v - j0)[..., None]
+        t = lambda i, j: img[np.clip(j, 0, sh - 1), np.clip(i, 0, sw - 1)].astype(np.float64) / 255.0
+        out = (1 - a) * (1 - b) * t(i0, j0) + a * (1 - b) * t(i0 + 1, j0) + (1 - a) * b * t(i0, j0 + 1) + a * b * t(i0 + 1, j0 + 1)
+        return np.floor(out * 255.0 + 0.5)
+
+    for dw, dh in [(18, 14), (5, 3), (1, 1), (10, 7), (9, 1)]:
+        got = port.present_bilinear(img, dw, dh).astype(np.float64)
+        assert np.abs(got - f64(dw, dh)).max() <= 1
+    # the corners of an enlarged image are the source corners (clamp to edge)
+    big = port.present_bilinear(img, 36, 28)
+    assert np.array_equal(big[0, 0], img[0, 0]) and np.array_equal(big[-1, -1], img[-1, -1])

@@ -251,6 +251,11 @@ class OffscreenPass:
         self._check(lib.vr_download(self._h, _ptr(out)))
         return out
 
+    def present(self, dst_ptr: int, width: int, height: int, pitch_bytes: int = 0, stream: int | None = None, frame_index: int = 0):
+        """The viewport's LINEAR / CLAMP_TO_EDGE sampling of the frame (offscreen_pass.cpp:361-375) into a device
+        RGBA8 buffer of width x height."""
+        self._check(lib.vr_present_frame(self._h, int(frame_index), dst_ptr, int(width), int(height), int(pitch_bytes), stream))
+
     def write_image(self, path: str):
         """The display image as binary PPM (or 4-channel PAM if the name ends in .pam)."""
         self._check(lib.vr_write_image(self._h, str(path).encode()))

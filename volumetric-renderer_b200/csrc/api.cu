@@ -914,6 +914,24 @@ extern "C" int vr_get_image_frame(vr_ctx *c, uint32_t frame_index, void **dev, s
     return VR_OK;
 }
 
+/* the viewport's LINEAR / CLAMP_TO_EDGE sampling of the offscreen image (offscreen_pass.cpp:361-375) */
+extern "C" int vr_present_frame(vr_ctx *c, uint32_t frame_index, void *dst_dev_rgba8, uint32_t dst_width, uint32_t dst_height,
+                                size_t dst_pitch_bytes, void *cuda_stream)
+{
+    if (!c || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return fail(c, VR_ERR_INVALID, "vr_present_frame: bad arguments");
+    if (dst_width == 0 || dst_height == 0) return VR_OK; /* like framebuffer_size_changed(0, 0): nothing to show */
+    if (!dst_dev_rgba8 || (dst_pitch_bytes && (dst_pitch_bytes % 4 || dst_pitch_bytes / 4 < dst_width)))
+        return fail(c, VR_ERR_INVALID, "vr_present_frame: bad destination");
+    const uchar4 *src = frame_index == 0 ? (c->ext_image ? c->ext_image : c->d_image)
+                                         : (c->ext_image_slot[frame_index] ? c->ext_image_slot[frame_index] : c->d_image_slot[frame_index]);
+    if (!src) return fail(c, VR_ERR_STATE, "vr_present_frame: no frame has been rendered into this slot");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : c->last_stream; /* after the frame's render */
+    VR_CUDA(c, vr_launch_present(src, c->W, c->H, reinterpret_cast<uchar4 *>(dst_dev_rgba8), dst_width, dst_height,
+                                 dst_pitch_bytes ? dst_pitch_bytes / 4 : dst_width, s));
+    return VR_OK;
+}
+
 extern "C" int vr_download_frame_async(vr_ctx *c, uint32_t frame_index, void *host, void *cuda_stream)
 {
     if (!c || !host || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return fail(c, VR_ERR_INVALID, "vr_download_frame_async: bad arguments");

@@ -195,6 +195,8 @@ cudaError_t vr_launch_wait(const void *flags, int n, uint32_t value, uint32_t ti
                            cudaStream_t s);
 
 /* K2 (composite.cu) */
+cudaError_t vr_launch_present(const uchar4 *src, uint32_t sw, uint32_t sh, uchar4 *dst, uint32_t dw, uint32_t dh,
+                              size_t dst_pitch_px, cudaStream_t s);
 cudaError_t vr_launch_composite(const float4 *const *d_parts_table, uint32_t nparts, uint64_t begin, uint64_t end,
                                 uchar4 *out, float4 *raw_out, cudaStream_t s);
 
