@@ -210,20 +210,32 @@ def run_ours(args):
 
     # ---- end to end through the public API: host uniforms in, RGBA8 frame out to pinned host memory ---
     host = [torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(F)]
-    for j, k in enumerate(warm_frames[:3]):
+    # Each step leaves the complete frame in pinned host memory.  --full-download: the whole RGBA8 image is copied
+    # every step; default: vr_download_frame_dirty_async copies the rectangle that can differ from what that host
+    # buffer already holds (outside the cube's screen box a frame is the clear colour) -- d2h bytes are counted.
+    fetch = op.download_async if args.full_download else op.download_dirty_async
+    for j, k in enumerate(warm_frames[:F] if len(warm_frames) >= F else list(warm_frames) * F):
         op.set_uniforms(*uniforms[k])
         op.record(streams[j % F].cuda_stream, j % F)
-        op.download_async(host[j % F].data_ptr(), streams[j % F].cuda_stream, j % F)
+        fetch(host[j % F].data_ptr(), streams[j % F].cuda_stream, j % F)   # first delivery into a buffer is always full
     barrier()
+    d2h_bytes = 0
     t0 = time.perf_counter()
     for j, k in enumerate(my_frames):
         f = j % F
         streams[f].synchronize()           # frame j-F is in host memory (its buffer may be reused now)
         op.set_uniforms(*uniforms[k])      # 192-byte uniform block: the step's input, goes down with the launch
         op.record(streams[f].cuda_stream, f)
-        op.download_async(host[f].data_ptr(), streams[f].cuda_stream, f)
+        d2h_bytes += fetch(host[f].data_ptr(), streams[f].cuda_stream, f) or W * H * 4
     barrier()                              # every frame of the K steps has landed in host memory
     e2e_ms = (time.perf_counter() - t0) * 1e3
+    # the host frames must be what a full download gives
+    for f in range(min(F, K)):
+        full = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True)
+        op.download_async(full.data_ptr(), streams[f].cuda_stream, f)
+        streams[f].synchronize()
+        if not torch.equal(full, host[f]):
+            raise SystemExit(f"bench.py: host frame of slot {f} differs from a full download")
     host = host[(K - 1) % F]
     checksum = int(host.view(torch.int32).sum().item())
 
@@ -301,7 +313,9 @@ def run_ours(args):
                              "fetch_only_ms_per_step": fetch_only_ms,
                              "fetch_only_share_of_step": (fetch_only_ms / (dev_ms / K)) if fetch_only_ms else None},
             "e2e": {"value": all_ref / (e2e_ms * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": 192,
-                    "d2h_bytes_per_step": W * H * 4, "ms_per_step": e2e_ms / K, "fps": world * K / (e2e_ms * 1e-3),
+                    "d2h_bytes_per_step": d2h_bytes / K, "frame_bytes": W * H * 4,
+                    "d2h": "full frame every step" if args.full_download else "dirty rectangle (vr_download_frame_dirty_async); the host frame is complete and checked against a full download",
+                    "ms_per_step": e2e_ms / K, "fps": world * K / (e2e_ms * 1e-3),
                     "frame_checksum": checksum},
             "gpu_launches": K,
             "clocks": clocks.result(),
@@ -551,6 +565,7 @@ def main():
     ap.add_argument("--workload", choices=sorted(WORKLOADS) + ["c4", "c5"], default="c2")
     ap.add_argument("--size", type=int, default=0, help="c4/c5: volume edge override")
     ap.add_argument("--frame", default="", help="c4/c5: WxH override")
+    ap.add_argument("--full-download", action="store_true", help="e2e: copy the whole frame to the host every step")
     ap.add_argument("--merge", choices=["p2p", "nccl"], default="p2p", help="c5: peer-memory merge or NCCL exchange")
     ap.add_argument("--exact", action="store_true", help="verification sampler instead of hardware trilinear")
     ap.add_argument("--no-ess", action="store_true")

@@ -114,6 +114,13 @@ int vr_render(vr_ctx *ctx, void *cuda_stream);
 int vr_render_frame(vr_ctx *ctx, uint32_t frame_index, void *cuda_stream);
 int vr_get_image_frame(vr_ctx *ctx, uint32_t frame_index, void **dev_rgba8, size_t *pitch_bytes);
 int vr_download_frame_async(vr_ctx *ctx, uint32_t frame_index, void *host_rgba8, void *cuda_stream);
+/* vr_download_frame_async that moves only what can differ from what `host_rgba8` already holds.  Outside the
+ * screen bounding box of the cube every pixel of a frame is the clear colour (offscreen_pass.cpp:170-173), so
+ * after one full delivery into a host buffer, later frames need only the union of their box and the box of the
+ * frame delivered there before (one strided copy).  The host image is complete and identical to a full download
+ * as long as the caller leaves the buffer alone between calls; the context remembers the last 8 host buffers
+ * (address + frame size).  Frames of a partitioned context are always delivered in full.  bytes_copied may be NULL. */
+int vr_download_frame_dirty_async(vr_ctx *ctx, uint32_t frame_index, void *host_rgba8, void *cuda_stream, size_t *bytes_copied);
 int vr_sync(vr_ctx *ctx);
 
 /* The uniform block the reference fills by pulling the camera inside record()

@@ -554,3 +554,42 @@ def test_present_resamples_like_the_viewport_sampler(vr, port, size):
         op.present(0, 0, 0)  # zero size: no-op, like framebuffer_size_changed(0, 0)
     finally:
         op.close()
+
+
+def test_dirty_rectangle_download_keeps_the_host_frame_complete(vr, port):
+    """vr_download_frame_dirty_async: after one full delivery into a host buffer only the union of the cube's screen
+    boxes (this frame, the frame delivered there before) is copied; the host image always equals a full download."""
+    import torch
+    vol = small_volume(port, 1, np.uint16, 32)
+    op = vr.OffscreenPass(320, 200)
+    try:
+        op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+        op.transfer_function_changed(tf(port, "B"))
+        host = [torch.zeros((200, 320, 4), dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+        streams = [torch.cuda.Stream() for _ in range(2)]
+        # orbit, zoom far out (small box), zoom in until the cube leaves the frame (box = frame), back out
+        moves = [((30 * i, 10 * i), z) for i, z in enumerate([0.0, 0.0, -3.0, -3.0, -3.0, 0.0, 2.0, 2.3, 2.3, 0.0, -1.0, -1.0])]
+        sizes = []
+        for j, (mv, zoom) in enumerate(moves):
+            f = j % 2
+            cam, _ = twin_cameras(vr, port, [mv], zoom)
+            op.set_camera(cam)
+            op.record(streams[f].cuda_stream, f)
+            n = op.download_dirty_async(host[f].data_ptr(), streams[f].cuda_stream, f)
+            streams[f].synchronize()
+            want = op.download_frame(f)
+            assert np.array_equal(host[f].numpy(), want), f"frame {j}"
+            sizes.append(n)
+        full = 320 * 200 * 4
+        assert sizes[0] == full and sizes[1] == full          # first delivery into each buffer
+        assert 0 < sizes[2] < full and 0 < sizes[4] < sizes[2]  # far away: a small box; two small boxes: smaller still
+        assert max(sizes) <= full
+        # a resize forgets every buffer
+        op.framebuffer_size_changed(160, 100)
+        small = torch.zeros((100, 160, 4), dtype=torch.uint8, pin_memory=True)
+        op.record(streams[0].cuda_stream, 0)
+        assert op.download_dirty_async(small.data_ptr(), streams[0].cuda_stream, 0) == 160 * 100 * 4
+        streams[0].synchronize()
+        assert np.array_equal(small.numpy(), op.download_frame(0))
+    finally:
+        op.close()

@@ -267,6 +267,22 @@ class OffscreenPass:
     def download_async(self, host_ptr: int, stream: int | None = None, frame_index: int = 0):
         self._check(lib.vr_download_frame_async(self._h, frame_index, host_ptr, stream))
 
+    def download_frame(self, frame_index: int, stream: int | None = None) -> np.ndarray:
+        """The whole RGBA8 target of a frame in flight (vr_download_frame_async on `stream`, then a stream sync)."""
+        import torch
+        w, h = self.size
+        out = np.empty((h, w, 4), np.uint8)
+        self._check(lib.vr_download_frame_async(self._h, int(frame_index), _ptr(out), stream))
+        torch.cuda.synchronize()
+        return out
+
+    def download_dirty_async(self, host_ptr: int, stream: int | None = None, frame_index: int = 0) -> int:
+        """vr_download_frame_dirty_async: bring a host RGBA8 buffer up to date with the frame, copying only the
+        rectangle that can have changed since the last delivery into that buffer.  Returns the bytes copied."""
+        n = C.c_size_t()
+        self._check(lib.vr_download_frame_dirty_async(self._h, frame_index, host_ptr, stream, C.byref(n)))
+        return n.value
+
     def download_raw(self) -> np.ndarray:
         w, h = self.size
         out = np.empty((h, w, 4), np.float32)

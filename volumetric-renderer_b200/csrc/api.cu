@@ -446,6 +446,8 @@ extern "C" int vr_resize(vr_ctx *c, uint32_t width, uint32_t height)
     if (width == 0 || height == 0) return VR_OK; /* offscreen_pass.cpp:237-239 */
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaDeviceSynchronize()); /* vkDeviceWaitIdle, :241 */
+    for (int i = 0; i < VR_MAX_FRAMES_IN_FLIGHT; i++) c->slot_bbox_valid[i] = false; /* new targets: nothing rendered yet */
+    for (auto &t : c->host_targets) t.ptr = nullptr;
     return alloc_target(c, width, height);
 }
 
@@ -852,6 +854,10 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     }
     if (pair) fill_params(c, p, pair_axis);
     c->last_pair = pair, c->last_pair_axis = pair_axis;
+    /* outside p.bbox every pixel of this frame is the clear colour (screen_bbox is conservative); with a
+     * partition the frame is only partly this context's */
+    for (int i = 0; i < 4; i++) c->slot_bbox[frame_index][i] = p.bbox[i];
+    c->slot_bbox_valid[frame_index] = p.pt_nranks <= 1 && !c->sort_last;
     p.out = target;
     if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
@@ -940,6 +946,54 @@ extern "C" int vr_download_frame_async(vr_ctx *c, uint32_t frame_index, void *ho
     VR_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->last_stream;
     VR_CUDA(c, cudaMemcpyAsync(host, src, (size_t)c->W * c->H * sizeof(uchar4), cudaMemcpyDeviceToHost, s));
+    return VR_OK;
+}
+
+/* Copy only what can have changed.  Invariant per known host buffer: outside `rect` it holds the clear colour. */
+extern "C" int vr_download_frame_dirty_async(vr_ctx *c, uint32_t frame_index, void *host, void *cuda_stream, size_t *bytes_copied)
+{
+    if (!c || !host || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return fail(c, VR_ERR_INVALID, "vr_download_frame_dirty_async: bad arguments");
+    const uchar4 *src = frame_index == 0 ? c->d_image : c->d_image_slot[frame_index];
+    if (!src) return fail(c, VR_ERR_STATE, "vr_download_frame_dirty_async: that frame was never rendered");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->last_stream;
+    vr_ctx::HostTarget *e = nullptr, *lru = &c->host_targets[0];
+    for (auto &t : c->host_targets) {
+        if (t.ptr == host && t.W == c->W && t.H == c->H) e = &t;
+        if (t.stamp < lru->stamp) lru = &t;
+    }
+    const uint32_t *now = c->slot_bbox[frame_index];
+    const size_t all = (size_t)c->W * c->H * sizeof(uchar4);
+    size_t bytes = 0;
+    if (!c->slot_bbox_valid[frame_index]) {
+        /* a frame this context does not own alone (partitioned), or not rendered since a resize: everything */
+        VR_CUDA(c, cudaMemcpyAsync(host, src, all, cudaMemcpyDeviceToHost, s));
+        if (e) e->ptr = nullptr; /* what the buffer holds is no longer known */
+        if (bytes_copied) *bytes_copied = all;
+        return VR_OK;
+    }
+    if (!e) {
+        /* first delivery into this buffer: everything */
+        bytes = all;
+        VR_CUDA(c, cudaMemcpyAsync(host, src, all, cudaMemcpyDeviceToHost, s));
+        e = lru;
+        e->ptr = host, e->W = c->W, e->H = c->H;
+    } else {
+        const bool a = e->rect[2] > e->rect[0] && e->rect[3] > e->rect[1], b = now[2] > now[0] && now[3] > now[1];
+        uint32_t r[4] = {0, 0, 0, 0};
+        if (a && b) r[0] = std::min(e->rect[0], now[0]), r[1] = std::min(e->rect[1], now[1]), r[2] = std::max(e->rect[2], now[2]), r[3] = std::max(e->rect[3], now[3]);
+        else if (a) std::memcpy(r, e->rect, sizeof r);
+        else if (b) std::memcpy(r, now, sizeof r);
+        if (r[2] > r[0] && r[3] > r[1]) {
+            const size_t off = (size_t)r[1] * c->W + r[0], pitch = (size_t)c->W * sizeof(uchar4);
+            bytes = (size_t)(r[2] - r[0]) * (r[3] - r[1]) * sizeof(uchar4);
+            VR_CUDA(c, cudaMemcpy2DAsync(static_cast<uchar4 *>(host) + off, pitch, src + off, pitch, (size_t)(r[2] - r[0]) * sizeof(uchar4),
+                                         r[3] - r[1], cudaMemcpyDeviceToHost, s));
+        }
+    }
+    for (int i = 0; i < 4; i++) e->rect[i] = now[i];
+    e->stamp = ++c->host_target_clock;
+    if (bytes_copied) *bytes_copied = bytes;
     return VR_OK;
 }
 

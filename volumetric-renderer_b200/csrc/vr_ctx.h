@@ -156,6 +156,16 @@ struct vr_ctx {
     uint32_t *d_occ = nullptr;
     int occ_words = 0;
     unsigned char *d_dist = nullptr; /* 8 x cells */
+    /* dirty-rectangle downloads (vr_download_frame_dirty_async): where each slot's last frame can differ from the
+     * clear colour, and what each known host buffer holds */
+    uint32_t slot_bbox[VR_MAX_FRAMES_IN_FLIGHT][4] = {};
+    bool slot_bbox_valid[VR_MAX_FRAMES_IN_FLIGHT] = {false, false, false, false};
+    struct HostTarget {
+        void *ptr = nullptr;
+        uint32_t W = 0, H = 0, rect[4] = {0, 0, 0, 0};
+        uint64_t stamp = 0;
+    } host_targets[8];
+    uint64_t host_target_clock = 0;
     bool bench_fetch_only = false;   /* vr_bench_fetch_only: frames run the fetch-only build of K1 */
     uint32_t *d_sat = nullptr;       /* summed-volume table of the occupancy bits, (n+1)^3 */
     bool occ_dirty = true;
