@@ -253,6 +253,10 @@ int vr_download_volume(vr_ctx *ctx, void *host_out);
  * (tiles of tile_px x tile_px in row-major order); other pixels are left untouched.
  * nranks = 1 restores the whole frame. */
 int vr_set_partition_sort_first(vr_ctx *ctx, uint32_t rank, uint32_t nranks, uint32_t tile_px);
+/* The rank that renders partition tile (tile_x, tile_y) (pixels / tile_px): tiles are dealt along diagonals,
+ * (tile_x + tile_y * m) % nranks with m the smallest number >= 3 coprime to nranks, so that every rank gets an even
+ * share of any screen rectangle whatever the number of tiles per row. */
+uint32_t vr_sort_first_owner(uint32_t tile_x, uint32_t tile_y, uint32_t nranks);
 
 /* Sort-last: this context holds voxels [org, org+n) (+ ghost layers) of a
  * global grid `full` and accumulates only samples whose position lies in its half-open

@@ -47,7 +47,7 @@ def test_sort_first_tiles_reassemble(vr, port, nranks):
         n_ref += op.stats().n_ref
         op.close()
         ty, tx = np.meshgrid(np.arange(H) // tile, np.arange(W) // tile, indexing="ij")
-        mine = (ty * ((W + tile - 1) // tile) + tx) % nranks == r
+        mine = vr.sort_first_owner(tx, ty, nranks) == r
         assert (img[~mine] == 0).all(), "a rank wrote outside its tiles"
         got[mine] = img[mine]
         owner[mine] = r

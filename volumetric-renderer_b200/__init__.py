@@ -394,6 +394,13 @@ def read_csv(paths) -> "Dataset":
         lib.vr_free_host(data)
 
 
+def sort_first_owner(tile_x, tile_y, nranks: int):
+    """vr_sort_first_owner for integer arrays: the rank that renders each partition tile."""
+    m = next(m for m in range(3, 3 + 2 * max(nranks, 1) + 3) if np.gcd(m, nranks) == 1)
+    assert lib.vr_sort_first_owner(1, 1, nranks) == (1 + m) % nranks
+    return (np.asarray(tile_x) + np.asarray(tile_y) * m) % nranks
+
+
 def partition_box(grid, full_dims, index: int):
     g, f = np.asarray(grid, np.uint32), np.asarray(full_dims, np.uint32)
     org, dims = np.zeros(3, np.uint32), np.zeros(3, np.uint32)

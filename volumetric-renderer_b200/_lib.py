@@ -50,6 +50,7 @@ SIGNATURES = {
     "vr_load_nrrd": (C.c_int, [_P, C.c_char_p]),
     "vr_nrrd_read_host": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), _U, C.POINTER(_P), C.c_char_p, C.c_size_t]),
     "vr_free_host": (None, [_P]),
+    "vr_sort_first_owner": (C.c_uint32, [C.c_uint32, C.c_uint32, C.c_uint32]),
     "vr_present_frame": (C.c_int, [_P, C.c_uint32, _P, C.c_uint32, C.c_uint32, C.c_size_t, _P]),
     "vr_load_csv": (C.c_int, [_P, C.POINTER(C.c_char_p), C.c_uint32]),
     "vr_csv_read_host": (C.c_int, [C.POINTER(C.c_char_p), C.c_uint32, _U, C.POINTER(_P), C.POINTER(C.c_float), C.POINTER(C.c_float),

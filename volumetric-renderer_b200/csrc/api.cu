@@ -747,6 +747,7 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
     p.ert_eps = c->opt.early_term ? c->opt.early_term_eps : -1.0f;
     p.pt_px = c->pt_px, p.pt_rank = c->pt_rank, p.pt_nranks = c->pt_nranks;
     p.pt_nx = (c->W + c->pt_px - 1) / c->pt_px, p.pt_ny = (c->H + c->pt_px - 1) / c->pt_px;
+    p.pt_m = vr_sort_first_stride(c->pt_nranks);
     p.warp_w = (uint32_t)c->tune_warp_w;
     p.carveout = c->tune_carveout;
     p.tile_h = (uint32_t)c->tune_threads / VR_TILE;
@@ -763,6 +764,24 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
         const int R = (std::max(w, h) + 1) / 2; /* the (2R+1)^2 spiral square covers the rectangle */
         p.sp_cx = p.rect[0] + w / 2, p.sp_cy = p.rect[1] + h / 2;
         p.sp_count = (uint32_t)((2 * R + 1) * (2 * R + 1));
+        /* sort-first: launch this rank's partition tiles only (7/8 of a spiral over the whole box would be blocks
+         * that find out they own nothing: 12 % of the frame time at 8 ranks, profiles/r1_exp_c4_balance.txt) */
+        if (p.pt_nranks > 1 && p.pt_px % VR_TILE == 0 && p.pt_px % p.tile_h == 0) {
+            p.pt_enum = 1;
+            p.pt_sub_x = p.pt_px / VR_TILE, p.pt_sub_y = p.pt_px / p.tile_h;
+            p.pt_x0 = (uint32_t)p.rect[0] / p.pt_sub_x, p.pt_x1 = ((uint32_t)p.rect[2] + p.pt_sub_x - 1) / p.pt_sub_x;
+            p.pt_y0 = (uint32_t)p.rect[1] / p.pt_sub_y;
+            const uint32_t rows = ((uint32_t)p.rect[3] + p.pt_sub_y - 1) / p.pt_sub_y - p.pt_y0;
+            p.pt_cnt = (p.pt_x1 - p.pt_x0 + p.pt_nranks - 1) / p.pt_nranks;
+            p.pt_rows = rows;
+            p.sp_count = rows * p.pt_cnt * p.pt_sub_x * p.pt_sub_y;
+        }
+    }
+    if (p.pt_nranks > 1 && p.pt_px % VR_TILE == 0 && p.pt_px % p.tile_h == 0) {
+        /* ... and one clear block per partition tile of this rank */
+        p.pt_enum = 1;
+        p.pt_cnt_clear = (p.pt_nx + p.pt_nranks - 1) / p.pt_nranks;
+        p.nclr_x = p.pt_cnt_clear * p.pt_ny, p.nclr_y = 1;
     }
 }
 }  // namespace
@@ -1148,6 +1167,11 @@ extern "C" int vr_set_partition_sort_first(vr_ctx *c, uint32_t rank, uint32_t nr
         return fail(c, VR_ERR_INVALID, "vr_set_partition_sort_first: need rank < nranks and tile_px a multiple of 16");
     c->pt_rank = rank, c->pt_nranks = nranks, c->pt_px = tile_px;
     return VR_OK;
+}
+
+extern "C" uint32_t vr_sort_first_owner(uint32_t tile_x, uint32_t tile_y, uint32_t nranks)
+{
+    return nranks ? (tile_x + tile_y * vr_sort_first_stride(nranks)) % nranks : 0;
 }
 
 extern "C" int vr_set_partition_sort_last(vr_ctx *c, const uint32_t full_dims[3], const uint32_t own_org[3],

@@ -407,7 +407,25 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     const uint32_t nthreads = blockDim.x;
     int tx, ty;
     const bool in_bbox = blockIdx.x < p.sp_count;
-    if (in_bbox) {
+    if (in_bbox && p.pt_enum) {
+        /* sort-first: the marching blocks enumerate this rank's partition tiles only, row by row; partition tile
+         * (x, y) belongs to rank (x + y * pt_m) % pt_nranks, so in row y the owned ones are every pt_nranks-th
+         * from the first x >= pt_x0 with that residue */
+        const uint32_t block = blockIdx.x;
+        const uint32_t per_tile = p.pt_sub_x * p.pt_sub_y, per_row = p.pt_cnt * per_tile;
+        const uint32_t row = block / per_row, rem = block - row * per_row;
+        const uint32_t j = rem / per_tile, sub = rem - j * per_tile;
+        /* rows from the middle of the box outwards (c, c+1, c-1, ...): the long rays start first, the short ones
+         * at the top and bottom edge fill the tail */
+        const uint32_t mid = (p.pt_rows - 1u) >> 1;
+        const uint32_t pty = p.pt_y0 + ((row & 1u) ? mid + ((row + 1u) >> 1) : mid - (row >> 1));
+        const uint32_t want = (p.pt_rank + p.pt_nranks - (pty * p.pt_m + p.pt_x0) % p.pt_nranks) % p.pt_nranks;
+        const uint32_t ptx = p.pt_x0 + want + j * p.pt_nranks;
+        if (ptx >= p.pt_x1) return;
+        const uint32_t sy = sub / p.pt_sub_x, sx = sub - sy * p.pt_sub_x;
+        tx = (int)(ptx * p.pt_sub_x + sx), ty = (int)(pty * p.pt_sub_y + sy);
+        if (tx < p.rect[0] || ty < p.rect[1] || tx >= p.rect[2] || ty >= p.rect[3]) return;
+    } else if (in_bbox) {
         int ox = 0, oy = 0;
         const int b = (int)blockIdx.x;
         if (b > 0) {
@@ -428,17 +446,29 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         /* clear colour only (offscreen_pass.cpp:170-173): a block clears a 64x32 pixel region in groups of
          * four pixels (one 16-byte store), leaving out the tiles the spiral blocks own */
         const uint32_t j = blockIdx.x - p.sp_count;
-        const uint32_t jy = j / p.nclr_x;
-        const uint32_t ry = jy * 32u, rx = (j - jy * p.nclr_x) * 64u;
+        uint32_t rx, ry, rw = 64u, rh = 32u;
+        if (p.pt_enum) {
+            /* sort-first: one block per partition tile of this rank, row by row */
+            const uint32_t pty = j / p.pt_cnt_clear, jj = j - pty * p.pt_cnt_clear;
+            const uint32_t ptx = (p.pt_rank + p.pt_nranks - (pty * p.pt_m) % p.pt_nranks) % p.pt_nranks + jj * p.pt_nranks;
+            if (ptx >= p.pt_nx) return;
+            rx = ptx * p.pt_px, ry = pty * p.pt_px, rw = rh = p.pt_px;
+        } else {
+            const uint32_t jy = j / p.nclr_x;
+            ry = jy * 32u, rx = (j - jy * p.nclr_x) * 64u;
+        }
         const uint32_t c8 = (uint32_t)(VR_CLEAR_RGB * 255.0f + 0.5f), cw = c8 | (c8 << 8) | (c8 << 16) | 0xff000000u;
         const bool wide = (p.W & 3u) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;
         /* the spiral blocks' rectangle in pixels (a group of four pixels never straddles a 16-pixel tile column) */
         const int rpx0 = p.rect[0] * VR_TILE, rpx1 = p.rect[2] * VR_TILE, rpy0 = p.rect[1] * (int)p.tile_h, rpy1 = p.rect[3] * (int)p.tile_h;
-        for (uint32_t g = threadIdx.x; g < 512u; g += nthreads) {
-            const uint32_t gx = rx + (g & 15u) * 4u, gy = ry + (g >> 4);
+        /* rows of rw / 4 groups of four pixels, 16 groups side by side per pass */
+        for (uint32_t g = threadIdx.x; g < (rw >> 2) * rh; g += nthreads) {
+            uint32_t col = g & 15u, rowi = g >> 4;
+            if (rw != 64u) rowi = g / (rw >> 2), col = g - rowi * (rw >> 2);
+            const uint32_t gx = rx + col * 4u, gy = ry + rowi;
             if (gx >= p.W || gy >= p.H) continue;
             if ((int)gx >= rpx0 && (int)gy >= rpy0 && (int)gx < rpx1 && (int)gy < rpy1) continue;
-            if (p.pt_nranks > 1 && ((gy / p.pt_px) * p.pt_nx + gx / p.pt_px) % p.pt_nranks != p.pt_rank) continue;
+            if (!p.pt_enum && p.pt_nranks > 1 && ((gy / p.pt_px) * p.pt_m + gx / p.pt_px) % p.pt_nranks != p.pt_rank) continue;
             const size_t gp = (size_t)gy * p.W + gx;
             if (wide) {
                 *reinterpret_cast<uint4 *>(p.out + gp) = make_uint4(cw, cw, cw, cw);
@@ -453,7 +483,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
     const uint32_t x0 = (uint32_t)tx * VR_TILE, y0 = (uint32_t)ty * p.tile_h;
     if (x0 >= p.W || y0 >= p.H) return; /* uniform per CTA */
     /* sort-first: partition tiles of pt_px pixels dealt round-robin to ranks */
-    if (p.pt_nranks > 1 && ((y0 / p.pt_px) * p.pt_nx + x0 / p.pt_px) % p.pt_nranks != p.pt_rank) return;
+    if (p.pt_nranks > 1 && ((y0 / p.pt_px) * p.pt_m + x0 / p.pt_px) % p.pt_nranks != p.pt_rank) return;
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     /* warp footprint ww x (32/ww) pixels, warps tiled across the 16-pixel-wide CTA tile */

@@ -82,6 +82,11 @@ struct MarchParams {
     float ert_eps;
     /* screen partition (sort-first): partition tiles of pt_px pixels, round-robin */
     uint32_t pt_px, pt_nx, pt_ny, pt_rank, pt_nranks;
+    /* sort-first launch over this rank's tiles only (pt_enum): the partition tiles [pt_x0, pt_x1) x [pt_y0, ..) that
+     * meet the bounding box, pt_cnt owned candidates per row of them, pt_sub_x x pt_sub_y CTA tiles in each */
+    uint32_t pt_enum, pt_x0, pt_x1, pt_y0, pt_rows, pt_cnt, pt_sub_x, pt_sub_y;
+    uint32_t pt_m;   /* partition tile (x, y) belongs to rank (x + y * pt_m) % pt_nranks (vr_sort_first_owner) */
+    uint32_t pt_cnt_clear; /* owned candidates per full row of partition tiles */
     /* CTA tiles: ntx x nty over the target; rect = tiles that can be covered (x0,y0,x1,y1, exclusive);
      * the first sp_count blocks spiral out from tile (sp_cx, sp_cy) over the square containing rect */
     uint32_t ntx, nty, sp_count;
@@ -207,6 +212,20 @@ cudaError_t vr_launch_wait(const void *flags, int n, uint32_t value, uint32_t ti
 /* K2 (composite.cu) */
 cudaError_t vr_launch_present(const uchar4 *src, uint32_t sw, uint32_t sh, uchar4 *dst, uint32_t dw, uint32_t dh,
                               size_t dst_pitch_px, cudaStream_t s);
+/* sort-first ownership: tiles are dealt along diagonals, rank = (x + y * m) % n with m the smallest number >= 3
+ * that has no common factor with n -- rows are shifted against each other, so every rank gets an even share of any
+ * screen rectangle whatever the number of tiles per row */
+inline uint32_t vr_sort_first_stride(uint32_t n)
+{
+    for (uint32_t m = 3;; m++) {
+        uint32_t a = m, b = n;
+        while (b) {
+            const uint32_t t = a % b;
+            a = b, b = t;
+        }
+        if (a == 1) return m;
+    }
+}
 cudaError_t vr_launch_composite(const float4 *const *d_parts_table, uint32_t nparts, uint64_t begin, uint64_t end,
                                 uchar4 *out, float4 *raw_out, cudaStream_t s);
 

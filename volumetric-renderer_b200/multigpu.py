@@ -3,7 +3,7 @@ plumbing (rendezvous, barriers, the NCCL fallback exchange), the data path in th
 
 The reference is single-GPU; these are the two partitions BASELINE.json names.
 
-SortFirst   image tiles dealt round-robin to ranks, volume replicated.  Every rank's K1 stores its
+SortFirst   image tiles dealt along diagonals to ranks (vr_sort_first_owner), volume replicated.  Every rank's K1 stores its
             tiles straight into the display rank's RGBA8 image through a CUDA-IPC mapped pointer
             (NVLink peer writes): the gather is the kernel's own epilogue, there is no collective.
 SortLast    volume split into a regular grid of sub-boxes (one per rank, one ghost voxel towards
