@@ -467,7 +467,7 @@ def run_partitioned(args):
                    early_term_eps=1.0 / 1024.0, collect_stats=1)
     if c4:
         op.synth_volume(vr.SYNTH_FBM, 0x5EED0004, vr.U16, n)
-        part = mg.SortFirst(op, rank, world, tile_px=64)
+        part = mg.SortFirst(op, rank, world, tile_px=args.tile_px, slots=args.slots)
     else:
         part = mg.SortLast(op, rank, world, (n, n, n), mode=args.merge)
         op.synth_subvolume(vr.SYNTH_FBM, 0x5EED0005, vr.U16)
@@ -536,7 +536,7 @@ def run_partitioned(args):
             "metric": f"ray samples/s ({args.workload})", "value": counts[0].item() / dt, "unit": "samples/s",
             "n_gpus": world, "steps": K, "warmup": Wu, "ms_per_step": step_s * 1e3, "fps": K / dt,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": (f"c4: {n}^3 u16 fBm replicated, {W}x{H}, sort-first 64-px tiles round-robin, peer stores into rank 0's image"
+            "config": {"workload": (f"c4: {n}^3 u16 fBm replicated, {W}x{H}, sort-first {args.tile_px}-px tiles dealt along diagonals, each rank launches its own tiles, peer stores into rank 0's image ({args.slots} slots)"
                                     if c4 else f"c5: {n}^3 u16 fBm in {world} sub-boxes {part.grid}, {W}x{H}, sort-last, direct-send merge ({args.merge})"),
                        "timing": "wall clock over K frames enqueued back to back (frames handed off between ranks by stream-ordered counters in peer memory; nccl merge: collectives), one device sync + barrier at the end, max over ranks",
                        "l2": "inputs larger than L2"},
@@ -565,6 +565,8 @@ def main():
     ap.add_argument("--workload", choices=sorted(WORKLOADS) + ["c4", "c5"], default="c2")
     ap.add_argument("--size", type=int, default=0, help="c4/c5: volume edge override")
     ap.add_argument("--frame", default="", help="c4/c5: WxH override")
+    ap.add_argument("--tile-px", type=int, default=64, help="c4: sort-first partition tile edge in pixels")
+    ap.add_argument("--slots", type=int, default=2, help="c4: image slots on the display rank (frames a rank may run ahead)")
     ap.add_argument("--full-download", action="store_true", help="e2e: copy the whole frame to the host every step")
     ap.add_argument("--merge", choices=["p2p", "nccl"], default="p2p", help="c5: peer-memory merge or NCCL exchange")
     ap.add_argument("--exact", action="store_true", help="verification sampler instead of hardware trilinear")
