@@ -102,3 +102,30 @@ def test_frame_parallel_assignment_is_a_partition():
     N, K = 4, 90
     seen = sorted((r + j * N) % 360 for r in range(N) for j in range(K))
     assert seen == list(range(360))
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 4, 5, 6, 7, 8, 12, 16])
+def test_sort_first_dealing_is_even_in_every_rectangle(nranks):
+    """vr_sort_first_owner deals partition tiles along diagonals, (x + y*m) % n with m coprime to n: the C entry
+    point and the Python helper agree, every tile has one owner, and any rectangle of tiles (the cube's screen box)
+    that is at least n tiles wide gives every rank the same share to within one tile per row -- also when the
+    number of tiles per row is a multiple of n (120 tiles at 8K with 8 ranks used to give vertical strips)."""
+    import volumetric_renderer_b200 as vr
+    ty, tx = np.meshgrid(np.arange(40), np.arange(120), indexing="ij")
+    own = vr.sort_first_owner(tx, ty, nranks)
+    assert own.min() == 0 and own.max() == nranks - 1
+    for x, y in [(0, 0), (1, 0), (0, 1), (7, 5), (119, 39), (64, 33)]:
+        assert vr.lib.vr_sort_first_owner(x, y, nranks) == own[y, x]
+    rng = np.random.default_rng(nranks)
+    for _ in range(20):
+        w, h = int(rng.integers(nranks, 60)), int(rng.integers(1, 30))
+        x0, y0 = int(rng.integers(0, 120 - w)), int(rng.integers(0, 40 - h))
+        counts = np.bincount(own[y0:y0 + h, x0:x0 + w].ravel(), minlength=nranks)
+        assert counts.max() - counts.min() <= h, (w, h, counts)
+        if h >= nranks:  # the per-row remainders rotate with the rows: closer than one tile per row
+            assert counts.max() - counts.min() <= max(2, h // 2), (w, h, counts)
+    # no two horizontally or vertically adjacent tiles share a rank (n >= 2)
+    if nranks >= 2:
+        assert (own[:, 1:] != own[:, :-1]).all()
+    if nranks >= 4:
+        assert (own[1:, :] != own[:-1, :]).all()

@@ -110,6 +110,13 @@ class _PeerFlags:
         self.base = []
 
 
+def _present_priority() -> int:
+    """Priority of the display rank's second stream (the one-warp wait / signal kernels of the frame hand-off).
+    VR_PRESENT_PRIORITY=1 asks for the highest priority so that they are not queued behind the CTAs of a frame."""
+    import os
+    return -1 if os.environ.get("VR_PRESENT_PRIORITY", "0") == "1" else 0
+
+
 class SortFirst:
     """Sort-first image-tile partition (BASELINE.json config 4).
 
@@ -138,7 +145,7 @@ class SortFirst:
             self._flags = _PeerFlags(op, rank, world, group)
             if rank == display_rank:
                 import torch
-                self._present = torch.cuda.Stream()
+                self._present = torch.cuda.Stream(priority=_present_priority())
             dist.barrier(group)
 
     def render(self, stream: int | None = None) -> int:
@@ -211,7 +218,7 @@ class SortLast:
             self._flags = _PeerFlags(op, rank, world, group)
             if rank == display_rank:
                 import torch
-                self._present = torch.cuda.Stream()
+                self._present = torch.cuda.Stream(priority=_present_priority())
             dist.barrier(group)
 
     def set_global_density_range(self):
