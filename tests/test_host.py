@@ -170,6 +170,175 @@ def test_nrrd_reader_rejects_what_the_reference_rejects(vr, ref, tmp_path):
 
 # ---- partition helpers -----------------------------------------------------------------------------
 
+_B = ["type: uchar", "dimension: 3", "sizes: 2 2 2", "encoding: raw"]
+_P8 = bytes(range(1, 9))
+NRRD_HEADER_CASES = [
+    # (name, header lines after the magic, payload, magic): the product reader must accept exactly what NrrdIO accepts
+    ("baseline", _B, _P8, "NRRD0004"),
+    ("upper-case key and values", ["TYPE: UCHAR", "Dimension: 3", "sizes: 2 2 2", "encoding: RAW"], _P8, "NRRD0004"),
+    ("unknown field", _B + ["foo: bar"], _P8, "NRRD0004"),
+    ("line without colon", _B + ["garbage line"], _P8, "NRRD0004"),
+    ("colon without space", ["type:uchar", "dimension:3", "sizes:2 2 2", "encoding:raw"], _P8, "NRRD0004"),
+    ("space before the colon", ["type : uchar"] + _B[1:], _P8, "NRRD0004"),
+    ("leading space", [" type: uchar"] + _B[1:], _P8, "NRRD0004"),
+    ("trailing space in a value", ["type: uchar "] + _B[1:], _P8, "NRRD0004"),
+    ("sizes before dimension", ["type: uchar", "sizes: 2 2 2", "dimension: 3", "encoding: raw"], _P8, "NRRD0004"),
+    ("spacings before dimension", ["type: uchar", "spacings: 1 1 1", "dimension: 3", "sizes: 2 2 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("field given twice", _B + ["type: uchar"], _P8, "NRRD0004"),
+    ("alias given twice", _B + ["old min: 0", "oldmin: 0"], _P8, "NRRD0004"),
+    ("content twice", _B + ["content: a", "content: b"], _P8, "NRRD0004"),
+    ("empty content", _B + ["content:"], _P8, "NRRD0004"),
+    ("key/value pairs, comments", ["# c", "a:=b", ":=x"] + _B + ["k k:=v v", "# d"], _P8, "NRRD0001"),
+    ("free-text fields", _B + ["number: abc", "min: abc", "max: x", "old max: 1.5", "sample units: HU"], _P8, "NRRD0002"),
+    ("old min must be a number", _B + ["old min: x"], _P8, "NRRD0004"),
+    ("aliases", _B + ["centerings: cell node ???", "axismins: 0 0 0", "axismaxs: 1 1 1", "lineskip: 0", "byteskip: 0", "sampleunits: mm"], _P8, "NRRD0004"),
+    ("space origin before space", _B + ["space origin: (0,0,0)", "space: right-anterior-superior"], _P8, "NRRD0004"),
+    ("space directions before space", _B + ["space directions: (1,0,0) (0,1,0) (0,0,1)", "space: RAS"], _P8, "NRRD0004"),
+    ("space, origin, directions", _B + ["space: left-posterior-superior", "space origin: (0,0,0)", "space directions: none (0,1,0) (0,0,1)"], _P8, "NRRD0004"),
+    ("space and space dimension", _B + ["space: RAS", "space dimension: 3"], _P8, "NRRD0004"),
+    ("space dimension 2", _B + ["space dimension: 2", "space directions: (1,0) (0,1) (0,0)"], _P8, "NRRD0004"),
+    ("direction with too few components", _B + ["space: RAS", "space directions: (1,0) (0,1) (0,0)"], _P8, "NRRD0004"),
+    ("too few directions", _B + ["space: RAS", "space directions: (1,0,0) (0,1,0)"], _P8, "NRRD0004"),
+    ("directions and spacings", _B + ["space: RAS", "space directions: (1,0,0) (0,1,0) (0,0,1)", "spacings: 1 1 1"], _P8, "NRRD0004"),
+    ("space and spacings", _B + ["space: RAS", "spacings: 1 1 1"], _P8, "NRRD0004"),
+    ("space with per-axis fields", _B + ["space: LPS", 'labels: "x" "y" "z"', 'units: "mm" "mm" "mm"', "axis mins: 0 0 0", "thicknesses: 1 1 1"], _P8, "NRRD0004"),
+    ("directions and axis mins", _B + ["space: LPS", "space directions: (1,0,0) (0,1,0) (0,0,1)", "axis mins: 0 0 0"], _P8, "NRRD0004"),
+    ("directions and axis maxs", _B + ["space: LPS", "space directions: (1,0,0) (0,1,0) (0,0,1)", "axis maxs: 0 0 0"], _P8, "NRRD0004"),
+    ("directions and units", _B + ["space: LPS", "space directions: none (0,1,0) (0,0,1)", 'units: "mm" "mm" "mm"'], _P8, "NRRD0004"),
+    ("directions and thicknesses", _B + ["space: LPS", "space directions: (1,0,0) (0,1,0) (0,0,1)", "thicknesses: 1 1 1"], _P8, "NRRD0004"),
+    ("unknown space", _B + ["space: foo"], _P8, "NRRD0004"),
+    ("space units without space", _B + ['space units: "mm" "mm" "mm"'], _P8, "NRRD0004"),
+    ("measurement frame without space", _B + ["measurement frame: (1,0,0) (0,1,0) (0,0,1)"], _P8, "NRRD0004"),
+    ("measurement frame", _B + ["space: RAS", "measurement frame: (1,0,0) (0,1,0) (0,0,1)"], _P8, "NRRD0004"),
+    ("magic 0006", _B, _P8, "NRRD0006"),
+    ("magic 0000", _B, _P8, "NRRD0000"),
+    ("no encoding", _B[:3], _P8, "NRRD0004"),
+    ("no type", _B[1:], _P8, "NRRD0004"),
+    ("ushort raw without endian", ["type: ushort", "dimension: 3", "sizes: 2 2 1", "encoding: raw"], _P8, "NRRD0004"),
+    ("ushort hex without endian", ["type: ushort", "dimension: 3", "sizes: 2 2 1", "encoding: hex"], b"0001000200030004\n", "NRRD0004"),
+    ("ushort ascii without endian", ["type: ushort", "dimension: 3", "sizes: 2 2 2", "encoding: ascii"], b"1 2 3 4 5 6 7 8\n", "NRRD0004"),
+    ("endian for uchar", _B + ["endian: little"], _P8, "NRRD0004"),
+    ("bad endian", ["type: ushort", "dimension: 3", "sizes: 2 2 1", "encoding: raw", "endian: middle"], _P8, "NRRD0004"),
+    ("two sizes", ["type: uchar", "dimension: 3", "sizes: 2 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("four sizes", ["type: uchar", "dimension: 3", "sizes: 2 2 2 1", "encoding: raw"], _P8, "NRRD0004"),
+    ("zero size", ["type: uchar", "dimension: 3", "sizes: 2 0 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("negative size", ["type: uchar", "dimension: 3", "sizes: 2 -2 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("signed size", ["type: uchar", "dimension: 3", "sizes: +2 2 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("fractional size and dimension", ["type: uchar", "dimension: 3.0", "sizes: 2.0 2 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("tab-separated sizes", ["type: uchar", "dimension: 03", "sizes: 2\t2\t2", "encoding: raw"], _P8, "NRRD0004"),
+    ("dimension 17", ["type: uchar", "dimension: 17", "sizes: 2 2 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("dimension 0", ["type: uchar", "dimension: 0", "sizes: 2 2 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("two spacings", _B + ["spacings: 1 1"], _P8, "NRRD0004"),
+    ("four spacings", _B + ["spacings: 1 1 1 1"], _P8, "NRRD0004"),
+    ("nan spacing", _B + ["spacings: nan 1 1"], _P8, "NRRD0004"),
+    ("non-numeric spacings", _B + ["spacings: a b c"], _P8, "NRRD0004"),
+    ("two thicknesses", _B + ["thicknesses: 1 1"], _P8, "NRRD0004"),
+    ("two axis mins", _B + ["axis mins: 0 0"], _P8, "NRRD0004"),
+    ("unknown kind", _B + ["kinds: foo domain domain"], _P8, "NRRD0004"),
+    ("kinds that fit", _B + ["kinds: 2-vector complex Domain"], _P8, "NRRD0004"),
+    ("kind that does not fit", _B + ["kinds: 3-vector domain domain"], _P8, "NRRD0004"),
+    ("stub needs size 1", _B + ["kinds: stub domain domain"], _P8, "NRRD0004"),
+    ("unknown center", _B + ["centers: foo cell cell"], _P8, "NRRD0004"),
+    ("two labels", _B + ['labels: "x" "y"'], _P8, "NRRD0004"),
+    ("four labels", _B + ['labels: "x" "y" "z" "w"'], _P8, "NRRD0004"),
+    ("unquoted labels", _B + ["labels: x y z"], _P8, "NRRD0004"),
+    ("three labels and units", _B + ['labels: "x" "y y" "z"', 'units: "mm" "mm" "mm"'], _P8, "NRRD0004"),
+    ("block type", ["type: block", "dimension: 3", "sizes: 2 2 2", "encoding: raw"], _P8, "NRRD0004"),
+    ("block size for uchar", _B + ["block size: 4"], _P8, "NRRD0004"),
+    ("gzip", _B[:3] + ["encoding: gzip"], _P8, "NRRD0004"),
+    ("bzip2", _B[:3] + ["encoding: bzip2"], _P8, "NRRD0004"),
+    ("negative line skip", _B + ["line skip: -1"], _P8, "NRRD0004"),
+    ("byte skip -1", _B + ["byte skip: -1"], bytes(10) + _P8, "NRRD0004"),
+    ("extra payload", _B, bytes([1]) * 20, "NRRD0004"),
+    ("short payload", _B, bytes([1]) * 5, "NRRD0004"),
+    ("missing data file", _B + ["data file: nothere.raw"], _P8, "NRRD0004"),
+    ("ascii too few", _B[:3] + ["encoding: ascii"], b"1 2 3\n", "NRRD0004"),
+    ("ascii too many", _B[:3] + ["encoding: ascii"], b"1 2 3 4 5 6 7 8 9 10\n", "NRRD0004"),
+    ("ascii not a number", _B[:3] + ["encoding: ascii"], b"1 2 x 4 5 6 7 8\n", "NRRD0004"),
+    ("ascii out of range, negative, fractional", _B[:3] + ["encoding: txt"], b"1 300 -3 4.5 5 6 7 8\n", "NRRD0004"),
+    ("hex odd", _B[:3] + ["encoding: hex"], b"010203040506070\n", "NRRD0004"),
+    ("hex not hex", _B[:3] + ["encoding: hex"], b"01020304050607zz\n", "NRRD0004"),
+    ("hex with white space", _B[:3] + ["encoding: hex"], b"01 02 03 04\n05 06 07 08\n", "NRRD0004"),
+]
+
+
+@pytest.mark.parametrize("case", NRRD_HEADER_CASES, ids=[c[0] for c in NRRD_HEADER_CASES])
+def test_nrrd_reader_accepts_exactly_what_nrrdio_accepts(vr, ref, tmp_path, case):
+    """Header rules of NrrdIO (what NrrdFileParser::parse, nrrd_file_parser.cpp:23-30, lets through): field
+    syntax, known fields, no field twice, ordering, per-axis counts, names, required fields, payload forms."""
+    _, lines, payload, magic = case
+    p = tmp_path / "h.nrrd"
+    p.write_bytes((magic + "\n" + "\n".join(lines) + "\n\n").encode() + payload)
+    try:
+        want = ref.load_nrrd(str(p))[0]
+    except RuntimeError:
+        want = None
+    try:
+        got = vr.read_nrrd(str(p))
+    except vr.VrError:
+        got = None
+    assert (got is None) == (want is None), "accepted" if got is not None else "rejected"
+    if want is not None:
+        assert got.shape == want.shape and np.array_equal(got.astype(np.float32), want)
+
+
+def test_nrrd_reader_against_nrrdio_on_random_headers(vr, ref, tmp_path):
+    """Seeded random headers -- every type name, encoding, version, optional fields in valid and invalid orders,
+    both line endings: same verdict as the reference parser and, where it reads the file, the same values."""
+    import random
+    rng = random.Random(20260411)
+    types = {"uchar": np.uint8, "unsigned char": np.uint8, "uint8": np.uint8, "uint8_t": np.uint8, "signed char": np.int8,
+             "int8": np.int8, "short": np.int16, "int16": np.int16, "short int": np.int16, "ushort": np.uint16,
+             "unsigned short": np.uint16, "uint16_t": np.uint16, "int": np.int32, "signed int": np.int32, "int32": np.int32,
+             "uint": np.uint32, "unsigned int": np.uint32, "longlong": np.int64, "long long": np.int64, "int64": np.int64,
+             "ulonglong": np.uint64, "unsigned long long": np.uint64, "uint64": np.uint64, "float": np.float32, "double": np.float64}
+    optional = ["spacings: 1 2 3", "kinds: domain domain domain", "centers: cell cell cell", "content: hello world", "# a comment",
+                "space: left-posterior-superior", 'labels: "x" "y" "z"', 'units: "mm" "mm" "mm"', "min: 0", "max: 5", "old min: 0",
+                "thicknesses: 1 1 1", "axis mins: 0 0 0", "sample units: HU", "line skip: 0", "byte skip: 0", "key:=value", "a b:=c d",
+                "space directions: (1,0,0) (0,1,0) (0,0,1)", "space origin: (0,0,0)"]
+    accepted = rejected = 0
+    for it in range(160):
+        tname = rng.choice(list(types))
+        dt = types[tname]
+        nx, ny, nz = rng.randint(1, 5), rng.randint(1, 4), rng.randint(1, 3)
+        arr = np.random.default_rng(it).integers(0, 100, (nz, ny, nx)).astype(dt)
+        enc, endian = rng.choice(["raw", "ascii", "txt", "text", "hex"]), rng.choice(["little", "big"])
+        fields = [f"type: {tname}", f"sizes: {nx} {ny} {nz}", f"encoding: {enc}"]
+        if (arr.dtype.itemsize > 1 and enc in ("raw", "hex")) or rng.random() < 0.3:
+            fields.append(f"endian: {endian}")
+        fields += [o for o in optional if rng.random() < 0.2]
+        rng.shuffle(fields)
+        if rng.random() < 0.75:   # mostly valid: dimension first, space before the space vectors, no spacings with directions
+            fields = ["dimension: 3"] + [f for f in fields if f.startswith("space:")] + [f for f in fields if not f.startswith("space:")]
+            if any(f.startswith("space directions") for f in fields):
+                fields = [f for f in fields if not f.startswith("spacings")]
+            if not any(f.startswith("space:") for f in fields):
+                fields = [f for f in fields if not f.startswith("space ")]
+        else:
+            fields.insert(rng.randint(0, len(fields)), "dimension: 3")
+        eol = rng.choice(["\n", "\r\n"])
+        data = arr.astype(arr.dtype.newbyteorder("<" if endian == "little" else ">"))
+        payload = (data.tobytes() if enc == "raw" else data.tobytes().hex().encode() if enc == "hex" else
+                   ("\n".join(" ".join(repr(x.item()) for x in row) for row in arr.reshape(-1, nx)) + "\n").encode())
+        p = tmp_path / f"r{it}.nrrd"
+        p.write_bytes((rng.choice(["NRRD0001", "NRRD0003", "NRRD0004", "NRRD0005"]) + eol + eol.join(fields) + eol + eol).encode() + payload)
+        try:
+            want = ref.load_nrrd(str(p))[0]
+        except RuntimeError:
+            want = None
+        try:
+            got = vr.read_nrrd(str(p))
+        except vr.VrError:
+            got = None
+        assert (got is None) == (want is None), (it, fields)
+        if want is not None:
+            accepted += 1
+            assert got.shape == want.shape and np.array_equal(got.astype(np.float32), want), (it, fields)
+        else:
+            rejected += 1
+    assert accepted >= 60 and rejected >= 15, (accepted, rejected)
+
+
 def write_csv_stack(tmp_path, vol, fmt="%.9g", eol="\n", last_eol=True, name="s"):
     paths = []
     for z, sl in enumerate(vol):
