@@ -410,6 +410,46 @@ def test_csv_reader_rejects_what_the_reference_rejects(vr, ref, tmp_path, files,
     assert str(want.value) in str(got.value)  # the text the reference's error popup would show
 
 
+def test_csv_reader_against_reference_parser_on_random_text(vr, ref, tmp_path):
+    """Seeded random slice stacks -- grids of plausible fields with noise, and plain random text over the CSV
+    alphabet: same verdict, same error text, same bits and the same min / max as the reference parser."""
+    import random
+    rng = random.Random(4711)
+    alphabet = "0123456789" * 3 + ".,,,,-+eE \n\n\n\r\tx" + "infa"
+    tokens = ["1", "-2.5", "3e2", " 4", "5 ", "0x1p3", "nan", "inf", "1e-50", "7abc", ".5", "-.5e1", "+3"]
+    accepted = 0
+    for it in range(400):
+        paths = []
+        for z in range(rng.randint(1, 3)):
+            if it % 2:
+                nx, ny = 1 + it % 4, 1 + (it // 4) % 3
+                rows = [",".join(rng.choice(tokens) for _ in range(nx)) for _ in range(ny)]
+                text = rng.choice(["\n", "\r\n"]).join(rows) + rng.choice(["", "\n", "\n\n", ","])
+                if rng.random() < 0.15:
+                    text = text.replace(",", ",,", 1)
+            else:
+                text = "".join(rng.choice(alphabet) for _ in range(rng.randint(0, 30)))
+            p = tmp_path / f"f{it}_{z}.csv"
+            p.write_bytes(text.encode())
+            paths.append(str(p))
+        try:
+            want, werr = ref.load_csv(paths), None
+        except RuntimeError as e:
+            want, werr = None, str(e)
+        try:
+            got, gerr = vr.read_csv(paths), None
+        except vr.VrError as e:
+            got, gerr = None, str(e)
+        assert (got is None) == (want is None), (it, paths)
+        if want is None:
+            assert werr in gerr
+        else:
+            accepted += 1
+            assert got.data.shape == want[0].shape and np.array_equal(bits(got.data), bits(want[0]))
+            assert np.array_equal(bits(np.float32([got.min, got.max])), bits(np.float32([want[1], want[2]])))
+    assert 40 <= accepted <= 360
+
+
 def test_partition_boxes_tile_the_grid(vr):
     for grid, full in [((2, 2, 2), (64, 64, 64)), ((3, 2, 1), (50, 33, 7)), ((1, 1, 1), (5, 5, 5)), ((2, 1, 1), (7, 3, 3))]:
         seen = np.zeros(full[::-1], np.int32)
