@@ -165,6 +165,22 @@ class OffscreenPass
         check(vr_download(ctx, img.data()));
         return img;
     }
+    // The viewport's sampling of the image (LINEAR, CLAMP_TO_EDGE; offscreen_pass.cpp:361-375, drawn by
+    // main_window.cpp:157-165): the frame resampled into a device RGBA8 buffer of another size.
+    void present(void *dst_device_rgba8, uint32_t width, uint32_t height, size_t pitch_bytes = 0, void *cuda_stream = nullptr,
+                 uint32_t frame_index = 0)
+    {
+        check(vr_present_frame(ctx, frame_index, dst_device_rgba8, width, height, pitch_bytes, cuda_stream));
+    }
+    // Bring a host RGBA8 buffer up to date with a frame in flight, copying only what can have changed since the
+    // last delivery into that buffer (outside the cube's screen box a frame is the clear colour, :170-173).
+    size_t download_dirty_async(void *host_rgba8, void *cuda_stream = nullptr, uint32_t frame_index = 0)
+    {
+        size_t bytes = 0;
+        check(vr_download_frame_dirty_async(ctx, frame_index, host_rgba8, cuda_stream, &bytes));
+        return bytes;
+    }
+    void write_image(const std::string &path) { check(vr_write_image(ctx, path.c_str())); }
     void wait_idle() { check(vr_sync(ctx)); }
     vr_ctx *handle() { return ctx; }
 
