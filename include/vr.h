@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define VR_ABI_VERSION 1
+#define VR_ABI_VERSION 2
 
 typedef enum vr_status {
     VR_OK = 0,
@@ -86,6 +86,18 @@ typedef struct vr_stats {
     uint64_t n_fetch;        /* volume fetches actually executed (after empty-space skipping) */
 } vr_stats;
 
+/* What the last vr_render_frame launched (every cost decision of the context, for harnesses and logs). */
+typedef struct vr_frame_info {
+    int32_t layout;            /* VR_LAYOUT_ARRAY3D or VR_LAYOUT_PAIRED: the copy the frame sampled */
+    int32_t pair_axis;         /* model axis 0..2 the pairs ran along; -1 on the 3-D array */
+    int32_t empty_skip_active; /* 1: the occupancy grid was consulted (options.empty_skip AND enough empty cells) */
+    int32_t exact_sampler;     /* 1: the verification sampler ran */
+    uint32_t bbox[4];          /* x0, y0, x1, y1 (exclusive): pixels the cube can cover */
+    uint32_t march_blocks;     /* CTAs launched over tiles of the bounding box */
+    uint32_t clear_blocks;     /* CTAs launched only to restore the clear colour (0 when the target already holds it) */
+    uint64_t target_bytes;     /* upper bound of the bytes the launch stores into the RGBA8 target (peer memory under sort-first) */
+} vr_frame_info;
+
 /* ---- lifetime ---------------------------------------------------------------------- */
 
 /* OffscreenPass::OffscreenPass(context, width, height) (offscreen_pass.cpp:112-134).
@@ -112,6 +124,8 @@ int vr_render(vr_ctx *ctx, void *cuda_stream);
  * another stream while frame k is still rendering or being downloaded.  vr_render = frame 0. */
 #define VR_MAX_FRAMES_IN_FLIGHT 4
 int vr_render_frame(vr_ctx *ctx, uint32_t frame_index, void *cuda_stream);
+/* The decisions vr_render_frame took for the frame it enqueued last. */
+int vr_get_last_frame_info(const vr_ctx *ctx, vr_frame_info *out);
 int vr_get_image_frame(vr_ctx *ctx, uint32_t frame_index, void **dev_rgba8, size_t *pitch_bytes);
 int vr_download_frame_async(vr_ctx *ctx, uint32_t frame_index, void *host_rgba8, void *cuda_stream);
 /* vr_download_frame_async that moves only what can differ from what `host_rgba8` already holds.  Outside the
@@ -324,7 +338,10 @@ int vr_set_image_target_frame(vr_ctx *ctx, uint32_t frame_index, void *dev_rgba8
 
 /* Texture-fetch roofline micro-benchmark: filtered fetches of an L1-resident volume of `dtype` from all
  * SMs; returns fetches per second (device-timed).  hw_filter: 0 = point tex3D, 1 = trilinear tex3D
- * (VR_LAYOUT_ARRAY3D's fetch), 2 = bilinear fetch of the paired layered array (VR_LAYOUT_PAIRED's fetch). */
+ * (VR_LAYOUT_ARRAY3D's fetch), 2 = bilinear fetch of the paired layered array (VR_LAYOUT_PAIRED's fetch).
+ * DRAM-fed ceilings of the same path (u8/u16 only): 3 = a 1 GiB paired layered array (8x the L2) streamed exactly
+ * once with ideal quad locality, one bilinear fetch per texel (4 new bytes per fetch for u16: K1's ratio on
+ * config 2); 4 = the same array with one fetch per 2x2 texels (16 new bytes per fetch: the byte ceiling). */
 int vr_bench_tex_peak(int device, int dtype, int hw_filter, double *fetches_per_s);
 /* Measurement aid (bench.py, roofline_tex.fetch_only): while on, vr_render / vr_render_frame run a build of
  * the march kernel that does everything up to and including the volume fetches of the frame (ray setup,

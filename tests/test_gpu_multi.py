@@ -47,6 +47,43 @@ def test_sort_first_ranks_write_into_one_image(vr, port):
     assert np.array_equal(got, want)
 
 
+def test_sort_first_moving_camera_restores_the_clear_colour(vr, port):
+    """Sort-first over several frames into ONE display image (rank contexts on one device, run in turn): every rank
+    restores the clear colour only on its own tiles and only where the previous frame drew outside this frame's
+    tiles; the assembled frame must stay bit-identical to one GPU while the cube moves, shrinks and grows."""
+    W, H, nranks = 328, 200, 3
+    lut = tf(port, "B")
+    ops = []
+    for r in range(nranks + 1):          # the last one is the single-GPU truth
+        op = vr.OffscreenPass(W, H)
+        op.synth_volume(vr.SYNTH_FBM, 0x5EED0002, vr.U16, 48)
+        op.transfer_function_changed(lut)
+        ops.append(op)
+    target, _ = ops[0].get_image()
+    for r in range(nranks):
+        ops[r].set_partition_sort_first(r, nranks, 32)
+        if r:
+            ops[r].set_image_target(target)
+    try:
+        stored = []
+        for j, z in enumerate([0.0, 0.0, -3.0, -3.0, 0.0, 2.0, 2.3, 0.0, -1.0]):
+            cam = vr.Camera().rotate((30.0 * j, 10.0 * j))
+            if z:
+                cam.zoom(z)
+            for op in ops:
+                op.set_camera(cam)
+            for r in range(nranks):
+                ops[r].record()
+                ops[r].sync()
+            stored.append(sum(ops[r].last_frame_info().target_bytes for r in range(nranks)))
+            ops[nranks].record()
+            assert np.array_equal(ops[0].download(), ops[nranks].download()), f"frame {j}"
+        assert stored[3] < stored[0] // 4        # a small box that did not move: almost nothing is stored
+    finally:
+        for op in ops:
+            op.close()
+
+
 def test_stream_flags_signal_wait_and_time_out(vr):
     """vr_stream_signal stores into local or foreign counters in stream order; vr_stream_wait holds a stream
     until its counters reach the value; a wait nobody answers gives up and makes the next vr_sync fail

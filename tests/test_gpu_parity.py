@@ -593,3 +593,78 @@ def test_dirty_rectangle_download_keeps_the_host_frame_complete(vr, port):
         assert np.array_equal(small.numpy(), op.download_frame(0))
     finally:
         op.close()
+
+
+def test_failed_upload_leaves_the_context_usable(vr, port):
+    """an upload that is refused (paired layout asked for a float volume) must not leave a half-installed
+    volume behind: the old volume keeps rendering, bit for bit."""
+    vol = small_volume(port, 1, np.uint16, 32)
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+        op.transfer_function_changed(tf(port, "C"))   # TF-C: empty-space skipping is active on this volume or not -- both paths below
+        cam, _ = twin_cameras(vr, port, [(-120, 80)])
+        op.set_camera(cam)
+        op.record()
+        before = op.download()
+        op.set_volume_layout(vr.LAYOUT_PAIRED)
+        with pytest.raises(vr.VrError):
+            op.volume_dataset_changed(vr.Dataset(np.zeros((8, 8, 8), np.float32), 0.0, 1.0))
+        for ess in (1, 0):
+            op.set_options(empty_skip=ess)
+            op.record()
+            assert np.array_equal(op.download(), before)
+        assert op.volume_info()[1] == (32, 32, 32)
+        # and a later good upload works
+        op.set_volume_layout(vr.LAYOUT_AUTO)
+        op.volume_dataset_changed(vr.Dataset(np.zeros((8, 8, 8), np.float32), 0.0, 1.0))
+        op.record()
+        op.download()
+    finally:
+        op.close()
+
+
+def test_dirty_clear_leaves_the_frames_unchanged(vr, port, monkeypatch):
+    """A frame restores the clear colour only where the previous frame into the same target drew outside its own
+    tiles (offscreen_pass.cpp:170-173 clears everything every frame): every frame -- RGBA8 and the float4 output --
+    must equal the one a context that clears the whole target gives, across orbit, zoom, slot reuse and resize."""
+    vol = small_volume(port, 1, np.uint16, 32)
+    moves = [((30 * i, 10 * i), z) for i, z in enumerate([0.0, 0.0, -3.0, -3.0, -3.0, 0.0, 2.0, 2.3, 2.3, 0.0, -1.0, -1.0, 2.6, 0.0])]
+
+    def run(dirty):
+        monkeypatch.setenv("VR_DIRTY_CLEAR", "1" if dirty else "0")
+        op = vr.OffscreenPass(320, 200)
+        frames, blocks = [], []
+        try:
+            op.set_options(write_raw=1)
+            op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+            op.transfer_function_changed(tf(port, "B"))
+            for j, (mv, zoom) in enumerate(moves):
+                f = j % 2
+                cam, _ = twin_cameras(vr, port, [mv], zoom)
+                op.set_camera(cam)
+                op.record(None, f)
+                blocks.append(op.last_frame_info().clear_blocks)
+                frames.append(op.download_frame(f))
+                if f == 0:
+                    frames.append(op.download_raw())
+            op.framebuffer_size_changed(160, 100)
+            for f in (0, 1, 0):
+                op.record(None, f)
+                blocks.append(op.last_frame_info().clear_blocks)
+                frames.append(op.download_frame(f))
+        finally:
+            op.close()
+        return frames, blocks
+
+    want, full_blocks = run(False)
+    got, blocks = run(True)
+    assert len(want) == len(got)
+    for k, (a, b) in enumerate(zip(want, got)):
+        assert np.array_equal(a, b), f"output {k}"
+    assert all(b > 0 for b in full_blocks)
+    assert blocks[0] > 0 and blocks[1] > 0            # first frame into each target: everything
+    assert blocks[4] == 0                             # same small box again in the same slot: nothing to restore
+    assert blocks[5] == 0                             # far -> near: the new tiles cover the old ones
+    assert 0 < blocks[11] < full_blocks[11]           # near -> far restores the rim between the two boxes only
+    assert blocks[-3] > 0 and blocks[-2] > 0 and blocks[-1] == 0   # new targets after the resize

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol(vr):
     assert not missing, f"declared in include/vr.h but not exported: {missing}"
     unbound = [n for n in sorted(declared) if n not in _lib.SIGNATURES]
     assert not unbound, f"declared but not bound in _lib.py: {unbound}"
-    assert vr.lib.vr_abi_version() == 1
+    assert vr.lib.vr_abi_version() == 2
 
 
 def test_no_cpu_fallback_without_device(vr):

@@ -23,7 +23,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import (F32, U8, U16, LAYOUT_ARRAY3D, LAYOUT_AUTO, LAYOUT_PAIRED, SAMPLER_EXACT, SAMPLER_HW, SYNTH_BLOBS,
-                   SYNTH_FBM, SYNTH_MARSCHNER_LOBB, Options, Stats)
+                   SYNTH_FBM, SYNTH_MARSCHNER_LOBB, FrameInfo, Options, Stats)
 
 lib = _lib.load()
 
@@ -202,6 +202,12 @@ class OffscreenPass:
         v, f = C.c_int(0), C.c_int(0)
         self._check(lib.vr_get_volume_layout(self._h, C.byref(v), C.byref(f)))
         return f.value - 1 if f.value else None
+
+    def last_frame_info(self) -> FrameInfo:
+        """vr_get_last_frame_info: layout / pair axis / skipping / launch shape of the frame recorded last."""
+        fi = FrameInfo()
+        self._check(lib.vr_get_last_frame_info(self._h, C.byref(fi)))
+        return fi
 
     def set_march(self, ray_dist: float, step_size: float):
         self._check(lib.vr_set_march(self._h, ray_dist, step_size))

@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvr_b200.so")
+LIB_PATH = os.environ.get("VR_LIB_PATH") or os.path.join(HERE, "libvr_b200.so")  # VR_LIB_PATH: an alternative build (experiments)
 
 VR_OK = 0
 U8, U16, F32 = 0, 1, 2
@@ -28,6 +28,11 @@ class Stats(C.Structure):
                 ("n_fetch", C.c_uint64)]
 
 
+class FrameInfo(C.Structure):
+    _fields_ = [("layout", C.c_int32), ("pair_axis", C.c_int32), ("empty_skip_active", C.c_int32), ("exact_sampler", C.c_int32),
+                ("bbox", C.c_uint32 * 4), ("march_blocks", C.c_uint32), ("clear_blocks", C.c_uint32), ("target_bytes", C.c_uint64)]
+
+
 # name -> (restype, argtypes); every symbol include/vr.h declares
 _P = C.c_void_p
 _F = C.POINTER(C.c_float)
@@ -39,6 +44,7 @@ SIGNATURES = {
     "vr_abi_version": (C.c_int, []),
     "vr_render": (C.c_int, [_P, _P]),
     "vr_render_frame": (C.c_int, [_P, C.c_uint32, _P]),
+    "vr_get_last_frame_info": (C.c_int, [_P, C.POINTER(FrameInfo)]),
     "vr_get_image_frame": (C.c_int, [_P, C.c_uint32, C.POINTER(_P), C.POINTER(C.c_size_t)]),
     "vr_download_frame_async": (C.c_int, [_P, C.c_uint32, _P, _P]),
     "vr_download_frame_dirty_async": (C.c_int, [_P, C.c_uint32, _P, _P, C.POINTER(C.c_size_t)]),

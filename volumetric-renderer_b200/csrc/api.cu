@@ -190,13 +190,47 @@ int alloc_target(vr_ctx *c, uint32_t w, uint32_t h)
     return VR_OK;
 }
 
-/* Make `dev` (linear, x fastest, local extent) the context's volume. */
+/* Can this volume be held in the paired layout at all?  (u8/u16, every axis within two layered arrays) */
+bool volume_can_pair(const vr_ctx *c, int dtype, uint32_t nx, uint32_t ny, uint32_t nz)
+{
+    const uint32_t nd[3] = {nx, ny, nz};
+    const int split = std::min(std::max(c->tune_pair_split, 2), 2048);
+    bool can_pair = dtype == VR_U8 || dtype == VR_U16;
+    for (int a = 0; a < 3; a++) can_pair = can_pair && nd[a] + 1 <= 2u * (uint32_t)split && nd[a] <= 32768;
+    return can_pair;
+}
+
+int install_volume_unchecked(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, const float *mn,
+                             const float *mx);
+
+/* Make `dev` (linear, x fastest, local extent) the context's volume.  A request that cannot be honoured is refused
+ * before anything is touched (the old volume stays); a failure while the new one is being built (out of memory, a
+ * CUDA error) leaves the context without a volume -- vr_render then reports "no volume" -- never half-installed. */
 int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, const float *mn,
                    const float *mx)
+{
+    if (c->layout_req == VR_LAYOUT_PAIRED && !volume_can_pair(c, dtype, nx, ny, nz))
+        return fail(c, VR_ERR_INVALID, "VR_LAYOUT_PAIRED needs a u8/u16 volume of at most 4095 voxels per axis");
+    const int rc = install_volume_unchecked(c, dev, dtype, nx, ny, nz, mn, mx);
+    if (rc != VR_OK) {
+        const std::string why = c->err;
+        cudaStreamSynchronize(c->stream);
+        release_volume(c);
+        c->nx = c->ny = c->nz = 0;
+        c->occ_n[0] = c->occ_n[1] = c->occ_n[2] = 0, c->occ_words = 0, c->occ_empty_cells = 0;
+        c->occ_dirty = true;
+        c->err = why;
+    }
+    return rc;
+}
+
+int install_volume_unchecked(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, const float *mn,
+                             const float *mx)
 {
     release_volume(c);
     c->dtype = dtype, c->nx = nx, c->ny = ny, c->nz = nz;
     c->layout_used = c->layout_req;
+    for (int i = 0; i < VR_MAX_FRAMES_IN_FLIGHT; i++) c->slot_clear[i].valid = false; /* (cheap) a new volume starts from a full clear */
     cudaChannelFormatDesc cd = dtype == VR_U8    ? cudaCreateChannelDesc<unsigned char>()
                                : dtype == VR_U16 ? cudaCreateChannelDesc<unsigned short>()
                                                  : cudaCreateChannelDesc<float>();
@@ -229,14 +263,9 @@ int install_volume(vr_ctx *c, const void *dev, int dtype, uint32_t nx, uint32_t 
      * a layered array holds at most 2048 layers, so an axis longer than 2047 voxels is split over two */
     const uint32_t nd[3] = {nx, ny, nz};
     const int split = std::min(std::max(c->tune_pair_split, 2), 2048);
-    bool can_pair = dtype == VR_U8 || dtype == VR_U16;
+    const bool can_pair = volume_can_pair(c, dtype, nx, ny, nz);
     size_t pair_bytes = 0;
-    for (int a = 0; a < 3; a++) {
-        can_pair = can_pair && nd[a] + 1 <= 2u * (uint32_t)split && nd[a] <= 32768;
-        pair_bytes += (size_t)nx * ny * nz / nd[a] * ((size_t)nd[a] + 1) * 2 * dtype_size(dtype);
-    }
-    if (c->layout_req == VR_LAYOUT_PAIRED && !can_pair)
-        return fail(c, VR_ERR_INVALID, "VR_LAYOUT_PAIRED needs a u8/u16 volume of at most 4095 voxels per axis");
+    for (int a = 0; a < 3; a++) pair_bytes += (size_t)nx * ny * nz / nd[a] * ((size_t)nd[a] + 1) * 2 * dtype_size(dtype);
     bool want_pairs = c->layout_req == VR_LAYOUT_PAIRED;
     if (c->layout_req == VR_LAYOUT_AUTO && can_pair && pair_bytes <= c->tune_pair_max_bytes) {
         size_t free_b = 0, total_b = 0;
@@ -362,6 +391,7 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     if (const char *e = std::getenv("VR_ESS_MIN_EMPTY")) c->tune_ess_min_empty = (float)std::atof(e);
     if (const char *e = std::getenv("VR_CTA_THREADS")) c->tune_threads = std::atoi(e) == 256 ? 256 : 128;
     if (const char *e = std::getenv("VR_BBOX")) c->tune_bbox = std::atoi(e);
+    if (const char *e = std::getenv("VR_DIRTY_CLEAR")) c->tune_dirty_clear = std::atoi(e);
     if (const char *e = std::getenv("VR_WARP_W")) {
         const int w = std::atoi(e);
         if (w == 4 || w == 8 || w == 16) c->tune_warp_w = w;
@@ -446,7 +476,7 @@ extern "C" int vr_resize(vr_ctx *c, uint32_t width, uint32_t height)
     if (width == 0 || height == 0) return VR_OK; /* offscreen_pass.cpp:237-239 */
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaDeviceSynchronize()); /* vkDeviceWaitIdle, :241 */
-    for (int i = 0; i < VR_MAX_FRAMES_IN_FLIGHT; i++) c->slot_bbox_valid[i] = false; /* new targets: nothing rendered yet */
+    for (int i = 0; i < VR_MAX_FRAMES_IN_FLIGHT; i++) c->slot_bbox_valid[i] = false, c->slot_clear[i].valid = false; /* new targets: nothing rendered yet */
     for (auto &t : c->host_targets) t.ptr = nullptr;
     return alloc_target(c, width, height);
 }
@@ -671,8 +701,10 @@ void permute3(T *v, const int perm[3])
     for (int j = 0; j < 3; j++) v[j] = t[perm[j]];
 }
 
-/* pair_axis < 0: the frame samples the 3-D array; else the model axis the pairs run along */
-void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
+/* pair_axis < 0: the frame samples the 3-D array; else the model axis the pairs run along.
+ * clear: pixel rectangle (x0, y0, x1, y1) of the target that may hold something else than the clear colour and must
+ * be restored outside this frame's tiles; nullptr = the whole target. */
+void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis, const uint32_t *clear = nullptr)
 {
     std::memset(&p, 0, sizeof(p));
     for (int r = 0; r < 4; r++) p.c0[r] = c->rc[0][r], p.c1[r] = c->rc[1][r], p.c2[r] = c->rc[2][r], p.c3[r] = c->rc[3][r];
@@ -753,7 +785,12 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
     p.tile_h = (uint32_t)c->tune_threads / VR_TILE;
     screen_bbox(c, p.bbox);
     p.ntx = (c->W + VR_TILE - 1) / VR_TILE, p.nty = (c->H + p.tile_h - 1) / p.tile_h;
-    p.nclr_x = (c->W + 63) / 64, p.nclr_y = (c->H + 31) / 32;
+    uint32_t clr[4] = {0, 0, c->W, c->H};
+    if (clear)
+        for (int i = 0; i < 4; i++) clr[i] = std::min(clear[i], i & 1 ? c->H : c->W);
+    const bool clr_any = clr[2] > clr[0] && clr[3] > clr[1];
+    p.clr_org[0] = clr[0] & ~63u, p.clr_org[1] = clr[1] & ~31u;
+    p.nclr_x = clr_any ? (clr[2] - p.clr_org[0] + 63) / 64 : 0, p.nclr_y = clr_any ? (clr[3] - p.clr_org[1] + 31) / 32 : 0;
     p.rect[0] = (int)(p.bbox[0] / VR_TILE), p.rect[1] = (int)(p.bbox[1] / p.tile_h);
     p.rect[2] = (int)((p.bbox[2] + VR_TILE - 1) / VR_TILE), p.rect[3] = (int)((p.bbox[3] + p.tile_h - 1) / p.tile_h);
     if (p.bbox[2] <= p.bbox[0] || p.bbox[3] <= p.bbox[1]) {
@@ -780,9 +817,19 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis)
     if (p.pt_nranks > 1 && p.pt_px % VR_TILE == 0 && p.pt_px % p.tile_h == 0) {
         /* ... and one clear block per partition tile of this rank */
         p.pt_enum = 1;
-        p.pt_cnt_clear = (p.pt_nx + p.pt_nranks - 1) / p.pt_nranks;
-        p.nclr_x = p.pt_cnt_clear * p.pt_ny, p.nclr_y = 1;
+        p.clr_t[0] = clr[0] / p.pt_px, p.clr_t[1] = clr[1] / p.pt_px;
+        p.clr_t[2] = std::min((clr[2] + p.pt_px - 1) / p.pt_px, p.pt_nx), p.clr_t[3] = std::min((clr[3] + p.pt_px - 1) / p.pt_px, p.pt_ny);
+        const bool any = clr_any && p.clr_t[2] > p.clr_t[0] && p.clr_t[3] > p.clr_t[1];
+        p.pt_cnt_clear = any ? (p.clr_t[2] - p.clr_t[0] + p.pt_nranks - 1) / p.pt_nranks : 0;
+        p.nclr_x = any ? p.pt_cnt_clear * (p.clr_t[3] - p.clr_t[1]) : 0, p.nclr_y = any ? 1 : 0;
     }
+}
+
+/* the pixel rectangle whose tiles the march blocks of this launch write completely */
+void drawn_rect(const vr_ctx *c, const MarchParams &p, uint32_t out[4])
+{
+    out[0] = std::min((uint32_t)p.rect[0] * VR_TILE, c->W), out[1] = std::min((uint32_t)p.rect[1] * p.tile_h, c->H);
+    out[2] = std::min((uint32_t)p.rect[2] * VR_TILE, c->W), out[3] = std::min((uint32_t)p.rect[3] * p.tile_h, c->H);
 }
 }  // namespace
 
@@ -871,8 +918,37 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
         if (c->tune_pair_axis >= 0) pair_axis = c->tune_pair_axis;
         if (policy == 2) pair = !ess && bw * bh >= (int64_t)sms * 10 * 128 && best < t3d;
     }
-    if (pair) fill_params(c, p, pair_axis);
+    /* Dirty clear.  The reference clears the whole attachment every frame (offscreen_pass.cpp:170-173); here a
+     * target keeps the clear colour outside the tiles the last frame into it marched, so a frame restores only
+     * those of them that lie outside its own tiles -- on an orbit a thin frame of pixels instead of the 83 % of the
+     * target outside the box (under sort-first: bytes that would cross NVLink into the display rank). */
+    float4 *raw_target = (frame_index == 0 && c->opt.write_raw) ? c->d_raw : nullptr;
+    vr_ctx::SlotClear &sc = c->slot_clear[frame_index];
+    const bool keep = c->tune_dirty_clear && sc.valid && sc.target == (const void *)target && sc.raw == (const void *)raw_target &&
+                      sc.W == c->W && sc.H == c->H && sc.pt_rank == c->pt_rank && sc.pt_nranks == c->pt_nranks && sc.pt_px == c->pt_px;
+    fill_params(c, p, pair ? pair_axis : -1, keep ? sc.drawn : nullptr);
+    {
+        uint32_t now[4];
+        drawn_rect(c, p, now);
+        /* nothing to restore when the previous frame's tiles all lie inside this frame's */
+        if (keep && (!(sc.drawn[2] > sc.drawn[0] && sc.drawn[3] > sc.drawn[1]) ||
+                     (now[0] <= sc.drawn[0] && now[1] <= sc.drawn[1] && now[2] >= sc.drawn[2] && now[3] >= sc.drawn[3])))
+            p.nclr_x = p.nclr_y = 0;
+        sc.valid = true, sc.target = target, sc.raw = raw_target, sc.W = c->W, sc.H = c->H;
+        sc.pt_rank = c->pt_rank, sc.pt_nranks = c->pt_nranks, sc.pt_px = c->pt_px;
+        std::memcpy(sc.drawn, now, sizeof now);
+    }
     c->last_pair = pair, c->last_pair_axis = pair_axis;
+    {
+        vr_frame_info &fi = c->last_info;
+        fi.layout = pair ? VR_LAYOUT_PAIRED : VR_LAYOUT_ARRAY3D, fi.pair_axis = pair ? pair_axis : -1;
+        fi.empty_skip_active = ess ? 1 : 0, fi.exact_sampler = exact ? 1 : 0;
+        for (int i = 0; i < 4; i++) fi.bbox[i] = p.bbox[i];
+        fi.march_blocks = p.sp_count, fi.clear_blocks = p.nclr_x * p.nclr_y;
+        const uint64_t tile_px = (uint64_t)VR_TILE * p.tile_h, clear_px = p.pt_enum ? (uint64_t)p.pt_px * p.pt_px : 64ull * 32ull;
+        const uint64_t rect_tiles = (uint64_t)std::max(p.rect[2] - p.rect[0], 0) * (uint64_t)std::max(p.rect[3] - p.rect[1], 0);
+        fi.target_bytes = 4ull * (std::min<uint64_t>(p.sp_count, (rect_tiles + c->pt_nranks - 1) / c->pt_nranks + p.pt_cnt) * tile_px + (uint64_t)fi.clear_blocks * clear_px);
+    }
     /* outside p.bbox every pixel of this frame is the clear colour (screen_bbox is conservative); with a
      * partition the frame is only partly this context's */
     for (int i = 0; i < 4; i++) c->slot_bbox[frame_index][i] = p.bbox[i];
@@ -896,6 +972,13 @@ extern "C" int vr_bench_fetch_only(vr_ctx *c, int on)
 {
     if (!c) return VR_ERR_INVALID;
     c->bench_fetch_only = on != 0;
+    return VR_OK;
+}
+
+extern "C" int vr_get_last_frame_info(const vr_ctx *c, vr_frame_info *out)
+{
+    if (!c || !out) return VR_ERR_INVALID;
+    *out = c->last_info;
     return VR_OK;
 }
 
@@ -1321,6 +1404,7 @@ extern "C" int vr_set_image_target_frame(vr_ctx *c, uint32_t frame_index, void *
     if (!c || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return fail(c, VR_ERR_INVALID, "vr_set_image_target_frame: bad arguments");
     if (frame_index == 0) c->ext_image = reinterpret_cast<uchar4 *>(dev_rgba8);
     else c->ext_image_slot[frame_index] = reinterpret_cast<uchar4 *>(dev_rgba8);
+    c->slot_clear[frame_index].valid = false; /* what a (re-)attached target holds is not known: the next frame clears all of it */
     return VR_OK;
 }
 

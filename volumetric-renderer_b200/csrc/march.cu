@@ -29,6 +29,12 @@
 
 #include "vr_ctx.h"
 
+/* Blocks of 128 threads per SM the hardware-sampler build is compiled for: 5 x 256 threads = 10 blocks of 128
+ * = 48 registers per thread (without the cap: 54 registers, 9 blocks). */
+#ifndef VR_MIN_BLOCKS
+#define VR_MIN_BLOCKS 5
+#endif
+
 namespace
 {
 
@@ -394,7 +400,7 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
  * PART: sort-last sub-volume.  PAIR: 0 = 3-D array, 1 = paired layout, 2 = paired layout whose copy spans
  * two layered arrays.  UB: steps per batch (HW sampler; two batches are in flight). */
 template <bool EXACT, bool ESS, bool STATS, bool PART, int PAIR, int UB, bool PROBE = false>
-__global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant__ MarchParams p)
+__global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART || UB > 2) ? 1 : VR_MIN_BLOCKS) k_march(const __grid_constant__ MarchParams p)
 {
     extern __shared__ float4 smem[];
     float4 *sP = smem;                              /* EXACT: nlut + 3 decoded texels */
@@ -402,8 +408,9 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
 
     /* Which tile.  The first sp_count blocks walk the tiles of the cube's screen bounding box in a
      * square spiral from its centre: the longest rays (through the middle of the cube) start
-     * first and the short ones at the silhouette fill the tail.  The remaining blocks cover the
-     * rest of the target with the clear colour. */
+     * first and the short ones at the silhouette fill the tail.  The remaining blocks restore the
+     * clear colour where the target does not hold it already (api.cu: dirty clear -- the whole target
+     * on the first frame into it, afterwards only what the previous frame drew outside this frame's tiles). */
     const uint32_t nthreads = blockDim.x;
     int tx, ty;
     const bool in_bbox = blockIdx.x < p.sp_count;
@@ -448,14 +455,16 @@ __global__ void __launch_bounds__(VR_CTA_THREADS) k_march(const __grid_constant_
         const uint32_t j = blockIdx.x - p.sp_count;
         uint32_t rx, ry, rw = 64u, rh = 32u;
         if (p.pt_enum) {
-            /* sort-first: one block per partition tile of this rank, row by row */
-            const uint32_t pty = j / p.pt_cnt_clear, jj = j - pty * p.pt_cnt_clear;
-            const uint32_t ptx = (p.pt_rank + p.pt_nranks - (pty * p.pt_m) % p.pt_nranks) % p.pt_nranks + jj * p.pt_nranks;
-            if (ptx >= p.pt_nx) return;
+            /* sort-first: one block per partition tile of this rank inside clr_t, row by row */
+            const uint32_t row = j / p.pt_cnt_clear, jj = j - row * p.pt_cnt_clear;
+            const uint32_t pty = p.clr_t[1] + row;
+            const uint32_t want = (p.pt_rank + p.pt_nranks - (pty * p.pt_m + p.clr_t[0]) % p.pt_nranks) % p.pt_nranks;
+            const uint32_t ptx = p.clr_t[0] + want + jj * p.pt_nranks;
+            if (ptx >= p.clr_t[2]) return;
             rx = ptx * p.pt_px, ry = pty * p.pt_px, rw = rh = p.pt_px;
         } else {
             const uint32_t jy = j / p.nclr_x;
-            ry = jy * 32u, rx = (j - jy * p.nclr_x) * 64u;
+            ry = p.clr_org[1] + jy * 32u, rx = p.clr_org[0] + (j - jy * p.nclr_x) * 64u;
         }
         const uint32_t c8 = (uint32_t)(VR_CLEAR_RGB * 255.0f + 0.5f), cw = c8 | (c8 << 8) | (c8 << 16) | 0xff000000u;
         const bool wide = (p.W & 3u) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;

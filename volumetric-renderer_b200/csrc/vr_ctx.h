@@ -90,7 +90,9 @@ struct MarchParams {
     /* CTA tiles: ntx x nty over the target; rect = tiles that can be covered (x0,y0,x1,y1, exclusive);
      * the first sp_count blocks spiral out from tile (sp_cx, sp_cy) over the square containing rect */
     uint32_t ntx, nty, sp_count;
-    uint32_t nclr_x, nclr_y; /* clear-colour blocks: 64x32 pixel regions over the target */
+    uint32_t nclr_x, nclr_y; /* clear-colour blocks: 64x32 pixel regions from clr_org on (pt_enum: nclr_x blocks, one per owned partition tile of clr_t) */
+    uint32_t clr_org[2];     /* pixel origin of the clear regions (multiples of 64, 32) */
+    uint32_t clr_t[4];       /* sort-first: partition tiles [x0, x1) x [y0, y1) that need the clear colour */
     int sp_cx, sp_cy, rect[4];
     int carveout;                                             /* shared-memory carve-out hint in percent, -1 = driver default */
     uint32_t warp_w;                                          /* warp footprint width: 4, 8 or 16 pixels */
@@ -149,6 +151,7 @@ struct vr_ctx {
     uint4 *d_lut_h = nullptr;
     /* tuning knobs (environment: VR_BATCH, VR_CTA_THREADS, VR_BBOX, VR_WARP_W, VR_CARVEOUT, VR_ESS_MIN_EMPTY) */
     int tune_batch = 2, tune_threads = 128, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
+    int tune_dirty_clear = 1; /* VR_DIRTY_CLEAR=0: restore the clear colour over the whole target every frame */
     int tune_pair_axis = -1;  /* VR_PAIR_AXIS: force the pair axis (experiments); -1 = the axis the camera looks down most */
     int tune_pair_policy = 2; /* VR_PAIR_POLICY: 0 never sample the paired layout, 1 always, 2 per frame (vr_render_frame) */
     size_t tune_pair_max_bytes = (size_t)160 << 30; /* and never more than the free memory minus a reserve */ /* AUTO layout: pair only if the paired copy fits this (VR_PAIR_MAX_MB) */
@@ -163,6 +166,15 @@ struct vr_ctx {
     unsigned char *d_dist = nullptr; /* 8 x cells */
     /* dirty-rectangle downloads (vr_download_frame_dirty_async): where each slot's last frame can differ from the
      * clear colour, and what each known host buffer holds */
+    /* what each frame slot's target holds outside the tiles its last frame marched (dirty clear, vr_render_frame):
+     * valid = every pixel this context owns of `target` (and `raw`) outside `drawn` is the clear colour (zero) */
+    struct SlotClear {
+        bool valid = false;
+        const void *target = nullptr, *raw = nullptr;
+        uint32_t W = 0, H = 0, drawn[4] = {0, 0, 0, 0};
+        uint32_t pt_rank = 0, pt_nranks = 1, pt_px = 0;
+    } slot_clear[VR_MAX_FRAMES_IN_FLIGHT];
+    vr_frame_info last_info = {};
     uint32_t slot_bbox[VR_MAX_FRAMES_IN_FLIGHT][4] = {};
     bool slot_bbox_valid[VR_MAX_FRAMES_IN_FLIGHT] = {false, false, false, false};
     struct HostTarget {
