@@ -110,6 +110,8 @@ int vr_destroy(vr_ctx *ctx);
  * the message of a failed vr_create. */
 const char *vr_last_error(const vr_ctx *ctx);
 int vr_abi_version(void);
+/* Version tag of the kernels in this build (what profiles/ and bench lines are stamped with). */
+const char *vr_kernel_version(void);
 
 /* ---- per-frame ----------------------------------------------------------------------- */
 
@@ -254,7 +256,12 @@ int vr_gradient_discretize(const float *color_markers, uint32_t nc, const float 
 
 /* ---- synthetic volumes (BASELINE.json configs), generated on the device ---------------- */
 
-typedef enum vr_synth_kind { VR_SYNTH_MARSCHNER_LOBB = 0, VR_SYNTH_FBM = 1, VR_SYNTH_BLOBS = 2 } vr_synth_kind;
+typedef enum vr_synth_kind {
+    VR_SYNTH_MARSCHNER_LOBB = 0,
+    VR_SYNTH_FBM = 1,
+    VR_SYNTH_BLOBS = 2,
+    VR_SYNTH_BLOBS_FBM = 3 /* config 5: the blobs as an envelope of the fractal noise (background exactly 0) */
+} vr_synth_kind;
 /* Generate the volume on the device and make it the context's volume (min/max computed on
  * the device). */
 int vr_synth_volume(vr_ctx *ctx, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz);

@@ -183,6 +183,27 @@ class Oracle:
         self.lib.vro_free(ptr)
         return a.reshape(dims[2], dims[1], dims[0]), mn.value, mx.value
 
+    def raster_cube(self, frame: Frame):
+        """oracle/raster.c: the reference's cube drawn by a software rasteriser under Vulkan's rules.
+        Returns (mask [H,W] u8: 0 or 1 + face, tex [H,W,3] f32: interpolated in_tex_coords, depth [H,W] f32)."""
+        h, w = frame.height, frame.width
+        mask, tex, depth = np.zeros((h, w), np.uint8), np.zeros((h, w, 3), np.float32), np.zeros((h, w), np.float32)
+        self.lib.vro_raster_cube.restype = C.c_int
+        self.lib.vro_raster_cube.argtypes = [C.POINTER(Frame), C.c_void_p, C.c_void_p, C.c_void_p]
+        if self.lib.vro_raster_cube(C.byref(frame), mask.ctypes.data, tex.ctypes.data, depth.ctypes.data) < 0:
+            raise RuntimeError("vro_raster_cube failed")
+        return mask, tex, depth
+
+    def entry_map(self, frame: Frame):
+        """vro_pixel_entry (the analytic coverage + entry the oracle and the kernel use) for every pixel."""
+        h, w = frame.height, frame.width
+        mask, tex = np.zeros((h, w), np.uint8), np.zeros((h, w, 3), np.float32)
+        self.lib.vro_entry_map.restype = C.c_int
+        self.lib.vro_entry_map.argtypes = [C.POINTER(Frame), C.c_void_p, C.c_void_p]
+        if self.lib.vro_entry_map(C.byref(frame), mask.ctypes.data, tex.ctypes.data) < 0:
+            raise RuntimeError("vro_entry_map failed")
+        return mask, tex
+
     def synth(self, kind: int, seed: int, dtype, n, nthreads=0) -> np.ndarray:
         nx, ny, nz = (n, n, n) if isinstance(n, int) else n
         code = dtype if isinstance(dtype, int) else _DTYPE_OF[np.dtype(dtype)]

@@ -108,6 +108,14 @@ int vro_load_csv(const char *const *paths, uint32_t npaths, uint32_t dims[3], fl
                  char *msg, size_t msg_len);
 void vro_free(void *);
 
+/* Independent check of S2 (port build only, oracle/raster.c): the cube's twelve triangles
+ * (src/rendering/offscreen_pass.cpp:55-90) rasterised under Vulkan's rules with the state at :661-712.
+ * mask[H*W]: 0 = no fragment, else 1 + face index; tex[H*W*3]: interpolated in_tex_coords; depth[H*W] or NULL.
+ * Returns the number of covered pixels (< 0 on failure). */
+int vro_raster_cube(const vro_frame *frame, uint8_t *mask, float *tex, float *depth);
+/* The analytic decision of vro_pixel_entry for every pixel, in the same form. */
+int vro_entry_map(const vro_frame *frame, uint8_t *mask, float *tex);
+
 /* Synthetic volumes of SURVEY.md section 8(d) (port build only; reference returns -1).
  * kind: 0 = Marschner-Lobb, 1 = fBm value noise, 2 = sparse Gaussian blobs. */
 int vro_synth(int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, void *out,

@@ -16,16 +16,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def main():
-    import torch
+def run_checks(vr, mg, rank, world, local):
+    """The checks proper (the process group is up, the device is set).  Returns the list of failures of THIS
+    rank; callers reduce over the ranks.  Also run by bench.py for its `partitioned.check` record."""
     import torch.distributed as dist
 
-    import volumetric_renderer_b200 as vr
-    from volumetric_renderer_b200 import multigpu as mg
-
-    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-    torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W, H, n = 400, 304, 96
     lut = vr.Gradient([(0.0, (0, 0, 0.5)), (0.5, (1, 0.5, 0)), (1.0, (1, 1, 1))], [(0.0, 0.0), (0.3, 0.0), (1.0, 0.08)]).discretize(256)
     cam = vr.Camera().rotate((-120.0, 80.0))
@@ -55,14 +50,16 @@ def main():
         if not np.array_equal(got, want):
             failures.append(f"sort-first differs in {(got != want).any(axis=-1).sum()} pixels")
     dist.barrier()
-    # pipelined: 9 more frames with a moving camera and no host synchronisation in between; the two
-    # image slots then hold the last two frames, each complete and bit-identical to one GPU
+    # pipelined: 9 more frames with a moving camera (the cube shrinks and grows: the clear colour is restored by
+    # the rank that owns the tile) and no host synchronisation in between; the two image slots then hold the last
+    # two frames, each complete and bit-identical to one GPU
     cams = []
     for k in range(9):
         c = vr.Camera().rotate((-120.0 + 40.0 * k, 80.0 - 10.0 * k))
+        c.zoom((-2.0, 0.0, 1.5, 0.0, -3.0, 1.0, 0.0, -1.0, 0.5)[k])
         cams.append(c)
         op.set_camera(c)
-        slot = sf.render()
+        sf.render()
     sf.finish()
     if rank == 0:
         for k in (7, 8):
@@ -82,7 +79,7 @@ def main():
     sf.close()
     op.close()
 
-    # ---- sort-last: peer-memory direct-send, then the NCCL exchange fallback --------------------------
+    # ---- sort-last: peer-memory direct-send, then the NCCL exchange fallback; two view octants ------------------
     for mode in ("p2p", "nccl"):
         op = vr.OffscreenPass(W, H, device=local)
         op.transfer_function_changed(lut)
@@ -104,9 +101,41 @@ def main():
             if d.max() > 1 or (d > 0).mean() > 0.01:
                 failures.append(f"sort-last/{mode}: max diff {d.max()}, differing {(d > 0).mean():.4f}")
         dist.barrier()
+        # a second camera in another octant, closer in (other view order, other bounding rectangles)
+        cam2 = vr.Camera().rotate((250.0, -140.0))
+        cam2.zoom(1.0)
+        op.set_camera(cam2)
+        sl.render(cam2.get_position())
+        sl.finish()
+        if rank == 0:
+            ref = vr.OffscreenPass(W, H, device=local)
+            ref.synth_volume(vr.SYNTH_FBM, 0x5EED0004, vr.U16, n)
+            ref.transfer_function_changed(lut)
+            ref.set_camera(cam2)
+            ref.record()
+            want2 = ref.download()
+            ref.close()
+            got = op.download()
+            d = np.abs(got.astype(int) - want2.astype(int))
+            if d.max() > 1 or (d > 0).mean() > 0.01:
+                failures.append(f"sort-last/{mode} second view: max diff {d.max()}, differing {(d > 0).mean():.4f}")
+        dist.barrier()
         sl.close()
         op.close()
+    return failures
 
+
+def main():
+    import torch
+    import torch.distributed as dist
+
+    import volumetric_renderer_b200 as vr
+    from volumetric_renderer_b200 import multigpu as mg
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    failures = run_checks(vr, mg, rank, world, local)
     ok = torch.tensor([len(failures)], device="cuda")
     dist.all_reduce(ok)
     if rank == 0:

@@ -22,10 +22,11 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _lib
-from ._lib import (F32, U8, U16, LAYOUT_ARRAY3D, LAYOUT_AUTO, LAYOUT_PAIRED, SAMPLER_EXACT, SAMPLER_HW, SYNTH_BLOBS,
+from ._lib import (F32, U8, U16, LAYOUT_ARRAY3D, LAYOUT_AUTO, LAYOUT_PAIRED, SAMPLER_EXACT, SAMPLER_HW, SYNTH_BLOBS, SYNTH_BLOBS_FBM,
                    SYNTH_FBM, SYNTH_MARSCHNER_LOBB, FrameInfo, Options, Stats)
 
 lib = _lib.load()
+KERNEL_VERSION = lib.vr_kernel_version().decode()
 
 _NP = {U8: np.uint8, U16: np.uint16, F32: np.float32}
 _CODE = {np.dtype(np.uint8): U8, np.dtype(np.uint16): U16, np.dtype(np.float32): F32}

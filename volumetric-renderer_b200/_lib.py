@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("VR_LIB_PATH") or os.path.join(HERE, "libvr_b200.so") 
 VR_OK = 0
 U8, U16, F32 = 0, 1, 2
 SAMPLER_HW, SAMPLER_EXACT = 0, 1
-SYNTH_MARSCHNER_LOBB, SYNTH_FBM, SYNTH_BLOBS = 0, 1, 2
+SYNTH_MARSCHNER_LOBB, SYNTH_FBM, SYNTH_BLOBS, SYNTH_BLOBS_FBM = 0, 1, 2, 3
 LAYOUT_AUTO, LAYOUT_ARRAY3D, LAYOUT_PAIRED = 0, 1, 2
 
 
@@ -42,6 +42,7 @@ SIGNATURES = {
     "vr_destroy": (C.c_int, [_P]),
     "vr_last_error": (C.c_char_p, [_P]),
     "vr_abi_version": (C.c_int, []),
+    "vr_kernel_version": (C.c_char_p, []),
     "vr_render": (C.c_int, [_P, _P]),
     "vr_render_frame": (C.c_int, [_P, C.c_uint32, _P]),
     "vr_get_last_frame_info": (C.c_int, [_P, C.POINTER(FrameInfo)]),

@@ -364,6 +364,7 @@ int default_state(vr_ctx *c)
 /* =============================================================== lifetime == */
 
 extern "C" int vr_abi_version(void) { return VR_ABI_VERSION; }
+extern "C" const char *vr_kernel_version(void) { return VR_KERNEL_VERSION; }
 
 extern "C" const char *vr_last_error(const vr_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
@@ -1200,7 +1201,7 @@ extern "C" int vr_download_volume(vr_ctx *c, void *host)
 
 extern "C" int vr_synth_volume(vr_ctx *c, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz)
 {
-    if (!c || kind < 0 || kind > 2 || dtype < VR_U8 || dtype > VR_F32 || nx == 0 || ny == 0 || nz == 0)
+    if (!c || kind < 0 || kind > VR_SYNTH_BLOBS_FBM || dtype < VR_U8 || dtype > VR_F32 || nx == 0 || ny == 0 || nz == 0)
         return fail(c, VR_ERR_INVALID, "vr_synth_volume: bad arguments");
     if (c->sort_last) return fail(c, VR_ERR_STATE, "vr_synth_volume: context is sort-last partitioned (use vr_synth_subvolume)");
     VR_CUDA(c, cudaSetDevice(c->device));
@@ -1221,7 +1222,7 @@ extern "C" int vr_synth_volume(vr_ctx *c, int kind, uint32_t seed, int dtype, ui
 
 extern "C" int vr_synth_subvolume(vr_ctx *c, int kind, uint32_t seed, int dtype)
 {
-    if (!c || kind < 0 || kind > 2 || dtype < VR_U8 || dtype > VR_F32) return fail(c, VR_ERR_INVALID, "vr_synth_subvolume: bad arguments");
+    if (!c || kind < 0 || kind > VR_SYNTH_BLOBS_FBM || dtype < VR_U8 || dtype > VR_F32) return fail(c, VR_ERR_INVALID, "vr_synth_subvolume: bad arguments");
     if (!c->sort_last) return fail(c, VR_ERR_STATE, "vr_synth_subvolume: call vr_set_partition_sort_last first");
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaDeviceSynchronize());

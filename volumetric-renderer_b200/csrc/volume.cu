@@ -391,6 +391,8 @@ __global__ void __launch_bounds__(256) k_synth(const __grid_constant__ SynthPara
                 v = fbm(s.seed, (float)i + 0.5f, (float)j + 0.5f, (float)k + 0.5f, s.inv_period);
             } else {
                 v = blobs_at(blobs, (float)i + 0.5f, (float)j + 0.5f, (float)k + 0.5f);
+                if (s.kind == VR_SYNTH_BLOBS_FBM && v > 0.0f)
+                    v *= 0.25f + 0.75f * fbm(s.seed, (float)i + 0.5f, (float)j + 0.5f, (float)k + 0.5f, s.inv_period);
             }
         }
         switch (s.dtype) {
