@@ -303,6 +303,17 @@ int vr_composite(vr_ctx *ctx, const void *const *parts, uint32_t nparts, uint64_
 int vr_composite_to(vr_ctx *ctx, const void *const *parts, uint32_t nparts, uint64_t pixel_begin, uint64_t pixel_end,
                     void *out_rgba8, void *cuda_stream);
 
+/* Sort-last exchanges bounding rectangles, not full frames.  A context under vr_set_partition_sort_last marches and
+ * stores only the pixels inside the screen bounding box of ITS sub-box; everywhere else its float4 output stays
+ * (0,0,0,0), the identity of the merge.  vr_partition_screen_rect returns that box (x0, y0, x1, y1, exclusive) for
+ * any sub-box of the grid under this context's camera and target size -- every rank computes every rank's box --
+ * and vr_composite_rects is vr_composite_to that neither reads nor composites partial k outside rects[4k..4k+3]
+ * (rects = NULL: every partial covers the frame). */
+int vr_partition_screen_rect(const vr_ctx *ctx, const uint32_t full_dims[3], const uint32_t org[3], const uint32_t dims[3],
+                             uint32_t rect[4]);
+int vr_composite_rects(vr_ctx *ctx, const void *const *parts, const uint32_t *rects, uint32_t nparts, uint64_t pixel_begin,
+                       uint64_t pixel_end, void *out_rgba8, void *cuda_stream);
+
 /* Peer memory for one-process-per-GPU runs (CUDA IPC; all GPUs of one NVLink/NVSwitch box).
  * vr_ipc_export: 64-byte handle of this context's RGBA8 image (which = 0) or float4 output
  * (which = 1).  vr_ipc_open maps a peer's buffer into this process (peer access is enabled on

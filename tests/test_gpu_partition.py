@@ -56,15 +56,21 @@ def test_sort_first_tiles_reassemble(vr, port, nranks):
     assert n_ref == want_stats.n_ref
 
 
-@pytest.mark.parametrize("grid", [(2, 1, 1), (2, 2, 1), (2, 2, 2), (3, 2, 1)])
+# camera moves: one per sign octant of the view direction, two of them close in (other bounding rectangles)
+OCTANT_MOVES = [([(-120, 80)], 0.0), ([(60, 80)], 0.0), ([(240, 80)], 1.2), ([(420, 80)], 0.0),
+                ([(-120, -140)], 0.0), ([(60, -140)], 1.6), ([(240, -140)], 0.0), ([(420, -140)], 0.0)]
+
+
+@pytest.mark.parametrize("grid,view", [((2, 1, 1), 0), ((2, 2, 1), 0), ((2, 2, 2), 0), ((3, 2, 1), 0)] + [((2, 2, 2), v) for v in range(1, 8)]
+                         + [((3, 2, 1), 5), ((1, 2, 2), 2)])
 @pytest.mark.parametrize("sampler", ["exact", "hw", "hw-pairs"])
-def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, sampler):
+def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, view, sampler):
     import torch  # device memory plumbing only
 
     n = 48
     lut = tf(port, "B")
-    moves = [(-120, 80)]
-    cam, ocam = twin_cameras(vr, port, moves)
+    moves, zoom = OCTANT_MOVES[view]
+    cam, ocam = twin_cameras(vr, port, moves, zoom)
     smp = vr.SAMPLER_EXACT if sampler == "exact" else vr.SAMPLER_HW
     lay = vr.LAYOUT_PAIRED if sampler == "hw-pairs" else vr.LAYOUT_ARRAY3D   # pairs: every rank's sub-box in the paired layout
     single = setup_pass(vr, W, H, lut, cam, layout=lay, sampler=smp)
@@ -74,9 +80,10 @@ def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, sampler)
     want, want_raw, want_stats = single.download(), single.download_raw(), single.stats()
 
     nbox = grid[0] * grid[1] * grid[2]
-    parts, passes, n_inslice = [], [], 0
+    parts, passes, n_inslice, rects, boxes = [], [], 0, [], []
     for b in range(nbox):
         org, dims = vr.partition_box(grid, (n, n, n), b)
+        boxes.append((org, dims))
         op = setup_pass(vr, W, H, lut, cam, layout=lay, sampler=smp)
         op.set_partition_sort_last((n, n, n), org, dims)
         op.synth_subvolume(vr.SYNTH_FBM, 0x5EED0005, vr.U16)
@@ -87,18 +94,34 @@ def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, sampler)
         n_inslice += op.stats().n_inslice
         parts.append(op.get_raw())
         passes.append(op)
-    assert n_inslice == want_stats.n_inslice, "every sample must be owned by exactly one rank"
+        # the rank stores nothing outside the screen box of its sub-box: there its partial is the identity
+        r = op.partition_screen_rect((n, n, n), org, dims)
+        assert r == tuple(op.last_frame_info().bbox)
+        rects.append(r)
+        raw = op.download_raw()
+        outside = np.ones((H, W), bool)
+        outside[r[1]:r[3], r[0]:r[2]] = False
+        assert not raw[outside].any()
+    if sampler == "exact":
+        assert n_inslice == want_stats.n_inslice, "every sample must be owned by exactly one rank"
+    else:
+        # hardware sampler: the ranks step pos_i = entry + i * d (one FMA, the same on every rank: each sample still has
+        # exactly one owner), one GPU accumulates -- a ray may gain or lose its last sample at the far face
+        assert abs(int(n_inslice) - int(want_stats.n_inslice)) <= 2e-4 * want_stats.n_inslice
 
     order = vr.partition_order(grid, (n, n, n), cam.get_position())
     single.composite([parts[i] for i in order], 0, W * H)
+    got_full = single.download()
+    single.composite([parts[i] for i in order], 0, W * H, rects=[rects[i] for i in order])
     got = single.download()
+    assert np.array_equal(got, got_full), "reading only the bounding rectangles must change nothing"
     for op in passes:
         op.close()
     single.close()
     d = np.abs(got.astype(int) - want.astype(int))
     assert d.max() <= 1 and (d > 0).mean() < 0.01, (d.max(), (d > 0).mean())
     if sampler == "exact":
-        # the wrong order would be visibly wrong; check that against a reversed merge of the oracle data
+        # the wrong order would be visibly wrong; check against the oracle's frame
         o = port.render(oracle_frame(port, ocam, W, H, mn, mx), port.synth(1, 0x5EED0005, np.uint16, n), lut)
         assert p999(got, o["rgba8"]) <= 1
 

@@ -331,9 +331,23 @@ class OffscreenPass:
     def clear_partition(self):
         self._check(lib.vr_clear_partition(self._h))
 
-    def composite(self, part_ptrs, pixel_begin: int, pixel_end: int, stream: int | None = None, out_ptr: int | None = None):
+    def composite(self, part_ptrs, pixel_begin: int, pixel_end: int, stream: int | None = None, out_ptr: int | None = None,
+                  rects=None):
+        """K2.  rects: per partial (x0, y0, x1, y1) outside which it is the identity and is not read (vr_composite_rects)."""
         arr = (C.c_void_p * len(part_ptrs))(*part_ptrs)
-        self._check(lib.vr_composite_to(self._h, arr, len(part_ptrs), pixel_begin, pixel_end, out_ptr, stream))
+        r = None
+        if rects is not None:
+            r = np.ascontiguousarray(rects, np.uint32).reshape(-1)
+            assert r.size == 4 * len(part_ptrs)
+        self._check(lib.vr_composite_rects(self._h, arr, _ptr(r) if r is not None else None, len(part_ptrs), pixel_begin, pixel_end,
+                                           out_ptr, stream))
+
+    def partition_screen_rect(self, full_dims, org, dims):
+        """vr_partition_screen_rect: pixels (x0, y0, x1, y1) the rays through that sub-box can cover under the current camera."""
+        f, o, d = (np.asarray(x, np.uint32) for x in (full_dims, org, dims))
+        out = np.zeros(4, np.uint32)
+        self._check(lib.vr_partition_screen_rect(self._h, _ptr(f), _ptr(o), _ptr(d), _ptr(out)))
+        return tuple(int(x) for x in out)
 
     def ipc_export(self, which: int = 0) -> bytes:
         buf = (C.c_ubyte * 64)()

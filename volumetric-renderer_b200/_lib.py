@@ -97,6 +97,8 @@ SIGNATURES = {
     "vr_clear_partition": (C.c_int, [_P]),
     "vr_composite": (C.c_int, [_P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _P]),
     "vr_composite_to": (C.c_int, [_P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _P, _P]),
+    "vr_partition_screen_rect": (C.c_int, [_P, _P, _P, _P, _P]),
+    "vr_composite_rects": (C.c_int, [_P, _P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _P, _P]),
     "vr_get_flags": (C.c_int, [_P, C.POINTER(_P)]),
     "vr_stream_signal": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, _P]),
     "vr_stream_wait": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32, _P]),

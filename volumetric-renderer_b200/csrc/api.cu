@@ -670,16 +670,19 @@ int ensure_slot(vr_ctx *c, uint32_t frame_index)
 
 /* Pixels the cube can cover: the projections of its 8 corners bound its silhouette when all of
  * them are in front of the eye; otherwise (camera inside or near the cube) the whole target. */
-void screen_bbox(const vr_ctx *c, uint32_t bbox[4])
+void screen_bbox(const vr_ctx *c, uint32_t bbox[4], const double *box_lo = nullptr, const double *box_hi = nullptr)
 {
     bbox[0] = 0, bbox[1] = 0, bbox[2] = c->W, bbox[3] = c->H;
     if (!c->tune_bbox) return;
+    const double unit_lo[3] = {-0.5, -0.5, -0.5}, unit_hi[3] = {0.5, 0.5, 0.5};
+    if (!box_lo) box_lo = unit_lo;
+    if (!box_hi) box_hi = unit_hi;
     double v[16], p[16], pv[16];
     for (int i = 0; i < 16; i++) v[i] = (double)c->view[i], p[i] = (double)c->proj[i];
     mat4_mul_d(p, v, pv);
     double x0 = 1e30, y0 = 1e30, x1 = -1e30, y1 = -1e30;
     for (int k = 0; k < 8; k++) {
-        const double q[3] = {(k & 1) ? 0.5 : -0.5, (k & 2) ? 0.5 : -0.5, (k & 4) ? 0.5 : -0.5};
+        const double q[3] = {(k & 1) ? box_hi[0] : box_lo[0], (k & 2) ? box_hi[1] : box_lo[1], (k & 4) ? box_hi[2] : box_lo[2]};
         double h[4];
         for (int r = 0; r < 4; r++) h[r] = pv[r] * q[0] + pv[4 + r] * q[1] + pv[8 + r] * q[2] + pv[12 + r];
         if (!(h[3] > 1e-4)) return;
@@ -693,6 +696,19 @@ void screen_bbox(const vr_ctx *c, uint32_t bbox[4])
     bbox[1] = (uint32_t)std::min(std::max(ly, 0.0), (double)c->H);
     bbox[2] = (uint32_t)std::min(std::max(hx, 0.0), (double)c->W);
     bbox[3] = (uint32_t)std::min(std::max(hy, 0.0), (double)c->H);
+}
+
+/* Pixels the rays through a sub-box of the grid can cover (sort-last: what a rank marches and stores; outside it
+ * the rank's partial is the identity).  The box is the half-open ownership region widened by half a voxel: a sample
+ * owned by the rank lies inside it. */
+void subbox_screen_rect(const vr_ctx *c, const uint32_t full[3], const uint32_t org[3], const uint32_t dims[3], uint32_t rect[4])
+{
+    double lo[3], hi[3];
+    for (int i = 0; i < 3; i++) {
+        lo[i] = std::max(((double)org[i] - 0.5) / (double)full[i], 0.0) - 0.5;
+        hi[i] = std::min(((double)org[i] + (double)dims[i] + 0.5) / (double)full[i], 1.0) - 0.5;
+    }
+    screen_bbox(c, rect, lo, hi);
 }
 
 template <typename T>
@@ -784,7 +800,8 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis, const uint32_t 
     p.warp_w = (uint32_t)c->tune_warp_w;
     p.carveout = c->tune_carveout;
     p.tile_h = (uint32_t)c->tune_threads / VR_TILE;
-    screen_bbox(c, p.bbox);
+    if (c->sort_last) subbox_screen_rect(c, c->full, c->own_org, c->own_dims, p.bbox);
+    else screen_bbox(c, p.bbox);
     p.ntx = (c->W + VR_TILE - 1) / VR_TILE, p.nty = (c->H + p.tile_h - 1) / p.tile_h;
     uint32_t clr[4] = {0, 0, c->W, c->H};
     if (clear)
@@ -1476,12 +1493,28 @@ extern "C" int vr_ipc_close(vr_ctx *c, void *dev_ptr)
 extern "C" int vr_composite_to(vr_ctx *c, const void *const *parts, uint32_t nparts, uint64_t pixel_begin,
                                uint64_t pixel_end, void *out_rgba8, void *cuda_stream)
 {
+    return vr_composite_rects(c, parts, nullptr, nparts, pixel_begin, pixel_end, out_rgba8, cuda_stream);
+}
+
+extern "C" int vr_partition_screen_rect(const vr_ctx *c, const uint32_t full_dims[3], const uint32_t org[3], const uint32_t dims[3],
+                                        uint32_t rect[4])
+{
+    if (!c || !full_dims || !org || !dims || !rect) return VR_ERR_INVALID;
+    for (int i = 0; i < 3; i++)
+        if (full_dims[i] == 0 || dims[i] == 0 || org[i] + dims[i] > full_dims[i]) return VR_ERR_INVALID;
+    subbox_screen_rect(c, full_dims, org, dims, rect);
+    return VR_OK;
+}
+
+extern "C" int vr_composite_rects(vr_ctx *c, const void *const *parts, const uint32_t *rects, uint32_t nparts, uint64_t pixel_begin,
+                                  uint64_t pixel_end, void *out_rgba8, void *cuda_stream)
+{
     if (!c || !parts || nparts == 0) return fail(c, VR_ERR_INVALID, "vr_composite: bad arguments");
     if (pixel_end > (uint64_t)c->W * c->H || pixel_begin > pixel_end) return fail(c, VR_ERR_INVALID, "vr_composite: pixel range outside the frame");
     VR_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
     c->last_stream = s;
     uchar4 *out = out_rgba8 ? reinterpret_cast<uchar4 *>(out_rgba8) : (c->ext_image ? c->ext_image : c->d_image);
-    VR_CUDA(c, vr_launch_composite(reinterpret_cast<const float4 *const *>(parts), nparts, pixel_begin, pixel_end, out, nullptr, s));
+    VR_CUDA(c, vr_launch_composite(reinterpret_cast<const float4 *const *>(parts), rects, nparts, pixel_begin, pixel_end, c->W, out, nullptr, s));
     return VR_OK;
 }

@@ -24,6 +24,12 @@ namespace
 struct PartTable {
     const float4 *p[VR_MAX_PARTS];
 };
+/* Pixel rectangle (x0, y0, x1, y1, exclusive) outside which a partial is the identity (0, 0, 0, 0): the screen
+ * bounding box of that rank's sub-box.  Such pixels are neither stored by K1 nor read here ("send
+ * bounding rectangles, not full frames"). */
+struct RectTable {
+    uint32_t r[VR_MAX_PARTS][4];
+};
 
 __device__ __forceinline__ float4 ld_stream(const float4 *ptr)
 {
@@ -35,18 +41,25 @@ __device__ __forceinline__ float4 ld_stream(const float4 *ptr)
     return v;
 }
 
-__global__ void __launch_bounds__(256) k_composite(const __grid_constant__ PartTable tab, uint32_t nparts,
-                                                   uint64_t begin, uint64_t end, uchar4 *out, float4 *raw_out)
+template <bool RECTS>
+__global__ void __launch_bounds__(256) k_composite(const __grid_constant__ PartTable tab, const __grid_constant__ RectTable rects,
+                                                   uint32_t nparts, uint64_t begin, uint64_t end, uint32_t W, uchar4 *out, float4 *raw_out)
 {
     for (uint64_t i = begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < end;
          i += (uint64_t)gridDim.x * blockDim.x) {
         float cr = 0.f, cg = 0.f, cb = 0.f, T = 1.f;
+        uint32_t x = 0, y = 0;
+        if (RECTS) y = (uint32_t)(i / W), x = (uint32_t)(i - (uint64_t)y * W);
         /* issue up to 8 loads before the dependent chain */
         for (uint32_t k0 = 0; k0 < nparts; k0 += 8) {
             float4 v[8];
 #pragma unroll
             for (int k = 0; k < 8; k++)
-                if (k0 + k < nparts) v[k] = ld_stream(tab.p[k0 + k] + i);
+                if (k0 + k < nparts) {
+                    v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (!RECTS || (x >= rects.r[k0 + k][0] && y >= rects.r[k0 + k][1] && x < rects.r[k0 + k][2] && y < rects.r[k0 + k][3]))
+                        v[k] = ld_stream(tab.p[k0 + k] + i);
+                }
 #pragma unroll
             for (int k = 0; k < 8; k++)
                 if (k0 + k < nparts) {
@@ -73,18 +86,23 @@ __global__ void __launch_bounds__(256) k_composite(const __grid_constant__ PartT
 }
 }  // namespace
 
-cudaError_t vr_launch_composite(const float4 *const *parts, uint32_t nparts, uint64_t begin, uint64_t end, uchar4 *out,
-                                float4 *raw_out, cudaStream_t s)
+cudaError_t vr_launch_composite(const float4 *const *parts, const uint32_t *rects, uint32_t nparts, uint64_t begin, uint64_t end,
+                                uint32_t W, uchar4 *out, float4 *raw_out, cudaStream_t s)
 {
     if (nparts == 0 || nparts > VR_MAX_PARTS) return cudaErrorInvalidValue;
     if (end <= begin) return cudaSuccess;
     PartTable tab;
+    RectTable rt = {};
     for (uint32_t k = 0; k < VR_MAX_PARTS; k++) tab.p[k] = k < nparts ? parts[k] : nullptr;
+    if (rects)
+        for (uint32_t k = 0; k < nparts; k++)
+            for (int j = 0; j < 4; j++) rt.r[k][j] = rects[4 * k + j];
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     uint64_t blocks = (end - begin + 255) / 256;
     if (blocks > (uint64_t)sms * 8) blocks = (uint64_t)sms * 8;
-    k_composite<<<(unsigned)blocks, 256, 0, s>>>(tab, nparts, begin, end, out, raw_out);
+    if (rects) k_composite<true><<<(unsigned)blocks, 256, 0, s>>>(tab, rt, nparts, begin, end, W, out, raw_out);
+    else k_composite<false><<<(unsigned)blocks, 256, 0, s>>>(tab, rt, nparts, begin, end, W, out, raw_out);
     return cudaGetLastError();
 }

@@ -199,18 +199,37 @@ struct Ray {
     float sgx, sgy, sgz;   /* ESS: sign of the direction, per axis */
     uint32_t doff;         /* ESS: offset of the distance map of the direction's octant */
     bool in_empty;         /* ESS: the last step generated fell into an empty fine cell */
+    /* sort-last, hardware sampler: positions are a pure function of the step index, pos_i = e + i * d (one FMA),
+     * so that every rank computes the same position for step i wherever it starts walking (see outer_interval) */
+    float ex, ey, ez, fi;
+    int i_end;             /* last step that can still be sampled (sort-last: where the ray leaves the rank's box) */
 };
+
+/* volume.frag:47, `ray_pos += ray_dir * step`.  FUNC (sort-last + hardware sampler): the same position evaluated as
+ * e + i * d with a single rounding -- within steps * ulp / 2 of the accumulated one (the bound safe_interval
+ * already allows for), identical on every rank. */
+template <bool FUNC>
+__device__ __forceinline__ void advance(Ray &r)
+{
+    if (FUNC) {
+        r.fi += 1.0f;
+        r.px = fmaf(r.fi, r.dx, r.ex), r.py = fmaf(r.fi, r.dy, r.ey), r.pz = fmaf(r.fi, r.dz, r.ez);
+    } else {
+        r.px += r.dx, r.py += r.dy, r.pz += r.dz;
+    }
+    r.i++;
+}
 
 /* The positions volume.frag:47 accumulates are monotone on every axis, and differ from
  * tex + i*d by at most steps * ulp(1)/2.  So the steps that pass the bounds test (:34-37), the
  * strict slice test (:39-40) and the sort-last ownership test form one interval of i, and the
  * analytic interval shrunk by that error bound and by one step at each end is inside it:
  * those steps can run without evaluating any of the tests, with identical results. */
-__device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r, int &fast_lo, int &fast_hi)
+__device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r, float e0, float e1, float e2, int &fast_lo, int &fast_hi)
 {
     const float eps = (float)(p.steps + 2) * 1.2e-7f;
     float tlo = 0.0f, thi = (float)(p.steps - 1);
-    const float p0[3] = {r.px, r.py, r.pz}, d[3] = {r.dx, r.dy, r.dz};
+    const float p0[3] = {e0, e1, e2}, d[3] = {r.dx, r.dy, r.dz}; /* the entry point: step 0 */
 #pragma unroll
     for (int a = 0; a < 3; a++) {
         const float lo = p.box_lo[a] + eps, hi = p.box_hi[a] - eps;
@@ -226,6 +245,33 @@ __device__ __forceinline__ void safe_interval(const MarchParams &p, const Ray &r
     if (tlo == tlo && thi == thi && thi - tlo >= 4.0f && tlo < 1.0e6f) {
         fast_lo = (int)ceilf(tlo) + 1;
         fast_hi = (int)floorf(thi) - 1;
+    }
+}
+
+/* Sort-last: the steps that CAN fall into the rank's box (bounds, slices and ownership intersected) lie inside the
+ * analytic interval of the box grown by the same error bound and by one step at each end.  A rank walks only
+ * those: it starts at step lo with pos = e + lo * d instead of stepping through its neighbours' boxes. */
+__device__ __forceinline__ void outer_interval(const MarchParams &p, const Ray &r, int &lo_i, int &hi_i)
+{
+    const float eps = (float)(p.steps + 2) * 1.2e-7f;
+    float tlo = 0.0f, thi = (float)(p.steps - 1);
+    const float p0[3] = {r.px, r.py, r.pz}, d[3] = {r.dx, r.dy, r.dz};
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        const float lo = p.box_lo[a] - eps, hi = p.box_hi[a] + eps;
+        if (d[a] != 0.0f) {
+            const float inv = __frcp_rn(d[a]);
+            const float ta = (lo - p0[a]) * inv, tb = (hi - p0[a]) * inv;
+            tlo = fmaxf(tlo, fminf(ta, tb));
+            thi = fminf(thi, fmaxf(ta, tb));
+        } else if (!(p0[a] >= lo && p0[a] <= hi)) {
+            thi = -4.0f;
+        }
+    }
+    lo_i = 0, hi_i = p.steps - 1;
+    if (tlo == tlo && thi == thi && tlo < 1.0e6f) {
+        lo_i = max((int)floorf(tlo) - 1, 0);
+        hi_i = min((int)ceilf(thi) + 1, p.steps - 1);
     }
 }
 
@@ -269,7 +315,12 @@ __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fas
         r.i += k;
         if (STATS) r.nb += (uint32_t)k, r.ns += (uint32_t)k;
         const float kf = (float)k;
-        r.px = fmaf(kf, r.dx, r.px), r.py = fmaf(kf, r.dy, r.py), r.pz = fmaf(kf, r.dz, r.pz);
+        if (PART) {
+            r.fi += kf;
+            r.px = fmaf(r.fi, r.dx, r.ex), r.py = fmaf(r.fi, r.dy, r.ey), r.pz = fmaf(r.fi, r.dz, r.ez);
+        } else {
+            r.px = fmaf(kf, r.dx, r.px), r.py = fmaf(kf, r.dy, r.py), r.pz = fmaf(kf, r.dz, r.pz);
+        }
     }
 }
 
@@ -294,7 +345,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
         bool s;
         if (CHECK) {
             /* volume.frag:33-37: loop bound and the strict bounds test */
-            const bool inb = !r.done && r.i < p.steps &&
+            const bool inb = !r.done && (PART ? r.i <= r.i_end : r.i < p.steps) &&
                              !(r.px > 1.0f || r.py > 1.0f || r.pz > 1.0f || r.px < 0.0f || r.py < 0.0f || r.pz < 0.0f);
             if (!inb) r.done = true;
             /* volume.frag:39-40: strict on both sides */
@@ -321,9 +372,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
         }
         if (CHECK || PRED) b.ok[u] = s;
         qx[u] = r.px, qy[u] = r.py, qz[u] = r.pz;
-        /* volume.frag:47 */
-        r.px += r.dx, r.py += r.dy, r.pz += r.dz;
-        r.i++;
+        advance<PART && !EXACT>(r);
     }
 #pragma unroll
     for (int u = 0; u < U; u++) {
@@ -551,11 +600,24 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
     ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
     ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.sgx = ray.sgy = ray.sgz = 1.0f, ray.doff = 0u, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
+    ray.ex = posx, ray.ey = posy, ray.ez = posz, ray.fi = 0.0f, ray.i_end = p.steps - 1;
+    if (PART && !EXACT && covered) {
+        /* walk only the steps that can fall into this rank's box */
+        int lo_i, hi_i;
+        outer_interval(p, ray, lo_i, hi_i);
+        if (hi_i < lo_i) {
+            ray.done = true;
+        } else {
+            ray.i = lo_i, ray.fi = (float)lo_i, ray.i_end = hi_i;
+            ray.px = fmaf(ray.fi, dx, posx), ray.py = fmaf(ray.fi, dy, posy), ray.pz = fmaf(ray.fi, dz, posz);
+        }
+    }
+
     bool parked = false; /* fast phase: this lane only keeps its warp company */
     float t_saved = 1.0f;
     /* Steps fast_lo..fast_hi need no bounds / slice / ownership test (see safe_interval). */
     int fast_lo = 0x7fffffff, fast_hi = -1;
-    if (covered && !EXACT) safe_interval(p, ray, fast_lo, fast_hi);
+    if (covered && !EXACT) safe_interval(p, ray, posx, posy, posz, fast_lo, fast_hi);
 
     constexpr int U = EXACT ? 1 : UB;
     LutH L;
@@ -613,6 +675,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
                 if (ray.done && !parked) {
                     parked = true, t_saved = ray.T, ray.T = 0.0f;
                     ray.px = ray.py = ray.pz = 0.5f, ray.dx = ray.dy = ray.dz = 0.0f;
+                    ray.ex = ray.ey = ray.ez = 0.5f;
                 }
                 batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, a);
 #pragma unroll 1

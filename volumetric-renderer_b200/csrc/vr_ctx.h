@@ -239,7 +239,7 @@ inline uint32_t vr_sort_first_stride(uint32_t n)
         if (a == 1) return m;
     }
 }
-cudaError_t vr_launch_composite(const float4 *const *d_parts_table, uint32_t nparts, uint64_t begin, uint64_t end,
-                                uchar4 *out, float4 *raw_out, cudaStream_t s);
+cudaError_t vr_launch_composite(const float4 *const *d_parts_table, const uint32_t *rects, uint32_t nparts, uint64_t begin, uint64_t end,
+                                uint32_t W, uchar4 *out, float4 *raw_out, cudaStream_t s);
 
 #endif

@@ -201,7 +201,8 @@ class SortLast:
         self.full = tuple(int(x) for x in full_dims)
         self.grid = tuple(grid) if grid else grid_for_world(world)
         assert self.grid[0] * self.grid[1] * self.grid[2] == world
-        self.org, self.dims = partition_box(self.grid, self.full, rank)
+        self._boxes = [partition_box(self.grid, self.full, r) for r in range(world)]
+        self.org, self.dims = self._boxes[rank]
         op.set_options(write_raw=1)
         op.set_partition_sort_last(self.full, self.org, self.dims)
         w, h = op.size
@@ -241,10 +242,12 @@ class SortLast:
         from . import partition_order
         op, rank, world = self.op, self.rank, self.world
         order = [int(b) for b in partition_order(self.grid, self.full, camera_position)]
+        # every rank's partial is the identity outside the screen box of its sub-box: K1 stores and K2 reads only inside
+        rects = [op.partition_screen_rect(self.full, *self._boxes[r]) for r in order]
         b, e = self.ranges[rank]
         if world == 1:
             op.record(stream)
-            op.composite([op.get_raw()], 0, self.npix, stream)
+            op.composite([op.get_raw()], 0, self.npix, stream, rects=rects)
             if self.on_frame:
                 self.on_frame(0, stream)
             return
@@ -263,7 +266,7 @@ class SortLast:
             if k >= 1 and rank != disp:
                 op.stream_wait(f.ptr(rank, _F_CONSUMED), 1, k, stream)        # frame k-1 has left the display image
             if e > b:
-                op.composite([self._peers_raw[r] for r in order], b, e, stream, out_ptr=self._peer_img)
+                op.composite([self._peers_raw[r] for r in order], b, e, stream, out_ptr=self._peer_img, rects=rects)
             op.stream_signal([f.ptr(r, _F_READ_DONE + rank) for r in range(world)] + [f.ptr(disp, _F_RANGE_DONE + rank)],
                              k + 1, stream)
             if rank == disp:
