@@ -580,7 +580,7 @@ def measure_partitioned(vr, mode, rank, world, local, n, W, H, K, Wu, synth=None
         op.synth_volume(synth[0], synth[1], vr.U16, n)
         part = mg.SortFirst(op, rank, world, tile_px=tile_px, slots=slots)
     else:
-        part = mg.SortLast(op, rank, world, (n, n, n), mode=merge, grid=grid)
+        part = mg.SortLast(op, rank, world, (n, n, n), mode=merge, grid=grid, slots=slots)
         op.synth_subvolume(synth[0], synth[1], vr.U16)
         part.set_global_density_range()
     frames = partitioned_frames(vr, W, H)
@@ -624,7 +624,7 @@ def measure_partitioned(vr, mode, rank, world, local, n, W, H, K, Wu, synth=None
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     dt = tt.item()
-    checksum = int(np_sum_image(op)) if rank == 0 else None
+    checksum = int(np_sum_image(op, part.image_slot())) if rank == 0 else None
     fi = op.last_frame_info()
     out = {"n_gpus": world, "ms_per_step": dt / K * 1e3, "steps": K, "samples_per_s": counts[0].item() / dt,
            "executed_samples_per_s": counts[1].item() / dt, "executed_per_frame": counts[1].item() / K,
@@ -774,9 +774,9 @@ def run_partitioned(args):
         dist.destroy_process_group()
 
 
-def np_sum_image(op):
+def np_sum_image(op, slot=0):
     import numpy as np
-    return op.download().astype(np.int64).sum()
+    return op.download_frame(slot).astype(np.int64).sum()
 
 
 def main():

@@ -217,6 +217,9 @@ int vr_download_async(vr_ctx *ctx, void *host_rgba8, void *cuda_stream);
 /* The fragment shader's own output before the blend: float4 per pixel, premultiplied rgb
  * and alpha = 1 - transmittance, (0,0,0,0) where no fragment.  Needs options.write_raw. */
 int vr_get_raw(vr_ctx *ctx, void **dev_rgba_f32);
+/* The float4 output of any frame in flight (options.write_raw; allocated on first use).  Under a sort-last partition a
+ * frame's output IS this partial: vr_render_frame then stores no RGBA8 image (vr_composite* produces it). */
+int vr_get_raw_frame(vr_ctx *ctx, uint32_t frame_index, void **dev_rgba_f32);
 int vr_download_raw(vr_ctx *ctx, float *host_rgba_f32);
 /* The display image as a file: binary PPM (P6, the alpha channel is dropped) or, if `path` ends in
  * ".pam", PAM with all four channels.  Stands where the reference hands the image to ImGui for display
@@ -341,7 +344,7 @@ int vr_partition_order(const uint32_t grid[3], const uint32_t full_dims[3], cons
  * The reference orders its two frames in flight with per-frame fences (src/rendering/main_pass.cpp:55-57,
  * :115-117); across GPUs the same ordering is kept by 32-bit counters in device memory, written and
  * awaited in stream order by one-warp kernels: no host synchronisation and no collective per frame. */
-#define VR_FLAG_COUNT 256
+#define VR_FLAG_COUNT 1024
 /* The context's block of VR_FLAG_COUNT zero-initialised uint32 counters (export with vr_ipc_export(ctx, 2, ..)). */
 int vr_get_flags(vr_ctx *ctx, void **dev_u32);
 /* After everything enqueued so far on the stream: store `value` into the n <= 32 counters `flags[i]`
@@ -350,7 +353,8 @@ int vr_stream_signal(vr_ctx *ctx, void *const *flags, uint32_t n, uint32_t value
 /* Hold the stream until the n <= 256 consecutive LOCAL counters at `flags` have all reached `value`
  * (counters only grow).  After timeout_ms the wait gives up and the next vr_sync fails with VR_ERR_STATE. */
 int vr_stream_wait(vr_ctx *ctx, const void *flags, uint32_t n, uint32_t value, uint32_t timeout_ms, void *cuda_stream);
-/* vr_set_image_target for any frame in flight; vr_ipc_export accepts which = 16 + frame_index for those
+/* vr_ipc_export also accepts which = 32 + frame_index: the float4 output of that frame slot (vr_get_raw_frame).
+ * vr_set_image_target for any frame in flight; vr_ipc_export accepts which = 16 + frame_index for those
  * targets (allocated on first use). */
 int vr_set_image_target_frame(vr_ctx *ctx, uint32_t frame_index, void *dev_rgba8);
 

@@ -96,7 +96,7 @@ def run_checks(vr, mg, rank, world, local):
             sl.render(cam.get_position())
         sl.finish()
         if rank == 0:
-            got = op.download()
+            got = op.download_frame(sl.image_slot())
             d = np.abs(got.astype(int) - want.astype(int))
             if d.max() > 1 or (d > 0).mean() > 0.01:
                 failures.append(f"sort-last/{mode}: max diff {d.max()}, differing {(d > 0).mean():.4f}")
@@ -115,7 +115,7 @@ def run_checks(vr, mg, rank, world, local):
             ref.record()
             want2 = ref.download()
             ref.close()
-            got = op.download()
+            got = op.download_frame(sl.image_slot())
             d = np.abs(got.astype(int) - want2.astype(int))
             if d.max() > 1 or (d > 0).mean() > 0.01:
                 failures.append(f"sort-last/{mode} second view: max diff {d.max()}, differing {(d > 0).mean():.4f}")

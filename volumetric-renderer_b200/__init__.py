@@ -246,9 +246,17 @@ class OffscreenPass:
         self._check(lib.vr_get_image(self._h, C.byref(p), C.byref(pitch)))
         return p.value, pitch.value
 
-    def get_raw(self) -> int:
+    def get_image_frame(self, frame_index: int) -> int:
+        """Device pointer of the RGBA8 target of a frame slot (allocated on first use)."""
+        if frame_index:
+            self.ipc_export(16 + frame_index)   # allocates the slot
+        p, pitch = C.c_void_p(), C.c_size_t()
+        self._check(lib.vr_get_image_frame(self._h, frame_index, C.byref(p), C.byref(pitch)))
+        return p.value
+
+    def get_raw(self, frame_index: int = 0) -> int:
         p = C.c_void_p()
-        self._check(lib.vr_get_raw(self._h, C.byref(p)))
+        self._check(lib.vr_get_raw_frame(self._h, frame_index, C.byref(p)))
         return p.value
 
     def download(self, out: np.ndarray | None = None) -> np.ndarray:

@@ -75,6 +75,7 @@ SIGNATURES = {
     "vr_download": (C.c_int, [_P, _P]),
     "vr_download_async": (C.c_int, [_P, _P, _P]),
     "vr_get_raw": (C.c_int, [_P, C.POINTER(_P)]),
+    "vr_get_raw_frame": (C.c_int, [_P, C.c_uint32, C.POINTER(_P)]),
     "vr_download_raw": (C.c_int, [_P, _P]),
     "vr_write_image": (C.c_int, [_P, C.c_char_p]),
     "vr_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),

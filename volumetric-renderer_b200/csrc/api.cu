@@ -178,8 +178,10 @@ int alloc_target(vr_ctx *c, uint32_t w, uint32_t h)
 {
     if (c->d_image) cudaFree(c->d_image), c->d_image = nullptr;
     if (c->d_raw) cudaFree(c->d_raw), c->d_raw = nullptr;
-    for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
+    for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++) {
         if (c->d_image_slot[k]) cudaFree(c->d_image_slot[k]), c->d_image_slot[k] = nullptr;
+        if (c->d_raw_slot[k]) cudaFree(c->d_raw_slot[k]), c->d_raw_slot[k] = nullptr;
+    }
     c->W = w, c->H = h;
     VR_CUDA(c, cudaMalloc(&c->d_image, (size_t)w * h * sizeof(uchar4)));
     VR_CUDA(c, cudaMemset(c->d_image, 0, (size_t)w * h * sizeof(uchar4)));
@@ -438,8 +440,10 @@ extern "C" int vr_destroy(vr_ctx *c)
     if (c->d_lut_h) cudaFree(c->d_lut_h);
     if (c->d_image) cudaFree(c->d_image);
     if (c->d_raw) cudaFree(c->d_raw);
-    for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
+    for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++) {
         if (c->d_image_slot[k]) cudaFree(c->d_image_slot[k]);
+        if (c->d_raw_slot[k]) cudaFree(c->d_raw_slot[k]);
+    }
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->d_flags) cudaFree(c->d_flags);
     if (c->h_counters) cudaFreeHost(c->h_counters);
@@ -665,6 +669,14 @@ int ensure_slot(vr_ctx *c, uint32_t frame_index)
     if (frame_index == 0 || c->d_image_slot[frame_index]) return VR_OK;
     VR_CUDA(c, cudaMalloc(&c->d_image_slot[frame_index], (size_t)c->W * c->H * sizeof(uchar4)));
     VR_CUDA(c, cudaMemset(c->d_image_slot[frame_index], 0, (size_t)c->W * c->H * sizeof(uchar4)));
+    return VR_OK;
+}
+
+int ensure_raw_slot(vr_ctx *c, uint32_t frame_index)
+{
+    if (frame_index == 0 || c->d_raw_slot[frame_index]) return VR_OK;
+    VR_CUDA(c, cudaMalloc(&c->d_raw_slot[frame_index], (size_t)c->W * c->H * sizeof(float4)));
+    VR_CUDA(c, cudaMemset(c->d_raw_slot[frame_index], 0, (size_t)c->W * c->H * sizeof(float4)));
     return VR_OK;
 }
 
@@ -940,7 +952,14 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
      * target keeps the clear colour outside the tiles the last frame into it marched, so a frame restores only
      * those of them that lie outside its own tiles -- on an orbit a thin frame of pixels instead of the 83 % of the
      * target outside the box (under sort-first: bytes that would cross NVLink into the display rank). */
-    float4 *raw_target = (frame_index == 0 && c->opt.write_raw) ? c->d_raw : nullptr;
+    float4 *raw_target = nullptr;
+    if (c->opt.write_raw) {
+        const int rc = ensure_raw_slot(c, frame_index);
+        if (rc != VR_OK) return rc;
+        raw_target = frame_index == 0 ? c->d_raw : c->d_raw_slot[frame_index];
+    }
+    /* a sort-last rank's frame is its float4 partial; the RGBA8 image comes out of the merge (vr_composite*) */
+    if (c->sort_last && raw_target) target = nullptr;
     vr_ctx::SlotClear &sc = c->slot_clear[frame_index];
     const bool keep = c->tune_dirty_clear && sc.valid && sc.target == (const void *)target && sc.raw == (const void *)raw_target &&
                       sc.W == c->W && sc.H == c->H && sc.pt_rank == c->pt_rank && sc.pt_nranks == c->pt_nranks && sc.pt_px == c->pt_px;
@@ -972,7 +991,7 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     for (int i = 0; i < 4; i++) c->slot_bbox[frame_index][i] = p.bbox[i];
     c->slot_bbox_valid[frame_index] = p.pt_nranks <= 1 && !c->sort_last;
     p.out = target;
-    if (frame_index > 0) p.raw = nullptr; /* the float4 output exists for frame 0 only */
+    p.raw = raw_target;
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
     if (c->bench_fetch_only) {
         if (exact || ess || c->opt.collect_stats || c->sort_last || (pair && p.pair_split != 0x10000))
@@ -1162,6 +1181,17 @@ extern "C" int vr_get_raw(vr_ctx *c, void **dev)
     if (!c || !dev) return VR_ERR_INVALID;
     if (!c->d_raw) return fail(c, VR_ERR_STATE, "vr_get_raw: options.write_raw is off");
     *dev = c->d_raw;
+    return VR_OK;
+}
+
+extern "C" int vr_get_raw_frame(vr_ctx *c, uint32_t frame_index, void **dev)
+{
+    if (!c || !dev || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return VR_ERR_INVALID;
+    if (!c->opt.write_raw || !c->d_raw) return fail(c, VR_ERR_STATE, "vr_get_raw_frame: options.write_raw is off");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    const int rc = ensure_raw_slot(c, frame_index);
+    if (rc != VR_OK) return rc;
+    *dev = frame_index == 0 ? c->d_raw : c->d_raw_slot[frame_index];
     return VR_OK;
 }
 
@@ -1456,7 +1486,17 @@ extern "C" int vr_stream_wait(vr_ctx *c, const void *flags, uint32_t n, uint32_t
 extern "C" int vr_ipc_export(vr_ctx *c, int which, unsigned char handle[64])
 {
     const bool frame_slot = which >= 16 && which < 16 + VR_MAX_FRAMES_IN_FLIGHT;
-    if (!c || !handle || (which != 0 && which != 1 && which != 2 && !frame_slot)) return fail(c, VR_ERR_INVALID, "vr_ipc_export: bad arguments");
+    const bool raw_slot = which >= 32 && which < 32 + VR_MAX_FRAMES_IN_FLIGHT;
+    if (!c || !handle || (which != 0 && which != 1 && which != 2 && !frame_slot && !raw_slot)) return fail(c, VR_ERR_INVALID, "vr_ipc_export: bad arguments");
+    if (raw_slot) {
+        void *rp = nullptr;
+        const int rc = vr_get_raw_frame(c, (uint32_t)(which - 32), &rp);
+        if (rc != VR_OK) return rc;
+        cudaIpcMemHandle_t h;
+        VR_CUDA(c, cudaIpcGetMemHandle(&h, rp));
+        std::memcpy(handle, &h, 64);
+        return VR_OK;
+    }
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
     if (frame_slot) {
         const int rc = ensure_slot(c, (uint32_t)(which - 16));

@@ -517,6 +517,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
         }
         const uint32_t c8 = (uint32_t)(VR_CLEAR_RGB * 255.0f + 0.5f), cw = c8 | (c8 << 8) | (c8 << 16) | 0xff000000u;
         const bool wide = (p.W & 3u) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15u) == 0;
+        const bool rgba = p.out != nullptr; /* sort-last: the float4 partial only */
         /* the spiral blocks' rectangle in pixels (a group of four pixels never straddles a 16-pixel tile column) */
         const int rpx0 = p.rect[0] * VR_TILE, rpx1 = p.rect[2] * VR_TILE, rpy0 = p.rect[1] * (int)p.tile_h, rpy1 = p.rect[3] * (int)p.tile_h;
         /* rows of rw / 4 groups of four pixels, 16 groups side by side per pass */
@@ -528,7 +529,8 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
             if ((int)gx >= rpx0 && (int)gy >= rpy0 && (int)gx < rpx1 && (int)gy < rpy1) continue;
             if (!p.pt_enum && p.pt_nranks > 1 && ((gy / p.pt_px) * p.pt_m + gx / p.pt_px) % p.pt_nranks != p.pt_rank) continue;
             const size_t gp = (size_t)gy * p.W + gx;
-            if (wide) {
+            if (!rgba) {
+            } else if (wide) {
                 *reinterpret_cast<uint4 *>(p.out + gp) = make_uint4(cw, cw, cw, cw);
             } else {
                 for (uint32_t k = 0; k < 4u && gx + k < p.W; k++) p.out[gp + k] = make_uchar4(c8, c8, c8, 255);
@@ -559,7 +561,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
         /* nothing to march in this tile: clear colour only (offscreen_pass.cpp:170-173) */
         if (valid) {
             const unsigned char c = (unsigned char)(VR_CLEAR_RGB * 255.0f + 0.5f);
-            p.out[pix] = make_uchar4(c, c, c, 255);
+            if (p.out) p.out[pix] = make_uchar4(c, c, c, 255);
             if (p.raw) p.raw[pix] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         return;
@@ -744,7 +746,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
             o = make_uchar4(c, c, c, 255);
             rawv = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        p.out[pix] = o;
+        if (p.out) p.out[pix] = o;
         if (p.raw) p.raw[pix] = rawv;
     }
 

@@ -110,6 +110,7 @@ struct vr_ctx {
     uchar4 *d_image = nullptr;                                       /* frame 0 */
     uchar4 *d_image_slot[VR_MAX_FRAMES_IN_FLIGHT] = {nullptr, nullptr, nullptr, nullptr}; /* frames 1.. (lazily) */
     float4 *d_raw = nullptr;
+    float4 *d_raw_slot[VR_MAX_FRAMES_IN_FLIGHT] = {nullptr, nullptr, nullptr, nullptr}; /* float4 output of frames 1.. (lazily) */
     uchar4 *ext_image = nullptr; /* vr_set_image_target: frame 0 is written there instead (peer memory) */
     uchar4 *ext_image_slot[VR_MAX_FRAMES_IN_FLIGHT] = {nullptr, nullptr, nullptr, nullptr}; /* same for frames 1.. */
     uint32_t *d_flags = nullptr; /* VR_FLAG_COUNT counters for stream-ordered hand-off between ranks (sync.cu) */

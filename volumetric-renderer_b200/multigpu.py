@@ -84,12 +84,13 @@ def _gather_handles(handle: bytes, world: int, group=None):
     return out
 
 
-# flag block layout (uint32 index) used by the partitions below; world <= 31
-_F_ARRIVE = 0      # display rank: [slot * 32 + r] = frames rank r has stored into image slot `slot`
-_F_READY = 0       # sort-last, every rank: [r] = frames whose partial rank r has finished
-_F_READ_DONE = 32  # sort-last, every rank: [r] = frames rank r has finished merging (my partial is free again)
-_F_RANGE_DONE = 64 # sort-last, display rank: [r] = frames whose pixel range r is merged into the image
-_F_CONSUMED = 128  # every rank: [slot] = frames presented out of image slot `slot` (the slot is free again)
+# flag block layout (uint32 index, VR_FLAG_COUNT = 1024) used by the partitions below; world <= 31, slots <= 4
+_F_ARRIVE = 0        # sort-first, display rank: [slot * 32 + r] = frames rank r has stored into image slot `slot`
+_F_CONSUMED = 128    # sort-first, every rank: [slot] = frames presented out of image slot `slot` (the slot is free again)
+_L_READY = 256       # sort-last, every rank: [slot * 32 + r] = frames whose partial (slot) rank r has finished marching
+_L_READ_DONE = 384   # sort-last, every rank: [slot * 32 + r] = frames rank r has finished merging (my partial slot is free again)
+_L_RANGE_DONE = 512  # sort-last, display rank: [slot * 32 + r] = frames whose pixel range r is merged into image slot `slot`
+_L_CONSUMED = 640    # sort-last, every rank: [slot] = frames presented out of image slot `slot`
 
 
 class _PeerFlags:
@@ -172,6 +173,11 @@ class SortFirst:
             op.stream_signal([f.ptr(r, _F_CONSUMED + s) for r in range(self.world)], k + 1, ps)
         return s
 
+    def image_slot(self, k: int | None = None) -> int:
+        """Image slot of the display rank that holds frame k (default: the frame enqueued last)."""
+        k = self._k - 1 if k is None else k
+        return k % self.slots if self.world > 1 else 0
+
     def finish(self):
         """Every enqueued frame is complete in the display rank's image slots when this returns."""
         import torch.distributed as dist
@@ -191,10 +197,15 @@ class SortFirst:
 
 
 class SortLast:
-    """Sort-last sub-box partition with view-ordered direct-send compositing (BASELINE.json config 5)."""
+    """Sort-last sub-box partition with view-ordered direct-send compositing (BASELINE.json config 5).
+
+    mode "p2p": frames are pipelined over `slots` partial buffers and display-image slots, with the march (K1) and the
+    merge (K2) of a rank on two streams: a rank marches frame k + 1 while frame k is still being merged, and may run
+    up to `slots` - 1 frames ahead of the slowest rank -- the front-most sub-box of a view has up to 1.4x the samples
+    of the rear-most (perspective), and which rank that is changes along an orbit (tools/exp_sl_balance.py)."""
 
     def __init__(self, op, rank: int, world: int, full_dims, grid=None, display_rank: int = 0, mode: str = "p2p",
-                 group=None, on_frame=None):
+                 group=None, on_frame=None, slots: int = 2):
         import torch.distributed as dist
         from . import partition_box
         self.op, self.rank, self.world, self.display, self.mode, self.group = op, rank, world, display_rank, mode, group
@@ -208,17 +219,22 @@ class SortLast:
         w, h = op.size
         self.npix = w * h
         self.ranges = pixel_ranges(self.npix, world)
+        self.slots = slots if (world > 1 and mode == "p2p") else 1
+        assert 1 <= self.slots <= 4 and world <= 31
         self._peers_raw, self._peer_img = None, None
-        self._flags, self._present, self._k, self.on_frame = None, None, 0, on_frame
-        assert world <= 31
+        self._flags, self._present, self._merge, self._k, self.on_frame = None, None, None, 0, on_frame
         if world > 1 and mode == "p2p":
-            raws = _gather_handles(op.ipc_export(1), world, group)
-            imgs = _gather_handles(op.ipc_export(0), world, group)
-            self._peers_raw = [op.get_raw() if r == rank else op.ipc_open(raws[r]) for r in range(world)]
-            self._peer_img = None if rank == display_rank else op.ipc_open(imgs[display_rank])
+            import torch
+            self._peers_raw, self._peer_img = [], []
+            for s in range(self.slots):
+                raws = _gather_handles(op.ipc_export(32 + s), world, group)
+                imgs = _gather_handles(op.ipc_export(16 + s) if rank == display_rank else b"", world, group)
+                self._peers_raw.append([op.get_raw(s) if r == rank else op.ipc_open(raws[r]) for r in range(world)])
+                self._peer_img.append(None if rank == display_rank else op.ipc_open(imgs[display_rank]))
+            self._own_img = [op.get_image_frame(s) for s in range(self.slots)] if rank == display_rank else None
             self._flags = _PeerFlags(op, rank, world, group)
+            self._merge = torch.cuda.Stream()
             if rank == display_rank:
-                import torch
                 self._present = torch.cuda.Stream(priority=_present_priority())
             dist.barrier(group)
 
@@ -234,9 +250,14 @@ class SortLast:
         self.op.set_density_range(mn, mx)
         return mn, mx
 
+    def image_slot(self, k: int | None = None) -> int:
+        """Image slot of the display rank that holds frame k (default: the frame enqueued last)."""
+        k = self._k - 1 if k is None else k
+        return k % self.slots
+
     def render(self, camera_position, stream: int | None = None):
         """March this rank's samples, then merge.  The frame is complete in the display rank's image
-        after finish()."""
+        (slot image_slot()) after finish()."""
         import torch
         import torch.distributed as dist
         from . import partition_order
@@ -250,32 +271,38 @@ class SortLast:
             op.composite([op.get_raw()], 0, self.npix, stream, rects=rects)
             if self.on_frame:
                 self.on_frame(0, stream)
+            self._k += 1
             return
         if self.mode == "p2p":
-            # Stream-ordered hand-off (include/vr.h: vr_stream_signal / vr_stream_wait): no host
-            # synchronisation and no collective per frame.  Frame k (counters hold k + 1 when done):
-            f, k, disp = self._flags, self._k, self.display
+            # Stream-ordered hand-off (include/vr.h: vr_stream_signal / vr_stream_wait): no host synchronisation and
+            # no collective per frame.  Frame k lives in partial slot / image slot s = k % slots; counters hold k + 1
+            # when frame k has passed the stage.
+            f, k, disp, S = self._flags, self._k, self.display, self.slots
+            s = k % S
             self._k += 1
-            if k >= 1:
-                op.stream_wait(f.ptr(rank, _F_READ_DONE), world, k, stream)   # everyone has merged my partial of frame k-1
-                if rank == disp:
-                    op.stream_wait(f.ptr(rank, _F_CONSUMED), 1, k, stream)    # K1 also stores into the image being presented
-            op.record(stream)
-            op.stream_signal([f.ptr(r, _F_READY + rank) for r in range(world)], k + 1, stream)
-            op.stream_wait(f.ptr(rank, _F_READY), world, k + 1, stream)        # every partial of frame k is complete
-            if k >= 1 and rank != disp:
-                op.stream_wait(f.ptr(rank, _F_CONSUMED), 1, k, stream)        # frame k-1 has left the display image
+            ms = self._merge.cuda_stream
+            # -- march stream: my partial slot must have been merged by everyone (frame k - S), then K1 --
+            if k >= S:
+                op.stream_wait(f.ptr(rank, _L_READ_DONE + s * 32), world, k - S + 1, stream)
+            op.record(stream, s)
+            op.stream_signal([f.ptr(r, _L_READY + s * 32 + rank) for r in range(world)], k + 1, stream)
+            # -- merge stream: every partial of frame k complete, image slot s presented (frame k - S), then K2 --
+            op.stream_wait(f.ptr(rank, _L_READY + s * 32), world, k + 1, ms)
+            if k >= S:
+                op.stream_wait(f.ptr(rank, _L_CONSUMED + s), 1, k - S + 1, ms)
             if e > b:
-                op.composite([self._peers_raw[r] for r in order], b, e, stream, out_ptr=self._peer_img, rects=rects)
-            op.stream_signal([f.ptr(r, _F_READ_DONE + rank) for r in range(world)] + [f.ptr(disp, _F_RANGE_DONE + rank)],
-                             k + 1, stream)
+                op.composite([self._peers_raw[s][r] for r in order], b, e, ms, out_ptr=self._peer_img[s] if rank != disp else self._own_img[s],
+                             rects=rects)
+            op.stream_signal([f.ptr(r, _L_READ_DONE + s * 32 + rank) for r in range(world)] + [f.ptr(disp, _L_RANGE_DONE + s * 32 + rank)],
+                             k + 1, ms)
             if rank == disp:
                 ps = self._present.cuda_stream
-                op.stream_wait(f.ptr(rank, _F_RANGE_DONE), world, k + 1, ps)  # the frame is complete in the image
+                op.stream_wait(f.ptr(rank, _L_RANGE_DONE + s * 32), world, k + 1, ps)  # the frame is complete in image slot s
                 if self.on_frame:
-                    self.on_frame(0, ps)
-                op.stream_signal([f.ptr(r, _F_CONSUMED) for r in range(world)], k + 1, ps)
+                    self.on_frame(s, ps)
+                op.stream_signal([f.ptr(r, _L_CONSUMED + s) for r in range(world)], k + 1, ps)
             return
+        self._k += 1
         op.record(stream)
         op.sync()
         dist.barrier(self.group)  # every partial is complete before anyone reads it
@@ -311,11 +338,13 @@ class SortLast:
     def close(self):
         if self._peers_raw:
             self.op.sync()
-            for r, p in enumerate(self._peers_raw):
-                if r != self.rank:
+            for slot in self._peers_raw:
+                for r, p in enumerate(slot):
+                    if r != self.rank:
+                        self.op.ipc_close(p)
+            for p in self._peer_img:
+                if p:
                     self.op.ipc_close(p)
-            if self._peer_img:
-                self.op.ipc_close(self._peer_img)
             self._peers_raw, self._peer_img = None, None
         if self._flags:
             self._flags.close()
