@@ -137,6 +137,10 @@ int vr_download_frame_async(vr_ctx *ctx, uint32_t frame_index, void *host_rgba8,
  * as long as the caller leaves the buffer alone between calls; the context remembers the last 8 host buffers
  * (address + frame size).  Frames of a partitioned context are always delivered in full.  bytes_copied may be NULL. */
 int vr_download_frame_dirty_async(vr_ctx *ctx, uint32_t frame_index, void *host_rgba8, void *cuda_stream, size_t *bytes_copied);
+/* The dirty-rectangle path remembers host buffers by ADDRESS (and frame size).  A buffer that is freed and another
+ * one allocated at the same address, or written by anyone else, must be forgotten first (NULL: forget all); full
+ * downloads into a known buffer update what is remembered about it. */
+int vr_forget_host_buffer(vr_ctx *ctx, const void *host_rgba8);
 int vr_sync(vr_ctx *ctx);
 
 /* The uniform block the reference fills by pulling the camera inside record()

@@ -668,3 +668,70 @@ def test_dirty_clear_leaves_the_frames_unchanged(vr, port, monkeypatch):
     assert blocks[5] == 0                             # far -> near: the new tiles cover the old ones
     assert 0 < blocks[11] < full_blocks[11]           # near -> far restores the rim between the two boxes only
     assert blocks[-3] > 0 and blocks[-2] > 0 and blocks[-1] == 0   # new targets after the resize
+
+
+@pytest.mark.parametrize("sampler", ["exact", "hw"])
+def test_non_finite_voxels_are_not_skipped(vr, port, sampler):
+    """a NaN density samples LUT texel 0, +-Inf the end texels (volume.frag:42-43 through the CLAMP_TO_EDGE
+    sampler).  fminf / fmaxf drop NaNs, so a cell of NaN voxels used to get an empty range and was skipped even when
+    texel 0 is visible: frames with and without empty-space skipping must agree."""
+    rng = np.random.default_rng(5)
+    vol = np.zeros((32, 32, 32), np.float32)
+    vol[4:12, 4:12, 4:12] = np.nan
+    vol[20:28, 6:10, 18:30] = np.inf
+    vol[14:18, 20:30, 2:9] = -np.inf
+    vol[22, 22, 22] = 0.7
+    lut = tf(port, "B").copy()
+    lut[0] = 0x80FF4020      # texel 0 visible: alpha 0x80
+    lut[255] = 0x60102030
+    lut[1:200] &= 0x00FFFFFF  # everything between is transparent
+    frames = []
+    for ess in (0, 1):
+        op = vr.OffscreenPass(W, H)
+        try:
+            op.set_options(sampler=vr.SAMPLER_EXACT if sampler == "exact" else vr.SAMPLER_HW, empty_skip=ess, write_raw=1)
+            op.volume_dataset_changed(vr.Dataset(vol, 0.0, 1.0))
+            op.transfer_function_changed(lut)
+            cam, _ = twin_cameras(vr, port, [(-120, 80)])
+            op.set_camera(cam)
+            op.record()
+            frames.append((op.download(), op.download_raw()))
+            if ess:
+                assert op.last_frame_info().empty_skip_active == 1
+        finally:
+            op.close()
+    assert frames[0][0].astype(int).max() > 40, "the non-finite regions must be visible at all"
+    if sampler == "exact":
+        assert np.array_equal(frames[0][1].view(np.uint32), frames[1][1].view(np.uint32))
+    assert np.abs(frames[0][0].astype(int) - frames[1][0].astype(int)).max() <= (0 if sampler == "exact" else 1)
+
+
+def test_full_downloads_keep_the_dirty_rectangle_bookkeeping_right(vr, port):
+    """a full download into a buffer the dirty path knows must update what is remembered about it, and a
+    buffer can be forgotten (an allocator may hand the same address out again with other contents)."""
+    import torch
+    vol = small_volume(port, 1, np.uint16, 32)
+    op = vr.OffscreenPass(320, 200)
+    try:
+        op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+        op.transfer_function_changed(tf(port, "B"))
+        host = torch.zeros((200, 320, 4), dtype=torch.uint8, pin_memory=True)
+        s = torch.cuda.Stream()
+
+        def frame(zoom, how):
+            cam, _ = twin_cameras(vr, port, [(30, 10)], zoom)
+            op.set_camera(cam)
+            op.record(s.cuda_stream, 0)
+            n = how(host.data_ptr(), s.cuda_stream, 0)
+            s.synchronize()
+            assert np.array_equal(host.numpy(), op.download_frame(0))
+            return n
+
+        frame(0.0, op.download_dirty_async)                 # first delivery: full
+        frame(2.3, op.download_async)                       # a full download of a frame that fills the target ...
+        assert frame(-3.0, op.download_dirty_async) > 0.5 * 320 * 200 * 4   # ... so the next dirty copy must cover it
+        host.fill_(7)                                       # someone else scribbles over the buffer
+        op.forget_host_buffer(host.data_ptr())
+        assert frame(-3.0, op.download_dirty_async) == 320 * 200 * 4
+    finally:
+        op.close()

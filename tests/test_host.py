@@ -148,6 +148,20 @@ def test_nrrd_reader_encodings(vr, ref, tmp_path, encoding, endian, detached):
     assert np.array_equal(got, arr) and np.array_equal(got.astype(np.float32), want)
 
 
+@pytest.mark.parametrize("encoding", ["raw", "ascii", "hex"])
+@pytest.mark.parametrize("tname", ["uchar", "double"])
+def test_nrrd_header_claiming_a_huge_volume_is_an_error_not_a_crash(vr, tmp_path, encoding, tname):
+    """sizes come from the header alone.  A tiny file claiming 65536^3 voxels (or sizes whose product wraps
+    64 bits) must fail with a status -- the reference reports 'Failed to read file' -- not allocate or terminate."""
+    for sizes in ("65536 65536 65536", "4294967295 4294967295 4294967295", "2048 2048 2048"):
+        p = tmp_path / f"huge_{encoding}_{tname}_{sizes.split()[0]}.nrrd"
+        open(p, "wb").write(f"NRRD0004\ntype: {tname}\ndimension: 3\nsizes: {sizes}\nencoding: {encoding}\nendian: little\n\n".encode()
+                            + b"0 1 2 3 4 5 6 7\n")
+        with pytest.raises(vr.VrError) as e:
+            vr.read_nrrd(str(p))
+        assert "Failed to read file" in str(e.value)
+
+
 def test_nrrd_reader_rejects_what_the_reference_rejects(vr, ref, tmp_path):
     p = tmp_path / "two_d.nrrd"
     open(p, "wb").write(b"NRRD0004\ntype: uchar\ndimension: 2\nsizes: 4 4\nencoding: raw\n\n" + bytes(16))

@@ -66,4 +66,25 @@ for N in (2, 4, 8):
           f"  sum of rank means / one GPU = {t.mean(axis=1).sum() / t1.mean():.3f}")
     out[f"n{N}"] = {"grid": list(grid), "lock_step_ms": float(lock), "pipelined_ms": float(pipe), "ideal_ms": float(ideal),
                     "rank_means": [float(x) for x in t.mean(axis=1)]}
+# two bricks per rank, a brick and its point mirror (the mirror of a near brick is a far brick: the perspective
+# imbalance of a view cancels inside every rank)
+for N in (2, 4, 8):
+    grid = mg.grid_for_world(2 * N)
+    nb = 2 * N
+    tb = np.zeros((nb, 36))
+    for b in range(nb):
+        org, dims = vr.partition_box(grid, (n, n, n), b)
+        op = vr.OffscreenPass(W, H)
+        op.transfer_function_changed(lut)
+        op.set_options(sampler=vr.SAMPLER_HW, empty_skip=1, early_term=1, early_term_eps=1.0 / 1024.0, write_raw=1)
+        op.set_partition_sort_last((n, n, n), org, dims)
+        op.synth_subvolume(vr.SYNTH_FBM, 0x5EED0004, vr.U16)
+        op.set_density_range(gmn, gmx)
+        tb[b] = time_frames(op)
+        op.close()
+    t = np.array([tb[r] + tb[nb - 1 - r] for r in range(N)])
+    lock, pipe, ideal = t.max(axis=0).mean(), t.mean(axis=1).max(), t1.mean() / N
+    print(f"N={N} mirror pairs of grid {grid}: ideal {ideal:.4f}  lock-step bound {lock:.4f} (eff {ideal / lock:.3f})  pipelined bound {pipe:.4f} (eff {ideal / pipe:.3f})"
+          f"  sum of rank means / one GPU = {t.mean(axis=1).sum() / t1.mean():.3f}")
+    out[f"n{N}_pairs"] = {"grid": list(grid), "lock_step_ms": float(lock), "pipelined_ms": float(pipe), "ideal_ms": float(ideal)}
 print(json.dumps(out))

@@ -298,6 +298,10 @@ class OffscreenPass:
         self._check(lib.vr_download_frame_dirty_async(self._h, frame_index, host_ptr, stream, C.byref(n)))
         return n.value
 
+    def forget_host_buffer(self, host_ptr: int | None = None):
+        """vr_forget_host_buffer: the dirty-rectangle path must not assume anything about that buffer (None: any)."""
+        self._check(lib.vr_forget_host_buffer(self._h, host_ptr))
+
     def download_raw(self) -> np.ndarray:
         w, h = self.size
         out = np.empty((h, w, 4), np.float32)

@@ -49,6 +49,7 @@ SIGNATURES = {
     "vr_get_image_frame": (C.c_int, [_P, C.c_uint32, C.POINTER(_P), C.POINTER(C.c_size_t)]),
     "vr_download_frame_async": (C.c_int, [_P, C.c_uint32, _P, _P]),
     "vr_download_frame_dirty_async": (C.c_int, [_P, C.c_uint32, _P, _P, C.POINTER(C.c_size_t)]),
+    "vr_forget_host_buffer": (C.c_int, [_P, _P]),
     "vr_sync": (C.c_int, [_P]),
     "vr_set_camera": (C.c_int, [_P, _P, _P, _P]),
     "vr_resize": (C.c_int, [_P, C.c_uint32, C.c_uint32]),

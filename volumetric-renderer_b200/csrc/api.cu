@@ -989,7 +989,8 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     /* outside p.bbox every pixel of this frame is the clear colour (screen_bbox is conservative); with a
      * partition the frame is only partly this context's */
     for (int i = 0; i < 4; i++) c->slot_bbox[frame_index][i] = p.bbox[i];
-    c->slot_bbox_valid[frame_index] = p.pt_nranks <= 1 && !c->sort_last;
+    c->slot_bbox_valid[frame_index] = p.pt_nranks <= 1 && !c->sort_last &&
+                                      target == (frame_index == 0 ? c->d_image : c->d_image_slot[frame_index]); /* not a redirected target */
     p.out = target;
     p.raw = raw_target;
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
@@ -1077,6 +1078,28 @@ extern "C" int vr_present_frame(vr_ctx *c, uint32_t frame_index, void *dst_dev_r
     return VR_OK;
 }
 
+/* A full delivery into a host buffer the dirty-rectangle path knows: the buffer now holds exactly that frame. */
+static void note_full_delivery(vr_ctx *c, uint32_t frame_index, void *host)
+{
+    for (auto &t : c->host_targets)
+        if (t.ptr == host) {
+            if (t.W == c->W && t.H == c->H && c->slot_bbox_valid[frame_index]) {
+                for (int i = 0; i < 4; i++) t.rect[i] = c->slot_bbox[frame_index][i];
+                t.stamp = ++c->host_target_clock;
+            } else {
+                t.ptr = nullptr;
+            }
+        }
+}
+
+extern "C" int vr_forget_host_buffer(vr_ctx *c, const void *host)
+{
+    if (!c) return VR_ERR_INVALID;
+    for (auto &t : c->host_targets)
+        if (!host || t.ptr == host) t.ptr = nullptr;
+    return VR_OK;
+}
+
 extern "C" int vr_download_frame_async(vr_ctx *c, uint32_t frame_index, void *host, void *cuda_stream)
 {
     if (!c || !host || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return fail(c, VR_ERR_INVALID, "vr_download_frame_async: bad arguments");
@@ -1085,6 +1108,7 @@ extern "C" int vr_download_frame_async(vr_ctx *c, uint32_t frame_index, void *ho
     VR_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->last_stream;
     VR_CUDA(c, cudaMemcpyAsync(host, src, (size_t)c->W * c->H * sizeof(uchar4), cudaMemcpyDeviceToHost, s));
+    note_full_delivery(c, frame_index, host);
     return VR_OK;
 }
 
@@ -1142,6 +1166,7 @@ extern "C" int vr_download_async(vr_ctx *c, void *host, void *cuda_stream)
     VR_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->last_stream;
     VR_CUDA(c, cudaMemcpyAsync(host, c->d_image, (size_t)c->W * c->H * sizeof(uchar4), cudaMemcpyDeviceToHost, s));
+    note_full_delivery(c, 0, host);
     return VR_OK;
 }
 

@@ -19,6 +19,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <new>
+#include <stdexcept>
 #include <sstream>
 
 namespace
@@ -214,7 +216,23 @@ void store_as(uint8_t *dst, size_t i, double v, long long iv, unsigned long long
 }
 }  // namespace
 
+static int nrrd_read_impl(const char *path, VrNrrd &out, std::string &err, VrNrrdPayload *payload);
+
+/* no exception crosses the ABI: the extern "C" loaders (api.cu) call only this */
 int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err, VrNrrdPayload *payload)
+{
+    try {
+        return nrrd_read_impl(path, out, err, payload);
+    } catch (const std::bad_alloc &) {
+        err = "Failed to read file: out of memory";
+        return VR_ERR_NOMEM;
+    } catch (const std::exception &e) {
+        err = std::string("Failed to read file: ") + e.what();
+        return VR_ERR_FORMAT;
+    }
+}
+
+static int nrrd_read_impl(const char *path, VrNrrd &out, std::string &err, VrNrrdPayload *payload)
 {
     std::ifstream f(path, std::ios::binary);
     if (!f) {
@@ -382,8 +400,15 @@ int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err, VrNrrdPayload 
             (i < axis_maxs.size() && lower(axis_maxs[i]) != "nan") || (i < units.size() && !units[i].empty()))
             return bad("axis with a space direction and a spacing, axis min / max or units");
     }
-    const size_t n = (size_t)sizes[0] * sizes[1] * sizes[2];
     const size_t esz = scalar_size(type);
+    /* sizes come from the header alone: refuse what cannot be a volume before anything is allocated from them
+     * (each may be up to 2^32-1; the product must not wrap, and the reference could not hold it either) */
+    unsigned __int128 n128 = (unsigned __int128)sizes[0] * (unsigned __int128)sizes[1] * (unsigned __int128)sizes[2];
+    if (n128 == 0 || n128 * esz > ((unsigned __int128)1 << 46)) {
+        err = "Failed to read file: sizes out of range";
+        return VR_ERR_FORMAT;
+    }
+    const size_t n = (size_t)n128;
     const bool enc_ascii = encoding == "ascii" || encoding == "text" || encoding == "txt";
     if (encoding != "raw" && encoding != "hex" && !enc_ascii) return bad("unsupported encoding " + encoding);
     if (esz > 1 && !enc_ascii && endian.empty()) return bad("endian required");
@@ -430,6 +455,18 @@ int vr_nrrd_read(const char *path, VrNrrd &out, std::string &err, VrNrrdPayload 
         return VR_OK;
     }
 
+    {
+        /* raw and hex payloads cannot be shorter than the data they claim; an ascii value takes at least two bytes */
+        const std::streamoff here = in->tellg();
+        in->seekg(0, std::ios::end);
+        const std::streamoff end = in->tellg();
+        in->seekg(here, std::ios::beg);
+        const unsigned __int128 need = encoding == "raw" ? (unsigned __int128)n * esz : (enc_ascii ? (unsigned __int128)n * 2 - 1 : (unsigned __int128)n * esz * 2);
+        if (here < 0 || end < here || (unsigned __int128)(end - here) < need) {
+            err = "Failed to read file: truncated data";
+            return VR_ERR_IO;
+        }
+    }
     std::vector<uint8_t> rawbytes(n * esz);
     if (encoding == "raw") {
         if (byte_skip == -1) {

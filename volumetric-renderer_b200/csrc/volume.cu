@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(64) k_cell_ranges(const void *__restrict__ v, 
     const int x0 = cx * cell - 1, y0 = cy * cell - 1, z0 = cz * cell - 1;
     const int w = cell + 2;
     float mn = CUDART_INF_F, mx = -CUDART_INF_F;
+    bool bad = false;
     for (int row = threadIdx.x; row < w * w; row += blockDim.x) {
         const int y = y0 + row % w, z = z0 + row / w;
         if (y < 0 || y >= ny || z < 0 || z >= nz) {
@@ -103,8 +104,12 @@ __global__ void __launch_bounds__(64) k_cell_ranges(const void *__restrict__ v, 
             const int x = x0 + k;
             const float f = (x < 0 || x >= nx) ? 0.0f : ld_any(v, dtype, base + x);
             mn = fminf(mn, f), mx = fmaxf(mx, f);
+            /* fminf / fmaxf drop a NaN; a NaN density samples LUT texel 0 and +-Inf the end texels (march.cu), so a
+             * cell holding any non-finite voxel gets the widest range: it is empty only if the whole LUT is */
+            if (!(fabsf(f) <= 3.402823466e38f)) bad = true;
         }
     }
+    if (bad) mn = -CUDART_INF_F, mx = CUDART_INF_F;
     block_minmax(mn, mx, ranges + c);
 }
 
