@@ -342,6 +342,38 @@ int vr_partition_box(const uint32_t grid[3], const uint32_t full_dims[3], uint32
 int vr_partition_order(const uint32_t grid[3], const uint32_t full_dims[3], const float camera_position[3],
                        uint32_t *out);
 
+/* ---- one process driving several GPUs (the C++ multi-GPU host; csrc/group.cu) ------------------------------
+ * The reference constructs one pass (src/rendering/vulkan_context.cpp:51) and records it once per frame
+ * (src/rendering/main_pass.cpp:91); a group stands in the same place with one context per device.  Mutators apply
+ * to every rank; vr_group_render enqueues one frame on all devices and returns (frames are handed between the
+ * devices by CUDA events: no host synchronisation per frame, `slots` frames in flight); the finished frame is in the
+ * display rank's (rank 0) image.  devs may name a device more than once (logical ranks on one GPU: how the
+ * single-GPU tests run it).  vr_group_context lends a rank's context for per-rank calls (replicas: its camera). */
+typedef struct vr_group vr_group;
+typedef enum vr_partition {
+    VR_PARTITION_REPLICAS = 0,   /* independent frames: every rank renders its own camera */
+    VR_PARTITION_SORT_FIRST = 1, /* image tiles dealt to the ranks, volume replicated (BASELINE.json config 4) */
+    VR_PARTITION_SORT_LAST = 2   /* one sub-box per rank, view-ordered merge of the partials (config 5) */
+} vr_partition;
+int vr_create_group(uint32_t ndev, const int *devs, int partition, uint32_t width, uint32_t height, uint32_t slots, vr_group **out);
+int vr_group_destroy(vr_group *group);
+const char *vr_group_last_error(const vr_group *group); /* NULL: of a failed vr_create_group */
+uint32_t vr_group_size(const vr_group *group);
+vr_ctx *vr_group_context(vr_group *group, uint32_t rank);
+int vr_group_set_camera(vr_group *group, const float view[16], const float proj[16], const float camera_position[3]);
+int vr_group_set_transfer_function(vr_group *group, const uint32_t *rgba8_srgb, uint32_t n);
+int vr_group_set_slicing(vr_group *group, const float min_slice[3], const float max_slice[3]);
+int vr_group_set_options(vr_group *group, const vr_options *options);
+/* volume_dataset_changed for the group: replicated (replicas, sort-first) or cut into one sub-box per rank plus a
+ * ghost voxel towards each neighbour (sort-last; min/max NULL: measured per rank on the device and reduced). */
+int vr_group_set_volume(vr_group *group, const void *data, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
+                        const float *min_density, const float *max_density);
+int vr_group_synth_volume(vr_group *group, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz);
+int vr_group_render(vr_group *group);
+int vr_group_sync(vr_group *group);
+/* The frame recorded last, complete (waits for it).  rank: replicas only (else the display rank's image). */
+int vr_group_download(vr_group *group, uint32_t rank, void *host_rgba8);
+
 /* ---- measurement ----------------------------------------------------------------------- */
 
 /* ---- stream-ordered frame hand-off between ranks (one process per GPU) --------------------

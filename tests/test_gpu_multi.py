@@ -84,6 +84,79 @@ def test_sort_first_moving_camera_restores_the_clear_colour(vr, port):
             op.close()
 
 
+def _group_devices(n):
+    """n ranks: on the visible GPUs when there are enough, else logical ranks on device 0 (events order them)."""
+    import torch
+    have = torch.cuda.device_count()
+    return list(range(n)) if have >= n else [0] * n
+
+
+@pytest.mark.parametrize("nranks", [2, 3])
+@pytest.mark.parametrize("partition", ["sort_first", "sort_last"])
+def test_group_renders_the_single_gpu_frames(vr, port, partition, nranks):
+    """vr_create_group (include/vr.h, csrc/group.cu; SURVEY 8b last row): ONE process records a frame on N ranks the way
+    the application records its one pass (src/rendering/main_pass.cpp:91).  Frames in flight, moving camera; sort-first
+    must reproduce the single-GPU frame bit for bit, sort-last within 1/255 on < 1 % of the pixels."""
+    W, H, n = 328, 200, 48
+    lut = tf(port, "B")
+    single = vr.OffscreenPass(W, H)
+    single.synth_volume(vr.SYNTH_FBM, 0x5EED0002, vr.U16, n)
+    single.transfer_function_changed(lut)
+    vol = single.download_volume()
+    g = vr.PassGroup(_group_devices(nranks), vr.PARTITION_SORT_FIRST if partition == "sort_first" else vr.PARTITION_SORT_LAST, W, H, slots=2)
+    try:
+        assert len(g) == nranks
+        g.transfer_function_changed(lut)
+        if partition == "sort_first":
+            g.synth_volume(vr.SYNTH_FBM, 0x5EED0002, vr.U16, n)
+        else:
+            g.volume_dataset_changed(vr.Dataset(vol))      # cut into sub-boxes + ghosts on the host, global range reduced
+        cams = []
+        for j, z in enumerate([0.0, 0.0, -3.0, 1.5, 0.0, 2.0, -1.0]):
+            cam = vr.Camera().rotate((50.0 * j - 120.0, 80.0 - 35.0 * j))
+            if z:
+                cam.zoom(z)
+            cams.append(cam)
+        for j, cam in enumerate(cams):                      # enqueue everything, no host synchronisation in between
+            g.set_camera(cam)
+            g.record()
+            if j in (2, 4, 6):
+                got = g.download()
+                single.set_camera(cam)
+                single.record()
+                want = single.download()
+                d = np.abs(got.astype(int) - want.astype(int))
+                if partition == "sort_first":
+                    assert d.max() == 0, f"frame {j}: {np.count_nonzero(d.max(axis=-1))} pixels differ"
+                else:
+                    assert d.max() <= 1 and (d > 0).mean() < 0.01, (j, d.max(), (d > 0).mean())
+    finally:
+        g.close()
+        single.close()
+
+
+def test_group_replicas_render_their_own_cameras(vr, port):
+    W, H = 160, 120
+    g = vr.PassGroup(_group_devices(2), vr.PARTITION_REPLICAS, W, H)
+    single = vr.OffscreenPass(W, H)
+    try:
+        lut = tf(port, "B")
+        for x in (g, single):
+            x.synth_volume(vr.SYNTH_FBM, 0x5EED0002, vr.U16, 32)
+            x.transfer_function_changed(lut)
+        cams = [vr.Camera().rotate((40.0, 10.0)), vr.Camera().rotate((-200.0, 60.0))]
+        for r, cam in enumerate(cams):
+            g.set_rank_camera(r, cam)
+        g.record()
+        for r, cam in enumerate(cams):
+            single.set_camera(cam)
+            single.record()
+            assert np.array_equal(g.download(r), single.download())
+    finally:
+        g.close()
+        single.close()
+
+
 def test_stream_flags_signal_wait_and_time_out(vr):
     """vr_stream_signal stores into local or foreign counters in stream order; vr_stream_wait holds a stream
     until its counters reach the value; a wait nobody answers gives up and makes the next vr_sync fail

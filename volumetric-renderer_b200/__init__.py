@@ -22,7 +22,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _lib
-from ._lib import (F32, U8, U16, LAYOUT_ARRAY3D, LAYOUT_AUTO, LAYOUT_PAIRED, SAMPLER_EXACT, SAMPLER_HW, SYNTH_BLOBS, SYNTH_BLOBS_FBM,
+from ._lib import (F32, U8, U16, LAYOUT_ARRAY3D, LAYOUT_AUTO, LAYOUT_PAIRED, PARTITION_REPLICAS, PARTITION_SORT_FIRST, PARTITION_SORT_LAST, SAMPLER_EXACT, SAMPLER_HW, SYNTH_BLOBS, SYNTH_BLOBS_FBM,
                    SYNTH_FBM, SYNTH_MARSCHNER_LOBB, FrameInfo, Options, Stats)
 
 lib = _lib.load()
@@ -391,6 +391,85 @@ class OffscreenPass:
 
     def stream_wait(self, flags_ptr: int, n: int, value: int, stream: int | None = None, timeout_ms: int = 10000):
         self._check(lib.vr_stream_wait(self._h, flags_ptr, n, value & 0xFFFFFFFF, timeout_ms, stream))
+
+
+class PassGroup:
+    """vr_group (include/vr.h, csrc/group.cu): one process driving several GPUs -- the pass the application constructs
+    at src/rendering/vulkan_context.cpp:51, spread over `devices` (a device may be named more than once)."""
+
+    def __init__(self, devices, partition: int, width: int, height: int, slots: int = 2):
+        devs = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        rc = lib.vr_create_group(len(devices), devs, partition, width, height, slots, C.byref(h))
+        if rc != _lib.VR_OK:
+            raise VrError(rc, lib.vr_group_last_error(None).decode())
+        self._h, self.size = h, (width, height)
+
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib.vr_group_destroy(h)
+
+    __del__ = close
+
+    def _check(self, rc: int):
+        if rc != _lib.VR_OK:
+            raise VrError(rc, lib.vr_group_last_error(self._h).decode())
+
+    def __len__(self):
+        return lib.vr_group_size(self._h)
+
+    def set_uniforms(self, view, proj, camera_position):
+        v, p, c = (np.ascontiguousarray(x, np.float32) for x in (view, proj, camera_position))
+        self._check(lib.vr_group_set_camera(self._h, _ptr(v), _ptr(p), _ptr(c)))
+
+    def set_camera(self, camera: Camera):
+        self.set_uniforms(camera.get_view(), projection(*self.size), camera.get_position())
+
+    def set_rank_camera(self, rank: int, camera: Camera):
+        """replicas: the camera of one rank's frame."""
+        ctx = lib.vr_group_context(self._h, rank)
+        if lib.vr_set_camera_orbit(ctx, camera._h) != _lib.VR_OK:
+            raise VrError(1, lib.vr_last_error(ctx).decode())
+
+    def transfer_function_changed(self, data):
+        d = np.ascontiguousarray(data, np.uint32)
+        self._check(lib.vr_group_set_transfer_function(self._h, _ptr(d), len(d)))
+
+    def slicing_changed(self, min_slice, max_slice):
+        lo, hi = np.asarray(min_slice, np.float32), np.asarray(max_slice, np.float32)
+        self._check(lib.vr_group_set_slicing(self._h, _ptr(lo), _ptr(hi)))
+
+    def set_options(self, **kw):
+        o = Options()
+        lib.vr_get_options(lib.vr_group_context(self._h, 0), C.byref(o))
+        for k, v in kw.items():
+            setattr(o, k, v)
+        self._check(lib.vr_group_set_options(self._h, C.byref(o)))
+
+    def volume_dataset_changed(self, dataset: "Dataset"):
+        a = np.ascontiguousarray(dataset.data if dataset.data.dtype in _CODE else dataset.data.astype(np.float32))
+        mn = C.c_float(dataset.min) if dataset.min is not None else None
+        mx = C.c_float(dataset.max) if dataset.max is not None else None
+        nz, ny, nx = a.shape
+        self._check(lib.vr_group_set_volume(self._h, _ptr(a), _CODE[a.dtype], nx, ny, nz, C.byref(mn) if mn is not None else None,
+                                            C.byref(mx) if mx is not None else None))
+
+    def synth_volume(self, kind: int, seed: int, dtype: int, n):
+        nx, ny, nz = (n, n, n) if isinstance(n, int) else n
+        self._check(lib.vr_group_synth_volume(self._h, kind, seed & 0xFFFFFFFF, dtype, nx, ny, nz))
+
+    def record(self):
+        self._check(lib.vr_group_render(self._h))
+
+    def sync(self):
+        self._check(lib.vr_group_sync(self._h))
+
+    def download(self, rank: int = 0) -> np.ndarray:
+        w, h = self.size
+        out = np.empty((h, w, 4), np.uint8)
+        self._check(lib.vr_group_download(self._h, rank, _ptr(out)))
+        return out
 
 
 def read_nrrd(path: str) -> np.ndarray:

@@ -16,6 +16,7 @@ U8, U16, F32 = 0, 1, 2
 SAMPLER_HW, SAMPLER_EXACT = 0, 1
 SYNTH_MARSCHNER_LOBB, SYNTH_FBM, SYNTH_BLOBS, SYNTH_BLOBS_FBM = 0, 1, 2, 3
 LAYOUT_AUTO, LAYOUT_ARRAY3D, LAYOUT_PAIRED = 0, 1, 2
+PARTITION_REPLICAS, PARTITION_SORT_FIRST, PARTITION_SORT_LAST = 0, 1, 2
 
 
 class Options(C.Structure):
@@ -111,6 +112,20 @@ SIGNATURES = {
     "vr_set_image_target": (C.c_int, [_P, _P]),
     "vr_partition_box": (C.c_int, [_P, _P, C.c_uint32, _P, _P]),
     "vr_partition_order": (C.c_int, [_P, _P, _P, _P]),
+    "vr_create_group": (C.c_int, [C.c_uint32, C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
+    "vr_group_destroy": (C.c_int, [_P]),
+    "vr_group_last_error": (C.c_char_p, [_P]),
+    "vr_group_size": (C.c_uint32, [_P]),
+    "vr_group_context": (_P, [_P, C.c_uint32]),
+    "vr_group_set_camera": (C.c_int, [_P, _P, _P, _P]),
+    "vr_group_set_transfer_function": (C.c_int, [_P, _P, C.c_uint32]),
+    "vr_group_set_slicing": (C.c_int, [_P, _P, _P]),
+    "vr_group_set_options": (C.c_int, [_P, C.POINTER(Options)]),
+    "vr_group_set_volume": (C.c_int, [_P, _P, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, _F, _F]),
+    "vr_group_synth_volume": (C.c_int, [_P, C.c_int, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "vr_group_render": (C.c_int, [_P]),
+    "vr_group_sync": (C.c_int, [_P]),
+    "vr_group_download": (C.c_int, [_P, C.c_uint32, _P]),
     "vr_bench_tex_peak": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "vr_bench_fetch_only": (C.c_int, [_P, C.c_int]),
     "vr_debug_ray_context": (C.c_int, [_P, _P]),

@@ -1,0 +1,399 @@
+/*
+ * group.cu -- vr_group: ONE process driving the GPUs of one box (the C++ multi-GPU host of the path).
+ *
+ * The reference constructs its single pass at src/rendering/vulkan_context.cpp:51 and calls record() once per
+ * frame (src/rendering/main_pass.cpp:91); a group stands in the same place and records one frame on N devices.
+ * Everything here is host code over the C ABI of vr.h: a context per rank, peer access instead of CUDA IPC (one
+ * address space), and CUDA EVENTS instead of the flag kernels of sync.cu for the frame hand-off -- within one
+ * process cudaStreamWaitEvent orders streams of different devices, so nothing ever spins on the GPU.
+ *
+ *   replicas     every rank renders the frame of its own camera (set through vr_group_context)
+ *   sort-first   image tiles dealt to the ranks, volume replicated; every rank's K1 stores its tiles into the display
+ *                rank's image slot over NVLink; `slots` frames in flight
+ *   sort-last    one sub-box per rank (+ ghosts); K1 -> float4 partial (slot), K2 merges pixel range r of all
+ *                partials in view order into the display rank's image slot; march and merge on two streams
+ *
+ * (The one-process-per-GPU variant of the same protocols, for torchrun: volumetric-renderer_b200/multigpu.py.)
+ */
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <array>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "vr_ctx.h"
+
+struct vr_group {
+    int partition = VR_PARTITION_REPLICAS;
+    uint32_t n = 0, slots = 2, W = 0, H = 0;
+    std::vector<int> dev;
+    std::vector<vr_ctx *> ctx;
+    std::vector<cudaStream_t> march, merge; /* per rank */
+    cudaStream_t present = nullptr;         /* display rank (0) */
+    /* events [rank][slot] */
+    std::vector<std::vector<cudaEvent_t>> ready, merged;
+    std::vector<cudaEvent_t> consumed; /* [slot], display rank */
+    std::vector<void *> image_slot;    /* display rank's RGBA8 targets */
+    std::vector<std::vector<void *>> raw_slot; /* [rank][slot] */
+    uint64_t frame = 0;
+    uint32_t full[3] = {0, 0, 0}, grid[3] = {1, 1, 1};
+    std::vector<std::array<uint32_t, 6>> box; /* org, dims per rank */
+    float cam_pos[3] = {0, -3, 0};
+    std::string err;
+};
+
+namespace
+{
+thread_local std::string g_group_error;
+
+int gfail(vr_group *g, int status, const std::string &msg)
+{
+    if (g) g->err = msg;
+    else g_group_error = msg;
+    return status;
+}
+
+#define G_CUDA(g, call)                                                                              \
+    do {                                                                                             \
+        cudaError_t e__ = (call);                                                                    \
+        if (e__ != cudaSuccess) return gfail(g, VR_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+    } while (0)
+#define G_VR(g, r, call)                                                                              \
+    do {                                                                                              \
+        const int rc__ = (call);                                                                      \
+        if (rc__ != VR_OK) return gfail(g, rc__, std::string("rank ") + std::to_string(r) + ": " + vr_last_error((g)->ctx[r])); \
+    } while (0)
+
+/* split the axes as evenly as possible: 8 -> 2x2x2, 4 -> 2x2x1, 6 -> 3x2x1 (multigpu.grid_for_world) */
+void grid_for_world(uint32_t world, uint32_t g[3])
+{
+    g[0] = g[1] = g[2] = 1;
+    std::vector<uint32_t> factors;
+    uint32_t w = world;
+    for (uint32_t f = 2; w > 1; f++)
+        while (w % f == 0) factors.push_back(f), w /= f;
+    std::sort(factors.rbegin(), factors.rend());
+    for (uint32_t f : factors) {
+        int a = 0;
+        for (int i = 1; i < 3; i++)
+            if (g[i] < g[a]) a = i;
+        g[a] *= f;
+    }
+}
+
+/* pixel range of rank r for the direct-send merge (multiples of 32 pixels; multigpu.pixel_ranges) */
+void pixel_range(uint64_t npix, uint32_t world, uint32_t r, uint64_t &b, uint64_t &e)
+{
+    uint64_t per = (npix + world - 1) / world;
+    per = (per + 31) / 32 * 32;
+    b = std::min<uint64_t>((uint64_t)r * per, npix), e = std::min<uint64_t>((uint64_t)(r + 1) * per, npix);
+}
+
+int make_partition(vr_group *g, uint32_t nx, uint32_t ny, uint32_t nz)
+{
+    g->full[0] = nx, g->full[1] = ny, g->full[2] = nz;
+    grid_for_world(g->n, g->grid);
+    g->box.assign(g->n, {});
+    for (uint32_t r = 0; r < g->n; r++) {
+        uint32_t org[3], dims[3];
+        if (vr_partition_box(g->grid, g->full, r, org, dims) != VR_OK)
+            return gfail(g, VR_ERR_INVALID, "vr_group: the volume is too small for one sub-box per rank");
+        for (int i = 0; i < 3; i++) g->box[r][i] = org[i], g->box[r][3 + i] = dims[i];
+        G_VR(g, r, vr_set_partition_sort_last(g->ctx[r], g->full, org, dims));
+    }
+    return VR_OK;
+}
+
+int reduce_density_range(vr_group *g)
+{
+    float mn = 0.f, mx = 0.f;
+    for (uint32_t r = 0; r < g->n; r++) {
+        float a, b;
+        G_VR(g, r, vr_get_volume_info(g->ctx[r], nullptr, nullptr, &a, &b));
+        mn = r ? std::min(mn, a) : a, mx = r ? std::max(mx, b) : b;
+    }
+    for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_set_density_range(g->ctx[r], mn, mx));
+    return VR_OK;
+}
+
+/* image / partial slots and their peer pointers; called once the partition and the options are known */
+int wire(vr_group *g)
+{
+    g->image_slot.assign(g->slots, nullptr);
+    if (g->partition == VR_PARTITION_REPLICAS) return VR_OK;
+    for (uint32_t s = 0; s < g->slots; s++) {
+        unsigned char h[64];
+        if (s) G_VR(g, 0, vr_ipc_export(g->ctx[0], 16 + (int)s, h)); /* allocates the slot (the handle itself is not needed here) */
+        G_VR(g, 0, vr_get_image_frame(g->ctx[0], s, &g->image_slot[s], nullptr));
+    }
+    if (g->partition == VR_PARTITION_SORT_FIRST) {
+        for (uint32_t r = 0; r < g->n; r++) {
+            G_VR(g, r, vr_set_partition_sort_first(g->ctx[r], r, g->n, 64));
+            for (uint32_t s = 0; s < g->slots; s++)
+                if (r) G_VR(g, r, vr_set_image_target_frame(g->ctx[r], s, g->image_slot[s]));
+        }
+    } else {
+        g->raw_slot.assign(g->n, std::vector<void *>(g->slots, nullptr));
+        for (uint32_t r = 0; r < g->n; r++) {
+            vr_options o;
+            G_VR(g, r, vr_get_options(g->ctx[r], &o));
+            o.write_raw = 1;
+            G_VR(g, r, vr_set_options(g->ctx[r], &o));
+            for (uint32_t s = 0; s < g->slots; s++) G_VR(g, r, vr_get_raw_frame(g->ctx[r], s, &g->raw_slot[r][s]));
+        }
+    }
+    return VR_OK;
+}
+}  // namespace
+
+extern "C" const char *vr_group_last_error(const vr_group *g) { return g ? g->err.c_str() : g_group_error.c_str(); }
+extern "C" uint32_t vr_group_size(const vr_group *g) { return g ? g->n : 0; }
+extern "C" vr_ctx *vr_group_context(vr_group *g, uint32_t rank) { return (g && rank < g->n) ? g->ctx[rank] : nullptr; }
+
+extern "C" int vr_group_destroy(vr_group *g)
+{
+    if (!g) return VR_OK;
+    for (uint32_t r = 0; r < g->ctx.size(); r++) {
+        cudaSetDevice(g->dev[r]);
+        cudaDeviceSynchronize();
+    }
+    for (uint32_t r = 0; r < g->ctx.size(); r++) {
+        cudaSetDevice(g->dev[r]);
+        for (auto &e : g->ready.size() > r ? g->ready[r] : std::vector<cudaEvent_t>()) cudaEventDestroy(e);
+        for (auto &e : g->merged.size() > r ? g->merged[r] : std::vector<cudaEvent_t>()) cudaEventDestroy(e);
+        if (r < g->march.size() && g->march[r]) cudaStreamDestroy(g->march[r]);
+        if (r < g->merge.size() && g->merge[r]) cudaStreamDestroy(g->merge[r]);
+    }
+    if (!g->dev.empty()) cudaSetDevice(g->dev[0]);
+    for (auto &e : g->consumed) cudaEventDestroy(e);
+    if (g->present) cudaStreamDestroy(g->present);
+    for (auto *c : g->ctx) vr_destroy(c);
+    delete g;
+    return VR_OK;
+}
+
+extern "C" int vr_create_group(uint32_t ndev, const int *devs, int partition, uint32_t width, uint32_t height, uint32_t slots,
+                               vr_group **out)
+{
+    if (!out || !devs || ndev == 0 || ndev > 31 || width == 0 || height == 0 || partition < VR_PARTITION_REPLICAS ||
+        partition > VR_PARTITION_SORT_LAST)
+        return gfail(nullptr, VR_ERR_INVALID, "vr_create_group: bad arguments");
+    *out = nullptr;
+    vr_group *g = new (std::nothrow) vr_group;
+    if (!g) return gfail(nullptr, VR_ERR_NOMEM, "out of host memory");
+    g->partition = partition, g->n = ndev, g->W = width, g->H = height;
+    g->slots = std::min<uint32_t>(std::max<uint32_t>(slots ? slots : 2, 1), VR_MAX_FRAMES_IN_FLIGHT);
+    g->dev.assign(devs, devs + ndev);
+    auto bail = [&](int rc, const std::string &msg) {
+        g_group_error = msg;
+        vr_group_destroy(g);
+        return rc;
+    };
+    for (uint32_t r = 0; r < ndev; r++) {
+        vr_ctx *c = nullptr;
+        const int rc = vr_create(devs[r], width, height, &c);
+        if (rc != VR_OK) return bail(rc, std::string("vr_create_group: rank ") + std::to_string(r) + ": " + vr_last_error(nullptr));
+        g->ctx.push_back(c);
+    }
+    /* every device reaches every other's memory (one address space: plain pointers, no IPC handles) */
+    for (uint32_t a = 0; a < ndev; a++)
+        for (uint32_t b = 0; b < ndev; b++) {
+            if (devs[a] == devs[b]) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, devs[a], devs[b]);
+            if (!can && partition != VR_PARTITION_REPLICAS) return bail(VR_ERR_CUDA, "vr_create_group: the devices cannot access each other's memory");
+            cudaSetDevice(devs[a]);
+            const cudaError_t e = cudaDeviceEnablePeerAccess(devs[b], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled && partition != VR_PARTITION_REPLICAS)
+                return bail(VR_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+            cudaGetLastError();
+        }
+    g->march.assign(ndev, nullptr), g->merge.assign(ndev, nullptr);
+    g->ready.assign(ndev, std::vector<cudaEvent_t>(g->slots, nullptr));
+    g->merged.assign(ndev, std::vector<cudaEvent_t>(g->slots, nullptr));
+    for (uint32_t r = 0; r < ndev; r++) {
+        if (cudaSetDevice(devs[r]) != cudaSuccess || cudaStreamCreateWithFlags(&g->march[r], cudaStreamNonBlocking) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&g->merge[r], cudaStreamNonBlocking) != cudaSuccess)
+            return bail(VR_ERR_CUDA, "vr_create_group: cudaStreamCreate failed");
+        for (uint32_t s = 0; s < g->slots; s++)
+            if (cudaEventCreateWithFlags(&g->ready[r][s], cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&g->merged[r][s], cudaEventDisableTiming) != cudaSuccess)
+                return bail(VR_ERR_CUDA, "vr_create_group: cudaEventCreate failed");
+    }
+    cudaSetDevice(devs[0]);
+    if (cudaStreamCreateWithFlags(&g->present, cudaStreamNonBlocking) != cudaSuccess) return bail(VR_ERR_CUDA, "vr_create_group: cudaStreamCreate failed");
+    g->consumed.assign(g->slots, nullptr);
+    for (uint32_t s = 0; s < g->slots; s++)
+        if (cudaEventCreateWithFlags(&g->consumed[s], cudaEventDisableTiming) != cudaSuccess) return bail(VR_ERR_CUDA, "vr_create_group: cudaEventCreate failed");
+    if (partition == VR_PARTITION_SORT_FIRST) {
+        const int rc = wire(g);
+        if (rc != VR_OK) return bail(rc, g->err);
+    }
+    *out = g;
+    return VR_OK;
+}
+
+/* ---- mutators: the reference's members, applied to every rank ------------------------------------------------- */
+
+extern "C" int vr_group_set_camera(vr_group *g, const float view[16], const float proj[16], const float cam[3])
+{
+    if (!g || !cam) return gfail(g, VR_ERR_INVALID, "vr_group_set_camera: null argument");
+    for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_set_camera(g->ctx[r], view, proj, cam));
+    std::memcpy(g->cam_pos, cam, sizeof g->cam_pos);
+    return VR_OK;
+}
+
+extern "C" int vr_group_set_transfer_function(vr_group *g, const uint32_t *rgba8, uint32_t n)
+{
+    if (!g) return VR_ERR_INVALID;
+    for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_set_transfer_function(g->ctx[r], rgba8, n));
+    return VR_OK;
+}
+
+extern "C" int vr_group_set_slicing(vr_group *g, const float mn[3], const float mx[3])
+{
+    if (!g) return VR_ERR_INVALID;
+    for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_set_slicing(g->ctx[r], mn, mx));
+    return VR_OK;
+}
+
+extern "C" int vr_group_set_options(vr_group *g, const vr_options *o)
+{
+    if (!g || !o) return VR_ERR_INVALID;
+    vr_options oo = *o;
+    if (g->partition == VR_PARTITION_SORT_LAST) oo.write_raw = 1; /* the partial IS the float4 output */
+    for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_set_options(g->ctx[r], &oo));
+    return VR_OK;
+}
+
+extern "C" int vr_group_set_volume(vr_group *g, const void *data, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, const float *mn,
+                                   const float *mx)
+{
+    if (!g || !data || dtype < VR_U8 || dtype > VR_F32 || !nx || !ny || !nz) return gfail(g, VR_ERR_INVALID, "vr_group_set_volume: bad arguments");
+    if (g->partition != VR_PARTITION_SORT_LAST) {
+        for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_set_volume(g->ctx[r], data, dtype, nx, ny, nz, mn, mx)); /* replicated */
+        return VR_OK;
+    }
+    int rc = make_partition(g, nx, ny, nz);
+    if (rc != VR_OK) return rc;
+    const size_t esz = dtype == VR_U8 ? 1 : (dtype == VR_U16 ? 2 : 4);
+    std::vector<unsigned char> sub;
+    for (uint32_t r = 0; r < g->n; r++) {
+        /* the rank's sub-box plus one ghost voxel towards each neighbour, cut out of the host array */
+        uint32_t lo[3], l[3];
+        for (int i = 0; i < 3; i++) {
+            const uint32_t org = g->box[r][i], dims = g->box[r][3 + i], end = org + dims;
+            lo[i] = org - (org > 0 ? 1 : 0);
+            l[i] = dims + (org > 0 ? 1 : 0) + (end < g->full[i] ? 1 : 0);
+        }
+        sub.resize((size_t)l[0] * l[1] * l[2] * esz);
+        for (uint32_t z = 0; z < l[2]; z++)
+            for (uint32_t y = 0; y < l[1]; y++)
+                std::memcpy(sub.data() + ((size_t)z * l[1] + y) * l[0] * esz,
+                            static_cast<const unsigned char *>(data) + (((size_t)(lo[2] + z) * ny + (lo[1] + y)) * nx + lo[0]) * esz, (size_t)l[0] * esz);
+        G_VR(g, r, vr_set_volume(g->ctx[r], sub.data(), dtype, l[0], l[1], l[2], mn, mx));
+    }
+    if (!mn || !mx) {
+        rc = reduce_density_range(g);
+        if (rc != VR_OK) return rc;
+    }
+    return wire(g);
+}
+
+extern "C" int vr_group_synth_volume(vr_group *g, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz)
+{
+    if (!g) return VR_ERR_INVALID;
+    if (g->partition != VR_PARTITION_SORT_LAST) {
+        for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_synth_volume(g->ctx[r], kind, seed, dtype, nx, ny, nz));
+        return VR_OK;
+    }
+    int rc = make_partition(g, nx, ny, nz);
+    if (rc != VR_OK) return rc;
+    for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_synth_subvolume(g->ctx[r], kind, seed, dtype));
+    rc = reduce_density_range(g);
+    return rc != VR_OK ? rc : wire(g);
+}
+
+/* ---- one frame on all ranks ----------------------------------------------------------------------------------- */
+
+extern "C" int vr_group_render(vr_group *g)
+{
+    if (!g) return VR_ERR_INVALID;
+    const uint64_t k = g->frame;
+    const uint32_t S = g->slots, s = (uint32_t)(k % S), n = g->n;
+    if (g->partition == VR_PARTITION_REPLICAS) {
+        for (uint32_t r = 0; r < n; r++) G_VR(g, r, vr_render_frame(g->ctx[r], s, g->march[r]));
+        g->frame++;
+        return VR_OK;
+    }
+    if (g->partition == VR_PARTITION_SORT_FIRST) {
+        for (uint32_t r = 0; r < n; r++) {
+            G_CUDA(g, cudaSetDevice(g->dev[r]));
+            if (k >= S) G_CUDA(g, cudaStreamWaitEvent(g->march[r], g->consumed[s], 0)); /* frame k - S has left image slot s */
+            G_VR(g, r, vr_render_frame(g->ctx[r], s, g->march[r]));                      /* tiles straight into the display rank's slot */
+            G_CUDA(g, cudaEventRecord(g->ready[r][s], g->march[r]));
+        }
+        G_CUDA(g, cudaSetDevice(g->dev[0]));
+        for (uint32_t r = 0; r < n; r++) G_CUDA(g, cudaStreamWaitEvent(g->present, g->ready[r][s], 0));
+        G_CUDA(g, cudaEventRecord(g->consumed[s], g->present)); /* the frame is complete (a consumer would read it here) */
+        g->frame++;
+        return VR_OK;
+    }
+    /* sort-last */
+    if (g->raw_slot.empty()) return gfail(g, VR_ERR_STATE, "vr_group_render: no volume (vr_group_set_volume / vr_group_synth_volume)");
+    std::vector<uint32_t> order(n);
+    if (vr_partition_order(g->grid, g->full, g->cam_pos, order.data()) != VR_OK) return gfail(g, VR_ERR_INVALID, "vr_partition_order failed");
+    std::vector<uint32_t> rects(4 * n);
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t b = order[i];
+        if (vr_partition_screen_rect(g->ctx[0], g->full, &g->box[b][0], &g->box[b][3], &rects[4 * i]) != VR_OK)
+            return gfail(g, VR_ERR_INVALID, "vr_partition_screen_rect failed");
+    }
+    for (uint32_t r = 0; r < n; r++) {
+        G_CUDA(g, cudaSetDevice(g->dev[r]));
+        if (k >= S)
+            for (uint32_t q = 0; q < n; q++) G_CUDA(g, cudaStreamWaitEvent(g->march[r], g->merged[q][s], 0)); /* everyone has merged my partial of frame k - S */
+        G_VR(g, r, vr_render_frame(g->ctx[r], s, g->march[r]));
+        G_CUDA(g, cudaEventRecord(g->ready[r][s], g->march[r]));
+    }
+    const uint64_t npix = (uint64_t)g->W * g->H;
+    std::vector<const void *> parts(n);
+    for (uint32_t i = 0; i < n; i++) parts[i] = g->raw_slot[order[i]][s];
+    for (uint32_t r = 0; r < n; r++) {
+        G_CUDA(g, cudaSetDevice(g->dev[r]));
+        for (uint32_t q = 0; q < n; q++) G_CUDA(g, cudaStreamWaitEvent(g->merge[r], g->ready[q][s], 0));
+        if (k >= S) G_CUDA(g, cudaStreamWaitEvent(g->merge[r], g->consumed[s], 0));
+        uint64_t b, e;
+        pixel_range(npix, n, r, b, e);
+        if (e > b) G_VR(g, r, vr_composite_rects(g->ctx[r], parts.data(), rects.data(), n, b, e, g->image_slot[s], g->merge[r]));
+        G_CUDA(g, cudaEventRecord(g->merged[r][s], g->merge[r]));
+    }
+    G_CUDA(g, cudaSetDevice(g->dev[0]));
+    for (uint32_t r = 0; r < n; r++) G_CUDA(g, cudaStreamWaitEvent(g->present, g->merged[r][s], 0));
+    G_CUDA(g, cudaEventRecord(g->consumed[s], g->present));
+    g->frame++;
+    return VR_OK;
+}
+
+extern "C" int vr_group_sync(vr_group *g)
+{
+    if (!g) return VR_ERR_INVALID;
+    for (uint32_t r = 0; r < g->n; r++) G_VR(g, r, vr_sync(g->ctx[r]));
+    return VR_OK;
+}
+
+/* The frame recorded last, complete, from the display rank's slot (replicas: rank's own frame). */
+extern "C" int vr_group_download(vr_group *g, uint32_t rank, void *host_rgba8)
+{
+    if (!g || !host_rgba8 || rank >= g->n) return gfail(g, VR_ERR_INVALID, "vr_group_download: bad arguments");
+    if (g->frame == 0) return gfail(g, VR_ERR_STATE, "vr_group_download: nothing rendered yet");
+    const int rc = vr_group_sync(g);
+    if (rc != VR_OK) return rc;
+    const uint32_t s = (uint32_t)((g->frame - 1) % g->slots), r = g->partition == VR_PARTITION_REPLICAS ? rank : 0;
+    G_VR(g, r, vr_download_frame_async(g->ctx[r], s, host_rgba8, nullptr));
+    G_VR(g, r, vr_sync(g->ctx[r]));
+    return VR_OK;
+}
