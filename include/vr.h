@@ -128,6 +128,15 @@ int vr_render(vr_ctx *ctx, void *cuda_stream);
 int vr_render_frame(vr_ctx *ctx, uint32_t frame_index, void *cuda_stream);
 /* The decisions vr_render_frame took for the frame it enqueued last. */
 int vr_get_last_frame_info(const vr_ctx *ctx, vr_frame_info *out);
+/* Empty-space skipping in screen space (no reference counterpart; the frame is unchanged).  When skipping is active
+ * and no statistics are collected, a small kernel ahead of the march projects every occupied cell of the volume and
+ * marks the 16 x tile_h pixel tiles its screen box touches; the march sets no rays up in the other tiles and stores
+ * the clear colour there.  This returns the mask of the frame recorded last into `frame_index` (synchronises):
+ * bit (ty * tiles_x + tx) of `words`, plus one trailing word that is non-zero when some cell could not be
+ * projected and the march ignored the mask.  `words` may be NULL to query the shape; capacity is in words and must
+ * be >= (tiles_x * tiles_y + 31) / 32 + 1.  VR_ERR_STATE when that frame used no mask. */
+int vr_get_tile_mask(vr_ctx *ctx, uint32_t frame_index, uint32_t *words, uint32_t capacity, uint32_t *tiles_x, uint32_t *tiles_y,
+                     uint32_t *tile_h);
 int vr_get_image_frame(vr_ctx *ctx, uint32_t frame_index, void **dev_rgba8, size_t *pitch_bytes);
 int vr_download_frame_async(vr_ctx *ctx, uint32_t frame_index, void *host_rgba8, void *cuda_stream);
 /* vr_download_frame_async that moves only what can differ from what `host_rgba8` already holds.  Outside the

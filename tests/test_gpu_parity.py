@@ -676,7 +676,7 @@ def test_non_finite_voxels_are_not_skipped(vr, port, sampler):
     sampler).  fminf / fmaxf drop NaNs, so a cell of NaN voxels used to get an empty range and was skipped even when
     texel 0 is visible: frames with and without empty-space skipping must agree."""
     rng = np.random.default_rng(5)
-    vol = np.zeros((32, 32, 32), np.float32)
+    vol = np.full((32, 32, 32), 0.5, np.float32)   # background: a transparent texel, so that most cells are empty
     vol[4:12, 4:12, 4:12] = np.nan
     vol[20:28, 6:10, 18:30] = np.inf
     vol[14:18, 20:30, 2:9] = -np.inf
@@ -733,5 +733,92 @@ def test_full_downloads_keep_the_dirty_rectangle_bookkeeping_right(vr, port):
         host.fill_(7)                                       # someone else scribbles over the buffer
         op.forget_host_buffer(host.data_ptr())
         assert frame(-3.0, op.download_dirty_async) == 320 * 200 * 4
+    finally:
+        op.close()
+
+
+MASK_VIEWS = [([(45 * 4, 30 * 4)], 0.0), ([(135 * 4, -30 * 4)], 0.0), ([(0, 0)], 0.0), ([(0, 89 * 4)], 0.0), ([(225 * 4, 30 * 4)], 2.0),
+              ([(315 * 4, -30 * 4)], 2.7), ([(90 * 4, 0)], -3.0)]
+
+
+@pytest.mark.parametrize("layout", ["array3d", "paired"])
+def test_screen_space_tile_mask_changes_nothing(vr, port, layout, monkeypatch):
+    """with skipping on, tiles no occupied cell projects into get the clear colour without a ray being
+    set up.  The frames (RGBA8 and the float4 before the blend) must be BIT-identical to the ones of a context without
+    the mask, the mask must cover every pixel that drew anything, and on a sparse volume it must drop tiles."""
+    vol = small_volume(port, 2, np.uint16, 64)
+    lut = tf(port, "C")
+    lay = vr.LAYOUT_PAIRED if layout == "paired" else vr.LAYOUT_ARRAY3D
+    w, h = 480, 270
+
+    def run(mask):
+        monkeypatch.setenv("VR_TILE_MASK", "1" if mask else "0")
+        op = vr.OffscreenPass(w, h)
+        out = []
+        try:
+            op.set_volume_layout(lay)
+            op.set_options(sampler=vr.SAMPLER_HW, write_raw=1, empty_skip=1, early_term=0)
+            op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+            op.transfer_function_changed(lut)
+            for j, (mv, zoom) in enumerate(MASK_VIEWS):
+                cam, _ = twin_cameras(vr, port, mv, zoom)
+                op.set_camera(cam)
+                if j == 3:
+                    op.slicing_changed((0.0, 0.2, 0.0), (0.7, 1.0, 1.0))
+                op.record(None, j % 2)
+                out.append((op.download_frame(j % 2), op.download_raw() if j % 2 == 0 else None, op.tile_mask(j % 2), op.last_frame_info()))
+                if j == 3:
+                    op.slicing_changed((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))
+            # statistics need every ray: no mask for that frame
+            op.set_options(sampler=vr.SAMPLER_HW, write_raw=1, empty_skip=1, early_term=0, collect_stats=1)
+            op.record()
+            assert op.tile_mask(0) is None
+        finally:
+            op.close()
+        return out
+
+    want, got = run(False), run(True)
+    dropped = 0
+    for j, (a, b) in enumerate(zip(want, got)):
+        assert a[2] is None and b[2] is not None
+        assert np.array_equal(a[0], b[0]), f"view {j}: RGBA8 differs"
+        if a[1] is not None:
+            assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), f"view {j}: float4 differs"
+        bits, ignored, th = b[2]
+        if MASK_VIEWS[j][1] < 2.5:
+            assert not ignored, f"view {j}"
+        elif ignored:
+            continue   # a cell behind the eye: the march ignored the mask (the frames above are identical all the same)
+        clear = a[0][0, 0]
+        drew = (a[0] != clear).any(axis=2)
+        ys, xs = np.nonzero(drew)
+        assert bits[ys // th, xs // 16].all(), f"view {j}: a pixel that drew lies in an unmarked tile"
+        x0, y0, x1, y1 = b[3].bbox
+        inside = bits[y0 // th:(y1 + th - 1) // th, x0 // 16:(x1 + 15) // 16]
+        dropped += inside.size - int(inside.sum())
+    assert dropped > 0, "the sparse volume must leave tiles of the cube's screen box unmarked"
+
+
+def test_tile_mask_is_ignored_when_a_cell_is_behind_the_eye(vr, port):
+    """Camera inside the near range of the cube: cells with w <= 0 cannot be projected -- the mask is built, flagged, and
+    the frame equals the oracle's as without it."""
+    vol = small_volume(port, 2, np.uint16, 32)
+    lut = tf(port, "C")
+    op = vr.OffscreenPass(320, 200)
+    try:
+        op.set_options(sampler=vr.SAMPLER_HW, empty_skip=1, early_term=0)
+        op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+        op.transfer_function_changed(lut)
+        cam, ocam = twin_cameras(vr, port, [(100, 60)], 2.9)
+        for _ in range(40):
+            cam.zoom(0.5)
+            ocam.zoom(0.5)
+        op.set_camera(cam)
+        op.record()
+        img = op.download()
+        m = op.tile_mask(0)
+        want = port.render(oracle_frame(port, ocam, 320, 200, float(vol.min()), float(vol.max())), vol, lut)
+        assert_within_tolerance(img, want["rgba8"], "closest zoom")
+        assert m is not None
     finally:
         op.close()

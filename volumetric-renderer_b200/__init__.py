@@ -210,6 +210,19 @@ class OffscreenPass:
         self._check(lib.vr_get_last_frame_info(self._h, C.byref(fi)))
         return fi
 
+    def tile_mask(self, frame_index: int = 0):
+        """vr_get_tile_mask: (bool array [tiles_y, tiles_x] of the tiles the march set rays up in, ignored flag, tile height);
+        None when the frame recorded last into that slot used no mask."""
+        import numpy as np
+        tx, ty, th = C.c_uint32(0), C.c_uint32(0), C.c_uint32(0)
+        if lib.vr_get_tile_mask(self._h, frame_index, None, 0, C.byref(tx), C.byref(ty), C.byref(th)) != 0:
+            return None
+        n = (tx.value * ty.value + 31) // 32 + 1
+        words = np.zeros(n, np.uint32)
+        self._check(lib.vr_get_tile_mask(self._h, frame_index, words.ctypes.data_as(C.POINTER(C.c_uint32)), n, None, None, None))
+        bits = np.unpackbits(words[:-1].view(np.uint8), bitorder="little")[: tx.value * ty.value].astype(bool)
+        return bits.reshape(ty.value, tx.value), bool(words[-1]), th.value
+
     def set_march(self, ray_dist: float, step_size: float):
         self._check(lib.vr_set_march(self._h, ray_dist, step_size))
 

@@ -47,6 +47,8 @@ SIGNATURES = {
     "vr_render": (C.c_int, [_P, _P]),
     "vr_render_frame": (C.c_int, [_P, C.c_uint32, _P]),
     "vr_get_last_frame_info": (C.c_int, [_P, C.POINTER(FrameInfo)]),
+    "vr_get_tile_mask": (C.c_int, [_P, C.c_uint32, C.POINTER(C.c_uint32), C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
+                                   C.POINTER(C.c_uint32)]),
     "vr_get_image_frame": (C.c_int, [_P, C.c_uint32, C.POINTER(_P), C.POINTER(C.c_size_t)]),
     "vr_download_frame_async": (C.c_int, [_P, C.c_uint32, _P, _P]),
     "vr_download_frame_dirty_async": (C.c_int, [_P, C.c_uint32, _P, _P, C.POINTER(C.c_size_t)]),

@@ -172,6 +172,8 @@ void release_volume(vr_ctx *c)
     if (c->d_occ) cudaFree(c->d_occ), c->d_occ = nullptr;
     if (c->d_dist) cudaFree(c->d_dist), c->d_dist = nullptr;
     if (c->d_sat) cudaFree(c->d_sat), c->d_sat = nullptr;
+    if (c->d_occ_list) cudaFree(c->d_occ_list), c->d_occ_list = nullptr;
+    if (c->d_occ_count) cudaFree(c->d_occ_count), c->d_occ_count = nullptr;
 }
 
 int alloc_target(vr_ctx *c, uint32_t w, uint32_t h)
@@ -182,6 +184,8 @@ int alloc_target(vr_ctx *c, uint32_t w, uint32_t h)
         if (c->d_image_slot[k]) cudaFree(c->d_image_slot[k]), c->d_image_slot[k] = nullptr;
         if (c->d_raw_slot[k]) cudaFree(c->d_raw_slot[k]), c->d_raw_slot[k] = nullptr;
     }
+    for (int k = 0; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
+        if (c->d_tile_mask[k]) cudaFree(c->d_tile_mask[k]), c->d_tile_mask[k] = nullptr;
     c->W = w, c->H = h;
     VR_CUDA(c, cudaMalloc(&c->d_image, (size_t)w * h * sizeof(uchar4)));
     VR_CUDA(c, cudaMemset(c->d_image, 0, (size_t)w * h * sizeof(uchar4)));
@@ -327,6 +331,8 @@ int install_volume_unchecked(vr_ctx *c, const void *dev, int dtype, uint32_t nx,
     VR_CUDA(c, cudaMalloc(&c->d_occ, sizeof(uint32_t) * c->occ_words));
     VR_CUDA(c, cudaMalloc(&c->d_dist, (size_t)ncells * 8));
     VR_CUDA(c, cudaMalloc(&c->d_sat, sizeof(uint32_t) * (size_t)(c->occ_n[0] + 1) * (c->occ_n[1] + 1) * (c->occ_n[2] + 1)));
+    VR_CUDA(c, cudaMalloc(&c->d_occ_list, sizeof(uint32_t) * (size_t)ncells));
+    VR_CUDA(c, cudaMalloc(&c->d_occ_count, sizeof(uint32_t)));
     VR_CUDA(c, vr_k0_cell_ranges(dev, dtype, nx, ny, nz, cell, c->occ_n, c->d_cell_range, c->stream));
     c->occ_dirty = true;
     VR_CUDA(c, cudaStreamSynchronize(c->stream)); /* the reference's upload is synchronous too */
@@ -395,6 +401,7 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     if (const char *e = std::getenv("VR_CTA_THREADS")) c->tune_threads = std::atoi(e) == 256 ? 256 : 128;
     if (const char *e = std::getenv("VR_BBOX")) c->tune_bbox = std::atoi(e);
     if (const char *e = std::getenv("VR_DIRTY_CLEAR")) c->tune_dirty_clear = std::atoi(e);
+    if (const char *e = std::getenv("VR_TILE_MASK")) c->tune_tile_mask = std::atoi(e);
     if (const char *e = std::getenv("VR_WARP_W")) {
         const int w = std::atoi(e);
         if (w == 4 || w == 8 || w == 16) c->tune_warp_w = w;
@@ -444,6 +451,8 @@ extern "C" int vr_destroy(vr_ctx *c)
         if (c->d_image_slot[k]) cudaFree(c->d_image_slot[k]);
         if (c->d_raw_slot[k]) cudaFree(c->d_raw_slot[k]);
     }
+    for (int k = 0; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
+        if (c->d_tile_mask[k]) cudaFree(c->d_tile_mask[k]);
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->d_flags) cudaFree(c->d_flags);
     if (c->h_counters) cudaFreeHost(c->h_counters);
@@ -657,6 +666,7 @@ int prepare_occupancy(vr_ctx *c, cudaStream_t s)
     VR_CUDA(c, vr_k0_classify(c->d_cell_range, c->occ_n, c->d_lut_pad, c->nlut, c->min_density, c->max_density, c->d_occ,
                               c->occ_words, c->d_counters + 4, s));
     VR_CUDA(c, vr_k0_distance(c->d_occ, c->occ_n, c->d_dist, c->d_sat, s));
+    VR_CUDA(c, vr_k0_list_occupied(c->d_occ, c->occ_n, c->d_occ_list, c->d_occ_count, s));
     VR_CUDA(c, cudaMemcpyAsync(&c->h_counters[4], c->d_counters + 4, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     VR_CUDA(c, cudaStreamSynchronize(s));
     c->occ_empty_cells = c->h_counters[4];
@@ -994,6 +1004,45 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
     p.out = target;
     p.raw = raw_target;
     if (c->opt.collect_stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), s));
+    p.tile_mask = nullptr, p.mask_words = 0;
+    c->slot_mask_valid[frame_index] = false;
+    if (ess && !exact && !c->opt.collect_stats && c->tune_tile_mask && p.sp_count) {
+        /* screen-space mask of the tiles that can meet an occupied cell (one small launch ahead of K1, same stream) */
+        const uint32_t words = (p.ntx * p.nty + 31u) / 32u;
+        if (c->d_tile_mask[frame_index] && c->tile_mask_words != words)
+            for (int k = 0; k < VR_MAX_FRAMES_IN_FLIGHT; k++)
+                if (c->d_tile_mask[k]) {
+                    VR_CUDA(c, cudaDeviceSynchronize());
+                    cudaFree(c->d_tile_mask[k]), c->d_tile_mask[k] = nullptr;
+                }
+        if (!c->d_tile_mask[frame_index]) {
+            VR_CUDA(c, cudaMalloc(&c->d_tile_mask[frame_index], sizeof(uint32_t) * 2 * (words + 1)));
+            VR_CUDA(c, cudaMemsetAsync(c->d_tile_mask[frame_index], 0, sizeof(uint32_t) * 2 * (words + 1), s));
+            c->tile_mask_cur[frame_index] = 0;
+        }
+        c->tile_mask_words = words;
+        float pv[16], lo[3], cell[3];
+        {
+            double v[16], pr[16], m[16];
+            for (int i = 0; i < 16; i++) v[i] = (double)c->view[i], pr[i] = (double)c->proj[i];
+            mat4_mul_d(pr, v, m);
+            for (int i = 0; i < 16; i++) pv[i] = (float)m[i];
+        }
+        const uint32_t ld[3] = {c->nx, c->ny, c->nz};
+        for (int i = 0; i < 3; i++) {
+            const double full = c->sort_last ? (double)c->full[i] : (double)ld[i], org = c->sort_last ? (double)c->tex_org[i] : 0.0;
+            lo[i] = (float)(org / full - 0.5), cell[i] = (float)((double)c->occ_cell / full);
+        }
+        const uint32_t cur = c->tile_mask_cur[frame_index];
+        uint32_t *mask = c->d_tile_mask[frame_index] + (size_t)cur * (words + 1), *other = c->d_tile_mask[frame_index] + (size_t)(cur ^ 1u) * (words + 1);
+        const uint64_t ncells = (uint64_t)c->occ_n[0] * c->occ_n[1] * c->occ_n[2];
+        VR_CUDA(c, vr_k0_tile_mask(pv, lo, cell, c->occ_n, c->d_occ_list, c->d_occ_count, (uint32_t)(ncells - c->occ_empty_cells), c->W, c->H,
+                                   p.ntx, p.tile_h, mask, other, words, s));
+        c->tile_mask_cur[frame_index] = cur ^ 1u;
+        p.tile_mask = mask, p.mask_words = words;
+        c->slot_mask_valid[frame_index] = true;
+        c->slot_mask_shape[frame_index][0] = p.ntx, c->slot_mask_shape[frame_index][1] = p.nty, c->slot_mask_shape[frame_index][2] = p.tile_h;
+    }
     if (c->bench_fetch_only) {
         if (exact || ess || c->opt.collect_stats || c->sort_last || (pair && p.pair_split != 0x10000))
             return fail(c, VR_ERR_STATE, "vr_bench_fetch_only: hardware sampler, no skipping, no statistics, whole volume, pair copy in one array");
@@ -1017,6 +1066,26 @@ extern "C" int vr_get_last_frame_info(const vr_ctx *c, vr_frame_info *out)
 {
     if (!c || !out) return VR_ERR_INVALID;
     *out = c->last_info;
+    return VR_OK;
+}
+
+extern "C" int vr_get_tile_mask(vr_ctx *c, uint32_t frame_index, uint32_t *words, uint32_t capacity, uint32_t *tiles_x, uint32_t *tiles_y,
+                                uint32_t *tile_h)
+{
+    if (!c || frame_index >= VR_MAX_FRAMES_IN_FLIGHT) return VR_ERR_INVALID;
+    if (!c->d_tile_mask[frame_index] || !c->slot_mask_valid[frame_index])
+        return fail(c, VR_ERR_STATE, "vr_get_tile_mask: the frame recorded last into this slot used no tile mask");
+    const uint32_t n = c->tile_mask_words + 1;
+    if (tiles_x) *tiles_x = c->slot_mask_shape[frame_index][0];
+    if (tiles_y) *tiles_y = c->slot_mask_shape[frame_index][1];
+    if (tile_h) *tile_h = c->slot_mask_shape[frame_index][2];
+    if (!words) return VR_OK;
+    if (capacity < n) return fail(c, VR_ERR_INVALID, "vr_get_tile_mask: capacity " + std::to_string(capacity) + " < " + std::to_string(n) + " words");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaDeviceSynchronize());
+    /* the buffer the frame recorded last used is the one that is not next in turn */
+    VR_CUDA(c, cudaMemcpy(words, c->d_tile_mask[frame_index] + (size_t)(c->tile_mask_cur[frame_index] ^ 1u) * n, sizeof(uint32_t) * n,
+                          cudaMemcpyDeviceToHost));
     return VR_OK;
 }
 

@@ -198,7 +198,7 @@ struct Ray {
     float ifx, ify, ifz;   /* ESS: 1 / (d * occ_scale): steps per cell, per axis (1e30 where d = 0) */
     float sgx, sgy, sgz;   /* ESS: sign of the direction, per axis */
     uint32_t doff;         /* ESS: offset of the distance map of the direction's octant */
-    bool in_empty;         /* ESS: the last step generated fell into an empty fine cell */
+    bool in_empty;         /* ESS, hardware sampler: the lane sits the coming batch out (skip_empty) */
     /* sort-last, hardware sampler: positions are a pure function of the step index, pos_i = e + i * d (one FMA),
      * so that every rank computes the same position for step i wherever it starts walking (see outer_interval) */
     float ex, ey, ez, fi;
@@ -288,19 +288,23 @@ __device__ __forceinline__ void outer_interval(const MarchParams &p, const Ray &
 template <bool STATS, bool PART>
 __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fast_lo, int fast_hi)
 {
+    /* One look-up per BATCH, here, not one per step (hardware sampler): the batch that follows samples all its
+     * steps when the cell of its first position may contribute, and none -- the lane sits the batch out, its position
+     * unchanged -- when eight jumps did not reach such a cell.  A step sampled in an empty cell next to an occupied one
+     * composites alpha 0: the result is unchanged, a blob costs at most U - 1 wasted fetches where the ray leaves it. */
+    r.in_empty = false;
+    if (r.done) return;
 #pragma unroll 1
     for (int guard = 0; guard < 8; guard++) {
-        if (r.done || !r.in_empty || r.i < fast_lo || r.i > fast_hi) return;
+        /* outside the safe interval (the first and last steps of the ray, at a slicing plane): sample every step */
+        if (r.i < fast_lo || r.i > fast_hi) return;
         /* position in cell units (> 0 and inside the grid: the safe interval is inside the box) */
         const float fx = PART ? fmaf(r.px, p.occ_scale[0], -p.occ_off[0]) : r.px * p.occ_scale[0];
         const float fy = PART ? fmaf(r.py, p.occ_scale[1], -p.occ_off[1]) : r.py * p.occ_scale[1];
         const float fz = PART ? fmaf(r.pz, p.occ_scale[2], -p.occ_off[2]) : r.pz * p.occ_scale[2];
         const int cx = min((int)fx, p.occ_n[0] - 1), cy = min((int)fy, p.occ_n[1] - 1), cz = min((int)fz, p.occ_n[2] - 1);
         const int d = (int)__ldg(p.dist + r.doff + (cz * p.occ_stride[2] + cy * p.occ_stride[1] + cx * p.occ_stride[0]));
-        if (d == 0) {
-            r.in_empty = false;
-            return;
-        }
+        if (d == 0) return;
         /* steps until the ray leaves the cube: per axis the exit plane is the cell's entry face + d cells
          * along the direction, i.e. the cell centre +- (d - 1/2), pulled in by a margin that covers the
          * rounding of the positions (<= steps * ulp, far below 2e-3 cells); sg = direction sign,
@@ -322,6 +326,7 @@ __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fas
             r.px = fmaf(kf, r.dx, r.px), r.py = fmaf(kf, r.dy, r.py), r.pz = fmaf(kf, r.dz, r.pz);
         }
     }
+    r.in_empty = true; /* still in empty space: no step of the coming batch */
 }
 
 /* One batch of U consecutive iterations of volume.frag:33-48, split in two halves so that the
@@ -343,11 +348,12 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
 #pragma unroll
     for (int u = 0; u < U; u++) {
         bool s;
+        const bool out = ESS && !EXACT && r.in_empty; /* sits this batch out (skip_empty) */
         if (CHECK) {
             /* volume.frag:33-37: loop bound and the strict bounds test */
-            const bool inb = !r.done && (PART ? r.i <= r.i_end : r.i < p.steps) &&
+            const bool inb = !r.done && !out && (PART ? r.i <= r.i_end : r.i < p.steps) &&
                              !(r.px > 1.0f || r.py > 1.0f || r.pz > 1.0f || r.px < 0.0f || r.py < 0.0f || r.pz < 0.0f);
-            if (!inb) r.done = true;
+            if (!inb && !out) r.done = true;
             /* volume.frag:39-40: strict on both sides */
             s = inb && r.px < p.max_slice[0] && r.py < p.max_slice[1] && r.pz < p.max_slice[2] &&
                 r.px > p.min_slice[0] && r.py > p.min_slice[1] && r.pz > p.min_slice[2];
@@ -359,20 +365,23 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
                 r.ns += s;
             }
         } else {
-            s = PRED ? !r.done : true;
+            s = PRED ? (!r.done && !out) : true;
             if (STATS) {
-                r.nb += !r.done;
-                r.ns += !r.done;
+                r.nb += !r.done && !out;
+                r.ns += !r.done && !out;
             }
         }
-        if (ESS) {
-            const bool occ = !s || cell_distance<PART>(p, r.doff, r.px, r.py, r.pz) == 0;
-            r.in_empty = !occ;
-            s = s && occ;
+        if (ESS && EXACT) {
+            /* the exact sampler walks every step (bit-identical positions) and looks each one up */
+            s = s && cell_distance<PART>(p, r.doff, r.px, r.py, r.pz) == 0;
         }
         if (CHECK || PRED) b.ok[u] = s;
         qx[u] = r.px, qy[u] = r.py, qz[u] = r.pz;
-        advance<PART && !EXACT>(r);
+        if (ESS && !EXACT) {
+            if (!r.in_empty) advance<PART>(r); /* a lane that sits the batch out stays where skip_empty left it */
+        } else {
+            advance<PART && !EXACT>(r);
+        }
     }
 #pragma unroll
     for (int u = 0; u < U; u++) {
@@ -445,6 +454,45 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
     if (!EXACT && ERT && r.T < p.ert_eps) r.stop = true, r.done = true;
 }
 
+/* Which tile block b of the marching blocks works on; false = none (outside the rectangle / not this rank's). */
+__device__ __forceinline__ bool tile_of_block(const MarchParams &p, uint32_t block, int &tx, int &ty)
+{
+    if (p.pt_enum) {
+        /* sort-first: the marching blocks enumerate this rank's partition tiles only, row by row; partition tile
+         * (x, y) belongs to rank (x + y * pt_m) % pt_nranks, so in row y the owned ones are every pt_nranks-th
+         * from the first x >= pt_x0 with that residue */
+        const uint32_t per_tile = p.pt_sub_x * p.pt_sub_y, per_row = p.pt_cnt * per_tile;
+        const uint32_t row = block / per_row, rem = block - row * per_row;
+        const uint32_t j = rem / per_tile, sub = rem - j * per_tile;
+        /* rows from the middle of the box outwards (c, c+1, c-1, ...): the long rays start first, the short ones
+         * at the top and bottom edge fill the tail */
+        const uint32_t mid = (p.pt_rows - 1u) >> 1;
+        const uint32_t pty = p.pt_y0 + ((row & 1u) ? mid + ((row + 1u) >> 1) : mid - (row >> 1));
+        const uint32_t want = (p.pt_rank + p.pt_nranks - (pty * p.pt_m + p.pt_x0) % p.pt_nranks) % p.pt_nranks;
+        const uint32_t ptx = p.pt_x0 + want + j * p.pt_nranks;
+        if (ptx >= p.pt_x1) return false;
+        const uint32_t sy = sub / p.pt_sub_x, sx = sub - sy * p.pt_sub_x;
+        tx = (int)(ptx * p.pt_sub_x + sx), ty = (int)(pty * p.pt_sub_y + sy);
+    } else {
+        int ox = 0, oy = 0;
+        const int b = (int)block;
+        if (b > 0) {
+            int r = (int)ceilf((sqrtf((float)(b + 1)) - 1.0f) * 0.5f);
+            while ((2 * r - 1) * (2 * r - 1) > b) r--;
+            while ((2 * r + 1) * (2 * r + 1) <= b) r++;
+            /* ring r holds 8r tiles, four sides of 2r: no integer division */
+            const int k = b - (2 * r - 1) * (2 * r - 1), r2 = 2 * r;
+            const int seg = (k >= r2) + (k >= 2 * r2) + (k >= 3 * r2), off = k - seg * r2;
+            if (seg == 0) ox = r, oy = -r + 1 + off;
+            else if (seg == 1) ox = r - 1 - off, oy = r;
+            else if (seg == 2) ox = -r, oy = r - 1 - off;
+            else ox = -r + 1 + off, oy = -r;
+        }
+        tx = p.sp_cx + ox, ty = p.sp_cy + oy;
+    }
+    return !(tx < p.rect[0] || ty < p.rect[1] || tx >= p.rect[2] || ty >= p.rect[3]);
+}
+
 /* EXACT: verification sampler.  ESS: occupancy grid consulted.  STATS: sample counters.
  * PART: sort-last sub-volume.  PAIR: 0 = 3-D array, 1 = paired layout, 2 = paired layout whose copy spans
  * two layered arrays.  UB: steps per batch (HW sampler; two batches are in flight). */
@@ -461,43 +509,26 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
      * clear colour where the target does not hold it already (api.cu: dirty clear -- the whole target
      * on the first frame into it, afterwards only what the previous frame drew outside this frame's tiles). */
     const uint32_t nthreads = blockDim.x;
-    int tx, ty;
+    int tx = 0, ty = 0;
     const bool in_bbox = blockIdx.x < p.sp_count;
-    if (in_bbox && p.pt_enum) {
-        /* sort-first: the marching blocks enumerate this rank's partition tiles only, row by row; partition tile
-         * (x, y) belongs to rank (x + y * pt_m) % pt_nranks, so in row y the owned ones are every pt_nranks-th
-         * from the first x >= pt_x0 with that residue */
-        const uint32_t block = blockIdx.x;
-        const uint32_t per_tile = p.pt_sub_x * p.pt_sub_y, per_row = p.pt_cnt * per_tile;
-        const uint32_t row = block / per_row, rem = block - row * per_row;
-        const uint32_t j = rem / per_tile, sub = rem - j * per_tile;
-        /* rows from the middle of the box outwards (c, c+1, c-1, ...): the long rays start first, the short ones
-         * at the top and bottom edge fill the tail */
-        const uint32_t mid = (p.pt_rows - 1u) >> 1;
-        const uint32_t pty = p.pt_y0 + ((row & 1u) ? mid + ((row + 1u) >> 1) : mid - (row >> 1));
-        const uint32_t want = (p.pt_rank + p.pt_nranks - (pty * p.pt_m + p.pt_x0) % p.pt_nranks) % p.pt_nranks;
-        const uint32_t ptx = p.pt_x0 + want + j * p.pt_nranks;
-        if (ptx >= p.pt_x1) return;
-        const uint32_t sy = sub / p.pt_sub_x, sx = sub - sy * p.pt_sub_x;
-        tx = (int)(ptx * p.pt_sub_x + sx), ty = (int)(pty * p.pt_sub_y + sy);
-        if (tx < p.rect[0] || ty < p.rect[1] || tx >= p.rect[2] || ty >= p.rect[3]) return;
-    } else if (in_bbox) {
-        int ox = 0, oy = 0;
-        const int b = (int)blockIdx.x;
-        if (b > 0) {
-            int r = (int)ceilf((sqrtf((float)(b + 1)) - 1.0f) * 0.5f);
-            while ((2 * r - 1) * (2 * r - 1) > b) r--;
-            while ((2 * r + 1) * (2 * r + 1) <= b) r++;
-            /* ring r holds 8r tiles, four sides of 2r: no integer division */
-            const int k = b - (2 * r - 1) * (2 * r - 1), r2 = 2 * r;
-            const int seg = (k >= r2) + (k >= 2 * r2) + (k >= 3 * r2), off = k - seg * r2;
-            if (seg == 0) ox = r, oy = -r + 1 + off;
-            else if (seg == 1) ox = r - 1 - off, oy = r;
-            else if (seg == 2) ox = -r, oy = r - 1 - off;
-            else ox = -r + 1 + off, oy = -r;
+    bool tile_empty = false;
+    if (in_bbox) {
+        /* one warp works the tile out (integer divisions, a square root), the others read it from shared memory */
+        __shared__ int s_tile[3];
+        if (threadIdx.x < 32) {
+            int state = tile_of_block(p, blockIdx.x, tx, ty) ? 1 : 0;
+            /* empty-space skipping in screen space: no ray of this tile meets an occupied cell (volume.cu k_tile_mask) --
+             * every sample would have alpha 0, the pixels are the clear colour: no ray is set up at all */
+            if (state && ESS && !STATS && p.tile_mask) {
+                const uint32_t t = (uint32_t)ty * p.ntx + (uint32_t)tx;
+                if (!((__ldg(p.tile_mask + (t >> 5)) >> (t & 31u)) & 1u) && __ldg(p.tile_mask + p.mask_words) == 0u) state = 2;
+            }
+            if (threadIdx.x == 0) s_tile[0] = tx, s_tile[1] = ty, s_tile[2] = state;
         }
-        tx = p.sp_cx + ox, ty = p.sp_cy + oy;
-        if (tx < p.rect[0] || ty < p.rect[1] || tx >= p.rect[2] || ty >= p.rect[3]) return;
+        __syncthreads();
+        tx = s_tile[0], ty = s_tile[1];
+        if (s_tile[2] == 0) return;
+        tile_empty = s_tile[2] == 2;
     } else {
         /* clear colour only (offscreen_pass.cpp:170-173): a block clears a 64x32 pixel region in groups of
          * four pixels (one 16-byte store), leaving out the tiles the spiral blocks own */
@@ -555,9 +586,9 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
     const size_t pix = (size_t)py * p.W + px;
 
     Entry e;
-    const bool covered = valid && pixel_entry(p, px, py, e);
+    const bool covered = !tile_empty && valid && pixel_entry(p, px, py, e);
 
-    if (!__syncthreads_or(covered)) {
+    if (tile_empty || !__syncthreads_or(covered)) {
         /* nothing to march in this tile: clear colour only (offscreen_pass.cpp:170-173) */
         if (valid) {
             const unsigned char c = (unsigned char)(VR_CLEAR_RGB * 255.0f + 0.5f);

@@ -466,6 +466,109 @@ cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const flo
     return cudaGetLastError();
 }
 
+/* ---- screen-space mask of the tiles whose rays can meet an occupied cell -------------------------------------
+ *   With a sparse volume most rays inside the cube's screen box cross empty cells only: their
+ * pixels are the clear colour, and the ray set-up (an unprojection, a slab test, three reciprocals, a normalisation:
+ * about a third of config 3's instructions) is spent for nothing.  Once per LUT / volume change the occupied cells
+ * are gathered into a list; once per frame every listed cell is projected (its eight corners through proj * view)
+ * and the CTA tiles under its screen bounding box are marked.  A sample contributes only if it is POSITIONED in an
+ * occupied cell (k_classify), and a pixel whose ray passes through a cell lies inside the projection of that cell,
+ * so an unmarked tile is the clear colour exactly: K1 stores it without setting a ray up. */
+__global__ void __launch_bounds__(256) k_list_occupied(const uint32_t *__restrict__ occ, int ncells, uint32_t *list, uint32_t *count)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool on = c < ncells && ((occ[c >> 5] >> (c & 31)) & 1u);
+    const uint32_t m = __ballot_sync(0xffffffffu, on);
+    uint32_t base = 0;
+    if ((threadIdx.x & 31) == 0 && m) base = atomicAdd(count, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (on) list[base + __popc(m & ((1u << (threadIdx.x & 31)) - 1u))] = (uint32_t)c;
+}
+
+struct TileMaskParams {
+    /* clip-space x, y, w of cell (0,0,0)'s low corner and their increments per cell along each axis: the eight
+     * corners of a cell are sums of these (proj * view is affine in the model position) */
+    float h0[3], ax[3], ay[3], az[3];
+    int cnx, cny;
+    uint32_t W, H, ntx, tile_h, words;
+    uint32_t *mask; /* words + 1: the bits, then a flag set when a cell cannot be projected (behind the eye): K1 ignores the mask */
+    uint32_t *wipe; /* the slot's other buffer, read by the frame before: zeroed here for the frame after */
+};
+
+__global__ void __launch_bounds__(256) k_tile_mask(const __grid_constant__ TileMaskParams p, const uint32_t *__restrict__ list,
+                                                   const uint32_t *__restrict__ count)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint32_t w = i; w <= p.words; w += gridDim.x * blockDim.x) p.wipe[w] = 0u;
+    if (i >= *count) return;
+    const int c = (int)list[i];
+    const int cx = c % p.cnx, cy = (c / p.cnx) % p.cny, cz = c / (p.cnx * p.cny);
+    const float fx = (float)cx, fy = (float)cy, fz = (float)cz;
+    float b[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) b[k] = fmaf(fz, p.az[k], fmaf(fy, p.ay[k], fmaf(fx, p.ax[k], p.h0[k])));
+    float x0 = 1e30f, y0 = 1e30f, x1 = -1e30f, y1 = -1e30f, wmin = 1e30f;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const float hx = b[0] + ((k & 1) ? p.ax[0] : 0.f) + ((k & 2) ? p.ay[0] : 0.f) + ((k & 4) ? p.az[0] : 0.f);
+        const float hy = b[1] + ((k & 1) ? p.ax[1] : 0.f) + ((k & 2) ? p.ay[1] : 0.f) + ((k & 4) ? p.az[1] : 0.f);
+        const float hw = b[2] + ((k & 1) ? p.ax[2] : 0.f) + ((k & 2) ? p.ay[2] : 0.f) + ((k & 4) ? p.az[2] : 0.f);
+        const float iw = __frcp_rn(hw); /* the bounds below carry a pixel and a half of slack */
+        const float sx = hx * iw, sy = hy * iw;
+        wmin = fminf(wmin, hw);
+        x0 = fminf(x0, sx), x1 = fmaxf(x1, sx), y0 = fminf(y0, sy), y1 = fmaxf(y1, sy);
+    }
+    if (!(wmin > 1e-4f) || !(x0 == x0) || !(x1 == x1) || !(y0 == y0) || !(y1 == y1)) {
+        p.mask[p.words] = 1u;
+        return;
+    }
+    /* NDC -> pixels; pixel centres inside [lo - 1.5, hi + 1.5) */
+    const float hwid = 0.5f * (float)p.W, hhgt = 0.5f * (float)p.H;
+    const int px0 = max((int)floorf(fmaf(x0, hwid, hwid) - 1.5f), 0), px1 = min((int)ceilf(fmaf(x1, hwid, hwid) + 1.5f), (int)p.W - 1);
+    const int py0 = max((int)floorf(fmaf(y0, hhgt, hhgt) - 1.5f), 0), py1 = min((int)ceilf(fmaf(y1, hhgt, hhgt) + 1.5f), (int)p.H - 1);
+    if (px1 < px0 || py1 < py0) return;
+    const int tx0 = px0 / VR_TILE, tx1 = px1 / VR_TILE, ty0 = py0 / (int)p.tile_h, ty1 = py1 / (int)p.tile_h;
+    for (int ty = ty0; ty <= ty1; ty++) {
+        /* the tiles of one row are consecutive bits: whole words at a time */
+        const uint32_t b0 = (uint32_t)ty * p.ntx + (uint32_t)tx0, b1 = (uint32_t)ty * p.ntx + (uint32_t)tx1;
+        for (uint32_t w = b0 >> 5; w <= (b1 >> 5); w++) {
+            const uint32_t lo_bit = w == (b0 >> 5) ? (b0 & 31u) : 0u, hi_bit = w == (b1 >> 5) ? (b1 & 31u) : 31u;
+            const uint32_t bits = (hi_bit == 31u ? 0xffffffffu : ((1u << (hi_bit + 1u)) - 1u)) & ~((1u << lo_bit) - 1u);
+            /* cells of one list neighbourhood fall into the same tiles: most find their bits set already (a stale
+             * read only costs a redundant atomic) */
+            if ((__ldcg(p.mask + w) & bits) != bits) atomicOr(&p.mask[w], bits);
+        }
+    }
+}
+
+cudaError_t vr_k0_list_occupied(const uint32_t *d_occ, const int occ_n[3], uint32_t *d_list, uint32_t *d_count, cudaStream_t s)
+{
+    const int n = occ_n[0] * occ_n[1] * occ_n[2];
+    cudaError_t e = cudaMemsetAsync(d_count, 0, sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    k_list_occupied<<<(n + 255) / 256, 256, 0, s>>>(d_occ, n, d_list, d_count);
+    return cudaGetLastError();
+}
+
+cudaError_t vr_k0_tile_mask(const float pv[16], const float lo[3], const float cell[3], const int occ_n[3], const uint32_t *d_list,
+                            const uint32_t *d_count, uint32_t max_count, uint32_t W, uint32_t H, uint32_t ntx, uint32_t tile_h,
+                            uint32_t *d_mask, uint32_t *d_wipe, uint32_t mask_words, cudaStream_t s)
+{
+    TileMaskParams p;
+    const int row[3] = {0, 1, 3}; /* clip x, y, w */
+    for (int k = 0; k < 3; k++) {
+        const int r = row[k];
+        p.h0[k] = pv[r] * lo[0] + pv[4 + r] * lo[1] + pv[8 + r] * lo[2] + pv[12 + r];
+        p.ax[k] = pv[r] * cell[0], p.ay[k] = pv[4 + r] * cell[1], p.az[k] = pv[8 + r] * cell[2];
+    }
+    p.cnx = occ_n[0], p.cny = occ_n[1], p.W = W, p.H = H, p.ntx = ntx, p.tile_h = tile_h, p.words = mask_words;
+    p.mask = d_mask, p.wipe = d_wipe;
+    /* one thread per occupied cell (the host knows how many since the classification), and at least the threads the wipe needs */
+    const uint32_t threads = max_count > mask_words + 1 ? max_count : mask_words + 1;
+    k_tile_mask<<<(threads + 255u) / 256u, 256, 0, s>>>(p, d_list, d_count);
+    return cudaGetLastError();
+}
+
 cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, uint32_t *d_sat,
                            cudaStream_t s)
 {

@@ -72,6 +72,9 @@ struct MarchParams {
     int occ_stride[3]; /* distance-map index = sum c[a] * occ_stride[a] (sampling-space order) */
     int occ_words;
     float occ_scale[3], occ_off[3]; /* cell = int(pos * occ_scale - occ_off) */
+    const uint32_t *tile_mask; /* bit per CTA tile (ty * ntx + tx): 0 = no ray of the tile meets an occupied cell; word [mask_words] != 0:
+                                * ignore the mask; nullptr = no mask this frame (volume.cu k_tile_mask) */
+    uint32_t mask_words;
     const unsigned char *dist; /* 8 maps (one per direction octant) x cells: edge of the largest empty cube with the cell at
                                 * its corner, extending along the octant; 0 = occupied (volume.cu k_octant_distance) */
     uint32_t occ_oct[3];       /* offset of the octant's map contributed by a negative direction on sampling axis a */
@@ -187,6 +190,15 @@ struct vr_ctx {
     uint64_t host_target_clock = 0;
     bool bench_fetch_only = false;   /* vr_bench_fetch_only: frames run the fetch-only build of K1 */
     uint32_t *d_sat = nullptr;       /* summed-volume table of the occupancy bits, (n+1)^3 */
+    uint32_t *d_occ_list = nullptr;  /* indices of the occupied cells, + their count in d_occ_count */
+    uint32_t *d_occ_count = nullptr;
+    /* per frame slot two buffers of mask_words + 1 words, used in turn: the kernel that fills one zeroes the other */
+    uint32_t *d_tile_mask[VR_MAX_FRAMES_IN_FLIGHT] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t tile_mask_cur[VR_MAX_FRAMES_IN_FLIGHT] = {0, 0, 0, 0};
+    uint32_t tile_mask_words = 0;
+    bool slot_mask_valid[VR_MAX_FRAMES_IN_FLIGHT] = {false, false, false, false};
+    uint32_t slot_mask_shape[VR_MAX_FRAMES_IN_FLIGHT][3] = {}; /* tiles in x, tiles in y, tile height of the frame recorded last */
+    int tune_tile_mask = 1;          /* VR_TILE_MASK=0: no screen-space mask */
     bool occ_dirty = true;
     uint64_t occ_empty_cells = 0;
 
@@ -212,6 +224,11 @@ cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const flo
                            unsigned long long *d_empty_count, cudaStream_t s);
 cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, uint32_t *d_sat,
                            cudaStream_t s);
+/* list of the occupied cells (after k_classify); per frame: the CTA tiles whose rays can meet one of them */
+cudaError_t vr_k0_list_occupied(const uint32_t *d_occ, const int occ_n[3], uint32_t *d_list, uint32_t *d_count, cudaStream_t s);
+cudaError_t vr_k0_tile_mask(const float pv[16], const float lo[3], const float cell[3], const int occ_n[3], const uint32_t *d_list,
+                            const uint32_t *d_count, uint32_t max_count, uint32_t W, uint32_t H, uint32_t ntx, uint32_t tile_h,
+                            uint32_t *d_mask, uint32_t *d_wipe, uint32_t mask_words, cudaStream_t s);
 /* fill the layered array paired along `axis` (n_axis + 1 layers) from the linear volume; dtype u8 or u16 */
 cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int axis,
                              cudaArray_t pair_array, cudaArray_t pair_array_hi, int split, cudaStream_t s);
