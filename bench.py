@@ -337,6 +337,16 @@ def run_ours(args):
     else:
         all_ref, all_exec = float(total_ref), float(total_exec)
 
+    # screen-space tile mask (skipping active, no statistics): one more launch of ours per frame, ahead of K1
+    mask = op.tile_mask(0)
+    mask_info = None
+    if mask is not None:
+        bits, ignored, th = mask
+        x0, y0, x1, y1 = op.last_frame_info().bbox
+        inside = bits[y0 // th:(y1 + th - 1) // th, x0 // 16:(x1 + 15) // 16]
+        mask_info = {"tiles_in_screen_box": int(inside.size), "tiles_marched": int(inside.sum()), "ignored": bool(ignored),
+                     "what": "k_tile_mask projects the occupied cells ahead of K1; unmarked tiles get the clear colour without ray set-up (last frame of the run)"}
+    launches_per_step = 2 if mask is not None else 1
     line = None
     if rank == 0:
         peaks = load_peaks()
@@ -363,7 +373,8 @@ def run_ours(args):
             "config": {"workload": f"{args.workload}: {desc}", "volume_dtype": dname, "kernel_version": vr.KERNEL_VERSION,
                        "sampler": "exact(8 point fetches + fp32 lerp)" if args.exact else "hw trilinear",
                        "empty_space_skipping": {"requested": bool(prod["empty_skip"]), "active": bool(ess_active),
-                                                "why": "the context consults the occupancy grid only when >= 25 % of the cells are empty"},
+                                                "why": "the context consults the occupancy grid only when >= 25 % of the cells are empty",
+                                                "screen_space_mask": mask_info},
                        "early_ray_termination_eps": prod["early_term_eps"] if prod["early_term"] else 0,
                        "l2": f"inputs larger than L2 ({n ** 3 * esz / 2 ** 20:.0f} MiB volume, no flush)",
                        "frames_in_flight": F,
@@ -396,7 +407,7 @@ def run_ours(args):
                     "ms_per_step": e2e_ms / (K * e2e_reps), "ms_per_step_full_frame_every_step": e2e_full_ms / (K * e2e_reps),
                     "value_full_frame_every_step": all_ref * e2e_reps / (e2e_full_ms * 1e-3), "fps": world * K * e2e_reps / (e2e_ms * 1e-3),
                     "reps": e2e_reps, "frame_checksum": checksum},
-            "gpu_launches": K * reps,
+            "gpu_launches": K * reps * launches_per_step,
             "clocks": clocks.result(),
             "occupancy": {"cells": list(cells), "cell_voxels": cell_vox, "empty_cells": int(empty)},
         }
@@ -702,7 +713,8 @@ def partitioned_record(vr, rank, world, local, args):
         rec["c4"] = c4
         n1_4k = c4["alone_ms_per_step"].get("3840x2160")
         if world > 1 and time_left() > 150:
-            c5s = measure_partitioned(vr, "last", rank, world, local, n, 3840, 2160, K, Wu, ess=int(not args.no_ess), ert=int(not args.no_ert))
+            c5s = measure_partitioned(vr, "last", rank, world, local, n, 3840, 2160, K, Wu, ess=int(not args.no_ess), ert=int(not args.no_ert),
+                                      slots=args.slots_last)
             c5s["n1_ms_per_step"] = n1_4k
             c5s["efficiency"] = (n1_4k / (world * c5s["ms_per_step"])) if n1_4k else None
             c5s["workload"] = f"sort-last on a volume that fits one GPU: {n}^3 u16 fBm in {world} sub-boxes, 3840x2160, direct-send merge over NVLink, 36-frame orbit"
@@ -712,7 +724,7 @@ def partitioned_record(vr, rank, world, local, args):
                                      "workload": f"{n}^3 u16 fBm, 3840x2160 on one GPU (the denominator of the sort-last curve)"}
         if world == 8 and not args.size and time_left() > 200:
             c5 = measure_partitioned(vr, "last", rank, world, local, 4096, 3840, 2160, K, Wu, synth=(vr.SYNTH_BLOBS_FBM, 0x5EED0005), tf="C",
-                                     ess=int(not args.no_ess), ert=int(not args.no_ert))
+                                     ess=int(not args.no_ess), ert=int(not args.no_ert), slots=args.slots_last)
             c5["workload"] = "c5: 4096^3 u16 blobs+fBm (128 GiB) in 2x2x2 sub-boxes, TF-C, 3840x2160, sort-last direct-send, 36-frame orbit"
             rec["c5"] = c5
     except Exception as e:  # the C2 line must survive a failure of the extra measurements
@@ -743,7 +755,7 @@ def run_partitioned(args):
     m = measure_partitioned(vr, "first" if c4 else "last", rank, world, local, n, W, H, K, Wu,
                             synth=(vr.SYNTH_FBM, 0x5EED0004 if c4 else 0x5EED0005) if dense else (vr.SYNTH_BLOBS_FBM, 0x5EED0005),
                             tf="B" if dense else "C", ess=int(not args.no_ess), ert=int(not args.no_ert), tile_px=args.tile_px,
-                            slots=args.slots, merge=args.merge, alone_sizes=((W, H),) if (c4 and args.alone) else ())
+                            slots=args.slots if c4 else args.slots_last, merge=args.merge, alone_sizes=((W, H),) if (c4 and args.alone) else ())
     if rank == 0:
         peaks = load_peaks()
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
@@ -789,6 +801,7 @@ def main():
     ap.add_argument("--size", type=int, default=0, help="c4/c5 and the partitioned record: volume edge override")
     ap.add_argument("--frame", default="", help="c4/c5: WxH override")
     ap.add_argument("--tile-px", type=int, default=64, help="c4: sort-first partition tile edge in pixels")
+    ap.add_argument("--slots-last", type=int, default=4, help="sort-last: raw/image slots per rank (frames a rank may run ahead of the merge)")
     ap.add_argument("--slots", type=int, default=2, help="c4: image slots on the display rank (frames a rank may run ahead)")
     ap.add_argument("--full-download", action="store_true", help="e2e: copy the whole frame to the host every step")
     ap.add_argument("--merge", choices=["p2p", "nccl"], default="p2p", help="c5: peer-memory merge or NCCL exchange")

@@ -232,3 +232,21 @@ def test_cpp_host_mirror_renders_the_same_frames(vr, tmp_path):
     assert ppm.startswith(b"P6\n160 120\n255\n")
     body = np.frombuffer(ppm[len(b"P6\n160 120\n255\n"):], np.uint8).reshape(H, W, 3)
     assert np.array_equal(body, img[..., :3])
+
+
+@pytest.mark.parametrize("mode", ["sort_first", "sort_last"])
+def test_cpp_group_mirror_matches_one_gpu(vr, mode):
+    """host/example_group (C++ VolB200::Rendering::PassGroup over vr_create_group): the group's frames against a single
+    pass in the same program -- identical for sort-first, within one 8-bit level for sort-last."""
+    exe = os.path.join(ROOT, "volumetric-renderer_b200", "host", "example_group")
+    if not os.path.exists(exe):
+        pytest.skip("example_group not built")
+    devs = _group_devices(3)
+    r = subprocess.run([exe, mode, "200", "144", "48", "3"] + [str(d) for d in devs], capture_output=True, text=True, timeout=180)
+    assert r.returncode == 0, r.stderr
+    f = dict(kv.split("=") for kv in r.stdout.split())
+    assert int(f["ranks"]) == 3 and int(f["frames"]) == 3
+    if mode == "sort_first":
+        assert f["checksum_group"] == f["checksum_single"] and int(f["max_abs_diff"]) == 0
+    else:
+        assert int(f["max_abs_diff"]) <= 1

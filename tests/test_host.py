@@ -510,9 +510,9 @@ def test_cpp_mirror_builds_and_fails_loudly_without_a_device(vr):
     import subprocess
     import torch
     pkg = os.path.join(ROOT, "volumetric-renderer_b200")
-    subprocess.run(["make", "-s", "-C", pkg, os.path.join(pkg, "host", "example_orbit")], check=True)
+    subprocess.run(["make", "-s", "-C", pkg, os.path.join(pkg, "host", "example_orbit"), os.path.join(pkg, "host", "example_group")], check=True)
     exe = os.path.join(pkg, "host", "example_orbit")
-    assert os.path.exists(exe)
+    assert os.path.exists(exe) and os.path.exists(os.path.join(pkg, "host", "example_group"))
     if not torch.cuda.is_available():
         r = subprocess.run([exe, "/tmp/_vr_none.ppm", "32", "32", "8", "1"], capture_output=True, text=True)
         assert r.returncode == 1 and "no CPU fallback" in r.stderr

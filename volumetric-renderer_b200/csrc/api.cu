@@ -171,6 +171,8 @@ void release_volume(vr_ctx *c)
     if (c->d_cell_range) cudaFree(c->d_cell_range), c->d_cell_range = nullptr;
     if (c->d_occ) cudaFree(c->d_occ), c->d_occ = nullptr;
     if (c->d_dist) cudaFree(c->d_dist), c->d_dist = nullptr;
+    if (c->dist_tex) cudaDestroyTextureObject(c->dist_tex), c->dist_tex = 0;
+    if (c->dist_array) cudaFreeArray(c->dist_array), c->dist_array = nullptr;
     if (c->d_sat) cudaFree(c->d_sat), c->d_sat = nullptr;
     if (c->d_occ_list) cudaFree(c->d_occ_list), c->d_occ_list = nullptr;
     if (c->d_occ_count) cudaFree(c->d_occ_count), c->d_occ_count = nullptr;
@@ -330,6 +332,16 @@ int install_volume_unchecked(vr_ctx *c, const void *dev, int dtype, uint32_t nx,
     VR_CUDA(c, cudaMalloc(&c->d_cell_range, sizeof(float2) * ncells));
     VR_CUDA(c, cudaMalloc(&c->d_occ, sizeof(uint32_t) * c->occ_words));
     VR_CUDA(c, cudaMalloc(&c->d_dist, (size_t)ncells * 8));
+    {   /* occ_n <= tune_occ_max_axis (256 by default): far below the 16384 texels a 3-D array may be deep */
+        const cudaChannelFormatDesc fmt = cudaCreateChannelDesc<unsigned char>();
+        VR_CUDA(c, cudaMalloc3DArray(&c->dist_array, &fmt, make_cudaExtent((size_t)c->occ_n[0], (size_t)c->occ_n[1], (size_t)c->occ_n[2] * 8)));
+        cudaResourceDesc rd{};
+        rd.resType = cudaResourceTypeArray, rd.res.array.array = c->dist_array;
+        cudaTextureDesc td{};
+        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint, td.readMode = cudaReadModeNormalizedFloat, td.normalizedCoords = 0;
+        VR_CUDA(c, cudaCreateTextureObject(&c->dist_tex, &rd, &td, nullptr));
+    }
     VR_CUDA(c, cudaMalloc(&c->d_sat, sizeof(uint32_t) * (size_t)(c->occ_n[0] + 1) * (c->occ_n[1] + 1) * (c->occ_n[2] + 1)));
     VR_CUDA(c, cudaMalloc(&c->d_occ_list, sizeof(uint32_t) * (size_t)ncells));
     VR_CUDA(c, cudaMalloc(&c->d_occ_count, sizeof(uint32_t)));
@@ -396,7 +408,9 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     c->opt.early_term_eps = 1.0f / 1024.0f;
     c->opt.collect_stats = 0;
     c->opt.write_raw = 0;
-    if (const char *e = std::getenv("VR_BATCH")) c->tune_batch = std::atoi(e);
+    if (const char *e = std::getenv("VR_BATCH")) c->tune_batch = c->tune_batch_ess = std::atoi(e);
+    if (const char *e = std::getenv("VR_BATCH_ESS")) c->tune_batch_ess = std::atoi(e);
+    if (const char *e = std::getenv("VR_ESS_GUARD")) c->tune_ess_guard = std::max(1, std::atoi(e));
     if (const char *e = std::getenv("VR_ESS_MIN_EMPTY")) c->tune_ess_min_empty = (float)std::atof(e);
     if (const char *e = std::getenv("VR_CTA_THREADS")) c->tune_threads = std::atoi(e) == 256 ? 256 : 128;
     if (const char *e = std::getenv("VR_BBOX")) c->tune_bbox = std::atoi(e);
@@ -666,6 +680,14 @@ int prepare_occupancy(vr_ctx *c, cudaStream_t s)
     VR_CUDA(c, vr_k0_classify(c->d_cell_range, c->occ_n, c->d_lut_pad, c->nlut, c->min_density, c->max_density, c->d_occ,
                               c->occ_words, c->d_counters + 4, s));
     VR_CUDA(c, vr_k0_distance(c->d_occ, c->occ_n, c->d_dist, c->d_sat, s));
+    if (c->dist_array) {
+        cudaMemcpy3DParms cp{};
+        cp.srcPtr = make_cudaPitchedPtr(c->d_dist, (size_t)c->occ_n[0], (size_t)c->occ_n[0], (size_t)c->occ_n[1]);
+        cp.dstArray = c->dist_array;
+        cp.extent = make_cudaExtent((size_t)c->occ_n[0], (size_t)c->occ_n[1], (size_t)c->occ_n[2] * 8);
+        cp.kind = cudaMemcpyDeviceToDevice;
+        VR_CUDA(c, cudaMemcpy3DAsync(&cp, s));
+    }
     VR_CUDA(c, vr_k0_list_occupied(c->d_occ, c->occ_n, c->d_occ_list, c->d_occ_count, s));
     VR_CUDA(c, cudaMemcpyAsync(&c->h_counters[4], c->d_counters + 4, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     VR_CUDA(c, cudaStreamSynchronize(s));
@@ -777,7 +799,9 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis, const uint32_t 
         p.occ_f_hi[i] = (float)ldims[i] / (float)c->occ_cell;
         p.occ_scale[i] = (float)full / (float)c->occ_cell;
         p.occ_off[i] = (float)p.org[i] / (float)c->occ_cell;
+        p.occ_offh[i] = p.occ_off[i] + 0.5f;
     }
+    p.dist_tex = pair_axis >= 0 ? 0 : c->dist_tex; /* the paired layouts sample in permuted axes: they index the linear maps */
     p.dtype = c->dtype;
     p.dscale = c->dtype == VR_U8 ? 255.0f : (c->dtype == VR_U16 ? 65535.0f : 1.0f);
     p.lut_pad = c->d_lut_pad, p.lut_dif = c->d_lut_dif, p.lut_h = c->d_lut_h, p.nlut = c->nlut;
@@ -1037,7 +1061,7 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
         uint32_t *mask = c->d_tile_mask[frame_index] + (size_t)cur * (words + 1), *other = c->d_tile_mask[frame_index] + (size_t)(cur ^ 1u) * (words + 1);
         const uint64_t ncells = (uint64_t)c->occ_n[0] * c->occ_n[1] * c->occ_n[2];
         VR_CUDA(c, vr_k0_tile_mask(pv, lo, cell, c->occ_n, c->d_occ_list, c->d_occ_count, (uint32_t)(ncells - c->occ_empty_cells), c->W, c->H,
-                                   p.ntx, p.tile_h, mask, other, words, s));
+                                   p.ntx, p.tile_h, mask, other, words, c->tune_tile_mask != 2, s));
         c->tile_mask_cur[frame_index] = cur ^ 1u;
         p.tile_mask = mask, p.mask_words = words;
         c->slot_mask_valid[frame_index] = true;
@@ -1049,7 +1073,8 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
         VR_CUDA(c, vr_launch_march_probe(p, pair, c->tune_batch, c->tune_threads, s));
         return VR_OK;
     }
-    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, pair, c->tune_batch, c->tune_threads, s));
+    p.ess_guard = c->tune_ess_guard;
+    VR_CUDA(c, vr_launch_march(p, exact, ess, c->opt.collect_stats != 0, c->sort_last, pair, ess ? c->tune_batch_ess : c->tune_batch, c->tune_threads, s));
     if (c->opt.collect_stats)
         VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     return VR_OK;

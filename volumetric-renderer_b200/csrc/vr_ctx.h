@@ -72,6 +72,9 @@ struct MarchParams {
     int occ_stride[3]; /* distance-map index = sum c[a] * occ_stride[a] (sampling-space order) */
     int occ_words;
     float occ_scale[3], occ_off[3]; /* cell = int(pos * occ_scale - occ_off) */
+    int ess_guard;             /* empty-space jumps a lane may take ahead of one batch */
+    cudaTextureObject_t dist_tex; /* the distance maps as a texture (octant o at z = o * occ_n[2] ..), 0 = none */
+    float occ_offh[3];         /* occ_off + 1/2 */
     const uint32_t *tile_mask; /* bit per CTA tile (ty * ntx + tx): 0 = no ray of the tile meets an occupied cell; word [mask_words] != 0:
                                 * ignore the mask; nullptr = no mask this frame (volume.cu k_tile_mask) */
     uint32_t mask_words;
@@ -155,6 +158,8 @@ struct vr_ctx {
     float4 *d_lut_pad = nullptr, *d_lut_dif = nullptr;
     uint4 *d_lut_h = nullptr;
     /* tuning knobs (environment: VR_BATCH, VR_CTA_THREADS, VR_BBOX, VR_WARP_W, VR_CARVEOUT, VR_ESS_MIN_EMPTY) */
+    int tune_batch_ess = 4;  /* steps per batch when the occupancy grid is consulted: one look-up per batch (march.cu skip_empty) */
+    int tune_ess_guard = 8;  /* jumps per batch at most */
     int tune_batch = 2, tune_threads = 128, tune_bbox = 1, tune_warp_w = 8, tune_carveout = -1;
     int tune_dirty_clear = 1; /* VR_DIRTY_CLEAR=0: restore the clear colour over the whole target every frame */
     int tune_pair_axis = -1;  /* VR_PAIR_AXIS: force the pair axis (experiments); -1 = the axis the camera looks down most */
@@ -169,6 +174,10 @@ struct vr_ctx {
     uint32_t *d_occ = nullptr;
     int occ_words = 0;
     unsigned char *d_dist = nullptr; /* 8 x cells */
+    /* the same eight maps stacked along z in a 3-D array (n0 x n1 x 8 n2), point-sampled: the look-up on the 3-D-array
+     * path is one texture instruction instead of an index computed in integer arithmetic */
+    cudaArray_t dist_array = nullptr;
+    cudaTextureObject_t dist_tex = 0;
     /* dirty-rectangle downloads (vr_download_frame_dirty_async): where each slot's last frame can differ from the
      * clear colour, and what each known host buffer holds */
     /* what each frame slot's target holds outside the tiles its last frame marched (dirty clear, vr_render_frame):
@@ -198,7 +207,7 @@ struct vr_ctx {
     uint32_t tile_mask_words = 0;
     bool slot_mask_valid[VR_MAX_FRAMES_IN_FLIGHT] = {false, false, false, false};
     uint32_t slot_mask_shape[VR_MAX_FRAMES_IN_FLIGHT][3] = {}; /* tiles in x, tiles in y, tile height of the frame recorded last */
-    int tune_tile_mask = 1;          /* VR_TILE_MASK=0: no screen-space mask */
+    int tune_tile_mask = 1;          /* VR_TILE_MASK=0: no screen-space mask; 2: marked in global memory directly (frames too large to stage) */
     bool occ_dirty = true;
     uint64_t occ_empty_cells = 0;
 
@@ -228,7 +237,7 @@ cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned c
 cudaError_t vr_k0_list_occupied(const uint32_t *d_occ, const int occ_n[3], uint32_t *d_list, uint32_t *d_count, cudaStream_t s);
 cudaError_t vr_k0_tile_mask(const float pv[16], const float lo[3], const float cell[3], const int occ_n[3], const uint32_t *d_list,
                             const uint32_t *d_count, uint32_t max_count, uint32_t W, uint32_t H, uint32_t ntx, uint32_t tile_h,
-                            uint32_t *d_mask, uint32_t *d_wipe, uint32_t mask_words, cudaStream_t s);
+                            uint32_t *d_mask, uint32_t *d_wipe, uint32_t mask_words, bool staged, cudaStream_t s);
 /* fill the layered array paired along `axis` (n_axis + 1 layers) from the linear volume; dtype u8 or u16 */
 cudaError_t vr_k0_pack_pairs(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int axis,
                              cudaArray_t pair_array, cudaArray_t pair_array_hi, int split, cudaStream_t s);

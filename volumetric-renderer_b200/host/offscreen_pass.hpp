@@ -191,5 +191,73 @@ class OffscreenPass
     }
     vr_ctx *ctx = nullptr;
 };
+
+// One pass spread over several GPUs of one process (include/vr.h, vr_create_group).  It stands where the
+// application constructs and records its single pass (src/rendering/vulkan_context.cpp:51, main_pass.cpp:91) and
+// keeps OffscreenPass's member names; mutators reach every device, record() enqueues one frame on all of them and
+// returns, the finished frame is the display rank's (rank 0) image.
+class PassGroup
+{
+  public:
+    PassGroup(const std::vector<int> &devices, vr_partition partition, uint32_t width, uint32_t height, uint32_t slots = 2) : w(width), h(height)
+    {
+        if (vr_create_group((uint32_t)devices.size(), devices.data(), partition, width, height, slots, &g) != VR_OK)
+            throw std::runtime_error(vr_group_last_error(nullptr));
+    }
+    ~PassGroup() { vr_group_destroy(g); }
+    PassGroup(const PassGroup &) = delete;
+    PassGroup &operator=(const PassGroup &) = delete;
+
+    uint32_t size() const { return vr_group_size(g); }
+    // record(command_buffer, frame_index): frames in flight are the group's own slots, taken in turn
+    void record(const Scene::Camera *camera = nullptr)
+    {
+        if (camera) {
+            mat4 view, proj;
+            vr_camera_get_view(camera->handle(), view.data());
+            vr_projection(w, h, proj.data());
+            set_uniforms(view, proj, camera->get_position());
+        }
+        check(vr_group_render(g));
+    }
+    void set_uniforms(const mat4 &view, const mat4 &proj, const vec3 &camera_position)
+    {
+        check(vr_group_set_camera(g, view.data(), proj.data(), camera_position.data()));
+    }
+    void volume_dataset_changed(Data::Dataset &dataset)
+    {
+        check(vr_group_set_volume(g, dataset.data.data(), VR_F32, dataset.dimensions[0], dataset.dimensions[1], dataset.dimensions[2],
+                                  &dataset.min, &dataset.max));
+    }
+    void volume_dataset_changed(const void *voxels, vr_dtype dtype, uint32_t nx, uint32_t ny, uint32_t nz)
+    {
+        check(vr_group_set_volume(g, voxels, dtype, nx, ny, nz, nullptr, nullptr));
+    }
+    void synth_volume(int kind, uint32_t seed, vr_dtype dtype, uint32_t n) { check(vr_group_synth_volume(g, kind, seed, dtype, n, n, n)); }
+    void slicing_changed(const vec3 &min, const vec3 &max) { check(vr_group_set_slicing(g, min.data(), max.data())); }
+    void transfer_function_changed(const std::vector<uint32_t> &data)
+    {
+        check(vr_group_set_transfer_function(g, data.data(), (uint32_t)data.size()));
+    }
+    void set_options(const vr_options &o) { check(vr_group_set_options(g, &o)); }
+    // the frame recorded last, complete (replicas: of `rank`)
+    std::vector<uint8_t> download(uint32_t rank = 0)
+    {
+        std::vector<uint8_t> img((size_t)w * h * 4);
+        check(vr_group_download(g, rank, img.data()));
+        return img;
+    }
+    void wait_idle() { check(vr_group_sync(g)); }
+    vr_ctx *context(uint32_t rank) { return vr_group_context(g, rank); }
+    vr_group *handle() { return g; }
+
+  private:
+    void check(int rc) const
+    {
+        if (rc != VR_OK) throw std::runtime_error(vr_group_last_error(g));
+    }
+    vr_group *g = nullptr;
+    uint32_t w, h;
+};
 }  // namespace Rendering
 }  // namespace VolB200
