@@ -10,3 +10,6 @@ d=json.loads(open("$O/bench_n$N.json").read().strip().splitlines()[-1])
 print("c2", d["n_gpus"], d["ms_per_step"], d["value"], "e2e", d["e2e"]["ms_per_step"], d["e2e"]["ms_per_step_full_frame_every_step"])
 print(json.dumps(d.get("partitioned"), indent=1)[:3000])
 PY
+# host-side picture for the full-frame D2H figure at N ranks
+( nvidia-smi topo -m; lscpu | grep -i "numa\|model name\|socket" ) > $O/topo_n$N.txt 2>&1
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29535 tools/exp_d2h.py > $O/exp_d2h_n$N.txt 2> $O/exp_d2h_n$N.err; tail -12 $O/exp_d2h_n$N.txt; tail -3 $O/exp_d2h_n$N.err

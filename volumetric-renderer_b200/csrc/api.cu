@@ -171,8 +171,6 @@ void release_volume(vr_ctx *c)
     if (c->d_cell_range) cudaFree(c->d_cell_range), c->d_cell_range = nullptr;
     if (c->d_occ) cudaFree(c->d_occ), c->d_occ = nullptr;
     if (c->d_dist) cudaFree(c->d_dist), c->d_dist = nullptr;
-    if (c->dist_tex) cudaDestroyTextureObject(c->dist_tex), c->dist_tex = 0;
-    if (c->dist_array) cudaFreeArray(c->dist_array), c->dist_array = nullptr;
     if (c->d_sat) cudaFree(c->d_sat), c->d_sat = nullptr;
     if (c->d_occ_list) cudaFree(c->d_occ_list), c->d_occ_list = nullptr;
     if (c->d_occ_count) cudaFree(c->d_occ_count), c->d_occ_count = nullptr;
@@ -332,16 +330,6 @@ int install_volume_unchecked(vr_ctx *c, const void *dev, int dtype, uint32_t nx,
     VR_CUDA(c, cudaMalloc(&c->d_cell_range, sizeof(float2) * ncells));
     VR_CUDA(c, cudaMalloc(&c->d_occ, sizeof(uint32_t) * c->occ_words));
     VR_CUDA(c, cudaMalloc(&c->d_dist, (size_t)ncells * 8));
-    {   /* occ_n <= tune_occ_max_axis (256 by default): far below the 16384 texels a 3-D array may be deep */
-        const cudaChannelFormatDesc fmt = cudaCreateChannelDesc<unsigned char>();
-        VR_CUDA(c, cudaMalloc3DArray(&c->dist_array, &fmt, make_cudaExtent((size_t)c->occ_n[0], (size_t)c->occ_n[1], (size_t)c->occ_n[2] * 8)));
-        cudaResourceDesc rd{};
-        rd.resType = cudaResourceTypeArray, rd.res.array.array = c->dist_array;
-        cudaTextureDesc td{};
-        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
-        td.filterMode = cudaFilterModePoint, td.readMode = cudaReadModeNormalizedFloat, td.normalizedCoords = 0;
-        VR_CUDA(c, cudaCreateTextureObject(&c->dist_tex, &rd, &td, nullptr));
-    }
     VR_CUDA(c, cudaMalloc(&c->d_sat, sizeof(uint32_t) * (size_t)(c->occ_n[0] + 1) * (c->occ_n[1] + 1) * (c->occ_n[2] + 1)));
     VR_CUDA(c, cudaMalloc(&c->d_occ_list, sizeof(uint32_t) * (size_t)ncells));
     VR_CUDA(c, cudaMalloc(&c->d_occ_count, sizeof(uint32_t)));
@@ -680,14 +668,6 @@ int prepare_occupancy(vr_ctx *c, cudaStream_t s)
     VR_CUDA(c, vr_k0_classify(c->d_cell_range, c->occ_n, c->d_lut_pad, c->nlut, c->min_density, c->max_density, c->d_occ,
                               c->occ_words, c->d_counters + 4, s));
     VR_CUDA(c, vr_k0_distance(c->d_occ, c->occ_n, c->d_dist, c->d_sat, s));
-    if (c->dist_array) {
-        cudaMemcpy3DParms cp{};
-        cp.srcPtr = make_cudaPitchedPtr(c->d_dist, (size_t)c->occ_n[0], (size_t)c->occ_n[0], (size_t)c->occ_n[1]);
-        cp.dstArray = c->dist_array;
-        cp.extent = make_cudaExtent((size_t)c->occ_n[0], (size_t)c->occ_n[1], (size_t)c->occ_n[2] * 8);
-        cp.kind = cudaMemcpyDeviceToDevice;
-        VR_CUDA(c, cudaMemcpy3DAsync(&cp, s));
-    }
     VR_CUDA(c, vr_k0_list_occupied(c->d_occ, c->occ_n, c->d_occ_list, c->d_occ_count, s));
     VR_CUDA(c, cudaMemcpyAsync(&c->h_counters[4], c->d_counters + 4, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     VR_CUDA(c, cudaStreamSynchronize(s));
@@ -801,7 +781,6 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis, const uint32_t 
         p.occ_off[i] = (float)p.org[i] / (float)c->occ_cell;
         p.occ_offh[i] = p.occ_off[i] + 0.5f;
     }
-    p.dist_tex = pair_axis >= 0 ? 0 : c->dist_tex; /* the paired layouts sample in permuted axes: they index the linear maps */
     p.dtype = c->dtype;
     p.dscale = c->dtype == VR_U8 ? 255.0f : (c->dtype == VR_U16 ? 65535.0f : 1.0f);
     p.lut_pad = c->d_lut_pad, p.lut_dif = c->d_lut_dif, p.lut_h = c->d_lut_h, p.nlut = c->nlut;
@@ -821,7 +800,7 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis, const uint32_t 
         permute3(p.dims, perm), permute3(p.org, perm), permute3(p.forg, perm), permute3(p.inv_ldims, perm);
         permute3(p.own_lo, perm), permute3(p.own_hi, perm), permute3(p.box_lo, perm), permute3(p.box_hi, perm);
         permute3(p.occ_n, perm), permute3(p.occ_stride, perm), permute3(p.occ_scale, perm), permute3(p.occ_off, perm);
-        permute3(p.occ_f_hi, perm), permute3(p.occ_oct, perm);
+        permute3(p.occ_f_hi, perm), permute3(p.occ_oct, perm), permute3(p.occ_offh, perm);
     }
     for (int i = 0; i < 2; i++) {
         p.pair_a[i] = p.dims[i] * p.inv_ldims[i];

@@ -31,9 +31,10 @@
 
 /* Blocks of 128 threads per SM the hardware-sampler build is compiled for: 5 x 256 threads = 10 blocks of 128
  * = 48 registers per thread (without the cap: 54 registers, 9 blocks). */
-/* 1: the 3-D-array path reads the distance maps through the texture unit (api.cu creates it with the occupancy grid) */
-#ifndef VR_DIST_TEX
-#define VR_DIST_TEX 1
+/* 1: the cell index of an empty-space look-up comes out of a magic-number addition instead of three float -> int and
+ * three int -> float conversions (skip_empty) */
+#ifndef VR_ESS_MAGIC
+#define VR_ESS_MAGIC 1
 #endif
 #ifndef VR_MIN_BLOCKS
 #define VR_MIN_BLOCKS 5
@@ -202,7 +203,6 @@ struct Ray {
     float ifx, ify, ifz;   /* ESS: 1 / (d * occ_scale): steps per cell, per axis (1e30 where d = 0) */
     float sgx, sgy, sgz;   /* ESS: sign of the direction, per axis */
     uint32_t doff;         /* ESS: offset of the distance map of the direction's octant */
-    float zoff;            /* ESS, 3-D array path: z of the ray's octant in the stacked distance texture + 1/2 */
     bool in_empty;         /* ESS, hardware sampler: the lane sits the coming batch out (skip_empty) */
     /* sort-last, hardware sampler: positions are a pure function of the step index, pos_i = e + i * d (one FMA),
      * so that every rank computes the same position for step i wherever it starts walking (see outer_interval) */
@@ -290,7 +290,7 @@ __device__ __forceinline__ void outer_interval(const MarchParams &p, const Ray &
  * filter) -- the exact sampler never jumps.  Jumps are taken only inside the ray's safe interval (see
  * safe_interval), where every position is inside the volume, the slices and the rank's own box: no
  * clipping of the cube, and every skipped step counts as visited for the statistics. */
-template <bool STATS, bool PART, bool DTEX>
+template <bool STATS, bool PART>
 __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fast_lo, int fast_hi)
 {
     /* One look-up per BATCH, here, not one per step (hardware sampler): the batch that follows samples all its
@@ -303,20 +303,21 @@ __device__ __forceinline__ void skip_empty(const MarchParams &p, Ray &r, int fas
     for (int guard = 0; guard < p.ess_guard; guard++) {
         /* outside the safe interval (the first and last steps of the ray, at a slicing plane): sample every step */
         if (r.i < fast_lo || r.i > fast_hi) return;
-        if (DTEX) {
-            /* 3-D array path: the maps are a point-sampled texture, octant o at z = o * n2.  g = position in cells - 1/2;
-             * (g + M) - M rounds it to the cell index (a position exactly on a face may land in either cell: both hold it).
-             * No float <-> integer conversion, no index arithmetic. */
+        if (VR_ESS_MAGIC) {
+            /* g = position in cells - 1/2; g + M rounds it to the cell index, held in the low mantissa bits (a position
+             * exactly on a face may land in either cell: both hold it) -- no float <-> integer conversion for the index.
+             * Inside the safe interval the position is strictly inside the grid: no clamp. */
             const float gx = fmaf(r.px, p.occ_scale[0], -p.occ_offh[0]), gy = fmaf(r.py, p.occ_scale[1], -p.occ_offh[1]),
                         gz = fmaf(r.pz, p.occ_scale[2], -p.occ_offh[2]);
-            const float cxf = (gx + VR_MAGIC) - VR_MAGIC, cyf = (gy + VR_MAGIC) - VR_MAGIC, czf = (gz + VR_MAGIC) - VR_MAGIC;
-            const float dn = tex3D<float>(p.dist_tex, cxf + 0.5f, cyf + 0.5f, czf + r.zoff); /* d / 255 */
-            if (dn == 0.0f) return;
+            const float mx = gx + VR_MAGIC, my = gy + VR_MAGIC, mz = gz + VR_MAGIC;
+            const int cx = __float_as_int(mx) - (int)VR_MAGIC_BITS, cy = __float_as_int(my) - (int)VR_MAGIC_BITS, cz = __float_as_int(mz) - (int)VR_MAGIC_BITS;
+            const int d = (int)__ldg(p.dist + r.doff + (cz * p.occ_stride[2] + cy * p.occ_stride[1] + cx * p.occ_stride[0]));
+            if (d == 0) return;
             /* as below: exit plane = cell centre +- (d - 1/2 - margin), and centre - position = c - g */
-            const float R = fmaf(dn, 255.0f, -(0.5f + 2.0e-3f));
-            const float tx = fmaf(r.sgx, R, cxf - gx) * r.ifx;
-            const float ty = fmaf(r.sgy, R, cyf - gy) * r.ify;
-            const float tz = fmaf(r.sgz, R, czf - gz) * r.ifz;
+            const float R = (float)d - (0.5f + 2.0e-3f);
+            const float tx = fmaf(r.sgx, R, (mx - VR_MAGIC) - gx) * r.ifx;
+            const float ty = fmaf(r.sgy, R, (my - VR_MAGIC) - gy) * r.ify;
+            const float tz = fmaf(r.sgz, R, (mz - VR_MAGIC) - gz) * r.ifz;
             int k = (int)fminf(fminf(fminf(tx, ty), tz), 65536.0f);
             k = min(max(k, 1), fast_hi - r.i + 1);
             r.i += k;
@@ -663,7 +664,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
     Ray ray;
     ray.cr = cr, ray.cg = cg, ray.cb = cb, ray.T = T;
     ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
-    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.sgx = ray.sgy = ray.sgz = 1.0f, ray.doff = 0u, ray.zoff = 0.5f, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
+    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.sgx = ray.sgy = ray.sgz = 1.0f, ray.doff = 0u, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
     ray.ex = posx, ray.ey = posy, ray.ez = posz, ray.fi = 0.0f, ray.i_end = p.steps - 1;
     if (PART && !EXACT && covered) {
@@ -696,15 +697,13 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
         ray.ifz = sz_ != 0.0f ? __frcp_rn(sz_) : 1.0e30f;
         ray.sgx = ray.ifx < 0.0f ? -1.0f : 1.0f, ray.sgy = ray.ify < 0.0f ? -1.0f : 1.0f, ray.sgz = ray.ifz < 0.0f ? -1.0f : 1.0f;
         ray.doff = (ray.ifx < 0.0f ? p.occ_oct[0] : 0u) + (ray.ify < 0.0f ? p.occ_oct[1] : 0u) + (ray.ifz < 0.0f ? p.occ_oct[2] : 0u);
-        if (PAIR == 0) /* the octant's map in the stacked texture, + 1/2 for the texel centre */
-            ray.zoff = (float)(((ray.ifx < 0.0f ? 1 : 0) + (ray.ify < 0.0f ? 2 : 0) + (ray.ifz < 0.0f ? 4 : 0)) * p.occ_n[2]) + 0.5f;
     }
     /* Warp-uniform choice per batch.  Checked: every test of volume.frag:34-40 is evaluated (always
      * correct).  Unchecked: every live lane is inside its safe interval; predicated if some lane is
      * finished or the occupancy grid is consulted, else no per-lane flag at all. */
 #define VR_ISSUE(B_)                                                                                        \
     do {                                                                                                    \
-        if (ESS && !EXACT) skip_empty<STATS, PART, PAIR == 0 && VR_DIST_TEX>(p, ray, fast_lo, fast_hi);                               \
+        if (ESS && !EXACT) skip_empty<STATS, PART>(p, ray, fast_lo, fast_hi);                               \
         const bool in_safe = ray.i >= fast_lo && ray.i + U - 1 <= fast_hi;                                  \
         if (!EXACT && !ESS && __all_sync(0xffffffffu, !ray.done && in_safe))                                \
             batch_issue<EXACT, ESS, STATS, PART, PAIR, U, false, false>(p, ray, B_);                        \

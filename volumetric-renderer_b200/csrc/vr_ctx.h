@@ -73,7 +73,6 @@ struct MarchParams {
     int occ_words;
     float occ_scale[3], occ_off[3]; /* cell = int(pos * occ_scale - occ_off) */
     int ess_guard;             /* empty-space jumps a lane may take ahead of one batch */
-    cudaTextureObject_t dist_tex; /* the distance maps as a texture (octant o at z = o * occ_n[2] ..), 0 = none */
     float occ_offh[3];         /* occ_off + 1/2 */
     const uint32_t *tile_mask; /* bit per CTA tile (ty * ntx + tx): 0 = no ray of the tile meets an occupied cell; word [mask_words] != 0:
                                 * ignore the mask; nullptr = no mask this frame (volume.cu k_tile_mask) */
@@ -174,10 +173,6 @@ struct vr_ctx {
     uint32_t *d_occ = nullptr;
     int occ_words = 0;
     unsigned char *d_dist = nullptr; /* 8 x cells */
-    /* the same eight maps stacked along z in a 3-D array (n0 x n1 x 8 n2), point-sampled: the look-up on the 3-D-array
-     * path is one texture instruction instead of an index computed in integer arithmetic */
-    cudaArray_t dist_array = nullptr;
-    cudaTextureObject_t dist_tex = 0;
     /* dirty-rectangle downloads (vr_download_frame_dirty_async): where each slot's last frame can differ from the
      * clear colour, and what each known host buffer holds */
     /* what each frame slot's target holds outside the tiles its last frame marched (dirty clear, vr_render_frame):
