@@ -10,8 +10,8 @@ try:
 except Exception as e: print("$L parse", e); print(open("gpurun_out/r2_c3_$L.err").read()[-800:])
 PY
 }
-run magic A=1
-run f2i VR_LIB_PATH=$PWD/tools/libvr_b200_f2i.so
-run magic2 A=1
-run f2i2 VR_LIB_PATH=$PWD/tools/libvr_b200_f2i.so
+run new A=1
+run prev VR_LIB_PATH=$PWD/tools/libvr_b200_prev.so
+run new2 A=1
+run prev2 VR_LIB_PATH=$PWD/tools/libvr_b200_prev.so
 timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_fullsize.py tests/test_gpu_partition.py -x -q 2>&1 | tail -3
