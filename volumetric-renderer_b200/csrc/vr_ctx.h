@@ -12,7 +12,7 @@
 
 #include "../../include/vr.h"
 
-#define VR_KERNEL_VERSION "r2.v9" /* bump when K1 changes: profiles/traffic.json is keyed by it */
+#define VR_KERNEL_VERSION "r2.v10" /* bump when K1 changes: profiles/traffic.json is keyed by it */
 #define VR_TILE 16        /* a CTA marches a 16x16 pixel tile: 8 warps of 8x4 pixels */
 #define VR_CTA_THREADS 256
 #define VR_BATCH 4        /* steps whose fetches are issued back to back before compositing */
