@@ -200,6 +200,16 @@ int vr_set_slicing(vr_ctx *ctx, const float min_slice[3], const float max_slice[
 /* OffscreenPass::transfer_function_changed(data) (offscreen_pass.cpp:279-288): n >= 1
  * texels packed R | G<<8 | B<<16 | A<<24, interpreted as VK_FORMAT_R8G8B8A8_SRGB (:1076). */
 int vr_set_transfer_function(vr_ctx *ctx, const uint32_t *rgba8_srgb, uint32_t n);
+/* The same with the texels already in device memory (no host round trip).  Either way the tables the march reads
+ * -- sRGB decode, edge padding, the fp16 table of the hardware sampler, the running alpha count the occupancy
+ * classification uses -- are built on the device (csrc/lut.cu). */
+int vr_set_transfer_function_device(vr_ctx *ctx, const void *dev_rgba8_srgb, uint32_t n);
+/* Gradient::discretize (src/ui/components/gradient.cpp:90-108) + transfer_function_changed in one call, the
+ * discretisation done on the device: the texels are bit-identical to vr_gradient_discretize's.  Markers as there:
+ * color_markers nc x {location, r, g, b}, alpha_markers na x {location, a}, sorted by location. */
+int vr_set_gradient(vr_ctx *ctx, const float *color_markers, uint32_t nc, const float *alpha_markers, uint32_t na, uint32_t count);
+/* The packed texels in use (rgba8_srgb may be NULL to query n). */
+int vr_get_transfer_function(vr_ctx *ctx, uint32_t *rgba8_srgb, uint32_t capacity, uint32_t *n);
 
 /* The two shader literals ray_dist = 1.8, step_size = 0.005 (res/shaders/volume.frag:29-30)
  * as parameters; steps = int(ray_dist / step_size) in fp32 (:31). */

@@ -822,3 +822,45 @@ def test_tile_mask_is_ignored_when_a_cell_is_behind_the_eye(vr, port):
         assert m is not None
     finally:
         op.close()
+
+
+def test_gradient_discretised_on_the_device_equals_the_host_one(vr, port):
+    """SURVEY 8(f).2: vr_set_gradient runs Gradient::discretize (gradient.cpp:90-108) on the device.  The texels must be
+    bit-identical to vr_gradient_discretize's (itself checked against the reference's own gradient.cpp in test_host.py),
+    for random marker sets incl. coincident locations and out-of-range values, and a frame rendered from them equal to
+    the frame rendered from the host-made table."""
+    rng = np.random.default_rng(11)
+    vol = small_volume(port, 1, np.uint16, 32)
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_options(sampler=vr.SAMPLER_EXACT, write_raw=1)
+        op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+        for trial in range(12):
+            nc, na = int(rng.integers(1, 7)), int(rng.integers(1, 7))
+            cl = np.sort(rng.random(nc)).astype(np.float32)
+            al = np.sort(rng.random(na)).astype(np.float32)
+            if trial % 4 == 3 and nc > 1:
+                cl[1] = cl[0]                     # two markers at one location
+            g = vr.Gradient([(float(l), tuple(float(x) for x in rng.uniform(-0.2, 1.2, 3))) for l in cl],
+                            [(float(l), float(rng.uniform(-0.2, 1.2))) for l in al])
+            count = int(rng.choice([1, 2, 7, 256, 1000]))
+            with np.errstate(all="ignore"):
+                want = g.discretize(count)
+            op.gradient_changed(g, count)
+            got = op.get_transfer_function()
+            assert np.array_equal(got, want), f"trial {trial}: {(got != want).sum()} of {count} texels differ"
+        g = vr.Gradient([(0.0, (0, 0, 0.5)), (0.5, (1, 0.5, 0)), (1.0, (1, 1, 1))], [(0.0, 0.0), (0.3, 0.0), (1.0, 0.08)])
+        op.gradient_changed(g, 256)
+        op.record()
+        a = op.download_raw()
+        op.transfer_function_changed(g.discretize(256))
+        op.record()
+        assert np.array_equal(a.view(np.uint32), op.download_raw().view(np.uint32))
+        # texels handed over in device memory
+        import torch
+        t = torch.from_numpy(g.discretize(256).view(np.int32)).cuda()
+        op.transfer_function_changed_device(t.data_ptr(), 256)
+        op.record()
+        assert np.array_equal(a.view(np.uint32), op.download_raw().view(np.uint32))
+    finally:
+        op.close()

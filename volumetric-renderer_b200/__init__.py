@@ -166,6 +166,24 @@ class OffscreenPass:
         d = np.ascontiguousarray(data, np.uint32)
         self._check(lib.vr_set_transfer_function(self._h, _ptr(d), len(d)))
 
+    def transfer_function_changed_device(self, dev_ptr: int, n: int):
+        """vr_set_transfer_function_device: n packed texels already in device memory."""
+        self._check(lib.vr_set_transfer_function_device(self._h, C.c_void_p(dev_ptr), n))
+
+    def gradient_changed(self, gradient: "Gradient", count: int = 256):
+        """vr_set_gradient: Gradient::discretize on the device + transfer_function_changed (what main_window.cpp:250-257
+        does on every edit of the gradient)."""
+        cm = np.ascontiguousarray([[loc, *rgb] for loc, rgb in gradient.color_markers], np.float32)
+        am = np.ascontiguousarray([[loc, a] for loc, a in gradient.alpha_markers], np.float32)
+        self._check(lib.vr_set_gradient(self._h, _ptr(cm), len(cm), _ptr(am), len(am), count))
+
+    def get_transfer_function(self) -> np.ndarray:
+        n = C.c_uint32(0)
+        self._check(lib.vr_get_transfer_function(self._h, None, 0, C.byref(n)))
+        out = np.zeros(n.value, np.uint32)
+        self._check(lib.vr_get_transfer_function(self._h, _ptr(out), n.value, None))
+        return out
+
     # ---- the implicit camera pull of update_uniform_buffer, made a push ------------------
     def set_camera(self, camera: Camera):
         self._check(lib.vr_set_camera_orbit(self._h, camera._h))

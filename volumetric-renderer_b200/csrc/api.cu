@@ -114,45 +114,38 @@ float srgb8_to_linear(unsigned c8)
     return (float)(c <= 0.04045 ? c / 12.92 : std::pow((c + 0.055) / 1.055, 2.4));
 }
 
+/* (Re)build everything the march reads of the transfer function from the packed texels in d_lut_rgba8 (lut.cu). */
 int upload_lut(vr_ctx *c)
 {
     const uint32_t n = c->nlut;
-    std::vector<float4> L(n), P(n + 3), D(n + 2);
-    for (uint32_t i = 0; i < n; i++) {
-        const uint32_t p = c->h_lut[i];
-        L[i] = make_float4(srgb8_to_linear(p & 0xff), srgb8_to_linear((p >> 8) & 0xff), srgb8_to_linear((p >> 16) & 0xff),
-                           (float)((p >> 24) & 0xff) / 255.0f);
+    if (c->lut_tables_cap < n) {
+        if (c->d_lut_pad) cudaFree(c->d_lut_pad), c->d_lut_pad = nullptr;
+        if (c->d_lut_dif) cudaFree(c->d_lut_dif), c->d_lut_dif = nullptr;
+        if (c->d_lut_h) cudaFree(c->d_lut_h), c->d_lut_h = nullptr;
+        if (c->d_lut_nz) cudaFree(c->d_lut_nz), c->d_lut_nz = nullptr;
+        c->lut_tables_cap = 0;
+        VR_CUDA(c, cudaMalloc(&c->d_lut_h, sizeof(uint4) * (n + 2)));
+        VR_CUDA(c, cudaMalloc(&c->d_lut_pad, sizeof(float4) * (n + 3)));
+        VR_CUDA(c, cudaMalloc(&c->d_lut_dif, sizeof(float4) * (n + 2)));
+        VR_CUDA(c, cudaMalloc(&c->d_lut_nz, sizeof(uint32_t) * (n + 4)));
+        c->lut_tables_cap = n;
     }
-    for (uint32_t k = 0; k < n + 3; k++) {
-        long j = (long)k - 1;
-        j = j < 0 ? 0 : (j > (long)n - 1 ? (long)n - 1 : j);
-        P[k] = L[j];
-    }
-    for (uint32_t k = 0; k < n + 2; k++)
-        D[k] = make_float4(P[k + 1].x - P[k].x, P[k + 1].y - P[k].y, P[k + 1].z - P[k].z, P[k + 1].w - P[k].w);
-    /* hardware-sampler table: one 16-byte entry {P[k] + D[k]/2, D[k]} of eight fp16 -> one LDS.128 per sample (march.cu: lut_eval) */
-    std::vector<uint4> Hh(n + 2);
-    for (uint32_t k = 0; k < n + 2; k++) {
-        const float e[8] = {P[k].x + 0.5f * D[k].x, P[k].y + 0.5f * D[k].y, P[k].z + 0.5f * D[k].z, P[k].w + 0.5f * D[k].w,
-                            D[k].x, D[k].y, D[k].z, D[k].w};
-        unsigned short hb[8];
-        for (int j = 0; j < 8; j++) {
-            const __half hv = __float2half_rn(e[j]);
-            std::memcpy(&hb[j], &hv, 2);
-        }
-        Hh[k] = make_uint4(hb[0] | ((uint32_t)hb[1] << 16), hb[2] | ((uint32_t)hb[3] << 16), hb[4] | ((uint32_t)hb[5] << 16),
-                           hb[6] | ((uint32_t)hb[7] << 16));
-    }
-    if (c->d_lut_pad) cudaFree(c->d_lut_pad), c->d_lut_pad = nullptr;
-    if (c->d_lut_dif) cudaFree(c->d_lut_dif), c->d_lut_dif = nullptr;
-    if (c->d_lut_h) cudaFree(c->d_lut_h), c->d_lut_h = nullptr;
-    VR_CUDA(c, cudaMalloc(&c->d_lut_h, sizeof(uint4) * (n + 2)));
-    VR_CUDA(c, cudaMemcpy(c->d_lut_h, Hh.data(), sizeof(uint4) * (n + 2), cudaMemcpyHostToDevice));
-    VR_CUDA(c, cudaMalloc(&c->d_lut_pad, sizeof(float4) * (n + 3)));
-    VR_CUDA(c, cudaMalloc(&c->d_lut_dif, sizeof(float4) * (n + 2)));
-    VR_CUDA(c, cudaMemcpy(c->d_lut_pad, P.data(), sizeof(float4) * (n + 3), cudaMemcpyHostToDevice));
-    VR_CUDA(c, cudaMemcpy(c->d_lut_dif, D.data(), sizeof(float4) * (n + 2), cudaMemcpyHostToDevice));
+    VR_CUDA(c, vr_lut_tables(c->d_lut_rgba8, n, c->d_lut_pad, c->d_lut_dif, c->d_lut_h, c->d_lut_nz, c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
     c->occ_dirty = true;
+    return VR_OK;
+}
+
+/* room for n packed texels (+ the texel centres of a device-side discretize) */
+int reserve_lut(vr_ctx *c, uint32_t n)
+{
+    if (c->lut_texels_cap >= n) return VR_OK;
+    if (c->d_lut_rgba8) cudaFree(c->d_lut_rgba8), c->d_lut_rgba8 = nullptr;
+    if (c->d_lut_loc) cudaFree(c->d_lut_loc), c->d_lut_loc = nullptr;
+    c->lut_texels_cap = 0;
+    VR_CUDA(c, cudaMalloc(&c->d_lut_rgba8, sizeof(uint32_t) * n));
+    VR_CUDA(c, cudaMalloc(&c->d_lut_loc, sizeof(float) * n));
+    c->lut_texels_cap = n;
     return VR_OK;
 }
 
@@ -353,9 +346,15 @@ int default_state(vr_ctx *c)
     cudaFree(d0);
     if (rc != VR_OK) return rc;
     c->nlut = 1;
-    c->h_lut = (uint32_t *)std::malloc(sizeof(uint32_t));
-    if (!c->h_lut) return fail(c, VR_ERR_NOMEM, "out of host memory");
-    c->h_lut[0] = 0xFFFFFFFFu;
+    {   /* the sRGB decode of the LUT image (offscreen_pass.cpp:1076) as a table, made with the oracle's arithmetic */
+        float table[256];
+        for (unsigned i = 0; i < 256; i++) table[i] = srgb8_to_linear(i);
+        VR_CUDA(c, vr_lut_upload_srgb_table(table));
+    }
+    rc = reserve_lut(c, 1);
+    if (rc != VR_OK) return rc;
+    const uint32_t white = 0xFFFFFFFFu;
+    VR_CUDA(c, cudaMemcpy(c->d_lut_rgba8, &white, sizeof(white), cudaMemcpyHostToDevice));
     rc = upload_lut(c);
     if (rc != VR_OK) return rc;
     vr_camera *cam = vr_camera_new();
@@ -447,6 +446,10 @@ extern "C" int vr_destroy(vr_ctx *c)
     if (c->d_lut_pad) cudaFree(c->d_lut_pad);
     if (c->d_lut_dif) cudaFree(c->d_lut_dif);
     if (c->d_lut_h) cudaFree(c->d_lut_h);
+    if (c->d_lut_nz) cudaFree(c->d_lut_nz);
+    if (c->d_lut_rgba8) cudaFree(c->d_lut_rgba8);
+    if (c->d_lut_loc) cudaFree(c->d_lut_loc);
+    if (c->d_markers) cudaFree(c->d_markers);
     if (c->d_image) cudaFree(c->d_image);
     if (c->d_raw) cudaFree(c->d_raw);
     for (int k = 1; k < VR_MAX_FRAMES_IN_FLIGHT; k++) {
@@ -459,7 +462,6 @@ extern "C" int vr_destroy(vr_ctx *c)
     if (c->d_flags) cudaFree(c->d_flags);
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->stream) cudaStreamDestroy(c->stream);
-    std::free(c->h_lut);
     delete c;
     return VR_OK;
 }
@@ -606,12 +608,59 @@ extern "C" int vr_set_transfer_function(vr_ctx *c, const uint32_t *rgba8, uint32
     if (n > 4096) return fail(c, VR_ERR_INVALID, "vr_set_transfer_function: at most 4096 texels (shared-memory staged)");
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaDeviceSynchronize()); /* wait_till_idle, offscreen_pass.cpp:282 */
-    uint32_t *copy = (uint32_t *)std::malloc(sizeof(uint32_t) * n);
-    if (!copy) return fail(c, VR_ERR_NOMEM, "out of host memory");
-    std::memcpy(copy, rgba8, sizeof(uint32_t) * n);
-    std::free(c->h_lut);
-    c->h_lut = copy, c->nlut = n;
+    const int rc = reserve_lut(c, n);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaMemcpy(c->d_lut_rgba8, rgba8, sizeof(uint32_t) * n, cudaMemcpyHostToDevice));
+    c->nlut = n;
     return upload_lut(c);
+}
+
+extern "C" int vr_set_transfer_function_device(vr_ctx *c, const void *dev_rgba8, uint32_t n)
+{
+    if (!c || !dev_rgba8 || n == 0) return fail(c, VR_ERR_INVALID, "vr_set_transfer_function_device: need n >= 1 texels");
+    if (n > 4096) return fail(c, VR_ERR_INVALID, "vr_set_transfer_function_device: at most 4096 texels (shared-memory staged)");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaDeviceSynchronize());
+    const int rc = reserve_lut(c, n);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaMemcpy(c->d_lut_rgba8, dev_rgba8, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice));
+    c->nlut = n;
+    return upload_lut(c);
+}
+
+extern "C" int vr_set_gradient(vr_ctx *c, const float *color_markers, uint32_t nc, const float *alpha_markers, uint32_t na, uint32_t count)
+{
+    if (!c || !color_markers || !alpha_markers || nc == 0 || na == 0 || count == 0)
+        return fail(c, VR_ERR_INVALID, "vr_set_gradient: need markers and count >= 1");
+    if (count > 4096) return fail(c, VR_ERR_INVALID, "vr_set_gradient: at most 4096 texels (shared-memory staged)");
+    if (nc > 4096 || na > 4096) return fail(c, VR_ERR_INVALID, "vr_set_gradient: at most 4096 markers of a kind");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaDeviceSynchronize());
+    int rc = reserve_lut(c, count);
+    if (rc != VR_OK) return rc;
+    const size_t need = (size_t)4 * nc + (size_t)2 * na;
+    if (c->markers_cap < need) {
+        if (c->d_markers) cudaFree(c->d_markers), c->d_markers = nullptr;
+        c->markers_cap = 0;
+        VR_CUDA(c, cudaMalloc(&c->d_markers, sizeof(float) * need));
+        c->markers_cap = need;
+    }
+    VR_CUDA(c, cudaMemcpy(c->d_markers, color_markers, sizeof(float) * 4 * nc, cudaMemcpyHostToDevice));
+    VR_CUDA(c, cudaMemcpy(c->d_markers + 4 * nc, alpha_markers, sizeof(float) * 2 * na, cudaMemcpyHostToDevice));
+    VR_CUDA(c, vr_lut_gradient(c->d_markers, nc, na, count, c->d_lut_loc, c->d_lut_rgba8, c->stream));
+    c->nlut = count;
+    return upload_lut(c);
+}
+
+extern "C" int vr_get_transfer_function(vr_ctx *c, uint32_t *rgba8, uint32_t capacity, uint32_t *n)
+{
+    if (!c) return VR_ERR_INVALID;
+    if (n) *n = c->nlut;
+    if (!rgba8) return VR_OK;
+    if (capacity < c->nlut) return fail(c, VR_ERR_INVALID, "vr_get_transfer_function: capacity below the texel count");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaMemcpy(rgba8, c->d_lut_rgba8, sizeof(uint32_t) * c->nlut, cudaMemcpyDeviceToHost));
+    return VR_OK;
 }
 
 extern "C" int vr_set_march(vr_ctx *c, float ray_dist, float step_size)
@@ -665,7 +714,7 @@ namespace
 int prepare_occupancy(vr_ctx *c, cudaStream_t s)
 {
     if (!c->occ_dirty) return VR_OK;
-    VR_CUDA(c, vr_k0_classify(c->d_cell_range, c->occ_n, c->d_lut_pad, c->nlut, c->min_density, c->max_density, c->d_occ,
+    VR_CUDA(c, vr_k0_classify(c->d_cell_range, c->occ_n, c->d_lut_nz, c->nlut, c->min_density, c->max_density, c->d_occ,
                               c->occ_words, c->d_counters + 4, s));
     VR_CUDA(c, vr_k0_distance(c->d_occ, c->occ_n, c->d_dist, c->d_sat, s));
     VR_CUDA(c, vr_k0_list_occupied(c->d_occ, c->occ_n, c->d_occ_list, c->d_occ_count, s));

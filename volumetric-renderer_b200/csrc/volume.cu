@@ -128,7 +128,7 @@ __device__ __forceinline__ int lut_tap(float v, float min_density, float range, 
  * so volume.frag:44-45 leaves colour and transmittance unchanged -- skipping is exact.
  * The tap range is widened by one texel each side for the HW path's fused coordinate. */
 __global__ void __launch_bounds__(256) k_classify(const float2 *__restrict__ ranges, int ncells,
-                                                  const float4 *__restrict__ lut_pad, int nlut, float min_density,
+                                                  const uint32_t *__restrict__ lut_nz, int nlut, float min_density,
                                                   float max_density, uint32_t *occ, unsigned long long *empty_count)
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -141,12 +141,8 @@ __global__ void __launch_bounds__(256) k_classify(const float2 *__restrict__ ran
             int k0 = lut_tap(r.x, min_density, range, (float)nlut) - 1;
             int k1 = lut_tap(r.y, min_density, range, (float)nlut) + 2;
             k0 = max(k0, 0), k1 = min(k1, nlut + 2);
-            occupied = false;
-            for (int k = k0; k <= k1; k++)
-                if (lut_pad[k].w != 0.0f) {
-                    occupied = true;
-                    break;
-                }
+            /* padded texels k0..k1 with alpha != 0: two reads of the running count (lut.cu k_lut_tables) */
+            occupied = lut_nz[k1 + 1] != lut_nz[k0];
         }
     }
     const uint32_t word = __ballot_sync(0xffffffffu, occupied);
@@ -453,7 +449,7 @@ cudaError_t vr_k0_cell_ranges(const void *dev, int dtype, uint32_t nx, uint32_t 
     return cudaGetLastError();
 }
 
-cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const float4 *d_lut_pad, uint32_t nlut,
+cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const uint32_t *d_lut_nz, uint32_t nlut,
                            float min_density, float max_density, uint32_t *d_occ, int occ_words,
                            unsigned long long *d_empty_count, cudaStream_t s)
 {
@@ -461,7 +457,7 @@ cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const flo
     cudaError_t e = cudaMemsetAsync(d_empty_count, 0, sizeof(unsigned long long), s);
     if (e != cudaSuccess) return e;
     const int threads = occ_words * 32;
-    k_classify<<<(threads + 255) / 256, 256, 0, s>>>(d_ranges, ncells, d_lut_pad, (int)nlut, min_density, max_density,
+    k_classify<<<(threads + 255) / 256, 256, 0, s>>>(d_ranges, ncells, d_lut_nz, (int)nlut, min_density, max_density,
                                                      d_occ, d_empty_count);
     return cudaGetLastError();
 }

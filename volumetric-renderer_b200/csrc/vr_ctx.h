@@ -153,7 +153,12 @@ struct vr_ctx {
 
     /* LUT */
     uint32_t nlut = 0;
-    uint32_t *h_lut = nullptr; /* packed, as set */
+    uint32_t *d_lut_rgba8 = nullptr; /* the packed R8G8B8A8_SRGB texels as set (or discretised on the device), nlut of them */
+    float *d_lut_loc = nullptr;      /* texel centres of a device-side discretize */
+    uint32_t *d_lut_nz = nullptr;    /* nz[k] = padded texels before k with alpha != 0 (nlut + 4 entries): k_classify */
+    float *d_markers = nullptr;      /* gradient markers of vr_set_gradient */
+    uint32_t lut_texels_cap = 0, lut_tables_cap = 0;
+    size_t markers_cap = 0;
     float4 *d_lut_pad = nullptr, *d_lut_dif = nullptr;
     uint4 *d_lut_h = nullptr;
     /* tuning knobs (environment: VR_BATCH, VR_CTA_THREADS, VR_BBOX, VR_WARP_W, VR_CARVEOUT, VR_ESS_MIN_EMPTY) */
@@ -223,7 +228,11 @@ size_t vr_march_smem_bytes(const MarchParams &p, bool ess);
 cudaError_t vr_k0_global_minmax(const void *dev, int dtype, size_t n, float *h_min, float *h_max, cudaStream_t s);
 cudaError_t vr_k0_cell_ranges(const void *dev, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, int cell,
                               const int occ_n[3], float2 *d_ranges, cudaStream_t s);
-cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const float4 *d_lut_pad, uint32_t nlut,
+/* lut.cu: the transfer function built on the device */
+cudaError_t vr_lut_upload_srgb_table(const float table[256]);
+cudaError_t vr_lut_gradient(const float *d_markers, uint32_t nc, uint32_t na, uint32_t count, float *d_loc, uint32_t *d_texels, cudaStream_t s);
+cudaError_t vr_lut_tables(const uint32_t *d_texels, uint32_t n, float4 *d_pad, float4 *d_dif, uint4 *d_h, uint32_t *d_nz, cudaStream_t s);
+cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const uint32_t *d_lut_nz, uint32_t nlut,
                            float min_density, float max_density, uint32_t *d_occ, int occ_words,
                            unsigned long long *d_empty_count, cudaStream_t s);
 cudaError_t vr_k0_distance(const uint32_t *d_occ, const int occ_n[3], unsigned char *d_dist, uint32_t *d_sat,

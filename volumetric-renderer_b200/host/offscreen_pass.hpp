@@ -135,6 +135,14 @@ class OffscreenPass
     {
         check(vr_set_transfer_function(ctx, data.data(), (uint32_t)data.size()));
     }
+    // the gradient editor's edit (main_window.cpp:250-257) without the host-side discretize: built on the device
+    void transfer_function_changed(const UI::Components::Gradient &gradient, uint32_t count = 256)
+    {
+        std::vector<float> cm, am;
+        for (const auto &m : gradient.color_markers) cm.insert(cm.end(), {m.location, m.value[0], m.value[1], m.value[2]});
+        for (const auto &m : gradient.alpha_markers) am.insert(am.end(), {m.location, m.value});
+        check(vr_set_gradient(ctx, cm.data(), (uint32_t)gradient.color_markers.size(), am.data(), (uint32_t)gradient.alpha_markers.size(), count));
+    }
     // get_image_view() / get_sampler(): the colour attachment as a device pointer + pitch
     std::pair<void *, size_t> get_image_view(uint32_t frame_index = 0) const
     {
