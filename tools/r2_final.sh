@@ -36,5 +36,5 @@ timeout 300 $C3 > $O/plain_c3.json 2> $O/plain_c3.err && {
   timeout 600 $NCU -k regex:k_marchILb0ELb1ELb0ELb0ELi0 -s 6 -o $O/march_c3 $C3 > $O/ncu_c3.log 2>&1
   timeout 600 $NCU -k regex:k_tile_mask -s 6 -o $O/tile_mask_c3 $C3 > $O/ncu_mask_c3.log 2>&1
 }
-ls -la $O/*.ncu-rep; tail -2 $O/ncu_c2.log $O/ncu_c3.log $O/ncu_texstream.log $O/ncu_mask_c3.log
+ls -la $O/*.ncu-rep; for f in ncu_c2 ncu_c3 ncu_texstream ncu_mask_c3; do tail -n 2 $O/$f.log; done
 fi
