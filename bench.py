@@ -376,7 +376,9 @@ def run_ours(args):
                                                 "why": "the context consults the occupancy grid only when >= 25 % of the cells are empty",
                                                 "screen_space_mask": mask_info},
                        "early_ray_termination_eps": prod["early_term_eps"] if prod["early_term"] else 0,
-                       "l2": f"inputs larger than L2 ({n ** 3 * esz / 2 ** 20:.0f} MiB volume, no flush)",
+                       "l2": (f"inputs larger than L2 ({n ** 3 * esz / 2 ** 20:.0f} MiB volume, no flush)" if n ** 3 * esz > 126e6 else
+                              f"the {n ** 3 * esz / 2 ** 20:.0f} MiB volume FITS the 126 MB L2 and stays resident across frames (not flushed): "
+                              "a parity-size configuration, not a headline number"),
                        "frames_in_flight": F,
                        "frames": f"{K} steps per rank spread evenly over the 360-frame orbit (same mix of views for every N), repeated {reps}x inside the timed region",
                        "layout_per_frame": axis_hist,
