@@ -573,7 +573,7 @@ def partitioned_frames(vr, W, H):
 
 
 def measure_partitioned(vr, mode, rank, world, local, n, W, H, K, Wu, synth=None, tf="B", ess=1, ert=1, tile_px=64, slots=2,
-                        merge="p2p", grid=None, alone_sizes=()):
+                        merge="p2p", grid=None, alone_sizes=(), balance=0.0):
     """One partitioned configuration, timed by the wall clock over K frames enqueued back to back (frames are handed
     off between the ranks by stream-ordered counters in peer memory), one device sync + barrier at the end, max over
     ranks.  mode "first": volume replicated, image tiles dealt to the ranks; "last": sub-boxes, ordered merge.
@@ -593,7 +593,7 @@ def measure_partitioned(vr, mode, rank, world, local, n, W, H, K, Wu, synth=None
         op.synth_volume(synth[0], synth[1], vr.U16, n)
         part = mg.SortFirst(op, rank, world, tile_px=tile_px, slots=slots)
     else:
-        part = mg.SortLast(op, rank, world, (n, n, n), mode=merge, grid=grid, slots=slots)
+        part = mg.SortLast(op, rank, world, (n, n, n), mode=merge, grid=grid, slots=slots, balance=balance)
         op.synth_subvolume(synth[0], synth[1], vr.U16)
         part.set_global_density_range()
     frames = partitioned_frames(vr, W, H)
@@ -716,7 +716,8 @@ def partitioned_record(vr, rank, world, local, args):
         n1_4k = c4["alone_ms_per_step"].get("3840x2160")
         if world > 1 and time_left() > 150:
             c5s = measure_partitioned(vr, "last", rank, world, local, n, 3840, 2160, K, Wu, ess=int(not args.no_ess), ert=int(not args.no_ert),
-                                      slots=args.slots_last)
+                                      slots=args.slots_last, balance=args.balance)
+            c5s["balance"] = args.balance
             c5s["n1_ms_per_step"] = n1_4k
             c5s["efficiency"] = (n1_4k / (world * c5s["ms_per_step"])) if n1_4k else None
             c5s["workload"] = f"sort-last on a volume that fits one GPU: {n}^3 u16 fBm in {world} sub-boxes, 3840x2160, direct-send merge over NVLink, 36-frame orbit"
@@ -726,7 +727,8 @@ def partitioned_record(vr, rank, world, local, args):
                                      "workload": f"{n}^3 u16 fBm, 3840x2160 on one GPU (the denominator of the sort-last curve)"}
         if world == 8 and not args.size and time_left() > 200:
             c5 = measure_partitioned(vr, "last", rank, world, local, 4096, 3840, 2160, K, Wu, synth=(vr.SYNTH_BLOBS_FBM, 0x5EED0005), tf="C",
-                                     ess=int(not args.no_ess), ert=int(not args.no_ert), slots=args.slots_last)
+                                     ess=int(not args.no_ess), ert=int(not args.no_ert), slots=args.slots_last, balance=args.balance)
+            c5["balance"] = args.balance
             c5["workload"] = "c5: 4096^3 u16 blobs+fBm (128 GiB) in 2x2x2 sub-boxes, TF-C, 3840x2160, sort-last direct-send, 36-frame orbit"
             rec["c5"] = c5
     except Exception as e:  # the C2 line must survive a failure of the extra measurements
@@ -757,7 +759,8 @@ def run_partitioned(args):
     m = measure_partitioned(vr, "first" if c4 else "last", rank, world, local, n, W, H, K, Wu,
                             synth=(vr.SYNTH_FBM, 0x5EED0004 if c4 else 0x5EED0005) if dense else (vr.SYNTH_BLOBS_FBM, 0x5EED0005),
                             tf="B" if dense else "C", ess=int(not args.no_ess), ert=int(not args.no_ert), tile_px=args.tile_px,
-                            slots=args.slots if c4 else args.slots_last, merge=args.merge, alone_sizes=((W, H),) if (c4 and args.alone) else ())
+                            slots=args.slots if c4 else args.slots_last, merge=args.merge, alone_sizes=((W, H),) if (c4 and args.alone) else (),
+                            balance=0.0 if c4 else args.balance)
     if rank == 0:
         peaks = load_peaks()
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
@@ -775,7 +778,7 @@ def run_partitioned(args):
             "n1_ms_per_step": n1, "efficiency": (n1 / (world * m["ms_per_step"])) if n1 else None,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": (f"c4: {n}^3 u16 fBm replicated, {W}x{H}, sort-first {args.tile_px}-px tiles dealt along diagonals, each rank launches its own tiles, peer stores into rank 0's image ({args.slots} slots)"
-                                    if c4 else f"c5: {n}^3 u16 {'fBm, TF-B' if dense else 'blobs+fBm, TF-C'} in {world} sub-boxes {m.get('grid')}, {W}x{H}, sort-last, direct-send merge ({args.merge})"),
+                                    if c4 else f"c5: {n}^3 u16 {'fBm, TF-B' if dense else 'blobs+fBm, TF-C'} in {world} sub-boxes {m.get('grid')}, {W}x{H}, sort-last, direct-send merge ({args.merge}), split planes follow the camera within {args.balance} of the edge"),
                        "timing": "wall clock over K frames enqueued back to back (frames handed off between ranks by stream-ordered counters in peer memory; nccl merge: collectives), one device sync + barrier at the end, max over ranks",
                        "layout": m["layout"], "l2": "inputs larger than L2"},
             "executed_samples_per_s": m["executed_samples_per_s"],
@@ -803,6 +806,8 @@ def main():
     ap.add_argument("--size", type=int, default=0, help="c4/c5 and the partitioned record: volume edge override")
     ap.add_argument("--frame", default="", help="c4/c5: WxH override")
     ap.add_argument("--tile-px", type=int, default=64, help="c4: sort-first partition tile edge in pixels")
+    ap.add_argument("--balance", type=float, default=0.08, help="sort-last: how far (fraction of the edge) the split planes may follow the camera; "
+                    "each rank holds that margin around its sub-box (0 = fixed regular split)")
     ap.add_argument("--slots-last", type=int, default=4, help="sort-last: raw/image slots per rank (frames a rank may run ahead of the merge)")
     ap.add_argument("--slots", type=int, default=2, help="c4: image slots on the display rank (frames a rank may run ahead)")
     ap.add_argument("--full-download", action="store_true", help="e2e: copy the whole frame to the host every step")

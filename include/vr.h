@@ -361,6 +361,25 @@ int vr_partition_box(const uint32_t grid[3], const uint32_t full_dims[3], uint32
 int vr_partition_order(const uint32_t grid[3], const uint32_t full_dims[3], const float camera_position[3],
                        uint32_t *out);
 
+/* ---- sort-last load balance: split planes that follow the camera -------------------------------------------
+ * Under perspective the sub-boxes nearest the eye hold up to 1.4x the samples of the farthest, and a frame waits for
+ * its slowest rank.  A rank may therefore HOLD more than it owns: vr_partition_stored_box is the regular box grown by
+ * `margin` voxels on its interior faces (pass it to vr_set_partition_sort_last, then upload / synthesise), and per
+ * frame every rank computes the same planes from the camera (vr_partition_balance: per axis the interior planes at
+ * the quantiles of a 1 / r^2 sample density, at most `margin` voxels from the regular split; layout: the grid[0]-1
+ * planes of x, then y, then z, in voxels), takes its box from them (vr_partition_box_planes; planes NULL = the
+ * regular split) and declares it with vr_set_owned_box.  Every sample still has exactly one owner: the planes are
+ * integers, the same on all ranks.  vr_partition_order_planes is vr_partition_order for those planes. */
+int vr_set_owned_box(vr_ctx *ctx, const uint32_t org[3], const uint32_t dims[3]);
+int vr_partition_stored_box(const uint32_t grid[3], const uint32_t full_dims[3], uint32_t index, const uint32_t margin[3],
+                            uint32_t org[3], uint32_t dims[3]);
+int vr_partition_balance(const uint32_t grid[3], const uint32_t full_dims[3], const float camera_position[3], const uint32_t margin[3],
+                         uint32_t *planes);
+int vr_partition_box_planes(const uint32_t grid[3], const uint32_t full_dims[3], const uint32_t *planes, uint32_t index,
+                            uint32_t org[3], uint32_t dims[3]);
+int vr_partition_order_planes(const uint32_t grid[3], const uint32_t full_dims[3], const uint32_t *planes,
+                              const float camera_position[3], uint32_t *out);
+
 /* ---- one process driving several GPUs (the C++ multi-GPU host; csrc/group.cu) ------------------------------
  * The reference constructs one pass (src/rendering/vulkan_context.cpp:51) and records it once per frame
  * (src/rendering/main_pass.cpp:91); a group stands in the same place with one context per device.  Mutators apply
@@ -388,6 +407,9 @@ int vr_group_set_options(vr_group *group, const vr_options *options);
 int vr_group_set_volume(vr_group *group, const void *data, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
                         const float *min_density, const float *max_density);
 int vr_group_synth_volume(vr_group *group, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz);
+/* Sort-last load balance: how far (fraction of the volume's edge, default 0.08, 0 = fixed regular split) the split
+ * planes may follow the camera; the ranks hold that margin around their sub-boxes.  Applies to the next volume. */
+int vr_group_set_balance(vr_group *group, float fraction);
 int vr_group_render(vr_group *group);
 int vr_group_sync(vr_group *group);
 /* The frame recorded last, complete (waits for it).  rank: replicas only (else the display rank's image). */

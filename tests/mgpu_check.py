@@ -80,11 +80,17 @@ def run_checks(vr, mg, rank, world, local):
     op.close()
 
     # ---- sort-last: peer-memory direct-send, then the NCCL exchange fallback; two view octants ------------------
-    for mode in ("p2p", "nccl"):
+    # "balanced": the split planes follow the camera (vr_partition_balance), every rank holds a margin around its box
+    for mode in ("p2p", "nccl", "balanced"):
         op = vr.OffscreenPass(W, H, device=local)
         op.transfer_function_changed(lut)
         op.set_camera(cam)
-        sl = mg.SortLast(op, rank, world, (n, n, n), mode=mode)
+        if mode == "balanced":
+            sl = mg.SortLast(op, rank, world, (n, n, n), mode="p2p", balance=0.08)
+            if world in (2, 4, 8) and not sl.balanced:
+                failures.append("balanced sort-last did not get a margin")
+        else:
+            sl = mg.SortLast(op, rank, world, (n, n, n), mode=mode)
         op.synth_subvolume(vr.SYNTH_FBM, 0x5EED0004, vr.U16)
         mn, mx = sl.set_global_density_range()
         if (mn, mx) != (gmn, gmx):

@@ -135,3 +135,64 @@ def test_partition_order_is_front_to_back(vr):
         if y == 0:  # camera looks along +y from y = -3: the y=0 half is in front of the y=1 half
             assert pos[b] < pos[b | 2]
     assert sorted(order) == list(range(8))
+
+
+@pytest.mark.parametrize("grid,view", [((2, 2, 2), v) for v in range(8)] + [((2, 1, 1), 0), ((3, 2, 1), 5), ((2, 2, 1), 2)])
+@pytest.mark.parametrize("sampler", ["exact", "hw"])
+def test_sort_last_with_planes_that_follow_the_camera(vr, port, grid, view, sampler):
+    """Sort-last load balance (include/vr.h: vr_partition_balance): every rank HOLDS its regular sub-box grown by a margin
+    and OWNS, per frame, the box between split planes computed from the camera.  The planes must stay within the margin,
+    the composed frame must equal the single-GPU frame within the sort-last bar, and -- exact sampler -- every sample must
+    still be owned by exactly one rank."""
+    n = 48
+    margin = tuple(5 if g > 1 else 0 for g in grid)
+    lut = tf(port, "B")
+    moves, zoom = OCTANT_MOVES[view]
+    cam, ocam = twin_cameras(vr, port, moves, zoom)
+    smp = vr.SAMPLER_EXACT if sampler == "exact" else vr.SAMPLER_HW
+    single = setup_pass(vr, W, H, lut, cam, layout=vr.LAYOUT_ARRAY3D, sampler=smp)
+    single.synth_volume(vr.SYNTH_FBM, 0x5EED0005, vr.U16, n)
+    _, _, mn, mx = single.volume_info()
+    single.record()
+    want, want_stats = single.download(), single.stats()
+
+    full = (n, n, n)
+    nbox = grid[0] * grid[1] * grid[2]
+    planes = vr.partition_balance(grid, full, cam.get_position(), margin)
+    regular = [k * n // g for a, g in enumerate(grid) for k in range(1, g)]
+    assert len(planes) == len(regular) and all(abs(int(p) - r) <= 5 for p, r in zip(planes, regular))
+    assert any(int(p) != r for p, r in zip(planes, regular)), "an off-centre camera must move some plane"
+    parts, passes, rects, n_inslice, covered = [], [], [], 0, np.zeros((n, n, n), np.int32)
+    for b in range(nbox):
+        s_org, s_dims = vr.partition_stored_box(grid, full, b, margin)
+        r_org, r_dims = vr.partition_box(grid, full, b)
+        assert all(so <= ro and so + sd >= ro + rd for so, sd, ro, rd in zip(s_org, s_dims, r_org, r_dims))
+        o_org, o_dims = vr.partition_box_planes(grid, full, planes, b)
+        covered[o_org[2]:o_org[2] + o_dims[2], o_org[1]:o_org[1] + o_dims[1], o_org[0]:o_org[0] + o_dims[0]] += 1
+        op = setup_pass(vr, W, H, lut, cam, layout=vr.LAYOUT_ARRAY3D, sampler=smp)
+        op.set_partition_sort_last(full, s_org, s_dims)
+        op.synth_subvolume(vr.SYNTH_FBM, 0x5EED0005, vr.U16)
+        op.set_density_range(mn, mx)
+        op.set_owned_box(o_org, o_dims)
+        op.record()
+        op.sync()
+        n_inslice += op.stats().n_inslice
+        parts.append(op.get_raw())
+        rects.append(op.partition_screen_rect(full, o_org, o_dims))
+        assert rects[-1] == tuple(op.last_frame_info().bbox)
+        passes.append(op)
+    assert (covered == 1).all(), "the owned boxes must tile the volume"
+    with pytest.raises(vr.VrError):
+        passes[0].set_owned_box((0, 0, 0), full)      # more than the rank holds
+    if sampler == "exact":
+        assert n_inslice == want_stats.n_inslice, "every sample must be owned by exactly one rank"
+    else:
+        assert abs(int(n_inslice) - int(want_stats.n_inslice)) <= 2e-4 * want_stats.n_inslice
+    order = vr.partition_order(grid, full, cam.get_position(), planes)
+    single.composite([parts[i] for i in order], 0, W * H, rects=[rects[i] for i in order])
+    got = single.download()
+    for op in passes:
+        op.close()
+    single.close()
+    d = np.abs(got.astype(int) - want.astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 0.01, (d.max(), (d > 0).mean())

@@ -516,3 +516,39 @@ def test_cpp_mirror_builds_and_fails_loudly_without_a_device(vr):
     if not torch.cuda.is_available():
         r = subprocess.run([exe, "/tmp/_vr_none.ppm", "32", "32", "8", "1"], capture_output=True, text=True)
         assert r.returncode == 1 and "no CPU fallback" in r.stderr
+
+
+def test_partition_balance_planes(vr):
+    """vr_partition_balance / vr_partition_stored_box / vr_partition_box_planes (host only): a camera on an axis of symmetry
+    leaves the planes of the other axes in the middle, the plane of its own axis moves TOWARDS the camera (the near half
+    holds more samples), never further than the margin; margins that would let two planes meet are refused."""
+    grid, full = (2, 2, 2), (256, 256, 256)
+    pl = vr.partition_balance(grid, full, (0.0, -3.0, 0.0), (40, 40, 40))
+    assert list(pl) == [128, pl[1], 128] and 128 - 40 <= pl[1] < 128
+    assert pl[1] == 107                                   # 1/r^2 between 2.5 and 3.5: the median sits 0.083 of the edge nearer
+    pl = vr.partition_balance(grid, full, (3.0, 0.0, 0.0), (10, 10, 10))
+    assert list(pl) == [138, 128, 128]                    # clamped to the margin
+    assert list(vr.partition_balance(grid, full, (0.0, -3.0, 0.0), (0, 0, 0))) == [128, 128, 128]
+    far = vr.partition_balance(grid, full, (0.0, -300.0, 0.0), (40, 40, 40))
+    assert abs(int(far[1]) - 128) <= 1                    # parallel projection in the limit: nothing to balance
+    g3 = (3, 1, 2)
+    pl3 = vr.partition_balance(g3, (300, 64, 128), (-2.0, -2.0, 1.0), (20, 0, 9))
+    assert len(pl3) == 3 and pl3[0] < pl3[1] and abs(int(pl3[0]) - 100) <= 20 and abs(int(pl3[1]) - 200) <= 20 and abs(int(pl3[2]) - 64) <= 9
+    boxes = [vr.partition_box_planes(g3, (300, 64, 128), pl3, i) for i in range(6)]
+    vol = np.zeros((128, 64, 300), np.int32)
+    for o, d in boxes:
+        vol[o[2]:o[2] + d[2], o[1]:o[1] + d[1], o[0]:o[0] + d[0]] += 1
+    assert (vol == 1).all()
+    assert vr.partition_box_planes(g3, (300, 64, 128), None, 4) == vr.partition_box(g3, (300, 64, 128), 4)
+    for i in range(6):
+        so, sd = vr.partition_stored_box(g3, (300, 64, 128), i, (20, 0, 9))
+        ro, rd = vr.partition_box(g3, (300, 64, 128), i)
+        for a in range(3):
+            assert so[a] == max(ro[a] - (20, 0, 9)[a], 0) if ro[a] > 0 else so[a] == 0
+            assert so[a] + sd[a] == (ro[a] + rd[a] + (20, 0, 9)[a] if ro[a] + rd[a] < (300, 64, 128)[a] else (300, 64, 128)[a])
+    with pytest.raises(vr.VrError):
+        vr.partition_stored_box(grid, (16, 16, 16), 0, (4, 4, 4))     # 2 * 4 + 1 > 16 / 2
+    # the visiting order follows the planes: a camera inside the cube between the regular and the moved plane
+    o_reg = vr.partition_order((2, 1, 1), (256, 1, 1), (0.05, 0.0, 0.0))
+    o_mov = vr.partition_order((2, 1, 1), (256, 1, 1), (0.05, 0.0, 0.0), planes=[160])
+    assert list(o_reg) == [1, 0] and list(o_mov) == [0, 1]

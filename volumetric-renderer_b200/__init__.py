@@ -368,6 +368,11 @@ class OffscreenPass:
         f, o, d = (np.asarray(x, np.uint32) for x in (full_dims, own_org, own_dims))
         self._check(lib.vr_set_partition_sort_last(self._h, _ptr(f), _ptr(o), _ptr(d)))
 
+    def set_owned_box(self, org, dims):
+        """vr_set_owned_box: the part of the held sub-volume this rank samples in the coming frames (balanced planes)."""
+        o, d = (np.asarray(x, np.uint32) for x in (org, dims))
+        self._check(lib.vr_set_owned_box(self._h, _ptr(o), _ptr(d)))
+
     def synth_subvolume(self, kind: int, seed: int, dtype: int):
         self._check(lib.vr_synth_subvolume(self._h, kind, seed & 0xFFFFFFFF, dtype))
 
@@ -467,6 +472,10 @@ class PassGroup:
         d = np.ascontiguousarray(data, np.uint32)
         self._check(lib.vr_group_set_transfer_function(self._h, _ptr(d), len(d)))
 
+    def set_balance(self, fraction: float):
+        """vr_group_set_balance: sort-last split planes may follow the camera by this fraction of the edge (next volume)."""
+        self._check(lib.vr_group_set_balance(self._h, float(fraction)))
+
     def slicing_changed(self, min_slice, max_slice):
         lo, hi = np.asarray(min_slice, np.float32), np.asarray(max_slice, np.float32)
         self._check(lib.vr_group_set_slicing(self._h, _ptr(lo), _ptr(hi)))
@@ -553,14 +562,47 @@ def partition_box(grid, full_dims, index: int):
     return tuple(int(x) for x in org), tuple(int(x) for x in dims)
 
 
-def partition_order(grid, full_dims, camera_position) -> np.ndarray:
+def partition_order(grid, full_dims, camera_position, planes=None) -> np.ndarray:
     g, f = np.asarray(grid, np.uint32), np.asarray(full_dims, np.uint32)
     c = np.asarray(camera_position, np.float32)
     out = np.zeros(int(g[0]) * int(g[1]) * int(g[2]), np.uint32)
-    rc = lib.vr_partition_order(_ptr(g), _ptr(f), _ptr(c), _ptr(out))
+    pl = None if planes is None else np.ascontiguousarray(planes, np.uint32)
+    rc = lib.vr_partition_order_planes(_ptr(g), _ptr(f), None if pl is None else _ptr(pl), _ptr(c), _ptr(out))
     if rc != _lib.VR_OK:
         raise VrError(rc, "vr_partition_order: bad arguments")
     return out
+
+
+def partition_stored_box(grid, full_dims, index: int, margin):
+    """The regular sub-box grown by `margin` voxels on its interior faces: what a rank holds so that the split planes
+    can follow the camera (vr_partition_balance)."""
+    g, f, m = (np.asarray(x, np.uint32) for x in (grid, full_dims, margin))
+    org, dims = np.zeros(3, np.uint32), np.zeros(3, np.uint32)
+    rc = lib.vr_partition_stored_box(_ptr(g), _ptr(f), index, _ptr(m), _ptr(org), _ptr(dims))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, "vr_partition_stored_box: bad arguments (margin too large for the grid?)")
+    return tuple(int(x) for x in org), tuple(int(x) for x in dims)
+
+
+def partition_balance(grid, full_dims, camera_position, margin) -> np.ndarray:
+    """Split planes (voxels; x planes, then y, then z) that even out the samples per sub-box for this camera."""
+    g, f, m = (np.asarray(x, np.uint32) for x in (grid, full_dims, margin))
+    c = np.asarray(camera_position, np.float32)
+    out = np.zeros(max(int(g[0]) + int(g[1]) + int(g[2]) - 3, 1), np.uint32)
+    rc = lib.vr_partition_balance(_ptr(g), _ptr(f), _ptr(c), _ptr(m), _ptr(out))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, "vr_partition_balance: bad arguments")
+    return out[: int(g[0]) + int(g[1]) + int(g[2]) - 3]
+
+
+def partition_box_planes(grid, full_dims, planes, index: int):
+    g, f = np.asarray(grid, np.uint32), np.asarray(full_dims, np.uint32)
+    pl = None if planes is None else np.ascontiguousarray(planes, np.uint32)
+    org, dims = np.zeros(3, np.uint32), np.zeros(3, np.uint32)
+    rc = lib.vr_partition_box_planes(_ptr(g), _ptr(f), None if pl is None else _ptr(pl), index, _ptr(org), _ptr(dims))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, "vr_partition_box_planes: bad arguments")
+    return tuple(int(x) for x in org), tuple(int(x) for x in dims)
 
 
 def bench_tex_peak(device: int, dtype: int, hw_filter=True) -> float:

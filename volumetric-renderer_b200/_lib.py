@@ -117,6 +117,11 @@ SIGNATURES = {
     "vr_set_image_target": (C.c_int, [_P, _P]),
     "vr_partition_box": (C.c_int, [_P, _P, C.c_uint32, _P, _P]),
     "vr_partition_order": (C.c_int, [_P, _P, _P, _P]),
+    "vr_set_owned_box": (C.c_int, [_P, _P, _P]),
+    "vr_partition_stored_box": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P]),
+    "vr_partition_balance": (C.c_int, [_P, _P, _P, _P, _P]),
+    "vr_partition_box_planes": (C.c_int, [_P, _P, _P, C.c_uint32, _P, _P]),
+    "vr_partition_order_planes": (C.c_int, [_P, _P, _P, _P, _P]),
     "vr_create_group": (C.c_int, [C.c_uint32, C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
     "vr_group_destroy": (C.c_int, [_P]),
     "vr_group_last_error": (C.c_char_p, [_P]),
@@ -128,6 +133,7 @@ SIGNATURES = {
     "vr_group_set_options": (C.c_int, [_P, C.POINTER(Options)]),
     "vr_group_set_volume": (C.c_int, [_P, _P, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, _F, _F]),
     "vr_group_synth_volume": (C.c_int, [_P, C.c_int, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "vr_group_set_balance": (C.c_int, [_P, C.c_float]),
     "vr_group_render": (C.c_int, [_P]),
     "vr_group_sync": (C.c_int, [_P]),
     "vr_group_download": (C.c_int, [_P, C.c_uint32, _P]),

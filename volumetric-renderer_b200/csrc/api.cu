@@ -1421,9 +1421,9 @@ extern "C" int vr_synth_subvolume(vr_ctx *c, int kind, uint32_t seed, int dtype)
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaDeviceSynchronize());
     uint32_t l[3];
-    for (int i = 0; i < 3; i++) {
-        const uint32_t end = c->own_org[i] + c->own_dims[i];
-        l[i] = c->own_dims[i] + (c->own_org[i] > 0 ? 1 : 0) + (end < c->full[i] ? 1 : 0);
+    for (int i = 0; i < 3; i++) { /* the stored box plus one ghost voxel towards each neighbour */
+        const uint32_t end = c->st_org[i] + c->st_dims[i];
+        l[i] = c->st_dims[i] + (c->st_org[i] > 0 ? 1 : 0) + (end < c->full[i] ? 1 : 0);
     }
     void *lin = nullptr;
     VR_CUDA(c, cudaMalloc(&lin, (size_t)l[0] * l[1] * l[2] * dtype_size(dtype)));
@@ -1461,9 +1461,20 @@ extern "C" int vr_set_partition_sort_last(vr_ctx *c, const uint32_t full_dims[3]
             return fail(c, VR_ERR_INVALID, "vr_set_partition_sort_last: sub-box outside the grid");
     c->sort_last = true;
     for (int i = 0; i < 3; i++) {
-        c->full[i] = full_dims[i], c->own_org[i] = own_org[i], c->own_dims[i] = own_dims[i];
+        c->full[i] = full_dims[i], c->own_org[i] = c->st_org[i] = own_org[i], c->own_dims[i] = c->st_dims[i] = own_dims[i];
         c->tex_org[i] = (int)own_org[i] - (own_org[i] > 0 ? 1 : 0); /* one ghost voxel towards each neighbour */
     }
+    return VR_OK;
+}
+
+extern "C" int vr_set_owned_box(vr_ctx *c, const uint32_t org[3], const uint32_t dims[3])
+{
+    if (!c || !org || !dims) return fail(c, VR_ERR_INVALID, "vr_set_owned_box: null argument");
+    if (!c->sort_last) return fail(c, VR_ERR_STATE, "vr_set_owned_box: call vr_set_partition_sort_last first");
+    for (int i = 0; i < 3; i++)
+        if (dims[i] == 0 || org[i] < c->st_org[i] || org[i] + dims[i] > c->st_org[i] + c->st_dims[i])
+            return fail(c, VR_ERR_INVALID, "vr_set_owned_box: the box leaves the sub-volume this rank holds");
+    for (int i = 0; i < 3; i++) c->own_org[i] = org[i], c->own_dims[i] = dims[i];
     return VR_OK;
 }
 
@@ -1491,8 +1502,114 @@ extern "C" int vr_partition_box(const uint32_t grid[3], const uint32_t full_dims
     return VR_OK;
 }
 
+namespace
+{
+uint32_t regular_plane(const uint32_t grid[3], const uint32_t full_dims[3], int a, uint32_t k) { return (uint32_t)((uint64_t)k * full_dims[a] / grid[a]); }
+bool margins_ok(const uint32_t grid[3], const uint32_t full_dims[3], const uint32_t margin[3])
+{
+    for (int a = 0; a < 3; a++) {
+        if (grid[a] == 0 || grid[a] > full_dims[a]) return false;
+        /* two neighbouring planes may each move by the margin: they must not meet */
+        if (margin && grid[a] > 1 && (uint64_t)2 * margin[a] + 1 > full_dims[a] / grid[a]) return false;
+    }
+    return true;
+}
+}  // namespace
+
+extern "C" int vr_partition_stored_box(const uint32_t grid[3], const uint32_t full_dims[3], uint32_t index, const uint32_t margin[3],
+                                       uint32_t org[3], uint32_t dims[3])
+{
+    if (!grid || !full_dims || !margin || !org || !dims || !margins_ok(grid, full_dims, margin)) return VR_ERR_INVALID;
+    const uint32_t total = grid[0] * grid[1] * grid[2];
+    if (index >= total) return VR_ERR_INVALID;
+    const uint32_t b[3] = {index % grid[0], (index / grid[0]) % grid[1], index / (grid[0] * grid[1])};
+    for (int a = 0; a < 3; a++) {
+        const uint32_t lo = regular_plane(grid, full_dims, a, b[a]), hi = regular_plane(grid, full_dims, a, b[a] + 1);
+        const uint32_t slo = b[a] > 0 ? lo - margin[a] : lo, shi = b[a] + 1 < grid[a] ? hi + margin[a] : hi;
+        org[a] = slo, dims[a] = shi - slo;
+    }
+    return VR_OK;
+}
+
+extern "C" int vr_partition_balance(const uint32_t grid[3], const uint32_t full_dims[3], const float camera_position[3], const uint32_t margin[3],
+                                    uint32_t *planes)
+{
+    if (!grid || !full_dims || !camera_position || !margin || !planes || !margins_ok(grid, full_dims, margin)) return VR_ERR_INVALID;
+    /* Samples per unit volume of a perspective frame fall with the squared distance from the eye (a pixel's solid angle
+     * is fixed, the steps along its ray are equidistant): density ~ 1 / r^2 over the unit cube, integrated on Q^3 cell
+     * centres in double -- the same numbers on every rank.  Per axis the interior planes go to the quantiles k / g of
+     * the marginal, no further than `margin` voxels from the regular split. */
+    constexpr int Q = 16;
+    double marg[3][Q] = {};
+    for (int z = 0; z < Q; z++)
+        for (int y = 0; y < Q; y++)
+            for (int x = 0; x < Q; x++) {
+                const double px = (x + 0.5) / Q - 0.5 - (double)camera_position[0], py = (y + 0.5) / Q - 0.5 - (double)camera_position[1],
+                             pz = (z + 0.5) / Q - 0.5 - (double)camera_position[2];
+                const double r2 = px * px + py * py + pz * pz;
+                const double rho = 1.0 / (r2 > 1e-4 ? r2 : 1e-4);
+                marg[0][x] += rho, marg[1][y] += rho, marg[2][z] += rho;
+            }
+    uint32_t *out = planes;
+    for (int a = 0; a < 3; a++) {
+        double total = 0.0;
+        for (int i = 0; i < Q; i++) total += marg[a][i];
+        for (uint32_t k = 1; k < grid[a]; k++) {
+            const double want = total * (double)k / (double)grid[a];
+            double acc = 0.0, pos = 0.5;
+            for (int i = 0; i < Q; i++) {
+                if (acc + marg[a][i] >= want) {
+                    pos = ((double)i + (want - acc) / marg[a][i]) / Q; /* texture coordinate of the quantile */
+                    break;
+                }
+                acc += marg[a][i];
+            }
+            const int64_t reg = (int64_t)regular_plane(grid, full_dims, a, k);
+            int64_t v = (int64_t)std::llround(pos * (double)full_dims[a]);
+            v = std::min<int64_t>(std::max<int64_t>(v, reg - (int64_t)margin[a]), reg + (int64_t)margin[a]);
+            *out++ = (uint32_t)v;
+        }
+    }
+    return VR_OK;
+}
+
+namespace
+{
+/* plane k of axis a: 0 and grid[a] are the faces of the volume, the others come from `planes` (NULL: the regular split) */
+uint32_t plane_at(const uint32_t grid[3], const uint32_t full_dims[3], const uint32_t *planes, int a, uint32_t k)
+{
+    if (k == 0) return 0;
+    if (k >= grid[a]) return full_dims[a];
+    if (!planes) return regular_plane(grid, full_dims, a, k);
+    uint32_t off = 0;
+    for (int i = 0; i < a; i++) off += grid[i] - 1;
+    return planes[off + k - 1];
+}
+}  // namespace
+
+extern "C" int vr_partition_box_planes(const uint32_t grid[3], const uint32_t full_dims[3], const uint32_t *planes, uint32_t index,
+                                       uint32_t org[3], uint32_t dims[3])
+{
+    if (!grid || !full_dims || !org || !dims || !margins_ok(grid, full_dims, nullptr)) return VR_ERR_INVALID;
+    const uint32_t total = grid[0] * grid[1] * grid[2];
+    if (index >= total) return VR_ERR_INVALID;
+    const uint32_t b[3] = {index % grid[0], (index / grid[0]) % grid[1], index / (grid[0] * grid[1])};
+    for (int a = 0; a < 3; a++) {
+        const uint32_t lo = plane_at(grid, full_dims, planes, a, b[a]), hi = plane_at(grid, full_dims, planes, a, b[a] + 1);
+        if (hi <= lo || hi > full_dims[a]) return VR_ERR_INVALID;
+        org[a] = lo, dims[a] = hi - lo;
+    }
+    return VR_OK;
+}
+
 extern "C" int vr_partition_order(const uint32_t grid[3], const uint32_t full_dims[3], const float camera_position[3],
                                   uint32_t *out)
+{
+    return vr_partition_order_planes(grid, full_dims, nullptr, camera_position, out);
+}
+
+extern "C" int vr_partition_order_planes(const uint32_t grid[3], const uint32_t full_dims[3], const uint32_t *planes,
+                                         const float camera_position[3], uint32_t *out)
 {
     if (!grid || !full_dims || !camera_position || !out) return VR_ERR_INVALID;
     const uint32_t total = grid[0] * grid[1] * grid[2];
@@ -1506,7 +1623,7 @@ extern "C" int vr_partition_order(const uint32_t grid[3], const uint32_t full_di
         const double t = (double)camera_position[a] + 0.5; /* model -> texture space */
         int s = -1;
         for (uint32_t k = 0; k < grid[a]; k++) {
-            const double lo = (double)((uint64_t)k * full_dims[a] / grid[a]) / (double)full_dims[a];
+            const double lo = (double)plane_at(grid, full_dims, planes, a, k) / (double)full_dims[a];
             if (t >= lo) s = (int)k;
         }
         if (t >= 1.0) s = (int)grid[a];

@@ -40,7 +40,10 @@ struct vr_group {
     std::vector<std::vector<void *>> raw_slot; /* [rank][slot] */
     uint64_t frame = 0;
     uint32_t full[3] = {0, 0, 0}, grid[3] = {1, 1, 1};
-    std::vector<std::array<uint32_t, 6>> box; /* org, dims per rank */
+    std::vector<std::array<uint32_t, 6>> box;    /* org, dims each rank OWNS in the frame being recorded */
+    std::vector<std::array<uint32_t, 6>> stored; /* org, dims each rank HOLDS */
+    float balance = 0.08f;                       /* sort-last: how far the split planes may follow the camera (vr_group_set_balance) */
+    uint32_t margin[3] = {0, 0, 0};
     float cam_pos[3] = {0, -3, 0};
     std::string err;
 };
@@ -97,12 +100,18 @@ int make_partition(vr_group *g, uint32_t nx, uint32_t ny, uint32_t nz)
     g->full[0] = nx, g->full[1] = ny, g->full[2] = nz;
     grid_for_world(g->n, g->grid);
     g->box.assign(g->n, {});
+    g->stored.assign(g->n, {});
+    /* load balance: the planes may follow the camera by `balance` of the edge; every rank holds that margin around its box */
+    for (int i = 0; i < 3; i++) {
+        const uint32_t room = g->grid[i] > 1 ? (g->full[i] / g->grid[i] - 1) / 2 : 0;
+        g->margin[i] = g->grid[i] > 1 ? std::min<uint32_t>((uint32_t)(g->balance * (float)g->full[i]), room) : 0;
+    }
     for (uint32_t r = 0; r < g->n; r++) {
-        uint32_t org[3], dims[3];
-        if (vr_partition_box(g->grid, g->full, r, org, dims) != VR_OK)
+        uint32_t org[3], dims[3], sorg[3], sdims[3];
+        if (vr_partition_box(g->grid, g->full, r, org, dims) != VR_OK || vr_partition_stored_box(g->grid, g->full, r, g->margin, sorg, sdims) != VR_OK)
             return gfail(g, VR_ERR_INVALID, "vr_group: the volume is too small for one sub-box per rank");
-        for (int i = 0; i < 3; i++) g->box[r][i] = org[i], g->box[r][3 + i] = dims[i];
-        G_VR(g, r, vr_set_partition_sort_last(g->ctx[r], g->full, org, dims));
+        for (int i = 0; i < 3; i++) g->box[r][i] = org[i], g->box[r][3 + i] = dims[i], g->stored[r][i] = sorg[i], g->stored[r][3 + i] = sdims[i];
+        G_VR(g, r, vr_set_partition_sort_last(g->ctx[r], g->full, sorg, sdims));
     }
     return VR_OK;
 }
@@ -269,6 +278,13 @@ extern "C" int vr_group_set_options(vr_group *g, const vr_options *o)
     return VR_OK;
 }
 
+extern "C" int vr_group_set_balance(vr_group *g, float fraction)
+{
+    if (!g || !(fraction >= 0.0f) || fraction > 0.25f) return gfail(g, VR_ERR_INVALID, "vr_group_set_balance: need 0 <= fraction <= 0.25");
+    g->balance = fraction; /* takes effect with the next vr_group_set_volume / vr_group_synth_volume */
+    return VR_OK;
+}
+
 extern "C" int vr_group_set_volume(vr_group *g, const void *data, int dtype, uint32_t nx, uint32_t ny, uint32_t nz, const float *mn,
                                    const float *mx)
 {
@@ -282,10 +298,10 @@ extern "C" int vr_group_set_volume(vr_group *g, const void *data, int dtype, uin
     const size_t esz = dtype == VR_U8 ? 1 : (dtype == VR_U16 ? 2 : 4);
     std::vector<unsigned char> sub;
     for (uint32_t r = 0; r < g->n; r++) {
-        /* the rank's sub-box plus one ghost voxel towards each neighbour, cut out of the host array */
+        /* what the rank holds (its sub-box + the balance margin) plus one ghost voxel towards each neighbour, cut out of the host array */
         uint32_t lo[3], l[3];
         for (int i = 0; i < 3; i++) {
-            const uint32_t org = g->box[r][i], dims = g->box[r][3 + i], end = org + dims;
+            const uint32_t org = g->stored[r][i], dims = g->stored[r][3 + i], end = org + dims;
             lo[i] = org - (org > 0 ? 1 : 0);
             l[i] = dims + (org > 0 ? 1 : 0) + (end < g->full[i] ? 1 : 0);
         }
@@ -344,8 +360,19 @@ extern "C" int vr_group_render(vr_group *g)
     }
     /* sort-last */
     if (g->raw_slot.empty()) return gfail(g, VR_ERR_STATE, "vr_group_render: no volume (vr_group_set_volume / vr_group_synth_volume)");
-    std::vector<uint32_t> order(n);
-    if (vr_partition_order(g->grid, g->full, g->cam_pos, order.data()) != VR_OK) return gfail(g, VR_ERR_INVALID, "vr_partition_order failed");
+    std::vector<uint32_t> order(n), planes(g->grid[0] + g->grid[1] + g->grid[2]);
+    const bool balanced = g->margin[0] || g->margin[1] || g->margin[2];
+    if (balanced) {
+        /* this frame's split planes (a pure function of the camera) and every rank's box between them */
+        if (vr_partition_balance(g->grid, g->full, g->cam_pos, g->margin, planes.data()) != VR_OK) return gfail(g, VR_ERR_INVALID, "vr_partition_balance failed");
+        for (uint32_t r = 0; r < n; r++) {
+            if (vr_partition_box_planes(g->grid, g->full, planes.data(), r, &g->box[r][0], &g->box[r][3]) != VR_OK)
+                return gfail(g, VR_ERR_INVALID, "vr_partition_box_planes failed");
+            G_VR(g, r, vr_set_owned_box(g->ctx[r], &g->box[r][0], &g->box[r][3]));
+        }
+    }
+    if (vr_partition_order_planes(g->grid, g->full, balanced ? planes.data() : nullptr, g->cam_pos, order.data()) != VR_OK)
+        return gfail(g, VR_ERR_INVALID, "vr_partition_order failed");
     std::vector<uint32_t> rects(4 * n);
     for (uint32_t i = 0; i < n; i++) {
         const uint32_t b = order[i];

@@ -149,6 +149,7 @@ struct vr_ctx {
     /* sort-last */
     bool sort_last = false;
     uint32_t full[3] = {0, 0, 0}, own_org[3] = {0, 0, 0}, own_dims[3] = {0, 0, 0};
+    uint32_t st_org[3] = {0, 0, 0}, st_dims[3] = {0, 0, 0}; /* the box whose voxels this rank holds (>= the owned box: vr_set_owned_box) */
     int tex_org[3] = {0, 0, 0}; /* global voxel index of local texel 0 */
 
     /* LUT */

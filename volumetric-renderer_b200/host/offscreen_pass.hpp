@@ -248,6 +248,8 @@ class PassGroup
         check(vr_group_set_transfer_function(g, data.data(), (uint32_t)data.size()));
     }
     void set_options(const vr_options &o) { check(vr_group_set_options(g, &o)); }
+    // sort-last: how far the split planes may follow the camera (fraction of the edge; before the volume is set)
+    void set_balance(float fraction) { check(vr_group_set_balance(g, fraction)); }
     // the frame recorded last, complete (replicas: of `rank`)
     std::vector<uint8_t> download(uint32_t rank = 0)
     {

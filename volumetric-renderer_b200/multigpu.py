@@ -205,17 +205,24 @@ class SortLast:
     of the rear-most (perspective), and which rank that is changes along an orbit (tools/exp_sl_balance.py)."""
 
     def __init__(self, op, rank: int, world: int, full_dims, grid=None, display_rank: int = 0, mode: str = "p2p",
-                 group=None, on_frame=None, slots: int = 2):
+                 group=None, on_frame=None, slots: int = 2, balance: float = 0.0):
+        """balance: how far (fraction of the volume's edge) the split planes may follow the camera to even out the
+        samples per rank (vr_partition_balance).  A rank then holds its regular sub-box grown by that margin on the
+        interior faces -- (1/g + 2 b)^3 instead of (1/g)^3 of the volume -- and owns a different part of it per frame."""
         import torch.distributed as dist
-        from . import partition_box
+        from . import partition_box, partition_stored_box
         self.op, self.rank, self.world, self.display, self.mode, self.group = op, rank, world, display_rank, mode, group
         self.full = tuple(int(x) for x in full_dims)
         self.grid = tuple(grid) if grid else grid_for_world(world)
         assert self.grid[0] * self.grid[1] * self.grid[2] == world
+        # the margin must leave each box at least one voxel when both its planes move towards each other
+        self.margin = tuple(min(int(balance * n), max((n // g - 1) // 2, 0)) if g > 1 else 0 for n, g in zip(self.full, self.grid))
+        self.balanced = any(self.margin)
+        self._planes = None
         self._boxes = [partition_box(self.grid, self.full, r) for r in range(world)]
-        self.org, self.dims = self._boxes[rank]
+        self.org, self.dims = partition_stored_box(self.grid, self.full, rank, self.margin) if self.balanced else self._boxes[rank]
         op.set_options(write_raw=1)
-        op.set_partition_sort_last(self.full, self.org, self.dims)
+        op.set_partition_sort_last(self.full, self.org, self.dims)     # what this rank holds
         w, h = op.size
         self.npix = w * h
         self.ranges = pixel_ranges(self.npix, world)
@@ -260,9 +267,14 @@ class SortLast:
         (slot image_slot()) after finish()."""
         import torch
         import torch.distributed as dist
-        from . import partition_order
+        from . import partition_balance, partition_box_planes, partition_order
         op, rank, world = self.op, self.rank, self.world
-        order = [int(b) for b in partition_order(self.grid, self.full, camera_position)]
+        if self.balanced:
+            # the same planes on every rank (a pure function of the camera), then each rank's box of this frame
+            self._planes = partition_balance(self.grid, self.full, camera_position, self.margin)
+            self._boxes = [partition_box_planes(self.grid, self.full, self._planes, r) for r in range(world)]
+            op.set_owned_box(*self._boxes[rank])
+        order = [int(b) for b in partition_order(self.grid, self.full, camera_position, self._planes)]
         # every rank's partial is the identity outside the screen box of its sub-box: K1 stores and K2 reads only inside
         rects = [op.partition_screen_rect(self.full, *self._boxes[r]) for r in order]
         b, e = self.ranges[rank]
