@@ -778,7 +778,7 @@ def run_partitioned(args):
             "n1_ms_per_step": n1, "efficiency": (n1 / (world * m["ms_per_step"])) if n1 else None,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": (f"c4: {n}^3 u16 fBm replicated, {W}x{H}, sort-first {args.tile_px}-px tiles dealt along diagonals, each rank launches its own tiles, peer stores into rank 0's image ({args.slots} slots)"
-                                    if c4 else f"c5: {n}^3 u16 {'fBm, TF-B' if dense else 'blobs+fBm, TF-C'} in {world} sub-boxes {m.get('grid')}, {W}x{H}, sort-last, direct-send merge ({args.merge}), split planes follow the camera within {args.balance} of the edge"),
+                                    if c4 else f"c5: {n}^3 u16 {'fBm, TF-B' if dense else 'blobs+fBm, TF-C'} in {world} sub-boxes {m.get('grid')}, {W}x{H}, sort-last, direct-send merge ({args.merge}), split planes: {"fixed" if not args.balance else f"follow the camera within {args.balance} of the edge"}"),
                        "timing": "wall clock over K frames enqueued back to back (frames handed off between ranks by stream-ordered counters in peer memory; nccl merge: collectives), one device sync + barrier at the end, max over ranks",
                        "layout": m["layout"], "l2": "inputs larger than L2"},
             "executed_samples_per_s": m["executed_samples_per_s"],
@@ -806,8 +806,8 @@ def main():
     ap.add_argument("--size", type=int, default=0, help="c4/c5 and the partitioned record: volume edge override")
     ap.add_argument("--frame", default="", help="c4/c5: WxH override")
     ap.add_argument("--tile-px", type=int, default=64, help="c4: sort-first partition tile edge in pixels")
-    ap.add_argument("--balance", type=float, default=0.08, help="sort-last: how far (fraction of the edge) the split planes may follow the camera; "
-                    "each rank holds that margin around its sub-box (0 = fixed regular split)")
+    ap.add_argument("--balance", type=float, default=0.0, help="sort-last: how far (fraction of the edge) the split planes may follow the camera; "
+                    "each rank holds that margin around its sub-box (0 = fixed regular split, the default: measured slower, DESIGN.md section 5)")
     ap.add_argument("--slots-last", type=int, default=4, help="sort-last: raw/image slots per rank (frames a rank may run ahead of the merge)")
     ap.add_argument("--slots", type=int, default=2, help="c4: image slots on the display rank (frames a rank may run ahead)")
     ap.add_argument("--full-download", action="store_true", help="e2e: copy the whole frame to the host every step")

@@ -407,7 +407,7 @@ int vr_group_set_options(vr_group *group, const vr_options *options);
 int vr_group_set_volume(vr_group *group, const void *data, int dtype, uint32_t nx, uint32_t ny, uint32_t nz,
                         const float *min_density, const float *max_density);
 int vr_group_synth_volume(vr_group *group, int kind, uint32_t seed, int dtype, uint32_t nx, uint32_t ny, uint32_t nz);
-/* Sort-last load balance: how far (fraction of the volume's edge, default 0.08, 0 = fixed regular split) the split
+/* Sort-last load balance: how far (fraction of the volume's edge; default 0 = fixed regular split) the split
  * planes may follow the camera; the ranks hold that margin around their sub-boxes.  Applies to the next volume. */
 int vr_group_set_balance(vr_group *group, float fraction);
 int vr_group_render(vr_group *group);

@@ -42,7 +42,7 @@ struct vr_group {
     uint32_t full[3] = {0, 0, 0}, grid[3] = {1, 1, 1};
     std::vector<std::array<uint32_t, 6>> box;    /* org, dims each rank OWNS in the frame being recorded */
     std::vector<std::array<uint32_t, 6>> stored; /* org, dims each rank HOLDS */
-    float balance = 0.08f;                       /* sort-last: how far the split planes may follow the camera (vr_group_set_balance) */
+    float balance = 0.0f;                        /* sort-last: how far the split planes may follow the camera (vr_group_set_balance) */
     uint32_t margin[3] = {0, 0, 0};
     float cam_pos[3] = {0, -3, 0};
     std::string err;
