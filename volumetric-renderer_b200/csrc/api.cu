@@ -402,6 +402,7 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     if (const char *e = std::getenv("VR_CTA_THREADS")) c->tune_threads = std::atoi(e) == 256 ? 256 : 128;
     if (const char *e = std::getenv("VR_BBOX")) c->tune_bbox = std::atoi(e);
     if (const char *e = std::getenv("VR_DIRTY_CLEAR")) c->tune_dirty_clear = std::atoi(e);
+    if (const char *e = std::getenv("VR_PAIR_LOCAL")) c->tune_pair_local = std::atoi(e);
     if (const char *e = std::getenv("VR_TILE_MASK")) c->tune_tile_mask = std::atoi(e);
     if (const char *e = std::getenv("VR_WARP_W")) {
         const int w = std::atoi(e);
@@ -996,7 +997,7 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
         const double un = std::sqrt((double)u[0] * u[0] + (double)u[1] * u[1] + (double)u[2] * u[2]);
         const double dn = std::sqrt((double)c->cam_pos[0] * c->cam_pos[0] + (double)c->cam_pos[1] * c->cam_pos[1] + (double)c->cam_pos[2] * c->cam_pos[2]);
         const double ww = (double)c->tune_warp_w, wh = 32.0 / ww;
-        double best = 1e30;
+        double best = 1e30, cost[3] = {1e30, 1e30, 1e30};
         for (int a = 2; a >= 0; a--) { /* ties go to z, then y */
             const double full_a = c->sort_last ? (double)c->full[a] : (double)nd[a];
             const double pitch = 1.2 * full_a / (double)std::max<int64_t>(std::max(bw, bh), 1); /* voxels per pixel along a */
@@ -1005,7 +1006,31 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
             const double f = step_vox > 1.0 ? 1.0 / step_vox : 1.0;
             const double t = combine(S / 5.7e11 * (1.0 + 0.2 * std::max(0.0, L - 4.5)), 2.0 * V * f / 5.0e12) *
                              (1.0 + 1e-6 * L); /* equal cost: the axis with fewer layers per fetch */
+            cost[a] = t;
             if (t < best - 1e-12) best = t, pair_axis = a;
+        }
+        /* Sort-last: what a warp fetches together are the positions entry(pixel) + i d(pixel) of neighbouring pixels at the
+         * same step index i.  Rays that entered through the cube face perpendicular to w share their w coordinate at the
+         * face exactly and drift apart only by the divergence of their directions along the path inside the cube: behind
+         * that face the pairs along w cost what they cost when looking straight down w, whatever the view angle, while
+         * the ranks behind the other front face want the other axis.  On the frames between two axes this is a factor of
+         * two between the ranks of one frame (profiles/r2_exp_sl_stats.txt, r2_exp_sl_axis_table_n8.txt), and the frame
+         * waits for the slowest.  So where the estimate above rates two axes close, a rank takes the axis of the face the
+         * central ray of its screen rectangle enters the cube through. */
+        if (c->sort_last && c->ray_valid && c->tune_pair_local && bw > 0 && bh > 0) {
+            const double px = 0.5 * ((double)p.bbox[0] + (double)p.bbox[2]), py = 0.5 * ((double)p.bbox[1] + (double)p.bbox[3]);
+            const double xn = (px + 0.5) * (2.0 / (double)c->W) - 1.0, yn = (py + 0.5) * (2.0 / (double)c->H) - 1.0;
+            double nh[4], fh[4], tn = -1e300;
+            int face = -1;
+            for (int i = 0; i < 4; i++) nh[i] = xn * (double)c->rc[0][i] + yn * (double)c->rc[1][i] + (double)c->rc[3][i], fh[i] = nh[i] + (double)c->rc[2][i];
+            for (int i = 0; i < 3; i++) { /* slab test of march.cu pixel_entry: the axis of the entry face */
+                const double o = nh[i] / nh[3], d = fh[i] / fh[3] - o;
+                if (d != 0.0) {
+                    const double lo = std::min((-0.5 - o) / d, (0.5 - o) / d);
+                    if (lo > tn) tn = lo, face = i;
+                }
+            }
+            if (face >= 0 && face != pair_axis && cost[face] <= 1.35 * best) pair_axis = face;
         }
         if (c->tune_pair_axis >= 0) pair_axis = c->tune_pair_axis;
         if (policy == 2) pair = !ess && bw * bh >= (int64_t)sms * 10 * 128 && best < t3d;

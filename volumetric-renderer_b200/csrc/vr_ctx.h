@@ -208,6 +208,7 @@ struct vr_ctx {
     uint32_t tile_mask_words = 0;
     bool slot_mask_valid[VR_MAX_FRAMES_IN_FLIGHT] = {false, false, false, false};
     uint32_t slot_mask_shape[VR_MAX_FRAMES_IN_FLIGHT][3] = {}; /* tiles in x, tiles in y, tile height of the frame recorded last */
+    int tune_pair_local = 1;         /* VR_PAIR_LOCAL=0: a sort-last rank never overrides the pair axis by its entry face */
     int tune_tile_mask = 1;          /* VR_TILE_MASK=0: no screen-space mask; 2: marked in global memory directly (frames too large to stage) */
     bool occ_dirty = true;
     uint64_t occ_empty_cells = 0;
