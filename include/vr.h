@@ -415,6 +415,23 @@ int vr_group_sync(vr_group *group);
 /* The frame recorded last, complete (waits for it).  rank: replicas only (else the display rank's image). */
 int vr_group_download(vr_group *group, uint32_t rank, void *host_rgba8);
 
+/* ---- no-allocation entry point --------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * min / max of `count` values of type `dtype` (VR_U8 / VR_U16 / VR_F32) in device memory -- what vr_set_volume* does
+ * with NULL min/max (std::min_element / max_element of src/data/nrrd_file_parser.cpp:39-40) -- written as two
+ * floats {min, max} to DEVICE memory at dev_min_max.  Two kernel launches on `cuda_stream` (NULL = the default
+ * stream) and nothing else: no cudaMalloc / cudaFree, no host allocation, no copy, no synchronisation; the result is
+ * there when the stream has run.  The per-block partials live in a file-scope device array of 16 KiB that every GPU
+ * holding the library keeps until exit and that ALL calls on a device share: calls that overlap on the GPU
+ * (different streams without ordering) race -- serialise them.  Limits: 1 <= count <= vr_minmax_static_max_count()
+ * = 2^36 (a 4096^3 volume), dev_values 16-byte aligned; anything else is refused with VR_ERR_INVALID and a message
+ * in errbuf (may be NULL). */
+#define VR_MINMAX_STATIC_MAX_COUNT (1ull << 36)
+uint64_t vr_minmax_static_max_count(void);
+int vr_minmax_static(int device, const void *dev_values, int dtype, uint64_t count, float *dev_min_max, void *cuda_stream,
+                     char *errbuf, size_t errbuf_len);
+
 /* ---- measurement ----------------------------------------------------------------------- */
 
 /* ---- stream-ordered frame hand-off between ranks (one process per GPU) --------------------

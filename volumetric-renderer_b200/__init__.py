@@ -605,6 +605,16 @@ def partition_box_planes(grid, full_dims, planes, index: int):
     return tuple(int(x) for x in org), tuple(int(x) for x in dims)
 
 
+def minmax_static(device: int, dev_values: int, dtype: int, count: int, dev_min_max: int, stream: int | None = None):
+    """vr_minmax_static: {min, max} of `count` values in device memory, written to two floats in device memory at
+    dev_min_max; allocates nothing (its scratch is a static device array shared by all calls on the device: do not
+    overlap calls).  Asynchronous on `stream`."""
+    err = C.create_string_buffer(256)
+    rc = lib.vr_minmax_static(device, C.c_void_p(dev_values), dtype, count, C.c_void_p(dev_min_max), stream, err, len(err))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, err.value.decode())
+
+
 def bench_tex_peak(device: int, dtype: int, hw_filter=True) -> float:
     """hw_filter: 0 point, 1 trilinear tex3D (LAYOUT_ARRAY3D's fetch), 2 paired bilinear (LAYOUT_PAIRED's fetch)."""
     r = C.c_double()

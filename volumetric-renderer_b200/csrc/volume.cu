@@ -668,3 +668,95 @@ cudaError_t vr_k0_synth(void *dev, int kind, uint32_t seed, int dtype, uint32_t 
     k_synth<<<(unsigned)blocks, 256, 0, s>>>(sp, b);
     return cudaGetLastError();
 }
+
+/* ---- min/max of a device array with NO allocation (vr_minmax_static, include/vr.h) -------------------------------
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is k_global_minmax with its
+ * per-block partials in a file-scope device array instead of a cudaMalloc'd buffer, and the last reduction on the
+ * device instead of on the host: two launches on the caller's stream, nothing else -- no cudaMalloc, no cudaFree, no
+ * host allocation, no copy, no synchronisation.
+ *
+ * The array lives in every GPU that loads the library until the process exits: VR_STATIC_MINMAX_BLOCKS float2 = 16 KiB.
+ * ALL calls on a device share it, and it keeps the last call's contents: every launch overwrites each partial it reads
+ * later (one per block, all `blocks` of them), so nothing has to start at zero -- but two calls that overlap on the GPU
+ * (different streams, no ordering) race on it.  Serialise them.
+ *
+ * In host code `g_minmax_scratch` is a host-side stand-in, not a device address: the kernels get the address
+ * cudaGetSymbolAddress returns, taken once per device with that device current. */
+#define VR_STATIC_MINMAX_BLOCKS 2048
+#define VR_STATIC_MINMAX_MAX_DEVICES 64
+static __device__ __align__(256) float2 g_minmax_scratch[VR_STATIC_MINMAX_BLOCKS];
+
+namespace
+{
+float2 *g_minmax_scratch_ptr[VR_STATIC_MINMAX_MAX_DEVICES]; /* device address of the array on each device, 0 = not taken yet */
+int g_minmax_blocks[VR_STATIC_MINMAX_MAX_DEVICES];
+
+__global__ void __launch_bounds__(256) k_minmax_final(const float2 *__restrict__ partial, int n, float *out)
+{
+    float mn = CUDART_INF_F, mx = -CUDART_INF_F;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float2 p = partial[i];
+        mn = fminf(mn, p.x), mx = fmaxf(mx, p.y);
+    }
+    __shared__ float2 r;
+    block_minmax(mn, mx, &r);
+    __syncthreads();
+    if (threadIdx.x == 0) out[0] = r.x, out[1] = r.y;
+}
+
+int static_fail(char *errbuf, size_t len, int status, const char *msg, cudaError_t e = cudaSuccess)
+{
+    if (errbuf && len) {
+        if (e != cudaSuccess) std::snprintf(errbuf, len, "vr_minmax_static: %s: %s", msg, cudaGetErrorString(e));
+        else std::snprintf(errbuf, len, "vr_minmax_static: %s", msg);
+    }
+    return status;
+}
+}  // namespace
+
+extern "C" uint64_t vr_minmax_static_max_count(void) { return VR_MINMAX_STATIC_MAX_COUNT; }
+
+extern "C" int vr_minmax_static(int device, const void *dev_values, int dtype, uint64_t count, float *dev_min_max, void *cuda_stream,
+                                char *errbuf, size_t errbuf_len)
+{
+    if (!dev_values || !dev_min_max) return static_fail(errbuf, errbuf_len, VR_ERR_INVALID, "null input or output pointer");
+    if (dtype < VR_U8 || dtype > VR_F32) return static_fail(errbuf, errbuf_len, VR_ERR_INVALID, "dtype must be VR_U8, VR_U16 or VR_F32");
+    if (count == 0) return static_fail(errbuf, errbuf_len, VR_ERR_INVALID, "count must be >= 1");
+    if (count > VR_MINMAX_STATIC_MAX_COUNT)
+        return static_fail(errbuf, errbuf_len, VR_ERR_INVALID, "count exceeds the maximum of 2^36 values (vr_minmax_static_max_count): split the array");
+    if (reinterpret_cast<uintptr_t>(dev_values) & 15u) return static_fail(errbuf, errbuf_len, VR_ERR_INVALID, "dev_values must be 16-byte aligned");
+    if (reinterpret_cast<uintptr_t>(dev_min_max) & 3u) return static_fail(errbuf, errbuf_len, VR_ERR_INVALID, "dev_min_max must be 4-byte aligned");
+    if (device < 0 || device >= VR_STATIC_MINMAX_MAX_DEVICES) return static_fail(errbuf, errbuf_len, VR_ERR_INVALID, "device index out of range");
+    int before = -1;
+    cudaError_t e = cudaGetDevice(&before);
+    if (e != cudaSuccess) return static_fail(errbuf, errbuf_len, VR_ERR_CUDA, "no CUDA device (this backend has no CPU fallback)", e);
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return static_fail(errbuf, errbuf_len, VR_ERR_CUDA, "cudaSetDevice", e);
+    int rc = VR_OK;
+    if (!g_minmax_scratch_ptr[device]) {
+        /* set-up, once per device, with that device current: the array's address ON THIS DEVICE */
+        float2 *p = nullptr;
+        int sms = 0;
+        e = cudaGetSymbolAddress((void **)&p, g_minmax_scratch);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (e != cudaSuccess || !p) rc = static_fail(errbuf, errbuf_len, VR_ERR_CUDA, "cudaGetSymbolAddress of the scratch array", e);
+        else g_minmax_blocks[device] = std::min(sms * 8, VR_STATIC_MINMAX_BLOCKS), g_minmax_scratch_ptr[device] = p;
+    }
+    if (rc == VR_OK) {
+        cudaStream_t s = (cudaStream_t)cuda_stream;
+        float2 *partial = g_minmax_scratch_ptr[device];
+        const int blocks = g_minmax_blocks[device];
+        const size_t n = (size_t)count;
+        switch (dtype) {
+            case VR_U8: k_global_minmax<unsigned char><<<blocks, 256, 0, s>>>((const unsigned char *)dev_values, n, partial); break;
+            case VR_U16: k_global_minmax<unsigned short><<<blocks, 256, 0, s>>>((const unsigned short *)dev_values, n, partial); break;
+            default: k_global_minmax<float><<<blocks, 256, 0, s>>>((const float *)dev_values, n, partial); break;
+        }
+        k_minmax_final<<<1, 256, 0, s>>>(partial, blocks, dev_min_max);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) rc = static_fail(errbuf, errbuf_len, VR_ERR_CUDA, "kernel launch", e);
+    }
+    if (before >= 0 && before != device) cudaSetDevice(before);
+    return rc;
+}
