@@ -380,6 +380,23 @@ int vr_partition_box_planes(const uint32_t grid[3], const uint32_t full_dims[3],
 int vr_partition_order_planes(const uint32_t grid[3], const uint32_t full_dims[3], const uint32_t *planes,
                               const float camera_position[3], uint32_t *out);
 
+/* ---- one sort-last frame of one rank in ONE call (one process per GPU) --------------------------------------
+ * What multigpu.SortLast.render enqueues per frame -- split planes, owned box, view order, screen rectangles, the
+ * waits / march / signals on the march stream, the waits / merge / signals on the merge stream, the display rank's
+ * present hand-off -- as one host call: at eight ranks a frame is 0.2 ms, and a dozen calls through a scripting
+ * host cost as much.  Counters (indices into each rank's flag block, the layout multigpu.py documents):
+ * ready 256 + slot * 32 + r, read-done 384 + slot * 32 + r, range-done 512 + slot * 32 + r, consumed 640 + slot. */
+typedef struct vr_sort_last_wiring {
+    uint32_t rank, world, display, slots;
+    uint32_t grid[3], full[3], margin[3]; /* margin 0: fixed regular split (vr_partition_balance otherwise) */
+    void *const *flags;                    /* [world]: every rank's flag block, local or peer-mapped */
+    void *const *raw;                      /* [slots * world]: float4 partial of rank r in slot s at raw[s * world + r] */
+    void *const *image;                    /* [slots]: the display rank's RGBA8 target of slot s, local or peer-mapped */
+    uint64_t pixel_begin, pixel_end;       /* the pixel range this rank merges */
+} vr_sort_last_wiring;
+int vr_sort_last_frame(vr_ctx *ctx, const vr_sort_last_wiring *wiring, uint64_t frame, const float camera_position[3],
+                       void *march_stream, void *merge_stream, void *present_stream);
+
 /* ---- one process driving several GPUs (the C++ multi-GPU host; csrc/group.cu) ------------------------------
  * The reference constructs one pass (src/rendering/vulkan_context.cpp:51) and records it once per frame
  * (src/rendering/main_pass.cpp:91); a group stands in the same place with one context per device.  Mutators apply

@@ -29,6 +29,14 @@ class Stats(C.Structure):
                 ("n_fetch", C.c_uint64)]
 
 
+class SortLastWiring(C.Structure):
+    """vr_sort_last_wiring (include/vr.h)"""
+    _fields_ = [("rank", C.c_uint32), ("world", C.c_uint32), ("display", C.c_uint32), ("slots", C.c_uint32),
+                ("grid", C.c_uint32 * 3), ("full", C.c_uint32 * 3), ("margin", C.c_uint32 * 3),
+                ("flags", C.POINTER(C.c_void_p)), ("raw", C.POINTER(C.c_void_p)), ("image", C.POINTER(C.c_void_p)),
+                ("pixel_begin", C.c_uint64), ("pixel_end", C.c_uint64)]
+
+
 class FrameInfo(C.Structure):
     _fields_ = [("layout", C.c_int32), ("pair_axis", C.c_int32), ("empty_skip_active", C.c_int32), ("exact_sampler", C.c_int32),
                 ("bbox", C.c_uint32 * 4), ("march_blocks", C.c_uint32), ("clear_blocks", C.c_uint32), ("target_bytes", C.c_uint64)]
@@ -118,6 +126,7 @@ SIGNATURES = {
     "vr_partition_box": (C.c_int, [_P, _P, C.c_uint32, _P, _P]),
     "vr_partition_order": (C.c_int, [_P, _P, _P, _P]),
     "vr_set_owned_box": (C.c_int, [_P, _P, _P]),
+    "vr_sort_last_frame": (C.c_int, [_P, C.POINTER(SortLastWiring), C.c_uint64, _P, _P, _P, _P]),
     "vr_minmax_static_max_count": (C.c_uint64, []),
     "vr_minmax_static": (C.c_int, [C.c_int, _P, C.c_int, C.c_uint64, _P, _P, C.c_char_p, C.c_size_t]),
     "vr_partition_stored_box": (C.c_int, [_P, _P, C.c_uint32, _P, _P, _P]),

@@ -1825,6 +1825,60 @@ extern "C" int vr_composite_to(vr_ctx *c, const void *const *parts, uint32_t npa
     return vr_composite_rects(c, parts, nullptr, nparts, pixel_begin, pixel_end, out_rgba8, cuda_stream);
 }
 
+extern "C" int vr_sort_last_frame(vr_ctx *c, const vr_sort_last_wiring *w, uint64_t k, const float cam[3], void *march_stream,
+                                  void *merge_stream, void *present_stream)
+{
+    if (!c || !w || !cam || !w->flags || !w->raw || !w->image || w->world == 0 || w->world > 31 || w->rank >= w->world || w->display >= w->world ||
+        w->slots == 0 || w->slots > VR_MAX_FRAMES_IN_FLIGHT)
+        return fail(c, VR_ERR_INVALID, "vr_sort_last_frame: bad wiring");
+    if (!c->sort_last) return fail(c, VR_ERR_STATE, "vr_sort_last_frame: call vr_set_partition_sort_last first");
+    const uint32_t n = w->world, S = w->slots, s = (uint32_t)(k % S), rank = w->rank, disp = w->display;
+    const uint32_t READY = 256, READ_DONE = 384, RANGE_DONE = 512, CONSUMED = 640; /* multigpu.py _L_* */
+    auto flag = [&](uint32_t r, uint32_t index) { return (void *)(static_cast<char *>(w->flags[r]) + 4 * (size_t)index); };
+    if ((uint64_t)w->grid[0] * w->grid[1] * w->grid[2] != n) return fail(c, VR_ERR_INVALID, "vr_sort_last_frame: grid does not match the world size");
+    /* this frame's planes, boxes, order and rectangles: pure functions of the camera, the same on every rank */
+    uint32_t planes[3 * 32], order[32], rects[4 * 32], box[32][6];
+    const bool balanced = w->margin[0] || w->margin[1] || w->margin[2];
+    if (balanced && vr_partition_balance(w->grid, w->full, cam, w->margin, planes) != VR_OK) return fail(c, VR_ERR_INVALID, "vr_partition_balance failed");
+    for (uint32_t r = 0; r < n; r++)
+        if (vr_partition_box_planes(w->grid, w->full, balanced ? planes : nullptr, r, &box[r][0], &box[r][3]) != VR_OK)
+            return fail(c, VR_ERR_INVALID, "vr_partition_box_planes failed");
+    if (balanced) {
+        const int rc = vr_set_owned_box(c, &box[rank][0], &box[rank][3]);
+        if (rc != VR_OK) return rc;
+    }
+    if (vr_partition_order_planes(w->grid, w->full, balanced ? planes : nullptr, cam, order) != VR_OK) return fail(c, VR_ERR_INVALID, "vr_partition_order failed");
+    const void *parts[32];
+    for (uint32_t i = 0; i < n; i++) {
+        subbox_screen_rect(c, w->full, &box[order[i]][0], &box[order[i]][3], &rects[4 * i]);
+        parts[i] = w->raw[(size_t)s * n + order[i]];
+    }
+    const uint32_t frame_no = (uint32_t)(k + 1), freed = (uint32_t)(k + 1 - S);
+    int rc;
+    /* march stream: my partial slot has been merged by everyone (frame k - S), then K1, then "ready" to all */
+    if (k >= S && (rc = vr_stream_wait(c, flag(rank, READ_DONE + s * 32), n, freed, 10000, march_stream)) != VR_OK) return rc;
+    if ((rc = vr_render_frame(c, s, march_stream)) != VR_OK) return rc;
+    void *sig[33];
+    for (uint32_t r = 0; r < n; r++) sig[r] = flag(r, READY + s * 32 + rank);
+    if ((rc = vr_stream_signal(c, sig, n, frame_no, march_stream)) != VR_OK) return rc;
+    /* merge stream: every partial of frame k complete, image slot s presented (frame k - S), then K2 on my range */
+    if ((rc = vr_stream_wait(c, flag(rank, READY + s * 32), n, frame_no, 10000, merge_stream)) != VR_OK) return rc;
+    if (k >= S && (rc = vr_stream_wait(c, flag(rank, CONSUMED + s), 1, freed, 10000, merge_stream)) != VR_OK) return rc;
+    if (w->pixel_end > w->pixel_begin &&
+        (rc = vr_composite_rects(c, parts, rects, n, w->pixel_begin, w->pixel_end, w->image[s], merge_stream)) != VR_OK)
+        return rc;
+    for (uint32_t r = 0; r < n; r++) sig[r] = flag(r, READ_DONE + s * 32 + rank);
+    sig[n] = flag(disp, RANGE_DONE + s * 32 + rank);
+    if ((rc = vr_stream_signal(c, sig, n + 1, frame_no, merge_stream)) != VR_OK) return rc;
+    if (rank == disp) {
+        /* the frame is complete in image slot s once every range has been merged; then the slot is free again */
+        if ((rc = vr_stream_wait(c, flag(rank, RANGE_DONE + s * 32), n, frame_no, 10000, present_stream)) != VR_OK) return rc;
+        for (uint32_t r = 0; r < n; r++) sig[r] = flag(r, CONSUMED + s);
+        if ((rc = vr_stream_signal(c, sig, n, frame_no, present_stream)) != VR_OK) return rc;
+    }
+    return VR_OK;
+}
+
 extern "C" int vr_partition_screen_rect(const vr_ctx *c, const uint32_t full_dims[3], const uint32_t org[3], const uint32_t dims[3],
                                         uint32_t rect[4])
 {

@@ -18,6 +18,8 @@ plain functions so it is testable with the gloo backend.
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 
@@ -243,6 +245,21 @@ class SortLast:
             self._merge = torch.cuda.Stream()
             if rank == display_rank:
                 self._present = torch.cuda.Stream(priority=_present_priority())
+            # the whole frame as one host call (vr_sort_last_frame): the wiring it needs, kept alive here
+            import ctypes as C
+            from . import _lib
+            w = _lib.SortLastWiring()
+            w.rank, w.world, w.display, w.slots = rank, world, display_rank, self.slots
+            for i in range(3):
+                w.grid[i], w.full[i], w.margin[i] = self.grid[i], self.full[i], self.margin[i]
+            self._w_flags = (C.c_void_p * world)(*self._flags.base)
+            self._w_raw = (C.c_void_p * (self.slots * world))(*[self._peers_raw[s][r] for s in range(self.slots) for r in range(world)])
+            self._w_img = (C.c_void_p * self.slots)(*[(self._own_img[s] if rank == display_rank else self._peer_img[s]) for s in range(self.slots)])
+            w.flags = C.cast(self._w_flags, C.POINTER(C.c_void_p))
+            w.raw = C.cast(self._w_raw, C.POINTER(C.c_void_p))
+            w.image = C.cast(self._w_img, C.POINTER(C.c_void_p))
+            w.pixel_begin, w.pixel_end = self.ranges[rank]
+            self._wiring = w
             dist.barrier(group)
 
     def set_global_density_range(self):
@@ -269,6 +286,18 @@ class SortLast:
         import torch.distributed as dist
         from . import partition_balance, partition_box_planes, partition_order
         op, rank, world = self.op, self.rank, self.world
+        if world > 1 and self.mode == "p2p" and self.on_frame is None and os.environ.get("VR_SL_HOST", "c") == "c":
+            # the frame in one call into the library (the steps below, enqueued by vr_sort_last_frame)
+            import ctypes as C
+            import numpy as np
+            from . import lib
+            k = self._k
+            self._k += 1
+            cam = np.ascontiguousarray(camera_position, np.float32)
+            ps = self._present.cuda_stream if rank == self.display else None
+            op._check(lib.vr_sort_last_frame(op._h, C.byref(self._wiring), k, cam.ctypes.data_as(C.c_void_p), stream,
+                                             self._merge.cuda_stream, ps))
+            return
         if self.balanced:
             # the same planes on every rank (a pure function of the camera), then each rank's box of this frame
             self._planes = partition_balance(self.grid, self.full, camera_position, self.margin)
