@@ -141,6 +141,32 @@ class Oracle:
             raise RuntimeError(f"vro_render failed: {rc}")
         return dict(rgba8=rgba8, raw=raw, iters=iters, stats=st)
 
+    # -- pre-integrated classification (port only: no reference counterpart) -----
+    def preint_table(self, lut: np.ndarray, substeps: int) -> np.ndarray:
+        lut = np.ascontiguousarray(lut, np.uint32)
+        n = len(lut)
+        tab = np.zeros((n, n, 4), np.float32)
+        self.lib.vro_preint_table.restype = C.c_int
+        self.lib.vro_preint_table.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+        rc = self.lib.vro_preint_table(lut.ctypes.data, n, substeps, tab.ctypes.data)
+        if rc != 0:
+            raise RuntimeError(f"vro_preint_table failed: {rc}")
+        return tab
+
+    def render_preint(self, frame: Frame, volume: np.ndarray, lut: np.ndarray, substeps: int, nthreads=0):
+        assert volume.ndim == 3 and volume.flags.c_contiguous
+        vol = Volume(volume.ctypes.data, _DTYPE_OF[volume.dtype], volume.shape[2], volume.shape[1], volume.shape[0])
+        lut = np.ascontiguousarray(lut, np.uint32)
+        H, W = frame.height, frame.width
+        rgba8 = np.zeros((H, W, 4), np.uint8)
+        raw = np.zeros((H, W, 4), np.float32)
+        self.lib.vro_render_preint.restype = C.c_int
+        self.lib.vro_render_preint.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
+        rc = self.lib.vro_render_preint(C.byref(frame), C.byref(vol), lut.ctypes.data, len(lut), substeps, rgba8.ctypes.data, raw.ctypes.data, nthreads)
+        if rc != 0:
+            raise RuntimeError(f"vro_render_preint failed: {rc}")
+        return dict(rgba8=rgba8, raw=raw)
+
     # -- data ------------------------------------------------------------------
     def load_nrrd(self, path: str):
         dims = (C.c_uint32 * 3)()

@@ -73,6 +73,12 @@ int vro_render_rows(const vro_frame *frame, const vro_volume *vol, const uint32_
                     uint8_t *rgba8, float *raw, uint16_t *iters, vro_stats *stats, int nthreads,
                     uint32_t row_start, uint32_t row_stride);
 
+/* Pre-integrated classification (oracle/preint.c; port build only -- the mode has no counterpart in the reference).
+ * table: n * n entries of (premultiplied rgb, opacity), entry (back j, front i) at table[4 * (j * n + i)]. */
+int vro_preint_table(const uint32_t *lut, uint32_t nlut, uint32_t substeps, float *table);
+int vro_render_preint(const vro_frame *frame, const vro_volume *vol, const uint32_t *lut, uint32_t nlut, uint32_t substeps,
+                      uint8_t *rgba8, float *raw, int nthreads);
+
 /* Orbit camera (src/scene/camera.cpp:7-48). */
 typedef struct vro_camera vro_camera;
 vro_camera *vro_camera_new(void);
