@@ -199,6 +199,9 @@ def run_ours(args):
         fi = op.last_frame_info()
         info[k] = (fi.layout, fi.pair_axis, fi.empty_skip_active)
     op.set_options(collect_stats=0, **prod)
+    if args.preintegration:
+        # optional quality mode (changes the image; not the headline): segments classified from a 2-D table
+        op.set_preintegration(args.preintegration)
     cells, cell_vox, empty = op.occupancy_info()
     total_ref = sum(n_ref[k] for k in my_frames)
     total_exec = sum(n_exec[k] for k in my_frames)
@@ -372,6 +375,7 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {desc}", "volume_dtype": dname, "kernel_version": vr.KERNEL_VERSION,
                        "sampler": "exact(8 point fetches + fp32 lerp)" if args.exact else "hw trilinear",
+                       "preintegration_substeps": args.preintegration,
                        "empty_space_skipping": {"requested": bool(prod["empty_skip"]), "active": bool(ess_active),
                                                 "why": "the context consults the occupancy grid only when >= 25 % of the cells are empty",
                                                 "screen_space_mask": mask_info},
@@ -817,6 +821,8 @@ def main():
     ap.add_argument("--exact", action="store_true", help="verification sampler instead of hardware trilinear")
     ap.add_argument("--no-ess", action="store_true")
     ap.add_argument("--no-ert", action="store_true")
+    ap.add_argument("--preintegration", type=int, default=0, help="time the pre-integrated classification mode with this many sub-samples "
+                    "(quality mode, changes the image; use with --no-cpu-baseline --no-partitioned)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-partitioned", action="store_true", help="c2: leave out the partitioned record (configs 4/5 evidence)")
     ap.add_argument("--in-flight", type=int, default=3, help="frames in flight (streams), 1..4")

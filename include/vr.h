@@ -211,6 +211,24 @@ int vr_set_gradient(vr_ctx *ctx, const float *color_markers, uint32_t nc, const 
 /* The packed texels in use (rgba8_srgb may be NULL to query n). */
 int vr_get_transfer_function(vr_ctx *ctx, uint32_t *rgba8_srgb, uint32_t capacity, uint32_t *n);
 
+/* Pre-integrated classification: an OPTIONAL quality mode with no counterpart in the reference; it
+ * CHANGES the image and is off by default.  The reference classifies every sample on its own
+ * (res/shaders/volume.frag:41-45), which misses features of the transfer function thinner than the scalar difference
+ * between two samples.  With substeps >= 1 the march classifies the SEGMENT between two consecutive samples from an
+ * n x n table (front scalar, back scalar) built on the device from the current transfer function: `substeps`
+ * sub-samples of a linearly varying scalar, opacity-corrected so that a segment of constant scalar gives the
+ * reference's per-sample result exactly.  Entry (back j, front i): sub-samples at LUT coordinates
+ * s_m = (i + 1/2) + (m + 1/2) / substeps * (j - i), each classified by the 1-D sampler (LINEAR, CLAMP_TO_EDGE,
+ * sRGB-decoded), opacity a' = 1 - (1 - a)^(1 / substeps), composited front to back; the march looks the table up
+ * bilinearly at (x = t_front * n, y = t_back * n), clamp to edge, for consecutive in-slice samples (a sample outside
+ * the slices breaks the chain; the first sample of a chain contributes nothing by itself).  Positions, bounds and
+ * slice tests, blend and store are the reference's.  Needs the hardware sampler, a transfer function of at most 1024 texels, the whole
+ * volume (no sort-last partition) and no statistics -- vr_render fails with VR_ERR_STATE otherwise; empty-space
+ * skipping is not used in this mode.  0 switches it off.  vr_get_preintegration_table returns the n * n entries
+ * of (premultiplied rgb, opacity), entry (back j, front i) at table[4 * (j * n + i)]; table may be NULL to query n. */
+int vr_set_preintegration(vr_ctx *ctx, uint32_t substeps);
+int vr_get_preintegration_table(vr_ctx *ctx, float *table, uint32_t capacity_texels, uint32_t *n);
+
 /* The two shader literals ray_dist = 1.8, step_size = 0.005 (res/shaders/volume.frag:29-30)
  * as parameters; steps = int(ray_dist / step_size) in fp32 (:31). */
 int vr_set_march(vr_ctx *ctx, float ray_dist, float step_size);

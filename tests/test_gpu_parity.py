@@ -864,3 +864,124 @@ def test_gradient_discretised_on_the_device_equals_the_host_one(vr, port):
         assert np.array_equal(a.view(np.uint32), op.download_raw().view(np.uint32))
     finally:
         op.close()
+
+
+# ---- pre-integrated classification (optional quality mode, no reference counterpart; oracle/preint.c) -----------------
+
+PREINT_CASES = [
+    # (volume kind, dtype, size, TF, texels, moves, zoom, slices, layout)
+    (1, np.uint16, 48, "B", 256, [(-120, 80)], 0.0, None, "array3d"),
+    (1, np.uint16, 48, "B", 256, [(-120, 80)], 0.0, None, "paired"),
+    (2, np.uint16, 40, "C", 256, [(45, 30)], 0.0, None, "array3d"),
+    (0, np.uint8, 32, "A", 64, [(37, -21)], 1.0, None, "paired"),
+    (1, np.uint16, 48, "B", 256, [(200, 10)], 1.2, ((0.2, 0.1, 0.3), (0.9, 0.8, 0.7)), "array3d"),
+    (1, np.float32, (33, 20, 7), "B", 100, [(10, 55)], 0.5, None, "array3d"),
+]
+
+
+@pytest.mark.parametrize("case", PREINT_CASES, ids=[f"{c[3]}-{c[1].__name__}-{c[8]}-{i}" for i, c in enumerate(PREINT_CASES)])
+def test_preintegrated_mode_matches_its_oracle(vr, port, case):
+    """vr_set_preintegration: the table built on the device equals the oracle's (double on the CPU) to 1e-5, and the frame
+    is within the hardware-sampler tolerance of the oracle's pre-integrated frame (same positions and tests as the
+    reference loop, segments classified from the table)."""
+    kind, dt, size, tfn, texels, moves, zoom, slices, layout = case
+    vol = small_volume(port, kind, dt, size)
+    lut = tf(port, tfn, texels)
+    mn, mx = float(vol.min()), float(vol.max())
+    cam, ocam = twin_cameras(vr, port, moves, zoom)
+    lo, hi = slices if slices else ((0, 0, 0), (1, 1, 1))
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_volume_layout(vr.LAYOUT_PAIRED if layout == "paired" and dt != np.float32 else vr.LAYOUT_ARRAY3D)
+        op.set_options(sampler=vr.SAMPLER_HW, write_raw=1, empty_skip=1, early_term=0)
+        op.volume_dataset_changed(vr.Dataset(vol, mn, mx))
+        op.transfer_function_changed(lut)
+        op.slicing_changed(lo, hi)
+        op.set_camera(cam)
+        op.record()
+        plain = op.download()
+        op.set_preintegration(8)
+        tab = op.preintegration_table()
+        want_tab = port.preint_table(lut, 8)
+        assert tab.shape == want_tab.shape and np.abs(tab - want_tab).max() < 1e-5
+        op.record()
+        img, raw = op.download(), op.download_raw()
+        want = port.render_preint(oracle_frame(port, ocam, W, H, mn, mx, lo, hi), vol, lut, 8)
+        assert_within_tolerance(img, want["rgba8"], "pre-integrated frame")
+        assert np.abs(raw - want["raw"]).max() < 2.5e-2
+        # another sub-sample count rebuilds the table; switching the mode off gives the plain frame back, bit for bit
+        op.set_preintegration(2)
+        assert np.abs(op.preintegration_table() - port.preint_table(lut, 2)).max() < 1e-5
+        op.set_preintegration(0)
+        op.record()
+        assert np.array_equal(op.download(), plain)
+    finally:
+        op.close()
+
+
+def test_preintegration_sees_a_feature_the_samples_step_over(vr, port):
+    """What the mode is for: a transfer function with a thin opaque feature and a coarse step (0.02: 90 steps).  Per-sample
+    classification only sees the feature where a sample happens to fall on it; segments always cross it.  The
+    pre-integrated frame carries clearly more opacity than the per-sample frame (the oracle says how much), and the mode
+    follows a new transfer function (the table is rebuilt)."""
+    vol = small_volume(port, 1, np.uint16, 48)
+    mn, mx = float(vol.min()), float(vol.max())
+    spike = np.zeros(256, np.uint32)
+    spike[127], spike[128], spike[129] = 0x4020C0FF, 0x9920C0FF, 0x4020C0FF     # alpha 0.25 / 0.6 / 0.25, three texels wide
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_options(sampler=vr.SAMPLER_HW, write_raw=1, early_term=0)
+        op.set_march(1.8, 0.02)
+        op.volume_dataset_changed(vr.Dataset(vol, mn, mx))
+        op.transfer_function_changed(spike)
+        cam, ocam = twin_cameras(vr, port, [(-120, 80)])
+        op.set_camera(cam)
+        f = oracle_frame(port, ocam, W, H, mn, mx)
+        f.step_size = 0.02
+        want_plain = port.render(f, vol, spike, want_raw=True)["raw"][..., 3].sum()
+        want = port.render_preint(f, vol, spike, 16)
+        want_pre = want["raw"][..., 3].sum()
+        assert want_pre > 1.1 * want_plain
+        op.record()
+        a = op.download_raw()[..., 3].sum()
+        op.set_preintegration(16)
+        op.record()
+        got = op.download_raw()
+        b = got[..., 3].sum()
+        assert abs(a / want_plain - 1.0) < 1e-2 and abs(b / want_pre - 1.0) < 1e-2, (a, want_plain, b, want_pre)
+        err = np.abs(got - want["raw"])
+        assert np.percentile(err, 99.9) < 2e-2, (float(err.max()), float(np.percentile(err, 99.9)))
+        op.transfer_function_changed(tf(port, "B"))
+        op.record()
+        want = port.render_preint(f, vol, tf(port, "B"), 16)
+        assert_within_tolerance(op.download(), want["rgba8"], "after a transfer-function change")
+    finally:
+        op.close()
+
+
+def test_preintegration_refuses_what_it_does_not_support(vr, port):
+    vol = small_volume(port, 1, np.uint16, 32)
+    op = vr.OffscreenPass(64, 48)
+    try:
+        op.volume_dataset_changed(vr.Dataset(vol, float(vol.min()), float(vol.max())))
+        op.transfer_function_changed(tf(port, "B"))
+        with pytest.raises(vr.VrError):
+            op.set_preintegration(65)
+        with pytest.raises(vr.VrError, match="off"):
+            op.preintegration_table()
+        op.set_preintegration(4)
+        op.set_options(sampler=vr.SAMPLER_EXACT)
+        with pytest.raises(vr.VrError, match="pre-integration needs"):
+            op.record()
+        op.set_options(sampler=vr.SAMPLER_HW, collect_stats=1)
+        with pytest.raises(vr.VrError, match="pre-integration needs"):
+            op.record()
+        op.set_options(sampler=vr.SAMPLER_HW, collect_stats=0)
+        op.transfer_function_changed(np.zeros(2048, np.uint32))
+        with pytest.raises(vr.VrError, match="1024"):
+            op.record()
+        op.transfer_function_changed(tf(port, "B"))
+        op.record()
+        op.download()
+    finally:
+        op.close()

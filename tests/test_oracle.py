@@ -209,3 +209,59 @@ def test_analytic_coverage_and_entry_equal_the_rasterised_cube(port, case):
         on_face = np.take_along_axis(tex, axis_of_face[..., None], axis=-1)[..., 0][both]
         assert np.isin(on_face, (0.0, 1.0)).mean() > 0.999          # (a silhouette pixel may be attributed to the neighbouring face)
         assert (depth[both] >= 0.0).all() and (depth[both] <= 1.0).all()
+
+
+# ---- pre-integrated classification (oracle/preint.c; no reference counterpart) ---------------------------------------
+
+def _decoded(lut):
+    def srgb(c):
+        c = c / 255.0
+        return np.where(c <= 0.04045, c / 12.92, ((c + 0.055) / 1.055) ** 2.4)
+    lin = np.zeros((len(lut), 4))
+    lin[:, 0], lin[:, 1], lin[:, 2] = srgb(lut & 0xff), srgb((lut >> 8) & 0xff), srgb((lut >> 16) & 0xff)
+    lin[:, 3] = ((lut >> 24) & 0xff) / 255.0
+    return lin
+
+
+@pytest.mark.parametrize("name", ["A", "B", "C"])
+def test_preintegration_table_properties(port, name):
+    """The table's definition pinned by its properties: the diagonal (a segment of constant scalar) is the reference's
+    per-sample classification exactly -- (rgb * a, a) of the LUT texel; entries are symmetric in opacity (the product of the
+    sub-transmittances does not depend on the direction); opacity is monotone in the segment's coverage of opaque texels;
+    one sub-sample degenerates to classifying the segment's midpoint."""
+    from common import tf
+    lut = tf(port, name)
+    n = len(lut)
+    lin = _decoded(lut)
+    tab = port.preint_table(lut, 8)
+    d = tab[np.arange(n), np.arange(n)]
+    assert np.abs(d[:, 3] - lin[:, 3]).max() < 1e-6
+    assert np.abs(d[:, :3] - lin[:, :3] * lin[:, 3:4]).max() < 1e-6
+    assert np.abs(tab[..., 3] - tab[..., 3].T).max() < 1e-6
+    assert tab.min() >= 0.0 and tab[..., 3].max() <= 1.0
+    one = port.preint_table(lut, 1)
+    i, j = 10, 200          # midpoint of texel centres 10.5 and 200.5 = 105.5 = centre of texel 105
+    assert np.allclose(one[j, i, 3], lin[105, 3], atol=1e-6) and np.allclose(one[j, i, :3], lin[105, :3] * lin[105, 3], atol=1e-6)
+    # a segment that crosses a thin opaque feature sees it, which the end points alone do not
+    spike = np.zeros(64, np.uint32)
+    spike[31] = 0xFF0000FF
+    t = port.preint_table(spike, 16)
+    assert t[50, 10, 3] > 0.02 and t[10, 10, 3] == 0.0 and t[50, 50, 3] == 0.0
+
+
+def test_preintegrated_render_of_a_constant_volume_equals_the_per_sample_render(port):
+    """Constant scalar at a texel centre: every segment is a diagonal entry = the per-sample classification, so the frame
+    equals the reference loop's frame up to the one sample the first segment of a ray does not have."""
+    from common import oracle_frame, tf
+    lut = tf(port, "B")
+    vol = np.full((16, 16, 16), 180, np.uint8)
+    cam = port.camera()
+    cam.rotate(-120.0, 80.0)
+    # density range chosen so that 180 falls on a texel centre: t * 256 = k + 1/2
+    f = oracle_frame(port, cam, 96, 64, 0.0, 180.0 * 256.0 / 200.5)
+    a = port.render(f, vol, lut, want_raw=True)["raw"]
+    b = port.render_preint(f, vol, lut, 8)["raw"]
+    # interior of the volume only matters: border samples blend with the zero border -> compare where alpha is large
+    m = a[..., 3] > 0.5
+    assert m.any()
+    assert np.abs(a[m] - b[m]).max() < 0.05

@@ -241,6 +241,18 @@ class OffscreenPass:
         bits = np.unpackbits(words[:-1].view(np.uint8), bitorder="little")[: tx.value * ty.value].astype(bool)
         return bits.reshape(ty.value, tx.value), bool(words[-1]), th.value
 
+    def set_preintegration(self, substeps: int):
+        """vr_set_preintegration: classify segments between consecutive samples from a 2-D table (quality mode, changes the
+        image, no reference counterpart); 0 = off."""
+        self._check(lib.vr_set_preintegration(self._h, substeps))
+
+    def preintegration_table(self) -> np.ndarray:
+        n = C.c_uint32(0)
+        self._check(lib.vr_get_preintegration_table(self._h, None, 0, C.byref(n)))
+        tab = np.zeros((n.value, n.value, 4), np.float32)
+        self._check(lib.vr_get_preintegration_table(self._h, _ptr(tab), n.value * n.value, None))
+        return tab
+
     def set_march(self, ray_dist: float, step_size: float):
         self._check(lib.vr_set_march(self._h, ray_dist, step_size))
 

@@ -82,6 +82,8 @@ SIGNATURES = {
     "vr_set_gradient": (C.c_int, [_P, _P, C.c_uint32, _P, C.c_uint32, C.c_uint32]),
     "vr_get_transfer_function": (C.c_int, [_P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
     "vr_set_march": (C.c_int, [_P, C.c_float, C.c_float]),
+    "vr_set_preintegration": (C.c_int, [_P, C.c_uint32]),
+    "vr_get_preintegration_table": (C.c_int, [_P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
     "vr_set_volume_layout": (C.c_int, [_P, C.c_int]),
     "vr_get_volume_layout": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "vr_get_options": (C.c_int, [_P, C.POINTER(Options)]),

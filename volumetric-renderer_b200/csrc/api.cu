@@ -133,6 +133,7 @@ int upload_lut(vr_ctx *c)
     VR_CUDA(c, vr_lut_tables(c->d_lut_rgba8, n, c->d_lut_pad, c->d_lut_dif, c->d_lut_h, c->d_lut_nz, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     c->occ_dirty = true;
+    c->preint_dirty = true;
     return VR_OK;
 }
 
@@ -448,6 +449,10 @@ extern "C" int vr_destroy(vr_ctx *c)
     if (c->d_lut_dif) cudaFree(c->d_lut_dif);
     if (c->d_lut_h) cudaFree(c->d_lut_h);
     if (c->d_lut_nz) cudaFree(c->d_lut_nz);
+    if (c->preint_tex) cudaDestroyTextureObject(c->preint_tex);
+    if (c->preint_array) cudaFreeArray(c->preint_array);
+    if (c->d_preint) cudaFree(c->d_preint);
+    if (c->d_preint_h) cudaFree(c->d_preint_h);
     if (c->d_lut_rgba8) cudaFree(c->d_lut_rgba8);
     if (c->d_lut_loc) cudaFree(c->d_lut_loc);
     if (c->d_markers) cudaFree(c->d_markers);
@@ -664,6 +669,36 @@ extern "C" int vr_get_transfer_function(vr_ctx *c, uint32_t *rgba8, uint32_t cap
     return VR_OK;
 }
 
+namespace
+{
+int prepare_preint(vr_ctx *c, cudaStream_t s);
+}
+
+extern "C" int vr_set_preintegration(vr_ctx *c, uint32_t substeps)
+{
+    if (!c || substeps > 64) return fail(c, VR_ERR_INVALID, "vr_set_preintegration: 0 (off) or 1..64 sub-samples per table entry");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaDeviceSynchronize());
+    if (substeps != c->preint_substeps) c->preint_dirty = true;
+    c->preint_substeps = substeps;
+    return VR_OK;
+}
+
+extern "C" int vr_get_preintegration_table(vr_ctx *c, float *table, uint32_t capacity_texels, uint32_t *n)
+{
+    if (!c) return VR_ERR_INVALID;
+    if (!c->preint_substeps) return fail(c, VR_ERR_STATE, "vr_get_preintegration_table: pre-integration is off");
+    if (c->nlut > VR_PREINT_MAX_TEXELS) return fail(c, VR_ERR_STATE, "vr_get_preintegration_table: at most 1024 texels");
+    if (n) *n = c->nlut;
+    if (!table) return VR_OK;
+    if ((uint64_t)capacity_texels < (uint64_t)c->nlut * c->nlut) return fail(c, VR_ERR_INVALID, "vr_get_preintegration_table: capacity below n * n entries");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    const int rc = prepare_preint(c, c->stream);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaMemcpy(table, c->d_preint, sizeof(float4) * (size_t)c->nlut * c->nlut, cudaMemcpyDeviceToHost));
+    return VR_OK;
+}
+
 extern "C" int vr_set_march(vr_ctx *c, float ray_dist, float step_size)
 {
     if (!c || !(step_size > 0.0f) || !(ray_dist >= 0.0f)) return fail(c, VR_ERR_INVALID, "vr_set_march: bad arguments");
@@ -723,6 +758,38 @@ int prepare_occupancy(vr_ctx *c, cudaStream_t s)
     VR_CUDA(c, cudaStreamSynchronize(s));
     c->occ_empty_cells = c->h_counters[4];
     c->occ_dirty = false;
+    return VR_OK;
+}
+
+/* (re)build the pre-integration table when the transfer function or the sub-sample count changed */
+int prepare_preint(vr_ctx *c, cudaStream_t s)
+{
+    if (!c->preint_dirty && c->preint_tex && c->preint_n == c->nlut) return VR_OK;
+    const uint32_t n = c->nlut;
+    if (c->preint_n != n || !c->preint_tex) {
+        VR_CUDA(c, cudaDeviceSynchronize());
+        if (c->preint_tex) cudaDestroyTextureObject(c->preint_tex), c->preint_tex = 0;
+        if (c->preint_array) cudaFreeArray(c->preint_array), c->preint_array = nullptr;
+        if (c->d_preint) cudaFree(c->d_preint), c->d_preint = nullptr;
+        if (c->d_preint_h) cudaFree(c->d_preint_h), c->d_preint_h = nullptr;
+        c->preint_n = 0;
+        VR_CUDA(c, cudaMalloc(&c->d_preint, sizeof(float4) * (size_t)n * n));
+        VR_CUDA(c, cudaMalloc(&c->d_preint_h, sizeof(uint2) * (size_t)n * n));
+        const cudaChannelFormatDesc fmt = cudaCreateChannelDescHalf4();
+        VR_CUDA(c, cudaMallocArray(&c->preint_array, &fmt, n, n));
+        cudaResourceDesc rd{};
+        rd.resType = cudaResourceTypeArray, rd.res.array.array = c->preint_array;
+        cudaTextureDesc td{};
+        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModeLinear, td.readMode = cudaReadModeElementType, td.normalizedCoords = 0;
+        VR_CUDA(c, cudaCreateTextureObject(&c->preint_tex, &rd, &td, nullptr));
+        c->preint_n = n;
+    }
+    VR_CUDA(c, vr_lut_preint_table(c->d_lut_pad, n, c->preint_substeps, c->d_preint, c->d_preint_h, s));
+    VR_CUDA(c, cudaMemcpy2DToArrayAsync(c->preint_array, 0, 0, c->d_preint_h, sizeof(uint2) * n, sizeof(uint2) * n, n, cudaMemcpyDeviceToDevice, s));
+    /* frames in flight on other streams may still sample the old table: like a transfer-function change, this waits */
+    VR_CUDA(c, cudaStreamSynchronize(s));
+    c->preint_dirty = false;
     return VR_OK;
 }
 
@@ -943,6 +1010,18 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
      * reproduces the oracle's definition of that case */
     const bool exact = c->opt.sampler == VR_SAMPLER_EXACT || !nondegenerate;
     bool ess = c->opt.empty_skip && nondegenerate;
+    const bool preint = c->preint_substeps != 0;
+    if (preint) {
+        /* pre-integrated classification (vr_set_preintegration): segments between consecutive samples, so every step is
+         * walked (no skipping); hardware sampler, whole volume, no statistics */
+        if (exact || c->sort_last || c->opt.collect_stats || c->bench_fetch_only)
+            return fail(c, VR_ERR_STATE, "vr_render: pre-integration needs the hardware sampler, a density range > 0, the whole volume (no sort-last "
+                                         "partition) and no statistics");
+        if (c->nlut > VR_PREINT_MAX_TEXELS) return fail(c, VR_ERR_STATE, "vr_render: pre-integration takes transfer functions of at most 1024 texels");
+        ess = false;
+        const int rc = prepare_preint(c, s);
+        if (rc != VR_OK) return rc;
+    }
     if (ess) {
         const int rc = prepare_occupancy(c, s);
         if (rc != VR_OK) return rc;
@@ -1119,6 +1198,11 @@ extern "C" int vr_render_frame(vr_ctx *c, uint32_t frame_index, void *cuda_strea
         p.tile_mask = mask, p.mask_words = words;
         c->slot_mask_valid[frame_index] = true;
         c->slot_mask_shape[frame_index][0] = p.ntx, c->slot_mask_shape[frame_index][1] = p.nty, c->slot_mask_shape[frame_index][2] = p.tile_h;
+    }
+    if (preint) {
+        p.tex_pre = c->preint_tex;
+        VR_CUDA(c, vr_launch_march_preint(p, pair, c->tune_threads, s));
+        return VR_OK;
     }
     if (c->bench_fetch_only) {
         if (exact || ess || c->opt.collect_stats || c->sort_last || (pair && p.pair_split != 0x10000))

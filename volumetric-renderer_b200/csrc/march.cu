@@ -208,6 +208,9 @@ struct Ray {
      * so that every rank computes the same position for step i wherever it starts walking (see outer_interval) */
     float ex, ey, ez, fi;
     int i_end;             /* last step that can still be sampled (sort-last: where the ray leaves the rank's box) */
+    /* pre-integrated classification (PRE): table coordinate of the sample before this one, and whether there is one */
+    float prev;
+    bool prev_ok;
 };
 
 /* volume.frag:47, `ray_pos += ray_dir * step`.  FUNC (sort-last + hardware sampler): the same position evaluated as
@@ -439,7 +442,7 @@ __device__ __forceinline__ void batch_issue(const MarchParams &p, Ray &r, Batch<
 }
 
 /* Second half: normalise, transfer function, composite (volume.frag:42-45). */
-template <bool EXACT, bool STATS, int PAIR, int U, bool PRED, bool ERT = true, bool PROBE = false>
+template <bool EXACT, bool STATS, int PAIR, int U, bool PRED, bool ERT = true, bool PROBE = false, bool PRE = false>
 __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batch<U> &b, const float4 *sP,
                                               const LutH &L)
 {
@@ -473,6 +476,21 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
                     r.cr += dens;
                     continue;
                 }
+                if (PRE) {
+                    /* pre-integrated classification (no reference counterpart; defined in include/vr.h): the SEGMENT between the
+                     * sample before and this one is looked up in the 2-D table -- x = front, y = back, unnormalised LUT
+                     * coordinates t * n (= the padded-table coordinate of lut_eval), clamp to edge, NaN -> 0 */
+                    const float tc = fminf(fmaxf(fmaf(dens, L.A, L.Bh), 0.0f), (float)p.nlut);
+                    if (r.prev_ok) {
+                        const float4 sg4 = tex2D<float4>(p.tex_pre, r.prev, tc);
+                        r.cr = fmaf(r.T, sg4.x, r.cr);
+                        r.cg = fmaf(r.T, sg4.y, r.cg);
+                        r.cb = fmaf(r.T, sg4.z, r.cb);
+                        r.T = fmaf(-r.T, sg4.w, r.T);
+                    }
+                    r.prev = tc, r.prev_ok = true;
+                    continue;
+                }
                 lut_eval(L, dens, sr, sg, sb, sa);
                 const float ta = r.T * sa;
                 r.cr = fmaf(ta, sr, r.cr);
@@ -480,6 +498,8 @@ __device__ __forceinline__ void batch_consume(const MarchParams &p, Ray &r, Batc
                 r.cb = fmaf(ta, sb, r.cb);
                 r.T = fmaf(-r.T, sa, r.T);
             }
+        } else if (PRE && PRED && !(b.ok[u])) {
+            r.prev_ok = false; /* a step outside the slices (or past the end) breaks the chain of segments */
         }
     }
     /* the hardware path tests for early termination once per batch: the samples composited past
@@ -529,8 +549,8 @@ __device__ __forceinline__ bool tile_of_block(const MarchParams &p, uint32_t blo
 /* EXACT: verification sampler.  ESS: occupancy grid consulted.  STATS: sample counters.
  * PART: sort-last sub-volume.  PAIR: 0 = 3-D array, 1 = paired layout, 2 = paired layout whose copy spans
  * two layered arrays.  UB: steps per batch (HW sampler; two batches are in flight). */
-template <bool EXACT, bool ESS, bool STATS, bool PART, int PAIR, int UB, bool PROBE = false>
-__global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART || UB > 2) ? 1 : VR_MIN_BLOCKS) k_march(const __grid_constant__ MarchParams p)
+template <bool EXACT, bool ESS, bool STATS, bool PART, int PAIR, int UB, bool PROBE = false, bool PRE = false>
+__global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART || PRE || UB > 2) ? 1 : VR_MIN_BLOCKS) k_march(const __grid_constant__ MarchParams p)
 {
     extern __shared__ float4 smem[];
     float4 *sP = smem;                              /* EXACT: nlut + 3 decoded texels */
@@ -664,7 +684,7 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
     Ray ray;
     ray.cr = cr, ray.cg = cg, ray.cb = cb, ray.T = T;
     ray.px = posx, ray.py = posy, ray.pz = posz, ray.dx = dx, ray.dy = dy, ray.dz = dz;
-    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.sgx = ray.sgy = ray.sgz = 1.0f, ray.doff = 0u, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
+    ray.i = 0, ray.done = !covered, ray.stop = false, ray.ifx = ray.ify = ray.ifz = 0.0f, ray.sgx = ray.sgy = ray.sgz = 1.0f, ray.doff = 0u, ray.prev = 0.0f, ray.prev_ok = false, ray.in_empty = true, ray.nb = 0, ray.ns = 0, ray.nf = 0;
 
     ray.ex = posx, ray.ey = posy, ray.ez = posz, ray.fi = 0.0f, ray.i_end = p.steps - 1;
     if (PART && !EXACT && covered) {
@@ -714,8 +734,8 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
     } while (0)
 #define VR_CONSUME(B_)                                                                                      \
     do {                                                                                                    \
-        if (B_.pred) batch_consume<EXACT, STATS, PAIR, U, true, true, PROBE>(p, ray, B_, sP, L);            \
-        else batch_consume<EXACT, STATS, PAIR, U, false, true, PROBE>(p, ray, B_, sP, L);                   \
+        if (B_.pred) batch_consume<EXACT, STATS, PAIR, U, true, true, PROBE, PRE>(p, ray, B_, sP, L);       \
+        else batch_consume<EXACT, STATS, PAIR, U, false, true, PROBE, PRE>(p, ray, B_, sP, L);              \
     } while (0)
     if (EXACT) {
         Batch<U> a;
@@ -747,12 +767,12 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
 #pragma unroll 1
                 for (int it = 0; it < nb; it++) {
                     batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, b);
-                    batch_consume<false, STATS, PAIR, U, false, false, PROBE>(p, ray, a, sP, L);
+                    batch_consume<false, STATS, PAIR, U, false, false, PROBE, PRE>(p, ray, a, sP, L);
                     batch_issue<false, false, STATS, PART, PAIR, U, false, false>(p, ray, a);
-                    batch_consume<false, STATS, PAIR, U, false, false, PROBE>(p, ray, b, sP, L);
+                    batch_consume<false, STATS, PAIR, U, false, false, PROBE, PRE>(p, ray, b, sP, L);
                     if (__all_sync(0xffffffffu, ray.T < p.ert_eps)) break; /* parked lanes: T = 0 (never true when ERT is off: nb bounds the loop) */
                 }
-                batch_consume<false, STATS, PAIR, U, false, false, PROBE>(p, ray, a, sP, L);
+                batch_consume<false, STATS, PAIR, U, false, false, PROBE, PRE>(p, ray, a, sP, L);
                 if (!ray.done && ray.T < p.ert_eps) ray.stop = true, ray.done = true;
                 continue;
             }
@@ -883,6 +903,19 @@ cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int ub, int t
         if (pair) k_march<false, false, false, false, 1, 2, true><<<(unsigned)ctas, threads, smem, s>>>(p);
         else k_march<false, false, false, false, 0, 2, true><<<(unsigned)ctas, threads, smem, s>>>(p);
     }
+    return cudaGetLastError();
+}
+
+/* pre-integrated classification: hardware sampler, no skipping, no statistics, no sub-volume; 2 steps per batch */
+cudaError_t vr_launch_march_preint(const MarchParams &p, bool pair, int threads, cudaStream_t s)
+{
+    const uint64_t ctas = (uint64_t)p.sp_count + (uint64_t)p.nclr_x * p.nclr_y;
+    if (ctas == 0) return cudaSuccess;
+    if (ctas > 0x7fffffffull) return cudaErrorInvalidConfiguration;
+    const size_t smem = vr_march_smem_bytes(p, false);
+    if (pair && p.pair_split != 0x10000) k_march<false, false, false, false, 2, 2, false, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+    else if (pair) k_march<false, false, false, false, 1, 2, false, true><<<(unsigned)ctas, threads, smem, s>>>(p);
+    else k_march<false, false, false, false, 0, 2, false, true><<<(unsigned)ctas, threads, smem, s>>>(p);
     return cudaGetLastError();
 }
 

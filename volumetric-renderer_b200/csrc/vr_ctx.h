@@ -13,6 +13,7 @@
 #include "../../include/vr.h"
 
 #define VR_KERNEL_VERSION "r2.v10" /* bump when K1 changes: profiles/traffic.json is keyed by it */
+#define VR_PREINT_MAX_TEXELS 1024 /* pre-integration table: n x n float4, 16 MiB at most */
 #define VR_TILE 16        /* a CTA marches a 16x16 pixel tile: 8 warps of 8x4 pixels */
 #define VR_CTA_THREADS 256
 #define VR_BATCH 4        /* steps whose fetches are issued back to back before compositing */
@@ -45,6 +46,7 @@ struct MarchParams {
      * space (u, v, w): every per-axis field of this block is stored in that order by the host, and the
      * kernel permutes the ray's entry position and direction once (pair_axis). */
     cudaTextureObject_t tex_pair;
+    cudaTextureObject_t tex_pre;     /* pre-integrated classification: n x n half4 (premultiplied rgb, opacity), x = front, y = back */
     cudaTextureObject_t tex_pair_hi; /* layers >= pair_split live in a second array (2048-layer limit of layered arrays) */
     int pair_split;                  /* 0x10000 when one array holds them all */
     int pair_axis;              /* model axis of w: 2 (identity), 1: (u,v,w) = (x,z,y), 0: (u,v,w) = (y,z,x) */
@@ -159,6 +161,13 @@ struct vr_ctx {
     uint32_t *d_lut_nz = nullptr;    /* nz[k] = padded texels before k with alpha != 0 (nlut + 4 entries): k_classify */
     float *d_markers = nullptr;      /* gradient markers of vr_set_gradient */
     uint32_t lut_texels_cap = 0, lut_tables_cap = 0;
+    /* pre-integrated classification (vr_set_preintegration): 0 = off, else sub-samples per table entry */
+    uint32_t preint_substeps = 0, preint_n = 0;
+    bool preint_dirty = true;
+    float4 *d_preint = nullptr;        /* the table in fp32 (vr_get_preintegration_table) */
+    uint2 *d_preint_h = nullptr;       /* the table as four fp16 per entry, copied into the array below */
+    cudaArray_t preint_array = nullptr;
+    cudaTextureObject_t preint_tex = 0;
     size_t markers_cap = 0;
     float4 *d_lut_pad = nullptr, *d_lut_dif = nullptr;
     uint4 *d_lut_h = nullptr;
@@ -221,6 +230,7 @@ struct vr_ctx {
 /* ---- kernels / device-side stages (each .cu implements its own) ---- */
 
 /* K1 (march.cu) */
+cudaError_t vr_launch_march_preint(const MarchParams &p, bool pair, int threads, cudaStream_t s);
 cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int ub, int threads, cudaStream_t s);
 cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, bool pair, int ub,
                             int threads, cudaStream_t s);
@@ -233,6 +243,7 @@ cudaError_t vr_k0_cell_ranges(const void *dev, int dtype, uint32_t nx, uint32_t 
 /* lut.cu: the transfer function built on the device */
 cudaError_t vr_lut_upload_srgb_table(const float table[256]);
 cudaError_t vr_lut_gradient(const float *d_markers, uint32_t nc, uint32_t na, uint32_t count, float *d_loc, uint32_t *d_texels, cudaStream_t s);
+cudaError_t vr_lut_preint_table(const float4 *d_pad, uint32_t n, uint32_t substeps, float4 *d_table, uint2 *d_table_h, cudaStream_t s);
 cudaError_t vr_lut_tables(const uint32_t *d_texels, uint32_t n, float4 *d_pad, float4 *d_dif, uint4 *d_h, uint32_t *d_nz, cudaStream_t s);
 cudaError_t vr_k0_classify(const float2 *d_ranges, const int occ_n[3], const uint32_t *d_lut_nz, uint32_t nlut,
                            float min_density, float max_density, uint32_t *d_occ, int occ_words,

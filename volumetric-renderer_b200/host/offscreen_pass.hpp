@@ -143,6 +143,8 @@ class OffscreenPass
         for (const auto &m : gradient.alpha_markers) am.insert(am.end(), {m.location, m.value});
         check(vr_set_gradient(ctx, cm.data(), (uint32_t)gradient.color_markers.size(), am.data(), (uint32_t)gradient.alpha_markers.size(), count));
     }
+    // optional quality mode, no reference counterpart: classify segments between samples from a 2-D table (0 = off)
+    void set_preintegration(uint32_t substeps) { check(vr_set_preintegration(ctx, substeps)); }
     // get_image_view() / get_sampler(): the colour attachment as a device pointer + pitch
     std::pair<void *, size_t> get_image_view(uint32_t frame_index = 0) const
     {
