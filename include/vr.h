@@ -177,9 +177,23 @@ int vr_set_volume_device(vr_ctx *ctx, const void *dev_data, int dtype, uint32_t 
  * native reader: 3-D scalar NRRD/NHDR, raw/ascii/hex encoding, any of the ten scalar
  * types (u8/u16 stay native on the device, the rest are widened to float like :49-77). */
 int vr_load_nrrd(vr_ctx *ctx, const char *path);
+/* Non-cubic voxels (SURVEY.md 8(f).1's extension; off by default).  The reference ignores the `spacings` /
+ * `space directions` of a file (src/data/nrrd_file_parser.cpp:32-33) and always draws the unit cube, and so do an
+ * upload and vr_load_nrrd here.  vr_set_volume_spacing(ctx, s) makes the volume fill the box [-e/2, e/2] with
+ * e_i = n_i s_i / max_j (n_j s_j) instead (n = the volume's dimensions, also of later uploads; NULL = back to the
+ * unit cube): the cube is drawn scaled, rays are normalised and stepped in physical space -- step_size is the same
+ * physical distance whichever way a ray points -- and everything else is the reference's loop (with s such that
+ * e = (1, 1, 1) the frame is the reference's bit for bit).  vr_get_volume_spacing returns what the NRRD loaded last
+ * states per axis (NaN where it states nothing) and the extents in use.  The partition helpers (vr_partition_order,
+ * vr_partition_balance) take the camera in the unit cube's coordinates: camera_position / e. */
+int vr_set_volume_spacing(vr_ctx *ctx, const float spacing[3]);
+int vr_get_volume_spacing(const vr_ctx *ctx, float file_spacing[3], float extent[3]);
 /* The reader alone, no context and no GPU: dtype/dims/data as vr_load_nrrd would upload them.
  * *data is malloc'd (release with vr_free_host); errbuf receives the message on failure. */
 int vr_nrrd_read_host(const char *path, int *dtype, uint32_t dims[3], void **data, char *errbuf, size_t errbuf_len);
+/* The header's per-axis sample distances alone: `spacings`, or the length of the axis's `space directions` vector; NaN
+ * where the header states none (what vr_get_volume_spacing reports after vr_load_nrrd). */
+int vr_nrrd_read_spacing(const char *path, double spacing[3], char *errbuf, size_t errbuf_len);
 void vr_free_host(void *p);
 /* CsvFileParser::parse + volume_dataset_changed (src/data/importer.cpp:30-46, src/data/csv_file_parser.cpp:14-50):
  * one CSV file per z slice, one line per y row, comma-separated floats along x.  min/max are the

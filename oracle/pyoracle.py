@@ -167,6 +167,24 @@ class Oracle:
             raise RuntimeError(f"vro_render_preint failed: {rc}")
         return dict(rgba8=rgba8, raw=raw)
 
+    # -- non-cubic voxels (port only: the reference ignores a file's spacings) -----
+    def render_spacing(self, frame: Frame, extent, volume: np.ndarray, lut: np.ndarray, nthreads=0):
+        assert volume.ndim == 3 and volume.flags.c_contiguous
+        vol = Volume(volume.ctypes.data, _DTYPE_OF[volume.dtype], volume.shape[2], volume.shape[1], volume.shape[0])
+        lut = np.ascontiguousarray(lut, np.uint32)
+        ext = (C.c_float * 3)(*[float(x) for x in extent])
+        H, W = frame.height, frame.width
+        rgba8 = np.zeros((H, W, 4), np.uint8)
+        raw = np.zeros((H, W, 4), np.float32)
+        st = Stats()
+        self.lib.vro_render_spacing.restype = C.c_int
+        self.lib.vro_render_spacing.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        rc = self.lib.vro_render_spacing(C.byref(frame), ext, C.byref(vol), lut.ctypes.data, len(lut), rgba8.ctypes.data, raw.ctypes.data,
+                                         C.byref(st), nthreads)
+        if rc != 0:
+            raise RuntimeError(f"vro_render_spacing failed: {rc}")
+        return dict(rgba8=rgba8, raw=raw, stats=st)
+
     # -- data ------------------------------------------------------------------
     def load_nrrd(self, path: str):
         dims = (C.c_uint32 * 3)()

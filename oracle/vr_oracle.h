@@ -79,6 +79,11 @@ int vro_preint_table(const uint32_t *lut, uint32_t nlut, uint32_t substeps, floa
 int vro_render_preint(const vro_frame *frame, const vro_volume *vol, const uint32_t *lut, uint32_t nlut, uint32_t substeps,
                       uint8_t *rgba8, float *raw, int nthreads);
 
+/* Non-cubic voxels (oracle/spacing.c; port build only -- the reference ignores a file's spacings): the volume fills the box
+ * [-extent/2, extent/2], extent in (0, 1].  extent = (1, 1, 1) is vro_render bit for bit. */
+int vro_render_spacing(const vro_frame *frame, const float extent[3], const vro_volume *vol, const uint32_t *lut, uint32_t nlut,
+                       uint8_t *rgba8, float *raw, vro_stats *stats, int nthreads);
+
 /* Orbit camera (src/scene/camera.cpp:7-48). */
 typedef struct vro_camera vro_camera;
 vro_camera *vro_camera_new(void);

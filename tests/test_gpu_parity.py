@@ -985,3 +985,94 @@ def test_preintegration_refuses_what_it_does_not_support(vr, port):
         op.download()
     finally:
         op.close()
+
+
+# ---- non-cubic voxels (vr_set_volume_spacing; the reference ignores a file's spacings; oracle/spacing.c) ---------------
+
+SPACING_CASES = [
+    # (dtype, dims (nx, ny, nz), spacing, moves, zoom, slices)
+    (np.uint16, 32, (1.0, 2.0, 4.0), [(-120, 80)], 0.0, None),
+    (np.uint16, 32, (3.0, 1.0, 1.5), [(200, 10)], 1.2, ((0.2, 0.1, 0.3), (0.9, 0.8, 0.7))),
+    (np.float32, (33, 20, 7), (1.0, 1.0, 1.0), [(10, 55)], 0.5, None),       # non-cubic grid of cubic voxels
+    (np.uint8, 32, (0.7, 0.7, 0.7), [(37, -21)], 0.0, None),                 # cubic: extents (1, 1, 1)
+]
+
+
+@pytest.mark.parametrize("case", SPACING_CASES, ids=[f"{c[0].__name__}-{i}" for i, c in enumerate(SPACING_CASES)])
+def test_honoured_spacings_match_the_oracle(vr, port, case):
+    """Exact sampler: float4 output, RGBA8 and counts BIT-identical to the CPU restatement (same fp32 operations); hardware
+    sampler with and without skipping, both layouts: within tolerance.  Switching the spacing off gives the unit-cube
+    frame back."""
+    dt, size, spacing, moves, zoom, slices = case
+    vol = small_volume(port, 1, dt, size)
+    nz, ny, nx = vol.shape
+    phys = np.array([nx * spacing[0], ny * spacing[1], nz * spacing[2]], np.float64)
+    ext = (phys / phys.max()).astype(np.float32)
+    lut = tf(port, "B")
+    mn, mx = float(vol.min()), float(vol.max())
+    cam, ocam = twin_cameras(vr, port, moves, zoom)
+    lo, hi = slices if slices else ((0, 0, 0), (1, 1, 1))
+    f = oracle_frame(port, ocam, W, H, mn, mx, lo, hi)
+    want = port.render_spacing(f, ext, vol, lut)
+    cube = port.render(f, vol, lut, want_raw=True)
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_options(sampler=vr.SAMPLER_EXACT, write_raw=1, collect_stats=1, early_term=0)
+        op.volume_dataset_changed(vr.Dataset(vol, mn, mx))
+        op.transfer_function_changed(lut)
+        op.slicing_changed(lo, hi)
+        op.set_camera(cam)
+        op.set_volume_spacing(spacing)
+        _, e = op.volume_spacing()
+        assert np.array_equal(e, ext)
+        op.record()
+        raw, img, st = op.download_raw(), op.download(), op.stats()
+        assert np.array_equal(raw.view(np.uint32), want["raw"].view(np.uint32)), "exact sampler: float4 output differs"
+        assert np.array_equal(img, want["rgba8"])
+        assert (st.n_ref, st.n_inslice, st.covered_pixels) == (want["stats"].n_ref, want["stats"].n_inslice, want["stats"].covered_pixels)
+        if (ext == 1.0).all():
+            assert np.array_equal(raw.view(np.uint32), cube["raw"].view(np.uint32)), "unit extents must be the reference's frame"
+        for ess in (0, 1):
+            op.set_options(sampler=vr.SAMPLER_HW, write_raw=1, collect_stats=0, empty_skip=ess, early_term=0)
+            op.record()
+            assert_within_tolerance(op.download(), want["rgba8"], f"hw sampler, skipping {ess}")
+        op.set_volume_spacing(None)
+        op.set_options(sampler=vr.SAMPLER_EXACT, write_raw=1, collect_stats=0, early_term=0)
+        op.record()
+        assert np.array_equal(op.download_raw().view(np.uint32), cube["raw"].view(np.uint32)), "spacing off: the unit cube again"
+    finally:
+        op.close()
+
+
+def test_spacings_of_a_nrrd_are_reported_and_applied_on_request(vr, port, tmp_path):
+    """vr_load_nrrd ignores the file's spacings like the reference (unit cube); vr_get_volume_spacing reports them and
+    vr_set_volume_spacing applies them -- also with the paired layout and the screen-space tile mask of the skipping path."""
+    vol = small_volume(port, 2, np.uint16, 40)
+    path = tmp_path / "v.nrrd"
+    hdr = "NRRD0004\ntype: ushort\ndimension: 3\nsizes: 40 40 40\nspacings: 1 1 2.5\nendian: little\nencoding: raw\n\n"
+    path.write_bytes(hdr.encode() + vol.astype("<u2").tobytes())
+    lut = tf(port, "C")
+    cam, ocam = twin_cameras(vr, port, [(45, 30)])
+    op = vr.OffscreenPass(W, H)
+    try:
+        op.set_volume_layout(vr.LAYOUT_PAIRED)
+        op.set_options(sampler=vr.SAMPLER_HW, empty_skip=1, early_term=0)
+        op.import_nrrd(str(path))
+        _, _, mn, mx = op.volume_info()
+        fs, e = op.volume_spacing()
+        assert list(fs) == [1.0, 1.0, 2.5] and list(e) == [1.0, 1.0, 1.0]
+        op.transfer_function_changed(lut)
+        op.set_camera(cam)
+        f = oracle_frame(port, ocam, W, H, mn, mx)
+        op.record()
+        assert_within_tolerance(op.download(), port.render(f, vol, lut)["rgba8"], "spacings ignored by default")
+        op.set_volume_spacing(fs)
+        _, e = op.volume_spacing()
+        assert np.allclose(e, [0.4, 0.4, 1.0])
+        op.record()
+        assert op.last_frame_paired() and op.tile_mask(0) is not None
+        assert_within_tolerance(op.download(), port.render_spacing(f, e, vol, lut)["rgba8"], "spacings honoured")
+        with pytest.raises(vr.VrError):
+            op.set_volume_spacing((1.0, 0.0, 1.0))
+    finally:
+        op.close()

@@ -552,3 +552,22 @@ def test_partition_balance_planes(vr):
     o_reg = vr.partition_order((2, 1, 1), (256, 1, 1), (0.05, 0.0, 0.0))
     o_mov = vr.partition_order((2, 1, 1), (256, 1, 1), (0.05, 0.0, 0.0), planes=[160])
     assert list(o_reg) == [1, 0] and list(o_mov) == [0, 1]
+
+
+def test_nrrd_spacings_are_read_but_not_applied_by_themselves(vr, tmp_path):
+    """the reference ignores `spacings` / `space directions` (nrrd_file_parser.cpp:32-33); the reader reports
+    them (NaN where the header states none) for a caller who wants them honoured (vr_set_volume_spacing)."""
+    body = bytes(2 * 3 * 4)
+    p = tmp_path / "a.nrrd"
+    p.write_bytes(b"NRRD0004\ntype: uchar\ndimension: 3\nsizes: 2 3 4\nspacings: 0.5 1.25 3\nencoding: raw\n\n" + body)
+    assert list(vr.nrrd_spacing(str(p))) == [0.5, 1.25, 3.0]
+    p.write_bytes(b"NRRD0004\ntype: uchar\ndimension: 3\nsizes: 2 3 4\nencoding: raw\n\n" + body)
+    assert np.isnan(vr.nrrd_spacing(str(p))).all()
+    p.write_bytes(b"NRRD0004\ntype: uchar\ndimension: 3\nspace dimension: 3\nsizes: 2 3 4\n"
+                  b"space directions: (3,4,0) (0,0.5,0) (0,0,-2)\nencoding: raw\n\n" + body)
+    assert list(vr.nrrd_spacing(str(p))) == [5.0, 0.5, 2.0]
+    p.write_bytes(b"NRRD0004\ntype: uchar\ndimension: 3\nsizes: 2 3 4\nspacings: nan 2 nan\nencoding: raw\n\n" + body)
+    s = vr.nrrd_spacing(str(p))
+    assert np.isnan(s[0]) and s[1] == 2.0 and np.isnan(s[2])
+    with pytest.raises(vr.VrError):
+        vr.nrrd_spacing(str(tmp_path / "missing.nrrd"))

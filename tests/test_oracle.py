@@ -265,3 +265,21 @@ def test_preintegrated_render_of_a_constant_volume_equals_the_per_sample_render(
     m = a[..., 3] > 0.5
     assert m.any()
     assert np.abs(a[m] - b[m]).max() < 0.05
+
+
+def test_spacing_oracle_with_unit_extents_is_the_reference_loop(port):
+    """oracle/spacing.c (non-cubic voxels; no reference counterpart) written in the unit cube's coordinates: extent (1, 1, 1)
+    must reproduce vro_render bit for bit; a flat box covers fewer pixels and its rays are shorter."""
+    from common import oracle_frame, tf
+    vol = port.synth(1, 0x5EED0001, np.uint16, 32)
+    lut = tf(port, "B")
+    cam = port.camera()
+    cam.rotate(-120.0, 80.0)
+    f = oracle_frame(port, cam, 96, 64, float(vol.min()), float(vol.max()))
+    a = port.render(f, vol, lut, want_raw=True)
+    b = port.render_spacing(f, (1.0, 1.0, 1.0), vol, lut)
+    assert np.array_equal(a["raw"].view(np.uint32), b["raw"].view(np.uint32)) and np.array_equal(a["rgba8"], b["rgba8"])
+    assert (a["stats"].n_ref, a["stats"].n_inslice, a["stats"].covered_pixels) == (b["stats"].n_ref, b["stats"].n_inslice, b["stats"].covered_pixels)
+    c = port.render_spacing(f, (1.0, 0.5, 0.25), vol, lut)
+    assert 0 < c["stats"].covered_pixels < a["stats"].covered_pixels
+    assert c["stats"].n_ref / c["stats"].covered_pixels < a["stats"].n_ref / a["stats"].covered_pixels

@@ -241,6 +241,20 @@ class OffscreenPass:
         bits = np.unpackbits(words[:-1].view(np.uint8), bitorder="little")[: tx.value * ty.value].astype(bool)
         return bits.reshape(ty.value, tx.value), bool(words[-1]), th.value
 
+    def set_volume_spacing(self, spacing):
+        """vr_set_volume_spacing: honour per-axis sample distances (non-cubic voxels); None = the reference's unit cube."""
+        if spacing is None:
+            self._check(lib.vr_set_volume_spacing(self._h, None))
+        else:
+            s = np.asarray(spacing, np.float32)
+            self._check(lib.vr_set_volume_spacing(self._h, _ptr(s)))
+
+    def volume_spacing(self):
+        """(spacings the NRRD loaded last states, NaN where none; extents of the box in use)"""
+        f, e = np.zeros(3, np.float32), np.zeros(3, np.float32)
+        self._check(lib.vr_get_volume_spacing(self._h, _ptr(f), _ptr(e)))
+        return f, e
+
     def set_preintegration(self, substeps: int):
         """vr_set_preintegration: classify segments between consecutive samples from a 2-D table (quality mode, changes the
         image, no reference counterpart); 0 = off."""
@@ -615,6 +629,16 @@ def partition_box_planes(grid, full_dims, planes, index: int):
     if rc != _lib.VR_OK:
         raise VrError(rc, "vr_partition_box_planes: bad arguments")
     return tuple(int(x) for x in org), tuple(int(x) for x in dims)
+
+
+def nrrd_spacing(path: str) -> np.ndarray:
+    """vr_nrrd_read_spacing: per-axis sample distances a NRRD header states (NaN where none)."""
+    out = np.zeros(3, np.float64)
+    err = C.create_string_buffer(512)
+    rc = lib.vr_nrrd_read_spacing(path.encode(), _ptr(out), err, len(err))
+    if rc != _lib.VR_OK:
+        raise VrError(rc, err.value.decode())
+    return out
 
 
 def minmax_static(device: int, dev_values: int, dtype: int, count: int, dev_min_max: int, stream: int | None = None):

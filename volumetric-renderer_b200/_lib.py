@@ -68,6 +68,7 @@ SIGNATURES = {
     "vr_set_volume_device": (C.c_int, [_P, _P, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, _F, _F]),
     "vr_load_nrrd": (C.c_int, [_P, C.c_char_p]),
     "vr_nrrd_read_host": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), _U, C.POINTER(_P), C.c_char_p, C.c_size_t]),
+    "vr_nrrd_read_spacing": (C.c_int, [C.c_char_p, _P, C.c_char_p, C.c_size_t]),
     "vr_free_host": (None, [_P]),
     "vr_sort_first_owner": (C.c_uint32, [C.c_uint32, C.c_uint32, C.c_uint32]),
     "vr_present_frame": (C.c_int, [_P, C.c_uint32, _P, C.c_uint32, C.c_uint32, C.c_size_t, _P]),
@@ -82,6 +83,8 @@ SIGNATURES = {
     "vr_set_gradient": (C.c_int, [_P, _P, C.c_uint32, _P, C.c_uint32, C.c_uint32]),
     "vr_get_transfer_function": (C.c_int, [_P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
     "vr_set_march": (C.c_int, [_P, C.c_float, C.c_float]),
+    "vr_set_volume_spacing": (C.c_int, [_P, _P]),
+    "vr_get_volume_spacing": (C.c_int, [_P, _P, _P]),
     "vr_set_preintegration": (C.c_int, [_P, C.c_uint32]),
     "vr_get_preintegration_table": (C.c_int, [_P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
     "vr_set_volume_layout": (C.c_int, [_P, C.c_int]),

@@ -94,6 +94,26 @@ bool mat4_inverse_d(const double *m, double *inv)
     return true;
 }
 
+bool update_ray_context(vr_ctx *c);
+
+/* The box the volume fills and the camera as the unit cube sees it (vr_set_volume_spacing).  Called when the camera, the
+ * spacing or the volume's dimensions change. */
+bool apply_extent(vr_ctx *c)
+{
+    for (int i = 0; i < 3; i++) c->ext[i] = 1.0f;
+    if (c->honour_spacing) {
+        const uint32_t d[3] = {c->sort_last ? c->full[0] : c->nx, c->sort_last ? c->full[1] : c->ny, c->sort_last ? c->full[2] : c->nz};
+        double phys[3], m = 0.0;
+        for (int i = 0; i < 3; i++) phys[i] = (double)d[i] * (double)c->spacing[i], m = std::max(m, phys[i]);
+        if (m > 0.0)
+            for (int i = 0; i < 3; i++) c->ext[i] = phys[i] > 0.0 ? (float)(phys[i] / m) : 1.0f;
+    }
+    for (int col = 0; col < 4; col++)
+        for (int r = 0; r < 4; r++) c->view[col * 4 + r] = col < 3 ? c->view_in[col * 4 + r] * c->ext[col] : c->view_in[col * 4 + r];
+    for (int i = 0; i < 3; i++) c->cam_pos[i] = c->cam_in[i] / c->ext[i];
+    return update_ray_context(c);
+}
+
 bool update_ray_context(vr_ctx *c)
 {
     double v[16], p[16], pv[16], inv[16];
@@ -229,6 +249,7 @@ int install_volume_unchecked(vr_ctx *c, const void *dev, int dtype, uint32_t nx,
 {
     release_volume(c);
     c->dtype = dtype, c->nx = nx, c->ny = ny, c->nz = nz;
+    if (c->honour_spacing) apply_extent(c); /* the box follows the dimensions */
     c->layout_used = c->layout_req;
     for (int i = 0; i < VR_MAX_FRAMES_IN_FLIGHT; i++) c->slot_clear[i].valid = false; /* (cheap) a new volume starts from a full clear */
     cudaChannelFormatDesc cd = dtype == VR_U8    ? cudaCreateChannelDesc<unsigned char>()
@@ -360,11 +381,11 @@ int default_state(vr_ctx *c)
     if (rc != VR_OK) return rc;
     vr_camera *cam = vr_camera_new();
     if (!cam) return fail(c, VR_ERR_NOMEM, "out of host memory");
-    vr_camera_get_view(cam, c->view);
-    vr_camera_get_position(cam, c->cam_pos);
+    vr_camera_get_view(cam, c->view_in);
+    vr_camera_get_position(cam, c->cam_in);
     vr_camera_free(cam);
     vr_projection(c->W, c->H, c->proj);
-    update_ray_context(c);
+    apply_extent(c);
     return VR_OK;
 }
 }  // namespace
@@ -477,10 +498,33 @@ extern "C" int vr_destroy(vr_ctx *c)
 extern "C" int vr_set_camera(vr_ctx *c, const float view[16], const float proj[16], const float camera_position[3])
 {
     if (!c || !view || !proj || !camera_position) return fail(c, VR_ERR_INVALID, "vr_set_camera: null argument");
-    std::memcpy(c->view, view, sizeof(c->view));
+    std::memcpy(c->view_in, view, sizeof(c->view_in));
     std::memcpy(c->proj, proj, sizeof(c->proj));
-    std::memcpy(c->cam_pos, camera_position, sizeof(c->cam_pos));
-    if (!update_ray_context(c)) return fail(c, VR_ERR_INVALID, "vr_set_camera: proj * view is singular");
+    std::memcpy(c->cam_in, camera_position, sizeof(c->cam_in));
+    if (!apply_extent(c)) return fail(c, VR_ERR_INVALID, "vr_set_camera: proj * view is singular");
+    return VR_OK;
+}
+
+extern "C" int vr_set_volume_spacing(vr_ctx *c, const float spacing[3])
+{
+    if (!c) return VR_ERR_INVALID;
+    if (spacing)
+        for (int i = 0; i < 3; i++)
+            if (!(spacing[i] > 0.0f) || !(spacing[i] <= 3.0e38f)) return fail(c, VR_ERR_INVALID, "vr_set_volume_spacing: spacings must be positive and finite");
+    c->honour_spacing = spacing != nullptr;
+    for (int i = 0; i < 3; i++) c->spacing[i] = spacing ? spacing[i] : 1.0f;
+    for (int i = 0; i < VR_MAX_FRAMES_IN_FLIGHT; i++) c->slot_clear[i].valid = false;
+    if (!apply_extent(c)) return fail(c, VR_ERR_INVALID, "vr_set_volume_spacing: proj * view is singular");
+    return VR_OK;
+}
+
+extern "C" int vr_get_volume_spacing(const vr_ctx *c, float file_spacing[3], float extent[3])
+{
+    if (!c) return VR_ERR_INVALID;
+    for (int i = 0; i < 3; i++) {
+        if (file_spacing) file_spacing[i] = c->file_spacing[i];
+        if (extent) extent[i] = c->ext[i];
+    }
     return VR_OK;
 }
 
@@ -571,6 +615,7 @@ extern "C" int vr_load_nrrd(vr_ctx *c, const char *path)
     std::string err;
     const int rc = vr_nrrd_read(path, n, err, &pl);
     if (rc != VR_OK) return fail(c, rc, err);
+    for (int i = 0; i < 3; i++) c->file_spacing[i] = (float)n.spacing[i]; /* ignored like the reference does, unless vr_set_volume_spacing */
     if (!pl.direct) return vr_set_volume(c, n.bytes.data(), n.dtype, n.dims[0], n.dims[1], n.dims[2], nullptr, nullptr);
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaDeviceSynchronize());
@@ -868,6 +913,7 @@ void fill_params(const vr_ctx *c, MarchParams &p, int pair_axis, const uint32_t 
     for (int r = 0; r < 4; r++) p.c0[r] = c->rc[0][r], p.c1[r] = c->rc[1][r], p.c2[r] = c->rc[2][r], p.c3[r] = c->rc[3][r];
     p.sx = 2.0f / (float)c->W, p.sy = 2.0f / (float)c->H;
     for (int i = 0; i < 3; i++) p.cam[i] = c->cam_pos[i], p.min_slice[i] = c->min_slice[i], p.max_slice[i] = c->max_slice[i];
+    for (int i = 0; i < 3; i++) p.ext[i] = c->ext[i], p.inv_ext[i] = 1.0f / c->ext[i];
     p.W = c->W, p.H = c->H;
     p.min_density = c->min_density, p.max_density = c->max_density;
     p.range = c->max_density - c->min_density;
@@ -1784,6 +1830,22 @@ extern "C" int vr_nrrd_read_host(const char *path, int *dtype, uint32_t dims[3],
 }
 
 extern "C" void vr_free_host(void *p) { std::free(p); }
+
+/* The header's per-axis sample distances alone (host only): `spacings`, or the length of `space directions`; NaN where none. */
+extern "C" int vr_nrrd_read_spacing(const char *path, double spacing[3], char *errbuf, size_t errbuf_len)
+{
+    if (!path || !spacing) return VR_ERR_INVALID;
+    VrNrrd n;
+    VrNrrdPayload pl; /* asking for the payload's place keeps a raw file's data from being read */
+    std::string err;
+    const int rc = vr_nrrd_read(path, n, err, &pl);
+    if (rc != VR_OK) {
+        if (errbuf && errbuf_len) std::snprintf(errbuf, errbuf_len, "%s", err.c_str());
+        return rc;
+    }
+    for (int i = 0; i < 3; i++) spacing[i] = n.spacing[i];
+    return VR_OK;
+}
 
 /* CSV slices (src/data/csv_file_parser.cpp:14-50 through src/data/importer.cpp:30-46) */
 extern "C" int vr_csv_read_host(const char *const *paths, uint32_t npaths, uint32_t dims[3], float **data, float *mn, float *mx,

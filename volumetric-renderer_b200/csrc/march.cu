@@ -661,12 +661,14 @@ __global__ void __launch_bounds__(VR_CTA_THREADS, (EXACT || ESS || STATS || PART
     float cr = 0.0f, cg = 0.0f, cb = 0.0f, T = 1.0f;
     float posx = 0.f, posy = 0.f, posz = 0.f, dx = 0.f, dy = 0.f, dz = 0.f;
     if (covered) {
-        const float vx = e.frag[0] - p.cam[0], vy = e.frag[1] - p.cam[1], vz = e.frag[2] - p.cam[2];
+        /* (* ext, * inv_ext: non-cubic voxels -- the direction is normalised in physical space, the step is taken in the
+         * cube's; both are (1, 1, 1) unless spacings are honoured, and a multiplication by 1 changes no bit) */
+        const float vx = (e.frag[0] - p.cam[0]) * p.ext[0], vy = (e.frag[1] - p.cam[1]) * p.ext[1], vz = (e.frag[2] - p.cam[2]) * p.ext[2];
         const float d2 = (vx * vx + vy * vy) + vz * vz;
         const float inv = 1.0f / sqrtf(d2); /* glm::normalize = v * inversesqrt(dot(v,v)) */
-        dx = (vx * inv) * p.step_size;
-        dy = (vy * inv) * p.step_size;
-        dz = (vz * inv) * p.step_size;
+        dx = ((vx * inv) * p.step_size) * p.inv_ext[0];
+        dy = ((vy * inv) * p.step_size) * p.inv_ext[1];
+        dz = ((vz * inv) * p.step_size) * p.inv_ext[2];
         posx = e.tex[0], posy = e.tex[1], posz = e.tex[2];
     }
     if (PAIR && p.pair_axis != 2) {

@@ -13,6 +13,7 @@
  */
 #include "nrrd.h"
 
+#include <cmath>
 #include <algorithm>
 #include <cctype>
 #include <cstdio>
@@ -399,6 +400,25 @@ static int nrrd_read_impl(const char *path, VrNrrd &out, std::string &err, VrNrr
         if ((i < spacings.size() && lower(spacings[i]) != "nan") || (i < axis_mins.size() && lower(axis_mins[i]) != "nan") ||
             (i < axis_maxs.size() && lower(axis_maxs[i]) != "nan") || (i < units.size() && !units[i].empty()))
             return bad("axis with a space direction and a spacing, axis min / max or units");
+    }
+    for (int i = 0; i < 3; i++) {
+        out.spacing[i] = __builtin_nan("");
+        if ((size_t)i < space_dirs.size() && lower(space_dirs[i]) != "none") {
+            /* "(a,b,c)": the length of the direction vector */
+            const std::string body = space_dirs[i].substr(1, space_dirs[i].size() - 2);
+            double n2 = 0.0;
+            size_t a = 0;
+            while (true) {
+                const size_t b = body.find(',', a);
+                const double v = std::strtod(trim(body.substr(a, b == std::string::npos ? std::string::npos : b - a)).c_str(), nullptr);
+                n2 += v * v;
+                if (b == std::string::npos) break;
+                a = b + 1;
+            }
+            out.spacing[i] = std::sqrt(n2);
+        } else if ((size_t)i < spacings.size() && lower(spacings[i]) != "nan") {
+            out.spacing[i] = std::fabs(std::strtod(spacings[i].c_str(), nullptr));
+        }
     }
     const size_t esz = scalar_size(type);
     /* sizes come from the header alone: refuse what cannot be a volume before anything is allocated from them

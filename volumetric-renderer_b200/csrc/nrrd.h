@@ -11,6 +11,10 @@
 struct VrNrrd {
     int dtype = VR_F32;          /* vr_dtype of `bytes` */
     uint32_t dims[3] = {0, 0, 0}; /* x fastest */
+    /* sample distance per axis as the header states it -- `spacings`, or the length of the axis's `space directions`
+     * vector -- NaN where it states none.  The reference ignores both (nrrd_file_parser.cpp:32-33) and so does an
+     * upload; vr_get_volume_spacing hands them to a caller who wants them honoured. */
+    double spacing[3] = {__builtin_nan(""), __builtin_nan(""), __builtin_nan("")};
     std::vector<uint8_t> bytes;
 };
 

@@ -75,6 +75,7 @@ struct MarchParams {
     int occ_words;
     float occ_scale[3], occ_off[3]; /* cell = int(pos * occ_scale - occ_off) */
     int ess_guard;             /* empty-space jumps a lane may take ahead of one batch */
+    float ext[3], inv_ext[3];  /* non-cubic voxels: physical = cube coordinate * ext; (1, 1, 1) unless spacings are honoured */
     float occ_offh[3];         /* occ_off + 1/2 */
     const uint32_t *tile_mask; /* bit per CTA tile (ty * ntx + tx): 0 = no ray of the tile meets an occupied cell; word [mask_words] != 0:
                                 * ignore the mask; nullptr = no mask this frame (volume.cu k_tile_mask) */
@@ -131,6 +132,13 @@ struct vr_ctx {
     float ray_dist = 1.8f, step_size = 0.005f;
     bool ray_valid = false; /* inverse(proj*view) exists */
     float rc[4][4];         /* columns of the inverse */
+    /* non-cubic voxels (vr_set_volume_spacing; off = the reference's unit cube): the volume fills [-ext/2, ext/2].  The
+     * march works in the unit cube's coordinates: view = view_in * diag(ext), cam_pos = cam_in / ext (fp32, exact for 1) */
+    bool honour_spacing = false;
+    float spacing[3] = {1.0f, 1.0f, 1.0f};
+    float file_spacing[3] = {__builtin_nanf(""), __builtin_nanf(""), __builtin_nanf("")}; /* of the NRRD loaded last */
+    float ext[3] = {1.0f, 1.0f, 1.0f};
+    float view_in[16], cam_in[3]; /* the camera as it was set */
 
     /* volume */
     int dtype = VR_F32;

@@ -143,6 +143,8 @@ class OffscreenPass
         for (const auto &m : gradient.alpha_markers) am.insert(am.end(), {m.location, m.value});
         check(vr_set_gradient(ctx, cm.data(), (uint32_t)gradient.color_markers.size(), am.data(), (uint32_t)gradient.alpha_markers.size(), count));
     }
+    // honour a file's voxel spacings (the reference ignores them): nullptr = the unit cube
+    void set_volume_spacing(const vec3 *spacing) { check(vr_set_volume_spacing(ctx, spacing ? spacing->data() : nullptr)); }
     // optional quality mode, no reference counterpart: classify segments between samples from a 2-D table (0 = off)
     void set_preintegration(uint32_t substeps) { check(vr_set_preintegration(ctx, substeps)); }
     // get_image_view() / get_sampler(): the colour attachment as a device pointer + pitch
