@@ -12,7 +12,7 @@
 
 #include "../../include/vr.h"
 
-#define VR_KERNEL_VERSION "r2.v10" /* bump when K1 changes: profiles/traffic.json is keyed by it */
+#define VR_KERNEL_VERSION "r2.v11" /* bump when K1 changes: profiles/traffic.json is keyed by it */
 #define VR_PREINT_MAX_TEXELS 1024 /* pre-integration table: n x n float4, 16 MiB at most */
 #define VR_TILE 16        /* a CTA marches a 16x16 pixel tile: 8 warps of 8x4 pixels */
 #define VR_CTA_THREADS 256
