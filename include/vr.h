@@ -424,7 +424,7 @@ typedef struct vr_sort_last_wiring {
     void *const *flags;                    /* [world]: every rank's flag block, local or peer-mapped */
     void *const *raw;                      /* [slots * world]: float4 partial of rank r in slot s at raw[s * world + r] */
     void *const *image;                    /* [slots]: the display rank's RGBA8 target of slot s, local or peer-mapped */
-    uint64_t pixel_begin, pixel_end;       /* the pixel range this rank merges */
+    uint64_t pixel_begin, pixel_end;       /* (not used: the merge deals 8-row bands of the region that can differ from the clear colour to the ranks) */
 } vr_sort_last_wiring;
 int vr_sort_last_frame(vr_ctx *ctx, const vr_sort_last_wiring *wiring, uint64_t frame, const float camera_position[3],
                        void *march_stream, void *merge_stream, void *present_stream);

@@ -425,6 +425,7 @@ extern "C" int vr_create(int device, uint32_t width, uint32_t height, vr_ctx **o
     if (const char *e = std::getenv("VR_BBOX")) c->tune_bbox = std::atoi(e);
     if (const char *e = std::getenv("VR_DIRTY_CLEAR")) c->tune_dirty_clear = std::atoi(e);
     if (const char *e = std::getenv("VR_PAIR_LOCAL")) c->tune_pair_local = std::atoi(e);
+    if (const char *e = std::getenv("VR_SL_REGION")) c->tune_sl_region = std::atoi(e);
     if (const char *e = std::getenv("VR_TILE_MASK")) c->tune_tile_mask = std::atoi(e);
     if (const char *e = std::getenv("VR_WARP_W")) {
         const int w = std::atoi(e);
@@ -2010,9 +2011,34 @@ extern "C" int vr_sort_last_frame(vr_ctx *c, const vr_sort_last_wiring *w, uint6
     /* merge stream: every partial of frame k complete, image slot s presented (frame k - S), then K2 on my range */
     if ((rc = vr_stream_wait(c, flag(rank, READY + s * 32), n, frame_no, 10000, merge_stream)) != VR_OK) return rc;
     if (k >= S && (rc = vr_stream_wait(c, flag(rank, CONSUMED + s), 1, freed, 10000, merge_stream)) != VR_OK) return rc;
-    if (w->pixel_end > w->pixel_begin &&
-        (rc = vr_composite_rects(c, parts, rects, n, w->pixel_begin, w->pixel_end, w->image[s], merge_stream)) != VR_OK)
-        return rc;
+    {
+        /* Outside the screen rectangles of the sub-boxes every partial is the identity and the merged pixel the clear
+         * colour.  The first frame into an image slot (k < S) merges the whole frame; later ones only the bounding
+         * rectangle of what this frame and the frame before it in the slot (k - S) can have drawn -- the same region on
+         * every rank, a pure function of the two cameras -- dealt to the ranks in bands of 8 rows. */
+        uint32_t cur[4] = {c->W, c->H, 0, 0};
+        for (uint32_t i = 0; i < n; i++)
+            if (rects[4 * i + 2] > rects[4 * i] && rects[4 * i + 3] > rects[4 * i + 1]) {
+                cur[0] = std::min(cur[0], rects[4 * i]), cur[1] = std::min(cur[1], rects[4 * i + 1]);
+                cur[2] = std::max(cur[2], rects[4 * i + 2]), cur[3] = std::max(cur[3], rects[4 * i + 3]);
+            }
+        if (cur[2] <= cur[0] || cur[3] <= cur[1]) cur[0] = cur[1] = cur[2] = cur[3] = 0;
+        uint32_t region[4] = {0, 0, c->W, c->H};
+        if (k >= S && c->tune_sl_region) {
+            const uint32_t *pr = c->sl_region[s];
+            const bool prev_empty = pr[2] <= pr[0] || pr[3] <= pr[1], cur_empty = cur[2] <= cur[0];
+            if (prev_empty && cur_empty) region[0] = region[1] = region[2] = region[3] = 0;
+            else if (prev_empty) std::memcpy(region, cur, sizeof region);
+            else if (cur_empty) std::memcpy(region, pr, sizeof region);
+            else region[0] = std::min(pr[0], cur[0]), region[1] = std::min(pr[1], cur[1]), region[2] = std::max(pr[2], cur[2]), region[3] = std::max(pr[3], cur[3]);
+        }
+        std::memcpy(c->sl_region[s], cur, sizeof cur);
+        VR_CUDA(c, cudaSetDevice(c->device));
+        cudaStream_t ms = merge_stream ? (cudaStream_t)merge_stream : c->stream;
+        c->last_stream = ms;
+        VR_CUDA(c, vr_launch_composite_region(reinterpret_cast<const float4 *const *>(parts), rects, n, region, rank, n, c->W,
+                                              reinterpret_cast<uchar4 *>(w->image[s]), ms));
+    }
     for (uint32_t r = 0; r < n; r++) sig[r] = flag(r, READ_DONE + s * 32 + rank);
     sig[n] = flag(disp, RANGE_DONE + s * 32 + rank);
     if ((rc = vr_stream_signal(c, sig, n + 1, frame_no, merge_stream)) != VR_OK) return rc;

@@ -134,6 +134,9 @@ struct vr_ctx {
     float rc[4][4];         /* columns of the inverse */
     /* non-cubic voxels (vr_set_volume_spacing; off = the reference's unit cube): the volume fills [-ext/2, ext/2].  The
      * march works in the unit cube's coordinates: view = view_in * diag(ext), cam_pos = cam_in / ext (fp32, exact for 1) */
+    /* sort-last merge (vr_sort_last_frame): the region of each image slot that the last frame merged into it may have left
+     * different from the clear colour -- the next frame into the slot merges the union of that and its own */
+    uint32_t sl_region[VR_MAX_FRAMES_IN_FLIGHT][4] = {};
     bool honour_spacing = false;
     float spacing[3] = {1.0f, 1.0f, 1.0f};
     float file_spacing[3] = {__builtin_nanf(""), __builtin_nanf(""), __builtin_nanf("")}; /* of the NRRD loaded last */
@@ -225,6 +228,7 @@ struct vr_ctx {
     uint32_t tile_mask_words = 0;
     bool slot_mask_valid[VR_MAX_FRAMES_IN_FLIGHT] = {false, false, false, false};
     uint32_t slot_mask_shape[VR_MAX_FRAMES_IN_FLIGHT][3] = {}; /* tiles in x, tiles in y, tile height of the frame recorded last */
+    int tune_sl_region = 1;          /* VR_SL_REGION=0: vr_sort_last_frame merges the whole frame every time */
     int tune_pair_local = 1;         /* VR_PAIR_LOCAL=0: a sort-last rank never overrides the pair axis by its entry face */
     int tune_tile_mask = 1;          /* VR_TILE_MASK=0: no screen-space mask; 2: marked in global memory directly (frames too large to stage) */
     bool occ_dirty = true;
@@ -238,6 +242,8 @@ struct vr_ctx {
 /* ---- kernels / device-side stages (each .cu implements its own) ---- */
 
 /* K1 (march.cu) */
+cudaError_t vr_launch_composite_region(const float4 *const *parts, const uint32_t *rects, uint32_t nparts, const uint32_t region[4], uint32_t rank,
+                                       uint32_t nranks, uint32_t W, uchar4 *out, cudaStream_t s);
 cudaError_t vr_launch_march_preint(const MarchParams &p, bool pair, int threads, cudaStream_t s);
 cudaError_t vr_launch_march_probe(const MarchParams &p, bool pair, int ub, int threads, cudaStream_t s);
 cudaError_t vr_launch_march(const MarchParams &p, bool exact, bool ess, bool stats, bool part, bool pair, int ub,
