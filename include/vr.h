@@ -412,6 +412,16 @@ int vr_partition_box_planes(const uint32_t grid[3], const uint32_t full_dims[3],
 int vr_partition_order_planes(const uint32_t grid[3], const uint32_t full_dims[3], const uint32_t *planes,
                               const float camera_position[3], uint32_t *out);
 
+/* vr_composite_rects over a pixel REGION (x0, y0, x1, y1) dealt in bands of 8 rows: band b of the region is merged by
+ * the caller with band_index == b % band_count.  vr_sort_last_region gives the region a sort-last frame has to merge
+ * into an image slot -- the bounding rectangle of this frame's sub-box rectangles and of those of the frame merged
+ * into that slot before (slot_region: the caller's four words per slot, updated; first_into_slot: the whole frame):
+ * outside it every partial is the identity and the slot already holds the clear colour. */
+int vr_composite_region(vr_ctx *ctx, const void *const *parts, const uint32_t *rects, uint32_t nparts, const uint32_t region[4],
+                        uint32_t band_index, uint32_t band_count, void *out_rgba8, void *cuda_stream);
+void vr_sort_last_region(const uint32_t *rects, uint32_t nparts, uint32_t width, uint32_t height, int first_into_slot, uint32_t slot_region[4],
+                         uint32_t region[4]);
+
 /* ---- one sort-last frame of one rank in ONE call (one process per GPU) --------------------------------------
  * What multigpu.SortLast.render enqueues per frame -- split planes, owned box, view order, screen rectangles, the
  * waits / march / signals on the march stream, the waits / merge / signals on the merge stream, the display rank's

@@ -131,6 +131,8 @@ SIGNATURES = {
     "vr_partition_box": (C.c_int, [_P, _P, C.c_uint32, _P, _P]),
     "vr_partition_order": (C.c_int, [_P, _P, _P, _P]),
     "vr_set_owned_box": (C.c_int, [_P, _P, _P]),
+    "vr_composite_region": (C.c_int, [_P, _P, _P, C.c_uint32, _P, C.c_uint32, C.c_uint32, _P, _P]),
+    "vr_sort_last_region": (None, [_P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, _P, _P]),
     "vr_sort_last_frame": (C.c_int, [_P, C.POINTER(SortLastWiring), C.c_uint64, _P, _P, _P, _P]),
     "vr_minmax_static_max_count": (C.c_uint64, []),
     "vr_minmax_static": (C.c_int, [C.c_int, _P, C.c_int, C.c_uint64, _P, _P, C.c_char_p, C.c_size_t]),

@@ -1972,6 +1972,44 @@ extern "C" int vr_composite_to(vr_ctx *c, const void *const *parts, uint32_t npa
     return vr_composite_rects(c, parts, nullptr, nparts, pixel_begin, pixel_end, out_rgba8, cuda_stream);
 }
 
+extern "C" int vr_composite_region(vr_ctx *c, const void *const *parts, const uint32_t *rects, uint32_t nparts, const uint32_t region[4],
+                                   uint32_t band_index, uint32_t band_count, void *out_rgba8, void *cuda_stream)
+{
+    if (!c || !parts || !rects || !region || nparts == 0 || band_count == 0 || band_index >= band_count)
+        return fail(c, VR_ERR_INVALID, "vr_composite_region: bad arguments");
+    if (region[2] > c->W || region[3] > c->H) return fail(c, VR_ERR_INVALID, "vr_composite_region: region outside the frame");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+    c->last_stream = s;
+    uchar4 *out = out_rgba8 ? reinterpret_cast<uchar4 *>(out_rgba8) : (c->ext_image ? c->ext_image : c->d_image);
+    VR_CUDA(c, vr_launch_composite_region(reinterpret_cast<const float4 *const *>(parts), rects, nparts, region, band_index, band_count, c->W, out, s));
+    return VR_OK;
+}
+
+/* the region of an image slot a sort-last frame has to merge: the bounding rectangle of what this frame (the union of its
+ * sub-box rectangles, stored in `slot_region` for the next time) and the frame before it in the slot can have drawn */
+extern "C" void vr_sort_last_region(const uint32_t *rects, uint32_t nparts, uint32_t W, uint32_t H, int first_into_slot, uint32_t slot_region[4],
+                                    uint32_t region[4])
+{
+    uint32_t cur[4] = {W, H, 0, 0};
+    for (uint32_t i = 0; i < nparts; i++)
+        if (rects[4 * i + 2] > rects[4 * i] && rects[4 * i + 3] > rects[4 * i + 1]) {
+            cur[0] = std::min(cur[0], rects[4 * i]), cur[1] = std::min(cur[1], rects[4 * i + 1]);
+            cur[2] = std::max(cur[2], rects[4 * i + 2]), cur[3] = std::max(cur[3], rects[4 * i + 3]);
+        }
+    if (cur[2] <= cur[0] || cur[3] <= cur[1]) cur[0] = cur[1] = cur[2] = cur[3] = 0;
+    region[0] = region[1] = 0, region[2] = W, region[3] = H;
+    if (!first_into_slot) {
+        const uint32_t *pr = slot_region;
+        const bool prev_empty = pr[2] <= pr[0] || pr[3] <= pr[1], cur_empty = cur[2] <= cur[0];
+        if (prev_empty && cur_empty) region[0] = region[1] = region[2] = region[3] = 0;
+        else if (prev_empty) std::memcpy(region, cur, sizeof cur);
+        else if (cur_empty) std::memcpy(region, pr, sizeof cur);
+        else region[0] = std::min(pr[0], cur[0]), region[1] = std::min(pr[1], cur[1]), region[2] = std::max(pr[2], cur[2]), region[3] = std::max(pr[3], cur[3]);
+    }
+    std::memcpy(slot_region, cur, sizeof cur);
+}
+
 extern "C" int vr_sort_last_frame(vr_ctx *c, const vr_sort_last_wiring *w, uint64_t k, const float cam[3], void *march_stream,
                                   void *merge_stream, void *present_stream)
 {
@@ -2016,28 +2054,9 @@ extern "C" int vr_sort_last_frame(vr_ctx *c, const vr_sort_last_wiring *w, uint6
          * colour.  The first frame into an image slot (k < S) merges the whole frame; later ones only the bounding
          * rectangle of what this frame and the frame before it in the slot (k - S) can have drawn -- the same region on
          * every rank, a pure function of the two cameras -- dealt to the ranks in bands of 8 rows. */
-        uint32_t cur[4] = {c->W, c->H, 0, 0};
-        for (uint32_t i = 0; i < n; i++)
-            if (rects[4 * i + 2] > rects[4 * i] && rects[4 * i + 3] > rects[4 * i + 1]) {
-                cur[0] = std::min(cur[0], rects[4 * i]), cur[1] = std::min(cur[1], rects[4 * i + 1]);
-                cur[2] = std::max(cur[2], rects[4 * i + 2]), cur[3] = std::max(cur[3], rects[4 * i + 3]);
-            }
-        if (cur[2] <= cur[0] || cur[3] <= cur[1]) cur[0] = cur[1] = cur[2] = cur[3] = 0;
-        uint32_t region[4] = {0, 0, c->W, c->H};
-        if (k >= S && c->tune_sl_region) {
-            const uint32_t *pr = c->sl_region[s];
-            const bool prev_empty = pr[2] <= pr[0] || pr[3] <= pr[1], cur_empty = cur[2] <= cur[0];
-            if (prev_empty && cur_empty) region[0] = region[1] = region[2] = region[3] = 0;
-            else if (prev_empty) std::memcpy(region, cur, sizeof region);
-            else if (cur_empty) std::memcpy(region, pr, sizeof region);
-            else region[0] = std::min(pr[0], cur[0]), region[1] = std::min(pr[1], cur[1]), region[2] = std::max(pr[2], cur[2]), region[3] = std::max(pr[3], cur[3]);
-        }
-        std::memcpy(c->sl_region[s], cur, sizeof cur);
-        VR_CUDA(c, cudaSetDevice(c->device));
-        cudaStream_t ms = merge_stream ? (cudaStream_t)merge_stream : c->stream;
-        c->last_stream = ms;
-        VR_CUDA(c, vr_launch_composite_region(reinterpret_cast<const float4 *const *>(parts), rects, n, region, rank, n, c->W,
-                                              reinterpret_cast<uchar4 *>(w->image[s]), ms));
+        uint32_t region[4];
+        vr_sort_last_region(rects, n, c->W, c->H, k < S || !c->tune_sl_region, c->sl_region[s], region);
+        if ((rc = vr_composite_region(c, parts, rects, n, region, rank, n, w->image[s], merge_stream)) != VR_OK) return rc;
     }
     for (uint32_t r = 0; r < n; r++) sig[r] = flag(r, READ_DONE + s * 32 + rank);
     sig[n] = flag(disp, RANGE_DONE + s * 32 + rank);

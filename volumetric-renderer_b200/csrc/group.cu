@@ -42,6 +42,7 @@ struct vr_group {
     uint32_t full[3] = {0, 0, 0}, grid[3] = {1, 1, 1};
     std::vector<std::array<uint32_t, 6>> box;    /* org, dims each rank OWNS in the frame being recorded */
     std::vector<std::array<uint32_t, 6>> stored; /* org, dims each rank HOLDS */
+    std::vector<std::array<uint32_t, 4>> slot_region; /* per image slot: what the frame merged into it last can have drawn */
     float balance = 0.0f;                        /* sort-last: how far the split planes may follow the camera (vr_group_set_balance) */
     uint32_t margin[3] = {0, 0, 0};
     float cam_pos[3] = {0, -3, 0};
@@ -87,13 +88,6 @@ void grid_for_world(uint32_t world, uint32_t g[3])
     }
 }
 
-/* pixel range of rank r for the direct-send merge (multiples of 32 pixels; multigpu.pixel_ranges) */
-void pixel_range(uint64_t npix, uint32_t world, uint32_t r, uint64_t &b, uint64_t &e)
-{
-    uint64_t per = (npix + world - 1) / world;
-    per = (per + 31) / 32 * 32;
-    b = std::min<uint64_t>((uint64_t)r * per, npix), e = std::min<uint64_t>((uint64_t)(r + 1) * per, npix);
-}
 
 int make_partition(vr_group *g, uint32_t nx, uint32_t ny, uint32_t nz)
 {
@@ -386,16 +380,17 @@ extern "C" int vr_group_render(vr_group *g)
         G_VR(g, r, vr_render_frame(g->ctx[r], s, g->march[r]));
         G_CUDA(g, cudaEventRecord(g->ready[r][s], g->march[r]));
     }
-    const uint64_t npix = (uint64_t)g->W * g->H;
+    /* only the region that can differ from the clear colour is merged, in bands of 8 rows dealt to the ranks */
+    if (g->slot_region.size() != S) g->slot_region.assign(S, {});
+    uint32_t region[4];
+    vr_sort_last_region(rects.data(), n, g->W, g->H, k < S, g->slot_region[s].data(), region);
     std::vector<const void *> parts(n);
     for (uint32_t i = 0; i < n; i++) parts[i] = g->raw_slot[order[i]][s];
     for (uint32_t r = 0; r < n; r++) {
         G_CUDA(g, cudaSetDevice(g->dev[r]));
         for (uint32_t q = 0; q < n; q++) G_CUDA(g, cudaStreamWaitEvent(g->merge[r], g->ready[q][s], 0));
         if (k >= S) G_CUDA(g, cudaStreamWaitEvent(g->merge[r], g->consumed[s], 0));
-        uint64_t b, e;
-        pixel_range(npix, n, r, b, e);
-        if (e > b) G_VR(g, r, vr_composite_rects(g->ctx[r], parts.data(), rects.data(), n, b, e, g->image_slot[s], g->merge[r]));
+        G_VR(g, r, vr_composite_region(g->ctx[r], parts.data(), rects.data(), n, region, r, n, g->image_slot[s], g->merge[r]));
         G_CUDA(g, cudaEventRecord(g->merged[r][s], g->merge[r]));
     }
     G_CUDA(g, cudaSetDevice(g->dev[0]));
