@@ -115,6 +115,18 @@ def test_sort_last_partials_compose_to_single_gpu_image(vr, port, grid, view, sa
     single.composite([parts[i] for i in order], 0, W * H, rects=[rects[i] for i in order])
     got = single.download()
     assert np.array_equal(got, got_full), "reading only the bounding rectangles must change nothing"
+    # the same merge over the region that can differ from the clear colour, in bands of 8 rows dealt to three callers
+    # (vr_composite_region: what a sort-last rank runs per frame): outside the region the target keeps the clear colour
+    slot_region = np.zeros(4, np.uint32)
+    ordered = [rects[i] for i in order]
+    assert vr.sort_last_region(ordered, W, H, True, slot_region) == (0, 0, W, H)
+    region = vr.sort_last_region(ordered, W, H, False, slot_region)
+    if zoom == 0.0:
+        assert region[2] - region[0] < W and region[3] - region[1] < H     # (close-ups fill the frame)
+    single.composite([parts[i] for i in order], 0, W * H, rects=[(0, 0, 0, 0)] * nbox)      # the whole target: clear colour
+    for band in range(3):
+        single.composite_region([parts[i] for i in order], ordered, region, band, 3)
+    assert np.array_equal(single.download(), got), "the region merge in bands must give the same frame"
     for op in passes:
         op.close()
     single.close()

@@ -571,3 +571,19 @@ def test_nrrd_spacings_are_read_but_not_applied_by_themselves(vr, tmp_path):
     assert np.isnan(s[0]) and s[1] == 2.0 and np.isnan(s[2])
     with pytest.raises(vr.VrError):
         vr.nrrd_spacing(str(tmp_path / "missing.nrrd"))
+
+
+def test_sort_last_merge_region(vr):
+    """vr_sort_last_region (host only): the first frame into an image slot merges the whole frame; later ones the bounding
+    rectangle of this frame's and the previous frame's sub-box rectangles; empty rectangles are ignored."""
+    slot = np.zeros(4, np.uint32)
+    a = [(100, 50, 300, 200), (250, 150, 400, 260), (0, 0, 0, 0)]
+    assert vr.sort_last_region(a, 640, 480, True, slot) == (0, 0, 640, 480)
+    assert tuple(slot) == (100, 50, 400, 260)
+    b = [(120, 40, 200, 100), (130, 60, 220, 300)]
+    assert vr.sort_last_region(b, 640, 480, False, slot) == (100, 40, 400, 300)     # union with what the slot held
+    assert tuple(slot) == (120, 40, 220, 300)
+    assert vr.sort_last_region([(5, 5, 5, 9)], 640, 480, False, slot) == (120, 40, 220, 300)   # nothing drawn now: restore the old region
+    assert tuple(slot) == (0, 0, 0, 0)
+    assert vr.sort_last_region([(0, 0, 0, 0)], 640, 480, False, slot) == (0, 0, 0, 0)          # nothing before, nothing now
+    assert vr.sort_last_region(b, 640, 480, False, slot) == (120, 40, 220, 300)

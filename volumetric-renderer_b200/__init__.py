@@ -416,6 +416,14 @@ class OffscreenPass:
         self._check(lib.vr_composite_rects(self._h, arr, _ptr(r) if r is not None else None, len(part_ptrs), pixel_begin, pixel_end,
                                            out_ptr, stream))
 
+    def composite_region(self, part_ptrs, rects, region, band_index: int, band_count: int, stream: int | None = None, out_ptr: int | None = None):
+        """vr_composite_region: K2 over the pixel region (x0, y0, x1, y1), the bands of 8 rows with index % band_count == band_index."""
+        arr = (C.c_void_p * len(part_ptrs))(*part_ptrs)
+        r = np.ascontiguousarray(rects, np.uint32).reshape(-1)
+        assert r.size == 4 * len(part_ptrs)
+        g = np.ascontiguousarray(region, np.uint32)
+        self._check(lib.vr_composite_region(self._h, arr, _ptr(r), len(part_ptrs), _ptr(g), band_index, band_count, out_ptr, stream))
+
     def partition_screen_rect(self, full_dims, org, dims):
         """vr_partition_screen_rect: pixels (x0, y0, x1, y1) the rays through that sub-box can cover under the current camera."""
         f, o, d = (np.asarray(x, np.uint32) for x in (full_dims, org, dims))
@@ -639,6 +647,15 @@ def nrrd_spacing(path: str) -> np.ndarray:
     if rc != _lib.VR_OK:
         raise VrError(rc, err.value.decode())
     return out
+
+
+def sort_last_region(rects, width: int, height: int, first_into_slot: bool, slot_region: np.ndarray):
+    """vr_sort_last_region: the region a sort-last frame has to merge into an image slot; slot_region (uint32[4]) is updated."""
+    r = np.ascontiguousarray(rects, np.uint32).reshape(-1)
+    assert slot_region.dtype == np.uint32 and slot_region.size == 4 and slot_region.flags.c_contiguous
+    out = np.zeros(4, np.uint32)
+    lib.vr_sort_last_region(_ptr(r), r.size // 4, width, height, int(first_into_slot), _ptr(slot_region), _ptr(out))
+    return tuple(int(x) for x in out)
 
 
 def minmax_static(device: int, dev_values: int, dtype: int, count: int, dev_min_max: int, stream: int | None = None):
