@@ -19,9 +19,13 @@
 
 #include <algorithm>
 #include <array>
+#include <atomic>
+#include <condition_variable>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "vr_ctx.h"
@@ -47,6 +51,27 @@ struct vr_group {
     uint32_t margin[3] = {0, 0, 0};
     float cam_pos[3] = {0, -3, 0};
     std::string err;
+    /* One worker thread per rank enqueues that rank's part of a frame (above two ranks: a frame is ~20 API calls per rank,
+     * and one thread issuing them for eight devices takes longer than the GPUs need for the frame).  A frame is two
+     * phases with a host barrier between them, because cudaStreamWaitEvent waits for the record made LAST when it is
+     * called: every rank's "ready" event must have been recorded (phase 1) before anyone waits on it (phase 2). */
+    std::vector<std::thread> workers;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::atomic<uint64_t> ticket{0};
+    std::atomic<uint32_t> done{0};
+    int phase = 0; /* 1 march, 2 merge, -1 quit */
+    struct Job {
+        uint64_t k = 0;
+        uint32_t s = 0;
+        const void *const *parts = nullptr;
+        const uint32_t *rects = nullptr;
+        uint32_t region[4] = {0, 0, 0, 0};
+    } job;
+    std::vector<int> wrc;
+    std::vector<std::string> werr;
+    cudaStream_t join = nullptr;            /* display rank: joins the ranks' "ready" events into all_ready[slot] */
+    std::vector<cudaEvent_t> all_ready;
 };
 
 namespace
@@ -156,9 +181,106 @@ extern "C" const char *vr_group_last_error(const vr_group *g) { return g ? g->er
 extern "C" uint32_t vr_group_size(const vr_group *g) { return g ? g->n : 0; }
 extern "C" vr_ctx *vr_group_context(vr_group *g, uint32_t rank) { return (g && rank < g->n) ? g->ctx[rank] : nullptr; }
 
+namespace
+{
+/* what rank r enqueues in a phase of frame k; returns a status, the message in *err */
+int rank_phase(vr_group *g, uint32_t r, int phase, std::string *err)
+{
+    const uint64_t k = g->job.k;
+    const uint32_t S = g->slots, s = g->job.s, n = g->n;
+    auto cu = [&](cudaError_t e, const char *what) {
+        if (e == cudaSuccess) return true;
+        *err = std::string(what) + ": " + cudaGetErrorString(e);
+        return false;
+    };
+    auto vr = [&](int rc) {
+        if (rc == VR_OK) return true;
+        *err = std::string("rank ") + std::to_string(r) + ": " + vr_last_error(g->ctx[r]);
+        return false;
+    };
+    if (!cu(cudaSetDevice(g->dev[r]), "cudaSetDevice")) return VR_ERR_CUDA;
+    if (phase == 1) {
+        /* the slot is free again: frame k - S has been presented out of the image slot (sort-first), every rank has merged
+         * my partial of it (sort-last: `consumed` is recorded behind all the `merged` events) */
+        if (k >= S && !cu(cudaStreamWaitEvent(g->march[r], g->consumed[s], 0), "cudaStreamWaitEvent")) return VR_ERR_CUDA;
+        const int rc = vr_render_frame(g->ctx[r], s, g->march[r]);
+        if (!vr(rc)) return rc;
+        if (!cu(cudaEventRecord(g->ready[r][s], g->march[r]), "cudaEventRecord")) return VR_ERR_CUDA;
+        return VR_OK;
+    }
+    /* phase 2, sort-last: every partial of frame k complete, image slot s presented, then K2 on my bands of the region */
+    if (!cu(cudaStreamWaitEvent(g->merge[r], g->all_ready[s], 0), "cudaStreamWaitEvent")) return VR_ERR_CUDA;
+    if (k >= S && !cu(cudaStreamWaitEvent(g->merge[r], g->consumed[s], 0), "cudaStreamWaitEvent")) return VR_ERR_CUDA;
+    const int rc = vr_composite_region(g->ctx[r], g->job.parts, g->job.rects, n, g->job.region, r, n, g->image_slot[s], g->merge[r]);
+    if (!vr(rc)) return rc;
+    if (!cu(cudaEventRecord(g->merged[r][s], g->merge[r]), "cudaEventRecord")) return VR_ERR_CUDA;
+    return VR_OK;
+}
+
+void worker_main(vr_group *g, uint32_t r)
+{
+    uint64_t seen = 0;
+    for (;;) {
+        int spins = 0;
+        while (g->ticket.load(std::memory_order_acquire) == seen) {
+            if (++spins < 4000) {
+                std::this_thread::yield();
+            } else { /* idle: sleep until the next frame */
+                std::unique_lock<std::mutex> lk(g->mu);
+                g->cv.wait(lk, [&] { return g->ticket.load(std::memory_order_acquire) != seen; });
+            }
+        }
+        seen = g->ticket.load(std::memory_order_acquire);
+        const int phase = g->phase;
+        if (phase < 0) return;
+        g->wrc[r] = rank_phase(g, r, phase, &g->werr[r]);
+        g->done.fetch_add(1, std::memory_order_release);
+    }
+}
+
+/* run a phase on every rank: on the workers when there are any, else inline; first failure wins */
+int run_phase(vr_group *g, int phase)
+{
+    const uint32_t n = g->n;
+    if (g->workers.empty()) {
+        for (uint32_t r = 0; r < n; r++) {
+            std::string err;
+            const int rc = rank_phase(g, r, phase, &err);
+            if (rc != VR_OK) return gfail(g, rc, err);
+        }
+        return VR_OK;
+    }
+    g->done.store(0, std::memory_order_relaxed);
+    {
+        std::lock_guard<std::mutex> lk(g->mu);
+        g->phase = phase;
+        g->ticket.fetch_add(1, std::memory_order_release);
+    }
+    g->cv.notify_all();
+    while (g->done.load(std::memory_order_acquire) < n) std::this_thread::yield();
+    for (uint32_t r = 0; r < n; r++)
+        if (g->wrc[r] != VR_OK) return gfail(g, g->wrc[r], g->werr[r]);
+    return VR_OK;
+}
+
+void stop_workers(vr_group *g)
+{
+    if (g->workers.empty()) return;
+    {
+        std::lock_guard<std::mutex> lk(g->mu);
+        g->phase = -1;
+        g->ticket.fetch_add(1, std::memory_order_release);
+    }
+    g->cv.notify_all();
+    for (auto &t : g->workers) t.join();
+    g->workers.clear();
+}
+}  // namespace
+
 extern "C" int vr_group_destroy(vr_group *g)
 {
     if (!g) return VR_OK;
+    stop_workers(g);
     for (uint32_t r = 0; r < g->ctx.size(); r++) {
         cudaSetDevice(g->dev[r]);
         cudaDeviceSynchronize();
@@ -172,7 +294,9 @@ extern "C" int vr_group_destroy(vr_group *g)
     }
     if (!g->dev.empty()) cudaSetDevice(g->dev[0]);
     for (auto &e : g->consumed) cudaEventDestroy(e);
+    for (auto &e : g->all_ready) cudaEventDestroy(e);
     if (g->present) cudaStreamDestroy(g->present);
+    if (g->join) cudaStreamDestroy(g->join);
     for (auto *c : g->ctx) vr_destroy(c);
     delete g;
     return VR_OK;
@@ -231,9 +355,21 @@ extern "C" int vr_create_group(uint32_t ndev, const int *devs, int partition, ui
     g->consumed.assign(g->slots, nullptr);
     for (uint32_t s = 0; s < g->slots; s++)
         if (cudaEventCreateWithFlags(&g->consumed[s], cudaEventDisableTiming) != cudaSuccess) return bail(VR_ERR_CUDA, "vr_create_group: cudaEventCreate failed");
+    if (cudaStreamCreateWithFlags(&g->join, cudaStreamNonBlocking) != cudaSuccess) return bail(VR_ERR_CUDA, "vr_create_group: cudaStreamCreate failed");
+    g->all_ready.assign(g->slots, nullptr);
+    for (uint32_t s = 0; s < g->slots; s++)
+        if (cudaEventCreateWithFlags(&g->all_ready[s], cudaEventDisableTiming) != cudaSuccess) return bail(VR_ERR_CUDA, "vr_create_group: cudaEventCreate failed");
     if (partition == VR_PARTITION_SORT_FIRST) {
         const int rc = wire(g);
         if (rc != VR_OK) return bail(rc, g->err);
+    }
+    g->wrc.assign(ndev, VR_OK), g->werr.assign(ndev, std::string());
+    if (ndev > 2 && partition != VR_PARTITION_REPLICAS) {
+        try {
+            for (uint32_t r = 0; r < ndev; r++) g->workers.emplace_back(worker_main, g, r);
+        } catch (...) {
+            return bail(VR_ERR_NOMEM, "vr_create_group: cannot start the worker threads");
+        }
     }
     *out = g;
     return VR_OK;
@@ -339,13 +475,11 @@ extern "C" int vr_group_render(vr_group *g)
         g->frame++;
         return VR_OK;
     }
+    g->job.k = k, g->job.s = s;
     if (g->partition == VR_PARTITION_SORT_FIRST) {
-        for (uint32_t r = 0; r < n; r++) {
-            G_CUDA(g, cudaSetDevice(g->dev[r]));
-            if (k >= S) G_CUDA(g, cudaStreamWaitEvent(g->march[r], g->consumed[s], 0)); /* frame k - S has left image slot s */
-            G_VR(g, r, vr_render_frame(g->ctx[r], s, g->march[r]));                      /* tiles straight into the display rank's slot */
-            G_CUDA(g, cudaEventRecord(g->ready[r][s], g->march[r]));
-        }
+        /* every rank: slot free -> K1 (tiles straight into the display rank's slot) -> ready */
+        const int rc = run_phase(g, 1);
+        if (rc != VR_OK) return rc;
         G_CUDA(g, cudaSetDevice(g->dev[0]));
         for (uint32_t r = 0; r < n; r++) G_CUDA(g, cudaStreamWaitEvent(g->present, g->ready[r][s], 0));
         G_CUDA(g, cudaEventRecord(g->consumed[s], g->present)); /* the frame is complete (a consumer would read it here) */
@@ -373,26 +507,23 @@ extern "C" int vr_group_render(vr_group *g)
         if (vr_partition_screen_rect(g->ctx[0], g->full, &g->box[b][0], &g->box[b][3], &rects[4 * i]) != VR_OK)
             return gfail(g, VR_ERR_INVALID, "vr_partition_screen_rect failed");
     }
-    for (uint32_t r = 0; r < n; r++) {
-        G_CUDA(g, cudaSetDevice(g->dev[r]));
-        if (k >= S)
-            for (uint32_t q = 0; q < n; q++) G_CUDA(g, cudaStreamWaitEvent(g->march[r], g->merged[q][s], 0)); /* everyone has merged my partial of frame k - S */
-        G_VR(g, r, vr_render_frame(g->ctx[r], s, g->march[r]));
-        G_CUDA(g, cudaEventRecord(g->ready[r][s], g->march[r]));
-    }
+    /* phase 1, every rank: partial slot free -> K1 -> ready */
+    int rc = run_phase(g, 1);
+    if (rc != VR_OK) return rc;
+    /* the ranks' ready events joined into one (a rank then waits on one event instead of n) */
+    G_CUDA(g, cudaSetDevice(g->dev[0]));
+    for (uint32_t r = 0; r < n; r++) G_CUDA(g, cudaStreamWaitEvent(g->join, g->ready[r][s], 0));
+    G_CUDA(g, cudaEventRecord(g->all_ready[s], g->join));
     /* only the region that can differ from the clear colour is merged, in bands of 8 rows dealt to the ranks */
     if (g->slot_region.size() != S) g->slot_region.assign(S, {});
-    uint32_t region[4];
-    vr_sort_last_region(rects.data(), n, g->W, g->H, k < S, g->slot_region[s].data(), region);
+    vr_sort_last_region(rects.data(), n, g->W, g->H, k < S, g->slot_region[s].data(), g->job.region);
     std::vector<const void *> parts(n);
     for (uint32_t i = 0; i < n; i++) parts[i] = g->raw_slot[order[i]][s];
-    for (uint32_t r = 0; r < n; r++) {
-        G_CUDA(g, cudaSetDevice(g->dev[r]));
-        for (uint32_t q = 0; q < n; q++) G_CUDA(g, cudaStreamWaitEvent(g->merge[r], g->ready[q][s], 0));
-        if (k >= S) G_CUDA(g, cudaStreamWaitEvent(g->merge[r], g->consumed[s], 0));
-        G_VR(g, r, vr_composite_region(g->ctx[r], parts.data(), rects.data(), n, region, r, n, g->image_slot[s], g->merge[r]));
-        G_CUDA(g, cudaEventRecord(g->merged[r][s], g->merge[r]));
-    }
+    g->job.parts = parts.data(), g->job.rects = rects.data();
+    /* phase 2, every rank: all partials ready, image slot presented -> K2 -> merged */
+    rc = run_phase(g, 2);
+    g->job.parts = nullptr, g->job.rects = nullptr;
+    if (rc != VR_OK) return rc;
     G_CUDA(g, cudaSetDevice(g->dev[0]));
     for (uint32_t r = 0; r < n; r++) G_CUDA(g, cudaStreamWaitEvent(g->present, g->merged[r][s], 0));
     G_CUDA(g, cudaEventRecord(g->consumed[s], g->present));
