@@ -678,6 +678,34 @@ def measure_partitioned(vr, mode, rank, world, local, n, W, H, K, Wu, synth=None
     return out
 
 
+def measure_group(vr, world, mode, n, W, H, K, slots):
+    """The same partitioned workload through the ONE-PROCESS host (vr_create_group, csrc/group.cu: a context per device,
+    frames handed between the devices by CUDA events, one worker thread per rank) -- called on rank 0 only, which drives all
+    `world` devices of the box while the other ranks wait.  Wall clock around K frames enqueued back to back + one sync."""
+    import numpy as np
+    part = vr.PARTITION_SORT_FIRST if mode == "first" else vr.PARTITION_SORT_LAST
+    g = vr.PassGroup(list(range(world)), part, W, H, slots)
+    try:
+        g.set_options(sampler=vr.SAMPLER_HW, empty_skip=1, early_term=1, early_term_eps=1.0 / 1024.0)
+        g.synth_volume(vr.SYNTH_FBM, 0x5EED0004, vr.U16, n)
+        g.transfer_function_changed(product_lut(vr, "B"))
+        frames = partitioned_frames(vr, W, H)
+        for k in range(6):
+            g.set_uniforms(*frames[k % 36])
+            g.record()
+        g.sync()
+        t0 = time.perf_counter()
+        for k in range(K):
+            g.set_uniforms(*frames[k % 36])
+            g.record()
+        g.sync()
+        dt = (time.perf_counter() - t0) / K
+        img = g.download()
+        return {"n_gpus": world, "ms_per_step": dt * 1e3, "steps": K, "frame_checksum": int(img.astype(np.int64).sum()), "slots": slots}
+    finally:
+        g.close()
+
+
 def partitioned_record(vr, rank, world, local, args):
     """The evidence for BASELINE.json's partitioned configs inside the driver's own run.
     world == 1: the single-GPU times (the denominators of the curve).  world > 1: the correctness check of
@@ -729,6 +757,32 @@ def partitioned_record(vr, rank, world, local, args):
         elif world == 1:
             rec["sort_last_2048"] = {"n_gpus": 1, "ms_per_step": n1_4k, "n1_ms_per_step": n1_4k, "efficiency": 1.0,
                                      "workload": f"{n}^3 u16 fBm, 3840x2160 on one GPU (the denominator of the sort-last curve)"}
+        if world > 1 and time_left() > 120:
+            # the one-process host on the same devices (rank 0 drives them all; the other ranks have released their volumes)
+            import gc
+            gc.collect()
+            torch.cuda.empty_cache()
+            torch.cuda.synchronize()
+            # the other ranks must wait on the HOST: an NCCL barrier is a kernel spinning on their GPUs, which rank 0's
+            # kernels on those GPUs would be time-sliced against
+            host_group = dist.new_group(backend="gloo")
+            dist.barrier(group=host_group)
+            grp = {"what": "vr_create_group from rank 0 alone: one process, a context per device, CUDA events between the devices, a worker thread per rank; "
+                           "same volume, orbit and frame sizes as c4 / sort_last_2048 above"}
+            if rank == 0:
+                try:
+                    gf = measure_group(vr, world, "first", n, 7680, 4320, 72, args.slots)
+                    gf["n1_ms_per_step"] = n1
+                    gf["efficiency"] = (n1 / (world * gf["ms_per_step"])) if n1 else None
+                    grp["c4"] = gf
+                    gl = measure_group(vr, world, "last", n, 3840, 2160, 72, args.slots_last)
+                    gl["n1_ms_per_step"] = n1_4k
+                    gl["efficiency"] = (n1_4k / (world * gl["ms_per_step"])) if n1_4k else None
+                    grp["sort_last_2048"] = gl
+                except Exception as e:  # noqa: BLE001
+                    grp["error"] = f"{type(e).__name__}: {e}"
+            dist.barrier(group=host_group)
+            rec["group"] = grp
         if world == 8 and not args.size and time_left() > 200:
             c5 = measure_partitioned(vr, "last", rank, world, local, 4096, 3840, 2160, K, Wu, synth=(vr.SYNTH_BLOBS_FBM, 0x5EED0005), tf="C",
                                      ess=int(not args.no_ess), ert=int(not args.no_ert), slots=args.slots_last, balance=args.balance)
