@@ -587,3 +587,17 @@ def test_sort_last_merge_region(vr):
     assert tuple(slot) == (0, 0, 0, 0)
     assert vr.sort_last_region([(0, 0, 0, 0)], 640, 480, False, slot) == (0, 0, 0, 0)          # nothing before, nothing now
     assert vr.sort_last_region(b, 640, 480, False, slot) == (120, 40, 220, 300)
+
+
+def test_abi_header_is_plain_c(tmp_path):
+    """include/vr.h is the drop-in boundary: it must compile as C99 on its own (no C++, no CUDA, no torch types in it)."""
+    import subprocess
+    src = tmp_path / "t.c"
+    src.write_text('#include "vr.h"\nint main(void) { vr_options o; vr_frame_info f; vr_sort_last_wiring w; (void)o; (void)f; (void)w; return VR_ABI_VERSION == 2 ? 0 : 1; }\n')
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-I", os.path.join(ROOT, "include"), str(src)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    import re
+    hdr = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "vr.h")).read(), flags=re.S)   # declarations only
+    for word in ("torch", "cudaStream_t", "std::", "Tensor", "#include <cuda"):
+        assert word not in hdr, word
