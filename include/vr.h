@@ -506,6 +506,10 @@ int vr_stream_signal(vr_ctx *ctx, void *const *flags, uint32_t n, uint32_t value
 /* Hold the stream until the n <= 256 consecutive LOCAL counters at `flags` have all reached `value`
  * (counters only grow).  After timeout_ms the wait gives up and the next vr_sync fails with VR_ERR_STATE. */
 int vr_stream_wait(vr_ctx *ctx, const void *flags, uint32_t n, uint32_t value, uint32_t timeout_ms, void *cuda_stream);
+/* 1 when the two calls above use the driver's stream memory operations (cuStreamWaitValue32 / cuStreamWriteValue32:
+ * environment VR_SYNC_MEMOPS=1, an experiment -- measured equal to the one-warp kernels, and without their time-out)
+ * instead of the kernels. */
+int vr_sync_uses_memops(void);
 /* vr_ipc_export also accepts which = 32 + frame_index: the float4 output of that frame slot (vr_get_raw_frame).
  * vr_set_image_target for any frame in flight; vr_ipc_export accepts which = 16 + frame_index for those
  * targets (allocated on first use). */

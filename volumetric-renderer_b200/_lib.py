@@ -123,6 +123,7 @@ SIGNATURES = {
     "vr_get_flags": (C.c_int, [_P, C.POINTER(_P)]),
     "vr_stream_signal": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, _P]),
     "vr_stream_wait": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32, _P]),
+    "vr_sync_uses_memops": (C.c_int, []),
     "vr_set_image_target_frame": (C.c_int, [_P, C.c_uint32, _P]),
     "vr_ipc_export": (C.c_int, [_P, C.c_int, _P]),
     "vr_ipc_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
